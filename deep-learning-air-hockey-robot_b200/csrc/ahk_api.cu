@@ -1,0 +1,262 @@
+// ahk_api.cu — the C ABI of include/ahk.h: handle management, argument checking, stream-ordered launches.
+// There is no CPU implementation behind these entry points: without a CUDA device ahk_create fails.
+#include "../../include/ahk.h"
+#include "ahk_kernels.cuh"
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <vector>
+
+namespace {
+
+thread_local char g_error[512] = "";
+
+int fail(int code, const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_error, sizeof g_error, fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+#define AHK_CUDA(expr)                                                                                      \
+    do {                                                                                                    \
+        cudaError_t err__ = (expr);                                                                         \
+        if (err__ != cudaSuccess) return fail(AHK_ERR_CUDA, "%s: %s", #expr, cudaGetErrorString(err__));   \
+    } while (0)
+
+} // namespace
+
+struct ahk_env {
+    ahk_config cfg{};
+    ahk_buffers buf{};
+    bool bound = false, table_set = false;
+    uint4 *table_dev = nullptr;      // [3][128][8] vectors
+    uint8_t *action_stage = nullptr; // [2][n] device staging for ahk_step_host
+    cudaStream_t host_stream = nullptr;
+    int head = 0;
+    int raster_grid = 0;
+    uint64_t launches = 0;
+};
+
+namespace {
+
+uint2 key_of(uint64_t seed) { return make_uint2(static_cast<uint32_t>(seed), static_cast<uint32_t>(seed >> 32)); }
+
+int check_ready(const ahk_env *e)
+{
+    if (!e) return fail(AHK_ERR_ARG, "env is NULL");
+    if (!e->bound) return fail(AHK_ERR_STATE, "ahk_bind_buffers has not been called");
+    if (!e->table_set) return fail(AHK_ERR_STATE, "ahk_set_table_image has not been called");
+    return AHK_OK;
+}
+
+ahk::EnvArgs env_args(const ahk_env *e)
+{
+    ahk::EnvArgs a{};
+    a.state = e->buf.state;
+    a.drawlist = e->buf.drawlist;
+    a.reward = e->buf.reward;
+    a.done = e->buf.done;
+    a.robot_label = e->buf.robot_label;
+    a.human_label = e->buf.human_label;
+    a.info = e->buf.info;
+    a.stats = e->buf.stats;
+    a.key = key_of(e->cfg.seed);
+    a.env_id_base = e->cfg.env_id_base;
+    a.n = e->cfg.n_envs;
+    a.auto_reset = e->cfg.auto_reset;
+    a.max_episode_steps = e->cfg.max_episode_steps;
+    return a;
+}
+
+int raster(ahk_env *e, cudaStream_t s)
+{
+    ahk::RasterArgs r{};
+    r.drawlist = e->buf.drawlist;
+    r.table = e->table_dev;
+    r.frames = e->buf.frames;
+    r.key = key_of(e->cfg.seed);
+    r.env_id_base = e->cfg.env_id_base;
+    r.n = e->cfg.n_envs;
+    r.head = e->head;
+    AHK_CUDA(ahk::launch_raster(r, e->raster_grid, s));
+    e->launches += 1;
+    return AHK_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+const char *ahk_last_error(void) { return g_error; }
+const char *ahk_version(void) { return "ahk 0.1 (sm_100a)"; }
+
+int ahk_create(const ahk_config *cfg, ahk_env **out)
+{
+    if (!cfg || !out) return fail(AHK_ERR_ARG, "cfg/out is NULL");
+    if (cfg->n_envs <= 0) return fail(AHK_ERR_ARG, "n_envs must be positive, got %d", cfg->n_envs);
+    if (cfg->max_episode_steps < 0 || cfg->max_episode_steps > 65535)
+        return fail(AHK_ERR_ARG, "max_episode_steps must be in [0, 65535], got %d", cfg->max_episode_steps);
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0)
+        return fail(AHK_ERR_NO_DEVICE, "no CUDA device: this engine has no CPU fallback");
+    if (cfg->device < 0 || cfg->device >= count) return fail(AHK_ERR_ARG, "device %d out of range [0, %d)", cfg->device, count);
+    AHK_CUDA(cudaSetDevice(cfg->device));
+    cudaDeviceProp prop{};
+    AHK_CUDA(cudaGetDeviceProperties(&prop, cfg->device));
+    if (prop.major < 10) return fail(AHK_ERR_NO_DEVICE, "device %d is sm_%d%d; this library is built for sm_100a only", cfg->device, prop.major, prop.minor);
+
+    ahk_env *e = new (std::nothrow) ahk_env();
+    if (!e) return fail(AHK_ERR_ARG, "out of host memory");
+    e->cfg = *cfg;
+    int per_sm = 2;
+    if (const char *s = getenv("AHK_RASTER_CTAS_PER_SM")) per_sm = atoi(s) > 0 ? atoi(s) : per_sm;
+    e->raster_grid = prop.multiProcessorCount * per_sm;
+    cudaError_t err = cudaMalloc(&e->table_dev, ahk::kFrameBytes);
+    if (err == cudaSuccess) err = cudaMalloc(&e->action_stage, 2 * static_cast<size_t>(cfg->n_envs));
+    if (err == cudaSuccess) err = cudaStreamCreateWithFlags(&e->host_stream, cudaStreamNonBlocking);
+    if (err == cudaSuccess) err = ahk::raster_prepare();
+    if (err != cudaSuccess) {
+        ahk_destroy(e);
+        return fail(AHK_ERR_CUDA, "ahk_create: %s", cudaGetErrorString(err));
+    }
+    *out = e;
+    return AHK_OK;
+}
+
+void ahk_destroy(ahk_env *e)
+{
+    if (!e) return;
+    cudaSetDevice(e->cfg.device);
+    if (e->table_dev) cudaFree(e->table_dev);
+    if (e->action_stage) cudaFree(e->action_stage);
+    if (e->host_stream) cudaStreamDestroy(e->host_stream);
+    delete e;
+}
+
+int ahk_set_table_image(ahk_env *e, const uint8_t *rgb, int height, int width)
+{
+    if (!e || !rgb) return fail(AHK_ERR_ARG, "env/rgb is NULL");
+    if (height != AHK_TABLE_H || width != AHK_TABLE_W)
+        return fail(AHK_ERR_ARG, "table image must be %dx%d (HxW), got %dx%d", AHK_TABLE_H, AHK_TABLE_W, height, width);
+    // Image.resize((128,128), NEAREST) + transpose(2,0,1) of the static layer (processor.py:34-36)
+    std::vector<uint8_t> chw(ahk::kFrameBytes);
+    for (int i = 0; i < ahk::kDim; ++i) {
+        const int y = ((2 * i + 1) * height) >> 8;
+        for (int j = 0; j < ahk::kDim; ++j) {
+            const int x = ((2 * j + 1) * width) >> 8;
+            const uint8_t *p = rgb + (static_cast<size_t>(y) * width + x) * 3;
+            for (int c = 0; c < 3; ++c) chw[(c * ahk::kDim + i) * ahk::kDim + j] = p[c];
+        }
+    }
+    AHK_CUDA(cudaSetDevice(e->cfg.device));
+    AHK_CUDA(cudaMemcpy(e->table_dev, chw.data(), chw.size(), cudaMemcpyHostToDevice));
+    e->table_set = true;
+    return AHK_OK;
+}
+
+int ahk_bind_buffers(ahk_env *e, const ahk_buffers *b)
+{
+    if (!e || !b) return fail(AHK_ERR_ARG, "env/bufs is NULL");
+    if (!b->state || !b->frames || !b->reward || !b->done || !b->robot_label || !b->human_label || !b->info || !b->drawlist)
+        return fail(AHK_ERR_ARG, "every buffer except stats must be non-NULL");
+    if ((reinterpret_cast<uintptr_t>(b->frames) | reinterpret_cast<uintptr_t>(b->drawlist)) & 15u)
+        return fail(AHK_ERR_ARG, "frames and drawlist must be 16-byte aligned");
+    e->buf = *b;
+    e->bound = true;
+    return AHK_OK;
+}
+
+int ahk_reset(ahk_env *e, const uint8_t *mask, const uint8_t *episode, const uint8_t *use, void *stream)
+{
+    if (int rc = check_ready(e)) return rc;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    ahk::EnvArgs a = env_args(e);
+    a.reset_mask = mask;
+    a.episode_override = episode;
+    a.use_override = use;
+    AHK_CUDA(ahk::launch_env(a, false, s));
+    e->launches += 1;
+    return raster(e, s);
+}
+
+int ahk_step(ahk_env *e, const uint8_t *robot, const uint8_t *human, void *stream)
+{
+    if (int rc = check_ready(e)) return rc;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    ahk::EnvArgs a = env_args(e);
+    a.robot = robot;
+    a.human = human;
+    e->head = (e->head + 1) % 3;
+    AHK_CUDA(ahk::launch_env(a, true, s));
+    e->launches += 1;
+    return raster(e, s);
+}
+
+int ahk_step_host(ahk_env *e, const uint8_t *robot, const uint8_t *human, float *reward, uint8_t *done,
+                  uint8_t *robot_label, uint8_t *human_label, uint8_t *frame)
+{
+    if (int rc = check_ready(e)) return rc;
+    AHK_CUDA(cudaSetDevice(e->cfg.device));
+    cudaStream_t s = e->host_stream;
+    const size_t n = static_cast<size_t>(e->cfg.n_envs);
+    uint8_t *robot_dev = nullptr, *human_dev = nullptr;
+    if (robot) { robot_dev = e->action_stage; AHK_CUDA(cudaMemcpyAsync(robot_dev, robot, n, cudaMemcpyHostToDevice, s)); }
+    if (human) { human_dev = e->action_stage + n; AHK_CUDA(cudaMemcpyAsync(human_dev, human, n, cudaMemcpyHostToDevice, s)); }
+    if (int rc = ahk_step(e, robot_dev, human_dev, s)) return rc;
+    if (reward) AHK_CUDA(cudaMemcpyAsync(reward, e->buf.reward, n * sizeof(float), cudaMemcpyDeviceToHost, s));
+    if (done) AHK_CUDA(cudaMemcpyAsync(done, e->buf.done, n, cudaMemcpyDeviceToHost, s));
+    if (robot_label) AHK_CUDA(cudaMemcpyAsync(robot_label, e->buf.robot_label, n, cudaMemcpyDeviceToHost, s));
+    if (human_label) AHK_CUDA(cudaMemcpyAsync(human_label, e->buf.human_label, n, cudaMemcpyDeviceToHost, s));
+    if (frame)
+        AHK_CUDA(cudaMemcpyAsync(frame, e->buf.frames + static_cast<size_t>(e->head) * n * ahk::kFrameBytes,
+                                 n * ahk::kFrameBytes, cudaMemcpyDeviceToHost, s));
+    AHK_CUDA(cudaStreamSynchronize(s));
+    return AHK_OK;
+}
+
+int ahk_observe(ahk_env *e, int format, void *out, void *stream)
+{
+    if (int rc = check_ready(e)) return rc;
+    if (!out) return fail(AHK_ERR_ARG, "out is NULL");
+    if (format < AHK_OBS_U8 || format > AHK_OBS_GRAY_DIFF_F64) return fail(AHK_ERR_ARG, "Processing mode is not supported");
+    ahk::ObserveArgs a{e->buf.frames, out, e->cfg.n_envs, e->head, format};
+    const size_t work = static_cast<size_t>(e->cfg.n_envs) * (format == AHK_OBS_GRAY_DIFF_F64 ? 1024 : 3 * ahk::kFrameVecs);
+    size_t grid = (work + 255) / 256;
+    if (grid > static_cast<size_t>(e->raster_grid) * 16) grid = static_cast<size_t>(e->raster_grid) * 16;
+    AHK_CUDA(ahk::launch_observe(a, static_cast<int>(grid), static_cast<cudaStream_t>(stream)));
+    e->launches += 1;
+    return AHK_OK;
+}
+
+int ahk_head(const ahk_env *e) { return e ? e->head : fail(AHK_ERR_ARG, "env is NULL"); }
+
+int ahk_set_head(ahk_env *e, int head)
+{
+    if (!e || head < 0 || head > 2) return fail(AHK_ERR_ARG, "head must be 0, 1 or 2");
+    e->head = head;
+    return AHK_OK;
+}
+
+int ahk_set_pending(ahk_env *e, const uint8_t *pending, void *stream)
+{
+    if (int rc = check_ready(e)) return rc;
+    if (!pending) return fail(AHK_ERR_ARG, "pending is NULL");
+    AHK_CUDA(ahk::launch_set_pending(e->buf.state, pending, e->cfg.n_envs, static_cast<cudaStream_t>(stream)));
+    e->launches += 1;
+    return AHK_OK;
+}
+
+int ahk_launch_count(const ahk_env *e, uint64_t *kernels)
+{
+    if (!e || !kernels) return fail(AHK_ERR_ARG, "env/kernels is NULL");
+    *kernels = e->launches;
+    return AHK_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,49 @@
+// ahk_kernels.cuh — kernel argument blocks and launchers shared by ahk_kernels.cu and ahk_api.cu.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+
+namespace ahk {
+
+constexpr int kTableW = 450, kTableH = 700; // native frame (SPEC.md §2)
+constexpr int kDim = 128;                   // processor.py:5
+constexpr int kFrameBytes = 3 * kDim * kDim;
+constexpr int kFrameVecs = kFrameBytes / 16; // 3072 128-bit vectors per frame
+constexpr int kEnvThreads = 128;
+constexpr int kRasterThreads = 256;
+
+struct EnvArgs {
+    uint32_t *state;   // [16][n]
+    uint32_t *drawlist; // [3][n][4]
+    float *reward;
+    uint8_t *done, *robot_label, *human_label, *info;
+    uint64_t *stats;
+    const uint8_t *robot, *human;                          // step: action labels or nullptr
+    const uint8_t *reset_mask, *episode_override, *use_override; // reset
+    uint2 key;
+    uint32_t env_id_base;
+    int n, auto_reset, max_episode_steps;
+};
+
+struct RasterArgs {
+    const uint32_t *drawlist;
+    const uint4 *table; // [3][128][8] vectors: the table image at the 128x128 sample points, CHW
+    uint8_t *frames;    // [3][n][3][128][128]
+    uint2 key;
+    uint32_t env_id_base;
+    int n, head;
+};
+
+struct ObserveArgs {
+    const uint8_t *frames;
+    void *out;
+    int n, head, format;
+};
+
+cudaError_t launch_env(const EnvArgs &a, bool step, cudaStream_t stream);
+cudaError_t raster_prepare();
+cudaError_t launch_raster(const RasterArgs &a, int grid, cudaStream_t stream);
+cudaError_t launch_observe(const ObserveArgs &a, int grid, cudaStream_t stream);
+cudaError_t launch_set_pending(uint32_t *state, const uint8_t *pending, int n, cudaStream_t stream);
+
+} // namespace ahk

@@ -1,0 +1,88 @@
+"""ctypes binding of lib/libahk.so (the C ABI in include/ahk.h).
+
+There is deliberately no fallback: if the CUDA library is missing or fails to load, importing the engine raises.
+"""
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(os.path.dirname(HERE), "lib", "libahk.so")
+
+ACT_NONE = 255
+EP_NORMAL, EP_MISSING, EP_RANDOM, EP_SAMPLE = 0, 1, 2, 255
+USE_ARM, USE_PUCK, USE_TOP_MALLET, USE_ALL = 1, 2, 4, 7
+OBS_U8, OBS_RGB_F32, OBS_GRAY_DIFF_F64 = 0, 1, 2
+STATE_WORDS, STATS_WORDS, FRAME_BYTES, DIM = 16, 32, 3 * 128 * 128, 128
+
+
+class Config(C.Structure):  # ahk_config
+    _fields_ = [("n_envs", C.c_int32), ("device", C.c_int32), ("seed", C.c_uint64), ("env_id_base", C.c_uint32),
+                ("auto_reset", C.c_int32), ("max_episode_steps", C.c_int32), ("reserved", C.c_int32 * 5)]
+
+
+class Buffers(C.Structure):  # ahk_buffers
+    _fields_ = [(name, C.c_void_p) for name in
+                ("state", "frames", "reward", "done", "robot_label", "human_label", "info", "stats", "drawlist")]
+
+
+class PolicyWeights(C.Structure):  # ahk_policy_weights
+    NAMES = ("conv1_w", "conv1_b", "bn1_gamma", "bn1_beta", "bn1_mean", "bn1_var",
+             "conv2_w", "conv2_b", "bn2_gamma", "bn2_beta", "bn2_mean", "bn2_var",
+             "conv3_w", "conv3_b", "bn3_gamma", "bn3_beta", "bn3_mean", "bn3_var",
+             "dense1_w", "dense1_b", "dense2_w", "dense2_b", "out_w", "out_b")
+    _fields_ = [(name, C.c_void_p) for name in NAMES]
+
+
+# every symbol include/ahk.h declares: name -> (restype, argtypes)
+_vp, _i = C.c_void_p, C.c_int
+SYMBOLS = {
+    "ahk_create": (_i, [C.POINTER(Config), C.POINTER(_vp)]),
+    "ahk_destroy": (None, [_vp]),
+    "ahk_set_table_image": (_i, [_vp, _vp, _i, _i]),
+    "ahk_bind_buffers": (_i, [_vp, C.POINTER(Buffers)]),
+    "ahk_reset": (_i, [_vp, _vp, _vp, _vp, _vp]),
+    "ahk_step": (_i, [_vp, _vp, _vp, _vp]),
+    "ahk_step_host": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "ahk_observe": (_i, [_vp, _i, _vp, _vp]),
+    "ahk_head": (_i, [_vp]),
+    "ahk_set_head": (_i, [_vp, _i]),
+    "ahk_set_pending": (_i, [_vp, _vp, _vp]),
+    "ahk_launch_count": (_i, [_vp, C.POINTER(C.c_uint64)]),
+    "ahk_last_error": (C.c_char_p, []),
+    "ahk_version": (C.c_char_p, []),
+    "ahk_policy_create": (_i, [_i, _i, C.POINTER(PolicyWeights), C.POINTER(_vp)]),
+    "ahk_policy_destroy": (None, [_vp]),
+    "ahk_policy_forward": (_i, [_vp, _vp, _i, _i, _vp, _vp, _vp]),
+}
+
+_lib = None
+
+
+def load():
+    """Load libahk.so and declare its signatures.  Raises if the library is absent: no fallback exists."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            "%s is missing: build it with `python __graft_entry__.py` (or make -C deep-learning-air-hockey-robot_b200/csrc). "
+            "The engine has no CPU or PyTorch fallback." % LIB_PATH)
+    lib = C.CDLL(LIB_PATH)
+    for name, (restype, argtypes) in SYMBOLS.items():
+        if name.startswith("ahk_policy") and not hasattr(lib, name):
+            continue  # TEMPORARY until ahk_policy.cu lands
+        fn = getattr(lib, name)  # AttributeError if the ABI and the binding disagree
+        fn.restype = restype
+        fn.argtypes = argtypes
+    _lib = lib
+    return lib
+
+
+def check(rc):
+    """Translate an ahk_status into the exception the reference's callers would expect."""
+    if rc == 0:
+        return
+    msg = load().ahk_last_error().decode()
+    if rc == -1:
+        raise ValueError(msg)  # e.g. 'Processing mode is not supported' (processor.py:66)
+    raise RuntimeError("libahk: %s (status %d)" % (msg, rc))

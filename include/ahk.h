@@ -1,0 +1,136 @@
+/*
+ * ahk.h — C ABI of the B200 batched air-hockey environment engine (libahk.so).
+ *
+ * The reference has no native boundary on this path: `ai/supervised/generate_data.py:35-51` and
+ * `ai/reinforcement/train.py:57-96` call the pure-Python gym wrapper
+ * `gym-air-hockey/gym_air_hockey/envs/air_hockey_env.py`, which calls the (missing) pure-Python simulator.
+ * Each entry point below names the reference interface it replaces; INTEGRATION.md shows the ctypes stub a
+ * maintainer of the reference would add.  Plain pointers and sizes only; no exceptions cross this boundary.
+ *
+ * Conventions
+ *   - every function returns AHK_OK (0) or a negative ahk_status; ahk_last_error() gives the text (thread-local).
+ *   - "dev" pointers are CUDA device pointers owned by the caller (PyTorch allocates them), "host" pointers are
+ *     ordinary (ideally pinned) host memory.  The engine allocates nothing on the step path.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream).  Calls are stream-ordered and
+ *     asynchronous unless the name ends in _host.
+ *   - action labels are the reference's 0..9 (`processor.py:7-18`); AHK_ACT_NONE (255) = None = the programmed AI
+ *     plays that side (`air_hockey_env.py:86-89`, `processor.py:74-76`).
+ */
+#ifndef AHK_H
+#define AHK_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define AHK_DIM 128                       /* processor.py:5 */
+#define AHK_FRAME_BYTES (3 * 128 * 128)   /* one CHW uint8 frame */
+#define AHK_TABLE_W 450
+#define AHK_TABLE_H 700
+#define AHK_STATE_WORDS 16                /* SoA words per env, see DESIGN.md "HBM layout" */
+#define AHK_N_ACTIONS 10                  /* air_hockey_env.py:16 */
+#define AHK_ACT_NONE 255
+#define AHK_STATS_WORDS 32
+
+typedef enum {
+    AHK_OK = 0,
+    AHK_ERR_ARG = -1,      /* bad argument (NULL, size, mode) */
+    AHK_ERR_CUDA = -2,     /* a CUDA call failed; text in ahk_last_error() */
+    AHK_ERR_STATE = -3,    /* call order: buffers not bound / table not set */
+    AHK_ERR_NO_DEVICE = -4 /* no CUDA device: there is NO CPU fallback */
+} ahk_status;
+
+enum { AHK_EP_NORMAL = 0, AHK_EP_MISSING = 1, AHK_EP_RANDOM = 2, AHK_EP_SAMPLE = 255 }; /* air_hockey_env.py:28 */
+enum { AHK_USE_ARM = 1, AHK_USE_PUCK = 2, AHK_USE_TOP_MALLET = 4, AHK_USE_ALL = 7 };     /* air_hockey_env.py:32-34 */
+enum { AHK_OBS_U8 = 0, AHK_OBS_RGB_F32 = 1, AHK_OBS_GRAY_DIFF_F64 = 2 };                /* processor.py:52,53-64 */
+
+typedef struct ahk_env ahk_env; /* opaque; one per GPU (one per process) */
+
+typedef struct {
+    int32_t n_envs;            /* environments on THIS device */
+    int32_t device;            /* CUDA ordinal */
+    uint64_t seed;             /* master seed (SPEC.md §4) */
+    uint32_t env_id_base;      /* global id of local env 0: results are independent of sharding */
+    int32_t auto_reset;        /* 1: reset an env at the start of the step after a terminal / max_episode_steps */
+    int32_t max_episode_steps; /* 0 = unlimited; generate_data.py:57 uses 200 */
+    int32_t reserved[5];
+} ahk_config;
+
+/* Device memory the engine works in; all caller-owned (SURVEY.md §8b "Ownership"). */
+typedef struct {
+    uint32_t *state;      /* [AHK_STATE_WORDS][n] SoA: f32 puck x,y,vx,vy | bottom | top | serve,reset,noise counters | meta */
+    uint8_t *frames;      /* [3][n][3][128][128] ring of CHW uint8 frames; slot `head` is the newest */
+    float *reward;        /* [n]  air_hockey_env.py:95-145 */
+    uint8_t *done;        /* [n]  terminal, air_hockey_env.py:90,147-148 */
+    uint8_t *robot_label; /* [n]  info['robot_action'], air_hockey_env.py:92,155 */
+    uint8_t *human_label; /* [n]  info['human_action'] */
+    uint8_t *info;        /* [n]  bit0 puck_was_hit 1 hit_the_border 2 puck_is_at_the_bottom 3 distance_decreased 4 in_the_target, bits5-6 scored (0 none,1 top,2 bottom) */
+    uint64_t *stats;      /* [AHK_STATS_WORDS] running sums: 0 steps, 1 episodes, 2 goals_top, 3 goals_bottom, 4 reward*2 (int64), 5.. robot label hist[10], 15.. human label hist[10] */
+    uint32_t *drawlist;   /* [3][n][4] scratch between the step and raster kernels */
+} ahk_buffers;
+
+/* ≙ AirHockeyEnv.__init__ (air_hockey_env.py:9-24) minus the first reset. */
+int ahk_create(const ahk_config *cfg, ahk_env **out);
+void ahk_destroy(ahk_env *env);
+
+/* ≙ the table sprite the missing simulator loaded.  rgb: host uint8[700][450][3].  The engine keeps the 128x128
+ * NEAREST samples (processor.py:34-35) in device memory and stages them in shared memory per CTA. */
+int ahk_set_table_image(ahk_env *env, const uint8_t *rgb_host, int height, int width);
+
+int ahk_bind_buffers(ahk_env *env, const ahk_buffers *bufs);
+
+/* ≙ AirHockeyEnv.reset (air_hockey_env.py:26-76), batched.  mask_dev [n] (NULL = every env): nonzero = reset.
+ * episode_dev/use_dev [n] (NULL = sample per SPEC.md §4): force the episode type / object mask, AHK_EP_SAMPLE = sample. */
+int ahk_reset(ahk_env *env, const uint8_t *mask_dev, const uint8_t *episode_dev, const uint8_t *use_dev, void *stream);
+
+/* ≙ AirHockeyEnv.step (air_hockey_env.py:84-155), batched: physics + programmed AI + reward/terminal/labels, then the
+ * new frame of every env rasterised into ring slot `head` (advanced first).  robot_dev/human_dev [n] labels or NULL. */
+int ahk_step(ahk_env *env, const uint8_t *robot_dev, const uint8_t *human_dev, void *stream);
+
+/* The same call with HOST buffers, for callers that live on the CPU like the reference's loops do: copies the
+ * actions in, steps, copies reward/done/labels (and, if frame_host != NULL, the new uint8 frame [n][3][128][128])
+ * out, and waits.  Any pointer may be NULL. */
+int ahk_step_host(ahk_env *env, const uint8_t *robot_host, const uint8_t *human_host, float *reward_host,
+                  uint8_t *done_host, uint8_t *robot_label_host, uint8_t *human_label_host, uint8_t *frame_host);
+
+/* ≙ DataProcessor.process_observation's return value (processor.py:52-64) materialised from the ring:
+ * AHK_OBS_U8 uint8[n][9][128][128] newest first; AHK_OBS_RGB_F32 float[n][9][128][128] = (x-128)/128;
+ * AHK_OBS_GRAY_DIFF_F64 double[n][1][128][128]. */
+int ahk_observe(ahk_env *env, int format, void *out_dev, void *stream);
+
+int ahk_head(const ahk_env *env);                 /* ring slot holding the newest frame */
+int ahk_set_head(ahk_env *env, int head);
+int ahk_set_pending(ahk_env *env, const uint8_t *pending_dev, void *stream); /* arm/disarm the auto-reset per env */
+int ahk_launch_count(const ahk_env *env, uint64_t *kernels); /* kernels launched so far by this handle */
+
+const char *ahk_last_error(void);
+const char *ahk_version(void);
+
+/* ---- CNN policy forward (ai/supervised/keras/models.py:20-65, the 'rgb' network; rl_agents.py:78-98) ---- */
+typedef struct {
+    /* BatchNorm (axis=1, eps 1e-3, AFTER the ReLU: models.py:26-29) is passed raw; the engine folds it. All float32, Keras layouts:
+     * conv kernels [kh][kw][cin][cout], dense [in][out]. */
+    const float *conv1_w, *conv1_b, *bn1_gamma, *bn1_beta, *bn1_mean, *bn1_var; /* 8x8x9x5   */
+    const float *conv2_w, *conv2_b, *bn2_gamma, *bn2_beta, *bn2_mean, *bn2_var; /* 4x4x5x32  */
+    const float *conv3_w, *conv3_b, *bn3_gamma, *bn3_beta, *bn3_mean, *bn3_var; /* 4x4x32x64 */
+    const float *dense1_w, *dense1_b; /* 4096x512 */
+    const float *dense2_w, *dense2_b; /* 512x512  */
+    const float *out_w, *out_b;       /* 512x10   */
+} ahk_policy_weights; /* host pointers */
+
+typedef struct ahk_policy ahk_policy;
+int ahk_policy_create(int device, int max_batch, const ahk_policy_weights *w, ahk_policy **out);
+void ahk_policy_destroy(ahk_policy *p);
+/* frames_dev: the ring [3][n][3][128][128]; head: newest slot.  logits_dev float[n][10] (pre-softmax, i.e. the DDQN
+ * linear head of rl_agents.py:160-172; softmax of it is the supervised model's output), action_dev uint8[n] argmax
+ * (either may be NULL). */
+int ahk_policy_forward(ahk_policy *p, const uint8_t *frames_dev, int n, int head, float *logits_dev,
+                       uint8_t *action_dev, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* AHK_H */

@@ -1,0 +1,232 @@
+"""ctypes binding of oracle/libahk_oracle.so — TEST INFRASTRUCTURE (see the header of ahk_oracle.c).
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs import this.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libahk_oracle.so")
+
+W, H, DIM, FRAME = 450, 700, 128, 3 * 128 * 128
+USE_ARM, USE_PUCK, USE_TOP, USE_ALL = 1, 2, 4, 7
+EP_NORMAL, EP_MISSING, EP_RANDOM = 0, 1, 2
+ACT_NONE = 255
+SCORED = {0: None, 1: "top", 2: "bottom"}
+
+
+def build(force=False):
+    src = os.path.join(HERE, "ahk_oracle.c")
+    if force or not os.path.exists(LIB_PATH) or os.path.getmtime(LIB_PATH) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-C", HERE, "-s", "CC=gcc"] + (["-B"] if force else []))
+    return LIB_PATH
+
+
+class Info(C.Structure):  # orc_info
+    _fields_ = [("scored", C.c_int32), ("robot_action", C.c_int8 * 2), ("human_action", C.c_int8 * 2),
+                ("puck_was_hit", C.c_uint8), ("hit_the_border", C.c_uint8), ("puck_is_at_the_bottom", C.c_uint8),
+                ("distance_decreased", C.c_uint8), ("in_the_target", C.c_uint8)]
+
+
+class StepOut(C.Structure):  # orc_step_out
+    _fields_ = [("reward", C.c_float), ("terminal", C.c_uint8), ("robot_label", C.c_uint8),
+                ("human_label", C.c_uint8), ("scored", C.c_uint8), ("flags", C.c_uint8)]
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        build()
+    L = C.CDLL(LIB_PATH)
+    vp, u8p, f32p, u32p = C.c_void_p, C.POINTER(C.c_uint8), C.POINTER(C.c_float), C.POINTER(C.c_uint32)
+    L.orc_philox.argtypes = [u32p, u32p, u32p]
+    L.orc_sizeof_sim.restype = C.c_int
+    L.orc_sim_init.argtypes = [vp, C.c_uint64, C.c_uint32]
+    L.orc_sim_reset.argtypes = [vp]
+    L.orc_sim_step.argtypes = [vp, C.POINTER(C.c_int8), C.POINTER(C.c_int8), C.c_int, C.POINTER(Info)]
+    L.orc_draw.argtypes = [vp, C.c_int, u8p, u8p]
+    L.orc_resize_nearest_chw.argtypes = [u8p, C.c_int, C.c_int, u8p]
+    L.orc_push_frame.argtypes = [f32p, u8p]
+    L.orc_observe_rgb.argtypes = [f32p, f32p]
+    L.orc_observe_gray_diff.argtypes = [f32p, C.POINTER(C.c_double)]
+    L.orc_noise_frame.argtypes = [u32p, C.c_uint32, C.c_uint32, u8p]
+    L.orc_action_to_label.argtypes = [C.POINTER(C.c_int8)]
+    L.orc_action_to_label.restype = C.c_int
+    L.orc_reward.argtypes = [C.c_int, C.POINTER(Info), C.c_int]
+    L.orc_reward.restype = C.c_float
+    L.orc_env_create.argtypes = [C.c_uint64, C.c_uint32, u8p]
+    L.orc_env_create.restype = vp
+    L.orc_env_destroy.argtypes = [vp]
+    L.orc_env_reset.argtypes = [vp, C.c_int, C.c_int]
+    L.orc_env_step.argtypes = [vp, C.c_int, C.c_int, C.POINTER(StepOut)]
+    L.orc_env_step_auto.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.POINTER(StepOut)]
+    L.orc_env_set_pending.argtypes = [vp, C.c_int]
+    L.orc_env_ring.argtypes = [vp]
+    L.orc_env_ring.restype = u8p
+    L.orc_env_native.argtypes = [vp]
+    L.orc_env_native.restype = u8p
+    L.orc_env_sim.argtypes = [vp]
+    L.orc_env_sim.restype = vp
+    L.orc_env_get_state.argtypes = [vp, f32p, u32p]
+    L.orc_env_set_state.argtypes = [vp, f32p, u32p]
+    L.orc_env_observe_rgb.argtypes = [vp, f32p]
+    L.orc_run_batch.argtypes = [C.POINTER(vp), C.c_int, C.c_int, C.c_int, C.c_int, f32p, f32p, u8p, u8p]
+    L.orc_run_batch.restype = C.c_uint64
+    _lib = L
+    return L
+
+
+def _p(a, t):
+    return a.ctypes.data_as(C.POINTER(t))
+
+
+def philox(ctr, key):
+    c = np.asarray(ctr, dtype=np.uint32)
+    k = np.asarray(key, dtype=np.uint32)
+    out = np.zeros(4, dtype=np.uint32)
+    lib().orc_philox(_p(c, C.c_uint32), _p(k, C.c_uint32), _p(out, C.c_uint32))
+    return out
+
+
+def resize_nearest_chw(frame):
+    frame = np.ascontiguousarray(frame, dtype=np.uint8)
+    out = np.empty((3, DIM, DIM), dtype=np.uint8)
+    lib().orc_resize_nearest_chw(_p(frame, C.c_uint8), frame.shape[0], frame.shape[1], _p(out, C.c_uint8))
+    return out
+
+
+def noise_frame(seed, env_id, noise_count):
+    key = np.array([seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF], dtype=np.uint32)
+    out = np.empty((3, DIM, DIM), dtype=np.uint8)
+    lib().orc_noise_frame(_p(key, C.c_uint32), env_id, noise_count, _p(out, C.c_uint8))
+    return out
+
+
+class Stack:
+    """DataProcessor's float32 3-frame shift register (processor.py:23,47-64)."""
+
+    def __init__(self):
+        self.buf = np.zeros((9, DIM, DIM), dtype=np.float32)
+
+    def push(self, chw):
+        chw = np.ascontiguousarray(chw, dtype=np.uint8)
+        lib().orc_push_frame(_p(self.buf, C.c_float), _p(chw, C.c_uint8))
+
+    def rgb(self):
+        out = np.empty((9, DIM, DIM), dtype=np.float32)
+        lib().orc_observe_rgb(_p(self.buf, C.c_float), _p(out, C.c_float))
+        return out
+
+    def gray_diff(self):
+        out = np.empty((1, DIM, DIM), dtype=np.float64)
+        lib().orc_observe_gray_diff(_p(self.buf, C.c_float), _p(out, C.c_double))
+        return out
+
+
+class Sim:
+    """The bare game (≙ the missing `air_hockey.AirHockey`): SPEC.md §5-§7."""
+
+    def __init__(self, seed=0, env_id=0, table=None):
+        L = lib()
+        self._buf = C.create_string_buffer(L.orc_sizeof_sim())
+        self._p = C.cast(self._buf, C.c_void_p)
+        L.orc_sim_init(self._p, seed, env_id)
+        self.table = np.ascontiguousarray(table, dtype=np.uint8) if table is not None else None
+
+    @property
+    def state(self):
+        """float32[12] view: puck(x,y,vx,vy), bottom, top."""
+        return np.frombuffer(self._buf, dtype=np.float32, count=12)
+
+    @property
+    def serve_count(self):
+        return int(np.frombuffer(self._buf, dtype=np.uint32, count=14)[12])
+
+    @serve_count.setter
+    def serve_count(self, v):
+        np.frombuffer(self._buf, dtype=np.uint32, count=14)[12] = v
+
+    def reset(self):
+        lib().orc_sim_reset(self._p)
+
+    def step(self, robot=None, human=None, use=USE_ALL):
+        info = Info()
+        r = (C.c_int8 * 2)(*[int(v) for v in robot]) if robot is not None else None
+        h = (C.c_int8 * 2)(*[int(v) for v in human]) if human is not None else None
+        lib().orc_sim_step(self._p, r, h, use, C.byref(info))
+        return info
+
+    def draw(self, use=USE_ALL):
+        frame = np.empty((H, W, 3), dtype=np.uint8)
+        lib().orc_draw(self._p, use, _p(self.table, C.c_uint8), _p(frame, C.c_uint8))
+        return frame
+
+
+class Env:
+    """One env with the reference wrapper's semantics (SPEC.md §9), uint8 ring instead of the float stack."""
+
+    def __init__(self, seed=0, env_id=0, table=None):
+        self.table = np.ascontiguousarray(table, dtype=np.uint8)
+        assert self.table.shape == (H, W, 3)
+        self._h = lib().orc_env_create(seed, env_id, _p(self.table, C.c_uint8))
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().orc_env_destroy(self._h)
+            self._h = None
+
+    def reset(self, episode=-1, use=USE_ALL):
+        lib().orc_env_reset(self._h, episode, use)
+
+    def step(self, robot=ACT_NONE, human=ACT_NONE):
+        o = StepOut()
+        lib().orc_env_step(self._h, robot, human, C.byref(o))
+        return o
+
+    def step_auto(self, robot=ACT_NONE, human=ACT_NONE, max_episode_steps=0):
+        o = StepOut()
+        lib().orc_env_step_auto(self._h, robot, human, max_episode_steps, C.byref(o))
+        return o
+
+    def ring(self):
+        """uint8[3][3][128][128], newest first (copy)."""
+        p = lib().orc_env_ring(self._h)
+        return np.ctypeslib.as_array(p, shape=(3, 3, DIM, DIM)).copy()
+
+    def get_state(self):
+        s = np.empty(12, dtype=np.float32)
+        m = np.empty(8, dtype=np.uint32)
+        lib().orc_env_get_state(self._h, _p(s, C.c_float), _p(m, C.c_uint32))
+        return s, m
+
+    def set_state(self, s, m):
+        s = np.ascontiguousarray(s, dtype=np.float32)
+        m = np.ascontiguousarray(m, dtype=np.uint32)
+        lib().orc_env_set_state(self._h, _p(s, C.c_float), _p(m, C.c_uint32))
+
+    def observe_rgb(self):
+        out = np.empty((9, DIM, DIM), dtype=np.float32)
+        lib().orc_env_observe_rgb(self._h, _p(out, C.c_float))
+        return out
+
+
+def run_batch(envs, steps, max_episode_steps=200, threads=1, want_obs=True):
+    """Timed CPU baseline: every env does `steps` auto-reset AI-vs-AI steps; returns (checksum, obs, reward, done, labels)."""
+    n = len(envs)
+    handles = (C.c_void_p * n)(*[e._h for e in envs])
+    obs = np.empty((n, 9, DIM, DIM), dtype=np.float32) if want_obs else None
+    reward = np.empty(n, dtype=np.float32)
+    done = np.empty(n, dtype=np.uint8)
+    labels = np.empty((n, 2), dtype=np.uint8)
+    chk = lib().orc_run_batch(handles, n, steps, max_episode_steps, threads,
+                              _p(obs, C.c_float) if want_obs else None, _p(reward, C.c_float),
+                              _p(done, C.c_uint8), _p(labels, C.c_uint8))
+    return chk, obs, reward, done, labels

@@ -40,6 +40,7 @@ struct ahk_env {
     cudaStream_t host_stream = nullptr;
     int head = 0;
     int raster_grid = 0;
+    bool raster_direct = false; // AHK_RASTER=direct selects the register-composed variant (A/B measurements)
     uint64_t launches = 0;
 };
 
@@ -84,7 +85,8 @@ int raster(ahk_env *e, cudaStream_t s)
     r.env_id_base = e->cfg.env_id_base;
     r.n = e->cfg.n_envs;
     r.head = e->head;
-    AHK_CUDA(ahk::launch_raster(r, e->raster_grid, s));
+    if (e->raster_direct) AHK_CUDA(ahk::launch_raster(r, e->raster_grid, s));
+    else AHK_CUDA(ahk::launch_raster_staged(r, e->raster_grid, s));
     e->launches += 1;
     return AHK_OK;
 }
@@ -114,13 +116,15 @@ int ahk_create(const ahk_config *cfg, ahk_env **out)
     ahk_env *e = new (std::nothrow) ahk_env();
     if (!e) return fail(AHK_ERR_ARG, "out of host memory");
     e->cfg = *cfg;
-    int per_sm = 2;
+    if (const char *s = getenv("AHK_RASTER")) e->raster_direct = strcmp(s, "direct") == 0;
+    int per_sm = e->raster_direct ? 4 : 2;
     if (const char *s = getenv("AHK_RASTER_CTAS_PER_SM")) per_sm = atoi(s) > 0 ? atoi(s) : per_sm;
     e->raster_grid = prop.multiProcessorCount * per_sm;
     cudaError_t err = cudaMalloc(&e->table_dev, ahk::kFrameBytes);
     if (err == cudaSuccess) err = cudaMalloc(&e->action_stage, 2 * static_cast<size_t>(cfg->n_envs));
     if (err == cudaSuccess) err = cudaStreamCreateWithFlags(&e->host_stream, cudaStreamNonBlocking);
     if (err == cudaSuccess) err = ahk::raster_prepare();
+    if (err == cudaSuccess) err = ahk::raster_staged_prepare();
     if (err != cudaSuccess) {
         ahk_destroy(e);
         return fail(AHK_ERR_CUDA, "ahk_create: %s", cudaGetErrorString(err));

@@ -127,7 +127,7 @@ __global__ void __launch_bounds__(kEnvThreads) env_kernel(EnvArgs a)
                 rec[0] = draw_record(s, use);
             }
             steps += 1u;
-            if (terminal || (a.max_episode_steps > 0 && steps >= static_cast<uint32_t>(a.max_episode_steps))) pending = 1u;
+            if (a.auto_reset && (terminal || (a.max_episode_steps > 0 && steps >= static_cast<uint32_t>(a.max_episode_steps)))) pending = 1u;
 
             a.reward[i] = 0.5f * static_cast<float>(r2);
             a.done[i] = static_cast<uint8_t>(terminal);
@@ -195,30 +195,37 @@ __device__ __forceinline__ uint32_t mallet_colour(int dx, int dy, uint32_t shine
     return d2 > 400 ? rim : body;
 }
 
-// colour of native pixel (x, y), top-most layer first (SPEC.md §7, painter's order reversed)
-__device__ __forceinline__ uint32_t shade(const Scene &sc, int x, int y, bool arm_row, int arm_xc, int arm_hw)
+constexpr uint32_t kLayerLine = 1u, kLayerPuck = 2u, kLayerBot = 4u, kLayerTop = 8u, kLayerArm = 16u;
+
+// what is constant along one output row (native row y)
+struct Row {
+    int y, arm_xc, arm_hw;
+};
+
+// colour of native pixel (x, row.y), top-most layer first (SPEC.md §7, painter's order reversed).  `layers` says which
+// layers can reach this 16-pixel vector at all; the others are not even tested.
+__device__ __forceinline__ uint32_t shade(const Scene &sc, const Row &row, uint32_t layers, int x)
 {
-    if (arm_row) {
-        const int a = abs(x - arm_xc);
-        if (a <= arm_hw) return a > arm_hw - 4 ? rgb(160, 110, 95) : rgb(200, 150, 130);
+    if (layers & kLayerArm) {
+        const int a = abs(x - row.arm_xc);
+        if (a <= row.arm_hw) return a > row.arm_hw - 4 ? rgb(160, 110, 95) : rgb(200, 150, 130);
     }
-    if (sc.use & kUseTop) {
-        const uint32_t c = mallet_colour(x - sc.itx, y - sc.ity, rgb(225, 215, 215), rgb(110, 70, 70), rgb(35, 20, 20), rgb(70, 40, 40));
+    if (layers & kLayerTop) {
+        const uint32_t c = mallet_colour(x - sc.itx, row.y - sc.ity, rgb(225, 215, 215), rgb(110, 70, 70), rgb(35, 20, 20), rgb(70, 40, 40));
         if (c != kNone) return c;
     }
-    {
-        const uint32_t c = mallet_colour(x - sc.ibx, y - sc.iby, rgb(220, 220, 230), rgb(90, 90, 100), rgb(20, 20, 24), rgb(40, 40, 48));
+    if (layers & kLayerBot) {
+        const uint32_t c = mallet_colour(x - sc.ibx, row.y - sc.iby, rgb(220, 220, 230), rgb(90, 90, 100), rgb(20, 20, 24), rgb(40, 40, 48));
         if (c != kNone) return c;
     }
-    if (sc.use & kUsePuck) {
-        const int dx = x - sc.ipx, dy = y - sc.ipy, d2 = dx * dx + dy * dy;
+    if (layers & kLayerPuck) {
+        const int dx = x - sc.ipx, dy = row.y - sc.ipy, d2 = dx * dx + dy * dy;
         if (d2 <= 324) {
             if ((dx + 5) * (dx + 5) + (dy + 5) * (dy + 5) <= 16) return rgb(240, 120, 130);
             return d2 > 196 ? rgb(150, 20, 30) : rgb(215, 40, 50);
         }
     }
-    if (y >= sc.iby - 3 && y <= sc.iby + 2) return rgb(235, 235, 225);
-    return kNone;
+    return (layers & kLayerLine) ? rgb(235, 235, 225) : kNone;
 }
 
 // native sample column / row of output pixel j / i: Pillow NEAREST, (j + 0.5) * 450 / 128 truncated (SPEC.md §8)
@@ -237,7 +244,7 @@ __device__ __forceinline__ void store_vec(uint8_t *dst, const uint4 &v)
     __stcs(reinterpret_cast<uint4 *>(dst), v);
 }
 
-__global__ void __launch_bounds__(kRasterThreads) raster_kernel(RasterArgs a)
+__global__ void __launch_bounds__(kRasterThreads, 4) raster_kernel(RasterArgs a)
 {
     extern __shared__ uint4 s_table[]; // [3][128][8] vectors of 16 pixels: the table at the sample points
     for (int v = threadIdx.x; v < kFrameVecs; v += kRasterThreads) s_table[v] = a.table[v];
@@ -278,41 +285,42 @@ __global__ void __launch_bounds__(kRasterThreads) raster_kernel(RasterArgs a)
         sc.itx = static_cast<int>(rec.z & 0xFFFFu); sc.ity = static_cast<int>(rec.z >> 16);
         sc.use = rec.w & 7u;
 
-#pragma unroll
+#pragma unroll 1
         for (int pass = 0; pass < 4; ++pass) {
             const int i = r0 + 32 * pass;
-            const int y = sample_y(i);
             const int vec = i * 8 + k;
             uint4 out0 = s_table[vec], out1 = s_table[1024 + vec], out2 = s_table[2048 + vec];
 
             // which layers can touch this 16-pixel span at all?
-            const bool arm_row = (sc.use & kUseArm) && y <= sc.ity + 10;
-            int arm_xc = 0, arm_hw = 0;
-            bool touched = y >= sc.iby - 3 && y <= sc.iby + 2; // rail line spans the full width
-            if (arm_row) {
-                const int t = sc.ity + 10 - y;
-                arm_xc = sc.itx + ((t * 5) >> 5);
-                arm_hw = 26 + ((t * 3) >> 4);
-                touched |= x_last >= arm_xc - arm_hw && x_first <= arm_xc + arm_hw;
+            Row row;
+            row.y = sample_y(i);
+            row.arm_xc = 0;
+            row.arm_hw = 0;
+            uint32_t layers = (row.y >= sc.iby - 3 && row.y <= sc.iby + 2) ? kLayerLine : 0u; // the rail line spans the full width
+            if ((sc.use & kUseArm) && row.y <= sc.ity + 10) {
+                const int t = sc.ity + 10 - row.y;
+                row.arm_xc = sc.itx + ((t * 5) >> 5);
+                row.arm_hw = 26 + ((t * 3) >> 4);
+                if (x_last >= row.arm_xc - row.arm_hw && x_first <= row.arm_xc + row.arm_hw) layers |= kLayerArm;
             }
-            touched |= abs(y - sc.iby) <= 24 && x_last >= sc.ibx - 24 && x_first <= sc.ibx + 24;
-            touched |= (sc.use & kUseTop) && abs(y - sc.ity) <= 24 && x_last >= sc.itx - 24 && x_first <= sc.itx + 24;
-            touched |= (sc.use & kUsePuck) && abs(y - sc.ipy) <= 18 && x_last >= sc.ipx - 18 && x_first <= sc.ipx + 18;
+            if (abs(row.y - sc.iby) <= 24 && x_last >= sc.ibx - 24 && x_first <= sc.ibx + 24) layers |= kLayerBot;
+            if ((sc.use & kUseTop) && abs(row.y - sc.ity) <= 24 && x_last >= sc.itx - 24 && x_first <= sc.itx + 24) layers |= kLayerTop;
+            if ((sc.use & kUsePuck) && abs(row.y - sc.ipy) <= 18 && x_last >= sc.ipx - 18 && x_first <= sc.ipx + 18) layers |= kLayerPuck;
 
-            if (touched) {
+            if (layers) {
                 uint32_t *w0 = reinterpret_cast<uint32_t *>(&out0);
                 uint32_t *w1 = reinterpret_cast<uint32_t *>(&out1);
                 uint32_t *w2 = reinterpret_cast<uint32_t *>(&out2);
 #pragma unroll
                 for (int g = 0; g < 4; ++g) {
-#define AHK_PIXEL(B)                                                                                   \
-    {                                                                                                  \
-        const uint32_t c = shade(sc, sample_x(16 * k + 4 * g + B), y, arm_row, arm_xc, arm_hw);         \
-        if (c != kNone) {                                                                              \
-            w0[g] = put_byte<0, B>(w0[g], c);                                                          \
-            w1[g] = put_byte<1, B>(w1[g], c);                                                          \
-            w2[g] = put_byte<2, B>(w2[g], c);                                                          \
-        }                                                                                              \
+#define AHK_PIXEL(B)                                                                 \
+    {                                                                                \
+        const uint32_t c = shade(sc, row, layers, sample_x(16 * k + 4 * g + B));     \
+        if (c != kNone) {                                                            \
+            w0[g] = put_byte<0, B>(w0[g], c);                                        \
+            w1[g] = put_byte<1, B>(w1[g], c);                                        \
+            w2[g] = put_byte<2, B>(w2[g], c);                                        \
+        }                                                                            \
     }
                     AHK_PIXEL(0) AHK_PIXEL(1) AHK_PIXEL(2) AHK_PIXEL(3)
 #undef AHK_PIXEL

@@ -11,6 +11,7 @@ constexpr int kFrameBytes = 3 * kDim * kDim;
 constexpr int kFrameVecs = kFrameBytes / 16; // 3072 128-bit vectors per frame
 constexpr int kEnvThreads = 128;
 constexpr int kRasterThreads = 256;
+constexpr int kRasterStagedSmem = 2 * kFrameBytes + kDim * 8; // table + staging frame + per-row spans
 
 struct EnvArgs {
     uint32_t *state;   // [16][n]
@@ -43,6 +44,8 @@ struct ObserveArgs {
 cudaError_t launch_env(const EnvArgs &a, bool step, cudaStream_t stream);
 cudaError_t raster_prepare();
 cudaError_t launch_raster(const RasterArgs &a, int grid, cudaStream_t stream);
+cudaError_t raster_staged_prepare();
+cudaError_t launch_raster_staged(const RasterArgs &a, int grid, cudaStream_t stream);
 cudaError_t launch_observe(const ObserveArgs &a, int grid, cudaStream_t stream);
 cudaError_t launch_set_pending(uint32_t *state, const uint8_t *pending, int n, cudaStream_t stream);
 

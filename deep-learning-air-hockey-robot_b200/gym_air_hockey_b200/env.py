@@ -298,6 +298,6 @@ class AirHockeyEnv(object):
 _REGISTRY = {'AirHockey-v0': AirHockeyEnv}  # gym_air_hockey/__init__.py:3-6
 
 
-def make(env_id, **kwargs):
+def make(name, **kwargs):
     """≙ gym.make('AirHockey-v0')."""
-    return _REGISTRY[env_id](**kwargs)
+    return _REGISTRY[name](**kwargs)

@@ -42,6 +42,7 @@ struct ahk_env {
     int raster_grid = 0;
     bool raster_direct = false; // AHK_RASTER=direct selects the register-composed variant (A/B measurements)
     uint64_t launches = 0;
+    cudaEvent_t ev[3] = {nullptr, nullptr, nullptr}; // ahk_step_profiled: before env_kernel, between, after raster
 };
 
 namespace {
@@ -117,12 +118,13 @@ int ahk_create(const ahk_config *cfg, ahk_env **out)
     if (!e) return fail(AHK_ERR_ARG, "out of host memory");
     e->cfg = *cfg;
     if (const char *s = getenv("AHK_RASTER")) e->raster_direct = strcmp(s, "direct") == 0;
-    int per_sm = e->raster_direct ? 4 : 2;
+    int per_sm = e->raster_direct ? 4 : 1;
     if (const char *s = getenv("AHK_RASTER_CTAS_PER_SM")) per_sm = atoi(s) > 0 ? atoi(s) : per_sm;
     e->raster_grid = prop.multiProcessorCount * per_sm;
     cudaError_t err = cudaMalloc(&e->table_dev, ahk::kFrameBytes);
     if (err == cudaSuccess) err = cudaMalloc(&e->action_stage, 2 * static_cast<size_t>(cfg->n_envs));
     if (err == cudaSuccess) err = cudaStreamCreateWithFlags(&e->host_stream, cudaStreamNonBlocking);
+    for (int k = 0; k < 3 && err == cudaSuccess; ++k) err = cudaEventCreate(&e->ev[k]);
     if (err == cudaSuccess) err = ahk::raster_prepare();
     if (err == cudaSuccess) err = ahk::raster_staged_prepare();
     if (err != cudaSuccess) {
@@ -140,6 +142,7 @@ void ahk_destroy(ahk_env *e)
     if (e->table_dev) cudaFree(e->table_dev);
     if (e->action_stage) cudaFree(e->action_stage);
     if (e->host_stream) cudaStreamDestroy(e->host_stream);
+    for (int k = 0; k < 3; ++k) if (e->ev[k]) cudaEventDestroy(e->ev[k]);
     delete e;
 }
 
@@ -200,6 +203,27 @@ int ahk_step(ahk_env *e, const uint8_t *robot, const uint8_t *human, void *strea
     AHK_CUDA(ahk::launch_env(a, true, s));
     e->launches += 1;
     return raster(e, s);
+}
+
+int ahk_step_profiled(ahk_env *e, const uint8_t *robot, const uint8_t *human, void *stream, float *env_ms, float *raster_ms)
+{
+    if (int rc = check_ready(e)) return rc;
+    if (!env_ms || !raster_ms) return fail(AHK_ERR_ARG, "env_ms/raster_ms is NULL");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    ahk::EnvArgs a = env_args(e);
+    a.robot = robot;
+    a.human = human;
+    e->head = (e->head + 1) % 3;
+    AHK_CUDA(cudaEventRecord(e->ev[0], s));
+    AHK_CUDA(ahk::launch_env(a, true, s));
+    e->launches += 1;
+    AHK_CUDA(cudaEventRecord(e->ev[1], s));
+    if (int rc = raster(e, s)) return rc;
+    AHK_CUDA(cudaEventRecord(e->ev[2], s));
+    AHK_CUDA(cudaEventSynchronize(e->ev[2]));
+    AHK_CUDA(cudaEventElapsedTime(env_ms, e->ev[0], e->ev[1]));
+    AHK_CUDA(cudaEventElapsedTime(raster_ms, e->ev[1], e->ev[2]));
+    return AHK_OK;
 }
 
 int ahk_step_host(ahk_env *e, const uint8_t *robot, const uint8_t *human, float *reward, uint8_t *done,

@@ -11,7 +11,9 @@ constexpr int kFrameBytes = 3 * kDim * kDim;
 constexpr int kFrameVecs = kFrameBytes / 16; // 3072 128-bit vectors per frame
 constexpr int kEnvThreads = 128;
 constexpr int kRasterThreads = 256;
-constexpr int kRasterStagedSmem = 2 * kFrameBytes + kDim * 8; // table + staging frame + per-row spans
+constexpr int kRasterGroups = 3;                                               // independent 256-thread groups per CTA
+constexpr int kRasterGroupTail = kDim * 8 + kRasterThreads * 20 + 16;          // per-row spans + record batch + counter
+constexpr int kRasterStagedSmem = (1 + kRasterGroups) * kFrameBytes + kRasterGroups * kRasterGroupTail; // table + stagings
 
 struct EnvArgs {
     uint32_t *state;   // [16][n]

@@ -4,8 +4,8 @@
 // stack (gym-air-hockey/gym_air_hockey/processor.py:31-49).  NEAREST resize of a native 450x700 drawing == evaluating
 // the drawing at the 128x128 sample points (SPEC.md §8), so nothing is ever drawn at native resolution.
 //
-// Persistent CTAs (2 per SM).  Shared memory per CTA: the table image at the sample points (48 KB, loaded once) and
-// one 48 KB staging frame.  Per frame:
+// One persistent CTA per SM = 3 groups of 256 threads.  Shared memory: the table image at the sample points (48 KB,
+// one bulk async load) shared by the groups, and one 48 KB staging frame per group.  Per frame, per group:
 //   phase 0  128 threads: per output row, where the rail line and the arm fall (exact inverse of the sample map);
 //   phase 1  all threads: staging = table, with line rows and arm spans substituted by byte masks — work is per
 //            128-bit vector, no per-pixel loop;
@@ -113,150 +113,212 @@ __device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.w
 __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
+// named barrier 1 + group over the kRasterThreads threads of one group (barrier 0 stays __syncthreads)
+__device__ __forceinline__ void group_sync(int group) { asm volatile("bar.sync %0, %1;" :: "r"(group + 1), "n"(kRasterThreads) : "memory"); }
+
+__device__ __forceinline__ void mbarrier_wait(uint32_t bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n\t.reg .pred done;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 done, [%0], %1;\n\t"
+        "@!done bra WAIT_%=;\n\t}"
+        :: "r"(bar), "r"(parity) : "memory");
+}
+
 } // namespace
 
-__global__ void __launch_bounds__(kRasterThreads, 2) raster_staged_kernel(RasterArgs a)
+// One CTA per SM, kRasterGroups independent groups of kRasterThreads threads.  The groups share the table image in
+// shared memory; each owns a staging frame, a record batch and a named barrier, and walks its own subset of frames — so
+// while one group waits for the TMA engine to drain its staging buffer, the others compose.
+__global__ void __launch_bounds__(kRasterGroups * kRasterThreads, 1) raster_staged_kernel(RasterArgs a)
 {
     extern __shared__ __align__(128) uint8_t smem[];
-    uint4 *s_table = reinterpret_cast<uint4 *>(smem);               // [3][128][8] vectors
-    uint4 *s_stage = reinterpret_cast<uint4 *>(smem + kFrameBytes); // same shape: the frame being composed
-    uint2 *s_row = reinterpret_cast<uint2 *>(smem + 2 * kFrameBytes); // [128] per-row spans
+    const int tid = threadIdx.x % kRasterThreads; // thread within the group
+    const int grp = threadIdx.x / kRasterThreads;
+    const uint4 *s_table = reinterpret_cast<const uint4 *>(smem);                          // [3][128][8] vectors
+    uint4 *s_stage = reinterpret_cast<uint4 *>(smem + (1 + grp) * kFrameBytes);             // the frame being composed
+    uint8_t *tail = smem + (1 + kRasterGroups) * kFrameBytes + grp * kRasterGroupTail;
+    uint2 *s_row = reinterpret_cast<uint2 *>(tail);                                         // [128] per-row spans
+    uint4 *s_recs = reinterpret_cast<uint4 *>(tail + kDim * 8);                             // [kRasterThreads] valid records
+    uint32_t *s_items = reinterpret_cast<uint32_t *>(tail + kDim * 8 + kRasterThreads * 16); // their item ids
+    int *s_count = reinterpret_cast<int *>(tail + kDim * 8 + kRasterThreads * 20);
+    __shared__ __align__(8) uint64_t s_table_ready;
 
-    const int tid = threadIdx.x;
-    for (int v = tid; v < kFrameVecs; v += kRasterThreads) s_table[v] = a.table[v];
+    // the table: one bulk async copy global -> shared (TMA), completion on an mbarrier
+    const uint32_t bar = static_cast<uint32_t>(__cvta_generic_to_shared(&s_table_ready));
+    if (threadIdx.x == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(bar) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(kFrameBytes) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     :: "r"(static_cast<uint32_t>(__cvta_generic_to_shared(smem))), "l"(a.table), "r"(kFrameBytes), "r"(bar) : "memory");
+    }
+    bool table_ready = false;
 
     const size_t n = static_cast<size_t>(a.n);
     const long long items = 3ll * a.n;
+    const long long lanes = static_cast<long long>(gridDim.x) * kRasterGroups; // groups in the whole grid
     bool store_in_flight = false;
 
-    for (long long item = blockIdx.x; item < items; item += gridDim.x) {
-        const int back = static_cast<int>(item / a.n); // 0 newest
-        const int env = static_cast<int>(item - static_cast<long long>(back) * a.n);
-        const uint4 rec = __ldg(reinterpret_cast<const uint4 *>(a.drawlist) + item);
-        if (!(rec.w & kDrawValid)) continue;
-        const int slot = (a.head + 3 - back) % 3;
-        uint8_t *frame = a.frames + (static_cast<size_t>(slot) * n + env) * kFrameBytes;
-
-        if (rec.w & kDrawNoise) { // SPEC.md §7 last paragraph
-            const uint32_t env_id = a.env_id_base + static_cast<uint32_t>(env);
-#pragma unroll 1
-            for (int v = tid; v < kFrameVecs; v += kRasterThreads) {
-                uint4 r = philox(static_cast<uint32_t>(v), rec.x, env_id, 2u, a.key);
-                r.x = __vsubus4(r.x, 0x01010101u); // per byte b -> (b * 255) >> 8 == max(b - 1, 0)
-                r.y = __vsubus4(r.y, 0x01010101u);
-                r.z = __vsubus4(r.z, 0x01010101u);
-                r.w = __vsubus4(r.w, 0x01010101u);
-                __stcs(reinterpret_cast<uint4 *>(frame) + v, r);
+    // This group owns items first, first + lanes, ...  Most of the 3n records are empty (only envs that were reset
+    // paint the two older slots), and a record read costs a trip to L2: fetch a batch of kRasterThreads records with
+    // one load per thread, keep the valid ones in shared memory, then paint from there.
+    for (long long batch = static_cast<long long>(blockIdx.x) * kRasterGroups + grp; batch < items; batch += lanes * kRasterThreads) {
+        group_sync(grp); // previous batch fully consumed
+        if (tid == 0) *s_count = 0;
+        group_sync(grp);
+        {
+            const long long item = batch + static_cast<long long>(tid) * lanes;
+            if (item < items) {
+                const uint4 rec = __ldg(reinterpret_cast<const uint4 *>(a.drawlist) + item);
+                if (rec.w & kDrawValid) {
+                    const int at = atomicAdd(s_count, 1);
+                    s_recs[at] = rec;
+                    s_items[at] = static_cast<uint32_t>(item);
+                }
             }
-            continue;
         }
+        group_sync(grp);
+        const int count = *s_count;
 
-        Scene sc;
-        sc.ipx = static_cast<int>(rec.x & 0xFFFFu); sc.ipy = static_cast<int>(rec.x >> 16);
-        sc.ibx = static_cast<int>(rec.y & 0xFFFFu); sc.iby = static_cast<int>(rec.y >> 16);
-        sc.itx = static_cast<int>(rec.z & 0xFFFFu); sc.ity = static_cast<int>(rec.z >> 16);
-        sc.use = rec.w & 7u;
+        for (int q = 0; q < count; ++q) {
+            const uint4 rec = s_recs[q];
+            const uint32_t item = s_items[q];
+            const int back = item >= 2u * a.n ? 2 : (item >= static_cast<uint32_t>(a.n) ? 1 : 0); // 0 newest
+            const int env = static_cast<int>(item - static_cast<uint32_t>(back) * a.n);
+            const int slot = (a.head + 3 - back) % 3;
+            uint8_t *frame = a.frames + (static_cast<size_t>(slot) * n + env) * kFrameBytes;
 
-        // ---- phase 0: per-row spans (does not touch the staging buffer, so it overlaps the previous bulk store)
-        if (tid < kDim) {
-            const int y = sample_y(tid);
-            uint32_t line = (y >= sc.iby - 3 && y <= sc.iby + 2) ? 1u : 0u;
-            uint32_t spans = 0u; // bytes: outer lo+1, outer hi+1, inner lo+1, inner hi+1; 0 = no arm on this row
-            if ((sc.use & kUseArm) && y <= sc.ity + 10) {
-                int xc, hw, olo, ohi, ilo, ihi;
-                arm_span(sc, y, xc, hw);
-                columns_within(xc - hw, xc + hw, olo, ohi);
-                columns_within(xc - hw + 4, xc + hw - 4, ilo, ihi);
-                if (olo <= ohi) spans = static_cast<uint32_t>(olo + 1) | static_cast<uint32_t>(ohi + 1) << 8 |
-                                        static_cast<uint32_t>(ilo + 1) << 16 | static_cast<uint32_t>(ihi + 1) << 24;
-            }
-            s_row[tid] = make_uint2(spans, line);
-        }
-        if (store_in_flight && tid == 0) bulk_wait_read(); // the TMA engine has finished reading the staging buffer
-        __syncthreads();
-
-        // ---- phase 1: staging = table + rail line + arm, one (row, 16-pixel vector) position for all 3 channels
+            if (rec.w & kDrawNoise) { // SPEC.md §7 last paragraph
+                const uint32_t env_id = a.env_id_base + static_cast<uint32_t>(env);
 #pragma unroll 1
-        for (int pos = tid; pos < kDim * 8; pos += kRasterThreads) {
-            const int i = pos >> 3, k = pos & 7;
-            uint4 out[3] = {s_table[pos], s_table[1024 + pos], s_table[2048 + pos]};
-            const uint2 info = s_row[i];
-            if (info.y) {
-#pragma unroll
-                for (int c = 0; c < 3; ++c) { const uint32_t s = splat(kLineColour, c); out[c] = make_uint4(s, s, s, s); }
+                for (int v = tid; v < kFrameVecs; v += kRasterThreads) {
+                    uint4 r = philox(static_cast<uint32_t>(v), rec.x, env_id, 2u, a.key);
+                    r.x = __vsubus4(r.x, 0x01010101u); // per byte b -> (b * 255) >> 8 == max(b - 1, 0)
+                    r.y = __vsubus4(r.y, 0x01010101u);
+                    r.z = __vsubus4(r.z, 0x01010101u);
+                    r.w = __vsubus4(r.w, 0x01010101u);
+                    __stcs(reinterpret_cast<uint4 *>(frame) + v, r);
+                }
+                continue;
             }
-            if (info.x) {
-                const int olo = static_cast<int>(info.x & 255u) - 1, ohi = static_cast<int>((info.x >> 8) & 255u) - 1;
-                const int ilo = static_cast<int>((info.x >> 16) & 255u) - 1, ihi = static_cast<int>(info.x >> 24) - 1;
-                const uint32_t outer = span_mask(olo, ohi, 16 * k);
-                if (outer) {
-                    const uint32_t inner = span_mask(ilo, ihi, 16 * k) & outer, edge = outer & ~inner;
+
+            Scene sc;
+            sc.ipx = static_cast<int>(rec.x & 0xFFFFu); sc.ipy = static_cast<int>(rec.x >> 16);
+            sc.ibx = static_cast<int>(rec.y & 0xFFFFu); sc.iby = static_cast<int>(rec.y >> 16);
+            sc.itx = static_cast<int>(rec.z & 0xFFFFu); sc.ity = static_cast<int>(rec.z >> 16);
+            sc.use = rec.w & 7u;
+
+            // ---- phase 0: per-row spans (does not touch the staging buffer, so it overlaps the previous bulk store)
+            if (tid < kDim) {
+                const int y = sample_y(tid);
+                uint32_t line = (y >= sc.iby - 3 && y <= sc.iby + 2) ? 1u : 0u;
+                uint32_t spans = 0u; // bytes: outer lo+1, outer hi+1, inner lo+1, inner hi+1; 0 = no arm on this row
+                if ((sc.use & kUseArm) && y <= sc.ity + 10) {
+                    int xc, hw, olo, ohi, ilo, ihi;
+                    arm_span(sc, y, xc, hw);
+                    columns_within(xc - hw, xc + hw, olo, ohi);
+                    columns_within(xc - hw + 4, xc + hw - 4, ilo, ihi);
+                    if (olo <= ohi) spans = static_cast<uint32_t>(olo + 1) | static_cast<uint32_t>(ohi + 1) << 8 |
+                                            static_cast<uint32_t>(ilo + 1) << 16 | static_cast<uint32_t>(ihi + 1) << 24;
+                }
+                s_row[tid] = make_uint2(spans, line);
+            }
+            if (store_in_flight && tid == 0) bulk_wait_read(); // the TMA engine has finished reading the staging buffer
+            if (!table_ready) {
+                mbarrier_wait(bar, 0u);
+                table_ready = true;
+            }
+            group_sync(grp);
+
+            // ---- phase 1: staging = table + rail line + arm, one (row, 16-pixel vector) position for all 3 channels
+#pragma unroll 1
+            for (int pos = tid; pos < kDim * 8; pos += kRasterThreads) {
+                const int i = pos >> 3, k = pos & 7;
+                uint4 out[3] = {s_table[pos], s_table[1024 + pos], s_table[2048 + pos]};
+                const uint2 info = s_row[i];
+                if (info.y) {
 #pragma unroll
-                    for (int g = 0; g < 4; ++g) {
-                        const uint32_t me = byte_lanes((edge >> (4 * g)) & 15u), mi = byte_lanes((inner >> (4 * g)) & 15u);
-                        if (me | mi) {
+                    for (int c = 0; c < 3; ++c) { const uint32_t s = splat(kLineColour, c); out[c] = make_uint4(s, s, s, s); }
+                }
+                if (info.x) {
+                    const int olo = static_cast<int>(info.x & 255u) - 1, ohi = static_cast<int>((info.x >> 8) & 255u) - 1;
+                    const int ilo = static_cast<int>((info.x >> 16) & 255u) - 1, ihi = static_cast<int>(info.x >> 24) - 1;
+                    const uint32_t outer = span_mask(olo, ohi, 16 * k);
+                    if (outer) {
+                        const uint32_t inner = span_mask(ilo, ihi, 16 * k) & outer, edge = outer & ~inner;
 #pragma unroll
-                            for (int c = 0; c < 3; ++c) {
-                                uint32_t *w = reinterpret_cast<uint32_t *>(&out[c]) + g;
-                                *w = (*w & ~(me | mi)) | (splat(kArmEdge, c) & me) | (splat(kArmInner, c) & mi);
+                        for (int g = 0; g < 4; ++g) {
+                            const uint32_t me = byte_lanes((edge >> (4 * g)) & 15u), mi = byte_lanes((inner >> (4 * g)) & 15u);
+                            if (me | mi) {
+#pragma unroll
+                                for (int c = 0; c < 3; ++c) {
+                                    uint32_t *w = reinterpret_cast<uint32_t *>(&out[c]) + g;
+                                    *w = (*w & ~(me | mi)) | (splat(kArmEdge, c) & me) | (splat(kArmInner, c) & mi);
+                                }
                             }
                         }
                     }
                 }
+                s_stage[pos] = out[0];
+                s_stage[1024 + pos] = out[1];
+                s_stage[2048 + pos] = out[2];
             }
-            s_stage[pos] = out[0];
-            s_stage[1024 + pos] = out[1];
-            s_stage[2048 + pos] = out[2];
-        }
-        __syncthreads();
+            group_sync(grp);
 
-        // ---- phase 2: puck and mallets — candidate pixels of three bounding boxes, 16 columns per box row
-        {
-            int r_lo[3], r_n[3], c_lo[3];
-            const int cx[3] = {sc.ipx, sc.ibx, sc.itx}, cy[3] = {sc.ipy, sc.iby, sc.ity}, rad[3] = {18, 24, 24};
-            const bool on[3] = {(sc.use & kUsePuck) != 0u, true, (sc.use & kUseTop) != 0u};
-            int total = 0;
+            // ---- phase 2: puck and mallets — candidate pixels of three bounding boxes, 16 columns per box row
+            {
+                int r_lo[3], r_n[3], c_lo[3];
+                const int cx[3] = {sc.ipx, sc.ibx, sc.itx}, cy[3] = {sc.ipy, sc.iby, sc.ity}, rad[3] = {18, 24, 24};
+                const bool on[3] = {(sc.use & kUsePuck) != 0u, true, (sc.use & kUseTop) != 0u};
+                int total = 0;
 #pragma unroll
-            for (int o = 0; o < 3; ++o) {
-                int lo, hi, clo, chi;
-                rows_within(cy[o] - rad[o], cy[o] + rad[o], lo, hi);
-                columns_within(cx[o] - rad[o], cx[o] + rad[o], clo, chi);
-                r_lo[o] = lo;
-                c_lo[o] = clo;
-                r_n[o] = (on[o] && hi >= lo && chi >= clo) ? hi - lo + 1 : 0;
-                total += r_n[o] * 16;
-            }
-            uint8_t *stage = reinterpret_cast<uint8_t *>(s_stage);
+                for (int o = 0; o < 3; ++o) {
+                    int lo, hi, clo, chi;
+                    rows_within(cy[o] - rad[o], cy[o] + rad[o], lo, hi);
+                    columns_within(cx[o] - rad[o], cx[o] + rad[o], clo, chi);
+                    r_lo[o] = lo;
+                    c_lo[o] = clo;
+                    r_n[o] = (on[o] && hi >= lo && chi >= clo) ? hi - lo + 1 : 0;
+                    total += r_n[o] * 16;
+                }
+                uint8_t *stage = reinterpret_cast<uint8_t *>(s_stage);
 #pragma unroll 1
-            for (int idx = tid; idx < total; idx += kRasterThreads) {
-                int local = idx, o = 0;
-                if (local >= r_n[0] * 16) { local -= r_n[0] * 16; o = 1; }
-                if (o == 1 && local >= r_n[1] * 16) { local -= r_n[1] * 16; o = 2; }
-                const int i = (o == 0 ? r_lo[0] : (o == 1 ? r_lo[1] : r_lo[2])) + (local >> 4);
-                const int j = (o == 0 ? c_lo[0] : (o == 1 ? c_lo[1] : c_lo[2])) + (local & 15);
-                if (j > 127) continue;
-                const uint32_t c = shade_bodies(sc, sample_x(j), sample_y(i));
-                if (c != kNone) {
-                    const int at = i * kDim + j;
-                    stage[at] = static_cast<uint8_t>(c);
-                    stage[kDim * kDim + at] = static_cast<uint8_t>(c >> 8);
-                    stage[2 * kDim * kDim + at] = static_cast<uint8_t>(c >> 16);
+                for (int idx = tid; idx < total; idx += kRasterThreads) {
+                    int local = idx, o = 0;
+                    if (local >= r_n[0] * 16) { local -= r_n[0] * 16; o = 1; }
+                    if (o == 1 && local >= r_n[1] * 16) { local -= r_n[1] * 16; o = 2; }
+                    const int i = (o == 0 ? r_lo[0] : (o == 1 ? r_lo[1] : r_lo[2])) + (local >> 4);
+                    const int j = (o == 0 ? c_lo[0] : (o == 1 ? c_lo[1] : c_lo[2])) + (local & 15);
+                    if (j > 127) continue;
+                    const uint32_t c = shade_bodies(sc, sample_x(j), sample_y(i));
+                    if (c != kNone) {
+                        const int at = i * kDim + j;
+                        stage[at] = static_cast<uint8_t>(c);
+                        stage[kDim * kDim + at] = static_cast<uint8_t>(c >> 8);
+                        stage[2 * kDim * kDim + at] = static_cast<uint8_t>(c >> 16);
+                    }
                 }
             }
-        }
-        fence_async_smem(); // generic-proxy writes to shared memory -> visible to the async proxy (TMA)
-        __syncthreads();
+            fence_async_smem(); // generic-proxy writes to shared memory -> visible to the async proxy (TMA)
+            group_sync(grp);
 
-        // ---- phase 3: hand the frame to the TMA engine
-        if (tid == 0) {
+            // ---- phase 3: hand the frame to the TMA engine
+            if (tid == 0) {
 #pragma unroll
-            for (int c = 0; c < 3; ++c)
-                bulk_store(frame + c * kDim * kDim, reinterpret_cast<const uint8_t *>(s_stage) + c * kDim * kDim, kDim * kDim);
-            bulk_commit();
+                for (int c = 0; c < 3; ++c)
+                    bulk_store(frame + c * kDim * kDim, reinterpret_cast<const uint8_t *>(s_stage) + c * kDim * kDim, kDim * kDim);
+                bulk_commit();
+            }
+            store_in_flight = true;
         }
-        store_in_flight = true;
     }
     if (store_in_flight && tid == 0) bulk_wait_all();
+    if (!table_ready) mbarrier_wait(bar, 0u); // never exit with the table copy still in flight
 }
 
 cudaError_t raster_staged_prepare()
@@ -266,7 +328,7 @@ cudaError_t raster_staged_prepare()
 
 cudaError_t launch_raster_staged(const RasterArgs &a, int grid, cudaStream_t stream)
 {
-    raster_staged_kernel<<<grid, kRasterThreads, kRasterStagedSmem, stream>>>(a);
+    raster_staged_kernel<<<grid, kRasterGroups * kRasterThreads, kRasterStagedSmem, stream>>>(a);
     return cudaGetLastError();
 }
 

@@ -42,6 +42,7 @@ SYMBOLS = {
     "ahk_bind_buffers": (_i, [_vp, C.POINTER(Buffers)]),
     "ahk_reset": (_i, [_vp, _vp, _vp, _vp, _vp]),
     "ahk_step": (_i, [_vp, _vp, _vp, _vp]),
+    "ahk_step_profiled": (_i, [_vp, _vp, _vp, _vp, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
     "ahk_step_host": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "ahk_observe": (_i, [_vp, _i, _vp, _vp]),
     "ahk_head": (_i, [_vp]),

@@ -141,6 +141,13 @@ class BatchedAirHockeyEnv(object):
         info = {'robot_action': self.robot_label, 'human_action': self.human_label}
         return self._obs(), self.reward, self.done.view(torch.bool), info
 
+    def step_profiled(self, robot_action=None, human_action=None):
+        """step() with CUDA events around each kernel: -> (env_kernel ms, raster kernel ms).  For bench.py's roofline."""
+        r, h = self._labels(robot_action), self._labels(human_action)
+        env_ms, raster_ms = C.c_float(), C.c_float()
+        _lib.check(self.lib.ahk_step_profiled(self._h, _ptr(r), _ptr(h), self._stream(), C.byref(env_ms), C.byref(raster_ms)))
+        return env_ms.value, raster_ms.value
+
     def step_host(self, robot_action=None, human_action=None, out=None, want_frame=False):
         """The same step for a caller on the CPU: numpy uint8 labels in (or None), numpy results out, one C call
         (ahk_step_host) that copies in, steps, copies out and waits.  `out` is a dict of preallocated (ideally

@@ -96,6 +96,11 @@ int ahk_step(ahk_env *env, const uint8_t *robot_dev, const uint8_t *human_dev, v
 int ahk_step_host(ahk_env *env, const uint8_t *robot_host, const uint8_t *human_host, float *reward_host,
                   uint8_t *done_host, uint8_t *robot_label_host, uint8_t *human_label_host, uint8_t *frame_host);
 
+/* ahk_step with CUDA events recorded on `stream` around each of its two kernels; waits, then reports their durations.
+ * Measurement aid for bench.py's roofline (not a hot-path call). */
+int ahk_step_profiled(ahk_env *env, const uint8_t *robot_dev, const uint8_t *human_dev, void *stream, float *env_ms,
+                      float *raster_ms);
+
 /* ≙ DataProcessor.process_observation's return value (processor.py:52-64) materialised from the ring:
  * AHK_OBS_U8 uint8[n][9][128][128] newest first; AHK_OBS_RGB_F32 float[n][9][128][128] = (x-128)/128;
  * AHK_OBS_GRAY_DIFF_F64 double[n][1][128][128]. */

@@ -31,6 +31,10 @@ int fail(int code, const char *fmt, ...)
 
 } // namespace
 
+namespace ahk {
+void set_error_text(const char *text) { snprintf(g_error, sizeof g_error, "%s", text); }
+} // namespace ahk
+
 struct ahk_env {
     ahk_config cfg{};
     ahk_buffers buf{};

@@ -43,6 +43,8 @@ struct ObserveArgs {
     int n, head, format;
 };
 
+void set_error_text(const char *text); // ahk_api.cu: fills the buffer behind ahk_last_error()
+
 cudaError_t launch_env(const EnvArgs &a, bool step, cudaStream_t stream);
 cudaError_t raster_prepare();
 cudaError_t launch_raster(const RasterArgs &a, int grid, cudaStream_t stream);

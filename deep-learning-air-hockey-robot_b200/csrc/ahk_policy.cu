@@ -1,0 +1,568 @@
+// ahk_policy.cu — K3: forward pass of the reference's 'rgb' CNN policy on the frame ring, on 5th-gen tensor cores.
+//
+// Network (ai/supervised/keras/models.py:20-65, Keras defaults: valid padding, bias, BatchNorm eps 1e-3 AFTER the ReLU):
+//   (9,128,128) -> conv1 5xk8 s3 + ReLU + BN -> (5,41,41) -> conv2 32xk4 s2 + ReLU + BN -> (32,19,19)
+//   -> conv3 64xk4 s2 + ReLU + BN -> (64,8,8) -> flatten (C,H,W) -> dense 512 ReLU -> dense 512 ReLU -> dense 10.
+// Used by the reference at batch 1 per env step (ai/reinforcement/rl_agents.py:78-98, ai/supervised/keras/test.py:42-43);
+// here at batch = number of envs, reading the uint8 ring the rasteriser just wrote (no float observation is built).
+//
+// Every layer is a GEMM  D[M x N] = act(A[M x K] * B[K x N] + bias)  issued as tcgen05.mma (kind::f16, bf16 operands,
+// fp32 accumulators in TMEM), one 128-row tile per CTA:
+//   * B (weights) is pre-packed on the host into the canonical no-swizzle K-major core-matrix layout, one contiguous
+//     blob per 64-wide K chunk, and lands in shared memory with ONE cp.async.bulk per chunk (mbarrier complete_tx);
+//   * A is gathered by the CTA's 128 threads (thread = tile row) straight into the same canonical layout — im2col on
+//     the fly for the convolutions; for conv1 from a bf16 copy of the needed input rows staged in shared memory,
+//     so each uint8 is converted once;
+//   * two smem stages; tcgen05.commit -> mbarrier recycles a stage when the MMAs that read it have retired;
+//   * epilogue: tcgen05.ld 32x32b (thread = TMEM lane = tile row), bias, ReLU, bf16, 16-byte stores.
+// Folded on the host, exactly: the input normalisation (x-128)/128 into conv1, and each BatchNorm (an affine map applied
+// after the ReLU) into the NEXT layer's weights and bias.
+#include "../../include/ahk.h"
+#include "ahk_kernels.cuh"
+
+#include <cuda_bf16.h>
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <vector>
+
+namespace ahk {
+namespace policy {
+
+constexpr int kBM = 128;     // rows per tile = UMMA M
+constexpr int kBK = 64;      // K per pipeline stage = 8 core matrices of 8 bf16
+constexpr int kThreads = 128;
+constexpr int kABytes = kBM * kBK * 2; // 16 KB per stage
+
+// ---- geometry of the network (models.py:20-65)
+constexpr int kC1 = 41, kP1 = kC1 * kC1; // conv1 output side / pixels
+constexpr int kC2 = 19, kP2 = kC2 * kC2;
+constexpr int kC3 = 8, kP3 = kC3 * kC3;
+constexpr int kAct1C = 8;                // conv1 channels 5 padded to 8 (one 16-byte K core per tap for conv2)
+
+enum Layer { kConv1 = 0, kConv2, kConv3, kDense1, kDense2, kOut };
+
+template <int L> struct Traits;
+template <> struct Traits<kConv1> { static constexpr int N = 16, K = 576, NSplit = 1; };  // 5 real outputs
+template <> struct Traits<kConv2> { static constexpr int N = 32, K = 128, NSplit = 1; };  // K = 16 taps x 8 (5 real)
+template <> struct Traits<kConv3> { static constexpr int N = 64, K = 512, NSplit = 1; };  // K = 16 taps x 32
+template <> struct Traits<kDense1> { static constexpr int N = 256, K = 4096, NSplit = 2; }; // 512 outputs in two halves
+template <> struct Traits<kDense2> { static constexpr int N = 256, K = 512, NSplit = 2; };
+template <> struct Traits<kOut> { static constexpr int N = 16, K = 512, NSplit = 1; };     // 10 real outputs
+
+struct Args {
+    const uint8_t *frames;      // conv1: the ring [3][n][3][128][128]
+    const __nv_bfloat16 *in;    // other layers: input activations
+    const uint4 *weights;       // packed B blobs: [NSplit][K/64] chunks of N*128 bytes
+    const float *bias;          // [NSplit * N]
+    __nv_bfloat16 *out;         // output activations (bf16)
+    float *logits;              // kOut: float [n][10]
+    uint8_t *action;            // kOut: argmax
+    int n;                      // samples
+    int m_total;                // valid rows of the flattened GEMM (conv1: per sample)
+    int head;
+};
+
+// ------------------------------------------------------------------------------------------------ PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
+
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) { asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(bar)), "r"(count) : "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) { asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(bar)), "r"(bytes) : "memory"); }
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n\t.reg .pred done;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 done, [%0], %1;\n\t"
+        "@!done bra WAIT_%=;\n\t}"
+        :: "r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_load(void *smem_dst, const void *gmem_src, uint32_t bytes, uint64_t *bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 :: "r"(smem_u32(smem_dst)), "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ void tmem_alloc(uint32_t *result_in_smem, uint32_t cols)
+{ // one full warp
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(smem_u32(result_in_smem)), "r"(cols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols)
+{
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(taddr), "r"(cols) : "memory");
+}
+
+// D[tmem] (+)= A[smem] * B[smem], M = 128, K = 16, bf16 x bf16 -> f32, issued by ONE thread
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// the mbarrier gets one arrival when every tcgen05 op issued so far by this thread has completed
+__device__ __forceinline__ void umma_commit(uint64_t *bar)
+{
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(smem_u32(bar)) : "memory");
+}
+
+// 16 consecutive fp32 columns of this thread's TMEM lane
+__device__ __forceinline__ void tmem_load16(uint32_t taddr, float (&v)[16])
+{
+    uint32_t r[16];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr) : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// shared-memory matrix descriptor, no swizzle, K-major (cute::UMMA::SmemDescriptor, version 1):
+//   LBO = bytes between the two K core matrices of one MMA, SBO = bytes between 8-row groups
+__device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t lbo, uint32_t sbo)
+{
+    return static_cast<uint64_t>((addr & 0x3FFFFu) >> 4) | static_cast<uint64_t>(lbo >> 4) << 16 |
+           static_cast<uint64_t>(sbo >> 4) << 32 | 1ull << 46;
+}
+// instruction descriptor (cute::UMMA::InstrDescriptor): D f32, A/B bf16, both K-major, M = 128
+__host__ __device__ constexpr uint32_t instr_desc(int n) { return 1u << 4 | 1u << 7 | 1u << 10 | static_cast<uint32_t>(n >> 3) << 17 | (128u >> 4) << 24; }
+
+// ------------------------------------------------------------------------------------------------ A gathers
+__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi)
+{ // exact for the integers 0..255; general values: truncation is never used (see cvt below for activations)
+    return __byte_perm(__float_as_uint(lo), __float_as_uint(hi), 0x7632);
+}
+
+// 4 uint8 -> 4 bf16 (exact): 0x4B0000xx is 8388608 + xx as a float
+__device__ __forceinline__ uint2 u8x4_to_bf16x4(uint32_t w)
+{
+    const float f0 = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7440)) - 8388608.0f;
+    const float f1 = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7441)) - 8388608.0f;
+    const float f2 = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7442)) - 8388608.0f;
+    const float f3 = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7443)) - 8388608.0f;
+    return make_uint2(pack_bf16(f0, f1), pack_bf16(f2, f3));
+}
+
+constexpr int kTileRows = 20;  // input rows one conv1 tile can touch: 5 output rows x stride 3 + (8 - 3)
+constexpr int kTilePitch = 136; // bf16 elements per staged row (128 + pad: keeps 8-element reads in range)
+constexpr int kConv1StageBytes = 9 * kTileRows * kTilePitch * 2;
+
+template <int L>
+__device__ __forceinline__ uint4 gather(const Args &a, const uint8_t *tile, int row_ok, int r0, int r1, int r2, int kc)
+{
+    // r0, r1, r2: per-row constants prepared by the caller (see kernel); kc: K core index (8 elements each)
+    if (!row_ok) return make_uint4(0, 0, 0, 0);
+    if (L == kConv1) {
+        // kc = c * 8 + ky ; r0 = byte offset of tile[0][3 (Y - Y0)][3 X] ; chunk = 8 consecutive kx
+        const int off = r0 + ((kc >> 3) * kTileRows + (kc & 7)) * (kTilePitch * 2);
+        const uint32_t *w = reinterpret_cast<const uint32_t *>(tile + (off & ~3));
+        const uint32_t sh = (off & 2) * 8;
+        const uint32_t w0 = w[0], w1 = w[1], w2 = w[2], w3 = w[3], w4 = w[4];
+        return make_uint4(__funnelshift_r(w0, w1, sh), __funnelshift_r(w1, w2, sh), __funnelshift_r(w2, w3, sh), __funnelshift_r(w3, w4, sh));
+    }
+    if (L == kConv2) { // kc = tap ; r0 = element offset of act1[s][2Y*41 + 2X][0]
+        const int ky = kc >> 2, kx = kc & 3;
+        return __ldg(reinterpret_cast<const uint4 *>(a.in + r0 + (ky * kC1 + kx) * kAct1C));
+    }
+    if (L == kConv3) { // kc = tap * 4 + channel block ; r0 = element offset of act2[s][2Y*19 + 2X][0]
+        const int tap = kc >> 2, cb = kc & 3, ky = tap >> 2, kx = tap & 3;
+        return __ldg(reinterpret_cast<const uint4 *>(a.in + r0 + (ky * kC2 + kx) * 32 + cb * 8));
+    }
+    // dense: r0 = element offset of in[row][0]
+    return __ldg(reinterpret_cast<const uint4 *>(a.in + r0 + kc * 8));
+}
+
+// ------------------------------------------------------------------------------------------------ the GEMM tile kernel
+template <int L>
+__global__ void __launch_bounds__(kThreads) layer_kernel(Args a)
+{
+    using T = Traits<L>;
+    constexpr int N = T::N, NCH = T::K / kBK;
+    constexpr int kBBytes = N * kBK * 2;
+    constexpr uint32_t kTmemCols = N < 32 ? 32 : N;
+
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint8_t *s_a = smem;                      // [2][16 KB]
+    uint8_t *s_b = smem + 2 * kABytes;        // [2][kBBytes]
+    uint8_t *s_tile = s_b + 2 * kBBytes;      // conv1 only: bf16 [9][20][136]
+    __shared__ __align__(8) uint64_t s_full[2], s_free[2], s_done;
+    __shared__ uint32_t s_tmem;
+    __shared__ float s_bias[N];
+
+    const int tid = threadIdx.x, warp = tid >> 5;
+    const int split = L == kConv1 ? 0 : blockIdx.y;         // which N half (dense layers)
+    const int sample = L == kConv1 ? blockIdx.x : 0;        // conv1: grid = (sample, tile of the 41x41 output)
+    const int tile_idx = L == kConv1 ? blockIdx.y : blockIdx.x;
+    const int row = tile_idx * kBM + tid;                   // row of the (flattened) GEMM this thread owns
+    const bool row_ok = row < a.m_total;
+
+    if (tid == 0) {
+        mbar_init(&s_full[0], 1); mbar_init(&s_full[1], 1);
+        mbar_init(&s_free[0], 1); mbar_init(&s_free[1], 1);
+        mbar_init(&s_done, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (tid < N) s_bias[tid] = a.bias[split * N + tid];
+    if (N > kThreads) for (int i = tid + kThreads; i < N; i += kThreads) s_bias[i] = a.bias[split * N + i];
+    if (warp == 0) tmem_alloc(&s_tmem, kTmemCols);
+
+    // ---- per-row constants of the gather
+    int r0 = 0;
+    if (L == kConv1) {
+        const int p0 = tile_idx * kBM, y0 = p0 / kC1;
+        const int y_last = min(kC1 - 1, (p0 + kBM - 1) / kC1);
+        const int rows = 3 * (y_last - y0) + 8; // input rows 3*y0 .. 3*y_last + 7
+        // stage the needed input rows of the 9 planes as bf16: plane c = (age c/3, colour c%3), newest frame first
+        for (int v = tid; v < 9 * kTileRows * 8; v += kThreads) { // one 16-pixel vector per trip
+            const int c = v / (kTileRows * 8), rem = v - c * (kTileRows * 8), rr = rem >> 3, xv = rem & 7;
+            uint4 px = make_uint4(0, 0, 0, 0);
+            if (rr < rows) {
+                const int slot = (a.head + 3 - c / 3) % 3;
+                const uint8_t *src = a.frames + ((static_cast<size_t>(slot) * a.n + sample) * 3 + (c % 3)) * (kDim * kDim) +
+                                     (3 * y0 + rr) * kDim + xv * 16;
+                px = __ldg(reinterpret_cast<const uint4 *>(src));
+            }
+            const uint2 q0 = u8x4_to_bf16x4(px.x), q1 = u8x4_to_bf16x4(px.y), q2 = u8x4_to_bf16x4(px.z), q3 = u8x4_to_bf16x4(px.w);
+            uint4 *dst = reinterpret_cast<uint4 *>(s_tile + ((c * kTileRows + rr) * kTilePitch + xv * 16) * 2);
+            dst[0] = make_uint4(q0.x, q0.y, q1.x, q1.y);
+            dst[1] = make_uint4(q2.x, q2.y, q3.x, q3.y);
+        }
+        for (int v = tid; v < 9 * kTileRows; v += kThreads) // zero the 8-element pad of each row
+            *reinterpret_cast<uint4 *>(s_tile + (v * kTilePitch + 128) * 2) = make_uint4(0, 0, 0, 0);
+        if (row_ok) {
+            const int y = row / kC1, x = row - y * kC1;
+            r0 = ((3 * (y - y0)) * kTilePitch + 3 * x) * 2;
+        }
+    } else if (L == kConv2) {
+        if (row_ok) {
+            const int s = row / kP2, p = row - s * kP2, y = p / kC2, x = p - y * kC2;
+            r0 = (s * kP1 + 2 * y * kC1 + 2 * x) * kAct1C;
+        }
+    } else if (L == kConv3) {
+        if (row_ok) {
+            const int s = row / kP3, p = row - s * kP3, y = p / kC3, x = p - y * kC3;
+            r0 = (s * kP2 + 2 * y * kC2 + 2 * x) * 32;
+        }
+    } else {
+        r0 = row * T::K;
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = s_tmem;
+
+    const uint4 *wsrc = a.weights + static_cast<size_t>(split) * NCH * (kBBytes / 16);
+    constexpr uint32_t kIdesc = instr_desc(N);
+
+#pragma unroll 1
+    for (int ch = 0; ch < NCH; ++ch) {
+        const int st = ch & 1, use = ch >> 1;
+        if (ch >= 2) mbar_wait(&s_free[st], (use - 1) & 1); // the MMAs that read this stage have retired
+        if (tid == 0) {
+            mbar_expect_tx(&s_full[st], kBBytes);
+            bulk_load(s_b + st * kBBytes, wsrc + static_cast<size_t>(ch) * (kBBytes / 16), kBBytes, &s_full[st]);
+        }
+        // A: this thread's row, 8 K cores of 16 bytes each -> canonical layout [K core][row group][row % 8]
+        uint8_t *dst = s_a + st * kABytes + (tid >> 3) * 128 + (tid & 7) * 16;
+#pragma unroll
+        for (int kc = 0; kc < 8; ++kc)
+            *reinterpret_cast<uint4 *>(dst + kc * (16 * 128)) = gather<L>(a, s_tile, row_ok, r0, 0, 0, ch * 8 + kc);
+        fence_async_smem();
+        __syncthreads();
+        if (tid == 0) {
+            mbar_wait(&s_full[st], use & 1);
+            tc_fence_after();
+            const uint32_t a_base = smem_u32(s_a + st * kABytes), b_base = smem_u32(s_b + st * kBBytes);
+#pragma unroll
+            for (int j = 0; j < kBK / 16; ++j) {
+                const uint64_t ad = smem_desc(a_base + j * 2 * (16 * 128), 16 * 128, 128);
+                const uint64_t bd = smem_desc(b_base + j * 2 * (N / 8 * 128), N / 8 * 128, 128);
+                umma_bf16(tmem, ad, bd, kIdesc, (ch | j) != 0);
+            }
+            umma_commit(&s_free[st]);
+            if (ch == NCH - 1) umma_commit(&s_done);
+        }
+    }
+    mbar_wait(&s_done, 0);
+    tc_fence_after();
+
+    // ---- epilogue: thread = TMEM lane = tile row
+    const uint32_t lane_addr = tmem + (static_cast<uint32_t>(warp * 32) << 16);
+    if (L == kOut) {
+        float v[16];
+        tmem_load16(lane_addr, v);
+        if (row_ok) {
+            int best = 0;
+            float best_v = v[0] + s_bias[0];
+#pragma unroll
+            for (int j = 0; j < AHK_N_ACTIONS; ++j) {
+                const float q = v[j] + s_bias[j];
+                if (a.logits) a.logits[static_cast<size_t>(row) * AHK_N_ACTIONS + j] = q;
+                if (q > best_v) { best_v = q; best = j; }
+            }
+            if (a.action) a.action[row] = static_cast<uint8_t>(best);
+        }
+    } else {
+        constexpr int kStore = L == kConv1 ? kAct1C : N;              // channels written per row
+        constexpr int kOutPitch = L == kConv1 ? kAct1C : (T::NSplit * N); // elements per output row
+        const size_t out_row = L == kConv1 ? static_cast<size_t>(sample) * kP1 + row : static_cast<size_t>(row);
+        __nv_bfloat16 *out = a.out + out_row * kOutPitch + split * N;
+#pragma unroll 1
+        for (int c0 = 0; c0 < kStore; c0 += 16) {
+            float v[16];
+            tmem_load16(lane_addr + c0, v);
+            uint32_t packed[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float lo = fmaxf(v[2 * j] + s_bias[c0 + 2 * j], 0.0f), hi = fmaxf(v[2 * j + 1] + s_bias[c0 + 2 * j + 1], 0.0f);
+                const __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+                packed[j] = *reinterpret_cast<const uint32_t *>(&h);
+            }
+            if (row_ok) {
+                *reinterpret_cast<uint4 *>(out + c0) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+                if (kStore - c0 > 8) *reinterpret_cast<uint4 *>(out + c0 + 8) = make_uint4(packed[4], packed[5], packed[6], packed[7]);
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem, kTmemCols);
+}
+
+template <int L> constexpr int smem_bytes() { return 2 * kABytes + 2 * Traits<L>::N * kBK * 2 + (L == kConv1 ? kConv1StageBytes : 0); }
+
+template <int L>
+cudaError_t launch(const Args &a, int tiles, int grid_y, cudaStream_t s)
+{
+    static bool prepared = false;
+    if (!prepared) {
+        cudaError_t e = cudaFuncSetAttribute(layer_kernel<L>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<L>());
+        if (e != cudaSuccess) return e;
+        prepared = true;
+    }
+    layer_kernel<L><<<dim3(tiles, grid_y), kThreads, smem_bytes<L>(), s>>>(a);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------ host: fold + pack
+uint16_t to_bf16(float f)
+{ // round to nearest even
+    uint32_t u;
+    memcpy(&u, &f, 4);
+    if ((u & 0x7F800000u) == 0x7F800000u) return static_cast<uint16_t>(u >> 16);
+    u += 0x7FFFu + ((u >> 16) & 1u);
+    return static_cast<uint16_t>(u >> 16);
+}
+
+// W: [K][n_real] row-major (fp32, already folded) -> bf16 blobs [n_split][K/64][K core 0..7][n_pad/8 groups][8 n][8 k]
+std::vector<uint16_t> pack_b(const std::vector<float> &w, int k_total, int n_real, int n_pad, int n_split)
+{
+    std::vector<uint16_t> out(static_cast<size_t>(k_total) * n_pad * n_split, 0);
+    const int groups = n_pad / 8;
+    for (int sp = 0; sp < n_split; ++sp)
+        for (int k = 0; k < k_total; ++k)
+            for (int n = 0; n < n_pad; ++n) {
+                const int col = sp * n_pad + n;
+                const float v = col < n_real ? w[static_cast<size_t>(k) * n_real + col] : 0.0f;
+                const int ch = k / kBK, kc = (k % kBK) / 8, ke = k % 8;
+                const size_t at = ((static_cast<size_t>(sp) * (k_total / kBK) + ch) * 8 + kc) * groups * 64 +
+                                  static_cast<size_t>(n / 8) * 64 + (n % 8) * 8 + ke;
+                out[at] = to_bf16(v);
+            }
+    return out;
+}
+
+} // namespace policy
+} // namespace ahk
+
+// ------------------------------------------------------------------------------------------------ C ABI
+using namespace ahk::policy;
+
+struct ahk_policy {
+    int device = 0, max_batch = 0;
+    uint16_t *w[6] = {};
+    float *b[6] = {};
+    __nv_bfloat16 *act1 = nullptr, *act2 = nullptr, *act3 = nullptr, *h1 = nullptr, *h2 = nullptr;
+    uint64_t launches = 0;
+};
+
+namespace {
+
+int pfail(int code, const char *fmt, const char *detail)
+{
+    char text[512];
+    snprintf(text, sizeof text, fmt, detail);
+    ahk::set_error_text(text); // the thread-local buffer behind ahk_last_error() lives in ahk_api.cu
+    return code;
+}
+
+#define POL_CUDA(expr)                                                                       \
+    do {                                                                                     \
+        cudaError_t err__ = (expr);                                                          \
+        if (err__ != cudaSuccess) return pfail(AHK_ERR_CUDA, #expr ": %s", cudaGetErrorString(err__)); \
+    } while (0)
+
+int upload(const std::vector<uint16_t> &w, const std::vector<float> &b, uint16_t **wd, float **bd)
+{
+    POL_CUDA(cudaMalloc(wd, w.size() * 2));
+    POL_CUDA(cudaMemcpy(*wd, w.data(), w.size() * 2, cudaMemcpyHostToDevice));
+    POL_CUDA(cudaMalloc(bd, b.size() * 4));
+    POL_CUDA(cudaMemcpy(*bd, b.data(), b.size() * 4, cudaMemcpyHostToDevice));
+    return AHK_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+int ahk_policy_create(int device, int max_batch, const ahk_policy_weights *w, ahk_policy **out)
+{
+    if (!w || !out || max_batch <= 0 || max_batch > 131072) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_create: bad argument (max_batch must be in [1, 131072])");
+    const float *const *fields = reinterpret_cast<const float *const *>(w);
+    for (int i = 0; i < 24; ++i)
+        if (!fields[i]) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_create: every weight pointer must be non-NULL");
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) return pfail(AHK_ERR_NO_DEVICE, "%s", "no CUDA device: the policy has no CPU fallback");
+    POL_CUDA(cudaSetDevice(device));
+
+    // BatchNorm after the ReLU is the affine map y = s * r + t per channel (eps = 1e-3, Keras default)
+    auto affine = [](const float *gamma, const float *beta, const float *mean, const float *var, int c, std::vector<float> &s, std::vector<float> &t) {
+        s.resize(c); t.resize(c);
+        for (int i = 0; i < c; ++i) {
+            s[i] = gamma[i] / std::sqrt(var[i] + 1e-3f);
+            t[i] = beta[i] - mean[i] * s[i];
+        }
+    };
+    std::vector<float> s1, t1, s2, t2, s3, t3;
+    affine(w->bn1_gamma, w->bn1_beta, w->bn1_mean, w->bn1_var, 5, s1, t1);
+    affine(w->bn2_gamma, w->bn2_beta, w->bn2_mean, w->bn2_var, 32, s2, t2);
+    affine(w->bn3_gamma, w->bn3_beta, w->bn3_mean, w->bn3_var, 64, s3, t3);
+
+    ahk_policy *p = new ahk_policy();
+    p->device = device;
+    p->max_batch = max_batch;
+    int rc = AHK_OK;
+
+    { // conv1: Keras kernel [ky][kx][c][o]; GEMM k = c*64 + ky*8 + kx; (x-128)/128 folded: W/128, b - sum(W)
+        std::vector<float> wf(576 * 5), bf(16, 0.0f);
+        for (int o = 0; o < 5; ++o) {
+            double sum = 0.0;
+            for (int ky = 0; ky < 8; ++ky) for (int kx = 0; kx < 8; ++kx) for (int c = 0; c < 9; ++c) {
+                const float v = w->conv1_w[((ky * 8 + kx) * 9 + c) * 5 + o];
+                wf[(c * 64 + ky * 8 + kx) * 5 + o] = v / 128.0f;
+                sum += v;
+            }
+            bf[o] = w->conv1_b[o] - static_cast<float>(sum);
+        }
+        rc = upload(pack_b(wf, 576, 5, 16, 1), bf, &p->w[0], &p->b[0]);
+    }
+    if (rc == AHK_OK) { // conv2: k = (ky*4+kx)*8 + c, BN1 folded
+        std::vector<float> wf(128 * 32, 0.0f), bf(32);
+        for (int o = 0; o < 32; ++o) {
+            double add = 0.0;
+            for (int ky = 0; ky < 4; ++ky) for (int kx = 0; kx < 4; ++kx) for (int c = 0; c < 5; ++c) {
+                const float v = w->conv2_w[((ky * 4 + kx) * 5 + c) * 32 + o];
+                wf[((ky * 4 + kx) * 8 + c) * 32 + o] = v * s1[c];
+                add += static_cast<double>(v) * t1[c];
+            }
+            bf[o] = w->conv2_b[o] + static_cast<float>(add);
+        }
+        rc = upload(pack_b(wf, 128, 32, 32, 1), bf, &p->w[1], &p->b[1]);
+    }
+    if (rc == AHK_OK) { // conv3: k = (ky*4+kx)*32 + c, BN2 folded
+        std::vector<float> wf(512 * 64), bf(64);
+        for (int o = 0; o < 64; ++o) {
+            double add = 0.0;
+            for (int ky = 0; ky < 4; ++ky) for (int kx = 0; kx < 4; ++kx) for (int c = 0; c < 32; ++c) {
+                const float v = w->conv3_w[((ky * 4 + kx) * 32 + c) * 64 + o];
+                wf[((ky * 4 + kx) * 32 + c) * 64 + o] = v * s2[c];
+                add += static_cast<double>(v) * t2[c];
+            }
+            bf[o] = w->conv3_b[o] + static_cast<float>(add);
+        }
+        rc = upload(pack_b(wf, 512, 64, 64, 1), bf, &p->w[2], &p->b[2]);
+    }
+    if (rc == AHK_OK) { // dense1: Keras flatten index f = c*64 + pixel; ours k = pixel*64 + c; BN3 folded
+        std::vector<float> wf(static_cast<size_t>(4096) * 512), bf(512);
+        std::vector<double> add(512, 0.0);
+        for (int c = 0; c < 64; ++c) for (int px = 0; px < 64; ++px) {
+            const float *src = w->dense1_w + static_cast<size_t>(c * 64 + px) * 512;
+            float *dst = wf.data() + static_cast<size_t>(px * 64 + c) * 512;
+            for (int o = 0; o < 512; ++o) { dst[o] = src[o] * s3[c]; add[o] += static_cast<double>(src[o]) * t3[c]; }
+        }
+        for (int o = 0; o < 512; ++o) bf[o] = w->dense1_b[o] + static_cast<float>(add[o]);
+        rc = upload(pack_b(wf, 4096, 512, 256, 2), bf, &p->w[3], &p->b[3]);
+    }
+    if (rc == AHK_OK) {
+        std::vector<float> wf(w->dense2_w, w->dense2_w + 512 * 512), bf(w->dense2_b, w->dense2_b + 512);
+        rc = upload(pack_b(wf, 512, 512, 256, 2), bf, &p->w[4], &p->b[4]);
+    }
+    if (rc == AHK_OK) {
+        std::vector<float> wf(w->out_w, w->out_w + 512 * 10), bf(16, 0.0f);
+        for (int o = 0; o < 10; ++o) bf[o] = w->out_b[o];
+        rc = upload(pack_b(wf, 512, 10, 16, 1), bf, &p->w[5], &p->b[5]);
+    }
+    const size_t nb = static_cast<size_t>(max_batch);
+    cudaError_t err = cudaSuccess;
+    if (rc == AHK_OK) {
+        err = cudaMalloc(&p->act1, nb * kP1 * kAct1C * 2);
+        if (err == cudaSuccess) err = cudaMalloc(&p->act2, nb * kP2 * 32 * 2);
+        if (err == cudaSuccess) err = cudaMalloc(&p->act3, nb * 4096 * 2);
+        if (err == cudaSuccess) err = cudaMalloc(&p->h1, nb * 512 * 2);
+        if (err == cudaSuccess) err = cudaMalloc(&p->h2, nb * 512 * 2);
+    }
+    if (rc != AHK_OK || err != cudaSuccess) {
+        ahk_policy_destroy(p);
+        return rc != AHK_OK ? rc : pfail(AHK_ERR_CUDA, "ahk_policy_create: %s", cudaGetErrorString(err));
+    }
+    *out = p;
+    return AHK_OK;
+}
+
+void ahk_policy_destroy(ahk_policy *p)
+{
+    if (!p) return;
+    cudaSetDevice(p->device);
+    for (int i = 0; i < 6; ++i) { if (p->w[i]) cudaFree(p->w[i]); if (p->b[i]) cudaFree(p->b[i]); }
+    cudaFree(p->act1); cudaFree(p->act2); cudaFree(p->act3); cudaFree(p->h1); cudaFree(p->h2);
+    delete p;
+}
+
+int ahk_policy_forward(ahk_policy *p, const uint8_t *frames, int n, int head, float *logits, uint8_t *action, void *stream)
+{
+    if (!p || !frames) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_forward: policy/frames is NULL");
+    if (n <= 0 || n > p->max_batch) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_forward: n must be in [1, max_batch]");
+    if (head < 0 || head > 2) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_forward: head must be 0, 1 or 2");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    auto tiles = [](long long rows) { return static_cast<int>((rows + kBM - 1) / kBM); };
+    Args a{};
+    a.n = n;
+    a.head = head;
+
+    a.frames = frames; a.weights = reinterpret_cast<const uint4 *>(p->w[0]); a.bias = p->b[0]; a.out = p->act1; a.m_total = kP1;
+    POL_CUDA(launch<kConv1>(a, n, tiles(kP1), s));
+    a.in = p->act1; a.weights = reinterpret_cast<const uint4 *>(p->w[1]); a.bias = p->b[1]; a.out = p->act2; a.m_total = n * kP2;
+    POL_CUDA(launch<kConv2>(a, tiles(static_cast<long long>(n) * kP2), 1, s));
+    a.in = p->act2; a.weights = reinterpret_cast<const uint4 *>(p->w[2]); a.bias = p->b[2]; a.out = p->act3; a.m_total = n * kP3;
+    POL_CUDA(launch<kConv3>(a, tiles(static_cast<long long>(n) * kP3), 1, s));
+    a.in = p->act3; a.weights = reinterpret_cast<const uint4 *>(p->w[3]); a.bias = p->b[3]; a.out = p->h1; a.m_total = n;
+    POL_CUDA(launch<kDense1>(a, tiles(n), 2, s));
+    a.in = p->h1; a.weights = reinterpret_cast<const uint4 *>(p->w[4]); a.bias = p->b[4]; a.out = p->h2; a.m_total = n;
+    POL_CUDA(launch<kDense2>(a, tiles(n), 2, s));
+    a.in = p->h2; a.weights = reinterpret_cast<const uint4 *>(p->w[5]); a.bias = p->b[5]; a.out = nullptr; a.logits = logits; a.action = action; a.m_total = n;
+    POL_CUDA(launch<kOut>(a, tiles(n), 1, s));
+    p->launches += 6;
+    return AHK_OK;
+}
+
+} // extern "C"

@@ -70,8 +70,6 @@ def load():
             "The engine has no CPU or PyTorch fallback." % LIB_PATH)
     lib = C.CDLL(LIB_PATH)
     for name, (restype, argtypes) in SYMBOLS.items():
-        if name.startswith("ahk_policy") and not hasattr(lib, name):
-            continue  # TEMPORARY until ahk_policy.cu lands
         fn = getattr(lib, name)  # AttributeError if the ABI and the binding disagree
         fn.restype = restype
         fn.argtypes = argtypes

@@ -1,0 +1,102 @@
+"""The reference's 'rgb' CNN policy (ai/supervised/keras/models.py:20-65) as a forward pass on the frame ring.
+
+`PolicyNetwork` owns an `ahk_policy` handle (include/ahk.h): six tcgen05 GEMM-tile kernels (csrc/ahk_policy.cu) that
+read the rasteriser's uint8 ring directly — the float32 (9,128,128) observation the reference feeds to
+`model.predict` (ai/reinforcement/rl_agents.py:78-98, ai/supervised/keras/test.py:42-43) is never materialised.
+Weights are given in Keras layouts (conv kernels [kh][kw][cin][cout], dense [in][out], BatchNorm gamma/beta/moving
+mean/moving variance), i.e. what `model.get_weights()` returns, so a trained `.h5` can be loaded by name.
+"""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+
+# name -> shape, in the order of ahk_policy_weights (include/ahk.h)
+SHAPES = (
+    ("conv1_w", (8, 8, 9, 5)), ("conv1_b", (5,)), ("bn1_gamma", (5,)), ("bn1_beta", (5,)), ("bn1_mean", (5,)), ("bn1_var", (5,)),
+    ("conv2_w", (4, 4, 5, 32)), ("conv2_b", (32,)), ("bn2_gamma", (32,)), ("bn2_beta", (32,)), ("bn2_mean", (32,)), ("bn2_var", (32,)),
+    ("conv3_w", (4, 4, 32, 64)), ("conv3_b", (64,)), ("bn3_gamma", (64,)), ("bn3_beta", (64,)), ("bn3_mean", (64,)), ("bn3_var", (64,)),
+    ("dense1_w", (4096, 512)), ("dense1_b", (512,)), ("dense2_w", (512, 512)), ("dense2_b", (512,)),
+    ("out_w", (512, 10)), ("out_b", (10,)),
+)
+FLOPS_PER_SAMPLE = 2 * 10227008
+
+
+def keras_default_init(seed=0, randomize_bn=False):
+    """Random-init weights the way Keras builds models.py:20-65: Glorot-uniform kernels, zero biases, BatchNorm
+    gamma 1 / beta 0 / mean 0 / variance 1.  randomize_bn=True draws non-trivial BatchNorm statistics instead (tests)."""
+    rs = np.random.RandomState(seed)
+    w = {}
+    for name, shape in SHAPES:
+        if name.endswith("_w"):
+            receptive = int(np.prod(shape[:-2])) if len(shape) == 4 else 1
+            fan_in, fan_out = receptive * shape[-2], receptive * shape[-1]
+            limit = np.sqrt(6.0 / (fan_in + fan_out))
+            w[name] = rs.uniform(-limit, limit, size=shape).astype(np.float32)
+        elif name.endswith(("_gamma", "_var")):
+            w[name] = (rs.uniform(0.5, 1.5, size=shape) if randomize_bn else np.ones(shape)).astype(np.float32)
+        elif name.endswith("_b") and randomize_bn:
+            w[name] = rs.uniform(-0.1, 0.1, size=shape).astype(np.float32)
+        elif randomize_bn:
+            w[name] = rs.uniform(-0.2, 0.2, size=shape).astype(np.float32)
+        else:
+            w[name] = np.zeros(shape, dtype=np.float32)
+    return w
+
+
+class PolicyNetwork(object):
+    """forward(env) -> (logits float32[N,10], action uint8[N]) as CUDA tensors, on the current stream.
+
+    logits are pre-softmax (the DDQN head of rl_agents.py:160-172 is linear; softmax(logits) is the supervised
+    model's output, models.py:62-65), action = argmax — what keras/test.py:42-43 feeds back into env.step."""
+
+    def __init__(self, weights=None, max_batch=4096, device=0):
+        self.lib = _lib.load()
+        if not torch.cuda.is_available():
+            raise RuntimeError('PolicyNetwork needs a CUDA device; there is no CPU fallback')
+        self.device = torch.device('cuda', device)
+        self.max_batch = int(max_batch)
+        weights = keras_default_init() if weights is None else weights
+        self.weights = {}
+        st = _lib.PolicyWeights()
+        for name, shape in SHAPES:
+            a = np.ascontiguousarray(weights[name], dtype=np.float32)
+            if a.shape != shape:
+                raise ValueError('%s: expected shape %s, got %s' % (name, shape, a.shape))
+            self.weights[name] = a  # keeps the host memory alive during ahk_policy_create
+            setattr(st, name, a.ctypes.data_as(C.c_void_p))
+        h = C.c_void_p()
+        _lib.check(self.lib.ahk_policy_create(self.device.index, self.max_batch, C.byref(st), C.byref(h)))
+        self._h = h
+        self.launches = 0
+
+    def forward_ring(self, frames, head, logits=None, action=None):
+        """frames: uint8 CUDA tensor [3, n, 3, 128, 128] (the env's ring), head: newest slot."""
+        n = frames.shape[1]
+        if frames.dtype != torch.uint8 or tuple(frames.shape) != (3, n, 3, 128, 128) or not frames.is_contiguous():
+            raise ValueError('frames must be a contiguous uint8 [3, n, 3, 128, 128] ring')
+        if logits is None:
+            logits = torch.empty((n, 10), dtype=torch.float32, device=self.device)
+        if action is None:
+            action = torch.empty((n,), dtype=torch.uint8, device=self.device)
+        stream = C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+        _lib.check(self.lib.ahk_policy_forward(self._h, C.c_void_p(frames.data_ptr()), n, int(head),
+                                               C.c_void_p(logits.data_ptr()), C.c_void_p(action.data_ptr()), stream))
+        self.launches += 6
+        return logits, action
+
+    def forward(self, env, logits=None, action=None):
+        return self.forward_ring(env.frames, env.head, logits, action)
+
+    def close(self):
+        if getattr(self, '_h', None):
+            self.lib.ahk_policy_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

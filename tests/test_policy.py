@@ -1,0 +1,84 @@
+"""CNN policy forward (ai/supervised/keras/models.py:20-65): the tcgen05 kernels against the PyTorch float32
+restatement (oracle/cnn_ref.py).
+
+Tolerance (stated here because north_star gives none for the network): operands are bfloat16 (8-bit mantissa), the
+accumulation float32.  Against the float32 model the logits must agree to 3e-2 of the logit range of the batch;
+against the same network with bfloat16 rounding at the kernels' rounding points (emulate_bf16) to 2e-3 — what is left
+there is accumulation order only.  Actions (argmax) must agree wherever the float32 top-2 margin exceeds the tolerance.
+"""
+import numpy as np
+import pytest
+
+
+def test_reference_restatement_shapes_and_consistency():
+    """CPU: the float32 restatement has the layer shapes models.py implies and the folded bf16 variant tracks it."""
+    import cnn_ref
+    from gym_air_hockey_b200.policy import FLOPS_PER_SAMPLE, SHAPES, keras_default_init
+    w = keras_default_init(seed=3, randomize_bn=True)
+    assert sum(int(np.prod(s)) for _, s in SHAPES) == 2404163          # parameter count
+    assert FLOPS_PER_SAMPLE == 20454016
+    obs = np.random.RandomState(0).randint(0, 256, size=(3, 9, 128, 128)).astype(np.uint8)
+    a = cnn_ref.forward(w, obs)
+    b = cnn_ref.forward(w, obs, emulate_bf16=True)
+    assert a.shape == (3, 10) and a.dtype == np.float32
+    scale = np.abs(a).max()
+    assert np.abs(a - b).max() <= 3e-2 * scale
+
+
+def test_keras_default_init_statistics():
+    from gym_air_hockey_b200.policy import keras_default_init
+    w = keras_default_init(seed=0)
+    assert np.all(w['bn1_gamma'] == 1) and np.all(w['bn2_var'] == 1) and np.all(w['conv1_b'] == 0)
+    lim = np.sqrt(6.0 / (8 * 8 * 9 + 8 * 8 * 5))
+    assert np.abs(w['conv1_w']).max() <= lim and np.abs(w['conv1_w']).max() > 0.9 * lim
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,source", [(1, "noise"), (37, "noise"), (200, "game")])
+def test_policy_forward_matches_reference(cuda, table, n, source):
+    import cnn_ref
+    from gym_air_hockey_b200 import BatchedAirHockeyEnv
+    from gym_air_hockey_b200.policy import PolicyNetwork, keras_default_init
+    torch = cuda
+    w = keras_default_init(seed=5, randomize_bn=True)
+    net = PolicyNetwork(w, max_batch=256)
+    if source == "game":
+        env = BatchedAirHockeyEnv(n, table=table, seed=9, max_episode_steps=50)
+        env.reset()
+        for _ in range(7):
+            env.step()
+        frames, head = env.frames, env.head
+    else:
+        frames = torch.from_numpy(np.random.RandomState(n).randint(0, 256, size=(3, n, 3, 128, 128)).astype(np.uint8)).cuda()
+        head = 1
+    logits, action = net.forward_ring(frames, head)
+    torch.cuda.synchronize()
+    logits, action = logits.cpu().numpy(), action.cpu().numpy()
+    fr = frames.cpu().numpy()
+    obs = np.concatenate([fr[(head + 3 - age) % 3] for age in range(3)], axis=1)  # newest first (processor.py:47-49)
+    ref32 = cnn_ref.forward(w, obs)
+    ref16 = cnn_ref.forward(w, obs, emulate_bf16=True)
+    scale = max(np.abs(ref32).max(), 1e-6)
+    assert np.isfinite(logits).all()
+    assert np.abs(logits - ref16).max() <= 2e-3 * scale, np.abs(logits - ref16).max() / scale
+    assert np.abs(logits - ref32).max() <= 3e-2 * scale, np.abs(logits - ref32).max() / scale
+    assert np.array_equal(action, logits.argmax(axis=1))
+    top2 = np.sort(ref32, axis=1)
+    clear = (top2[:, -1] - top2[:, -2]) > 6e-2 * scale
+    assert np.array_equal(action[clear], ref32.argmax(axis=1)[clear])
+
+
+@pytest.mark.gpu
+def test_policy_in_the_loop(cuda, table):
+    """keras/test.py:36-51 as a batched loop: frames -> CNN -> argmax -> env.step, all on the device."""
+    from gym_air_hockey_b200 import BatchedAirHockeyEnv
+    from gym_air_hockey_b200.policy import PolicyNetwork
+    n = 512
+    env = BatchedAirHockeyEnv(n, table=table, seed=1, max_episode_steps=64)
+    net = PolicyNetwork(max_batch=n)
+    env.reset()
+    for _ in range(20):
+        _, action = net.forward(env)
+        _, reward, done, info = env.step(action, None)
+        assert cuda.equal(info['robot_action'], cuda.where(action == 9, cuda.full_like(action, 4), action))  # label 9 -> stand -> 4
+    assert env.statistics()['steps'] == 20 * n

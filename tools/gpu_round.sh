@@ -1,0 +1,22 @@
+#!/bin/bash
+# One gpurun call: GPU parity tests, bench line, ncu launch list and one full capture of the dominant kernel.
+# Usage (from the repo root, on the GPU box):  bash tools/gpu_round.sh [tag]
+set -u
+TAG=${1:-r1}
+OUT=gpurun_out
+mkdir -p $OUT
+nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > $OUT/smi_$TAG.txt 2>&1
+timeout 900 python -m pytest tests -m gpu -x -q > $OUT/pytest_gpu_$TAG.log 2>&1; echo "pytest rc=$?" | tee -a $OUT/pytest_gpu_$TAG.log
+tail -5 $OUT/pytest_gpu_$TAG.log
+timeout 600 python bench.py > $OUT/bench_$TAG.json 2> $OUT/bench_$TAG.err; echo "bench rc=$?"
+cat $OUT/bench_$TAG.json
+timeout 300 python bench.py --impl reference --steps 5 --warmup 1 > $OUT/bench_ref_$TAG.json 2>> $OUT/bench_$TAG.err; echo "bench ref rc=$?"
+cat $OUT/bench_ref_$TAG.json
+CMD="python bench.py --steps 40 --warmup 5 --no-cpu-baseline"
+timeout 300 $CMD > $OUT/plain_$TAG.log 2>&1 &&
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $OUT/launches_$TAG.csv $CMD > $OUT/ncu_list_$TAG.log 2>&1
+echo "ncu list rc=$?"
+timeout 300 $CMD > $OUT/plain2_$TAG.log 2>&1 &&
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:raster_staged -s 10 -c 3 -o $OUT/raster_$TAG $CMD > $OUT/ncu_full_$TAG.log 2>&1
+echo "ncu full rc=$?"
+ls -la $OUT

@@ -4,7 +4,7 @@
     python bench.py [--gpus N] [--steps K] [--warmup W] [--envs-per-gpu E] [--impl ours|reference]
 
 A "step" is one pass of the hot path over the whole batch: physics + programmed AI + reward/terminal/labels for every
-env (env_kernel) and the new 3x128x128 uint8 frame of every env rasterised into the HBM ring (raster_kernel).
+env and the new 3x128x128 uint8 frame of every env rasterised into the HBM ring — one fused kernel (csrc/ahk_step.cu).
 Workload: BASELINE.json configs[1] — 4096 envs per GPU, AI on both sides, auto-reset on goals and every 200 steps
 (ai/supervised/generate_data.py:44-58).  N > 1 (torchrun): envs shard by global id, no collective on the step path;
 statistics are all-reduced once after the timed region (NCCL).  See DESIGN.md "Measurement".
@@ -182,8 +182,10 @@ def main():
     launches = env.launches - launches0
     clocks = sampler.summary() if sampler else None
 
-    # ---- the dominant kernel alone (raster_staged_kernel): CUDA events recorded on the launching stream around each
-    # of the step's two kernels (ahk_step_profiled), averaged over a separate pass of the same workload
+    # ---- the dominant kernel alone: CUDA events recorded on the launching stream around the step's kernel(s)
+    # (ahk_step_profiled), averaged over a separate pass of the same workload.  Default path: ONE fused kernel per
+    # step (step_kernel<1>: physics + AI + labels + raster), reported as raster_ms with env_ms == 0; with AHK_PATH=split
+    # the env kernel and the raster kernel are timed separately.
     prof_steps = min(max(args.steps // 4, 20), 400)
     env_ms = raster_ms = 0.0
     for _ in range(prof_steps):
@@ -219,13 +221,17 @@ def main():
         value = total_envs * args.steps / (ms * 1e-3)
         # roofline of the dominant kernel: algorithmic bytes of ONE raster launch = n frames x (49152 B written + 16 B
         # draw record read) over its event-timed duration; the whole step (49287 B/env-step) beside it
-        achieved = n * RASTER_BYTES_PER_FRAME / (raster_ms * 1e-3) / 1e9
+        fused = env_ms == 0.0
+        kernel_bytes = n * (BYTES_PER_STEP if fused else RASTER_BYTES_PER_FRAME)
+        kernel_name = "step_kernel<1> (fused physics+AI+label+raster)" if fused else \
+            ("raster_staged_kernel" if os.environ.get("AHK_RASTER") == "staged" else "step_kernel<2> (raster only)")
+        achieved = kernel_bytes / (raster_ms * 1e-3) / 1e9
         step_gbs = n * BYTES_PER_STEP / (ms / args.steps * 1e-3) / 1e9
         write_peak = None
-        wp = os.path.join(ROOT, "profiles", "write_peak_r1.json")
+        wp = os.path.join(ROOT, "profiles", "wprobe_r1b.json")  # tools/wprobe.cu: pure write streams over the same footprint
         if os.path.exists(wp):
             with open(wp) as f:
-                write_peak = json.load(f)["fill_4GiB"]["best_GBs"]
+                write_peak = max(r["steady_GBs"] for r in json.load(f)["results"])
         line = {
             "metric": METRIC, "value": value, "unit": "env-steps/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
@@ -237,12 +243,12 @@ def main():
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                          "frac": achieved / peaks["hbm_gbs"], "traffic": RASTER_TRAFFIC_NCU, "peak_kind": peak_kind + " copy (read+write)",
-                         "kernel": "raster_staged_kernel", "kernel_ms": raster_ms, "env_kernel_ms": env_ms,
-                         "bytes_per_launch": n * RASTER_BYTES_PER_FRAME,
+                         "kernel": kernel_name, "kernel_ms": raster_ms, "env_kernel_ms": env_ms,
+                         "bytes_per_launch": kernel_bytes,
                          "whole_step": {"achieved": step_gbs, "frac": step_gbs / peaks["hbm_gbs"], "bytes_per_env_step": BYTES_PER_STEP},
                          "write_only_peak": write_peak,
                          "frac_of_write_only_peak": (achieved / write_peak) if write_peak else None,
-                         "note": "the path only WRITES; a fill of 4 GiB on this GPU reaches write_only_peak GB/s (profiles/write_peak_r1.json), the copy peak counts read+write"},
+                         "note": "the path only WRITES; write_only_peak = best steady-state pure write stream (st.global.cs.v4 / cp.async.bulk) over the same 3 x 201 MB ring, tools/wprobe.cu -> profiles/wprobe_r1b.json; peak = MEASURED_PEAKS.json copy (read+write)"},
             "e2e": {"value": total_envs * e2e_steps / e2e_s, "unit": "env-steps/s", "h2d_bytes_per_step": 2 * n,
                     "d2h_bytes_per_step": 7 * n, "note": "ahk_step_host: actions from pinned host memory, reward/done/labels back to host; frames stay in the HBM ring"},
             "stats": {"steps": int(stats[0]), "episodes": int(stats[1]), "goals_top": int(stats[2]), "goals_bottom": int(stats[3])},

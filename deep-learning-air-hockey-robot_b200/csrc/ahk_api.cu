@@ -43,8 +43,12 @@ struct ahk_env {
     uint8_t *action_stage = nullptr; // [2][n] device staging for ahk_step_host
     cudaStream_t host_stream = nullptr;
     int head = 0;
-    int raster_grid = 0;
-    bool raster_direct = false; // AHK_RASTER=direct selects the register-composed variant (A/B measurements)
+    int sms = 0;
+    int raster_grid = 0;        // staged rasteriser (split path): one persistent CTA per SM
+    int step_grid = 0, envs_per_cta = 0; // fused kernel: CTA b owns envs [b * envs_per_cta, (b + 1) * envs_per_cta)
+    // A/B switches (measurements only): AHK_PATH=split runs env_kernel + a raster kernel instead of the fused kernel;
+    // AHK_RASTER=staged picks the TMA-staged rasteriser for the split path (default: the band rasteriser, draw only)
+    bool split = false, staged = false;
     uint64_t launches = 0;
     cudaEvent_t ev[3] = {nullptr, nullptr, nullptr}; // ahk_step_profiled: before env_kernel, between, after raster
 };
@@ -80,7 +84,7 @@ ahk::EnvArgs env_args(const ahk_env *e)
     return a;
 }
 
-int raster(ahk_env *e, cudaStream_t s)
+ahk::RasterArgs raster_args(const ahk_env *e)
 {
     ahk::RasterArgs r{};
     r.drawlist = e->buf.drawlist;
@@ -90,9 +94,22 @@ int raster(ahk_env *e, cudaStream_t s)
     r.env_id_base = e->cfg.env_id_base;
     r.n = e->cfg.n_envs;
     r.head = e->head;
-    if (e->raster_direct) AHK_CUDA(ahk::launch_raster(r, e->raster_grid, s));
-    else AHK_CUDA(ahk::launch_raster_staged(r, e->raster_grid, s));
-    e->launches += 1;
+    return r;
+}
+
+// One pass of the hot path: mode 0 = reset (+ warm-up frames), 1 = step.  Default: ONE fused kernel.
+int run(ahk_env *e, const ahk::EnvArgs &a, int mode, cudaStream_t s)
+{
+    ahk::StepArgs st{a, raster_args(e), e->envs_per_cta};
+    if (!e->split) {
+        AHK_CUDA(ahk::launch_step(st, mode, e->step_grid, s));
+        e->launches += 1;
+        return AHK_OK;
+    }
+    AHK_CUDA(ahk::launch_env(a, mode == 1, s));
+    if (e->staged) AHK_CUDA(ahk::launch_raster_staged(st.ras, e->raster_grid, s));
+    else AHK_CUDA(ahk::launch_step(st, 2, e->step_grid, s));
+    e->launches += 2;
     return AHK_OK;
 }
 
@@ -121,15 +138,17 @@ int ahk_create(const ahk_config *cfg, ahk_env **out)
     ahk_env *e = new (std::nothrow) ahk_env();
     if (!e) return fail(AHK_ERR_ARG, "out of host memory");
     e->cfg = *cfg;
-    if (const char *s = getenv("AHK_RASTER")) e->raster_direct = strcmp(s, "direct") == 0;
-    int per_sm = e->raster_direct ? 4 : 1;
-    if (const char *s = getenv("AHK_RASTER_CTAS_PER_SM")) per_sm = atoi(s) > 0 ? atoi(s) : per_sm;
-    e->raster_grid = prop.multiProcessorCount * per_sm;
+    if (const char *s = getenv("AHK_PATH")) e->split = strcmp(s, "split") == 0;
+    if (const char *s = getenv("AHK_RASTER")) e->staged = strcmp(s, "staged") == 0;
+    e->sms = prop.multiProcessorCount;
+    e->raster_grid = e->sms;
+    e->envs_per_cta = (cfg->n_envs + e->sms - 1) / e->sms;
+    e->step_grid = (cfg->n_envs + e->envs_per_cta - 1) / e->envs_per_cta;
     cudaError_t err = cudaMalloc(&e->table_dev, ahk::kFrameBytes);
     if (err == cudaSuccess) err = cudaMalloc(&e->action_stage, 2 * static_cast<size_t>(cfg->n_envs));
     if (err == cudaSuccess) err = cudaStreamCreateWithFlags(&e->host_stream, cudaStreamNonBlocking);
     for (int k = 0; k < 3 && err == cudaSuccess; ++k) err = cudaEventCreate(&e->ev[k]);
-    if (err == cudaSuccess) err = ahk::raster_prepare();
+    if (err == cudaSuccess) err = ahk::step_prepare();
     if (err == cudaSuccess) err = ahk::raster_staged_prepare();
     if (err != cudaSuccess) {
         ahk_destroy(e);
@@ -191,9 +210,7 @@ int ahk_reset(ahk_env *e, const uint8_t *mask, const uint8_t *episode, const uin
     a.reset_mask = mask;
     a.episode_override = episode;
     a.use_override = use;
-    AHK_CUDA(ahk::launch_env(a, false, s));
-    e->launches += 1;
-    return raster(e, s);
+    return run(e, a, 0, s);
 }
 
 int ahk_step(ahk_env *e, const uint8_t *robot, const uint8_t *human, void *stream)
@@ -204,9 +221,7 @@ int ahk_step(ahk_env *e, const uint8_t *robot, const uint8_t *human, void *strea
     a.robot = robot;
     a.human = human;
     e->head = (e->head + 1) % 3;
-    AHK_CUDA(ahk::launch_env(a, true, s));
-    e->launches += 1;
-    return raster(e, s);
+    return run(e, a, 1, s);
 }
 
 int ahk_step_profiled(ahk_env *e, const uint8_t *robot, const uint8_t *human, void *stream, float *env_ms, float *raster_ms)
@@ -219,10 +234,20 @@ int ahk_step_profiled(ahk_env *e, const uint8_t *robot, const uint8_t *human, vo
     a.human = human;
     e->head = (e->head + 1) % 3;
     AHK_CUDA(cudaEventRecord(e->ev[0], s));
+    if (!e->split) { // the fused kernel is the whole step: reported as the second figure, the first is 0
+        if (int rc = run(e, a, 1, s)) return rc;
+        AHK_CUDA(cudaEventRecord(e->ev[2], s));
+        AHK_CUDA(cudaEventSynchronize(e->ev[2]));
+        *env_ms = 0.0f;
+        AHK_CUDA(cudaEventElapsedTime(raster_ms, e->ev[0], e->ev[2]));
+        return AHK_OK;
+    }
+    ahk::StepArgs st{a, raster_args(e), e->envs_per_cta};
     AHK_CUDA(ahk::launch_env(a, true, s));
-    e->launches += 1;
     AHK_CUDA(cudaEventRecord(e->ev[1], s));
-    if (int rc = raster(e, s)) return rc;
+    if (e->staged) AHK_CUDA(ahk::launch_raster_staged(st.ras, e->raster_grid, s));
+    else AHK_CUDA(ahk::launch_step(st, 2, e->step_grid, s));
+    e->launches += 2;
     AHK_CUDA(cudaEventRecord(e->ev[2], s));
     AHK_CUDA(cudaEventSynchronize(e->ev[2]));
     AHK_CUDA(cudaEventElapsedTime(env_ms, e->ev[0], e->ev[1]));

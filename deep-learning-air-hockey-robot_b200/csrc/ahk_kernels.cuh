@@ -10,6 +10,7 @@ constexpr int kDim = 128;                   // processor.py:5
 constexpr int kFrameBytes = 3 * kDim * kDim;
 constexpr int kFrameVecs = kFrameBytes / 16; // 3072 128-bit vectors per frame
 constexpr int kEnvThreads = 128;
+constexpr int kStepThreads = 1024;                                             // fused step kernel: 32 warps, one CTA per SM
 constexpr int kRasterThreads = 256;
 constexpr int kRasterGroups = 3;                                               // independent 256-thread groups per CTA
 constexpr int kRasterGroupTail = kDim * 8 + kRasterThreads * 20 + 16;          // per-row spans + record batch + counter
@@ -37,6 +38,12 @@ struct RasterArgs {
     int n, head;
 };
 
+struct StepArgs { // the fused kernel: env block b of envs_per_cta environments belongs to CTA b
+    EnvArgs env;
+    RasterArgs ras;
+    int envs_per_cta;
+};
+
 struct ObserveArgs {
     const uint8_t *frames;
     void *out;
@@ -46,8 +53,8 @@ struct ObserveArgs {
 void set_error_text(const char *text); // ahk_api.cu: fills the buffer behind ahk_last_error()
 
 cudaError_t launch_env(const EnvArgs &a, bool step, cudaStream_t stream);
-cudaError_t raster_prepare();
-cudaError_t launch_raster(const RasterArgs &a, int grid, cudaStream_t stream);
+cudaError_t step_prepare();
+cudaError_t launch_step(const StepArgs &a, int mode, int grid, cudaStream_t stream); // mode 0 reset, 1 step, 2 draw only
 cudaError_t raster_staged_prepare();
 cudaError_t launch_raster_staged(const RasterArgs &a, int grid, cudaStream_t stream);
 cudaError_t launch_observe(const ObserveArgs &a, int grid, cudaStream_t stream);

@@ -69,7 +69,7 @@ typedef struct {
     uint8_t *human_label; /* [n]  info['human_action'] */
     uint8_t *info;        /* [n]  bit0 puck_was_hit 1 hit_the_border 2 puck_is_at_the_bottom 3 distance_decreased 4 in_the_target, bits5-6 scored (0 none,1 top,2 bottom) */
     uint64_t *stats;      /* [AHK_STATS_WORDS] running sums: 0 steps, 1 episodes, 2 goals_top, 3 goals_bottom, 4 reward*2 (int64), 5.. robot label hist[10], 15.. human label hist[10] */
-    uint32_t *drawlist;   /* [3][n][4] scratch between the step and raster kernels */
+    uint32_t *drawlist;   /* [3][n][4] scratch between the env and raster kernels (split path only; the fused kernel keeps it in shared memory) */
 } ahk_buffers;
 
 /* ≙ AirHockeyEnv.__init__ (air_hockey_env.py:9-24) minus the first reset. */
@@ -86,8 +86,8 @@ int ahk_bind_buffers(ahk_env *env, const ahk_buffers *bufs);
  * episode_dev/use_dev [n] (NULL = sample per SPEC.md §4): force the episode type / object mask, AHK_EP_SAMPLE = sample. */
 int ahk_reset(ahk_env *env, const uint8_t *mask_dev, const uint8_t *episode_dev, const uint8_t *use_dev, void *stream);
 
-/* ≙ AirHockeyEnv.step (air_hockey_env.py:84-155), batched: physics + programmed AI + reward/terminal/labels, then the
- * new frame of every env rasterised into ring slot `head` (advanced first).  robot_dev/human_dev [n] labels or NULL. */
+/* ≙ AirHockeyEnv.step (air_hockey_env.py:84-155), batched, ONE kernel: physics + programmed AI + reward/terminal/labels,
+ * then the new frame of every env rasterised into ring slot `head` (advanced first).  robot_dev/human_dev [n] labels or NULL. */
 int ahk_step(ahk_env *env, const uint8_t *robot_dev, const uint8_t *human_dev, void *stream);
 
 /* The same call with HOST buffers, for callers that live on the CPU like the reference's loops do: copies the
@@ -96,8 +96,10 @@ int ahk_step(ahk_env *env, const uint8_t *robot_dev, const uint8_t *human_dev, v
 int ahk_step_host(ahk_env *env, const uint8_t *robot_host, const uint8_t *human_host, float *reward_host,
                   uint8_t *done_host, uint8_t *robot_label_host, uint8_t *human_label_host, uint8_t *frame_host);
 
-/* ahk_step with CUDA events recorded on `stream` around each of its two kernels; waits, then reports their durations.
- * Measurement aid for bench.py's roofline (not a hot-path call). */
+/* ahk_step with CUDA events recorded on `stream` around its kernel(s); waits, then reports the durations.  Default
+ * (fused) path: *env_ms = 0 and *raster_ms = the one fused kernel (physics + AI + labels + raster).  With the A/B switch
+ * AHK_PATH=split in the environment: the env kernel and the raster kernel separately.  Measurement aid for bench.py's
+ * roofline (not a hot-path call). */
 int ahk_step_profiled(ahk_env *env, const uint8_t *robot_dev, const uint8_t *human_dev, void *stream, float *env_ms,
                       float *raster_ms);
 

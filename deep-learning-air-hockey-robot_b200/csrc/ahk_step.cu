@@ -48,7 +48,6 @@ struct Luts {
 };
 
 constexpr int kRecordBytes = 3 * kStepThreads * 16;
-constexpr int kStepSmem = kFrameBytes + kRecordBytes + static_cast<int>(sizeof(Luts));
 
 __device__ __forceinline__ void build_luts(Luts &l)
 {
@@ -72,14 +71,14 @@ __device__ __forceinline__ constexpr uint32_t splat(uint32_t colour, int channel
 
 // paint native columns x0..x1 of this lane's row with `colour`, inside the 16-pixel vector starting at column `base`
 template <uint32_t kColour>
-__device__ __forceinline__ void fill(uint32_t (&o)[3][4], const Luts &l, int x0, int x1, int base)
+__device__ __forceinline__ bool fill(uint32_t (&o)[3][4], const Luts &l, int x0, int x1, int base)
 {
     x0 = max(x0, 0);
     x1 = min(x1, kTableW - 1);
-    if (x0 > x1) return;
+    if (x0 > x1) return false;
     const int lo = l.col_lo[x0], hi = static_cast<int>(l.col_hi1[x1]) - 1;
     const int a = max(lo - base, 0), b = min(hi - base, 15);
-    if (a > b) return;
+    if (a > b) return false;
     const uint32_t m16 = (0xFFFFu >> (15 - b)) & (0xFFFFu << a);
 #pragma unroll
     for (int g = 0; g < 4; ++g) {
@@ -87,28 +86,28 @@ __device__ __forceinline__ void fill(uint32_t (&o)[3][4], const Luts &l, int x0,
 #pragma unroll
         for (int c = 0; c < 3; ++c) o[c][g] = (o[c][g] & ~m) | (splat(kColour, c) & m);
     }
+    return true;
 }
 
 // a disc of squared radius kR2 centred (cx, cy): on the row at vertical offset dy it covers cx - hw .. cx + hw
 template <int kR2, uint32_t kColour>
-__device__ __forceinline__ void disc(uint32_t (&o)[3][4], const Luts &l, int cx, int dy, int base)
+__device__ __forceinline__ bool disc(uint32_t (&o)[3][4], const Luts &l, int cx, int dy, int base)
 {
     const int v = kR2 - dy * dy;
-    if (v < 0) return;
+    if (v < 0) return false;
     const int hw = l.isqrt[v];
-    fill<kColour>(o, l, cx - hw, cx + hw, base);
+    return fill<kColour>(o, l, cx - hw, cx + hw, base);
 }
 
 // SPEC.md §7 items 4, 5 in painter's order: rim (d2 <= 576), body (<= 400), knob (<= 100), shine (3 px disc at (-3,-3))
 template <uint32_t kRim, uint32_t kBody, uint32_t kKnob, uint32_t kShine>
-__device__ __forceinline__ void mallet(uint32_t (&o)[3][4], const Luts &l, int cx, int cy, int y, int base)
+__device__ __forceinline__ bool mallet(uint32_t (&o)[3][4], const Luts &l, int cx, int dy, int base)
 {
-    const int dy = y - cy;
-    if (dy < -24 || dy > 24) return;
-    disc<576, kRim>(o, l, cx, dy, base);
-    disc<400, kBody>(o, l, cx, dy, base);
-    disc<100, kKnob>(o, l, cx, dy, base);
-    disc<9, kShine>(o, l, cx - 3, dy + 3, base);
+    bool hit = disc<576, kRim>(o, l, cx, dy, base);
+    hit |= disc<400, kBody>(o, l, cx, dy, base);
+    hit |= disc<100, kKnob>(o, l, cx, dy, base);
+    hit |= disc<9, kShine>(o, l, cx - 3, dy + 3, base);
+    return hit;
 }
 
 __device__ __forceinline__ void mbarrier_wait(uint32_t bar, uint32_t parity)
@@ -121,15 +120,46 @@ __device__ __forceinline__ void mbarrier_wait(uint32_t bar, uint32_t parity)
         :: "r"(bar), "r"(parity) : "memory");
 }
 
-// One work unit: output rows 16q .. 16q+15 of one frame, by one warp.
-__device__ __forceinline__ void draw_unit(const uint4 *__restrict__ s_table, const Luts &l, const uint4 rec, int q,
-                                          uint8_t *__restrict__ frame, uint32_t env_id, uint2 key, int lane)
+// ---- a work unit: kUnitRows output rows of one frame, by one warp, through a per-warp patch in shared memory
+constexpr int kUnitRows = 8;
+constexpr int kUnitVecs = kUnitRows * 8;         // vector positions per channel in a unit
+constexpr int kUnitsPerFrame = kDim / kUnitRows; // 16
+constexpr int kPatchBytes = 3 * kUnitVecs * 16;  // 3 KB per warp
+
+// One sprite pass over the warp's patch, sprite-major: lane = (row lane >> 2 of the unit, vector k0 + (lane & 3)), so a
+// sprite up to four vectors wide costs ONE pass per unit with every lane on a vector the sprite can reach.
+// reach(y): does the sprite touch native row y at all; paint(o, y, base): apply its layers to the 16-pixel vector
+// starting at column `base`, returning whether anything changed.  Passes run in painter's order (SPEC.md §7).
+template <typename Reach, typename Paint>
+__device__ __forceinline__ void sprite_pass(uint4 *patch, int i0, int k0, int lane, Reach reach, Paint paint)
+{
+    const int r = lane >> 2, k = k0 + (lane & 3);
+    const int y = sample_y(i0 + r);
+    if (k <= 7 && reach(y)) {
+        const int at = r * 8 + k;
+        const uint4 t0 = patch[at], t1 = patch[kUnitVecs + at], t2 = patch[2 * kUnitVecs + at];
+        uint32_t o[3][4] = {{t0.x, t0.y, t0.z, t0.w}, {t1.x, t1.y, t1.z, t1.w}, {t2.x, t2.y, t2.z, t2.w}};
+        if (paint(o, y, 16 * k)) {
+            patch[at] = make_uint4(o[0][0], o[0][1], o[0][2], o[0][3]);
+            patch[kUnitVecs + at] = make_uint4(o[1][0], o[1][1], o[1][2], o[1][3]);
+            patch[2 * kUnitVecs + at] = make_uint4(o[2][0], o[2][1], o[2][2], o[2][3]);
+        }
+    }
+    __syncwarp();
+}
+
+// first vector (0..7; 8 = none) a sprite whose leftmost native column is x0 can reach
+__device__ __forceinline__ int first_vector(const Luts &l, int x0) { return l.col_lo[min(max(x0, 0), kTableW - 1)] >> 4; }
+
+__device__ __forceinline__ void draw_unit(const uint4 *__restrict__ s_table, uint4 *__restrict__ patch, const Luts &l,
+                                          const uint4 rec, int q, uint8_t *__restrict__ frame, uint32_t env_id, uint2 key, int lane)
 {
     uint4 *out = reinterpret_cast<uint4 *>(frame);
+    const int p0 = q * kUnitVecs + lane, p1 = p0 + 32; // this lane's two vector positions (per channel) of the unit
     if (rec.w & kDrawNoise) { // SPEC.md §7 last paragraph: a `random` episode's frame is Philox noise
 #pragma unroll 1
-        for (int t = 0; t < 12; ++t) {
-            const int v = (t >> 2) * 1024 + q * 128 + (t & 3) * 32 + lane;
+        for (int t = 0; t < 6; ++t) {
+            const int v = (t >> 1) * 1024 + ((t & 1) ? p1 : p0);
             uint4 r = philox(static_cast<uint32_t>(v), rec.x, env_id, 2u, key);
             r.x = __vsubus4(r.x, 0x01010101u); // per byte b -> (b * 255) >> 8 == max(b - 1, 0)
             r.y = __vsubus4(r.y, 0x01010101u);
@@ -143,58 +173,98 @@ __device__ __forceinline__ void draw_unit(const uint4 *__restrict__ s_table, con
     const int ipx = static_cast<int>(rec.x & 0xFFFFu), ipy = static_cast<int>(rec.x >> 16);
     const int ibx = static_cast<int>(rec.y & 0xFFFFu), iby = static_cast<int>(rec.y >> 16);
     const int itx = static_cast<int>(rec.z & 0xFFFFu), ity = static_cast<int>(rec.z >> 16);
-    const bool use_arm = rec.w & kUseArm, use_puck = rec.w & kUsePuck, use_top = rec.w & kUseTop;
-    const int k = lane & 7, base = 16 * k;
 
-#pragma unroll 1
-    for (int band = 0; band < 4; ++band) {
-        const int i0 = 16 * q + 4 * band;
-        const int i = i0 + (lane >> 3), pos = i * 8 + k;
-        const uint4 t0 = s_table[pos], t1 = s_table[1024 + pos], t2 = s_table[2048 + pos];
+    // which sprites reach the unit's rows at all (warp-uniform)
+    const int i0 = q * kUnitRows;
+    const int yb0 = sample_y(i0), yb1 = sample_y(i0 + kUnitRows - 1);
+    const bool line_u = yb1 >= iby - 3 && yb0 <= iby + 2;
+    const bool puck_u = (rec.w & kUsePuck) && yb1 >= ipy - 18 && yb0 <= ipy + 18;
+    const bool bot_u = yb1 >= iby - 24 && yb0 <= iby + 24;
+    const bool top_u = (rec.w & kUseTop) && yb1 >= ity - 24 && yb0 <= ity + 24;
+    const bool arm_u = (rec.w & kUseArm) && yb0 <= ity + 10;
 
-        // which sprites reach the band's rows at all (warp-uniform)
-        const int yb0 = sample_y(i0), yb1 = sample_y(i0 + 3);
-        const bool line_b = yb1 >= iby - 3 && yb0 <= iby + 2;
-        const bool puck_b = use_puck && yb1 >= ipy - 18 && yb0 <= ipy + 18;
-        const bool bot_b = yb1 >= iby - 24 && yb0 <= iby + 24;
-        const bool top_b = use_top && yb1 >= ity - 24 && yb0 <= ity + 24;
-        const bool arm_b = use_arm && yb0 <= ity + 10;
-        if (!(line_b || puck_b || bot_b || top_b || arm_b)) { // the table shows through: straight copy
-            __stcs(out + pos, t0);
-            __stcs(out + 1024 + pos, t1);
-            __stcs(out + 2048 + pos, t2);
-            continue;
-        }
-
-        uint32_t o[3][4] = {{t0.x, t0.y, t0.z, t0.w}, {t1.x, t1.y, t1.z, t1.w}, {t2.x, t2.y, t2.z, t2.w}};
-        const int y = sample_y(i);
-        if (line_b && y >= iby - 3 && y <= iby + 2) { // item 2: the rail line spans the full width
+    uint4 v[6];
 #pragma unroll
-            for (int c = 0; c < 3; ++c)
+    for (int c = 0; c < 3; ++c) {
+        v[2 * c] = s_table[c * 1024 + p0];
+        v[2 * c + 1] = s_table[c * 1024 + p1];
+    }
+    if (!(line_u || puck_u || bot_u || top_u || arm_u)) { // the table shows through: straight shared -> global copy
 #pragma unroll
-                for (int g = 0; g < 4; ++g) o[c][g] = splat(kLineColour, c);
+        for (int c = 0; c < 3; ++c) {
+            __stcs(out + c * 1024 + p0, v[2 * c]);
+            __stcs(out + c * 1024 + p1, v[2 * c + 1]);
         }
-        if (puck_b) { // item 3: rim (d2 <= 324), body (<= 196), shine (4 px disc at (-5,-5))
-            const int dy = y - ipy;
-            if (dy >= -18 && dy <= 18) {
-                disc<324, kPuckRim>(o, l, ipx, dy, base);
-                disc<196, kPuckBody>(o, l, ipx, dy, base);
-                disc<16, kPuckShine>(o, l, ipx - 5, dy + 5, base);
+        return;
+    }
+
+    __syncwarp(); // the previous unit's reads of the patch are done
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        patch[c * kUnitVecs + lane] = v[2 * c];
+        patch[c * kUnitVecs + 32 + lane] = v[2 * c + 1];
+    }
+    __syncwarp();
+
+    if (line_u) { // item 2: the rail line spans the full width; lane = (row, vector), two halves of the unit
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int at = h * 32 + lane, y = sample_y(i0 + (at >> 3));
+            if (y >= iby - 3 && y <= iby + 2) {
+#pragma unroll
+                for (int c = 0; c < 3; ++c) { const uint32_t w = splat(kLineColour, c); patch[c * kUnitVecs + at] = make_uint4(w, w, w, w); }
             }
         }
-        if (bot_b) mallet<kBotRim, kBotBody, kBotKnob, kBotShine>(o, l, ibx, iby, y, base);
-        if (top_b) mallet<kTopRim, kTopBody, kTopKnob, kTopShine>(o, l, itx, ity, y, base);
-        if (arm_b && y <= ity + 10) { // item 6
-            const int t = ity + 10 - y;
-            const int xc = itx + ((t * 5) >> 5), hw = 26 + ((t * 3) >> 4);
-            fill<kArmEdge>(o, l, xc - hw, xc + hw, base);
-            fill<kArmInner>(o, l, xc - hw + 4, xc + hw - 4, base);
-        }
-        __stcs(out + pos, make_uint4(o[0][0], o[0][1], o[0][2], o[0][3]));
-        __stcs(out + 1024 + pos, make_uint4(o[1][0], o[1][1], o[1][2], o[1][3]));
-        __stcs(out + 2048 + pos, make_uint4(o[2][0], o[2][1], o[2][2], o[2][3]));
+        __syncwarp();
+    }
+    if (puck_u) // item 3: rim (d2 <= 324), body (<= 196), shine (4 px disc at (-5,-5))
+        sprite_pass(patch, i0, first_vector(l, ipx - 18), lane,
+                    [&](int y) { return y >= ipy - 18 && y <= ipy + 18; },
+                    [&](uint32_t (&o)[3][4], int y, int base) {
+                        const int dy = y - ipy;
+                        bool hit = disc<324, kPuckRim>(o, l, ipx, dy, base);
+                        hit |= disc<196, kPuckBody>(o, l, ipx, dy, base);
+                        hit |= disc<16, kPuckShine>(o, l, ipx - 5, dy + 5, base);
+                        return hit;
+                    });
+    if (bot_u) // item 4
+        sprite_pass(patch, i0, first_vector(l, ibx - 24), lane,
+                    [&](int y) { return y >= iby - 24 && y <= iby + 24; },
+                    [&](uint32_t (&o)[3][4], int y, int base) { return mallet<kBotRim, kBotBody, kBotKnob, kBotShine>(o, l, ibx, y - iby, base); });
+    if (top_u) // item 5
+        sprite_pass(patch, i0, first_vector(l, itx - 24), lane,
+                    [&](int y) { return y >= ity - 24 && y <= ity + 24; },
+                    [&](uint32_t (&o)[3][4], int y, int base) { return mallet<kTopRim, kTopBody, kTopKnob, kTopShine>(o, l, itx, y - ity, base); });
+    if (arm_u) { // item 6: a slanted band, widest at the top row of the unit; conservative column range, exact per lane
+        const int t_max = ity + 10 - yb0;
+        const int x_min = itx - 26 - ((t_max * 3) >> 4), x_max = itx + ((t_max * 5) >> 5) + 26 + ((t_max * 3) >> 4);
+        const int k_min = first_vector(l, x_min);
+        const int k_max = x_max < 0 ? -1 : (static_cast<int>(l.col_hi1[min(x_max, kTableW - 1)]) - 1) >> 4;
+        for (int k0 = k_min; k0 <= k_max; k0 += 4)
+            sprite_pass(patch, i0, k0, lane,
+                        [&](int y) { return y <= ity + 10; },
+                        [&](uint32_t (&o)[3][4], int y, int base) {
+                            const int t = ity + 10 - y;
+                            const int xc = itx + ((t * 5) >> 5), hw = 26 + ((t * 3) >> 4);
+                            bool hit = fill<kArmEdge>(o, l, xc - hw, xc + hw, base);
+                            hit |= fill<kArmInner>(o, l, xc - hw + 4, xc + hw - 4, base);
+                            return hit;
+                        });
+    }
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        v[2 * c] = patch[c * kUnitVecs + lane];
+        v[2 * c + 1] = patch[c * kUnitVecs + 32 + lane];
+    }
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        __stcs(out + c * 1024 + p0, v[2 * c]);
+        __stcs(out + c * 1024 + p1, v[2 * c + 1]);
     }
 }
+
+constexpr int kLutOffset = kFrameBytes + kRecordBytes + (kStepThreads / 32) * kPatchBytes;
+constexpr int kStepSmem = kLutOffset + static_cast<int>(sizeof(Luts));
 
 } // namespace
 
@@ -206,11 +276,12 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_kernel(StepArgs a)
     extern __shared__ __align__(128) uint8_t smem[];
     const uint4 *s_table = reinterpret_cast<const uint4 *>(smem);                 // [3][128][8] vectors
     uint4 *s_recs = reinterpret_cast<uint4 *>(smem + kFrameBytes);                // valid draw records of this round
-    Luts &luts = *reinterpret_cast<Luts *>(smem + kFrameBytes + kRecordBytes);
+    Luts &luts = *reinterpret_cast<Luts *>(smem + kLutOffset);
     __shared__ __align__(8) uint64_t s_table_ready;
     __shared__ int s_count;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    uint4 *s_patch = reinterpret_cast<uint4 *>(smem + kFrameBytes + kRecordBytes + warp * kPatchBytes); // this warp's scratch
     const uint32_t bar = static_cast<uint32_t>(__cvta_generic_to_shared(&s_table_ready));
     if (tid == 0) {
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(bar) : "memory");
@@ -257,17 +328,17 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_kernel(StepArgs a)
             if (valid) s_recs[at] = make_uint4(rec[b].x, rec[b].y, rec[b].z, (rec[b].w & 0xFFu) | static_cast<uint32_t>(tid) << 8 | static_cast<uint32_t>(b) << 20);
         }
         __syncthreads();
-        const int units = s_count * 8;
+        const int units = s_count * kUnitsPerFrame;
         if (!table_ready) {
             mbarrier_wait(bar, 0u);
             table_ready = true;
         }
         for (int u = warp; u < units; u += kStepThreads / 32) {
-            const uint4 rec_u = s_recs[u >> 3];
+            const uint4 rec_u = s_recs[u / kUnitsPerFrame];
             const int env = base + static_cast<int>((rec_u.w >> 8) & 0x3FFu), back = static_cast<int>(rec_u.w >> 20); // back 0 = newest
             const int slot = (a.ras.head + 3 - back) % 3;
             uint8_t *frame = a.ras.frames + (static_cast<size_t>(slot) * stride + env) * kFrameBytes;
-            draw_unit(s_table, luts, rec_u, u & 7, frame, a.ras.env_id_base + static_cast<uint32_t>(env), a.ras.key, lane);
+            draw_unit(s_table, s_patch, luts, rec_u, u % kUnitsPerFrame, frame, a.ras.env_id_base + static_cast<uint32_t>(env), a.ras.key, lane);
         }
     }
     if (!table_ready) mbarrier_wait(bar, 0u); // never exit with the table copy still in flight

@@ -50,6 +50,7 @@ struct ahk_env {
     // AHK_RASTER=staged picks the TMA-staged rasteriser for the split path (default: the band rasteriser, draw only)
     bool split = false, staged = false;
     uint64_t launches = 0;
+    unsigned long long *trace = nullptr; // ahk_set_trace
     cudaEvent_t ev[3] = {nullptr, nullptr, nullptr}; // ahk_step_profiled: before env_kernel, between, after raster
 };
 
@@ -100,7 +101,7 @@ ahk::RasterArgs raster_args(const ahk_env *e)
 // One pass of the hot path: mode 0 = reset (+ warm-up frames), 1 = step.  Default: ONE fused kernel.
 int run(ahk_env *e, const ahk::EnvArgs &a, int mode, cudaStream_t s)
 {
-    ahk::StepArgs st{a, raster_args(e), e->envs_per_cta};
+    ahk::StepArgs st{a, raster_args(e), e->envs_per_cta, e->trace};
     if (!e->split) {
         AHK_CUDA(ahk::launch_step(st, mode, e->step_grid, s));
         e->launches += 1;
@@ -242,7 +243,7 @@ int ahk_step_profiled(ahk_env *e, const uint8_t *robot, const uint8_t *human, vo
         AHK_CUDA(cudaEventElapsedTime(raster_ms, e->ev[0], e->ev[2]));
         return AHK_OK;
     }
-    ahk::StepArgs st{a, raster_args(e), e->envs_per_cta};
+    ahk::StepArgs st{a, raster_args(e), e->envs_per_cta, e->trace};
     AHK_CUDA(ahk::launch_env(a, true, s));
     AHK_CUDA(cudaEventRecord(e->ev[1], s));
     if (e->staged) AHK_CUDA(ahk::launch_raster_staged(st.ras, e->raster_grid, s));
@@ -306,6 +307,21 @@ int ahk_set_pending(ahk_env *e, const uint8_t *pending, void *stream)
     if (!pending) return fail(AHK_ERR_ARG, "pending is NULL");
     AHK_CUDA(ahk::launch_set_pending(e->buf.state, pending, e->cfg.n_envs, static_cast<cudaStream_t>(stream)));
     e->launches += 1;
+    return AHK_OK;
+}
+
+int ahk_set_trace(ahk_env *e, uint64_t *trace_dev)
+{
+    if (!e) return fail(AHK_ERR_ARG, "env is NULL");
+    e->trace = reinterpret_cast<unsigned long long *>(trace_dev);
+    return AHK_OK;
+}
+
+int ahk_trace_shape(const ahk_env *e, int *ctas, int *warps)
+{
+    if (!e || !ctas || !warps) return fail(AHK_ERR_ARG, "env/ctas/warps is NULL");
+    *ctas = e->step_grid;
+    *warps = ahk::kStepThreads / 32;
     return AHK_OK;
 }
 

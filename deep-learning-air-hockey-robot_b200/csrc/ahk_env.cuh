@@ -51,12 +51,14 @@ struct StatDelta {
 
 // Resets (if due) and/or steps env i; rec[0..2] are the draw records of ring slots head, head-1, head-2 (w == 0:
 // nothing to paint there).  kStep: AirHockeyEnv.step, auto-reset first when armed; !kStep: AirHockeyEnv.reset.
+// stamps (tools/prologue_probe.cu only; nullptr in the product, folded away): clock64 after the state load, the tick, the stores.
 template <bool kStep>
-__device__ __forceinline__ void env_update(const EnvArgs &a, int i, uint4 (&rec)[3], StatDelta &d)
+__device__ __forceinline__ void env_update(const EnvArgs &a, int i, uint4 (&rec)[3], StatDelta &d, long long *stamps = nullptr)
 {
     Sim s;
     uint32_t reset_count, noise_count, meta;
     load_sim(a.state, a.n, i, s, reset_count, noise_count, meta);
+    if (stamps) stamps[0] = static_cast<long long>(__float_as_uint(s.puck.x) + meta) * 0 + clock64();
     uint32_t steps = meta & 0xFFFFu, episode = (meta >> 16) & 3u, use = (meta >> 18) & 7u, pending = (meta >> 21) & 1u;
     const uint32_t env_id = a.env_id_base + static_cast<uint32_t>(i);
     rec[0] = rec[1] = rec[2] = make_uint4(0, 0, 0, 0);
@@ -108,6 +110,7 @@ __device__ __forceinline__ void env_update(const EnvArgs &a, int i, uint4 (&rec)
         const uint32_t human = a.human ? a.human[i] : kActNone;
         Tick t;
         sim_tick(s, robot, human, use, env_id, a.key, t);
+        if (stamps) stamps[1] = static_cast<long long>(t.info + __float_as_uint(s.puck.x)) * 0 + clock64();
         d.robot_label = static_cast<uint32_t>(t.rax * 3 + t.ray + 4); // processor.py:84-85
         d.human_label = static_cast<uint32_t>(t.hax * 3 + t.hay + 4);
         const int r2 = reward_x2(episode, t.info, d.robot_label);
@@ -133,6 +136,7 @@ __device__ __forceinline__ void env_update(const EnvArgs &a, int i, uint4 (&rec)
     }
 
     store_sim(a.state, a.n, i, s, reset_count, noise_count, make_meta(steps, episode, use, pending));
+    if (stamps) stamps[2] = clock64();
 }
 
 // running statistics (SURVEY.md §5 "Metrics"): warp-reduce, one atomic per warp per counter.  Call with the whole
@@ -165,6 +169,32 @@ __device__ __forceinline__ void accumulate_stats(uint64_t *stats, const StatDelt
             if (lane == 0 && nr) atomicAdd(st + 5 + l, static_cast<unsigned long long>(nr));
             if (lane == 0 && nh) atomicAdd(st + 15 + l, static_cast<unsigned long long>(nh));
         }
+    }
+}
+
+// The fused kernel's variant: the CTA collects its share in shared memory (s[kStatWords], same word order as
+// ahk_buffers.stats) and adds it to the global sums once, at the end — a handful of global atomics per CTA per step
+// whatever the env-to-lane mapping.  Call with the whole warp converged; `live`: this lane holds an env.
+constexpr int kStatWords = 25;
+template <bool kStep>
+__device__ __forceinline__ void stat_to_shared(unsigned *s, const StatDelta &d, bool live)
+{
+    constexpr unsigned full = 0xFFFFFFFFu;
+    const unsigned s_steps = __reduce_add_sync(full, d.steps);
+    const unsigned s_eps = __reduce_add_sync(full, d.episodes);
+    const unsigned s_top = __reduce_add_sync(full, d.goals_top);
+    const unsigned s_bot = __reduce_add_sync(full, d.goals_bottom);
+    const int s_rew = __reduce_add_sync(full, d.reward2);
+    if ((threadIdx.x & 31u) == 0u) {
+        if (s_steps) atomicAdd(s + 0, s_steps);
+        if (s_eps) atomicAdd(s + 1, s_eps);
+        if (s_top) atomicAdd(s + 2, s_top);
+        if (s_bot) atomicAdd(s + 3, s_bot);
+        if (s_rew) atomicAdd(s + 4, static_cast<unsigned>(s_rew)); // two's complement; sign-extended at the flush
+    }
+    if (kStep && live) {
+        atomicAdd(s + 5 + d.robot_label, 1u);
+        atomicAdd(s + 15 + d.human_label, 1u);
     }
 }
 

@@ -42,6 +42,7 @@ struct StepArgs { // the fused kernel: env block b of envs_per_cta environments 
     EnvArgs env;
     RasterArgs ras;
     int envs_per_cta;
+    unsigned long long *trace; // measurement aid (ahk_set_trace): [grid][32 warps][4] %globaltimer stamps; selects the traced kernel
 };
 
 struct ObserveArgs {

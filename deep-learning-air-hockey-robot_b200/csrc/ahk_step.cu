@@ -8,17 +8,21 @@
 //
 // Layout of the work (B200: 148 SMs, one persistent CTA of 32 warps per SM):
 //   * CTA b owns a contiguous block of environments.  One thread per env runs the game tick in registers on the SoA
-//     state (coalesced) and leaves 16-byte draw records in shared memory — the step's only block-wide barrier.
+//     state (coalesced) and leaves a 16-byte draw record per frame to paint in shared memory — the step's only
+//     block-wide barriers.  Running statistics are summed in shared memory and flushed once per CTA.
 //   * The table image at the sample points (48 KB) is fetched once per CTA with one bulk async copy (TMA engine,
 //     mbarrier completion) while the physics runs.
-//   * Rasterising is barrier-free and warp-independent.  A work unit is (frame, 16 output rows); a warp takes units
-//     round-robin.  Per 4-row band each lane owns one 16-pixel vector position: it loads the table's three channel
-//     vectors from shared memory, paints the sprite layers that reach its row as column intervals (integer-sqrt
-//     half-widths and the exact inverse of the sample map come from small shared-memory tables; an interval becomes
-//     a byte mask, a layer three LOP3s per word), and streams the result out with 128-bit st.global.cs.  Bands no
-//     sprite reaches — most of them — are a straight shared->global copy.
-// A pure write stream on this GPU peaks at 6.0-6.5 TB/s (tools/wprobe.cu, profiles/wprobe_r1b.json); the design goal
-// is to keep the SM side far enough below its issue budget that the stores run at that rate.
+//   * Rasterising is barrier-free and warp-independent.  A work unit is (frame, 8 output rows) = 3 KB; warps take
+//     units round-robin.  A unit no sprite reaches — two thirds of them — is a straight shared -> global copy (six
+//     128-bit loads and st.global.cs per lane).  Otherwise the unit is composed in a per-warp 3 KB patch, sprite by
+//     sprite in painter's order, with the lanes laid over the sprite's own bounding vectors: a row of a disc is a
+//     column interval (integer-sqrt half-width and the exact inverse of the sample map come from small shared-memory
+//     tables), an interval becomes a byte mask, a layer three LOP3s per word; then the patch is streamed out.
+// A pure write stream on this GPU peaks at 6.0-6.5 TB/s (tools/wprobe.cu, profiles/wprobe_r1b.json).  Measured
+// alternatives that lost: bulk-copying the table to each frame and overlaying the sprite vectors
+// afterwards (partial rewrites cost more DRAM time than they save SM time), bulk copies for runs of untouched units,
+// overlapping consecutive launches with programmatic dependent launch, a global ticket pool for the tail, spreading
+// the envs of a CTA one per warp, an even 148-way split of the envs.
 #include "ahk_env.cuh"
 
 namespace ahk {
@@ -108,6 +112,13 @@ __device__ __forceinline__ bool mallet(uint32_t (&o)[3][4], const Luts &l, int c
     hit |= disc<100, kKnob>(o, l, cx, dy, base);
     hit |= disc<9, kShine>(o, l, cx - 3, dy + 3, base);
     return hit;
+}
+
+__device__ __forceinline__ unsigned long long global_ns()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
 }
 
 __device__ __forceinline__ void mbarrier_wait(uint32_t bar, uint32_t parity)
@@ -270,7 +281,9 @@ constexpr int kStepSmem = kLutOffset + static_cast<int>(sizeof(Luts));
 
 // kMode 0: AirHockeyEnv.reset + draw; 1: AirHockeyEnv.step + draw; 2: draw only, records from the global draw list
 // (the split path, after env_kernel).
-template <int kMode>
+// kTrace: the measurement build of the same kernel (ahk_set_trace) — per warp four %globaltimer stamps: 0 CTA start,
+// 1 game tick done, 2 records + table staged, 3 last store issued.  The product kernel carries none of it.
+template <int kMode, bool kTrace = false>
 __global__ void __launch_bounds__(kStepThreads, 1) step_kernel(StepArgs a)
 {
     extern __shared__ __align__(128) uint8_t smem[];
@@ -279,10 +292,14 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_kernel(StepArgs a)
     Luts &luts = *reinterpret_cast<Luts *>(smem + kLutOffset);
     __shared__ __align__(8) uint64_t s_table_ready;
     __shared__ int s_count;
+    __shared__ unsigned s_stats[kStatWords];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    unsigned long long *trace = kTrace ? a.trace + (static_cast<size_t>(blockIdx.x) * (kStepThreads / 32) + warp) * 4 : nullptr;
+    if (kTrace && lane == 0) trace[0] = global_ns();
     uint4 *s_patch = reinterpret_cast<uint4 *>(smem + kFrameBytes + kRecordBytes + warp * kPatchBytes); // this warp's scratch
     const uint32_t bar = static_cast<uint32_t>(__cvta_generic_to_shared(&s_table_ready));
+    if (tid < kStatWords) s_stats[tid] = 0u;
     if (tid == 0) {
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(bar) : "memory");
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -310,12 +327,13 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_kernel(StepArgs a)
         if (kMode < 2) {
             StatDelta d;
             if (live) env_update<kMode == 1>(a.env, i, rec, d);
-            accumulate_stats<kMode == 1>(a.env.stats, d);
+            if (a.env.stats != nullptr) stat_to_shared<kMode == 1>(s_stats, d, live);
         } else if (live) {
             const uint4 *dl = reinterpret_cast<const uint4 *>(a.ras.drawlist);
 #pragma unroll
             for (int b = 0; b < 3; ++b) rec[b] = __ldg(dl + b * stride + i);
         }
+        if (kTrace && lane == 0 && base == lo) trace[1] = global_ns();
         // compact the valid records into shared memory: one atomic per warp per ring slot
 #pragma unroll
         for (int b = 0; b < 3; ++b) {
@@ -333,6 +351,7 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_kernel(StepArgs a)
             mbarrier_wait(bar, 0u);
             table_ready = true;
         }
+        if (kTrace && lane == 0 && base == lo) trace[2] = global_ns();
         for (int u = warp; u < units; u += kStepThreads / 32) {
             const uint4 rec_u = s_recs[u / kUnitsPerFrame];
             const int env = base + static_cast<int>((rec_u.w >> 8) & 0x3FFu), back = static_cast<int>(rec_u.w >> 20); // back 0 = newest
@@ -340,8 +359,15 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_kernel(StepArgs a)
             uint8_t *frame = a.ras.frames + (static_cast<size_t>(slot) * stride + env) * kFrameBytes;
             draw_unit(s_table, s_patch, luts, rec_u, u % kUnitsPerFrame, frame, a.ras.env_id_base + static_cast<uint32_t>(env), a.ras.key, lane);
         }
+        if (base + kStepThreads < hi) __syncthreads(); // every warp has read this round's record count before it is cleared
     }
+    if (kTrace && lane == 0) trace[3] = global_ns();
     if (!table_ready) mbarrier_wait(bar, 0u); // never exit with the table copy still in flight
+    if (kMode < 2 && a.env.stats != nullptr) {
+        unsigned long long *st = reinterpret_cast<unsigned long long *>(a.env.stats);
+        if (tid < kStatWords && s_stats[tid] != 0u)
+            atomicAdd(st + tid, tid == 4 ? static_cast<unsigned long long>(static_cast<long long>(static_cast<int>(s_stats[tid]))) : static_cast<unsigned long long>(s_stats[tid]));
+    }
 }
 
 cudaError_t step_prepare()
@@ -349,12 +375,14 @@ cudaError_t step_prepare()
     cudaError_t e = cudaFuncSetAttribute(step_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStepSmem);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(step_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStepSmem);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(step_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStepSmem);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(step_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStepSmem);
     return e;
 }
 
 cudaError_t launch_step(const StepArgs &a, int mode, int grid, cudaStream_t stream)
 {
     if (mode == 0) step_kernel<0><<<grid, kStepThreads, kStepSmem, stream>>>(a);
+    else if (mode == 1 && a.trace) step_kernel<1, true><<<grid, kStepThreads, kStepSmem, stream>>>(a);
     else if (mode == 1) step_kernel<1><<<grid, kStepThreads, kStepSmem, stream>>>(a);
     else step_kernel<2><<<grid, kStepThreads, kStepSmem, stream>>>(a);
     return cudaGetLastError();

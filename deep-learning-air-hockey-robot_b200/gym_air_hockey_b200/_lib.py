@@ -49,6 +49,8 @@ SYMBOLS = {
     "ahk_set_head": (_i, [_vp, _i]),
     "ahk_set_pending": (_i, [_vp, _vp, _vp]),
     "ahk_launch_count": (_i, [_vp, C.POINTER(C.c_uint64)]),
+    "ahk_set_trace": (_i, [_vp, _vp]),
+    "ahk_trace_shape": (_i, [_vp, C.POINTER(_i), C.POINTER(_i)]),
     "ahk_last_error": (C.c_char_p, []),
     "ahk_version": (C.c_char_p, []),
     "ahk_policy_create": (_i, [_i, _i, C.POINTER(PolicyWeights), C.POINTER(_vp)]),
@@ -68,8 +70,12 @@ def load():
         raise ImportError(
             "%s is missing: build it with `python __graft_entry__.py` (or make -C deep-learning-air-hockey-robot_b200/csrc). "
             "The engine has no CPU or PyTorch fallback." % LIB_PATH)
-    lib = C.CDLL(LIB_PATH)
+    # AHK_LIB: an older build of the same ABI for same-box A/B timing (tools/); never a different implementation
+    override = os.environ.get("AHK_LIB")
+    lib = C.CDLL(override or LIB_PATH)
     for name, (restype, argtypes) in SYMBOLS.items():
+        if override and not hasattr(lib, name):
+            continue
         fn = getattr(lib, name)  # AttributeError if the ABI and the binding disagree
         fn.restype = restype
         fn.argtypes = argtypes

@@ -113,6 +113,12 @@ int ahk_set_head(ahk_env *env, int head);
 int ahk_set_pending(ahk_env *env, const uint8_t *pending_dev, void *stream); /* arm/disarm the auto-reset per env */
 int ahk_launch_count(const ahk_env *env, uint64_t *kernels); /* kernels launched so far by this handle */
 
+/* Measurement aid (tools/phase_trace.py -> profiles/): when trace_dev != NULL the fused step kernel stores, per CTA and
+ * warp, four %globaltimer stamps (ns) — CTA start, game tick done, records + table staged, last store issued — into
+ * trace_dev[ctas][warps][4]; ahk_trace_shape gives ctas and warps.  NULL switches it off (the default). */
+int ahk_set_trace(ahk_env *env, uint64_t *trace_dev);
+int ahk_trace_shape(const ahk_env *env, int *ctas, int *warps);
+
 const char *ahk_last_error(void);
 const char *ahk_version(void);
 

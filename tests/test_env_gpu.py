@@ -126,6 +126,33 @@ def test_forced_episodes_and_masks(cuda, orc, noise_table):
         assert np.array_equal(ring[i], o.ring()), i
 
 
+def test_back_to_back_steps_overlap(cuda, orc, noise_table):
+    """Step kernels launched back to back overlap (the next launch's game tick runs under this launch's rasterising,
+    csrc/ahk_step.cu): no host synchronisation for 45 steps, then state, the whole 3-frame ring, the last step's
+    outputs and the statistics must equal the oracle's."""
+    n, seed, steps = 333, 21, 45
+    env = make_env(n, noise_table, seed=seed, max_episode_steps=17)
+    oracles = oracle_envs(orc, n, noise_table, seed)
+    env.reset()
+    for _ in range(steps):
+        _, reward, done, info = env.step()
+    cuda.cuda.synchronize()
+    outs = []
+    for o in oracles:
+        o.reset()
+        for _ in range(steps):
+            out = o.step_auto(255, 255, 17)
+        outs.append(out)
+    assert_same_state(env, oracles, "after %d unsynchronised steps" % steps)
+    ring = ring_newest_first(env)
+    for i, o in enumerate(oracles):
+        assert np.array_equal(ring[i], o.ring()), i
+    assert np.array_equal(reward.cpu().numpy(), np.array([o.reward for o in outs], dtype=np.float32))
+    assert np.array_equal(done.cpu().numpy(), np.array([bool(o.terminal) for o in outs]))
+    assert np.array_equal(info['robot_action'].cpu().numpy(), np.array([o.robot_label for o in outs], dtype=np.uint8))
+    assert env.statistics()['steps'] == n * steps
+
+
 def stress_states(n, rs):
     """configs[4]: pucks at top speed aimed at corners, walls at grazing angles, posts and mallet edges."""
     s = np.zeros((n, 12), dtype=np.float32)

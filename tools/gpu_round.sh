@@ -1,8 +1,9 @@
 #!/bin/bash
-# One gpurun call: GPU parity tests, bench line, ncu launch list and one full capture of the dominant kernel.
-# Usage (from the repo root, on the GPU box):  bash tools/gpu_round.sh [tag]
+# One gpurun call: GPU parity tests, bench line (+ reference arm), ncu launch list and one full capture of the dominant
+# kernel.  Usage (from the repo root, on the GPU box):  bash tools/gpu_round.sh [tag] [kernel-regex]
 set -u
 TAG=${1:-r1}
+KRE=${2:-step_kernel}
 OUT=gpurun_out
 mkdir -p $OUT
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > $OUT/smi_$TAG.txt 2>&1
@@ -17,6 +18,6 @@ timeout 300 $CMD > $OUT/plain_$TAG.log 2>&1 &&
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $OUT/launches_$TAG.csv $CMD > $OUT/ncu_list_$TAG.log 2>&1
 echo "ncu list rc=$?"
 timeout 300 $CMD > $OUT/plain2_$TAG.log 2>&1 &&
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:raster_staged -s 10 -c 3 -o $OUT/raster_$TAG $CMD > $OUT/ncu_full_$TAG.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:$KRE -s 10 -c 3 -o $OUT/prof_$TAG $CMD > $OUT/ncu_full_$TAG.log 2>&1
 echo "ncu full rc=$?"
 ls -la $OUT

@@ -24,7 +24,10 @@ for p in (os.path.join(ROOT, "deep-learning-air-hockey-robot_b200"), ROOT):
 
 BYTES_PER_STEP = 49152 + 64 + 64 + 7  # frame written + state read + state written + labels/reward/done
 RASTER_BYTES_PER_FRAME = 49152 + 16   # the raster kernel alone: one frame written + one 16-byte draw record read
-RASTER_TRAFFIC_NCU = None             # dram read+write bytes per raster launch from profiles/ (ncu --set full), filled in below
+# dram__bytes_read.sum + dram__bytes_write.sum of one step_kernel<1> launch at 4096 envs, ncu --set full
+# (profiles/step_kernel_r1j_ncu.txt).  Below the algorithmic 201.9 MB because a launch ends with ~50 MB of its frames
+# still dirty in the 126 MB L2 (they reach DRAM during the next launch): nothing is re-read, nothing written twice.
+STEP_TRAFFIC_NCU_4096 = 142.62e6  # mean of three captured launches: 142.23 MB written + 0.39 MB read
 METRIC = "labeled env-steps/sec (physics+render+label)"
 
 
@@ -225,7 +228,12 @@ def main():
         kernel_bytes = n * (BYTES_PER_STEP if fused else RASTER_BYTES_PER_FRAME)
         kernel_name = "step_kernel<1> (fused physics+AI+label+raster)" if fused else \
             ("raster_staged_kernel" if os.environ.get("AHK_RASTER") == "staged" else "step_kernel<2> (raster only)")
-        achieved = kernel_bytes / (raster_ms * 1e-3) / 1e9
+        # Fused path: the timed region IS K launches of the one kernel, back to back on one stream, so its average
+        # launch duration is region / K.  (Consecutive launches overlap by programmatic dependent launch: the next
+        # launch's prologue and game tick run under this one's tail.  raster_ms, taken with events BETWEEN launches,
+        # cannot overlap and is reported as isolated_kernel_ms.)
+        kernel_ms = ms / args.steps if fused else raster_ms
+        achieved = kernel_bytes / (kernel_ms * 1e-3) / 1e9
         step_gbs = n * BYTES_PER_STEP / (ms / args.steps * 1e-3) / 1e9
         write_peak = None
         wp = os.path.join(ROOT, "profiles", "wprobe_r1b.json")  # tools/wprobe.cu: pure write streams over the same footprint
@@ -242,8 +250,9 @@ def main():
             "gpu_launches": launches,
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                         "frac": achieved / peaks["hbm_gbs"], "traffic": RASTER_TRAFFIC_NCU, "peak_kind": peak_kind + " copy (read+write)",
-                         "kernel": kernel_name, "kernel_ms": raster_ms, "env_kernel_ms": env_ms,
+                         "frac": achieved / peaks["hbm_gbs"], "traffic": STEP_TRAFFIC_NCU_4096 if (fused and n == 4096) else None,
+                         "peak_kind": peak_kind + " copy (read+write)",
+                         "kernel": kernel_name, "kernel_ms": kernel_ms, "isolated_kernel_ms": raster_ms, "env_kernel_ms": env_ms,
                          "bytes_per_launch": kernel_bytes,
                          "whole_step": {"achieved": step_gbs, "frac": step_gbs / peaks["hbm_gbs"], "bytes_per_env_step": BYTES_PER_STEP},
                          "write_only_peak": write_peak,

@@ -51,6 +51,15 @@ struct ahk_env {
     bool split = false, staged = false;
     uint64_t launches = 0;
     unsigned long long *trace = nullptr; // ahk_set_trace
+    // adaptive partition (StepArgs): two boundary arrays (this launch / next launch), rates, finish counter
+    int *bounds_dev[2] = {nullptr, nullptr};
+    unsigned long long *end_dev = nullptr;
+    unsigned *done_dev = nullptr;
+    int bounds_cur = 0;
+    unsigned adapt_tick = 0, adapt_every = 8;
+    int switch_in = 0;
+    bool balance = true; // A/B switch AHK_BALANCE=0
+    int pdl = -1;        // programmatic dependent launch of consecutive step kernels; -1: by size (ahk_create); A/B switch AHK_PDL=0/1
     cudaEvent_t ev[3] = {nullptr, nullptr, nullptr}; // ahk_step_profiled: before env_kernel, between, after raster
 };
 
@@ -98,10 +107,36 @@ ahk::RasterArgs raster_args(const ahk_env *e)
     return r;
 }
 
+ahk::StepArgs step_args(ahk_env *e, const ahk::EnvArgs &a, int mode)
+{
+    ahk::StepArgs st{};
+    st.env = a;
+    st.ras = raster_args(e);
+    st.envs_per_cta = e->envs_per_cta;
+    // two trace slots, alternating per launch, so that overlapped consecutive launches can be laid side by side
+    st.trace = e->trace ? e->trace + (e->launches & 1u) * static_cast<size_t>(e->step_grid) * (ahk::kStepThreads / 32) * 4 : nullptr;
+    st.pdl = e->pdl;
+    if (e->balance && !e->split) {
+        // New boundaries are taken into use two launches after the one that computes them: with overlapped launches
+        // the very next kernel may already be reading its boundaries while the last CTA of this one writes.
+        if (e->switch_in > 0 && --e->switch_in == 0) e->bounds_cur ^= 1;
+        st.bounds = e->bounds_dev[e->bounds_cur];
+        // steps adapt, every 8th one (the last CTA's boundary computation is ~2 us on the launch's tail); a reset (three
+        // frames per env, once) only uses the current boundaries
+        if (mode == 1 && e->switch_in == 0 && (e->adapt_tick++ % e->adapt_every) == 0) {
+            st.bounds_next = e->bounds_dev[e->bounds_cur ^ 1];
+            st.end_ns = e->end_dev;
+            st.done_count = e->done_dev;
+            e->switch_in = 2;
+        }
+    }
+    return st;
+}
+
 // One pass of the hot path: mode 0 = reset (+ warm-up frames), 1 = step.  Default: ONE fused kernel.
 int run(ahk_env *e, const ahk::EnvArgs &a, int mode, cudaStream_t s)
 {
-    ahk::StepArgs st{a, raster_args(e), e->envs_per_cta, e->trace};
+    ahk::StepArgs st = step_args(e, a, mode);
     if (!e->split) {
         AHK_CUDA(ahk::launch_step(st, mode, e->step_grid, s));
         e->launches += 1;
@@ -140,13 +175,35 @@ int ahk_create(const ahk_config *cfg, ahk_env **out)
     if (!e) return fail(AHK_ERR_ARG, "out of host memory");
     e->cfg = *cfg;
     if (const char *s = getenv("AHK_PATH")) e->split = strcmp(s, "split") == 0;
+    if (const char *s = getenv("AHK_ADAPT_EVERY")) e->adapt_every = atoi(s) > 0 ? atoi(s) : 1;
+    if (const char *s = getenv("AHK_PDL")) e->pdl = atoi(s);
+    if (const char *s = getenv("AHK_BALANCE")) e->balance = atoi(s) != 0;
     if (const char *s = getenv("AHK_RASTER")) e->staged = strcmp(s, "staged") == 0;
     e->sms = prop.multiProcessorCount;
     e->raster_grid = e->sms;
     e->envs_per_cta = (cfg->n_envs + e->sms - 1) / e->sms;
     e->step_grid = (cfg->n_envs + e->envs_per_cta - 1) / e->envs_per_cta;
+    if (e->balance && !e->split && cfg->n_envs >= 4 * e->sms) e->step_grid = e->sms; // the adaptive partition uses every SM
+    else e->balance = false;
+    // Overlapping consecutive launches hides ~5 us of prologue + launch latency per step, but the next launch's CTAs
+    // then land on whichever SM retires first, so CTA index no longer names an SM and the adaptive partition (worth 7 %
+    // on long launches) loses its footing.  Measured cross-over ~10 k envs (profiles/launch_modes_r1.txt).
+    if (e->pdl < 0) e->pdl = cfg->n_envs <= 10240 ? 1 : 0;
     cudaError_t err = cudaMalloc(&e->table_dev, ahk::kFrameBytes);
     if (err == cudaSuccess) err = cudaMalloc(&e->action_stage, 2 * static_cast<size_t>(cfg->n_envs));
+    if (err == cudaSuccess && e->balance) {
+        const int g = e->step_grid;
+        std::vector<int> even(g + 1);
+        for (int b = 0; b <= g; ++b) even[b] = static_cast<int>(static_cast<long long>(b) * cfg->n_envs / g);
+        for (int k = 0; k < 2 && err == cudaSuccess; ++k) {
+            err = cudaMalloc(&e->bounds_dev[k], (g + 1) * sizeof(int));
+            if (err == cudaSuccess) err = cudaMemcpy(e->bounds_dev[k], even.data(), (g + 1) * sizeof(int), cudaMemcpyHostToDevice);
+        }
+        if (err == cudaSuccess) err = cudaMalloc(&e->end_dev, g * sizeof(unsigned long long));
+        if (err == cudaSuccess) err = cudaMemset(e->end_dev, 0, g * sizeof(unsigned long long));
+        if (err == cudaSuccess) err = cudaMalloc(&e->done_dev, sizeof(unsigned));
+        if (err == cudaSuccess) err = cudaMemset(e->done_dev, 0, sizeof(unsigned));
+    }
     if (err == cudaSuccess) err = cudaStreamCreateWithFlags(&e->host_stream, cudaStreamNonBlocking);
     for (int k = 0; k < 3 && err == cudaSuccess; ++k) err = cudaEventCreate(&e->ev[k]);
     if (err == cudaSuccess) err = ahk::step_prepare();
@@ -165,6 +222,9 @@ void ahk_destroy(ahk_env *e)
     cudaSetDevice(e->cfg.device);
     if (e->table_dev) cudaFree(e->table_dev);
     if (e->action_stage) cudaFree(e->action_stage);
+    for (int k = 0; k < 2; ++k) if (e->bounds_dev[k]) cudaFree(e->bounds_dev[k]);
+    if (e->end_dev) cudaFree(e->end_dev);
+    if (e->done_dev) cudaFree(e->done_dev);
     if (e->host_stream) cudaStreamDestroy(e->host_stream);
     for (int k = 0; k < 3; ++k) if (e->ev[k]) cudaEventDestroy(e->ev[k]);
     delete e;
@@ -243,7 +303,7 @@ int ahk_step_profiled(ahk_env *e, const uint8_t *robot, const uint8_t *human, vo
         AHK_CUDA(cudaEventElapsedTime(raster_ms, e->ev[0], e->ev[2]));
         return AHK_OK;
     }
-    ahk::StepArgs st{a, raster_args(e), e->envs_per_cta, e->trace};
+    ahk::StepArgs st = step_args(e, a, 1);
     AHK_CUDA(ahk::launch_env(a, true, s));
     AHK_CUDA(cudaEventRecord(e->ev[1], s));
     if (e->staged) AHK_CUDA(ahk::launch_raster_staged(st.ras, e->raster_grid, s));
@@ -323,6 +383,21 @@ int ahk_trace_shape(const ahk_env *e, int *ctas, int *warps)
     *ctas = e->step_grid;
     *warps = ahk::kStepThreads / 32;
     return AHK_OK;
+}
+
+int ahk_get_partition(ahk_env *e, int32_t *bounds_host, int capacity)
+{
+    if (!e || !bounds_host) return fail(AHK_ERR_ARG, "env/bounds_host is NULL");
+    const int g = e->step_grid;
+    if (capacity < g + 1) return fail(AHK_ERR_ARG, "capacity %d < %d", capacity, g + 1);
+    if (!e->balance) {
+        for (int b = 0; b <= g; ++b) bounds_host[b] = b * e->envs_per_cta < e->cfg.n_envs ? b * e->envs_per_cta : e->cfg.n_envs;
+        return g;
+    }
+    AHK_CUDA(cudaSetDevice(e->cfg.device));
+    AHK_CUDA(cudaDeviceSynchronize());
+    AHK_CUDA(cudaMemcpy(bounds_host, e->bounds_dev[e->bounds_cur], (g + 1) * sizeof(int), cudaMemcpyDeviceToHost));
+    return g;
 }
 
 int ahk_launch_count(const ahk_env *e, uint64_t *kernels)

@@ -13,14 +13,17 @@ namespace ahk {
 __device__ __forceinline__ void load_sim(const uint32_t *__restrict__ st, int n, int i, Sim &s, uint32_t &reset_count,
                                          uint32_t &noise_count, uint32_t &meta)
 {
-    auto f = [&](int w) { return __uint_as_float(st[static_cast<size_t>(w) * n + i]); };
+    // ld.global.cg: with overlapped launches and a moving partition another SM may have written these words while this
+    // SM's L1 was live
+    auto u = [&](int w) { return __ldcg(st + static_cast<size_t>(w) * n + i); };
+    auto f = [&](int w) { return __uint_as_float(u(w)); };
     s.puck = Body{f(0), f(1), f(2), f(3)};
     s.bot = Body{f(4), f(5), f(6), f(7)};
     s.top = Body{f(8), f(9), f(10), f(11)};
-    s.serve_count = st[static_cast<size_t>(12) * n + i];
-    reset_count = st[static_cast<size_t>(13) * n + i];
-    noise_count = st[static_cast<size_t>(14) * n + i];
-    meta = st[static_cast<size_t>(15) * n + i];
+    s.serve_count = u(12);
+    reset_count = u(13);
+    noise_count = u(14);
+    meta = u(15);
 }
 
 __device__ __forceinline__ void store_sim(uint32_t *__restrict__ st, int n, int i, const Sim &s, uint32_t reset_count,

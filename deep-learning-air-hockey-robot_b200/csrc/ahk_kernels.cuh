@@ -42,6 +42,14 @@ struct StepArgs { // the fused kernel: env block b of envs_per_cta environments 
     EnvArgs env;
     RasterArgs ras;
     int envs_per_cta;
+    // Adaptive partition (nullptr: CTA b owns [b * envs_per_cta, ...)).  SMs do not drain their stores equally fast (their
+    // place in the memory system), and the difference is stable from launch to launch: every CTA stamps its end time,
+    // the last CTA to finish moves the env boundaries against each CTA's lateness (ahk_step.cu, rebalance).
+    const int *bounds;       // [grid + 1] env boundaries for THIS launch
+    int *bounds_next;        // [grid + 1] written by the last CTA (nullptr: do not adapt)
+    unsigned long long *end_ns; // [grid] %globaltimer at each CTA's end, this launch
+    unsigned *done_count;    // CTAs finished in this launch
+    int pdl;                 // launched with programmatic stream serialization: griddepcontrol.* are live (2: experiment, no wait)
     unsigned long long *trace; // measurement aid (ahk_set_trace): [grid][32 warps][4] %globaltimer stamps; selects the traced kernel
 };
 

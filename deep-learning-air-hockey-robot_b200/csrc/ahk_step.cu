@@ -281,6 +281,80 @@ constexpr int kStepSmem = kLutOffset + static_cast<int>(sizeof(Luts));
 
 // kMode 0: AirHockeyEnv.reset + draw; 1: AirHockeyEnv.step + draw; 2: draw only, records from the global draw list
 // (the split path, after env_kernel).
+// Adaptive partition, end of a step launch.  SMs do not drain their stores equally fast, and with overlapped launches
+// the SM that finishes last also starts the next launch last: left alone, lateness feeds on itself.  So the shares are
+// steered on what matters, the END time: the last warp of each CTA stamps %globaltimer; the last CTA of the grid moves
+// every CTA's share of the envs against its lateness relative to the mean (an integral controller, gain 1/2, shares kept
+// within +-50 % of even) and writes the boundaries a later launch will use.  Results do not depend on the partition:
+// state lives in HBM, every env is ticked and drawn exactly once whoever owns it.
+__device__ __forceinline__ void rebalance(const StepArgs &a, unsigned *warps_done, const unsigned long long *raster_start, int lane)
+{
+    unsigned k = 0;
+    if (lane == 0) { __threadfence_block(); k = atomicAdd(warps_done, 1u); }
+    k = __shfl_sync(0xFFFFFFFFu, k, 0);
+    if (k != kStepThreads / 32 - 1) return; // this warp is the CTA's last
+    const int grid = static_cast<int>(gridDim.x);
+    unsigned finished = 0;
+    unsigned long long end = 0;
+    if (lane == 0) {
+        end = global_ns();
+        a.end_ns[blockIdx.x] = end;
+        __threadfence();
+        finished = atomicAdd(a.done_count, 1u);
+    }
+    finished = __shfl_sync(0xFFFFFFFFu, finished, 0);
+    if (finished != static_cast<unsigned>(grid) - 1u) return; // this CTA is the grid's last
+    __threadfence();
+    end = __shfl_sync(0xFFFFFFFFu, end, 0);
+    const float span = fmaxf(static_cast<float>(end - *raster_start), 1000.0f); // ns this CTA spent rasterising: the scale
+    constexpr int kPer = 8; // CTAs per lane: up to 256 CTAs
+    float early[kPer], share[kPer], sum_early = 0.0f;
+#pragma unroll
+    for (int j = 0; j < kPer; ++j) {
+        const int b = lane * kPer + j;
+        early[j] = share[j] = 0.0f;
+        if (b < grid) {
+            const unsigned long long e = __ldcg(a.end_ns + b);
+            early[j] = e < end ? static_cast<float>(end - e) : 0.0f; // ns before the last CTA
+            share[j] = static_cast<float>(a.bounds[b + 1] - a.bounds[b]);
+            sum_early += early[j];
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sum_early += __shfl_xor_sync(0xFFFFFFFFu, sum_early, o);
+    const float mean_early = sum_early / static_cast<float>(grid);
+    const float even = static_cast<float>(a.ras.n) / static_cast<float>(grid);
+    float mine = 0.0f;
+#pragma unroll
+    for (int j = 0; j < kPer; ++j) {
+        const int b = lane * kPer + j;
+        if (b < grid) {
+            const float late = (mean_early - early[j]) / span; // > 0: later than the average CTA, as a fraction of the launch
+            share[j] = fminf(fmaxf(share[j] - 0.5f * late * even, 0.5f * even), 1.5f * even);
+            mine += share[j];
+        }
+    }
+    float before = mine; // inclusive prefix over the lanes
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const float up = __shfl_up_sync(0xFFFFFFFFu, before, o);
+        if (lane >= o) before += up;
+    }
+    const float all = __shfl_sync(0xFFFFFFFFu, before, 31);
+    const float scale = static_cast<float>(a.ras.n) / all;
+    float cum = before - mine;
+    if (lane == 0) a.bounds_next[0] = 0;
+#pragma unroll
+    for (int j = 0; j < kPer; ++j) {
+        const int b = lane * kPer + j;
+        if (b < grid) {
+            cum += share[j];
+            a.bounds_next[b + 1] = b == grid - 1 ? a.ras.n : min(a.ras.n, __float2int_rn(cum * scale));
+        }
+    }
+    if (lane == 0) *a.done_count = 0u;
+}
+
 // kTrace: the measurement build of the same kernel (ahk_set_trace) — per warp four %globaltimer stamps: 0 CTA start,
 // 1 game tick done, 2 records + table staged, 3 last store issued.  The product kernel carries none of it.
 template <int kMode, bool kTrace = false>
@@ -293,6 +367,8 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_kernel(StepArgs a)
     __shared__ __align__(8) uint64_t s_table_ready;
     __shared__ int s_count;
     __shared__ unsigned s_stats[kStatWords];
+    __shared__ unsigned s_warps_done;
+    __shared__ unsigned long long s_raster_start;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     unsigned long long *trace = kTrace ? a.trace + (static_cast<size_t>(blockIdx.x) * (kStepThreads / 32) + warp) * 4 : nullptr;
@@ -300,6 +376,7 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_kernel(StepArgs a)
     uint4 *s_patch = reinterpret_cast<uint4 *>(smem + kFrameBytes + kRecordBytes + warp * kPatchBytes); // this warp's scratch
     const uint32_t bar = static_cast<uint32_t>(__cvta_generic_to_shared(&s_table_ready));
     if (tid < kStatWords) s_stats[tid] = 0u;
+    if (tid == 0) { s_warps_done = 0u; s_raster_start = 0ull; }
     if (tid == 0) {
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(bar) : "memory");
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -314,7 +391,8 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_kernel(StepArgs a)
     bool table_ready = false;
 
     const int n = a.ras.n;
-    const int lo = blockIdx.x * a.envs_per_cta, hi = min(n, lo + a.envs_per_cta);
+    int lo = blockIdx.x * a.envs_per_cta, hi = min(n, lo + a.envs_per_cta);
+    if (a.bounds != nullptr) { lo = a.bounds[blockIdx.x]; hi = a.bounds[blockIdx.x + 1]; }
     const size_t stride = static_cast<size_t>(n);
 
     for (int base = lo; base < hi; base += kStepThreads) {
@@ -333,6 +411,7 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_kernel(StepArgs a)
 #pragma unroll
             for (int b = 0; b < 3; ++b) rec[b] = __ldg(dl + b * stride + i);
         }
+        if (a.pdl) __threadfence(); // this thread's state and outputs are out before the barrier below, hence before the trigger
         if (kTrace && lane == 0 && base == lo) trace[1] = global_ns();
         // compact the valid records into shared memory: one atomic per warp per ring slot
 #pragma unroll
@@ -346,12 +425,18 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_kernel(StepArgs a)
             if (valid) s_recs[at] = make_uint4(rec[b].x, rec[b].y, rec[b].z, (rec[b].w & 0xFFu) | static_cast<uint32_t>(tid) << 8 | static_cast<uint32_t>(b) << 20);
         }
         __syncthreads();
+        // Programmatic dependent launch: once every CTA has ticked its last round the NEXT step kernel may be scheduled;
+        // its CTAs move in as ours retire, and its prologue and game tick (which read only the state fenced above) run
+        // while the rest of this grid is still draining its stores.
+        if (a.pdl && base + kStepThreads >= hi) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
         const int units = s_count * kUnitsPerFrame;
         if (!table_ready) {
             mbarrier_wait(bar, 0u);
             table_ready = true;
+            if (a.pdl == 1) asm volatile("griddepcontrol.wait;" ::: "memory"); // no frame is written before the previous launch has completed
         }
         if (kTrace && lane == 0 && base == lo) trace[2] = global_ns();
+        if (a.bounds_next != nullptr && tid == 0 && base == lo) s_raster_start = global_ns();
         for (int u = warp; u < units; u += kStepThreads / 32) {
             const uint4 rec_u = s_recs[u / kUnitsPerFrame];
             const int env = base + static_cast<int>((rec_u.w >> 8) & 0x3FFu), back = static_cast<int>(rec_u.w >> 20); // back 0 = newest
@@ -362,6 +447,7 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_kernel(StepArgs a)
         if (base + kStepThreads < hi) __syncthreads(); // every warp has read this round's record count before it is cleared
     }
     if (kTrace && lane == 0) trace[3] = global_ns();
+    if (kMode == 1 && a.bounds_next != nullptr) rebalance(a, &s_warps_done, &s_raster_start, lane);
     if (!table_ready) mbarrier_wait(bar, 0u); // never exit with the table copy still in flight
     if (kMode < 2 && a.env.stats != nullptr) {
         unsigned long long *st = reinterpret_cast<unsigned long long *>(a.env.stats);
@@ -381,11 +467,20 @@ cudaError_t step_prepare()
 
 cudaError_t launch_step(const StepArgs &a, int mode, int grid, cudaStream_t stream)
 {
-    if (mode == 0) step_kernel<0><<<grid, kStepThreads, kStepSmem, stream>>>(a);
-    else if (mode == 1 && a.trace) step_kernel<1, true><<<grid, kStepThreads, kStepSmem, stream>>>(a);
-    else if (mode == 1) step_kernel<1><<<grid, kStepThreads, kStepSmem, stream>>>(a);
-    else step_kernel<2><<<grid, kStepThreads, kStepSmem, stream>>>(a);
-    return cudaGetLastError();
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(static_cast<unsigned>(grid));
+    cfg.blockDim = dim3(kStepThreads);
+    cfg.dynamicSmemBytes = kStepSmem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = a.pdl ? 1 : 0;
+    if (mode == 0) return cudaLaunchKernelEx(&cfg, step_kernel<0>, a);
+    if (mode == 1 && a.trace) return cudaLaunchKernelEx(&cfg, step_kernel<1, true>, a);
+    if (mode == 1) return cudaLaunchKernelEx(&cfg, step_kernel<1>, a);
+    return cudaLaunchKernelEx(&cfg, step_kernel<2>, a);
 }
 
 } // namespace ahk

@@ -51,6 +51,7 @@ SYMBOLS = {
     "ahk_launch_count": (_i, [_vp, C.POINTER(C.c_uint64)]),
     "ahk_set_trace": (_i, [_vp, _vp]),
     "ahk_trace_shape": (_i, [_vp, C.POINTER(_i), C.POINTER(_i)]),
+    "ahk_get_partition": (_i, [_vp, C.POINTER(C.c_int32), _i]),
     "ahk_last_error": (C.c_char_p, []),
     "ahk_version": (C.c_char_p, []),
     "ahk_policy_create": (_i, [_i, _i, C.POINTER(PolicyWeights), C.POINTER(_vp)]),

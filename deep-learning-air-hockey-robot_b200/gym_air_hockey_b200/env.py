@@ -223,6 +223,14 @@ class BatchedAirHockeyEnv(object):
                   pick(use, 'use') << 18 | pick(pending, 'pending') << 21)
         self.state.copy_(torch.from_numpy(st.view(np.int32)))
 
+    def partition(self):
+        """Env boundaries of the step kernel's CTAs right now (int32[ctas + 1]; the adaptive partition)."""
+        buf = (C.c_int32 * 1024)()
+        g = self.lib.ahk_get_partition(self._h, buf, 1024)
+        if g < 0:
+            _lib.check(g)
+        return np.array(buf[:g + 1], dtype=np.int32)
+
     def statistics(self):
         """Running sums since construction (this GPU only; gather across ranks with parallel.gather_statistics)."""
         s = self.stats.cpu().numpy()

@@ -115,9 +115,13 @@ int ahk_launch_count(const ahk_env *env, uint64_t *kernels); /* kernels launched
 
 /* Measurement aid (tools/phase_trace.py -> profiles/): when trace_dev != NULL the fused step kernel stores, per CTA and
  * warp, four %globaltimer stamps (ns) — CTA start, game tick done, records + table staged, last store issued — into
- * trace_dev[ctas][warps][4]; ahk_trace_shape gives ctas and warps.  NULL switches it off (the default). */
+ * trace_dev[2][ctas][warps][4] (slot = launch count & 1, so consecutive overlapped launches can be compared);
+ * ahk_trace_shape gives ctas and warps.  NULL switches it off (the default). */
 int ahk_set_trace(ahk_env *env, uint64_t *trace_dev);
 int ahk_trace_shape(const ahk_env *env, int *ctas, int *warps);
+/* The env boundaries of the step kernel's CTAs right now (adaptive partition): bounds_host[0..ctas], returns
+ * ctas or a negative status.  Synchronises the device.  Diagnostics and tests only. */
+int ahk_get_partition(ahk_env *env, int32_t *bounds_host, int capacity);
 
 const char *ahk_last_error(void);
 const char *ahk_version(void);

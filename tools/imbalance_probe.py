@@ -15,13 +15,13 @@ def run(seed, steps=40, n=4096):
         env.step()
     ctas, warps = C.c_int(), C.c_int()
     env.lib.ahk_trace_shape(env._h, C.byref(ctas), C.byref(warps))
-    tr = torch.zeros((ctas.value, warps.value, 4), dtype=torch.int64, device='cuda')
+    tr = torch.zeros((2, ctas.value, warps.value, 4), dtype=torch.int64, device='cuda')
     env.lib.ahk_set_trace(env._h, C.c_void_p(tr.data_ptr()))
     ends, noise = [], []
     bounds = [b * n // ctas.value for b in range(ctas.value + 1)]
     for _ in range(steps):
         torch.cuda.synchronize(); env.step(); torch.cuda.synchronize()
-        t = tr.cpu().numpy().astype(np.float64)
+        t = tr[(env.launches - 1) & 1].cpu().numpy().astype(np.float64)
         ends.append((t[:, :, 3].max(axis=1) - t[:, :, 0].min()) / 1e3)
         ep = env.get_state()[1]['episode']
         noise.append([int((ep[bounds[b]:bounds[b + 1]] == 2).sum()) for b in range(ctas.value)])

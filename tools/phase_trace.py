@@ -19,7 +19,8 @@ for _ in range(20):
     env.step()
 ctas, warps = C.c_int(), C.c_int()
 _lib.check(env.lib.ahk_trace_shape(env._h, C.byref(ctas), C.byref(warps)))
-trace = torch.zeros((ctas.value, warps.value, 4), dtype=torch.int64, device=env.device)
+trace2 = torch.zeros((2, ctas.value, warps.value, 4), dtype=torch.int64, device=env.device)
+trace = trace2
 _lib.check(env.lib.ahk_set_trace(env._h, C.c_void_p(trace.data_ptr())))
 rows = []
 for _ in range(args.steps):
@@ -27,7 +28,7 @@ for _ in range(args.steps):
     torch.cuda.synchronize()
     env.step()
     torch.cuda.synchronize()
-    t = trace.cpu().numpy().astype(np.float64)
+    t = trace2[(env.launches - 1) & 1].cpu().numpy().astype(np.float64)
     t0 = t[:, :, 0].min()
     rows.append({
         "cta_start_spread_us": (t[:, 0, 0].max() - t0) / 1e3,

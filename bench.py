@@ -211,12 +211,43 @@ def main():
     barrier()
     e2e_s = time.perf_counter() - t0
 
-    t = torch.tensor([ms, e2e_s, raster_ms, env_ms], dtype=torch.float64, device="cuda")
+    # ---- the same call pipelined (ahk_step_host_begin/_wait, 4 steps in flight, each with its own host buffers): valid
+    # for this workload because the AI plays both sides — the next actions do not depend on this step's results
+    depth = 4
+    outs = [env.host_buffers(want_frame=False) for _ in range(depth)]
+    acts = [torch.full((n,), 255, dtype=torch.uint8).pin_memory().numpy() for _ in range(depth)]
+    tickets = [env.step_host_begin(acts[k], acts[k], outs[k]) for k in range(depth)]
+    for k in range(depth):
+        env.step_host_wait(tickets[k])
+    barrier()
+    t0 = time.perf_counter()
+    tickets = [env.step_host_begin(acts[k], acts[k], outs[k]) for k in range(depth)]
+    for i in range(e2e_steps):
+        k = i % depth
+        env.step_host_wait(tickets[k])
+        checksum = float(outs[k]['reward'][0])  # the host reads the step's result
+        if i + depth < e2e_steps:
+            tickets[k] = env.step_host_begin(acts[k], acts[k], outs[k])
+    barrier()
+    pipe_s = time.perf_counter() - t0
+
+    # ---- and with the new frame copied to the host every step (49 152 B per env over PCIe): the dataset-writer case
+    outf = env.host_buffers(want_frame=True)
+    frame_steps = max(min(e2e_steps // 20, 50), 5)
+    env.step_host(act, act, outf)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(frame_steps):
+        env.step_host(act, act, outf)
+    barrier()
+    frames_s = (time.perf_counter() - t0) / frame_steps
+
+    t = torch.tensor([ms, e2e_s, raster_ms, env_ms, pipe_s, frames_s], dtype=torch.float64, device="cuda")
     stats = env.stats.clone()
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(stats, op=dist.ReduceOp.SUM)  # episode statistics: the only collective, off the step path
-    ms, e2e_s, raster_ms, env_ms = (v.item() for v in t)
+    ms, e2e_s, raster_ms, env_ms, pipe_s, frames_s = (v.item() for v in t)
 
     if rank == 0:
         peaks, peak_kind = measured_peaks()
@@ -259,7 +290,10 @@ def main():
                          "frac_of_write_only_peak": (achieved / write_peak) if write_peak else None,
                          "note": "the path only WRITES; write_only_peak = best steady-state pure write stream (st.global.cs.v4 / cp.async.bulk) over the same 3 x 201 MB ring, tools/wprobe.cu -> profiles/wprobe_r1b.json; peak = MEASURED_PEAKS.json copy (read+write)"},
             "e2e": {"value": total_envs * e2e_steps / e2e_s, "unit": "env-steps/s", "h2d_bytes_per_step": 2 * n,
-                    "d2h_bytes_per_step": 7 * n, "note": "ahk_step_host: actions from pinned host memory, reward/done/labels back to host; frames stay in the HBM ring"},
+                    "d2h_bytes_per_step": 7 * n,
+                    "note": "ahk_step_host, one synchronous call per step: actions (2 B/env) read from pinned host memory and reward/done/labels (7 B/env) written to pinned host memory by the step kernel itself (mapped, zero-copy), then the host waits; frames stay in the HBM ring",
+                    "pipelined": {"value": total_envs * e2e_steps / pipe_s, "depth": depth, "note": "ahk_step_host_begin/_wait, same bytes per step; legal when actions do not depend on results (AI vs AI data generation)"},
+                    "with_frames_to_host": {"value": total_envs / frames_s, "d2h_bytes_per_step": (7 + 49152) * n, "note": "new uint8 frame of every env copied to pinned host memory each step (PCIe-bound)"}},
             "stats": {"steps": int(stats[0]), "episodes": int(stats[1]), "goals_top": int(stats[2]), "goals_bottom": int(stats[3])},
         }
         if world == 1 and not args.no_cpu_baseline:

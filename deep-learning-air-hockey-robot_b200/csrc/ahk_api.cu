@@ -42,6 +42,10 @@ struct ahk_env {
     uint4 *table_dev = nullptr;      // [3][128][8] vectors
     uint8_t *action_stage = nullptr; // [2][n] device staging for ahk_step_host
     cudaStream_t host_stream = nullptr;
+    static constexpr int kHostDepth = 8;  // ahk_step_host_begin calls that may be in flight
+    cudaEvent_t host_ev[kHostDepth] = {};
+    uint64_t host_ticket = 0;
+    bool zero_copy = true;                // A/B switch AHK_ZEROCOPY=0: always use the copy engine in ahk_step_host
     int head = 0;
     int sms = 0;
     int raster_grid = 0;        // staged rasteriser (split path): one persistent CTA per SM
@@ -149,6 +153,15 @@ int run(ahk_env *e, const ahk::EnvArgs &a, int mode, cudaStream_t s)
     return AHK_OK;
 }
 
+// Device-visible alias of a pinned (cudaHostAlloc / cudaHostRegister) host pointer, or nullptr for pageable memory.
+template <typename T> T *mapped(T *host)
+{
+    if (!host) return nullptr;
+    cudaPointerAttributes at{};
+    if (cudaPointerGetAttributes(&at, host) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return at.type == cudaMemoryTypeHost ? static_cast<T *>(at.devicePointer) : nullptr;
+}
+
 } // namespace
 
 extern "C" {
@@ -179,6 +192,7 @@ int ahk_create(const ahk_config *cfg, ahk_env **out)
     if (const char *s = getenv("AHK_PDL")) e->pdl = atoi(s);
     if (const char *s = getenv("AHK_BALANCE")) e->balance = atoi(s) != 0;
     if (const char *s = getenv("AHK_RASTER")) e->staged = strcmp(s, "staged") == 0;
+    if (const char *s = getenv("AHK_ZEROCOPY")) e->zero_copy = atoi(s) != 0;
     e->sms = prop.multiProcessorCount;
     e->raster_grid = e->sms;
     e->envs_per_cta = (cfg->n_envs + e->sms - 1) / e->sms;
@@ -206,6 +220,7 @@ int ahk_create(const ahk_config *cfg, ahk_env **out)
     }
     if (err == cudaSuccess) err = cudaStreamCreateWithFlags(&e->host_stream, cudaStreamNonBlocking);
     for (int k = 0; k < 3 && err == cudaSuccess; ++k) err = cudaEventCreate(&e->ev[k]);
+    for (int k = 0; k < ahk_env::kHostDepth && err == cudaSuccess; ++k) err = cudaEventCreateWithFlags(&e->host_ev[k], cudaEventDisableTiming);
     if (err == cudaSuccess) err = ahk::step_prepare();
     if (err == cudaSuccess) err = ahk::raster_staged_prepare();
     if (err != cudaSuccess) {
@@ -227,6 +242,7 @@ void ahk_destroy(ahk_env *e)
     if (e->done_dev) cudaFree(e->done_dev);
     if (e->host_stream) cudaStreamDestroy(e->host_stream);
     for (int k = 0; k < 3; ++k) if (e->ev[k]) cudaEventDestroy(e->ev[k]);
+    for (int k = 0; k < ahk_env::kHostDepth; ++k) if (e->host_ev[k]) cudaEventDestroy(e->host_ev[k]);
     delete e;
 }
 
@@ -316,26 +332,56 @@ int ahk_step_profiled(ahk_env *e, const uint8_t *robot, const uint8_t *human, vo
     return AHK_OK;
 }
 
-int ahk_step_host(ahk_env *e, const uint8_t *robot, const uint8_t *human, float *reward, uint8_t *done,
-                  uint8_t *robot_label, uint8_t *human_label, uint8_t *frame)
+int ahk_step_host_begin(ahk_env *e, const uint8_t *robot, const uint8_t *human, float *reward, uint8_t *done,
+                        uint8_t *robot_label, uint8_t *human_label, uint8_t *frame)
 {
     if (int rc = check_ready(e)) return rc;
     AHK_CUDA(cudaSetDevice(e->cfg.device));
     cudaStream_t s = e->host_stream;
     const size_t n = static_cast<size_t>(e->cfg.n_envs);
-    uint8_t *robot_dev = nullptr, *human_dev = nullptr;
-    if (robot) { robot_dev = e->action_stage; AHK_CUDA(cudaMemcpyAsync(robot_dev, robot, n, cudaMemcpyHostToDevice, s)); }
-    if (human) { human_dev = e->action_stage + n; AHK_CUDA(cudaMemcpyAsync(human_dev, human, n, cudaMemcpyHostToDevice, s)); }
-    if (int rc = ahk_step(e, robot_dev, human_dev, s)) return rc;
-    if (reward) AHK_CUDA(cudaMemcpyAsync(reward, e->buf.reward, n * sizeof(float), cudaMemcpyDeviceToHost, s));
-    if (done) AHK_CUDA(cudaMemcpyAsync(done, e->buf.done, n, cudaMemcpyDeviceToHost, s));
-    if (robot_label) AHK_CUDA(cudaMemcpyAsync(robot_label, e->buf.robot_label, n, cudaMemcpyDeviceToHost, s));
-    if (human_label) AHK_CUDA(cudaMemcpyAsync(human_label, e->buf.human_label, n, cudaMemcpyDeviceToHost, s));
+    // Pinned buffers are read and written by the step kernel itself (mapped host memory, 2 + 7 bytes per env over PCIe):
+    // the whole call is ONE kernel launch.  Pageable buffers go through the copy engine.
+    const bool zc = !e->split && e->zero_copy;
+    const uint8_t *robot_dev = zc ? mapped(robot) : nullptr, *human_dev = zc ? mapped(human) : nullptr;
+    if (robot && !robot_dev) { robot_dev = e->action_stage; AHK_CUDA(cudaMemcpyAsync(e->action_stage, robot, n, cudaMemcpyHostToDevice, s)); }
+    if (human && !human_dev) { human_dev = e->action_stage + n; AHK_CUDA(cudaMemcpyAsync(e->action_stage + n, human, n, cudaMemcpyHostToDevice, s)); }
+    ahk::EnvArgs a = env_args(e);
+    a.robot = robot_dev;
+    a.human = human_dev;
+    if (zc) {
+        a.h_reward = mapped(reward);
+        a.h_done = mapped(done);
+        a.h_robot_label = mapped(robot_label);
+        a.h_human_label = mapped(human_label);
+    }
+    e->head = (e->head + 1) % 3;
+    if (int rc = run(e, a, 1, s)) return rc;
+    if (reward && !a.h_reward) AHK_CUDA(cudaMemcpyAsync(reward, e->buf.reward, n * sizeof(float), cudaMemcpyDeviceToHost, s));
+    if (done && !a.h_done) AHK_CUDA(cudaMemcpyAsync(done, e->buf.done, n, cudaMemcpyDeviceToHost, s));
+    if (robot_label && !a.h_robot_label) AHK_CUDA(cudaMemcpyAsync(robot_label, e->buf.robot_label, n, cudaMemcpyDeviceToHost, s));
+    if (human_label && !a.h_human_label) AHK_CUDA(cudaMemcpyAsync(human_label, e->buf.human_label, n, cudaMemcpyDeviceToHost, s));
     if (frame)
         AHK_CUDA(cudaMemcpyAsync(frame, e->buf.frames + static_cast<size_t>(e->head) * n * ahk::kFrameBytes,
                                  n * ahk::kFrameBytes, cudaMemcpyDeviceToHost, s));
-    AHK_CUDA(cudaStreamSynchronize(s));
+    const int ticket = static_cast<int>(e->host_ticket++ % ahk_env::kHostDepth);
+    AHK_CUDA(cudaEventRecord(e->host_ev[ticket], s));
+    return ticket;
+}
+
+int ahk_step_host_wait(ahk_env *e, int ticket)
+{
+    if (!e) return fail(AHK_ERR_ARG, "env is NULL");
+    if (ticket < 0 || ticket >= ahk_env::kHostDepth) return fail(AHK_ERR_ARG, "ticket %d out of range", ticket);
+    AHK_CUDA(cudaEventSynchronize(e->host_ev[ticket]));
     return AHK_OK;
+}
+
+int ahk_step_host(ahk_env *e, const uint8_t *robot, const uint8_t *human, float *reward, uint8_t *done,
+                  uint8_t *robot_label, uint8_t *human_label, uint8_t *frame)
+{
+    const int ticket = ahk_step_host_begin(e, robot, human, reward, done, robot_label, human_label, frame);
+    if (ticket < 0) return ticket;
+    return ahk_step_host_wait(e, ticket);
 }
 
 int ahk_observe(ahk_env *e, int format, void *out, void *stream)

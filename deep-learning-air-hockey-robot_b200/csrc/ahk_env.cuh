@@ -132,6 +132,10 @@ __device__ __forceinline__ void env_update(const EnvArgs &a, int i, uint4 (&rec)
         a.robot_label[i] = static_cast<uint8_t>(d.robot_label);
         a.human_label[i] = static_cast<uint8_t>(d.human_label);
         a.info[i] = static_cast<uint8_t>(t.info);
+        if (a.h_reward) a.h_reward[i] = 0.5f * static_cast<float>(r2);
+        if (a.h_done) a.h_done[i] = static_cast<uint8_t>(terminal);
+        if (a.h_robot_label) a.h_robot_label[i] = static_cast<uint8_t>(d.robot_label);
+        if (a.h_human_label) a.h_human_label[i] = static_cast<uint8_t>(d.human_label);
         d.steps = 1;
         d.reward2 = r2;
         d.goals_top = (t.info >> 5) == kScoredTop;

@@ -23,6 +23,10 @@ struct EnvArgs {
     uint8_t *done, *robot_label, *human_label, *info;
     uint64_t *stats;
     const uint8_t *robot, *human;                          // step: action labels or nullptr
+    // ahk_step_host with pinned host buffers: zero-copy mirrors of reward/done/labels in mapped host memory, written by
+    // the kernel itself over PCIe next to the device copies (nullptr: none) — no copy engine on the e2e path
+    float *h_reward;
+    uint8_t *h_done, *h_robot_label, *h_human_label;
     const uint8_t *reset_mask, *episode_override, *use_override; // reset
     uint2 key;
     uint32_t env_id_base;

@@ -24,6 +24,7 @@
 
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -33,7 +34,6 @@ namespace policy {
 constexpr int kBM = 128;     // rows per tile = UMMA M
 constexpr int kBK = 64;      // K per pipeline stage = 8 core matrices of 8 bf16
 constexpr int kThreads = 128;
-constexpr int kABytes = kBM * kBK * 2; // 16 KB per stage
 
 // ---- geometry of the network (models.py:20-65)
 constexpr int kC1 = 41, kP1 = kC1 * kC1; // conv1 output side / pixels
@@ -44,7 +44,6 @@ constexpr int kAct1C = 8;                // conv1 channels 5 padded to 8 (one 16
 enum Layer { kConv1 = 0, kConv2, kConv3, kDense1, kDense2, kOut };
 
 template <int L> struct Traits;
-template <> struct Traits<kConv1> { static constexpr int N = 16, K = 576, NSplit = 1; };  // 5 real outputs
 template <> struct Traits<kConv2> { static constexpr int N = 32, K = 128, NSplit = 1; };  // K = 16 taps x 8 (5 real)
 template <> struct Traits<kConv3> { static constexpr int N = 64, K = 512, NSplit = 1; };  // K = 16 taps x 32
 template <> struct Traits<kDense1> { static constexpr int N = 256, K = 4096, NSplit = 2; }; // 512 outputs in two halves
@@ -152,23 +151,12 @@ __device__ __forceinline__ uint2 u8x4_to_bf16x4(uint32_t w)
     return make_uint2(pack_bf16(f0, f1), pack_bf16(f2, f3));
 }
 
-constexpr int kTileRows = 20;  // input rows one conv1 tile can touch: 5 output rows x stride 3 + (8 - 3)
-constexpr int kTilePitch = 136; // bf16 elements per staged row (128 + pad: keeps 8-element reads in range)
-constexpr int kConv1StageBytes = 9 * kTileRows * kTilePitch * 2;
-
+// A row of the GEMM as 16-byte K cores, gathered straight from the previous layer's activations (im2col on the fly):
+// r0 = element offset of the row's first input element, kc = K core index (8 elements each)
 template <int L>
-__device__ __forceinline__ uint4 gather(const Args &a, const uint8_t *tile, int row_ok, int r0, int r1, int r2, int kc)
+__device__ __forceinline__ uint4 gather(const Args &a, bool row_ok, int r0, int kc)
 {
-    // r0, r1, r2: per-row constants prepared by the caller (see kernel); kc: K core index (8 elements each)
     if (!row_ok) return make_uint4(0, 0, 0, 0);
-    if (L == kConv1) {
-        // kc = c * 8 + ky ; r0 = byte offset of tile[0][3 (Y - Y0)][3 X] ; chunk = 8 consecutive kx
-        const int off = r0 + ((kc >> 3) * kTileRows + (kc & 7)) * (kTilePitch * 2);
-        const uint32_t *w = reinterpret_cast<const uint32_t *>(tile + (off & ~3));
-        const uint32_t sh = (off & 2) * 8;
-        const uint32_t w0 = w[0], w1 = w[1], w2 = w[2], w3 = w[3], w4 = w[4];
-        return make_uint4(__funnelshift_r(w0, w1, sh), __funnelshift_r(w1, w2, sh), __funnelshift_r(w2, w3, sh), __funnelshift_r(w3, w4, sh));
-    }
     if (L == kConv2) { // kc = tap ; r0 = element offset of act1[s][2Y*41 + 2X][0]
         const int ky = kc >> 2, kx = kc & 3;
         return __ldg(reinterpret_cast<const uint4 *>(a.in + r0 + (ky * kC1 + kx) * kAct1C));
@@ -182,6 +170,14 @@ __device__ __forceinline__ uint4 gather(const Args &a, const uint8_t *tile, int 
 }
 
 // ------------------------------------------------------------------------------------------------ the GEMM tile kernel
+// conv2, conv3 and the dense layers.  Persistent over 128-row tiles (barriers, TMEM and bias set up once per CTA).
+// Gather mapping: one warp instruction fetches 8 rows x 4 consecutive K cores (64 contiguous bytes per row; conv2: four
+// adjacent pixels of one kernel row) — 8 lines per load instead of the 32 of a row-per-thread mapping — and stores them
+// to 8 distinct rows-within-core-matrix, i.e. across all banks, with the core matrices still 128-byte aligned
+// (an odd K-core pitch that de-conflicted a row-per-8-lanes mapping made the MMA's own A reads straddle lines: slower).
+constexpr int kALbo = 16 * 128;       // bytes between K cores of the A stage (= LBO of its descriptor)
+constexpr int kAStage = 8 * kALbo;
+
 template <int L>
 __global__ void __launch_bounds__(kThreads) layer_kernel(Args a)
 {
@@ -191,19 +187,14 @@ __global__ void __launch_bounds__(kThreads) layer_kernel(Args a)
     constexpr uint32_t kTmemCols = N < 32 ? 32 : N;
 
     extern __shared__ __align__(128) uint8_t smem[];
-    uint8_t *s_a = smem;                      // [2][16 KB]
-    uint8_t *s_b = smem + 2 * kABytes;        // [2][kBBytes]
-    uint8_t *s_tile = s_b + 2 * kBBytes;      // conv1 only: bf16 [9][20][136]
+    uint8_t *s_a = smem;                      // [2][kAStage]
+    uint8_t *s_b = smem + 2 * kAStage;        // [2][kBBytes]
     __shared__ __align__(8) uint64_t s_full[2], s_free[2], s_done;
     __shared__ uint32_t s_tmem;
     __shared__ float s_bias[N];
 
     const int tid = threadIdx.x, warp = tid >> 5;
-    const int split = L == kConv1 ? 0 : blockIdx.y;         // which N half (dense layers)
-    const int sample = L == kConv1 ? blockIdx.x : 0;        // conv1: grid = (sample, tile of the 41x41 output)
-    const int tile_idx = L == kConv1 ? blockIdx.y : blockIdx.x;
-    const int row = tile_idx * kBM + tid;                   // row of the (flattened) GEMM this thread owns
-    const bool row_ok = row < a.m_total;
+    const int split = blockIdx.y;             // which N half (dense layers)
 
     if (tid == 0) {
         mbar_init(&s_full[0], 1); mbar_init(&s_full[1], 1);
@@ -214,48 +205,6 @@ __global__ void __launch_bounds__(kThreads) layer_kernel(Args a)
     if (tid < N) s_bias[tid] = a.bias[split * N + tid];
     if (N > kThreads) for (int i = tid + kThreads; i < N; i += kThreads) s_bias[i] = a.bias[split * N + i];
     if (warp == 0) tmem_alloc(&s_tmem, kTmemCols);
-
-    // ---- per-row constants of the gather
-    int r0 = 0;
-    if (L == kConv1) {
-        const int p0 = tile_idx * kBM, y0 = p0 / kC1;
-        const int y_last = min(kC1 - 1, (p0 + kBM - 1) / kC1);
-        const int rows = 3 * (y_last - y0) + 8; // input rows 3*y0 .. 3*y_last + 7
-        // stage the needed input rows of the 9 planes as bf16: plane c = (age c/3, colour c%3), newest frame first
-        for (int v = tid; v < 9 * kTileRows * 8; v += kThreads) { // one 16-pixel vector per trip
-            const int c = v / (kTileRows * 8), rem = v - c * (kTileRows * 8), rr = rem >> 3, xv = rem & 7;
-            uint4 px = make_uint4(0, 0, 0, 0);
-            if (rr < rows) {
-                const int slot = (a.head + 3 - c / 3) % 3;
-                const uint8_t *src = a.frames + ((static_cast<size_t>(slot) * a.n + sample) * 3 + (c % 3)) * (kDim * kDim) +
-                                     (3 * y0 + rr) * kDim + xv * 16;
-                px = __ldg(reinterpret_cast<const uint4 *>(src));
-            }
-            const uint2 q0 = u8x4_to_bf16x4(px.x), q1 = u8x4_to_bf16x4(px.y), q2 = u8x4_to_bf16x4(px.z), q3 = u8x4_to_bf16x4(px.w);
-            uint4 *dst = reinterpret_cast<uint4 *>(s_tile + ((c * kTileRows + rr) * kTilePitch + xv * 16) * 2);
-            dst[0] = make_uint4(q0.x, q0.y, q1.x, q1.y);
-            dst[1] = make_uint4(q2.x, q2.y, q3.x, q3.y);
-        }
-        for (int v = tid; v < 9 * kTileRows; v += kThreads) // zero the 8-element pad of each row
-            *reinterpret_cast<uint4 *>(s_tile + (v * kTilePitch + 128) * 2) = make_uint4(0, 0, 0, 0);
-        if (row_ok) {
-            const int y = row / kC1, x = row - y * kC1;
-            r0 = ((3 * (y - y0)) * kTilePitch + 3 * x) * 2;
-        }
-    } else if (L == kConv2) {
-        if (row_ok) {
-            const int s = row / kP2, p = row - s * kP2, y = p / kC2, x = p - y * kC2;
-            r0 = (s * kP1 + 2 * y * kC1 + 2 * x) * kAct1C;
-        }
-    } else if (L == kConv3) {
-        if (row_ok) {
-            const int s = row / kP3, p = row - s * kP3, y = p / kC3, x = p - y * kC3;
-            r0 = (s * kP2 + 2 * y * kC2 + 2 * x) * 32;
-        }
-    } else {
-        r0 = row * T::K;
-    }
-
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -263,94 +212,324 @@ __global__ void __launch_bounds__(kThreads) layer_kernel(Args a)
 
     const uint4 *wsrc = a.weights + static_cast<size_t>(split) * NCH * (kBBytes / 16);
     constexpr uint32_t kIdesc = instr_desc(N);
+    const int n_tiles = (a.m_total + kBM - 1) / kBM;
+    // gather: this thread's K core of every chunk, and its 8 rows (i = 0..7): row group 2 i + (warp >> 1), row tid & 7
+    const int kc_lane = (warp & 1) * 4 + ((tid & 31) >> 3), g = (warp >> 1) * 8 + (tid & 7);
+    uint32_t chg = 0, it = 0;                  // chunks / tiles processed so far by this CTA (barrier phases)
 
 #pragma unroll 1
-    for (int ch = 0; ch < NCH; ++ch) {
-        const int st = ch & 1, use = ch >> 1;
-        if (ch >= 2) mbar_wait(&s_free[st], (use - 1) & 1); // the MMAs that read this stage have retired
-        if (tid == 0) {
-            mbar_expect_tx(&s_full[st], kBBytes);
-            bulk_load(s_b + st * kBBytes, wsrc + static_cast<size_t>(ch) * (kBBytes / 16), kBBytes, &s_full[st]);
-        }
-        // A: this thread's row, 8 K cores of 16 bytes each -> canonical layout [K core][row group][row % 8]
-        uint8_t *dst = s_a + st * kABytes + (tid >> 3) * 128 + (tid & 7) * 16;
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+        int r0[8];
+        unsigned ok = 0u;
 #pragma unroll
-        for (int kc = 0; kc < 8; ++kc)
-            *reinterpret_cast<uint4 *>(dst + kc * (16 * 128)) = gather<L>(a, s_tile, row_ok, r0, 0, 0, ch * 8 + kc);
-        fence_async_smem();
-        __syncthreads();
-        if (tid == 0) {
-            mbar_wait(&s_full[st], use & 1);
-            tc_fence_after();
-            const uint32_t a_base = smem_u32(s_a + st * kABytes), b_base = smem_u32(s_b + st * kBBytes);
-#pragma unroll
-            for (int j = 0; j < kBK / 16; ++j) {
-                const uint64_t ad = smem_desc(a_base + j * 2 * (16 * 128), 16 * 128, 128);
-                const uint64_t bd = smem_desc(b_base + j * 2 * (N / 8 * 128), N / 8 * 128, 128);
-                umma_bf16(tmem, ad, bd, kIdesc, (ch | j) != 0);
+        for (int i = 0; i < 8; ++i) {
+            const int row = tile * kBM + i * 16 + g;
+            r0[i] = 0;
+            if (row < a.m_total) {
+                ok |= 1u << i;
+                if (L == kConv2) {
+                    const int s = row / kP2, p = row - s * kP2, y = p / kC2, x = p - y * kC2;
+                    r0[i] = (s * kP1 + 2 * y * kC1 + 2 * x) * kAct1C;
+                } else if (L == kConv3) {
+                    const int s = row / kP3, p = row - s * kP3, y = p / kC3, x = p - y * kC3;
+                    r0[i] = (s * kP2 + 2 * y * kC2 + 2 * x) * 32;
+                } else {
+                    r0[i] = row * T::K;
+                }
             }
-            umma_commit(&s_free[st]);
-            if (ch == NCH - 1) umma_commit(&s_done);
         }
-    }
-    mbar_wait(&s_done, 0);
-    tc_fence_after();
+#pragma unroll 1
+        for (int ch = 0; ch < NCH; ++ch, ++chg) {
+            const uint32_t st = chg & 1u, use = chg >> 1;
+            if (chg >= 2u) mbar_wait(&s_free[st], (use - 1u) & 1u); // the MMAs that read this stage have retired
+            if (tid == 0) {
+                mbar_expect_tx(&s_full[st], kBBytes);
+                bulk_load(s_b + st * kBBytes, wsrc + static_cast<size_t>(ch) * (kBBytes / 16), kBBytes, &s_full[st]);
+            }
+            uint4 v[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[i] = gather<L>(a, (ok >> i) & 1u, r0[i], ch * 8 + kc_lane);
+            // canonical layout [K core][row group][row % 8]: row i*16 + g sits at g*16 + i*256 inside its K core
+            uint8_t *dst = s_a + st * kAStage + kc_lane * kALbo + g * 16;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) *reinterpret_cast<uint4 *>(dst + i * 256) = v[i];
+            fence_async_smem();
+            __syncthreads();
+            if (tid == 0) {
+                mbar_wait(&s_full[st], use & 1u);
+                tc_fence_after();
+                const uint32_t a_base = smem_u32(s_a + st * kAStage), b_base = smem_u32(s_b + st * kBBytes);
+#pragma unroll
+                for (int j = 0; j < kBK / 16; ++j) {
+                    const uint64_t ad = smem_desc(a_base + j * 2 * kALbo, kALbo, 128);
+                    const uint64_t bd = smem_desc(b_base + j * 2 * (N / 8 * 128), N / 8 * 128, 128);
+                    umma_bf16(tmem, ad, bd, kIdesc, (ch | j) != 0);
+                }
+                umma_commit(&s_free[st]);
+                if (ch == NCH - 1) umma_commit(&s_done);
+            }
+        }
+        mbar_wait(&s_done, it & 1u);
+        tc_fence_after();
 
-    // ---- epilogue: thread = TMEM lane = tile row
-    const uint32_t lane_addr = tmem + (static_cast<uint32_t>(warp * 32) << 16);
-    if (L == kOut) {
-        float v[16];
-        tmem_load16(lane_addr, v);
-        if (row_ok) {
-            int best = 0;
-            float best_v = v[0] + s_bias[0];
+        // ---- epilogue: thread = TMEM lane = tile row
+        const int row = tile * kBM + tid;
+        const bool row_ok = row < a.m_total;
+        const uint32_t lane_addr = tmem + (static_cast<uint32_t>(warp * 32) << 16);
+        if (L == kOut) {
+            float v[16];
+            tmem_load16(lane_addr, v);
+            if (row_ok) {
+                int best = 0;
+                float best_v = v[0] + s_bias[0];
 #pragma unroll
-            for (int j = 0; j < AHK_N_ACTIONS; ++j) {
-                const float q = v[j] + s_bias[j];
-                if (a.logits) a.logits[static_cast<size_t>(row) * AHK_N_ACTIONS + j] = q;
-                if (q > best_v) { best_v = q; best = j; }
+                for (int j = 0; j < AHK_N_ACTIONS; ++j) {
+                    const float q = v[j] + s_bias[j];
+                    if (a.logits) a.logits[static_cast<size_t>(row) * AHK_N_ACTIONS + j] = q;
+                    if (q > best_v) { best_v = q; best = j; }
+                }
+                if (a.action) a.action[row] = static_cast<uint8_t>(best);
             }
-            if (a.action) a.action[row] = static_cast<uint8_t>(best);
+        } else {
+            constexpr int kOutPitch = T::NSplit * N; // elements per output row
+            __nv_bfloat16 *out = a.out + static_cast<size_t>(row) * kOutPitch + split * N;
+#pragma unroll 1
+            for (int c0 = 0; c0 < N; c0 += 16) {
+                float v[16];
+                tmem_load16(lane_addr + c0, v);
+                uint32_t packed[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const float lo = fmaxf(v[2 * j] + s_bias[c0 + 2 * j], 0.0f), hi = fmaxf(v[2 * j + 1] + s_bias[c0 + 2 * j + 1], 0.0f);
+                    const __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+                    packed[j] = *reinterpret_cast<const uint32_t *>(&h);
+                }
+                if (row_ok) {
+                    *reinterpret_cast<uint4 *>(out + c0) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+                    *reinterpret_cast<uint4 *>(out + c0 + 8) = make_uint4(packed[4], packed[5], packed[6], packed[7]);
+                }
+            }
+        }
+        tc_fence_before();
+        __syncthreads(); // every lane of the accumulator has been read: the next tile's first MMA may overwrite it
+        tc_fence_after();
+    }
+    if (warp == 0) tmem_dealloc(tmem, kTmemCols);
+}
+
+template <int L> constexpr int smem_bytes() { return 2 * kAStage + 2 * Traits<L>::N * kBK * 2; }
+
+// grid.x = min(tiles, resident CTAs on the device): the kernel loops over its tiles
+template <int L>
+cudaError_t launch(const Args &a, int tiles, int grid_y, int sms, cudaStream_t s)
+{
+    static int per_sm = 0;
+    if (per_sm == 0) {
+        cudaError_t e = cudaFuncSetAttribute(layer_kernel<L>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<L>());
+        if (e != cudaSuccess) return e;
+        // resident CTAs per SM: shared memory (227 KB, + 1 KB reserved and ~1.3 KB static per CTA), tensor memory (512 columns)
+        constexpr int tmem_cols = Traits<L>::N < 32 ? 32 : Traits<L>::N;
+        per_sm = (227 * 1024) / (smem_bytes<L>() + 3 * 1024);
+        if (per_sm > 512 / tmem_cols) per_sm = 512 / tmem_cols;
+        if (per_sm > 8) per_sm = 8;
+        if (per_sm < 1) per_sm = 1;
+    }
+    const int resident = sms * per_sm / grid_y;
+    layer_kernel<L><<<dim3(tiles < resident ? tiles : (resident > 0 ? resident : 1), grid_y), kThreads, smem_bytes<L>(), s>>>(a);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------ conv1, Toeplitz form
+// conv1 (9 -> 5 channels, 8x8, stride 3: models.py:22-24) is 47 % of the network's MACs and hostile to an im2col GEMM:
+// N = 5, and every output pixel's 576-element A row would be built in shared memory by the CUDA cores (1.9 MB of
+// shared-memory writes per sample; the first version of this file did that and spent 6.2 ms per 8192 samples in it).
+// Here the A operand is the IMAGE ITSELF, bf16, never expanded:
+//   * M row m = (output row y, 8-pixel block xb of an input row); the K = 16 window of one MMA is the 16 consecutive
+//     pixels 8 xb .. 8 xb + 15 of input row 3 y + ky of plane c — in the canonical no-swizzle K-major layout that is
+//     simply the raw row (one core-matrix row = 8 pixels = 16 bytes, next M row = next 16 bytes) with LBO = 16 bytes:
+//     the second K core matrix of row m IS the first of row m + 1.
+//   * Output pixels whose 8-wide window lies inside that 16-pixel window: x = 8q + 3 ph + j with xb = 3q + ph, j < 3,
+//     at offset ph + 3j.  The stride-3 phase differs per row, one MMA applies one B to all rows, so B carries all three:
+//     N = 48 = 3 phases x (3 outputs x 5 channels, padded to 16), a banded (Toeplitz) copy of the 8-tap kernel row;
+//     the epilogue keeps the 16 columns of its row's phase.  Tensor work is 3.6x the useful MACs, and irrelevant: the
+//     MMAs are bound by streaming A from shared memory (4 KB each), 72 per 8 output rows instead of ~250 KB of im2col.
+//   * Input rows are stored by residue (row mod 3) so that (y, half row) -> address is linear (SBO = 128) for every ky.
+// Persistent, warp-specialised CTA (one per SM): 8 producer warps convert uint8 ring rows to bf16 slabs (one frame of
+// the 3-deep stack = 3 colour planes x 30 rows per stage, 4 stages), 1 warp issues the MMAs (24 per slab, 72 per tile),
+// 4 warps run the epilogue out of a double-buffered TMEM accumulator (bias, ReLU, bf16, [pixel][8] layout for conv2).
+namespace c1 {
+constexpr int kProducers = 256, kCta = kProducers + 32 + 128;
+constexpr int kStages = 4;
+constexpr int kYTile = 8, kTilesPerSample = 6;           // 41 output rows in tiles of 8
+constexpr int kRows = 30, kClassRows = 10;               // input rows per slab plane; rows per residue class
+constexpr int kRowBytes = kDim * 2, kClassBytes = kClassRows * kRowBytes, kPlaneBytes = 3 * kClassBytes, kSlabBytes = 3 * kPlaneBytes;
+constexpr int kSlabPitch = kSlabBytes + 256;             // + zeroed pad: the last row's K window spills 16 bytes
+constexpr int kN = 48;
+constexpr int kWBlock = 16 * kN * 2;                     // one (plane, ky) B operand: K = 16 x N = 48 bf16
+constexpr int kWBytes = 72 * kWBlock;                    // 110 592 B, resident in shared memory
+constexpr int kSmem = kWBytes + kStages * kSlabPitch;    // 203 776 B
+constexpr int kVecsPerSlab = 3 * kRows * 8;              // 16-pixel vectors per slab
+} // namespace c1
+
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) { asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(bar)) : "memory"); }
+
+__global__ void __launch_bounds__(c1::kCta, 1) conv1_kernel(Args a)
+{
+    using namespace c1;
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint8_t *s_w = smem;
+    uint8_t *s_slab = smem + kWBytes;
+    __shared__ __align__(8) uint64_t s_wfull, s_full[kStages], s_empty[kStages], s_tfull[2], s_tempty[2];
+    __shared__ uint32_t s_tmem;
+    __shared__ float s_bias[8];
+
+    const int tid = threadIdx.x, warp = tid >> 5;
+    const int items = a.n * kTilesPerSample;
+    if (tid == 0) {
+        mbar_init(&s_wfull, 1);
+        for (int i = 0; i < kStages; ++i) { mbar_init(&s_full[i], kProducers); mbar_init(&s_empty[i], 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&s_tfull[i], 1); mbar_init(&s_tempty[i], 128); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (tid < 8) s_bias[tid] = tid < 5 ? a.bias[tid] : 0.0f;
+    for (int i = tid; i < kStages * 16; i += kCta) // the pad behind each slab
+        *reinterpret_cast<uint4 *>(s_slab + (i >> 4) * kSlabPitch + kSlabBytes + (i & 15) * 16) = make_uint4(0, 0, 0, 0);
+    if (warp == kProducers / 32) tmem_alloc(&s_tmem, 128); // 2 accumulators x 64 columns (48 used)
+    fence_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = s_tmem;
+
+    if (tid < kProducers) {
+        // ---------------------------------------------------------------- producers: uint8 ring rows -> bf16 slabs
+        // per-thread constants: up to three 16-pixel vectors of every slab
+        int src_off[3], dst_off[3], lrow[3];
+#pragma unroll
+        for (int t = 0; t < 3; ++t) {
+            const int v = tid + t * kProducers;
+            const int colour = v / (kRows * 8), rem = v - colour * (kRows * 8), lr = rem >> 3, xv = rem & 7;
+            src_off[t] = (colour * kDim + lr) * kDim + xv * 16;
+            dst_off[t] = colour * kPlaneBytes + (lr % 3) * kClassBytes + (lr / 3) * kRowBytes + xv * 32;
+            lrow[t] = v < kVecsPerSlab ? lr : kDim; // kDim: never valid
+        }
+        const int my_items = blockIdx.x < items ? (items - 1 - blockIdx.x) / gridDim.x + 1 : 0;
+        const uint32_t slabs = 3u * my_items;
+        auto load = [&](uint32_t f, uint4 (&px)[3]) { // slab f of this CTA: item f / 3, stack age f % 3
+            const int item = blockIdx.x + static_cast<int>(f / 3u) * gridDim.x, age = static_cast<int>(f % 3u);
+            const int sample = item / kTilesPerSample, y0 = (item - sample * kTilesPerSample) * kYTile;
+            const uint8_t *src = a.frames + (static_cast<size_t>((a.head + 3 - age) % 3) * a.n + sample) * kFrameBytes + 3 * y0 * kDim;
+#pragma unroll
+            for (int t = 0; t < 3; ++t) {
+                px[t] = make_uint4(0, 0, 0, 0);
+                if (3 * y0 + lrow[t] < kDim) px[t] = __ldg(reinterpret_cast<const uint4 *>(src + src_off[t]));
+            }
+        };
+        uint4 cur[3], nxt[3];
+        if (slabs) load(0u, cur);
+        for (uint32_t f = 0; f < slabs; ++f) {
+            if (f + 1u < slabs) load(f + 1u, nxt); // in flight while this slab is converted: the loads never wait for a stage
+            const uint32_t st = f % kStages;
+            if (f >= kStages) mbar_wait(&s_empty[st], ((f / kStages) - 1u) & 1u);
+            uint8_t *slab = s_slab + st * kSlabPitch;
+#pragma unroll
+            for (int t = 0; t < 3; ++t) {
+                if (lrow[t] < kDim) {
+                    const uint2 q0 = u8x4_to_bf16x4(cur[t].x), q1 = u8x4_to_bf16x4(cur[t].y), q2 = u8x4_to_bf16x4(cur[t].z), q3 = u8x4_to_bf16x4(cur[t].w);
+                    uint4 *dst = reinterpret_cast<uint4 *>(slab + dst_off[t]);
+                    dst[0] = make_uint4(q0.x, q0.y, q1.x, q1.y);
+                    dst[1] = make_uint4(q2.x, q2.y, q3.x, q3.y);
+                }
+            }
+            fence_async_smem();
+            mbar_arrive(&s_full[st]);
+#pragma unroll
+            for (int t = 0; t < 3; ++t) cur[t] = nxt[t];
+        }
+    } else if (warp == kProducers / 32) {
+        // ---------------------------------------------------------------- MMA issue (one thread)
+        if ((tid & 31) == 0) {
+            mbar_expect_tx(&s_wfull, kWBytes);
+            for (int i = 0; i < 9; ++i) bulk_load(s_w + i * (kWBytes / 9), reinterpret_cast<const uint8_t *>(a.weights) + i * (kWBytes / 9), kWBytes / 9, &s_wfull);
+            mbar_wait(&s_wfull, 0);
+            constexpr uint32_t kIdesc = instr_desc(kN);
+            const uint32_t w_base = smem_u32(s_w);
+            uint32_t fill = 0, tile = 0;
+            for (int item = blockIdx.x; item < items; item += gridDim.x, ++tile) {
+                const uint32_t buf = tile & 1u;
+                if (tile >= 2) mbar_wait(&s_tempty[buf], ((tile >> 1) - 1) & 1);
+                tc_fence_after();
+                for (int age = 0; age < 3; ++age, ++fill) {
+                    const int st = fill % kStages;
+                    mbar_wait(&s_full[st], (fill / kStages) & 1);
+                    tc_fence_after();
+                    const uint32_t slab = smem_u32(s_slab + st * kSlabPitch);
+#pragma unroll
+                    for (int colour = 0; colour < 3; ++colour) {
+#pragma unroll
+                        for (int ky = 0; ky < 8; ++ky) {
+                            // rows 3 y + ky, y = 0..7: residue class ky % 3, from row index ky / 3 on; K step = 16 bytes
+                            const uint64_t ad = smem_desc(slab + colour * kPlaneBytes + (ky % 3) * kClassBytes + (ky / 3) * kRowBytes, 16, 128);
+                            const uint64_t bd = smem_desc(w_base + ((age * 3 + colour) * 8 + ky) * kWBlock, (kN / 8) * 128, 128);
+                            umma_bf16(tmem + buf * 64, ad, bd, kIdesc, (age | colour | ky) != 0);
+                        }
+                    }
+                    umma_commit(&s_empty[st]);
+                }
+                umma_commit(&s_tfull[buf]);
+            }
         }
     } else {
-        constexpr int kStore = L == kConv1 ? kAct1C : N;              // channels written per row
-        constexpr int kOutPitch = L == kConv1 ? kAct1C : (T::NSplit * N); // elements per output row
-        const size_t out_row = L == kConv1 ? static_cast<size_t>(sample) * kP1 + row : static_cast<size_t>(row);
-        __nv_bfloat16 *out = a.out + out_row * kOutPitch + split * N;
-#pragma unroll 1
-        for (int c0 = 0; c0 < kStore; c0 += 16) {
-            float v[16];
-            tmem_load16(lane_addr + c0, v);
-            uint32_t packed[8];
+        // ---------------------------------------------------------------- epilogue: 4 warps, thread = TMEM lane = M row
+        const int q4 = warp & 3;                 // the TMEM lane quarter this warp may read
+        const int m = q4 * 32 + (tid & 31);
+        const int yl = m >> 4, xb = m & 15, ph = xb % 3, xq = xb / 3;
+        uint32_t tile = 0;
+        for (int item = blockIdx.x; item < items; item += gridDim.x, ++tile) {
+            const int sample = item / kTilesPerSample, y = (item - sample * kTilesPerSample) * kYTile + yl;
+            const uint32_t buf = tile & 1u;
+            mbar_wait(&s_tfull[buf], (tile >> 1) & 1);
+            tc_fence_after();
+            const uint32_t taddr = tmem + buf * 64 + (static_cast<uint32_t>(q4 * 32) << 16);
+            float v0[16], v1[16], v2[16];
+            tmem_load16(taddr, v0);
+            tmem_load16(taddr + 16, v1);
+            tmem_load16(taddr + 32, v2);
+            tc_fence_before();
+            mbar_arrive(&s_tempty[buf]); // the accumulator is in registers: the MMA warp may overwrite it
+            if (y < kC1) {
+                const int x0 = 8 * xq + 3 * ph;
+                uint4 *out = reinterpret_cast<uint4 *>(a.out + (static_cast<size_t>(sample) * kP1 + y * kC1 + x0) * kAct1C);
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const float lo = fmaxf(v[2 * j] + s_bias[c0 + 2 * j], 0.0f), hi = fmaxf(v[2 * j + 1] + s_bias[c0 + 2 * j + 1], 0.0f);
-                const __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
-                packed[j] = *reinterpret_cast<const uint32_t *>(&h);
-            }
-            if (row_ok) {
-                *reinterpret_cast<uint4 *>(out + c0) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
-                if (kStore - c0 > 8) *reinterpret_cast<uint4 *>(out + c0 + 8) = make_uint4(packed[4], packed[5], packed[6], packed[7]);
+                for (int j = 0; j < 3; ++j) {
+                    float c[5];
+#pragma unroll
+                    for (int ch = 0; ch < 5; ++ch) {
+                        const float d = ph == 0 ? v0[j * 5 + ch] : (ph == 1 ? v1[j * 5 + ch] : v2[j * 5 + ch]);
+                        c[ch] = fmaxf(d + s_bias[ch], 0.0f);
+                    }
+                    if ((j < 2 || ph < 2) && x0 + j < kC1) {
+                        const __nv_bfloat162 p01 = __floats2bfloat162_rn(c[0], c[1]), p23 = __floats2bfloat162_rn(c[2], c[3]), p4 = __floats2bfloat162_rn(c[4], 0.0f);
+                        out[j] = make_uint4(*reinterpret_cast<const uint32_t *>(&p01), *reinterpret_cast<const uint32_t *>(&p23), *reinterpret_cast<const uint32_t *>(&p4), 0u);
+                    }
+                }
             }
         }
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 0) tmem_dealloc(tmem, kTmemCols);
+    if (warp == kProducers / 32) tmem_dealloc(tmem, 128);
 }
 
-template <int L> constexpr int smem_bytes() { return 2 * kABytes + 2 * Traits<L>::N * kBK * 2 + (L == kConv1 ? kConv1StageBytes : 0); }
-
-template <int L>
-cudaError_t launch(const Args &a, int tiles, int grid_y, cudaStream_t s)
+cudaError_t launch_conv1(const Args &a, int grid, cudaStream_t s)
 {
     static bool prepared = false;
     if (!prepared) {
-        cudaError_t e = cudaFuncSetAttribute(layer_kernel<L>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<L>());
+        cudaError_t e = cudaFuncSetAttribute(conv1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, c1::kSmem);
         if (e != cudaSuccess) return e;
         prepared = true;
     }
-    layer_kernel<L><<<dim3(tiles, grid_y), kThreads, smem_bytes<L>(), s>>>(a);
+    conv1_kernel<<<grid, c1::kCta, c1::kSmem, s>>>(a);
     return cudaGetLastError();
 }
 
@@ -382,6 +561,26 @@ std::vector<uint16_t> pack_b(const std::vector<float> &w, int k_total, int n_rea
     return out;
 }
 
+
+// conv1, Toeplitz form: W [576][5] folded (k = plane*64 + ky*8 + kx) -> 72 blocks (plane, ky) of the K-major canonical
+// B operand [K = 16][N = 48]: element (n, k) at (k/8) * 768 + (n/8) * 128 + (n%8) * 16 + (k%8) * 2 bytes;
+// n = phase*16 + j*5 + channel holds W[plane][ky][kx = k - (phase + 3j)][channel] (0 outside the 8 taps).
+std::vector<uint16_t> pack_conv1_toeplitz(const std::vector<float> &wf)
+{
+    std::vector<uint16_t> out(static_cast<size_t>(72) * 16 * 48, 0);
+    for (int blk = 0; blk < 72; ++blk)
+        for (int ph = 0; ph < 3; ++ph)
+            for (int j = 0; j < 3; ++j)
+                for (int ch = 0; ch < 5; ++ch)
+                    for (int kx = 0; kx < 8; ++kx) {
+                        const int k = kx + ph + 3 * j, n = ph * 16 + j * 5 + ch;
+                        if (k >= 16) continue; // phase 2, third output: belongs to the next block's first
+                        const size_t at = static_cast<size_t>(blk) * 768 + (k / 8) * 384 + (n / 8) * 64 + (n % 8) * 8 + (k % 8);
+                        out[at] = to_bf16(wf[(static_cast<size_t>(blk) * 8 + kx) * 5 + ch]);
+                    }
+    return out;
+}
+
 } // namespace policy
 } // namespace ahk
 
@@ -392,6 +591,9 @@ struct ahk_policy {
     int device = 0, max_batch = 0;
     uint16_t *w[6] = {};
     float *b[6] = {};
+    uint16_t *w1t = nullptr; // conv1 in Toeplitz form (conv1_kernel)
+    cudaEvent_t ev[7] = {};  // ahk_policy_forward_profiled: around each of the six layer kernels
+    int sms = 148;
     __nv_bfloat16 *act1 = nullptr, *act2 = nullptr, *act3 = nullptr, *h1 = nullptr, *h2 = nullptr;
     uint64_t launches = 0;
 };
@@ -451,6 +653,7 @@ int ahk_policy_create(int device, int max_batch, const ahk_policy_weights *w, ah
     ahk_policy *p = new ahk_policy();
     p->device = device;
     p->max_batch = max_batch;
+    cudaDeviceGetAttribute(&p->sms, cudaDevAttrMultiProcessorCount, device);
     int rc = AHK_OK;
 
     { // conv1: Keras kernel [ky][kx][c][o]; GEMM k = c*64 + ky*8 + kx; (x-128)/128 folded: W/128, b - sum(W)
@@ -464,7 +667,7 @@ int ahk_policy_create(int device, int max_batch, const ahk_policy_weights *w, ah
             }
             bf[o] = w->conv1_b[o] - static_cast<float>(sum);
         }
-        rc = upload(pack_b(wf, 576, 5, 16, 1), bf, &p->w[0], &p->b[0]);
+        rc = upload(pack_conv1_toeplitz(wf), bf, &p->w1t, &p->b[0]);
     }
     if (rc == AHK_OK) { // conv2: k = (ky*4+kx)*8 + c, BN1 folded
         std::vector<float> wf(128 * 32, 0.0f), bf(32);
@@ -514,6 +717,7 @@ int ahk_policy_create(int device, int max_batch, const ahk_policy_weights *w, ah
     }
     const size_t nb = static_cast<size_t>(max_batch);
     cudaError_t err = cudaSuccess;
+    for (int i = 0; i < 7 && err == cudaSuccess; ++i) err = cudaEventCreate(&p->ev[i]);
     if (rc == AHK_OK) {
         err = cudaMalloc(&p->act1, nb * kP1 * kAct1C * 2);
         if (err == cudaSuccess) err = cudaMalloc(&p->act2, nb * kP2 * 32 * 2);
@@ -534,11 +738,13 @@ void ahk_policy_destroy(ahk_policy *p)
     if (!p) return;
     cudaSetDevice(p->device);
     for (int i = 0; i < 6; ++i) { if (p->w[i]) cudaFree(p->w[i]); if (p->b[i]) cudaFree(p->b[i]); }
+    if (p->w1t) cudaFree(p->w1t);
+    for (int i = 0; i < 7; ++i) if (p->ev[i]) cudaEventDestroy(p->ev[i]);
     cudaFree(p->act1); cudaFree(p->act2); cudaFree(p->act3); cudaFree(p->h1); cudaFree(p->h2);
     delete p;
 }
 
-int ahk_policy_forward(ahk_policy *p, const uint8_t *frames, int n, int head, float *logits, uint8_t *action, void *stream)
+static int policy_forward(ahk_policy *p, const uint8_t *frames, int n, int head, float *logits, uint8_t *action, void *stream, bool timed)
 {
     if (!p || !frames) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_forward: policy/frames is NULL");
     if (n <= 0 || n > p->max_batch) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_forward: n must be in [1, max_batch]");
@@ -548,20 +754,45 @@ int ahk_policy_forward(ahk_policy *p, const uint8_t *frames, int n, int head, fl
     Args a{};
     a.n = n;
     a.head = head;
+    if (timed) POL_CUDA(cudaEventRecord(p->ev[0], s));
 
-    a.frames = frames; a.weights = reinterpret_cast<const uint4 *>(p->w[0]); a.bias = p->b[0]; a.out = p->act1; a.m_total = kP1;
-    POL_CUDA(launch<kConv1>(a, n, tiles(kP1), s));
+    a.frames = frames; a.weights = reinterpret_cast<const uint4 *>(p->w1t); a.bias = p->b[0]; a.out = p->act1; a.m_total = kP1;
+    {
+        const int items = n * c1::kTilesPerSample;
+        POL_CUDA(launch_conv1(a, items < p->sms ? items : p->sms, s));
+    }
+    if (timed) POL_CUDA(cudaEventRecord(p->ev[1], s));
     a.in = p->act1; a.weights = reinterpret_cast<const uint4 *>(p->w[1]); a.bias = p->b[1]; a.out = p->act2; a.m_total = n * kP2;
-    POL_CUDA(launch<kConv2>(a, tiles(static_cast<long long>(n) * kP2), 1, s));
+    POL_CUDA(launch<kConv2>(a, tiles(static_cast<long long>(n) * kP2), 1, p->sms, s));
+    if (timed) POL_CUDA(cudaEventRecord(p->ev[2], s));
     a.in = p->act2; a.weights = reinterpret_cast<const uint4 *>(p->w[2]); a.bias = p->b[2]; a.out = p->act3; a.m_total = n * kP3;
-    POL_CUDA(launch<kConv3>(a, tiles(static_cast<long long>(n) * kP3), 1, s));
+    POL_CUDA(launch<kConv3>(a, tiles(static_cast<long long>(n) * kP3), 1, p->sms, s));
+    if (timed) POL_CUDA(cudaEventRecord(p->ev[3], s));
     a.in = p->act3; a.weights = reinterpret_cast<const uint4 *>(p->w[3]); a.bias = p->b[3]; a.out = p->h1; a.m_total = n;
-    POL_CUDA(launch<kDense1>(a, tiles(n), 2, s));
+    POL_CUDA(launch<kDense1>(a, tiles(n), 2, p->sms, s));
+    if (timed) POL_CUDA(cudaEventRecord(p->ev[4], s));
     a.in = p->h1; a.weights = reinterpret_cast<const uint4 *>(p->w[4]); a.bias = p->b[4]; a.out = p->h2; a.m_total = n;
-    POL_CUDA(launch<kDense2>(a, tiles(n), 2, s));
+    POL_CUDA(launch<kDense2>(a, tiles(n), 2, p->sms, s));
+    if (timed) POL_CUDA(cudaEventRecord(p->ev[5], s));
     a.in = p->h2; a.weights = reinterpret_cast<const uint4 *>(p->w[5]); a.bias = p->b[5]; a.out = nullptr; a.logits = logits; a.action = action; a.m_total = n;
-    POL_CUDA(launch<kOut>(a, tiles(n), 1, s));
+    POL_CUDA(launch<kOut>(a, tiles(n), 1, p->sms, s));
+    if (timed) POL_CUDA(cudaEventRecord(p->ev[6], s));
     p->launches += 6;
+    return AHK_OK;
+}
+
+int ahk_policy_forward(ahk_policy *p, const uint8_t *frames, int n, int head, float *logits, uint8_t *action, void *stream)
+{
+    return policy_forward(p, frames, n, head, logits, action, stream, false);
+}
+
+int ahk_policy_forward_profiled(ahk_policy *p, const uint8_t *frames, int n, int head, float *logits, uint8_t *action,
+                                void *stream, float *layer_ms)
+{
+    if (!layer_ms) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_forward_profiled: layer_ms is NULL");
+    if (int rc = policy_forward(p, frames, n, head, logits, action, stream, true)) return rc;
+    POL_CUDA(cudaEventSynchronize(p->ev[6]));
+    for (int i = 0; i < 6; ++i) POL_CUDA(cudaEventElapsedTime(layer_ms + i, p->ev[i], p->ev[i + 1]));
     return AHK_OK;
 }
 

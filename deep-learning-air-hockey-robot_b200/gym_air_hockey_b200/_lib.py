@@ -44,6 +44,8 @@ SYMBOLS = {
     "ahk_step": (_i, [_vp, _vp, _vp, _vp]),
     "ahk_step_profiled": (_i, [_vp, _vp, _vp, _vp, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
     "ahk_step_host": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "ahk_step_host_begin": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "ahk_step_host_wait": (_i, [_vp, _i]),
     "ahk_observe": (_i, [_vp, _i, _vp, _vp]),
     "ahk_head": (_i, [_vp]),
     "ahk_set_head": (_i, [_vp, _i]),
@@ -57,6 +59,7 @@ SYMBOLS = {
     "ahk_policy_create": (_i, [_i, _i, C.POINTER(PolicyWeights), C.POINTER(_vp)]),
     "ahk_policy_destroy": (None, [_vp]),
     "ahk_policy_forward": (_i, [_vp, _vp, _i, _i, _vp, _vp, _vp]),
+    "ahk_policy_forward_profiled": (_i, [_vp, _vp, _i, _i, _vp, _vp, _vp, C.POINTER(C.c_float)]),
 }
 
 _lib = None

@@ -1,0 +1,193 @@
+"""Supervised dataset generation: the reference's `ai/supervised/generate_data.py:35-73` loop run
+over N environments at once, written in the reference's dataset layout (`ai/supervised/utils/data_utils.py:3-13`):
+three arrays `states`, `robot_actions`, `human_actions`.
+
+Reference: one env, `env.step()` with no actions (the programmed AI plays both sides, `generate_data.py:51`), reset on
+a goal or every 200 steps (`:57-58`), states as float32 (n, 9, 128, 128) normalised `(x-128)/128`, labels int8, one
+HDF5 file `<time>_<mode>_<n>.h5` (`:68-73`).  Here: the batched engine with `auto_reset` and `max_episode_steps=200`
+plays the same protocol per env; every step the stacked observation of all envs is materialised on the GPU
+(`ahk_observe`), copied to one of two pinned host buffers on a side stream while the next step runs, and appended to
+the output by a writer thread.  `h5py` is not installed in this image, so the container is chosen at run time: HDF5
+through h5py when it imports, else `.npz` shards holding the same three arrays (`load_data` reads either).
+
+Sample order is step-major: sample `t * n_envs + e` is env `e` after step `t`.  `states='u8'` keeps the uint8 stack
+(4x smaller; `load_data(..., normalise=True)` applies `(x-128)/128` on load) — the float32 form costs 589 824 B per
+sample of PCIe and disk, which is what bounds this path, not the GPU.
+"""
+import datetime
+import glob
+import os
+import queue
+import threading
+import time
+
+import numpy as np
+import torch
+
+try:  # pragma: no cover - not in this image
+    import h5py
+except ImportError:
+    h5py = None
+
+
+def data_file_name(mode, n_states, when=None, ext=None):
+    """`<YYYY-mm-dd-HH-MM-SS>_<mode>_<n>.h5` (generate_data.py:62-63,72); `.npz` shards when h5py is absent."""
+    when = int(time.time()) if when is None else when
+    stamp = datetime.datetime.fromtimestamp(when).strftime('%Y-%m-%d-%H-%M-%S')
+    return '%s_%s_%d.%s' % (stamp, mode, n_states, ext or ('h5' if h5py else 'npz'))
+
+
+def save_data(data_file, states, robot_actions, human_actions):
+    """≙ data_utils.save_data (data_utils.py:3-7)."""
+    if data_file.endswith('.h5'):
+        if h5py is None:
+            raise RuntimeError('h5py is not installed: write .npz shards instead')
+        with h5py.File(data_file, 'w') as f:
+            f.create_dataset('states', data=states)
+            f.create_dataset('robot_actions', data=robot_actions)
+            f.create_dataset('human_actions', data=human_actions)
+    else:
+        with open(data_file, 'wb') as f:
+            np.savez(f, states=states, robot_actions=robot_actions, human_actions=human_actions)
+
+
+def load_data(data_file, normalise=False):
+    """≙ data_utils.load_data (data_utils.py:9-13).  `data_file` may be one file or a glob of shards (concatenated in
+    name order).  normalise=True turns uint8 states into the reference's float32 `(x-128)/128` (processor.py:39-42)."""
+    files = sorted(glob.glob(data_file)) or [data_file]
+    parts = []
+    for name in files:
+        if name.endswith('.h5'):
+            if h5py is None:
+                raise RuntimeError('h5py is not installed')
+            with h5py.File(name, 'r') as f:
+                parts.append((f['states'][:], f['robot_actions'][:], f['human_actions'][:]))
+        else:
+            with np.load(name) as f:
+                parts.append((f['states'], f['robot_actions'], f['human_actions']))
+    states, robot, human = (np.concatenate([p[k] for p in parts]) if len(parts) > 1 else parts[0][k] for k in range(3))
+    if normalise and states.dtype == np.uint8:
+        states = (states.astype(np.float32) - 128.0) / 128.0
+    return states, robot, human
+
+
+class _Writer(threading.Thread):
+    """Appends finished host buffers to shards of `shard_states` samples; runs beside the generation loop."""
+
+    def __init__(self, out_dir, mode, shard_states, when, ext):
+        super().__init__(daemon=True)
+        self.out_dir, self.mode, self.shard_states, self.when, self.ext = out_dir, mode, shard_states, when, ext
+        self.q = queue.Queue(maxsize=2)
+        self.files, self.error = [], None
+        self._acc, self._count, self._shard = [], 0, 0
+
+    def _flush(self):
+        if not self._acc:
+            return
+        states = np.concatenate([a[0] for a in self._acc])
+        robot = np.concatenate([a[1] for a in self._acc])
+        human = np.concatenate([a[2] for a in self._acc])
+        name = data_file_name(self.mode, len(states), self.when, self.ext)
+        if self._shard or self.shard_states:
+            base, ext = os.path.splitext(name)
+            name = '%s_part%04d%s' % (base, self._shard, ext)
+        path = os.path.join(self.out_dir, name)
+        save_data(path, states, robot, human)
+        self.files.append(path)
+        self._acc, self._count, self._shard = [], 0, self._shard + 1
+
+    def run(self):
+        try:
+            while True:
+                item = self.q.get()
+                if item is None:
+                    break
+                states, robot, human, release = item
+                self._acc.append((states.copy(), robot.copy(), human.copy()))
+                release.set()  # the pinned buffer may be refilled
+                self._count += len(robot)
+                if self.shard_states and self._count >= self.shard_states:
+                    self._flush()
+            self._flush()
+        except Exception as e:  # surfaced by generate()
+            self.error = e
+            while self.q.get() is not None:
+                pass
+
+
+def generate(env, n_states, out_dir, states='f32', shard_states=0, when=None, keep_in_memory=False):
+    """Run the data-generation loop on `env` (a BatchedAirHockeyEnv built with auto_reset=True, max_episode_steps=200)
+    until at least n_states samples exist (whole steps: ceil(n_states / n_envs) * n_envs samples are produced and the
+    surplus dropped), writing `states` / `robot_actions` / `human_actions`.
+
+    states: 'f32' = the reference's normalised float32 stack (mode 'rgb') — or float64 gray-diff when env.processor.mode
+    is 'gray-diff' (processor.py:53-64); 'u8' = the raw uint8 stack.  shard_states: samples per output file (0 = one file).
+    -> dict(files, samples, seconds, samples_per_s, bytes_to_host).  keep_in_memory also returns the arrays (tests)."""
+    if states not in ('f32', 'u8'):
+        raise ValueError("states must be 'f32' or 'u8'")
+    os.makedirs(out_dir, exist_ok=True)
+    n = env.n_envs
+    mode = env.processor.mode
+    fmt = 'u8' if states == 'u8' else mode
+    steps = (int(n_states) + n - 1) // n
+    dev = env.device
+    copy_stream = torch.cuda.Stream(device=dev)
+    main = torch.cuda.current_stream(dev)
+
+    def pinned(shape, dtype):
+        return torch.empty(shape, dtype=dtype).pin_memory()
+
+    probe = env.observation(fmt)
+    slots = []
+    for _ in range(2):
+        slots.append({'obs': pinned(tuple(probe.shape), probe.dtype),
+                      'robot': pinned((n,), torch.uint8), 'human': pinned((n,), torch.uint8),
+                      'ready': torch.cuda.Event(), 'free': threading.Event()})
+        slots[-1]['free'].set()
+    del probe
+    writer = _Writer(out_dir, mode, int(shard_states), when, None)
+    writer.start()
+    kept = []
+    t0 = time.perf_counter()
+    pending = None
+    for t in range(steps + 1):
+        if t < steps:
+            s = slots[t & 1]
+            s['free'].wait()       # the writer has consumed this slot's previous contents
+            s['free'].clear()
+            env.step()
+            # the stacked observation must be taken before the next step overwrites the oldest ring slot
+            obs = env.observation(fmt)
+            rl, hl = env.robot_label.clone(), env.human_label.clone()
+            done_step = torch.cuda.Event()
+            done_step.record(main)
+            with torch.cuda.stream(copy_stream):
+                copy_stream.wait_event(done_step)
+                s['obs'].copy_(obs, non_blocking=True)
+                s['robot'].copy_(rl, non_blocking=True)
+                s['human'].copy_(hl, non_blocking=True)
+                s['ready'].record(copy_stream)
+            obs.record_stream(copy_stream)
+            rl.record_stream(copy_stream)
+            hl.record_stream(copy_stream)
+        if pending is not None:    # hand the previous step's buffers to the writer while this step runs
+            p = pending
+            p['ready'].synchronize()
+            take = min(n, int(n_states) - (t - 1) * n)
+            item = (p['obs'].numpy()[:take], p['robot'].numpy()[:take].view(np.int8), p['human'].numpy()[:take].view(np.int8), p['free'])
+            if keep_in_memory:
+                kept.append(tuple(a.copy() for a in item[:3]))
+            writer.q.put(item)
+        pending = slots[t & 1] if t < steps else None
+    writer.q.put(None)
+    writer.join()
+    if writer.error is not None:
+        raise writer.error
+    dt = time.perf_counter() - t0
+    samples = int(n_states)
+    per_sample = int(np.prod(slots[0]['obs'].shape[1:])) * slots[0]['obs'].element_size() + 2
+    out = {'files': writer.files, 'samples': samples, 'seconds': dt, 'samples_per_s': samples / dt,
+           'bytes_to_host': samples * per_sample, 'steps': steps}
+    if keep_in_memory:
+        out['arrays'] = tuple(np.concatenate([k[i] for k in kept]) for i in range(3))
+    return out

@@ -160,6 +160,20 @@ class BatchedAirHockeyEnv(object):
                                           p(out['robot_action']), p(out['human_action']), p(out.get('frame'))))
         return out
 
+    def step_host_begin(self, robot_action=None, human_action=None, out=None):
+        """Enqueue a host-buffer step without waiting (ahk_step_host_begin) -> ticket for step_host_wait.  For loops whose
+        next actions do not depend on this step's results (generate_data.py:51: the AI plays both sides): up to 8 steps
+        may be in flight, each with its own `out` buffers."""
+        p = lambda a: a.ctypes.data_as(C.c_void_p) if a is not None else None
+        t = self.lib.ahk_step_host_begin(self._h, p(robot_action), p(human_action), p(out['reward']), p(out['done']),
+                                         p(out['robot_action']), p(out['human_action']), p(out.get('frame')))
+        if t < 0:
+            _lib.check(t)
+        return t
+
+    def step_host_wait(self, ticket):
+        _lib.check(self.lib.ahk_step_host_wait(self._h, ticket))
+
     def host_buffers(self, want_frame=False):
         """Pinned host arrays for step_host."""
         n = self.n_envs

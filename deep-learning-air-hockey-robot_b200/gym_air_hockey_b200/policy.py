@@ -22,6 +22,8 @@ SHAPES = (
     ("out_w", (512, 10)), ("out_b", (10,)),
 )
 FLOPS_PER_SAMPLE = 2 * 10227008
+# MACs per sample by layer: conv1, conv2, conv3, dense1, dense2, out
+LAYER_MACS = (4841280, 924160, 2097152, 2097152, 262144, 5120)
 
 
 def keras_default_init(seed=0, randomize_bn=False):
@@ -86,6 +88,15 @@ class PolicyNetwork(object):
                                                C.c_void_p(logits.data_ptr()), C.c_void_p(action.data_ptr()), stream))
         self.launches += 6
         return logits, action
+
+    def forward_profiled(self, env, logits, action):
+        """forward() with CUDA events around each layer kernel -> [conv1, conv2, conv3, dense1, dense2, out] in ms."""
+        ms = (C.c_float * 6)()
+        stream = C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+        _lib.check(self.lib.ahk_policy_forward_profiled(self._h, C.c_void_p(env.frames.data_ptr()), env.n_envs, int(env.head),
+                                                        C.c_void_p(logits.data_ptr()), C.c_void_p(action.data_ptr()), stream, ms))
+        self.launches += 6
+        return list(ms)
 
     def forward(self, env, logits=None, action=None):
         return self.forward_ring(env.frames, env.head, logits, action)

@@ -90,11 +90,22 @@ int ahk_reset(ahk_env *env, const uint8_t *mask_dev, const uint8_t *episode_dev,
  * then the new frame of every env rasterised into ring slot `head` (advanced first).  robot_dev/human_dev [n] labels or NULL. */
 int ahk_step(ahk_env *env, const uint8_t *robot_dev, const uint8_t *human_dev, void *stream);
 
-/* The same call with HOST buffers, for callers that live on the CPU like the reference's loops do: copies the
- * actions in, steps, copies reward/done/labels (and, if frame_host != NULL, the new uint8 frame [n][3][128][128])
- * out, and waits.  Any pointer may be NULL. */
+/* The same call with HOST buffers, for callers that live on the CPU like the reference's loops do
+ * (generate_data.py:44-58, reinforcement/train.py:87-96): actions in, step, reward/done/labels (and, if
+ * frame_host != NULL, the new uint8 frame [n][3][128][128]) out, then waits.  Any pointer may be NULL.
+ * PINNED buffers (cudaHostAlloc / cudaHostRegister, e.g. torch's pin_memory) are read and written by the step kernel
+ * itself through their device mapping — 2 bytes in, 7 bytes out per env over PCIe, ONE kernel launch, no copy-engine
+ * transfers; pageable buffers go through cudaMemcpyAsync.  The frame, when asked for, is always a copy (49 152 B/env). */
 int ahk_step_host(ahk_env *env, const uint8_t *robot_host, const uint8_t *human_host, float *reward_host,
                   uint8_t *done_host, uint8_t *robot_label_host, uint8_t *human_label_host, uint8_t *frame_host);
+
+/* ahk_step_host split in two so that a caller whose next actions do not depend on this step's results — the data
+ * generation loop, where the programmed AI plays both sides (generate_data.py:51) — can keep up to 8 steps in flight
+ * (each with its own output buffers): _begin enqueues and returns a ticket (>= 0) or a negative status, _wait blocks
+ * until that step's results are in the host buffers.  ahk_step_host == _begin + _wait. */
+int ahk_step_host_begin(ahk_env *env, const uint8_t *robot_host, const uint8_t *human_host, float *reward_host,
+                        uint8_t *done_host, uint8_t *robot_label_host, uint8_t *human_label_host, uint8_t *frame_host);
+int ahk_step_host_wait(ahk_env *env, int ticket);
 
 /* ahk_step with CUDA events recorded on `stream` around its kernel(s); waits, then reports the durations.  Default
  * (fused) path: *env_ms = 0 and *raster_ms = the one fused kernel (physics + AI + labels + raster).  With the A/B switch
@@ -146,6 +157,10 @@ void ahk_policy_destroy(ahk_policy *p);
  * (either may be NULL). */
 int ahk_policy_forward(ahk_policy *p, const uint8_t *frames_dev, int n, int head, float *logits_dev,
                        uint8_t *action_dev, void *stream);
+/* The same forward pass with CUDA events recorded on `stream` around each of its six kernels (conv1, conv2, conv3,
+ * dense1, dense2, out); waits, then reports their durations in layer_ms[6].  Measurement aid for bench.py's roofline. */
+int ahk_policy_forward_profiled(ahk_policy *p, const uint8_t *frames_dev, int n, int head, float *logits_dev,
+                                uint8_t *action_dev, void *stream, float *layer_ms);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,50 @@
+"""Supervised dataset generation (ai/supervised/generate_data.py:35-73, utils/data_utils.py:3-13)."""
+import glob
+import os
+
+import numpy as np
+import pytest
+
+
+def test_file_name_and_round_trip(tmp_path):
+    """CPU: the container keeps the reference's three array names, dtypes and file-name pattern."""
+    from gym_air_hockey_b200 import dataset
+    name = dataset.data_file_name('rgb', 3000, when=1500000000, ext='h5')
+    assert name.endswith('_rgb_3000.h5') and len(name.split('_')[0]) == len('2017-07-14-02-40-00')
+    rs = np.random.RandomState(0)
+    states = rs.randint(0, 256, size=(5, 9, 128, 128)).astype(np.uint8)
+    robot, human = rs.randint(0, 9, size=5).astype(np.int8), rs.randint(0, 9, size=5).astype(np.int8)
+    for k in range(2):
+        dataset.save_data(str(tmp_path / ('x_part%04d.npz' % k)), states[k * 2:k * 2 + 3], robot[k * 2:k * 2 + 3], human[k * 2:k * 2 + 3])
+    s, r, h = dataset.load_data(str(tmp_path / 'x_part*.npz'), normalise=True)
+    assert s.dtype == np.float32 and s.shape == (6, 9, 128, 128) and r.dtype == np.int8
+    assert np.array_equal(s[:3], (states[:3].astype(np.float32) - 128.0) / 128.0)   # processor.py:39-42
+    assert np.array_equal(r, np.concatenate([robot[0:3], robot[2:5]])) and np.array_equal(h[3:], human[2:5])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("states", ["f32", "u8"])
+def test_generate_matches_stepping(cuda, table, tmp_path, states):
+    """The writer's samples are exactly what stepping the same engine by hand produces, in step-major order, in the
+    reference's dtypes: float32 normalised (n, 9, 128, 128) states, int8 labels."""
+    from gym_air_hockey_b200 import BatchedAirHockeyEnv, dataset
+    n, total = 6, 50
+    env = BatchedAirHockeyEnv(n, table=table, seed=21, max_episode_steps=20)
+    env.reset()
+    out = dataset.generate(env, total, str(tmp_path), states=states, shard_states=24, when=1500000000)
+    assert out['samples'] == total and out['steps'] == 9 and len(out['files']) >= 2
+    s, r, h = dataset.load_data(os.path.join(str(tmp_path), '*.npz'))
+    assert s.shape == (total, 9, 128, 128) and r.shape == (total,) and r.dtype == np.int8 and h.dtype == np.int8
+    assert s.dtype == (np.float32 if states == 'f32' else np.uint8)
+
+    ref = BatchedAirHockeyEnv(n, table=table, seed=21, max_episode_steps=20)
+    ref.reset()
+    want_s, want_r, want_h = [], [], []
+    for _ in range(9):
+        _, _, _, info = ref.step()
+        want_s.append(ref.observation('rgb' if states == 'f32' else 'u8').cpu().numpy())
+        want_r.append(info['robot_action'].cpu().numpy().astype(np.int8))
+        want_h.append(info['human_action'].cpu().numpy().astype(np.int8))
+    assert np.array_equal(s, np.concatenate(want_s)[:total])
+    assert np.array_equal(r, np.concatenate(want_r)[:total]) and np.array_equal(h, np.concatenate(want_h)[:total])
+    assert set(np.unique(r)) <= set(range(9))   # label 9 never comes from the simulator

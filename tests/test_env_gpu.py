@@ -283,6 +283,41 @@ def test_step_host_matches_device_path(cuda, table):
         assert np.array_equal(a.frames[a.head].cpu().numpy(), out['frame'])
 
 
+def test_step_host_pipelined_and_pageable(cuda, table):
+    """ahk_step_host_begin/_wait with four steps in flight (pinned buffers: the kernel reads the actions and writes the
+    results through mapped host memory) and plain pageable numpy buffers (copy engine) both replay the device path."""
+    n = 700
+    a = make_env(n, table, seed=11, max_episode_steps=25)
+    b = make_env(n, table, seed=11, max_episode_steps=25)
+    c = make_env(n, table, seed=11, max_episode_steps=25)
+    for e in (a, b, c):
+        e.reset()
+    rs = np.random.RandomState(3)
+    depth, steps = 4, 40
+    outs = [b.host_buffers() for _ in range(depth)]
+    acts = [cuda.empty(n, dtype=cuda.uint8).pin_memory().numpy() for _ in range(depth)]
+    pageable = {k: np.empty_like(v) for k, v in outs[0].items()}
+    expect, tickets = [], []
+    for t in range(steps + depth):
+        if t >= depth:  # retire the oldest step in flight
+            k = (t - depth) % depth
+            b.step_host_wait(tickets[t - depth])
+            for key, want in zip(('reward', 'done', 'robot_action', 'human_action'), expect[t - depth]):
+                assert np.array_equal(outs[k][key], want), (t, key)
+        if t < steps:
+            k = t % depth
+            acts[k][:] = rs.randint(0, 10, size=n)
+            _, reward, done, info = a.step(acts[k].copy(), acts[k].copy())
+            expect.append((reward.cpu().numpy(), done.cpu().numpy().astype(np.uint8), info['robot_action'].cpu().numpy(), info['human_action'].cpu().numpy()))
+            tickets.append(b.step_host_begin(acts[k], acts[k], outs[k]))
+            c.step_host(acts[k].copy(), acts[k].copy(), pageable)
+            for key, want in zip(('reward', 'done', 'robot_action', 'human_action'), expect[-1]):
+                assert np.array_equal(pageable[key], want), (t, key)
+    assert np.array_equal(a.frames.cpu().numpy(), b.frames.cpu().numpy())
+    assert np.array_equal(a.get_state()[0].view(np.uint32), b.get_state()[0].view(np.uint32))
+    assert np.array_equal(b.reward.cpu().numpy(), expect[-1][0])  # the device copies are written as well
+
+
 def test_full_size_properties(cuda, table):
     """configs[1] at full size (4096 envs): properties that need no oracle — determinism, independence of sharding
     (global env ids, SPEC.md §4), bodies inside the rink, statistics that add up."""

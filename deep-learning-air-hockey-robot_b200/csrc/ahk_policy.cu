@@ -111,6 +111,24 @@ __device__ __forceinline__ void umma_commit(uint64_t *bar)
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(smem_u32(bar)) : "memory");
 }
 
+// 16 consecutive fp32 columns of this thread's TMEM lane, without waiting for the data (tmem_wait_ld before use)
+__device__ __forceinline__ void tmem_load16_async(uint32_t taddr, uint32_t (&r)[16])
+{
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr) : "memory");
+}
+// c != 0 ? a : b without a branch
+__device__ __forceinline__ uint32_t select(uint32_t a, uint32_t b, int c)
+{
+    uint32_t d;
+    asm("{\n\t.reg .pred p;\n\tsetp.ne.s32 p, %3, 0;\n\tselp.b32 %0, %1, %2, p;\n\t}" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+__device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
 // 16 consecutive fp32 columns of this thread's TMEM lane
 __device__ __forceinline__ void tmem_load16(uint32_t taddr, float (&v)[16])
 {
@@ -217,10 +235,12 @@ __global__ void __launch_bounds__(kThreads) layer_kernel(Args a)
     const int kc_lane = (warp & 1) * 4 + ((tid & 31) >> 3), g = (warp >> 1) * 8 + (tid & 7);
     uint32_t chg = 0, it = 0;                  // chunks / tiles processed so far by this CTA (barrier phases)
 
-#pragma unroll 1
-    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
-        int r0[8];
-        unsigned ok = 0u;
+    // The gather runs one chunk ahead of its use (across tile boundaries too): the next chunk's loads are issued right
+    // after this chunk's registers have been stored and are in flight during the barrier, the MMA issue and the epilogue.
+    int r0[8];
+    unsigned ok = 0u;
+    auto rows_of = [&](int tile) { // per-row constants of the gather for `tile`
+        ok = 0u;
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
             const int row = tile * kBM + i * 16 + g;
@@ -238,6 +258,20 @@ __global__ void __launch_bounds__(kThreads) layer_kernel(Args a)
                 }
             }
         }
+    };
+    uint4 v[8];
+    int pf_tile = blockIdx.x, pf_ch = 0; // the chunk held in v / the next one to fetch
+    auto prefetch = [&]() {
+        if (pf_tile >= n_tiles) return;
+        if (pf_ch == 0) rows_of(pf_tile);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[i] = gather<L>(a, (ok >> i) & 1u, r0[i], pf_ch * 8 + kc_lane);
+        if (++pf_ch == NCH) { pf_ch = 0; pf_tile += gridDim.x; }
+    };
+    prefetch();
+
+#pragma unroll 1
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
 #pragma unroll 1
         for (int ch = 0; ch < NCH; ++ch, ++chg) {
             const uint32_t st = chg & 1u, use = chg >> 1;
@@ -246,13 +280,11 @@ __global__ void __launch_bounds__(kThreads) layer_kernel(Args a)
                 mbar_expect_tx(&s_full[st], kBBytes);
                 bulk_load(s_b + st * kBBytes, wsrc + static_cast<size_t>(ch) * (kBBytes / 16), kBBytes, &s_full[st]);
             }
-            uint4 v[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) v[i] = gather<L>(a, (ok >> i) & 1u, r0[i], ch * 8 + kc_lane);
             // canonical layout [K core][row group][row % 8]: row i*16 + g sits at g*16 + i*256 inside its K core
             uint8_t *dst = s_a + st * kAStage + kc_lane * kALbo + g * 16;
 #pragma unroll
             for (int i = 0; i < 8; ++i) *reinterpret_cast<uint4 *>(dst + i * 256) = v[i];
+            prefetch();
             fence_async_smem();
             __syncthreads();
             if (tid == 0) {
@@ -344,33 +376,48 @@ cudaError_t launch(const Args &a, int tiles, int grid_y, int sms, cudaStream_t s
 // N = 5, and every output pixel's 576-element A row would be built in shared memory by the CUDA cores (1.9 MB of
 // shared-memory writes per sample; the first version of this file did that and spent 6.2 ms per 8192 samples in it).
 // Here the A operand is the IMAGE ITSELF, bf16, never expanded:
-//   * M row m = (output row y, 8-pixel block xb of an input row); the K = 16 window of one MMA is the 16 consecutive
-//     pixels 8 xb .. 8 xb + 15 of input row 3 y + ky of plane c — in the canonical no-swizzle K-major layout that is
-//     simply the raw row (one core-matrix row = 8 pixels = 16 bytes, next M row = next 16 bytes) with LBO = 16 bytes:
-//     the second K core matrix of row m IS the first of row m + 1.
-//   * Output pixels whose 8-wide window lies inside that 16-pixel window: x = 8q + 3 ph + j with xb = 3q + ph, j < 3,
-//     at offset ph + 3j.  The stride-3 phase differs per row, one MMA applies one B to all rows, so B carries all three:
-//     N = 48 = 3 phases x (3 outputs x 5 channels, padded to 16), a banded (Toeplitz) copy of the 8-tap kernel row;
-//     the epilogue keeps the 16 columns of its row's phase.  Tensor work is 3.6x the useful MACs, and irrelevant: the
-//     MMAs are bound by streaming A from shared memory (4 KB each), 72 per 8 output rows instead of ~250 KB of im2col.
-//   * Input rows are stored by residue (row mod 3) so that (y, half row) -> address is linear (SBO = 128) for every ky.
+//   * M row m = (input-row index i, 8-pixel block xb); the K = 16 window of one MMA is the 16 consecutive pixels
+//     8 xb .. 8 xb + 15 of one input row of one plane — in the canonical no-swizzle K-major layout that is simply the
+//     raw row (one core-matrix row = 8 pixels = 16 bytes, next M row = next 16 bytes) with LBO = 16 bytes: the second
+//     K core matrix of row m IS the first of row m + 1.
+//   * Input rows are stored by residue class (row mod 3): class j, index i holds input row 3 i + j, so that
+//     (i, half row) -> address is linear (SBO = 128) and ONE A tile (plane, class j) serves the three kernel rows
+//     ky = j, j + 3, j + 6: the row contributes to output rows y = i, i - 1, i - 2.
+//   * Output pixels whose 8-wide window lies inside the 16-pixel window: x = 8q + 3 ph + jj with xb = 3q + ph, jj < 3,
+//     at offset ph + 3 jj.  The stride-3 phase differs per row and one MMA applies one B to all rows, so B carries all
+//     of it: N = 144 = 3 kernel-row groups x 3 phases x (3 outputs x 5 channels, padded to 16) — a banded (Toeplitz)
+//     copy of three 8-tap kernel rows.  27 MMAs (9 planes x 3 classes) per 8 input-row indices = 6 finished output rows;
+//     an MMA of this shape costs ~70 cycles whatever N <= 144 is (it is bound by streaming its 4 KB A tile from shared
+//     memory; measured with N = 48 and 72 MMAs per tile: tensor pipe 74 % busy, 1.15 ms per 8192 samples).
+//   * The epilogue keeps the 16 columns of its row's phase in each kernel-row group and adds the three groups across
+//     rows (y = i - kv) through a small shared-memory exchange, then bias, ReLU, bf16, [pixel][8] layout for conv2.
 // Persistent, warp-specialised CTA (one per SM): 8 producer warps convert uint8 ring rows to bf16 slabs (one frame of
-// the 3-deep stack = 3 colour planes x 30 rows per stage, 4 stages), 1 warp issues the MMAs (24 per slab, 72 per tile),
-// 4 warps run the epilogue out of a double-buffered TMEM accumulator (bias, ReLU, bf16, [pixel][8] layout for conv2).
+// the 3-deep stack = 3 colour planes x 24 rows per stage, 3 stages, next slab's loads in flight during the conversion),
+// 1 warp issues the MMAs, 4 warps run the epilogue out of a double-buffered TMEM accumulator.
 namespace c1 {
 constexpr int kProducers = 256, kCta = kProducers + 32 + 128;
-constexpr int kStages = 4;
-constexpr int kYTile = 8, kTilesPerSample = 6;           // 41 output rows in tiles of 8
-constexpr int kRows = 30, kClassRows = 10;               // input rows per slab plane; rows per residue class
-constexpr int kRowBytes = kDim * 2, kClassBytes = kClassRows * kRowBytes, kPlaneBytes = 3 * kClassBytes, kSlabBytes = 3 * kPlaneBytes;
-constexpr int kSlabPitch = kSlabBytes + 256;             // + zeroed pad: the last row's K window spills 16 bytes
-constexpr int kN = 48;
-constexpr int kWBlock = 16 * kN * 2;                     // one (plane, ky) B operand: K = 16 x N = 48 bf16
-constexpr int kWBytes = 72 * kWBlock;                    // 110 592 B, resident in shared memory
-constexpr int kSmem = kWBytes + kStages * kSlabPitch;    // 203 776 B
-constexpr int kVecsPerSlab = 3 * kRows * 8;              // 16-pixel vectors per slab
+constexpr int kStages = 3;
+constexpr int kITile = 8, kYTile = 6, kTilesPerSample = 7; // 8 input-row indices -> 6 finished output rows; 7 x 6 >= 41
+constexpr int kRows = 3 * kITile;                          // input rows per slab plane
+constexpr int kRowBytes = kDim * 2, kClassBytes = kITile * kRowBytes, kPlaneBytes = 3 * kClassBytes, kSlabBytes = 3 * kPlaneBytes;
+constexpr int kSlabPitch = kSlabBytes + 256;               // + zeroed pad: the last row's K window spills 16 bytes
+constexpr int kN = 144;
+constexpr int kWBlock = 16 * kN * 2;                       // one (plane, class) B operand: K = 16 x N = 144 bf16
+constexpr int kWBytes = 27 * kWBlock;                      // 124 416 B, resident in shared memory
+constexpr int kExBytes = 2 * kYTile * 16 * 16 * 4;         // exchange of the kv = 1, 2 partial sums: [2][6][16 xb][16] float, 
+constexpr int kSmem = kWBytes + kStages * kSlabPitch + kExBytes; // 192 768 B
+constexpr int kVecsPerSlab = 3 * kRows * 8;                // 16-pixel vectors per slab
+constexpr int kTmemCols = 512;                             // 2 accumulators x 256 columns (144 used)
 } // namespace c1
 
+// 16 bytes, read once; volatile so that it stays where it is written, ahead of the barrier waits (an ld.global.nc from
+// __ldg may be sunk past them to its first use, which defeats the prefetch)
+__device__ __forceinline__ uint4 load_stream(const uint8_t *p)
+{
+    uint4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    return v;
+}
 __device__ __forceinline__ void mbar_arrive(uint64_t *bar) { asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(bar)) : "memory"); }
 
 __global__ void __launch_bounds__(c1::kCta, 1) conv1_kernel(Args a)
@@ -379,6 +426,7 @@ __global__ void __launch_bounds__(c1::kCta, 1) conv1_kernel(Args a)
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t *s_w = smem;
     uint8_t *s_slab = smem + kWBytes;
+    float *s_ex = reinterpret_cast<float *>(smem + kWBytes + kStages * kSlabPitch);
     __shared__ __align__(8) uint64_t s_wfull, s_full[kStages], s_empty[kStages], s_tfull[2], s_tempty[2];
     __shared__ uint32_t s_tmem;
     __shared__ float s_bias[8];
@@ -394,7 +442,7 @@ __global__ void __launch_bounds__(c1::kCta, 1) conv1_kernel(Args a)
     if (tid < 8) s_bias[tid] = tid < 5 ? a.bias[tid] : 0.0f;
     for (int i = tid; i < kStages * 16; i += kCta) // the pad behind each slab
         *reinterpret_cast<uint4 *>(s_slab + (i >> 4) * kSlabPitch + kSlabBytes + (i & 15) * 16) = make_uint4(0, 0, 0, 0);
-    if (warp == kProducers / 32) tmem_alloc(&s_tmem, 128); // 2 accumulators x 64 columns (48 used)
+    if (warp == kProducers / 32) tmem_alloc(&s_tmem, kTmemCols);
     fence_async_smem();
     tc_fence_before();
     __syncthreads();
@@ -413,38 +461,65 @@ __global__ void __launch_bounds__(c1::kCta, 1) conv1_kernel(Args a)
             dst_off[t] = colour * kPlaneBytes + (lr % 3) * kClassBytes + (lr / 3) * kRowBytes + xv * 32;
             lrow[t] = v < kVecsPerSlab ? lr : kDim; // kDim: never valid
         }
+        const int swap = (tid >> 2) & 1; // xv >= 4
         const int my_items = blockIdx.x < items ? (items - 1 - blockIdx.x) / gridDim.x + 1 : 0;
-        const uint32_t slabs = 3u * my_items;
-        auto load = [&](uint32_t f, uint4 (&px)[3]) { // slab f of this CTA: item f / 3, stack age f % 3
-            const int item = blockIdx.x + static_cast<int>(f / 3u) * gridDim.x, age = static_cast<int>(f % 3u);
-            const int sample = item / kTilesPerSample, y0 = (item - sample * kTilesPerSample) * kYTile;
-            const uint8_t *src = a.frames + (static_cast<size_t>((a.head + 3 - age) % 3) * a.n + sample) * kFrameBytes + 3 * y0 * kDim;
+        // all three slabs (stack ages) of tile k: 9 vectors per thread
+        auto load = [&](int k, uint4 (&px)[3][3]) {
+            const int item = blockIdx.x + k * gridDim.x;
+            const int sample = item / kTilesPerSample, r_first = 3 * (item - sample * kTilesPerSample) * kYTile;
 #pragma unroll
-            for (int t = 0; t < 3; ++t) {
-                px[t] = make_uint4(0, 0, 0, 0);
-                if (3 * y0 + lrow[t] < kDim) px[t] = __ldg(reinterpret_cast<const uint4 *>(src + src_off[t]));
-            }
-        };
-        uint4 cur[3], nxt[3];
-        if (slabs) load(0u, cur);
-        for (uint32_t f = 0; f < slabs; ++f) {
-            if (f + 1u < slabs) load(f + 1u, nxt); // in flight while this slab is converted: the loads never wait for a stage
-            const uint32_t st = f % kStages;
-            if (f >= kStages) mbar_wait(&s_empty[st], ((f / kStages) - 1u) & 1u);
-            uint8_t *slab = s_slab + st * kSlabPitch;
+            for (int age = 0; age < 3; ++age) {
+                const uint8_t *src = a.frames + (static_cast<size_t>((a.head + 3 - age) % 3) * a.n + sample) * kFrameBytes + r_first * kDim;
 #pragma unroll
-            for (int t = 0; t < 3; ++t) {
-                if (lrow[t] < kDim) {
-                    const uint2 q0 = u8x4_to_bf16x4(cur[t].x), q1 = u8x4_to_bf16x4(cur[t].y), q2 = u8x4_to_bf16x4(cur[t].z), q3 = u8x4_to_bf16x4(cur[t].w);
-                    uint4 *dst = reinterpret_cast<uint4 *>(slab + dst_off[t]);
-                    dst[0] = make_uint4(q0.x, q0.y, q1.x, q1.y);
-                    dst[1] = make_uint4(q2.x, q2.y, q3.x, q3.y);
+                for (int t = 0; t < 3; ++t) {
+                    px[age][t] = make_uint4(0, 0, 0, 0);
+                    if (r_first + lrow[t] < kDim) px[age][t] = load_stream(src + src_off[t]);
                 }
             }
-            fence_async_smem();
-            mbar_arrive(&s_full[st]);
+        };
+        uint32_t f = 0; // slabs filled so far
+        // Tile k + 1's loads (27 KB per CTA) are issued before tile k is converted and stay in flight meanwhile: with one
+        // slab in flight the kernel ran at load latency (9 KB per microsecond per SM: 1.15 ms per 8192 samples).  The two
+        // register sets swap roles by unrolling, so nothing waits on a load it does not need yet.
+        auto convert = [&](int k, uint4 (&cur)[3][3], uint4 (&nxt)[3][3]) {
+            // Every vector of `cur` is touched before the next tile's loads are issued: the hardware tracks loads with a
+            // handful of scoreboard counters, and a new load sharing a counter with a vector still to be converted would
+            // make that conversion wait for the NEW load (seen as a full DRAM latency per tile in the stall samples).
+            uint32_t touched = 0u;
 #pragma unroll
-            for (int t = 0; t < 3; ++t) cur[t] = nxt[t];
+            for (int age = 0; age < 3; ++age)
+#pragma unroll
+                for (int t = 0; t < 3; ++t) touched ^= cur[age][t].x ^ cur[age][t].y ^ cur[age][t].z ^ cur[age][t].w;
+            if (touched == 0x9E3779B9u && a.n < 0) s_bias[7] = 1.0f; // never true; keeps the touches alive
+            if (k + 1 < my_items) load(k + 1, nxt);
+#pragma unroll
+            for (int age = 0; age < 3; ++age, ++f) {
+                const uint32_t st = f % kStages;
+                if (f >= kStages) mbar_wait(&s_empty[st], ((f / kStages) - 1u) & 1u);
+                uint8_t *slab = s_slab + st * kSlabPitch;
+#pragma unroll
+                for (int t = 0; t < 3; ++t) {
+                    if (lrow[t] < kDim) {
+                        const uint4 c = cur[age][t];
+                        const uint2 q0 = u8x4_to_bf16x4(c.x), q1 = u8x4_to_bf16x4(c.y), q2 = u8x4_to_bf16x4(c.z), q3 = u8x4_to_bf16x4(c.w);
+                        uint4 *dst = reinterpret_cast<uint4 *>(slab + dst_off[t]);
+                        // lanes 4..7 of each row store their halves in the other order: one instruction then covers all
+                        // eight 16-byte bank groups instead of four
+                        const uint4 lo = make_uint4(q0.x, q0.y, q1.x, q1.y), hi = make_uint4(q2.x, q2.y, q3.x, q3.y);
+                        dst[swap] = swap ? hi : lo;
+                        dst[swap ^ 1] = swap ? lo : hi;
+                    }
+                }
+                fence_async_smem();
+                mbar_arrive(&s_full[st]);
+            }
+        };
+        uint4 pa[3][3], pb[3][3];
+        if (my_items) load(0, pa);
+#pragma unroll 1
+        for (int k = 0; k < my_items; k += 2) {
+            convert(k, pa, pb);
+            if (k + 1 < my_items) convert(k + 1, pb, pa);
         }
     } else if (warp == kProducers / 32) {
         // ---------------------------------------------------------------- MMA issue (one thread)
@@ -460,18 +535,18 @@ __global__ void __launch_bounds__(c1::kCta, 1) conv1_kernel(Args a)
                 if (tile >= 2) mbar_wait(&s_tempty[buf], ((tile >> 1) - 1) & 1);
                 tc_fence_after();
                 for (int age = 0; age < 3; ++age, ++fill) {
-                    const int st = fill % kStages;
+                    const uint32_t st = fill % kStages;
                     mbar_wait(&s_full[st], (fill / kStages) & 1);
                     tc_fence_after();
                     const uint32_t slab = smem_u32(s_slab + st * kSlabPitch);
 #pragma unroll
                     for (int colour = 0; colour < 3; ++colour) {
 #pragma unroll
-                        for (int ky = 0; ky < 8; ++ky) {
-                            // rows 3 y + ky, y = 0..7: residue class ky % 3, from row index ky / 3 on; K step = 16 bytes
-                            const uint64_t ad = smem_desc(slab + colour * kPlaneBytes + (ky % 3) * kClassBytes + (ky / 3) * kRowBytes, 16, 128);
-                            const uint64_t bd = smem_desc(w_base + ((age * 3 + colour) * 8 + ky) * kWBlock, (kN / 8) * 128, 128);
-                            umma_bf16(tmem + buf * 64, ad, bd, kIdesc, (age | colour | ky) != 0);
+                        for (int cls = 0; cls < 3; ++cls) {
+                            // M row (i, xb) = input row 3 i + cls, pixels 8 xb ..: K step = 16 bytes, 8-row groups 128 bytes apart
+                            const uint64_t ad = smem_desc(slab + colour * kPlaneBytes + cls * kClassBytes, 16, 128);
+                            const uint64_t bd = smem_desc(w_base + ((age * 3 + colour) * 3 + cls) * kWBlock, (kN / 8) * 128, 128);
+                            umma_bf16(tmem + buf * 256, ad, bd, kIdesc, (age | colour | cls) != 0);
                         }
                     }
                     umma_commit(&s_empty[st]);
@@ -481,44 +556,76 @@ __global__ void __launch_bounds__(c1::kCta, 1) conv1_kernel(Args a)
         }
     } else {
         // ---------------------------------------------------------------- epilogue: 4 warps, thread = TMEM lane = M row
-        const int q4 = warp & 3;                 // the TMEM lane quarter this warp may read
+        // (one warp per scheduler, so its instruction count is its time: the phase select is branch-free — as divergent
+        // branches it made this role the kernel's bottleneck — and the TMEM loads are waited for three at a time)
+        const int q4 = warp & 3;                       // the TMEM lane quarter this warp may read
         const int m = q4 * 32 + (tid & 31);
-        const int yl = m >> 4, xb = m & 15, ph = xb % 3, xq = xb / 3;
+        const int il = m >> 4, xb = m & 15, ph = xb % 3, xq = xb / 3;
+        const int is_ph0 = ph == 0, is_ph2 = ph == 2;
+        float *ex = s_ex;
         uint32_t tile = 0;
         for (int item = blockIdx.x; item < items; item += gridDim.x, ++tile) {
-            const int sample = item / kTilesPerSample, y = (item - sample * kTilesPerSample) * kYTile + yl;
+            const int sample = item / kTilesPerSample, y0 = (item - sample * kTilesPerSample) * kYTile;
             const uint32_t buf = tile & 1u;
             mbar_wait(&s_tfull[buf], (tile >> 1) & 1);
             tc_fence_after();
-            const uint32_t taddr = tmem + buf * 64 + (static_cast<uint32_t>(q4 * 32) << 16);
-            float v0[16], v1[16], v2[16];
-            tmem_load16(taddr, v0);
-            tmem_load16(taddr + 16, v1);
-            tmem_load16(taddr + 32, v2);
+            const uint32_t taddr = tmem + buf * 256 + (static_cast<uint32_t>(q4 * 32) << 16);
+            float part[3][16]; // [kernel-row group kv][3 outputs x 5 channels] of this row's phase
+#pragma unroll
+            for (int kv = 0; kv < 3; ++kv) {
+                uint32_t v0[16], v1[16], v2[16];
+                tmem_load16_async(taddr + kv * 48, v0);
+                tmem_load16_async(taddr + kv * 48 + 16, v1);
+                tmem_load16_async(taddr + kv * 48 + 32, v2);
+                tmem_wait_ld();
+#pragma unroll
+                for (int e = 0; e < 16; ++e) part[kv][e] = __uint_as_float(select(v2[e], select(v0[e], v1[e], is_ph0), is_ph2));
+            }
             tc_fence_before();
             mbar_arrive(&s_tempty[buf]); // the accumulator is in registers: the MMA warp may overwrite it
-            if (y < kC1) {
+            // kernel-row group kv of input-row index i belongs to output row i - kv
+#pragma unroll
+            for (int kv = 1; kv < 3; ++kv) {
+                const int yl = il - kv;
+                if (yl >= 0 && yl < kYTile) {
+                    float4 *dst = reinterpret_cast<float4 *>(ex + (((kv - 1) * kYTile + yl) * 16 + xb) * 16);
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) dst[e] = make_float4(part[kv][4 * e], part[kv][4 * e + 1], part[kv][4 * e + 2], part[kv][4 * e + 3]);
+                }
+            }
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            const int y = y0 + il;
+            if (il < kYTile && y < kC1) {
+                const float4 *p1 = reinterpret_cast<const float4 *>(ex + ((0 * kYTile + il) * 16 + xb) * 16);
+                const float4 *p2 = reinterpret_cast<const float4 *>(ex + ((1 * kYTile + il) * 16 + xb) * 16);
+                float sum[16];
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const float4 u = p1[e], w = p2[e];
+                    sum[4 * e] = part[0][4 * e] + u.x + w.x;
+                    sum[4 * e + 1] = part[0][4 * e + 1] + u.y + w.y;
+                    sum[4 * e + 2] = part[0][4 * e + 2] + u.z + w.z;
+                    sum[4 * e + 3] = part[0][4 * e + 3] + u.w + w.w;
+                }
                 const int x0 = 8 * xq + 3 * ph;
                 uint4 *out = reinterpret_cast<uint4 *>(a.out + (static_cast<size_t>(sample) * kP1 + y * kC1 + x0) * kAct1C);
 #pragma unroll
                 for (int j = 0; j < 3; ++j) {
-                    float c[5];
-#pragma unroll
-                    for (int ch = 0; ch < 5; ++ch) {
-                        const float d = ph == 0 ? v0[j * 5 + ch] : (ph == 1 ? v1[j * 5 + ch] : v2[j * 5 + ch]);
-                        c[ch] = fmaxf(d + s_bias[ch], 0.0f);
-                    }
                     if ((j < 2 || ph < 2) && x0 + j < kC1) {
+                        float c[5];
+#pragma unroll
+                        for (int ch = 0; ch < 5; ++ch) c[ch] = fmaxf(sum[j * 5 + ch] + s_bias[ch], 0.0f);
                         const __nv_bfloat162 p01 = __floats2bfloat162_rn(c[0], c[1]), p23 = __floats2bfloat162_rn(c[2], c[3]), p4 = __floats2bfloat162_rn(c[4], 0.0f);
                         out[j] = make_uint4(*reinterpret_cast<const uint32_t *>(&p01), *reinterpret_cast<const uint32_t *>(&p23), *reinterpret_cast<const uint32_t *>(&p4), 0u);
                     }
                 }
             }
+            asm volatile("bar.sync 1, 128;" ::: "memory"); // the exchange buffer is free for the next tile
         }
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == kProducers / 32) tmem_dealloc(tmem, 128);
+    if (warp == kProducers / 32) tmem_dealloc(tmem, kTmemCols);
 }
 
 cudaError_t launch_conv1(const Args &a, int grid, cudaStream_t s)
@@ -562,22 +669,29 @@ std::vector<uint16_t> pack_b(const std::vector<float> &w, int k_total, int n_rea
 }
 
 
-// conv1, Toeplitz form: W [576][5] folded (k = plane*64 + ky*8 + kx) -> 72 blocks (plane, ky) of the K-major canonical
-// B operand [K = 16][N = 48]: element (n, k) at (k/8) * 768 + (n/8) * 128 + (n%8) * 16 + (k%8) * 2 bytes;
-// n = phase*16 + j*5 + channel holds W[plane][ky][kx = k - (phase + 3j)][channel] (0 outside the 8 taps).
+// conv1, Toeplitz form: W [576][5] folded (k = plane*64 + ky*8 + kx) -> 27 blocks (plane, class) of the K-major canonical
+// B operand [K = 16][N = 144]: element (n, k) at (k/8) * 2304 + (n/8) * 128 + (n%8) * 16 + (k%8) * 2 bytes;
+// n = kv*48 + phase*16 + j*5 + channel holds W[plane][ky = class + 3 kv][kx = k - (phase + 3j)][channel]
+// (0 outside the 8 taps and for ky = 8).
 std::vector<uint16_t> pack_conv1_toeplitz(const std::vector<float> &wf)
 {
-    std::vector<uint16_t> out(static_cast<size_t>(72) * 16 * 48, 0);
-    for (int blk = 0; blk < 72; ++blk)
-        for (int ph = 0; ph < 3; ++ph)
-            for (int j = 0; j < 3; ++j)
-                for (int ch = 0; ch < 5; ++ch)
-                    for (int kx = 0; kx < 8; ++kx) {
-                        const int k = kx + ph + 3 * j, n = ph * 16 + j * 5 + ch;
-                        if (k >= 16) continue; // phase 2, third output: belongs to the next block's first
-                        const size_t at = static_cast<size_t>(blk) * 768 + (k / 8) * 384 + (n / 8) * 64 + (n % 8) * 8 + (k % 8);
-                        out[at] = to_bf16(wf[(static_cast<size_t>(blk) * 8 + kx) * 5 + ch]);
-                    }
+    constexpr int N = 144;
+    std::vector<uint16_t> out(static_cast<size_t>(27) * 16 * N, 0);
+    for (int plane = 0; plane < 9; ++plane)
+        for (int cls = 0; cls < 3; ++cls)
+            for (int kv = 0; kv < 3; ++kv) {
+                const int ky = cls + 3 * kv;
+                if (ky >= 8) continue;
+                for (int ph = 0; ph < 3; ++ph)
+                    for (int j = 0; j < 3; ++j)
+                        for (int ch = 0; ch < 5; ++ch)
+                            for (int kx = 0; kx < 8; ++kx) {
+                                const int k = kx + ph + 3 * j, n = kv * 48 + ph * 16 + j * 5 + ch;
+                                if (k >= 16) continue; // phase 2, third output: belongs to the next block's first
+                                const size_t at = static_cast<size_t>(plane * 3 + cls) * (16 * N) + (k / 8) * (8 * N) + (n / 8) * 64 + (n % 8) * 8 + (k % 8);
+                                out[at] = to_bf16(wf[(static_cast<size_t>(plane * 8 + ky) * 8 + kx) * 5 + ch]);
+                            }
+            }
     return out;
 }
 

@@ -13,7 +13,8 @@ KEYS = ['gpu__time_duration.sum', 'dram__bytes_read.sum', 'dram__bytes_write.sum
         'l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum', 'sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active',
         'sm__inst_executed_pipe_tensor.sum', 'smsp__average_warp_latency_per_inst_issued.ratio',
         'sm__cycles_elapsed.max', 'smsp__cycles_active.avg', 'l1tex__t_bytes_pipe_lsu_mem_global_op_st.sum',
-        'smsp__thread_inst_executed_per_inst_executed.ratio', 'sm__pipe_tensor_subpipe_hmma_cycles_active.avg.pct_of_peak_sustained_active']
+        'smsp__thread_inst_executed_per_inst_executed.ratio', 'sm__pipe_tc_cycles_active.avg.pct_of_peak_sustained_active',
+        'l1tex__data_pipe_tc_wavefronts_mem_shared.sum.pct_of_peak_sustained_elapsed', 'sm__pipe_tensor_subpipe_hmma_cycles_active.avg.pct_of_peak_sustained_active']
 
 
 def raw(rep):

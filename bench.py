@@ -31,6 +31,28 @@ STEP_TRAFFIC_NCU_4096 = 142.62e6  # mean of three captured launches: 142.23 MB w
 METRIC = "labeled env-steps/sec (physics+render+label)"
 
 
+_REAL_STDOUT = None
+
+
+def quiet_stdout():
+    """Everything libraries print to stdout (NCCL's version banner, for one) goes to stderr; emit() writes the one JSON line
+    the driver parses to the real stdout."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(obj):
+    data = (json.dumps(obj) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def measured_peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
@@ -121,7 +143,7 @@ def run_reference(args):
     dt = time.perf_counter() - t0
     value = n_envs * sub * args.steps / dt
     sample = "%d envs x %d sim-steps per bench step, %d threads" % (n_envs, sub, threads)
-    print(json.dumps({
+    emit(({
         "impl": "reference", "metric": METRIC, "value": value, "unit": "env-steps/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -131,18 +153,148 @@ def run_reference(args):
     }))
 
 
+def run_rollout(args):
+    """--workload rollout: BASELINE.json configs[3] — policy-in-the-loop rollout (ai/reinforcement/train.py:87-96 at batch
+    n): every step = fused env step with the robot's action from the CNN + the CNN forward on the new frames (six tcgen05
+    kernels reading the uint8 ring).  65 536 envs over 8 GPUs = 8192 per GPU; the human side is the programmed AI;
+    episode_length 256 (train.py:45); random-init weights (Glorot, seed 0).  N > 1: a flat 2 403 961-float32 gradient
+    buffer is all-reduced over NCCL every 25 steps (training_interval, train.py:47) — the buffer is synthetic: the
+    backward pass is SURVEY.md §8f N2, not built."""
+    import torch
+    import torch.distributed as dist
+    from gym_air_hockey_b200 import BatchedAirHockeyEnv
+    from gym_air_hockey_b200.policy import FLOPS_PER_SAMPLE, LAYER_MACS, PolicyNetwork
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the engine has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    n = args.envs_per_gpu or 8192
+    steps, warmup = min(args.steps, 512), max(min(args.warmup, 20), 3)
+    env = BatchedAirHockeyEnv(n, device=local, seed=0, env_id_base=rank * n, auto_reset=True, max_episode_steps=256)
+    pol = PolicyNetwork(max_batch=n, device=local)
+    env.reset()
+    stream = torch.cuda.current_stream()
+    logits = torch.empty((n, 10), dtype=torch.float32, device="cuda")
+    action = torch.full((n,), 4, dtype=torch.uint8, device="cuda")
+    grad = torch.zeros(2403961, dtype=torch.float32, device="cuda")
+    pending = [None]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def cycle(t):
+        env.step(robot_action=action)
+        pol.forward(env, logits, action)
+        if world > 1 and t % 25 == 24:
+            if pending[0] is not None:
+                pending[0].wait()
+            pending[0] = dist.all_reduce(grad, async_op=True)
+
+    for t in range(warmup):
+        cycle(t)
+    barrier()
+    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    l0 = env.launches + pol.launches
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record(stream)
+    for t in range(steps):
+        cycle(t)
+    if pending[0] is not None:
+        pending[0].wait()
+    ev1.record(stream)
+    barrier()
+    ms = ev0.elapsed_time(ev1)
+    launches = env.launches + pol.launches - l0
+    clocks = sampler.summary() if sampler else None
+
+    layers = [0.0] * 6
+    prof = 20
+    for _ in range(prof):
+        env.step(robot_action=action)
+        for i, v in enumerate(pol.forward_profiled(env, logits, action)):
+            layers[i] += v / prof
+
+    # end to end: every step the host supplies an exploration override (epsilon-greedy, rl_agents.py:50-57: 255 = keep the
+    # policy's action) from pinned memory and reads reward + done back
+    override = torch.full((n,), 255, dtype=torch.uint8).pin_memory()
+    override[::10] = 4
+    rew_h, done_h = torch.empty(n, dtype=torch.float32).pin_memory(), torch.empty(n, dtype=torch.uint8).pin_memory()
+    e2e_steps = max(steps // 4, 10)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        ov = override.to("cuda", non_blocking=True)
+        act = torch.where(ov == 255, action, ov)
+        _, reward, done, _ = env.step(robot_action=act)
+        pol.forward(env, logits, action)
+        rew_h.copy_(reward, non_blocking=True)
+        done_h.copy_(env.done, non_blocking=True)
+        torch.cuda.synchronize()
+    barrier()
+    e2e_s = time.perf_counter() - t0
+
+    t = torch.tensor([ms, e2e_s] + layers, dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, e2e_s = t[0].item(), t[1].item()
+    layers = [v.item() for v in t[2:]]
+    if rank == 0:
+        peaks, peak_kind = measured_peaks()
+        total = n * world
+        names = ("conv1", "conv2", "conv3", "dense1", "dense2", "out")
+        fwd_ms = sum(layers)
+        top = max(range(6), key=lambda i: layers[i])
+        achieved = 2 * LAYER_MACS[top] * n / (layers[top] * 1e-3) / 1e12
+        peak = peaks.get("bf16_tflops_sustained", peaks["bf16_tflops"])
+        emit(({
+            "metric": "labeled env-steps/sec (physics+render+label+CNN policy)", "value": total * steps / (ms * 1e-3), "unit": "env-steps/s",
+            "n_gpus": world, "steps": steps, "warmup": warmup, "ms_per_step": ms / steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": "configs[3]: %d envs/GPU policy-in-the-loop rollout: fused env step + CNN forward (models.py:20-65, random init), robot = argmax, human = programmed AI, episode_length 256%s"
+                                   % (n, ", 9.6 MB gradient all-reduce (synthetic buffer) every 25 steps" if world > 1 else ""),
+                       "envs_per_gpu": n, "total_envs": total, "mode": "rgb",
+                       "l2": "each step writes %.0f MB of frames and reads the 3-frame stack (%.0f MB) per GPU (> 126 MB L2)" % (n * 49152 / 1e6, n * 147456 / 1e6)},
+            "gpu_launches": launches, "clocks": clocks,
+            "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": None,
+                         "peak_kind": peak_kind + " cuBLAS bf16 sustained", "kernel": names[top] + " (tcgen05, Toeplitz form)" if top == 0 else names[top],
+                         "kernel_ms": layers[top], "flops_per_launch": 2 * LAYER_MACS[top] * n,
+                         "layer_ms": dict(zip(names, layers)),
+                         "forward": {"ms": fwd_ms, "tflops": n * FLOPS_PER_SAMPLE / (fwd_ms * 1e-3) / 1e12, "frac": n * FLOPS_PER_SAMPLE / (fwd_ms * 1e-3) / 1e12 / peak,
+                                     "input_GBs": n * 147456 / (fwd_ms * 1e-3) / 1e9, "frac_of_hbm": n * 147456 / (fwd_ms * 1e-3) / 1e9 / peaks["hbm_gbs"]},
+                         "note": "algorithmic flops (SURVEY.md 8d); the network sits below the bf16 ridge at uint8 input (139 FLOP/B), and conv1 (N = 5 outputs) executes 3.6x its algorithmic MACs in Toeplitz form"},
+            "e2e": {"value": total * e2e_steps / e2e_s, "unit": "env-steps/s", "h2d_bytes_per_step": n, "d2h_bytes_per_step": 5 * n,
+                    "note": "per step: exploration override (1 B/env) from pinned host memory, env step + CNN forward on the device, reward + done (5 B/env) back to pinned host memory, host waits"},
+        }))
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=2000)
     ap.add_argument("--warmup", type=int, default=50)
-    ap.add_argument("--envs-per-gpu", type=int, default=4096)
+    ap.add_argument("--envs-per-gpu", type=int, default=0)
+    ap.add_argument("--workload", default="datagen", choices=["datagen", "rollout"])
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    quiet_stdout()
     if args.impl == "reference":
         return run_reference(args)
+    if args.workload == "rollout":
+        return run_rollout(args)
+    args.envs_per_gpu = args.envs_per_gpu or 4096
 
     import numpy as np
     import torch
@@ -300,7 +452,7 @@ def main():
             threads = os.cpu_count() or 1
             v, sample = cpu_baseline(max(threads * 2, 32), args.cpu_seconds, threads)
             line["cpu_baseline"] = {"value": v, "unit": "env-steps/s", "cores": threads, "kind": "port", "sample": sample}
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 

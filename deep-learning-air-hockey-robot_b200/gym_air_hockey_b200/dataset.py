@@ -115,13 +115,17 @@ class _Writer(threading.Thread):
                 pass
 
 
-def generate(env, n_states, out_dir, states='f32', shard_states=0, when=None, keep_in_memory=False):
+def generate(env, n_states, out_dir, states='f32', shard_states=0, when=None, keep_in_memory=False,
+             label_random_as_undefined=False):
     """Run the data-generation loop on `env` (a BatchedAirHockeyEnv built with auto_reset=True, max_episode_steps=200)
     until at least n_states samples exist (whole steps: ceil(n_states / n_envs) * n_envs samples are produced and the
     surplus dropped), writing `states` / `robot_actions` / `human_actions`.
 
     states: 'f32' = the reference's normalised float32 stack (mode 'rgb') — or float64 gray-diff when env.processor.mode
     is 'gray-diff' (processor.py:53-64); 'u8' = the raw uint8 stack.  shard_states: samples per output file (0 = one file).
+    label_random_as_undefined: samples of `random` episodes (pure-noise frames, air_hockey_env.py:73-74,147-151; one reset
+    in twenty, :28) get label 9 = "Undefined" on both sides — the class the reference only obtains by mixing foreign
+    images into the data afterwards (mix_random_images_with_data.py:44-71).
     -> dict(files, samples, seconds, samples_per_s, bytes_to_host).  keep_in_memory also returns the arrays (tests)."""
     if states not in ('f32', 'u8'):
         raise ValueError("states must be 'f32' or 'u8'")
@@ -159,6 +163,10 @@ def generate(env, n_states, out_dir, states='f32', shard_states=0, when=None, ke
             # the stacked observation must be taken before the next step overwrites the oldest ring slot
             obs = env.observation(fmt)
             rl, hl = env.robot_label.clone(), env.human_label.clone()
+            if label_random_as_undefined:
+                noise = ((env.state[15] >> 16) & 3) == 2  # episode type in the meta word
+                rl[noise] = 9
+                hl[noise] = 9
             done_step = torch.cuda.Event()
             done_step.record(main)
             with torch.cuda.stream(copy_stream):

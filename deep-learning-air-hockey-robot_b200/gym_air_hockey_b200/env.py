@@ -48,6 +48,7 @@ class BatchedAirHockeyEnv(object):
     def __init__(self, n_envs, mode='rgb', device=0, seed=0, env_id_base=0, auto_reset=True, max_episode_steps=200,
                  table=None, obs='ring'):
         self.lib = _lib.load()
+        self._ptr_cache = {}
         if not torch.cuda.is_available():
             raise RuntimeError('BatchedAirHockeyEnv needs a CUDA device; there is no CPU fallback')
         self.processor = DataProcessor(mode=mode)
@@ -152,19 +153,32 @@ class BatchedAirHockeyEnv(object):
         """The same step for a caller on the CPU: numpy uint8 labels in (or None), numpy results out, one C call
         (ahk_step_host) that copies in, steps, copies out and waits.  `out` is a dict of preallocated (ideally
         pinned) arrays 'reward','done','robot_action','human_action'[,'frame'] reused across calls."""
-        n = self.n_envs
         if out is None:
             out = self.host_buffers(want_frame)
-        p = lambda a: a.ctypes.data_as(C.c_void_p) if a is not None else None
-        _lib.check(self.lib.ahk_step_host(self._h, p(robot_action), p(human_action), p(out['reward']), p(out['done']),
-                                          p(out['robot_action']), p(out['human_action']), p(out.get('frame'))))
+        p = self._host_ptr
+        rc = self.lib.ahk_step_host(self._h, p(robot_action), p(human_action), p(out['reward']), p(out['done']),
+                                    p(out['robot_action']), p(out['human_action']), p(out.get('frame')))
+        if rc:
+            _lib.check(rc)
         return out
+
+    def _host_ptr(self, a):
+        """Address of a host array, cached per array object: building a ctypes pointer costs more than the C call."""
+        if a is None:
+            return None
+        hit = self._ptr_cache.get(id(a))
+        if hit is None or hit[0] is not a:
+            if len(self._ptr_cache) > 64:
+                self._ptr_cache.clear()
+            hit = (a, a.ctypes.data)
+            self._ptr_cache[id(a)] = hit
+        return hit[1]
 
     def step_host_begin(self, robot_action=None, human_action=None, out=None):
         """Enqueue a host-buffer step without waiting (ahk_step_host_begin) -> ticket for step_host_wait.  For loops whose
         next actions do not depend on this step's results (generate_data.py:51: the AI plays both sides): up to 8 steps
         may be in flight, each with its own `out` buffers."""
-        p = lambda a: a.ctypes.data_as(C.c_void_p) if a is not None else None
+        p = self._host_ptr
         t = self.lib.ahk_step_host_begin(self._h, p(robot_action), p(human_action), p(out['reward']), p(out['done']),
                                          p(out['robot_action']), p(out['human_action']), p(out.get('frame')))
         if t < 0:
@@ -172,7 +186,9 @@ class BatchedAirHockeyEnv(object):
         return t
 
     def step_host_wait(self, ticket):
-        _lib.check(self.lib.ahk_step_host_wait(self._h, ticket))
+        rc = self.lib.ahk_step_host_wait(self._h, ticket)
+        if rc:
+            _lib.check(rc)
 
     def host_buffers(self, want_frame=False):
         """Pinned host arrays for step_host."""

@@ -48,6 +48,42 @@ def keras_default_init(seed=0, randomize_bn=False):
     return w
 
 
+def weights_from_keras(arrays):
+    """`model.get_weights()` of the reference's 'rgb' network (models.py:20-65) -> the dict PolicyNetwork takes.
+    Keras lists them layer by layer — Conv2D kernel, bias; BatchNormalization gamma, beta, moving_mean, moving_variance;
+    ... Dense kernel, bias — which is exactly the order of SHAPES (and of ahk_policy_weights).  Also accepts the
+    DDQN variant whose last layer was swapped for a linear Dense(10) (rl_agents.py:160-172): same shapes."""
+    arrays = list(arrays)
+    if len(arrays) != len(SHAPES):
+        raise ValueError('expected %d weight arrays (models.py rgb network), got %d' % (len(SHAPES), len(arrays)))
+    out = {}
+    for (name, shape), a in zip(SHAPES, arrays):
+        a = np.asarray(a, dtype=np.float32)
+        if a.shape != shape:
+            raise ValueError('%s: expected shape %s, got %s' % (name, shape, a.shape))
+        out[name] = a
+    return out
+
+
+def load_weights(path):
+    """Weights saved from the reference: an .npz written with np.savez(path, *model.get_weights()) (arr_0 .. arr_23) or
+    with the SHAPES names as keys.  (Keras .h5 files need h5py, which this image lacks; `save_weights_npz` below is the
+    three-line export a reference user runs once next to `model.save`, ai/supervised/keras/train.py:98-100.)"""
+    with np.load(path) as f:
+        if all(name in f.files for name, _ in SHAPES):
+            return weights_from_keras([f[name] for name, _ in SHAPES])
+        return weights_from_keras([f['arr_%d' % i] for i in range(len(SHAPES))])
+
+
+def save_weights_npz(path, weights):
+    np.savez(path, **{name: np.asarray(weights[name], dtype=np.float32) for name, _ in SHAPES})
+
+
+def softmax(logits):
+    """The supervised model's output layer (models.py:62-65) on top of the linear logits the engine returns."""
+    return torch.softmax(logits, dim=1)
+
+
 class PolicyNetwork(object):
     """forward(env) -> (logits float32[N,10], action uint8[N]) as CUDA tensors, on the current stream.
 

@@ -48,3 +48,34 @@ def test_generate_matches_stepping(cuda, table, tmp_path, states):
     assert np.array_equal(s, np.concatenate(want_s)[:total])
     assert np.array_equal(r, np.concatenate(want_r)[:total]) and np.array_equal(h, np.concatenate(want_h)[:total])
     assert set(np.unique(r)) <= set(range(9))   # label 9 never comes from the simulator
+
+
+@pytest.mark.gpu
+def test_random_episodes_labelled_undefined(cuda, table, tmp_path):
+    """N4: noise frames of `random` episodes carry label 9 when asked to; every other sample keeps its 0..8 label."""
+    from gym_air_hockey_b200 import BatchedAirHockeyEnv, dataset
+    n = 64
+    env = BatchedAirHockeyEnv(n, table=table, seed=5, max_episode_steps=20)
+    env.reset(episode=np.where(np.arange(n) % 4 == 0, 2, 0).astype(np.uint8))
+    out = dataset.generate(env, 3 * n, str(tmp_path), states='u8', keep_in_memory=True, label_random_as_undefined=True)
+    s, r, h = out['arrays']
+    first = r[:n]
+    assert (first[::4] == 9).all() and (np.delete(first, np.arange(0, n, 4)) < 9).all()
+    assert ((r == 9) == (h == 9)).all()
+
+
+def test_weights_from_keras_list():
+    """N3: model.get_weights() order == ahk_policy_weights order; shape errors are reported by name."""
+    from gym_air_hockey_b200.policy import SHAPES, keras_default_init, weights_from_keras, save_weights_npz, load_weights
+    w = keras_default_init(seed=1, randomize_bn=True)
+    got = weights_from_keras([w[name] for name, _ in SHAPES])
+    assert all(np.array_equal(got[k], w[k]) for k in w)
+    with pytest.raises(ValueError, match='conv2_w'):
+        weights_from_keras([w[name] if name != 'conv2_w' else w[name][:3] for name, _ in SHAPES])
+    import tempfile, os
+    with tempfile.TemporaryDirectory() as d:
+        save_weights_npz(os.path.join(d, 'm.npz'), w)
+        back = load_weights(os.path.join(d, 'm.npz'))
+        np.savez(os.path.join(d, 'l.npz'), *[w[name] for name, _ in SHAPES])
+        back2 = load_weights(os.path.join(d, 'l.npz'))
+    assert all(np.array_equal(back[k], w[k]) and np.array_equal(back2[k], w[k]) for k in w)

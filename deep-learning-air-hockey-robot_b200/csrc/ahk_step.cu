@@ -21,8 +21,8 @@
 // A pure write stream on this GPU peaks at 6.0-6.5 TB/s (tools/wprobe.cu, profiles/wprobe_r1b.json).  Measured
 // alternatives that lost: bulk-copying the table to each frame and overlaying the sprite vectors
 // afterwards (partial rewrites cost more DRAM time than they save SM time), bulk copies for runs of untouched units,
-// overlapping consecutive launches with programmatic dependent launch, a global ticket pool for the tail, spreading
-// the envs of a CTA one per warp, an even 148-way split of the envs.
+// a global ticket pool for the tail, spreading the envs of a CTA one per warp, an even 148-way split of the envs.
+// Consecutive step launches overlap by programmatic dependent launch.
 #include "ahk_env.cuh"
 
 namespace ahk {

@@ -640,6 +640,197 @@ cudaError_t launch_conv1(const Args &a, int grid, cudaStream_t s)
     return cudaGetLastError();
 }
 
+// ------------------------------------------------------------------------------------------------ conv2 / conv3, pipelined
+// The same GEMM tiles as layer_kernel, as a persistent warp-specialised pipeline (the layer_kernel form of these two
+// layers sat at 5-6 % tensor-pipe activity: every chunk was gathered, stored, barriered and multiplied in sequence):
+//   * the layer's whole B operand (conv2 8 KB, conv3 64 KB) is resident in shared memory, loaded once per CTA;
+//   * 4 producer warps gather A chunks with cp.async (16 bytes per row and K core, straight into the canonical layout,
+//     zero-fill past the last row), kDepth chunks in flight per thread and no register staging; a chunk is published
+//     (fence.proxy.async + mbarrier arrive) once this thread's copies of it have landed;
+//   * 1 warp issues the MMAs and recycles stages with tcgen05.commit; 4 warps run the epilogue out of a double-buffered
+//     TMEM accumulator while the next tile is being multiplied.
+namespace ws {
+constexpr int kProducers = 128, kCta = kProducers + 32 + 128;
+// A stages / chunks in flight per producer thread besides the one being issued.  conv2 (8 KB of weights, 2 chunks per
+// tile) runs three CTAs per SM with a short pipeline each, conv3 (64 KB of weights) one CTA with a deep one.
+template <int L> struct Cfg { static constexpr int kStages = 8, kDepth = 6, kPerSm = 1; };
+template <> struct Cfg<kConv2> { static constexpr int kStages = 4, kDepth = 2, kPerSm = 3; };
+// K-core pitch of the A stage: 16 bytes more than the 16 row groups, so that the 8 lanes that fetch one row's 8 K cores
+// (128 contiguous global bytes: one L1 wavefront instead of two half-used ones) land in 8 different bank groups
+constexpr int kLbo = 16 * 128 + 16, kStage = 8 * kLbo;
+template <int L> constexpr int smem_bytes() { return Cfg<L>::kStages * kStage + Traits<L>::K * Traits<L>::N * 2; }
+} // namespace ws
+
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void *src, uint32_t bytes)
+{
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;" :: "r"(dst), "l"(src), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" :: "n"(N) : "memory"); }
+
+template <int L>
+__global__ void __launch_bounds__(ws::kCta, ws::Cfg<L>::kPerSm) conv_ws_kernel(Args a)
+{
+    using namespace ws;
+    constexpr int kStages = Cfg<L>::kStages, kDepth = Cfg<L>::kDepth;
+    using T = Traits<L>;
+    constexpr int N = T::N, NCH = T::K / kBK;
+    constexpr int kBBytes = N * kBK * 2;
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint8_t *s_a = smem;                       // [kStages][kAStage]
+    uint8_t *s_b = smem + kStages * kStage;   // [NCH][kBBytes], resident
+    __shared__ __align__(8) uint64_t s_wfull, s_full[kStages], s_empty[kStages], s_tfull[2], s_tempty[2];
+    __shared__ uint32_t s_tmem;
+    __shared__ float s_bias[N];
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int n_tiles = (a.m_total + kBM - 1) / kBM;
+    const int my_tiles = static_cast<int>(blockIdx.x) < n_tiles ? (n_tiles - 1 - blockIdx.x) / gridDim.x + 1 : 0;
+    if (tid == 0) {
+        mbar_init(&s_wfull, 1);
+        for (int i = 0; i < kStages; ++i) { mbar_init(&s_full[i], kProducers); mbar_init(&s_empty[i], 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&s_tfull[i], 1); mbar_init(&s_tempty[i], 128); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (tid < N) s_bias[tid] = a.bias[tid];
+    if (warp == kProducers / 32) tmem_alloc(&s_tmem, 2 * (N < 32 ? 32 : N));
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = s_tmem;
+
+    if (tid < kProducers) {
+        // ---------------------------------------------------------------- producers
+        const int kc_lane = lane & 7, g = warp * 4 + (lane >> 3); // rows i * 16 + g, i = 0..7
+        const uint32_t dst0 = smem_u32(s_a) + kc_lane * kLbo + g * 16;
+        const int chunks = my_tiles * NCH;
+        int r0[8];
+        unsigned ok = 0u;
+        auto publish = [&](int c) {
+            fence_async_smem();
+            mbar_arrive(&s_full[c % kStages]);
+        };
+#pragma unroll 1
+        for (int c = 0; c < chunks; ++c) {
+            const int ch = c % NCH;
+            if (ch == 0) { // per-row constants of the new tile
+                const int tile = blockIdx.x + (c / NCH) * gridDim.x;
+                ok = 0u;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int row = tile * kBM + i * 16 + g;
+                    r0[i] = 0;
+                    if (row < a.m_total) {
+                        ok |= 1u << i;
+                        if (L == kConv2) {
+                            const int s = row / kP2, p = row - s * kP2, y = p / kC2, x = p - y * kC2;
+                            r0[i] = (s * kP1 + 2 * y * kC1 + 2 * x) * kAct1C;
+                        } else {
+                            const int s = row / kP3, p = row - s * kP3, y = p / kC3, x = p - y * kC3;
+                            r0[i] = (s * kP2 + 2 * y * kC2 + 2 * x) * 32;
+                        }
+                    }
+                }
+            }
+            const int st = c % kStages;
+            if (c >= kStages) mbar_wait(&s_empty[st], ((c / kStages) - 1) & 1);
+            const int kc = ch * 8 + kc_lane;
+            int off;
+            if (L == kConv2) off = ((kc >> 2) * kC1 + (kc & 3)) * kAct1C;
+            else { const int tap = kc >> 2; off = ((tap >> 2) * kC2 + (tap & 3)) * 32 + (kc & 3) * 8; }
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const bool v = (ok >> i) & 1u;
+                cp_async16(dst0 + st * kStage + i * 256, a.in + (v ? r0[i] + off : 0), v ? 16u : 0u);
+            }
+            cp_async_commit();
+            if (c >= kDepth) { cp_async_wait<kDepth>(); publish(c - kDepth); }
+        }
+        cp_async_wait<0>();
+        for (int c = chunks > kDepth ? chunks - kDepth : 0; c < chunks; ++c) publish(c);
+    } else if (warp == kProducers / 32) {
+        // ---------------------------------------------------------------- MMA issue (one thread)
+        if (lane == 0) {
+            mbar_expect_tx(&s_wfull, NCH * kBBytes);
+            for (int i = 0; i < NCH; ++i) bulk_load(s_b + i * kBBytes, reinterpret_cast<const uint8_t *>(a.weights) + i * kBBytes, kBBytes, &s_wfull);
+            mbar_wait(&s_wfull, 0);
+            constexpr uint32_t kIdesc = instr_desc(N);
+            const uint32_t b_base = smem_u32(s_b);
+            constexpr uint32_t kBufCols = N < 32 ? 32 : N;
+            int c = 0;
+            for (int t = 0; t < my_tiles; ++t) {
+                const uint32_t buf = t & 1;
+                if (t >= 2) mbar_wait(&s_tempty[buf], ((t >> 1) - 1) & 1);
+                tc_fence_after();
+                for (int ch = 0; ch < NCH; ++ch, ++c) {
+                    const int st = c % kStages;
+                    mbar_wait(&s_full[st], (c / kStages) & 1);
+                    tc_fence_after();
+                    const uint32_t a_base = smem_u32(s_a + st * kStage);
+#pragma unroll
+                    for (int j = 0; j < kBK / 16; ++j) {
+                        const uint64_t ad = smem_desc(a_base + j * 2 * kLbo, kLbo, 128);
+                        const uint64_t bd = smem_desc(b_base + ch * kBBytes + j * 2 * (N / 8 * 128), N / 8 * 128, 128);
+                        umma_bf16(tmem + buf * kBufCols, ad, bd, kIdesc, (ch | j) != 0);
+                    }
+                    umma_commit(&s_empty[st]);
+                }
+                umma_commit(&s_tfull[buf]);
+            }
+        }
+    } else {
+        // ---------------------------------------------------------------- epilogue: thread = TMEM lane = tile row
+        const int q4 = warp & 3;
+        constexpr uint32_t kBufCols = N < 32 ? 32 : N;
+        for (int t = 0; t < my_tiles; ++t) {
+            const int tile = blockIdx.x + t * gridDim.x;
+            const uint32_t buf = t & 1;
+            const int row = tile * kBM + q4 * 32 + lane;
+            mbar_wait(&s_tfull[buf], (t >> 1) & 1);
+            tc_fence_after();
+            const uint32_t taddr = tmem + buf * kBufCols + (static_cast<uint32_t>(q4 * 32) << 16);
+            uint32_t v[N];
+#pragma unroll
+            for (int c0 = 0; c0 < N; c0 += 16) tmem_load16_async(taddr + c0, *reinterpret_cast<uint32_t (*)[16]>(&v[c0]));
+            tmem_wait_ld();
+            tc_fence_before();
+            mbar_arrive(&s_tempty[buf]);
+            if (row < a.m_total) {
+                uint4 *out = reinterpret_cast<uint4 *>(a.out + static_cast<size_t>(row) * N);
+#pragma unroll
+                for (int c0 = 0; c0 < N; c0 += 8) {
+                    uint32_t pk[4];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const float lo = fmaxf(__uint_as_float(v[c0 + 2 * j]) + s_bias[c0 + 2 * j], 0.0f);
+                        const float hi = fmaxf(__uint_as_float(v[c0 + 2 * j + 1]) + s_bias[c0 + 2 * j + 1], 0.0f);
+                        const __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+                        pk[j] = *reinterpret_cast<const uint32_t *>(&h);
+                    }
+                    out[c0 / 8] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == kProducers / 32) tmem_dealloc(tmem, 2 * (N < 32 ? 32 : N));
+}
+
+template <int L>
+cudaError_t launch_ws(const Args &a, int tiles, int sms, cudaStream_t s)
+{
+    static int per_sm = 0;
+    if (per_sm == 0) {
+        cudaError_t e = cudaFuncSetAttribute(conv_ws_kernel<L>, cudaFuncAttributeMaxDynamicSharedMemorySize, ws::smem_bytes<L>());
+        if (e != cudaSuccess) return e;
+        per_sm = ws::Cfg<L>::kPerSm;
+    }
+    const int resident = sms * per_sm;
+    conv_ws_kernel<L><<<tiles < resident ? tiles : resident, ws::kCta, ws::smem_bytes<L>(), s>>>(a);
+    return cudaGetLastError();
+}
+
 // ------------------------------------------------------------------------------------------------ host: fold + pack
 uint16_t to_bf16(float f)
 { // round to nearest even
@@ -708,6 +899,7 @@ struct ahk_policy {
     uint16_t *w1t = nullptr; // conv1 in Toeplitz form (conv1_kernel)
     cudaEvent_t ev[7] = {};  // ahk_policy_forward_profiled: around each of the six layer kernels
     int sms = 148;
+    bool legacy_conv = false; // A/B switch AHK_CONV23=tile: conv2/conv3 through layer_kernel instead of conv_ws_kernel
     __nv_bfloat16 *act1 = nullptr, *act2 = nullptr, *act3 = nullptr, *h1 = nullptr, *h2 = nullptr;
     uint64_t launches = 0;
 };
@@ -768,6 +960,7 @@ int ahk_policy_create(int device, int max_batch, const ahk_policy_weights *w, ah
     p->device = device;
     p->max_batch = max_batch;
     cudaDeviceGetAttribute(&p->sms, cudaDevAttrMultiProcessorCount, device);
+    if (const char *sw = getenv("AHK_CONV23")) p->legacy_conv = strcmp(sw, "tile") == 0;
     int rc = AHK_OK;
 
     { // conv1: Keras kernel [ky][kx][c][o]; GEMM k = c*64 + ky*8 + kx; (x-128)/128 folded: W/128, b - sum(W)
@@ -877,10 +1070,10 @@ static int policy_forward(ahk_policy *p, const uint8_t *frames, int n, int head,
     }
     if (timed) POL_CUDA(cudaEventRecord(p->ev[1], s));
     a.in = p->act1; a.weights = reinterpret_cast<const uint4 *>(p->w[1]); a.bias = p->b[1]; a.out = p->act2; a.m_total = n * kP2;
-    POL_CUDA(launch<kConv2>(a, tiles(static_cast<long long>(n) * kP2), 1, p->sms, s));
+    POL_CUDA(p->legacy_conv ? launch<kConv2>(a, tiles(static_cast<long long>(n) * kP2), 1, p->sms, s) : launch_ws<kConv2>(a, tiles(static_cast<long long>(n) * kP2), p->sms, s));
     if (timed) POL_CUDA(cudaEventRecord(p->ev[2], s));
     a.in = p->act2; a.weights = reinterpret_cast<const uint4 *>(p->w[2]); a.bias = p->b[2]; a.out = p->act3; a.m_total = n * kP3;
-    POL_CUDA(launch<kConv3>(a, tiles(static_cast<long long>(n) * kP3), 1, p->sms, s));
+    POL_CUDA(p->legacy_conv ? launch<kConv3>(a, tiles(static_cast<long long>(n) * kP3), 1, p->sms, s) : launch_ws<kConv3>(a, tiles(static_cast<long long>(n) * kP3), p->sms, s));
     if (timed) POL_CUDA(cudaEventRecord(p->ev[3], s));
     a.in = p->act3; a.weights = reinterpret_cast<const uint4 *>(p->w[3]); a.bias = p->b[3]; a.out = p->h1; a.m_total = n;
     POL_CUDA(launch<kDense1>(a, tiles(n), 2, p->sms, s));

@@ -41,7 +41,12 @@ constexpr int kC2 = 19, kP2 = kC2 * kC2;
 constexpr int kC3 = 8, kP3 = kC3 * kC3;
 constexpr int kAct1C = 8;                // conv1 channels 5 padded to 8 (one 16-byte K core per tap for conv2)
 
-enum Layer { kConv1 = 0, kConv2, kConv3, kDense1, kDense2, kOut };
+enum Layer { kConv1 = 0, kConv2, kConv3, kDense1, kDense2, kOut,
+             kG1, kG2, kG3, kG4, kGDense1 }; // the 'gray-diff' network (models.py:67-116); its 'out' layer is kOut
+
+// ---- geometry of the 'gray-diff' network: (1,128,128) -> 16 k8 s4 (31x31) -> 24 k4 s2 (14x14) -> 32 k4 s1 (11x11)
+//      -> 48 k4 s1 (8x8) -> flatten 3072 -> dense 512 -> 10
+constexpr int kGS1 = 31, kGP1 = kGS1 * kGS1, kGS2 = 14, kGP2 = kGS2 * kGS2, kGS3 = 11, kGP3 = kGS3 * kGS3, kGS4 = 8, kGP4 = kGS4 * kGS4;
 
 template <int L> struct Traits;
 template <> struct Traits<kConv2> { static constexpr int N = 32, K = 128, NSplit = 1; };  // K = 16 taps x 8 (5 real)
@@ -49,6 +54,11 @@ template <> struct Traits<kConv3> { static constexpr int N = 64, K = 512, NSplit
 template <> struct Traits<kDense1> { static constexpr int N = 256, K = 4096, NSplit = 2; }; // 512 outputs in two halves
 template <> struct Traits<kDense2> { static constexpr int N = 256, K = 512, NSplit = 2; };
 template <> struct Traits<kOut> { static constexpr int N = 16, K = 512, NSplit = 1; };     // 10 real outputs
+template <> struct Traits<kG1> { static constexpr int N = 16, K = 64, NSplit = 1; };       // K = 8 rows x 8 pixels of the gray image
+template <> struct Traits<kG2> { static constexpr int N = 32, K = 256, NSplit = 1; };      // 24 real outputs; K = 16 taps x 16
+template <> struct Traits<kG3> { static constexpr int N = 32, K = 512, NSplit = 1; };      // K = 16 taps x 32 (24 real)
+template <> struct Traits<kG4> { static constexpr int N = 48, K = 512, NSplit = 1; };      // K = 16 taps x 32
+template <> struct Traits<kGDense1> { static constexpr int N = 256, K = 3072, NSplit = 2; }; // K = 64 pixels x 48
 
 struct Args {
     const uint8_t *frames;      // conv1: the ring [3][n][3][128][128]
@@ -183,6 +193,18 @@ __device__ __forceinline__ uint4 gather(const Args &a, bool row_ok, int r0, int 
         const int tap = kc >> 2, cb = kc & 3, ky = tap >> 2, kx = tap & 3;
         return __ldg(reinterpret_cast<const uint4 *>(a.in + r0 + (ky * kC2 + kx) * 32 + cb * 8));
     }
+    if (L == kG1) { // kc = ky ; r0 = element offset of gray[s][4Y][4X]: 8 pixels, 8-byte aligned only
+        const uint2 lo = __ldg(reinterpret_cast<const uint2 *>(a.in + r0 + kc * kDim)), hi = __ldg(reinterpret_cast<const uint2 *>(a.in + r0 + kc * kDim + 4));
+        return make_uint4(lo.x, lo.y, hi.x, hi.y);
+    }
+    if (L == kG2) { // kc = tap * 2 + half ; r0 = element offset of g1[s][2Y*31 + 2X][0]
+        const int tap = kc >> 1, ky = tap >> 2, kx = tap & 3;
+        return __ldg(reinterpret_cast<const uint4 *>(a.in + r0 + (ky * kGS1 + kx) * 16 + (kc & 1) * 8));
+    }
+    if (L == kG3 || L == kG4) { // kc = tap * 4 + channel block ; stride 1
+        const int tap = kc >> 2, ky = tap >> 2, kx = tap & 3;
+        return __ldg(reinterpret_cast<const uint4 *>(a.in + r0 + (ky * (L == kG3 ? kGS2 : kGS3) + kx) * 32 + (kc & 3) * 8));
+    }
     // dense: r0 = element offset of in[row][0]
     return __ldg(reinterpret_cast<const uint4 *>(a.in + r0 + kc * 8));
 }
@@ -202,7 +224,7 @@ __global__ void __launch_bounds__(kThreads) layer_kernel(Args a)
     using T = Traits<L>;
     constexpr int N = T::N, NCH = T::K / kBK;
     constexpr int kBBytes = N * kBK * 2;
-    constexpr uint32_t kTmemCols = N < 32 ? 32 : N;
+    constexpr uint32_t kTmemCols = N <= 32 ? 32 : (N <= 64 ? 64 : (N <= 128 ? 128 : 256));
 
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t *s_a = smem;                      // [2][kAStage]
@@ -253,6 +275,18 @@ __global__ void __launch_bounds__(kThreads) layer_kernel(Args a)
                 } else if (L == kConv3) {
                     const int s = row / kP3, p = row - s * kP3, y = p / kC3, x = p - y * kC3;
                     r0[i] = (s * kP2 + 2 * y * kC2 + 2 * x) * 32;
+                } else if (L == kG1) {
+                    const int s = row / kGP1, p = row - s * kGP1, y = p / kGS1, x = p - y * kGS1;
+                    r0[i] = s * (kDim * kDim) + 4 * y * kDim + 4 * x;
+                } else if (L == kG2) {
+                    const int s = row / kGP2, p = row - s * kGP2, y = p / kGS2, x = p - y * kGS2;
+                    r0[i] = (s * kGP1 + 2 * y * kGS1 + 2 * x) * 16;
+                } else if (L == kG3) {
+                    const int s = row / kGP3, p = row - s * kGP3, y = p / kGS3, x = p - y * kGS3;
+                    r0[i] = (s * kGP2 + y * kGS2 + x) * 32;
+                } else if (L == kG4) {
+                    const int s = row / kGP4, p = row - s * kGP4, y = p / kGS4, x = p - y * kGS4;
+                    r0[i] = (s * kGP3 + y * kGS3 + x) * 32;
                 } else {
                     r0[i] = row * T::K;
                 }
@@ -360,7 +394,7 @@ cudaError_t launch(const Args &a, int tiles, int grid_y, int sms, cudaStream_t s
         cudaError_t e = cudaFuncSetAttribute(layer_kernel<L>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<L>());
         if (e != cudaSuccess) return e;
         // resident CTAs per SM: shared memory (227 KB, + 1 KB reserved and ~1.3 KB static per CTA), tensor memory (512 columns)
-        constexpr int tmem_cols = Traits<L>::N < 32 ? 32 : Traits<L>::N;
+        constexpr int tmem_cols = Traits<L>::N <= 32 ? 32 : (Traits<L>::N <= 64 ? 64 : (Traits<L>::N <= 128 ? 128 : 256));
         per_sm = (227 * 1024) / (smem_bytes<L>() + 3 * 1024);
         if (per_sm > 512 / tmem_cols) per_sm = 512 / tmem_cols;
         if (per_sm > 8) per_sm = 8;
@@ -831,6 +865,46 @@ cudaError_t launch_ws(const Args &a, int tiles, int sms, cudaStream_t s)
     return cudaGetLastError();
 }
 
+// ------------------------------------------------------------------------------------------------ gray-diff input
+// DataProcessor's 'gray-diff' observation (processor.py:53-64) straight from the ring, as the network's bf16 input:
+// per colour the uint8 wrap-around double difference oldest - middle - newest, 0.2989 R + 0.5870 G + 0.1140 B,
+// (x - 128) / 128.  One thread per 16 pixels.
+__global__ void __launch_bounds__(256) gray_diff_kernel(const uint8_t *__restrict__ frames, __nv_bfloat16 *__restrict__ out, int n, int head)
+{
+    const size_t total = static_cast<size_t>(n) * 1024;
+    for (size_t idx = blockIdx.x * 256ull + threadIdx.x; idx < total; idx += gridDim.x * 256ull) {
+        const size_t env = idx >> 10, v = idx & 1023;
+        uint4 q[3][3]; // [age][colour]
+#pragma unroll
+        for (int age = 0; age < 3; ++age) {
+            const uint4 *f = reinterpret_cast<const uint4 *>(frames + (static_cast<size_t>((head + 3 - age) % 3) * n + env) * kFrameBytes);
+#pragma unroll
+            for (int c = 0; c < 3; ++c) q[age][c] = __ldg(f + c * 1024 + v);
+        }
+        uint32_t packed[8];
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
+            float g[4];
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+                float ch[3];
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    const uint32_t o = (&q[2][c].x)[w] >> (8 * b), m = (&q[1][c].x)[w] >> (8 * b), nw = (&q[0][c].x)[w] >> (8 * b);
+                    ch[c] = static_cast<float>((o - m - nw) & 0xFFu);
+                }
+                g[b] = (0.2989f * ch[0] + 0.5870f * ch[1] + 0.1140f * ch[2] - 128.0f) * (1.0f / 128.0f);
+            }
+            const __nv_bfloat162 lo = __floats2bfloat162_rn(g[0], g[1]), hi = __floats2bfloat162_rn(g[2], g[3]);
+            packed[2 * w] = *reinterpret_cast<const uint32_t *>(&lo);
+            packed[2 * w + 1] = *reinterpret_cast<const uint32_t *>(&hi);
+        }
+        uint4 *dst = reinterpret_cast<uint4 *>(out + (env * 1024 + v) * 16);
+        dst[0] = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+        dst[1] = make_uint4(packed[4], packed[5], packed[6], packed[7]);
+    }
+}
+
 // ------------------------------------------------------------------------------------------------ host: fold + pack
 uint16_t to_bf16(float f)
 { // round to nearest even
@@ -898,6 +972,11 @@ struct ahk_policy {
     float *b[6] = {};
     uint16_t *w1t = nullptr; // conv1 in Toeplitz form (conv1_kernel)
     cudaEvent_t ev[7] = {};  // ahk_policy_forward_profiled: around each of the six layer kernels
+    // the 'gray-diff' network (ahk_policy_gray_create): weights/biases of its six layers, input image and activations
+    bool gray = false;
+    uint16_t *gw[6] = {};
+    float *gb[6] = {};
+    __nv_bfloat16 *gimg = nullptr, *ga1 = nullptr, *ga2 = nullptr, *ga3 = nullptr, *ga4 = nullptr, *gh1 = nullptr;
     int sms = 148;
     bool legacy_conv = false; // A/B switch AHK_CONV23=tile: conv2/conv3 through layer_kernel instead of conv_ws_kernel
     __nv_bfloat16 *act1 = nullptr, *act2 = nullptr, *act3 = nullptr, *h1 = nullptr, *h2 = nullptr;
@@ -1040,6 +1119,92 @@ int ahk_policy_create(int device, int max_batch, const ahk_policy_weights *w, ah
     return AHK_OK;
 }
 
+int ahk_policy_gray_create(int device, int max_batch, const ahk_policy_gray_weights *w, ahk_policy **out)
+{
+    if (!w || !out || max_batch <= 0 || max_batch > 131072) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_gray_create: bad argument (max_batch must be in [1, 131072])");
+    const float *const *fields = reinterpret_cast<const float *const *>(w);
+    for (int i = 0; i < 28; ++i)
+        if (!fields[i]) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_gray_create: every weight pointer must be non-NULL");
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) return pfail(AHK_ERR_NO_DEVICE, "%s", "no CUDA device: the policy has no CPU fallback");
+    POL_CUDA(cudaSetDevice(device));
+    ahk_policy *p = new ahk_policy();
+    p->device = device;
+    p->max_batch = max_batch;
+    p->gray = true;
+    cudaDeviceGetAttribute(&p->sms, cudaDevAttrMultiProcessorCount, device);
+
+    // BatchNorm after the ReLU: y = s * r + t per channel, folded into the next layer
+    auto affine = [](const float *gamma, const float *beta, const float *mean, const float *var, int c, std::vector<float> &s, std::vector<float> &t) {
+        s.resize(c); t.resize(c);
+        for (int i = 0; i < c; ++i) { s[i] = gamma[i] / std::sqrt(var[i] + 1e-3f); t[i] = beta[i] - mean[i] * s[i]; }
+    };
+    // a 4x4 convolution as GEMM weights [16 taps x cin_pad][cout]: k = tap * cin_pad + c, previous BatchNorm folded in
+    auto conv4x4 = [](const float *kw, const float *kb, int cin, int cin_pad, int cout, int cout_pad, const std::vector<float> &s,
+                      const std::vector<float> &t, std::vector<float> &wf, std::vector<float> &bf) {
+        wf.assign(static_cast<size_t>(16) * cin_pad * cout, 0.0f);
+        bf.assign(cout_pad, 0.0f);
+        for (int o = 0; o < cout; ++o) {
+            double add = 0.0;
+            for (int tap = 0; tap < 16; ++tap) for (int c = 0; c < cin; ++c) {
+                const float v = kw[(tap * cin + c) * cout + o];
+                wf[(static_cast<size_t>(tap) * cin_pad + c) * cout + o] = v * s[c];
+                add += static_cast<double>(v) * t[c];
+            }
+            bf[o] = kb[o] + static_cast<float>(add);
+        }
+    };
+    std::vector<float> s1, t1, s2, t2, s3, t3, s4, t4, wf, bf;
+    affine(w->bn1_gamma, w->bn1_beta, w->bn1_mean, w->bn1_var, 16, s1, t1);
+    affine(w->bn2_gamma, w->bn2_beta, w->bn2_mean, w->bn2_var, 24, s2, t2);
+    affine(w->bn3_gamma, w->bn3_beta, w->bn3_mean, w->bn3_var, 32, s3, t3);
+    affine(w->bn4_gamma, w->bn4_beta, w->bn4_mean, w->bn4_var, 48, s4, t4);
+    int rc = AHK_OK;
+    { // conv1: Keras kernel [ky][kx][1][o] is already [k = ky*8 + kx][o]; the input arrives normalised
+        wf.assign(w->conv1_w, w->conv1_w + 64 * 16);
+        bf.assign(w->conv1_b, w->conv1_b + 16);
+        rc = upload(pack_b(wf, 64, 16, 16, 1), bf, &p->gw[0], &p->gb[0]);
+    }
+    if (rc == AHK_OK) { conv4x4(w->conv2_w, w->conv2_b, 16, 16, 24, 32, s1, t1, wf, bf); rc = upload(pack_b(wf, 256, 24, 32, 1), bf, &p->gw[1], &p->gb[1]); }
+    if (rc == AHK_OK) { conv4x4(w->conv3_w, w->conv3_b, 24, 32, 32, 32, s2, t2, wf, bf); rc = upload(pack_b(wf, 512, 32, 32, 1), bf, &p->gw[2], &p->gb[2]); }
+    if (rc == AHK_OK) { conv4x4(w->conv4_w, w->conv4_b, 32, 32, 48, 48, s3, t3, wf, bf); rc = upload(pack_b(wf, 512, 48, 48, 1), bf, &p->gw[3], &p->gb[3]); }
+    if (rc == AHK_OK) { // dense1: Keras flatten index f = c*64 + pixel; ours k = pixel*48 + c; BN4 folded
+        wf.assign(static_cast<size_t>(3072) * 512, 0.0f);
+        bf.assign(512, 0.0f);
+        std::vector<double> add(512, 0.0);
+        for (int c = 0; c < 48; ++c) for (int px = 0; px < 64; ++px) {
+            const float *src = w->dense1_w + static_cast<size_t>(c * 64 + px) * 512;
+            float *dst = wf.data() + static_cast<size_t>(px * 48 + c) * 512;
+            for (int o = 0; o < 512; ++o) { dst[o] = src[o] * s4[c]; add[o] += static_cast<double>(src[o]) * t4[c]; }
+        }
+        for (int o = 0; o < 512; ++o) bf[o] = w->dense1_b[o] + static_cast<float>(add[o]);
+        rc = upload(pack_b(wf, 3072, 512, 256, 2), bf, &p->gw[4], &p->gb[4]);
+    }
+    if (rc == AHK_OK) {
+        wf.assign(w->out_w, w->out_w + 512 * 10);
+        bf.assign(16, 0.0f);
+        for (int o = 0; o < 10; ++o) bf[o] = w->out_b[o];
+        rc = upload(pack_b(wf, 512, 10, 16, 1), bf, &p->gw[5], &p->gb[5]);
+    }
+    const size_t nb = static_cast<size_t>(max_batch);
+    cudaError_t err = cudaSuccess;
+    for (int i = 0; i < 7 && err == cudaSuccess; ++i) err = cudaEventCreate(&p->ev[i]);
+    if (rc == AHK_OK) {
+        if (err == cudaSuccess) err = cudaMalloc(&p->gimg, nb * ahk::kDim * ahk::kDim * 2 + 64); // + slack: the last row's 16-byte window
+        if (err == cudaSuccess) err = cudaMalloc(&p->ga1, nb * kGP1 * 16 * 2);
+        if (err == cudaSuccess) err = cudaMalloc(&p->ga2, nb * kGP2 * 32 * 2);
+        if (err == cudaSuccess) err = cudaMalloc(&p->ga3, nb * kGP3 * 32 * 2);
+        if (err == cudaSuccess) err = cudaMalloc(&p->ga4, nb * kGP4 * 48 * 2);
+        if (err == cudaSuccess) err = cudaMalloc(&p->gh1, nb * 512 * 2);
+    }
+    if (rc != AHK_OK || err != cudaSuccess) {
+        ahk_policy_destroy(p);
+        return rc != AHK_OK ? rc : pfail(AHK_ERR_CUDA, "ahk_policy_gray_create: %s", cudaGetErrorString(err));
+    }
+    *out = p;
+    return AHK_OK;
+}
+
 void ahk_policy_destroy(ahk_policy *p)
 {
     if (!p) return;
@@ -1047,6 +1212,8 @@ void ahk_policy_destroy(ahk_policy *p)
     for (int i = 0; i < 6; ++i) { if (p->w[i]) cudaFree(p->w[i]); if (p->b[i]) cudaFree(p->b[i]); }
     if (p->w1t) cudaFree(p->w1t);
     for (int i = 0; i < 7; ++i) if (p->ev[i]) cudaEventDestroy(p->ev[i]);
+    for (int i = 0; i < 6; ++i) { if (p->gw[i]) cudaFree(p->gw[i]); if (p->gb[i]) cudaFree(p->gb[i]); }
+    cudaFree(p->gimg); cudaFree(p->ga1); cudaFree(p->ga2); cudaFree(p->ga3); cudaFree(p->ga4); cudaFree(p->gh1);
     cudaFree(p->act1); cudaFree(p->act2); cudaFree(p->act3); cudaFree(p->h1); cudaFree(p->h2);
     delete p;
 }
@@ -1061,6 +1228,33 @@ static int policy_forward(ahk_policy *p, const uint8_t *frames, int n, int head,
     Args a{};
     a.n = n;
     a.head = head;
+    if (p->gray) { // the 'gray-diff' network: input image + six GEMM-tile layers
+        const long long ln = n;
+        if (timed) POL_CUDA(cudaEventRecord(p->ev[0], s));
+        const int blocks = static_cast<int>((ln * 1024 + 255) / 256);
+        gray_diff_kernel<<<blocks < p->sms * 16 ? blocks : p->sms * 16, 256, 0, s>>>(frames, p->gimg, n, head);
+        POL_CUDA(cudaGetLastError());
+        a.in = p->gimg; a.weights = reinterpret_cast<const uint4 *>(p->gw[0]); a.bias = p->gb[0]; a.out = p->ga1; a.m_total = n * kGP1;
+        POL_CUDA(launch<kG1>(a, tiles(ln * kGP1), 1, p->sms, s));
+        if (timed) POL_CUDA(cudaEventRecord(p->ev[1], s));
+        a.in = p->ga1; a.weights = reinterpret_cast<const uint4 *>(p->gw[1]); a.bias = p->gb[1]; a.out = p->ga2; a.m_total = n * kGP2;
+        POL_CUDA(launch<kG2>(a, tiles(ln * kGP2), 1, p->sms, s));
+        if (timed) POL_CUDA(cudaEventRecord(p->ev[2], s));
+        a.in = p->ga2; a.weights = reinterpret_cast<const uint4 *>(p->gw[2]); a.bias = p->gb[2]; a.out = p->ga3; a.m_total = n * kGP3;
+        POL_CUDA(launch<kG3>(a, tiles(ln * kGP3), 1, p->sms, s));
+        if (timed) POL_CUDA(cudaEventRecord(p->ev[3], s));
+        a.in = p->ga3; a.weights = reinterpret_cast<const uint4 *>(p->gw[3]); a.bias = p->gb[3]; a.out = p->ga4; a.m_total = n * kGP4;
+        POL_CUDA(launch<kG4>(a, tiles(ln * kGP4), 1, p->sms, s));
+        if (timed) POL_CUDA(cudaEventRecord(p->ev[4], s));
+        a.in = p->ga4; a.weights = reinterpret_cast<const uint4 *>(p->gw[4]); a.bias = p->gb[4]; a.out = p->gh1; a.m_total = n;
+        POL_CUDA(launch<kGDense1>(a, tiles(n), 2, p->sms, s));
+        if (timed) POL_CUDA(cudaEventRecord(p->ev[5], s));
+        a.in = p->gh1; a.weights = reinterpret_cast<const uint4 *>(p->gw[5]); a.bias = p->gb[5]; a.out = nullptr; a.logits = logits; a.action = action; a.m_total = n;
+        POL_CUDA(launch<kOut>(a, tiles(n), 1, p->sms, s));
+        if (timed) POL_CUDA(cudaEventRecord(p->ev[6], s));
+        p->launches += 7;
+        return AHK_OK;
+    }
     if (timed) POL_CUDA(cudaEventRecord(p->ev[0], s));
 
     a.frames = frames; a.weights = reinterpret_cast<const uint4 *>(p->w1t); a.bias = p->b[0]; a.out = p->act1; a.m_total = kP1;

@@ -33,6 +33,13 @@ class PolicyWeights(C.Structure):  # ahk_policy_weights
     _fields_ = [(name, C.c_void_p) for name in NAMES]
 
 
+class GrayPolicyWeights(C.Structure):  # ahk_policy_gray_weights
+    NAMES = tuple("%s%d_%s" % (k, i, f) if k == "bn" else "conv%d_%s" % (i, f)
+                  for i in (1, 2, 3, 4) for k, f in (("conv", "w"), ("conv", "b"), ("bn", "gamma"), ("bn", "beta"), ("bn", "mean"), ("bn", "var"))) + \
+        ("dense1_w", "dense1_b", "out_w", "out_b")
+    _fields_ = [(name, C.c_void_p) for name in NAMES]
+
+
 # every symbol include/ahk.h declares: name -> (restype, argtypes)
 _vp, _i = C.c_void_p, C.c_int
 SYMBOLS = {
@@ -57,6 +64,7 @@ SYMBOLS = {
     "ahk_last_error": (C.c_char_p, []),
     "ahk_version": (C.c_char_p, []),
     "ahk_policy_create": (_i, [_i, _i, C.POINTER(PolicyWeights), C.POINTER(_vp)]),
+    "ahk_policy_gray_create": (_i, [_i, _i, C.POINTER(GrayPolicyWeights), C.POINTER(_vp)]),
     "ahk_policy_destroy": (None, [_vp]),
     "ahk_policy_forward": (_i, [_vp, _vp, _i, _i, _vp, _vp, _vp]),
     "ahk_policy_forward_profiled": (_i, [_vp, _vp, _i, _i, _vp, _vp, _vp, C.POINTER(C.c_float)]),

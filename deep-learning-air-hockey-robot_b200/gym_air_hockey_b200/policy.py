@@ -26,12 +26,23 @@ FLOPS_PER_SAMPLE = 2 * 10227008
 LAYER_MACS = (4841280, 924160, 2097152, 2097152, 262144, 5120)
 
 
-def keras_default_init(seed=0, randomize_bn=False):
+# the 'gray-diff' network (models.py:67-116), in the order of ahk_policy_gray_weights == model.get_weights()
+GRAY_SHAPES = (
+    ("conv1_w", (8, 8, 1, 16)), ("conv1_b", (16,)), ("bn1_gamma", (16,)), ("bn1_beta", (16,)), ("bn1_mean", (16,)), ("bn1_var", (16,)),
+    ("conv2_w", (4, 4, 16, 24)), ("conv2_b", (24,)), ("bn2_gamma", (24,)), ("bn2_beta", (24,)), ("bn2_mean", (24,)), ("bn2_var", (24,)),
+    ("conv3_w", (4, 4, 24, 32)), ("conv3_b", (32,)), ("bn3_gamma", (32,)), ("bn3_beta", (32,)), ("bn3_mean", (32,)), ("bn3_var", (32,)),
+    ("conv4_w", (4, 4, 32, 48)), ("conv4_b", (48,)), ("bn4_gamma", (48,)), ("bn4_beta", (48,)), ("bn4_mean", (48,)), ("bn4_var", (48,)),
+    ("dense1_w", (3072, 512)), ("dense1_b", (512,)), ("out_w", (512, 10)), ("out_b", (10,)),
+)
+GRAY_FLOPS_PER_SAMPLE = 2 * 6825984
+
+
+def keras_default_init(seed=0, randomize_bn=False, shapes=None):
     """Random-init weights the way Keras builds models.py:20-65: Glorot-uniform kernels, zero biases, BatchNorm
     gamma 1 / beta 0 / mean 0 / variance 1.  randomize_bn=True draws non-trivial BatchNorm statistics instead (tests)."""
     rs = np.random.RandomState(seed)
     w = {}
-    for name, shape in SHAPES:
+    for name, shape in (shapes or SHAPES):
         if name.endswith("_w"):
             receptive = int(np.prod(shape[:-2])) if len(shape) == 4 else 1
             fan_in, fan_out = receptive * shape[-2], receptive * shape[-1]
@@ -90,23 +101,29 @@ class PolicyNetwork(object):
     logits are pre-softmax (the DDQN head of rl_agents.py:160-172 is linear; softmax(logits) is the supervised
     model's output, models.py:62-65), action = argmax — what keras/test.py:42-43 feeds back into env.step."""
 
-    def __init__(self, weights=None, max_batch=4096, device=0):
+    def __init__(self, weights=None, max_batch=4096, device=0, mode='rgb'):
+        """mode: 'rgb' (models.py:20-65) or 'gray-diff' (models.py:67-116) — ai/config.py:1-3."""
         self.lib = _lib.load()
         if not torch.cuda.is_available():
             raise RuntimeError('PolicyNetwork needs a CUDA device; there is no CPU fallback')
+        if mode not in ('rgb', 'gray-diff'):
+            raise ValueError('Processing mode is not supported')
+        self.mode = mode
+        shapes = SHAPES if mode == 'rgb' else GRAY_SHAPES
         self.device = torch.device('cuda', device)
         self.max_batch = int(max_batch)
-        weights = keras_default_init() if weights is None else weights
+        weights = keras_default_init(shapes=shapes) if weights is None else weights
         self.weights = {}
-        st = _lib.PolicyWeights()
-        for name, shape in SHAPES:
+        st = _lib.PolicyWeights() if mode == 'rgb' else _lib.GrayPolicyWeights()
+        for name, shape in shapes:
             a = np.ascontiguousarray(weights[name], dtype=np.float32)
             if a.shape != shape:
                 raise ValueError('%s: expected shape %s, got %s' % (name, shape, a.shape))
             self.weights[name] = a  # keeps the host memory alive during ahk_policy_create
             setattr(st, name, a.ctypes.data_as(C.c_void_p))
         h = C.c_void_p()
-        _lib.check(self.lib.ahk_policy_create(self.device.index, self.max_batch, C.byref(st), C.byref(h)))
+        create = self.lib.ahk_policy_create if mode == 'rgb' else self.lib.ahk_policy_gray_create
+        _lib.check(create(self.device.index, self.max_batch, C.byref(st), C.byref(h)))
         self._h = h
         self.launches = 0
 

@@ -162,6 +162,21 @@ int ahk_policy_forward(ahk_policy *p, const uint8_t *frames_dev, int n, int head
 int ahk_policy_forward_profiled(ahk_policy *p, const uint8_t *frames_dev, int n, int head, float *logits_dev,
                                 uint8_t *action_dev, void *stream, float *layer_ms);
 
+/* ---- the 'gray-diff' network (ai/supervised/keras/models.py:67-116; ai/config.py:3 lists the mode) ----
+ * (1,128,128) gray-diff observation (processor.py:53-64, computed from the ring by the engine) -> conv 16 k8 s4 ->
+ * conv 24 k4 s2 -> conv 32 k4 s1 -> conv 48 k4 s1 (each ReLU then BatchNorm) -> flatten 3072 -> dense 512 -> dense 10.
+ * Same handle type and the same ahk_policy_forward / _forward_profiled / _destroy calls as the 'rgb' network
+ * (layer_ms = input + conv1, conv2, conv3, conv4, dense1, out). */
+typedef struct {
+    const float *conv1_w, *conv1_b, *bn1_gamma, *bn1_beta, *bn1_mean, *bn1_var; /* 8x8x1x16  */
+    const float *conv2_w, *conv2_b, *bn2_gamma, *bn2_beta, *bn2_mean, *bn2_var; /* 4x4x16x24 */
+    const float *conv3_w, *conv3_b, *bn3_gamma, *bn3_beta, *bn3_mean, *bn3_var; /* 4x4x24x32 */
+    const float *conv4_w, *conv4_b, *bn4_gamma, *bn4_beta, *bn4_mean, *bn4_var; /* 4x4x32x48 */
+    const float *dense1_w, *dense1_b; /* 3072x512 */
+    const float *out_w, *out_b;       /* 512x10   */
+} ahk_policy_gray_weights; /* host pointers, Keras layouts */
+int ahk_policy_gray_create(int device, int max_batch, const ahk_policy_gray_weights *w, ahk_policy **out);
+
 #ifdef __cplusplus
 }
 #endif

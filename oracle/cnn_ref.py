@@ -71,3 +71,52 @@ def forward(w, obs_u8, emulate_bf16=False):
     x = q(F.relu((x @ q(_t(d1)) + _t(bd1)).float().double()))
     x = q(F.relu((x @ q(_t(w['dense2_w'])) + _t(w['dense2_b'])).float().double()))
     return (x @ q(_t(w['out_w'])) + _t(w['out_b'])).float().numpy()
+
+
+def gray_diff_input(obs_u8):
+    """DataProcessor's 'gray-diff' observation (processor.py:53-64) of a uint8 [n, 9, 128, 128] stack (newest first):
+    uint8 wrap-around oldest - middle - newest per colour, 0.2989 R + 0.5870 G + 0.1140 B, (x - 128) / 128.
+    float64 [n, 1, 128, 128], as the reference returns it."""
+    o = np.ascontiguousarray(obs_u8, dtype=np.uint8)
+    diff = o[:, 6:9] - o[:, 3:6] - o[:, 0:3]  # uint8 arithmetic wraps
+    gray = 0.2989 * diff[:, 0] + 0.5870 * diff[:, 1] + 0.1140 * diff[:, 2]
+    return ((gray - 128.0) / 128.0)[:, None]
+
+
+def forward_gray(w, obs_u8, emulate_bf16=False):
+    """The 'gray-diff' network (models.py:67-116; same Keras defaults as above): conv 16 k8 s4 -> 24 k4 s2 -> 32 k4 s1
+    -> 48 k4 s1 (ReLU then BatchNorm each) -> flatten (C,H,W) 3072 -> dense 512 ReLU -> dense 10.  obs_u8: the uint8
+    stack; w: gym_air_hockey_b200.policy.GRAY_SHAPES arrays.  float32 logits [n, 10]."""
+    x = torch.from_numpy(gray_diff_input(obs_u8))
+    strides = (4, 2, 1, 1)
+    if not emulate_bf16:
+        x = x.float()
+        for i, st in enumerate(strides, start=1):
+            k = torch.from_numpy(np.ascontiguousarray(w['conv%d_w' % i].transpose(3, 2, 0, 1)))
+            x = F.relu(F.conv2d(x, k, torch.from_numpy(w['conv%d_b' % i]), stride=st))
+            s = torch.from_numpy(w['bn%d_gamma' % i] / np.sqrt(w['bn%d_var' % i] + np.float32(EPS)))
+            t = torch.from_numpy(w['bn%d_beta' % i]) - torch.from_numpy(w['bn%d_mean' % i]) * s
+            x = x * s.view(1, -1, 1, 1) + t.view(1, -1, 1, 1)
+        x = x.reshape(x.shape[0], -1)
+        x = F.relu(x @ torch.from_numpy(w['dense1_w']) + torch.from_numpy(w['dense1_b']))
+        return (x @ torch.from_numpy(w['out_w']) + torch.from_numpy(w['out_b'])).numpy()
+
+    # the engine's algebra: bf16 input image, each BatchNorm folded into the next layer, bf16 weights and activations
+    q = lambda t: t.float().bfloat16().double()
+    x = q(x.float())  # the input image is computed in float32 and stored as bfloat16
+    s_prev = t_prev = None
+    for i, st in enumerate(strides, start=1):
+        k = w['conv%d_w' % i].astype(np.float32)
+        b = w['conv%d_b' % i].astype(np.float32)
+        if s_prev is not None:
+            b = (b + (k.astype(np.float64) * t_prev.reshape(1, 1, -1, 1)).sum(axis=(0, 1, 2)).astype(np.float32)).astype(np.float32)
+            k = (k * s_prev.reshape(1, 1, -1, 1)).astype(np.float32)
+        x = q(F.relu(F.conv2d(x, q(_t(k.transpose(3, 2, 0, 1))), _t(b), stride=st).float().double()))
+        s_prev = (w['bn%d_gamma' % i] / np.sqrt(w['bn%d_var' % i] + np.float32(EPS))).astype(np.float32)
+        t_prev = (w['bn%d_beta' % i] - w['bn%d_mean' % i] * s_prev).astype(np.float32)
+    sf, tf = np.repeat(s_prev, 64), np.repeat(t_prev, 64)  # flatten index c*64 + pixel
+    d1 = (w['dense1_w'] * sf[:, None]).astype(np.float32)
+    bd1 = (w['dense1_b'] + (w['dense1_w'].astype(np.float64) * tf[:, None]).sum(axis=0).astype(np.float32)).astype(np.float32)
+    x = x.reshape(x.shape[0], -1)
+    x = q(F.relu((x @ q(_t(d1)) + _t(bd1)).float().double()))
+    return (x @ q(_t(w['out_w'])) + _t(w['out_b'])).float().numpy()

@@ -32,6 +32,7 @@ def test_struct_layouts_match_header():
     assert C.sizeof(_lib.Config) == 48            # int32 x2, uint64, uint32, int32 x2, int32 x5 (+ padding to 8)
     assert C.sizeof(_lib.Buffers) == 9 * 8
     assert C.sizeof(_lib.PolicyWeights) == 24 * 8
+    assert C.sizeof(_lib.GrayPolicyWeights) == 28 * 8
 
 
 def test_no_cpu_fallback():

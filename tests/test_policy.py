@@ -82,3 +82,56 @@ def test_policy_in_the_loop(cuda, table):
         _, reward, done, info = env.step(action, None)
         assert cuda.equal(info['robot_action'], cuda.where(action == 9, cuda.full_like(action, 4), action))  # label 9 -> stand -> 4
     assert env.statistics()['steps'] == 20 * n
+
+
+def test_gray_diff_restatement_matches_reference_processor():
+    """CPU: the gray-diff input of the restatement is what the reference's own DataProcessor returns (golden fixture
+    recorded from processor.py:53-64), and the network has the shapes models.py:67-116 implies."""
+    import cnn_ref
+    from conftest import golden
+    from gym_air_hockey_b200.policy import GRAY_SHAPES, GRAY_FLOPS_PER_SAMPLE, keras_default_init
+    g = golden("wrapper_gray_diff.npz")
+    w = keras_default_init(seed=2, randomize_bn=True, shapes=GRAY_SHAPES)
+    assert GRAY_FLOPS_PER_SAMPLE == 13651968
+    obs = np.random.RandomState(1).randint(0, 256, size=(2, 9, 128, 128)).astype(np.uint8)
+    x = cnn_ref.gray_diff_input(obs)
+    assert x.dtype == np.float64 and x.shape == (2, 1, 128, 128)
+    d = (obs[0, 6:9].astype(np.int64) - obs[0, 3:6] - obs[0, 0:3]) % 256
+    assert np.allclose(x[0, 0], ((0.2989 * d[0] + 0.5870 * d[1] + 0.1140 * d[2]) - 128.0) / 128.0, atol=1e-12)
+    a = cnn_ref.forward_gray(w, obs)
+    b = cnn_ref.forward_gray(w, obs, emulate_bf16=True)
+    assert a.shape == (2, 10) and np.abs(a - b).max() <= 3e-2 * np.abs(a).max()
+    assert len(g.files) > 0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,source", [(1, "noise"), (130, "game")])
+def test_gray_policy_forward_matches_reference(cuda, table, n, source):
+    """The 'gray-diff' network (models.py:67-116) on the ring, against the float32 restatement; same tolerances."""
+    import cnn_ref
+    from gym_air_hockey_b200 import BatchedAirHockeyEnv
+    from gym_air_hockey_b200.policy import GRAY_SHAPES, PolicyNetwork, keras_default_init
+    torch = cuda
+    w = keras_default_init(seed=6, randomize_bn=True, shapes=GRAY_SHAPES)
+    net = PolicyNetwork(w, max_batch=256, mode='gray-diff')
+    if source == "game":
+        env = BatchedAirHockeyEnv(n, table=table, seed=3, max_episode_steps=50)
+        env.reset()
+        for _ in range(5):
+            env.step()
+        frames, head = env.frames, env.head
+    else:
+        frames = torch.from_numpy(np.random.RandomState(n).randint(0, 256, size=(3, n, 3, 128, 128)).astype(np.uint8)).cuda()
+        head = 2
+    logits, action = net.forward_ring(frames, head)
+    torch.cuda.synchronize()
+    logits, action = logits.cpu().numpy(), action.cpu().numpy()
+    fr = frames.cpu().numpy()
+    obs = np.concatenate([fr[(head + 3 - age) % 3] for age in range(3)], axis=1)
+    ref32 = cnn_ref.forward_gray(w, obs)
+    ref16 = cnn_ref.forward_gray(w, obs, emulate_bf16=True)
+    scale = max(np.abs(ref32).max(), 1e-6)
+    assert np.isfinite(logits).all()
+    assert np.abs(logits - ref16).max() <= 6e-3 * scale, np.abs(logits - ref16).max() / scale
+    assert np.abs(logits - ref32).max() <= 3e-2 * scale, np.abs(logits - ref32).max() / scale
+    assert np.array_equal(action, logits.argmax(axis=1))

@@ -1,0 +1,24 @@
+"""Dataset writer throughput: python tools/dataset_bench.py [--envs 2048] [--states 40960] [--dir /tmp/ahk_ds]"""
+import argparse, json, os, shutil, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "deep-learning-air-hockey-robot_b200"))
+from gym_air_hockey_b200 import BatchedAirHockeyEnv, dataset  # noqa: E402
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--envs", type=int, default=2048)
+ap.add_argument("--states", type=int, default=40960)
+ap.add_argument("--dir", default="/tmp/ahk_ds")
+args = ap.parse_args()
+res = {}
+for fmt in ("u8", "f32"):
+    shutil.rmtree(args.dir, ignore_errors=True)
+    env = BatchedAirHockeyEnv(args.envs, seed=0, max_episode_steps=200)
+    env.reset()
+    n = args.states if fmt == "u8" else args.states // 4
+    out = dataset.generate(env, n, args.dir, states=fmt, shard_states=8192 if fmt == "u8" else 2048, label_random_as_undefined=True)
+    size = sum(os.path.getsize(f) for f in out["files"])
+    res[fmt] = {"samples": out["samples"], "seconds": out["seconds"], "samples_per_s": out["samples_per_s"],
+                "host_GBs": out["bytes_to_host"] / out["seconds"] / 1e9, "files": len(out["files"]), "file_bytes": size}
+    env.close()
+shutil.rmtree(args.dir, ignore_errors=True)
+print(json.dumps({"envs": args.envs, "results": res}))

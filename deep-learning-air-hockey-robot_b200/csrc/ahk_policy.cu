@@ -1001,9 +1001,9 @@ int pfail(int code, const char *fmt, const char *detail)
 
 int upload(const std::vector<uint16_t> &w, const std::vector<float> &b, uint16_t **wd, float **bd)
 {
-    POL_CUDA(cudaMalloc(wd, w.size() * 2));
+    if (!*wd) POL_CUDA(cudaMalloc(wd, w.size() * 2)); // ahk_policy_set_weights overwrites the same buffers (same sizes)
     POL_CUDA(cudaMemcpy(*wd, w.data(), w.size() * 2, cudaMemcpyHostToDevice));
-    POL_CUDA(cudaMalloc(bd, b.size() * 4));
+    if (!*bd) POL_CUDA(cudaMalloc(bd, b.size() * 4));
     POL_CUDA(cudaMemcpy(*bd, b.data(), b.size() * 4, cudaMemcpyHostToDevice));
     return AHK_OK;
 }
@@ -1012,16 +1012,9 @@ int upload(const std::vector<uint16_t> &w, const std::vector<float> &b, uint16_t
 
 extern "C" {
 
-int ahk_policy_create(int device, int max_batch, const ahk_policy_weights *w, ahk_policy **out)
+// Folds and packs the 'rgb' network's Keras weights and uploads them (allocating on first use).
+static int load_rgb_weights(ahk_policy *p, const ahk_policy_weights *w)
 {
-    if (!w || !out || max_batch <= 0 || max_batch > 131072) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_create: bad argument (max_batch must be in [1, 131072])");
-    const float *const *fields = reinterpret_cast<const float *const *>(w);
-    for (int i = 0; i < 24; ++i)
-        if (!fields[i]) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_create: every weight pointer must be non-NULL");
-    int count = 0;
-    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) return pfail(AHK_ERR_NO_DEVICE, "%s", "no CUDA device: the policy has no CPU fallback");
-    POL_CUDA(cudaSetDevice(device));
-
     // BatchNorm after the ReLU is the affine map y = s * r + t per channel (eps = 1e-3, Keras default)
     auto affine = [](const float *gamma, const float *beta, const float *mean, const float *var, int c, std::vector<float> &s, std::vector<float> &t) {
         s.resize(c); t.resize(c);
@@ -1035,11 +1028,6 @@ int ahk_policy_create(int device, int max_batch, const ahk_policy_weights *w, ah
     affine(w->bn2_gamma, w->bn2_beta, w->bn2_mean, w->bn2_var, 32, s2, t2);
     affine(w->bn3_gamma, w->bn3_beta, w->bn3_mean, w->bn3_var, 64, s3, t3);
 
-    ahk_policy *p = new ahk_policy();
-    p->device = device;
-    p->max_batch = max_batch;
-    cudaDeviceGetAttribute(&p->sms, cudaDevAttrMultiProcessorCount, device);
-    if (const char *sw = getenv("AHK_CONV23")) p->legacy_conv = strcmp(sw, "tile") == 0;
     int rc = AHK_OK;
 
     { // conv1: Keras kernel [ky][kx][c][o]; GEMM k = c*64 + ky*8 + kx; (x-128)/128 folded: W/128, b - sum(W)
@@ -1101,6 +1089,24 @@ int ahk_policy_create(int device, int max_batch, const ahk_policy_weights *w, ah
         for (int o = 0; o < 10; ++o) bf[o] = w->out_b[o];
         rc = upload(pack_b(wf, 512, 10, 16, 1), bf, &p->w[5], &p->b[5]);
     }
+    return rc;
+}
+
+int ahk_policy_create(int device, int max_batch, const ahk_policy_weights *w, ahk_policy **out)
+{
+    if (!w || !out || max_batch <= 0 || max_batch > 131072) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_create: bad argument (max_batch must be in [1, 131072])");
+    const float *const *fields = reinterpret_cast<const float *const *>(w);
+    for (int i = 0; i < 24; ++i)
+        if (!fields[i]) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_create: every weight pointer must be non-NULL");
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) return pfail(AHK_ERR_NO_DEVICE, "%s", "no CUDA device: the policy has no CPU fallback");
+    POL_CUDA(cudaSetDevice(device));
+    ahk_policy *p = new ahk_policy();
+    p->device = device;
+    p->max_batch = max_batch;
+    cudaDeviceGetAttribute(&p->sms, cudaDevAttrMultiProcessorCount, device);
+    if (const char *sw = getenv("AHK_CONV23")) p->legacy_conv = strcmp(sw, "tile") == 0;
+    int rc = load_rgb_weights(p, w);
     const size_t nb = static_cast<size_t>(max_batch);
     cudaError_t err = cudaSuccess;
     for (int i = 0; i < 7 && err == cudaSuccess; ++i) err = cudaEventCreate(&p->ev[i]);
@@ -1117,6 +1123,18 @@ int ahk_policy_create(int device, int max_batch, const ahk_policy_weights *w, ah
     }
     *out = p;
     return AHK_OK;
+}
+
+int ahk_policy_set_weights(ahk_policy *p, const ahk_policy_weights *w)
+{
+    if (!p || !w) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_set_weights: NULL argument");
+    if (p->gray) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_set_weights: handle holds the 'gray-diff' network");
+    const float *const *fields = reinterpret_cast<const float *const *>(w);
+    for (int i = 0; i < 24; ++i)
+        if (!fields[i]) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_set_weights: every weight pointer must be non-NULL");
+    POL_CUDA(cudaSetDevice(p->device));
+    POL_CUDA(cudaDeviceSynchronize()); // forward passes in flight still read the old weights
+    return load_rgb_weights(p, w);
 }
 
 int ahk_policy_gray_create(int device, int max_batch, const ahk_policy_gray_weights *w, ahk_policy **out)

@@ -162,6 +162,38 @@ int ahk_policy_forward(ahk_policy *p, const uint8_t *frames_dev, int n, int head
 int ahk_policy_forward_profiled(ahk_policy *p, const uint8_t *frames_dev, int n, int head, float *logits_dev,
                                 uint8_t *action_dev, void *stream, float *layer_ms);
 
+/* Replace the weights of an 'rgb' policy handle in place (same folding and packing as ahk_policy_create): ≙
+ * model.set_weights / the weights after model.fit (rl_agents.py:100-104,189) — the trainer pushes the updated network to
+ * the forward kernels every training interval.  Waits for the device first (forward passes in flight read the old ones). */
+int ahk_policy_set_weights(ahk_policy *p, const ahk_policy_weights *w);
+
+/* ---- batched RL step: ai/reinforcement/rl_agents.py around the CNN, on the device ----
+ * Replay memory ≙ Agent.experience_buffer (rl_agents.py:61-62,88-90), kept as a time-ordered store of single uint8
+ * frames, store_dev [capacity][n][3][128][128] (slot = step index mod capacity; the newest ring slot of every env is
+ * copied in after each step), instead of two float32 (9,128,128) stacks per transition.
+ * ≙ Agent._sample_experiences (rl_agents.py:64-77): for sample b, frames t-2, t-1, t, t+1 (t = t_dev[b], slots mod
+ * capacity) of env env_dev[b] -> out_dev [4][batch][3][128][128].  out_dev[0:3] with head 2 is the stacked state s_t and
+ * out_dev + batch*AHK_FRAME_BYTES (slots 1..3) with head 2 is s_{t+1}: both go to ahk_policy_forward as they are. */
+int ahk_replay_gather(const uint8_t *store_dev, int capacity, int n, const int32_t *t_dev, const int32_t *env_dev, int batch,
+                      uint8_t *out_dev, void *stream);
+/* ≙ DDQNAgent.train (rl_agents.py:177-191), all float[n][10]: q = Q(s), q_next_online = Q(s'), q_next_target =
+ * Q_target(s').  targets = q with targets[a] = reward + (1 - done) * discount * q_next_target[argmax q_next_online],
+ * clipped to [-1, 1].  Also the Keras mean_squared_error loss of q_fit against targets (loss_dev, one float) and its
+ * gradient dlogits = 2 (q_fit - targets) / (10 n); q_fit = output of the forward pass being fitted, NULL = q.
+ * targets_dev / dlogits_dev / loss_dev may be NULL. */
+int ahk_rl_ddqn_targets(const float *q_dev, const float *q_next_online_dev, const float *q_next_target_dev, const uint8_t *action_dev,
+                        const float *reward_dev, const uint8_t *done_dev, int n, float discount, const float *q_fit_dev,
+                        float *targets_dev, float *dlogits_dev, float *loss_dev, void *stream);
+/* ≙ PGAgent.train::discount_rewards (rl_agents.py:257-268) for n envs at once: reward_dev/done_dev/returns_dev are
+ * [steps][n]; per episode (a run of steps of one env ending at done != 0 or at the last step) G[t] = r[t] + discount *
+ * G[t+1], then standardised by the episode's own mean and population std (zeros when the std is 0), in float64. */
+int ahk_rl_pg_returns(const float *reward_dev, const uint8_t *done_dev, int steps, int n, float discount, float *returns_dev, void *stream);
+/* ≙ PGAgent.store_experience + train (rl_agents.py:246-253,270-274) for m = steps*n samples: prob_dev float[m][10] = the
+ * softmax output at act() time, targets = prob + learning_rate * (onehot(action) - prob) * returns; plus the categorical
+ * cross-entropy (models.py:119) of prob_fit (NULL = prob) against targets and its gradient w.r.t. the logits. */
+int ahk_rl_pg_targets(const float *prob_dev, const uint8_t *action_dev, const float *returns_dev, int m, float learning_rate,
+                      const float *prob_fit_dev, float *targets_dev, float *dlogits_dev, float *loss_dev, void *stream);
+
 /* ---- the 'gray-diff' network (ai/supervised/keras/models.py:67-116; ai/config.py:3 lists the mode) ----
  * (1,128,128) gray-diff observation (processor.py:53-64, computed from the ring by the engine) -> conv 16 k8 s4 ->
  * conv 24 k4 s2 -> conv 32 k4 s1 -> conv 48 k4 s1 (each ReLU then BatchNorm) -> flatten 3072 -> dense 512 -> dense 10.

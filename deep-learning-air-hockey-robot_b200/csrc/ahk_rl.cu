@@ -44,7 +44,7 @@ __global__ void __launch_bounds__(256) replay_gather_kernel(const uint4 *__restr
 __global__ void __launch_bounds__(256) ddqn_targets_kernel(const float *__restrict__ q, const float *__restrict__ qn_online,
                                                            const float *__restrict__ qn_target, const uint8_t *__restrict__ action,
                                                            const float *__restrict__ reward, const uint8_t *__restrict__ done, int n,
-                                                           float discount, const float *__restrict__ q_fit,
+                                                           double discount, const float *__restrict__ q_fit,
                                                            float *__restrict__ targets, float *__restrict__ dlogits,
                                                            float *__restrict__ loss)
 {
@@ -58,7 +58,7 @@ __global__ void __launch_bounds__(256) ddqn_targets_kernel(const float *__restri
 #pragma unroll
         for (int k = 1; k < AHK_N_ACTIONS; ++k) if (on[k] > on[best]) best = k;
         const double y = static_cast<double>(reward[i]) +
-                         static_cast<double>(1 - (done[i] ? 1 : 0)) * static_cast<double>(discount) * static_cast<double>(qn_target[i * AHK_N_ACTIONS + best]);
+                         static_cast<double>(1 - (done[i] ? 1 : 0)) * discount * static_cast<double>(qn_target[i * AHK_N_ACTIONS + best]);
         const int a = action[i] < AHK_N_ACTIONS ? action[i] : 0;
         const float scale = 2.0f / (static_cast<float>(n) * AHK_N_ACTIONS);
 #pragma unroll
@@ -200,7 +200,7 @@ int ahk_replay_gather(const uint8_t *store_dev, int capacity, int n, const int32
 }
 
 int ahk_rl_ddqn_targets(const float *q_dev, const float *q_next_online_dev, const float *q_next_target_dev, const uint8_t *action_dev,
-                        const float *reward_dev, const uint8_t *done_dev, int n, float discount, const float *q_fit_dev,
+                        const float *reward_dev, const uint8_t *done_dev, int n, double discount, const float *q_fit_dev,
                         float *targets_dev, float *dlogits_dev, float *loss_dev, void *stream)
 {
     if (!q_dev || !q_next_online_dev || !q_next_target_dev || !action_dev || !reward_dev || !done_dev || n <= 0)
@@ -212,11 +212,11 @@ int ahk_rl_ddqn_targets(const float *q_dev, const float *q_next_online_dev, cons
     return launched("ahk_rl_ddqn_targets");
 }
 
-int ahk_rl_pg_returns(const float *reward_dev, const uint8_t *done_dev, int steps, int n, float discount, float *returns_dev, void *stream)
+int ahk_rl_pg_returns(const float *reward_dev, const uint8_t *done_dev, int steps, int n, double discount, float *returns_dev, void *stream)
 {
     if (!reward_dev || !done_dev || !returns_dev || steps <= 0 || n <= 0) return rfail(AHK_ERR_ARG, "ahk_rl_pg_returns: bad argument");
     pg_returns_kernel<<<(n + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(reward_dev, done_dev, steps, n,
-                                                                                    static_cast<double>(discount), returns_dev);
+                                                                                    discount, returns_dev);
     return launched("ahk_rl_pg_returns");
 }
 

@@ -1,0 +1,408 @@
+"""Batched RL step: ai/reinforcement/rl_agents.py + train.py:44-118 for N environments on a GPU.
+
+What runs where
+* acting (`Agent.act`, rl_agents.py:92-101) and the three Q evaluations of `DDQNAgent.train` (rl_agents.py:179-181):
+  the tcgen05 forward kernels on uint8 frames (`PolicyNetwork`, csrc/ahk_policy.cu);
+* replay memory (`experience_buffer`, rl_agents.py:61-62,88-90) and sampling (rl_agents.py:64-77): `ReplayStore`, a
+  time-ordered uint8 frame store in HBM + `ahk_replay_gather` (csrc/ahk_rl.cu);
+* targets, loss and the gradient at the network output (rl_agents.py:183-187, 246-253, 257-274): `ahk_rl_ddqn_targets`,
+  `ahk_rl_pg_returns`, `ahk_rl_pg_targets` (csrc/ahk_rl.cu);
+* the backward pass and the optimizer step of `model.fit` (rl_agents.py:189, 276): **PyTorch autograd over
+  `TrainableNetwork`** (cuDNN/cuBLAS — library code, not hand-written kernels; DESIGN.md §7 says so), gradients summed
+  over ranks with `parallel.GradientBucket` (NCCL), `KerasSGD` restating the compiled optimizer (rl_agents.py:111,170);
+* after every fit the new weights (and BatchNorm moving statistics) go back to the forward kernels with
+  `ahk_policy_set_weights`.
+"""
+import ctypes as C
+
+import numpy as np
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from . import _lib
+from .parallel import GradientBucket
+from .policy import SHAPES, PolicyNetwork, keras_default_init
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else None
+
+
+def _stream(device):
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+# ---------------------------------------------------------------------------------------------- the network, trainable
+class TrainableNetwork(nn.Module):
+    """models.py:20-65 as a torch module for autograd: Conv2D(+ReLU) -> BatchNormalization(axis=1) x3, Flatten (C,H,W),
+    Dense 512 ReLU x2, Dense 10 (linear: logits; softmax on top is the supervised / PG output, models.py:62-65).
+    BatchNorm with the Keras defaults: epsilon 1e-3, momentum 0.99 (torch counts the other way: 0.01); in training mode it
+    normalises with batch statistics, as `model.fit` does."""
+
+    def __init__(self, weights=None):
+        super().__init__()
+        self.conv1, self.bn1 = nn.Conv2d(9, 5, 8, stride=3), nn.BatchNorm2d(5, eps=1e-3, momentum=0.01)
+        self.conv2, self.bn2 = nn.Conv2d(5, 32, 4, stride=2), nn.BatchNorm2d(32, eps=1e-3, momentum=0.01)
+        self.conv3, self.bn3 = nn.Conv2d(32, 64, 4, stride=2), nn.BatchNorm2d(64, eps=1e-3, momentum=0.01)
+        self.dense1, self.dense2, self.out = nn.Linear(4096, 512), nn.Linear(512, 512), nn.Linear(512, 10)
+        self.load_keras(keras_default_init() if weights is None else weights)
+
+    def forward(self, obs_u8):
+        """obs_u8: uint8 [B, 9, 128, 128], newest frame first (processor.py:47-49) -> logits float32 [B, 10]."""
+        x = (obs_u8.float() - 128.0) / 128.0  # processor.py:39-42
+        x = self.bn1(F.relu(self.conv1(x)))
+        x = self.bn2(F.relu(self.conv2(x)))
+        x = self.bn3(F.relu(self.conv3(x)))
+        x = x.flatten(1)
+        x = F.relu(self.dense1(x))
+        x = F.relu(self.dense2(x))
+        return self.out(x)
+
+    def load_keras(self, w):
+        """w: dict in Keras layouts (policy.SHAPES), i.e. model.get_weights() by name."""
+        with torch.no_grad():
+            for i in (1, 2, 3):
+                conv, bn = getattr(self, 'conv%d' % i), getattr(self, 'bn%d' % i)
+                conv.weight.copy_(torch.from_numpy(np.ascontiguousarray(np.asarray(w['conv%d_w' % i], dtype=np.float32).transpose(3, 2, 0, 1))))
+                conv.bias.copy_(torch.from_numpy(np.asarray(w['conv%d_b' % i], dtype=np.float32)))
+                bn.weight.copy_(torch.from_numpy(np.asarray(w['bn%d_gamma' % i], dtype=np.float32)))
+                bn.bias.copy_(torch.from_numpy(np.asarray(w['bn%d_beta' % i], dtype=np.float32)))
+                bn.running_mean.copy_(torch.from_numpy(np.asarray(w['bn%d_mean' % i], dtype=np.float32)))
+                bn.running_var.copy_(torch.from_numpy(np.asarray(w['bn%d_var' % i], dtype=np.float32)))
+            for name in ('dense1', 'dense2', 'out'):
+                lin = getattr(self, name)
+                lin.weight.copy_(torch.from_numpy(np.ascontiguousarray(np.asarray(w[name + '_w'], dtype=np.float32).T)))
+                lin.bias.copy_(torch.from_numpy(np.asarray(w[name + '_b'], dtype=np.float32)))
+
+    def keras_weights(self):
+        """-> dict of float32 numpy arrays in Keras layouts (what model.get_weights() would list; policy.SHAPES)."""
+        w = {}
+        with torch.no_grad():
+            for i in (1, 2, 3):
+                conv, bn = getattr(self, 'conv%d' % i), getattr(self, 'bn%d' % i)
+                w['conv%d_w' % i] = conv.weight.permute(2, 3, 1, 0).contiguous().cpu().numpy()
+                w['conv%d_b' % i] = conv.bias.cpu().numpy().copy()
+                w['bn%d_gamma' % i], w['bn%d_beta' % i] = bn.weight.cpu().numpy().copy(), bn.bias.cpu().numpy().copy()
+                w['bn%d_mean' % i], w['bn%d_var' % i] = bn.running_mean.cpu().numpy().copy(), bn.running_var.cpu().numpy().copy()
+            for name in ('dense1', 'dense2', 'out'):
+                lin = getattr(self, name)
+                w[name + '_w'] = lin.weight.t().contiguous().cpu().numpy()
+                w[name + '_b'] = lin.bias.cpu().numpy().copy()
+        return {name: np.ascontiguousarray(w[name], dtype=np.float32) for name, _ in SHAPES}
+
+
+class KerasSGD(object):
+    """keras.optimizers.SGD(lr, momentum, decay, clipnorm) as compiled at rl_agents.py:111,170 (Keras 2.x semantics):
+    gradients scaled by clipnorm / max(global L2 norm, clipnorm); lr_t = lr / (1 + decay * iterations);
+    v = momentum * v - lr_t * g; p += v."""
+
+    def __init__(self, params, lr=0.0075, momentum=0.5, decay=1e-6, clipnorm=2.0):
+        self.params = [p for p in params if p.requires_grad]
+        self.lr, self.momentum, self.decay, self.clipnorm = lr, momentum, decay, clipnorm
+        self.iterations = 0
+        self.velocity = [torch.zeros_like(p) for p in self.params]
+
+    @torch.no_grad()
+    def step(self):
+        grads = [p.grad if p.grad is not None else torch.zeros_like(p) for p in self.params]
+        if self.clipnorm and self.clipnorm > 0:
+            norm = torch.sqrt(sum((g.double() ** 2).sum() for g in grads)).float()
+            scale = torch.where(norm >= self.clipnorm, self.clipnorm / norm, torch.ones_like(norm))  # K.clip_norm
+            grads = [g * scale for g in grads]
+        lr_t = self.lr * (1.0 / (1.0 + self.decay * self.iterations))
+        for p, v, g in zip(self.params, self.velocity, grads):
+            v.mul_(self.momentum).sub_(g, alpha=lr_t)
+            p.add_(v)
+        self.iterations += 1
+
+
+# ---------------------------------------------------------------------------------------------- replay memory
+def valid_transitions(pending, cursor, filled, need_next=True):
+    """Which (slot, env) pairs of a ReplayStore can be sampled.  pending: uint8 [capacity, n], 1 where the env was armed
+    for an auto-reset after that step (so the NEXT step rewrote all three ring slots with warm-up frames,
+    air_hockey_env.py:69-72).  A transition at slot t uses frames t-2..t+1 (state = t, t-1, t-2; next state = t+1, t,
+    t-1): all four must be recorded, consecutive, and no reset may fall on steps t-1, t, t+1 (pending at t-2, t-1, t).
+    `cursor` = slot the next step will be written to, `filled` = recorded steps (<= capacity).  Returns bool [capacity, n]."""
+    cap = pending.shape[0]
+    age = (cursor - 1 - torch.arange(cap, device=pending.device)) % cap  # 0 = newest recorded slot
+    lo = 1 if need_next else 0                                              # t+1 must exist
+    ok_t = (age >= lo) & (age <= filled - 3)                                # t-2 must exist
+    clear = pending == 0
+    ok = clear.roll(2, 0) & clear.roll(1, 0)                                # steps t-1, t were not resets
+    if need_next:
+        ok = ok & clear                                                     # step t+1 was not a reset
+    return ok & ok_t[:, None]
+
+
+class ReplayStore(object):
+    """≙ Agent.experience_buffer (rl_agents.py:61-62,88-90): `capacity` steps of all n envs.  Frames are kept once, as
+    uint8 (49 152 B per env-step); the reference keeps two float32 (9,128,128) stacks per transition (1.18 MB)."""
+
+    def __init__(self, env, capacity):
+        if capacity < 4:
+            raise ValueError('capacity must be at least 4 steps')
+        self.lib = _lib.load()
+        self.n, self.capacity, self.device = env.n_envs, int(capacity), env.device
+        n, dev = self.n, self.device
+        self.frames = torch.zeros((self.capacity, n, 3, 128, 128), dtype=torch.uint8, device=dev)
+        self.action = torch.zeros((self.capacity, n), dtype=torch.uint8, device=dev)
+        self.reward = torch.zeros((self.capacity, n), dtype=torch.float32, device=dev)
+        self.done = torch.zeros((self.capacity, n), dtype=torch.uint8, device=dev)
+        self.pending = torch.zeros((self.capacity, n), dtype=torch.uint8, device=dev)
+        self.cursor, self.filled = 0, 0
+
+    def reset(self):
+        """≙ Agent._reset_experience_buffer (rl_agents.py:61-62)."""
+        self.cursor, self.filled = 0, 0
+
+    def record_observation(self, env):
+        """Store the newest frame of every env with no transition attached (the observation an episode starts from)."""
+        self._put(env, None, None, None)
+
+    def record(self, env, action, reward, done):
+        """≙ Agent.store_experience (rl_agents.py:88-90) after env.step(action): the frame the step produced, the action
+        that led to it, its reward and terminal flag.  (state, next_state) are implied by the neighbouring slots."""
+        self._put(env, action, reward, done)
+
+    def _put(self, env, action, reward, done):
+        t = self.cursor
+        self.frames[t].copy_(env.frames[env.head])  # 49 152 B per env, device to device
+        if action is None:
+            self.action[t].zero_(); self.reward[t].zero_(); self.done[t].zero_()
+        else:
+            self.action[t].copy_(action)
+            self.reward[t].copy_(reward)
+            self.done[t].copy_(done.view(torch.uint8) if done.dtype == torch.bool else done)
+        self.pending[t].copy_((env.state[15] >> 21) & 1)  # auto-reset armed: the next step starts a new episode
+        self.cursor = (t + 1) % self.capacity
+        self.filled = min(self.filled + 1, self.capacity)
+
+    def gather(self, t_idx, env_idx):
+        """-> uint8 [4, B, 3, 128, 128]: frames t-2, t-1, t, t+1 of each sampled env (ahk_replay_gather)."""
+        b = int(t_idx.numel())
+        out = torch.empty((4, b, 3, 128, 128), dtype=torch.uint8, device=self.device)
+        t32, e32 = t_idx.to(torch.int32).contiguous(), env_idx.to(torch.int32).contiguous()
+        _lib.check(self.lib.ahk_replay_gather(_ptr(self.frames), self.capacity, self.n, _ptr(t32), _ptr(e32), b, _ptr(out),
+                                              _stream(self.device)))
+        return out
+
+    def sample(self, batch_size, generator=None, need_next=True):
+        """≙ Agent._sample_experiences (rl_agents.py:64-77): up to batch_size distinct transitions, uniformly.
+        -> dict(frames [4,B,...], action = the action taken in s_t, reward, done of s_t -> s_{t+1}, t, env) or None."""
+        ok = valid_transitions(self.pending, self.cursor, self.filled, need_next)
+        flat = ok.reshape(-1).nonzero().squeeze(1)
+        if flat.numel() == 0:
+            return None
+        k = min(int(batch_size), int(flat.numel()))
+        pick = flat[torch.randperm(flat.numel(), device=self.device, generator=generator)[:k]]
+        t_idx, env_idx = pick // self.n, pick % self.n
+        nxt = (t_idx + 1) % self.capacity
+        return {'frames': self.gather(t_idx, env_idx), 't': t_idx, 'env': env_idx,
+                'action': self.action[nxt, env_idx].contiguous(), 'reward': self.reward[nxt, env_idx].contiguous(),
+                'done': self.done[nxt, env_idx].contiguous()}
+
+
+def stacked(frames3):
+    """uint8 [3, B, 3, 128, 128] oldest..newest -> the (9,128,128) stack per sample, newest first (processor.py:47-49)."""
+    return torch.cat((frames3[2], frames3[1], frames3[0]), dim=1)
+
+
+# ---------------------------------------------------------------------------------------------- agents
+class Agent(object):
+    """≙ rl_agents.Agent (rl_agents.py:19-127) for n envs at once.  `act` is ε-greedy per env with the reference's linear
+    schedule (rl_agents.py:48-56); `iteration` counts calls, as there."""
+
+    def __init__(self, env, weights=None, buffer_steps=64, batch_size=128, discount_rate=0.99, eps_min=0.0, eps_max=0.9,
+                 eps_decay_steps=1000, seed=0, group=None):
+        self.lib = _lib.load()
+        self.env, self.device, self.n = env, env.device, env.n_envs
+        self.n_actions = env.n_actions
+        self.batch_size, self.discount_rate = int(batch_size), float(discount_rate)
+        self.eps_min, self.eps_max, self.eps_decay_steps = eps_min, eps_max, eps_decay_steps
+        self.iteration = 0
+        self.group = group
+        self.model = TrainableNetwork(weights).to(self.device)
+        self.policy = PolicyNetwork(self.model.keras_weights(), max_batch=max(self.n, self.batch_size), device=self.device.index)
+        self.replay = ReplayStore(env, buffer_steps)
+        self.bucket = GradientBucket(self.model.parameters())
+        self.gen = torch.Generator(device=self.device)
+        self.gen.manual_seed(int(seed))
+        self.action_distribution = torch.zeros(self.n_actions, dtype=torch.int64, device=self.device)
+        self.loss_buffer = []
+        self.logits = torch.zeros((self.n, 10), dtype=torch.float32, device=self.device)
+        self.greedy = torch.zeros(self.n, dtype=torch.uint8, device=self.device)
+
+    def epsilon(self):
+        return max(self.eps_min, self.eps_max - (self.eps_max - self.eps_min) * self.iteration / self.eps_decay_steps)
+
+    def act(self):
+        """≙ Agent.act (rl_agents.py:92-101) on the env's current ring: forward kernels, then ε-greedy per env."""
+        self.iteration += 1
+        self.policy.forward(self.env, self.logits, self.greedy)
+        eps = self.epsilon()
+        explore = torch.rand(self.n, device=self.device, generator=self.gen) < eps
+        rand = torch.randint(0, self.n_actions, (self.n,), device=self.device, generator=self.gen, dtype=torch.int64).to(torch.uint8)
+        action = torch.where(explore, rand, self.greedy)
+        self.action_distribution += torch.bincount(action.long(), minlength=self.n_actions)
+        return action
+
+    def push_weights(self, policy=None):
+        """The fitted network -> the forward kernels (ahk_policy_set_weights)."""
+        policy = policy or self.policy
+        w = self.model.keras_weights()
+        st = _lib.PolicyWeights()
+        for name, _ in SHAPES:
+            setattr(st, name, w[name].ctypes.data_as(C.c_void_p))
+        _lib.check(self.lib.ahk_policy_set_weights(policy._h, C.byref(st)))
+        policy.weights = w
+
+    def _fit(self, obs_u8, backward_from):
+        """One `model.fit` batch (rl_agents.py:189,276): training-mode forward, `backward_from(logits) -> (dlogits, loss)`,
+        backward, gradient all-reduce over ranks, optimizer step, weights pushed to the forward kernels."""
+        self.model.train()
+        for p in self.model.parameters():
+            p.grad = None
+        logits = self.model(obs_u8)
+        dlogits, loss = backward_from(logits.detach())
+        logits.backward(dlogits)
+        self.bucket.all_reduce(group=self.group)
+        self.optimizer.step()
+        self.model.eval()
+        self.push_weights()
+        return loss
+
+
+class DDQNAgent(Agent):
+    """≙ rl_agents.DDQNAgent (rl_agents.py:129-197): linear Dense(10) head, mean-squared error, SGD(lr 0.0075,
+    momentum 0.5, decay 1e-6, clipnorm 2); target network = a second set of forward-kernel weights."""
+
+    def __init__(self, env, weights=None, replace_softmax=True, **kw):
+        if replace_softmax:  # rl_agents.py:160-172: a freshly initialised linear output layer (Glorot uniform, zero bias)
+            weights = dict(keras_default_init() if weights is None else weights)
+            fresh = keras_default_init(seed=kw.get('seed', 0) + 1)
+            weights['out_w'], weights['out_b'] = fresh['out_w'], fresh['out_b']
+        super().__init__(env, weights, **kw)
+        self.optimizer = KerasSGD(self.model.parameters())
+        self.target_policy = PolicyNetwork(self.model.keras_weights(), max_batch=self.batch_size, device=self.device.index)
+        self.use_target = False
+
+    def store_experience(self, action, reward, done):
+        self.replay.record(self.env, action, reward, done)
+
+    def update_target_weights(self):
+        """≙ Agent.update_target_weights (rl_agents.py:103-107)."""
+        self.push_weights(self.target_policy)
+        self.use_target = True
+
+    def train(self):
+        """≙ DDQNAgent.train (rl_agents.py:177-191).  -> loss (float) or None if nothing can be sampled yet."""
+        batch = self.replay.sample(self.batch_size, self.gen)
+        if batch is None:
+            return None
+        g, b = batch['frames'], int(batch['t'].numel())
+        q = self.policy.forward_ring(g[0:3], 2)[0]
+        q_next = self.policy.forward_ring(g[1:4], 2)[0]
+        q_next_target = (self.target_policy if self.use_target else self.policy).forward_ring(g[1:4], 2)[0]
+        targets = torch.empty_like(q)
+        loss = torch.zeros(1, dtype=torch.float32, device=self.device)
+
+        def backward_from(q_fit):
+            d = torch.empty_like(q_fit)
+            _lib.check(self.lib.ahk_rl_ddqn_targets(_ptr(q), _ptr(q_next), _ptr(q_next_target), _ptr(batch['action']),
+                                                    _ptr(batch['reward']), _ptr(batch['done']), b, self.discount_rate,
+                                                    _ptr(q_fit), _ptr(targets), _ptr(d), _ptr(loss), _stream(self.device)))
+            return d, loss
+
+        self._fit(stacked(g[0:3]), backward_from)
+        self.targets = targets
+        self.loss_buffer.append(float(loss.item()))
+        return self.loss_buffer[-1]
+
+
+class PGAgent(Agent):
+    """≙ rl_agents.PGAgent (rl_agents.py:199-286): softmax output, categorical cross-entropy against
+    prediction + learning_rate * (onehot - prediction) * standardised discounted return; the pretrained model keeps its
+    compiled optimizer, Adam with the Keras defaults (models.py:119)."""
+
+    def __init__(self, env, weights=None, learning_rate=0.01, episode_length=256, fit_batch=32, **kw):
+        kw.setdefault('buffer_steps', episode_length + 3)
+        super().__init__(env, weights, **kw)
+        self.learning_rate, self.episode_length, self.fit_batch = float(learning_rate), int(episode_length), int(fit_batch)
+        self.optimizer = torch.optim.Adam(self.model.parameters(), lr=1e-3, betas=(0.9, 0.999), eps=1e-7)
+        self.prob = torch.zeros((self.replay.capacity, self.n, 10), dtype=torch.float32, device=self.device)
+
+    def act(self):
+        action = super().act()
+        self._prediction = torch.softmax(self.logits, dim=1)  # self.prediction, rl_agents.py:99
+        return action
+
+    def store_experience(self, action, reward, done):
+        """≙ PGAgent.store_experience (rl_agents.py:246-253); the prediction of the state the action was taken in is
+        filed with the step's slot."""
+        self.prob[self.replay.cursor].copy_(self._prediction)
+        self.replay.record(self.env, action, reward, done)
+
+    def train(self):
+        """≙ PGAgent.train (rl_agents.py:255-282) over everything recorded since the last call; -> mean loss."""
+        rp = self.replay
+        steps = rp.filled
+        if steps < 4:
+            return None
+        order = (rp.cursor - steps + torch.arange(steps, device=self.device)) % rp.capacity  # slots, oldest first
+        # rewards of steps 1..steps-1 (slot 0 is the observation the rollout started from); an episode also ends where the
+        # engine armed an auto-reset without a goal (max_episode_steps ≙ train.py:86 `episode_step < episode_length`)
+        reward = rp.reward[order[1:]].contiguous()
+        ends = (rp.done[order[1:]] | rp.pending[order[1:]]).contiguous()
+        returns = torch.empty_like(reward)
+        _lib.check(self.lib.ahk_rl_pg_returns(_ptr(reward), _ptr(ends), steps - 1, self.n, self.discount_rate, _ptr(returns),
+                                              _stream(self.device)))
+        # sample (k, e): the action of step k was taken in the state whose newest frame sits one slot earlier
+        ok = valid_transitions(rp.pending, rp.cursor, rp.filled, need_next=True)[order]
+        k_idx, e_idx = ok[:-1].nonzero(as_tuple=True)  # state slot = order[k]; its action/reward/prob are at order[k+1]
+        perm = torch.randperm(k_idx.numel(), device=self.device, generator=self.gen)  # fit(shuffle=True)
+        losses = []
+        for lo in range(0, int(perm.numel()), self.fit_batch):
+            sel = perm[lo:lo + self.fit_batch]
+            k, e = k_idx[sel], e_idx[sel]
+            g = rp.gather(order[k], e)
+            prob = self.prob[order[k + 1], e].contiguous()
+            act = rp.action[order[k + 1], e].contiguous()
+            ret = returns[k, e].contiguous()  # returns[k] belongs to step k+1, the one taken from state k
+            loss = torch.zeros(1, dtype=torch.float32, device=self.device)
+
+            def backward_from(logits):
+                p_fit = torch.softmax(logits, dim=1).contiguous()
+                d = torch.empty_like(p_fit)
+                _lib.check(self.lib.ahk_rl_pg_targets(_ptr(prob), _ptr(act), _ptr(ret), int(sel.numel()), self.learning_rate,
+                                                      _ptr(p_fit), None, _ptr(d), _ptr(loss), _stream(self.device)))
+                return d, loss
+
+            self._fit(stacked(g[0:3]), backward_from)
+            losses.append(loss)
+        rp.reset()  # rl_agents.py:280
+        if not losses:
+            return None
+        self.loss_buffer.append(float(torch.cat(losses).mean().item()))
+        return self.loss_buffer[-1]
+
+
+def run_training(agent, steps, training_start=100, training_interval=25, copy_interval=2500):
+    """≙ the loop of ai/reinforcement/train.py:76-118 with every env stepping in lockstep: act, step, store; a DDQN agent
+    trains every `training_interval` iterations after `training_start` and copies to the target network every
+    `copy_interval`; a PG agent trains every `episode_length` steps.  -> list of losses."""
+    env, losses = agent.env, []
+    agent.replay.record_observation(env)
+    for _ in range(int(steps)):
+        action = agent.act()
+        _, reward, done, _ = env.step(action)
+        agent.store_experience(action, reward, done)
+        if isinstance(agent, DDQNAgent):
+            if agent.iteration > training_start and agent.iteration % training_interval == 0:
+                losses.append(agent.train())
+            if agent.iteration > copy_interval and agent.iteration % copy_interval == 0:
+                agent.update_target_weights()
+        elif agent.replay.filled >= agent.episode_length + 1:
+            losses.append(agent.train())
+            agent.replay.record_observation(env)
+    return [l for l in losses if l is not None]

@@ -182,12 +182,12 @@ int ahk_replay_gather(const uint8_t *store_dev, int capacity, int n, const int32
  * gradient dlogits = 2 (q_fit - targets) / (10 n); q_fit = output of the forward pass being fitted, NULL = q.
  * targets_dev / dlogits_dev / loss_dev may be NULL. */
 int ahk_rl_ddqn_targets(const float *q_dev, const float *q_next_online_dev, const float *q_next_target_dev, const uint8_t *action_dev,
-                        const float *reward_dev, const uint8_t *done_dev, int n, float discount, const float *q_fit_dev,
+                        const float *reward_dev, const uint8_t *done_dev, int n, double discount, const float *q_fit_dev,
                         float *targets_dev, float *dlogits_dev, float *loss_dev, void *stream);
 /* ≙ PGAgent.train::discount_rewards (rl_agents.py:257-268) for n envs at once: reward_dev/done_dev/returns_dev are
  * [steps][n]; per episode (a run of steps of one env ending at done != 0 or at the last step) G[t] = r[t] + discount *
  * G[t+1], then standardised by the episode's own mean and population std (zeros when the std is 0), in float64. */
-int ahk_rl_pg_returns(const float *reward_dev, const uint8_t *done_dev, int steps, int n, float discount, float *returns_dev, void *stream);
+int ahk_rl_pg_returns(const float *reward_dev, const uint8_t *done_dev, int steps, int n, double discount, float *returns_dev, void *stream);
 /* ≙ PGAgent.store_experience + train (rl_agents.py:246-253,270-274) for m = steps*n samples: prob_dev float[m][10] = the
  * softmax output at act() time, targets = prob + learning_rate * (onehot(action) - prob) * returns; plus the categorical
  * cross-entropy (models.py:119) of prob_fit (NULL = prob) against targets and its gradient w.r.t. the logits. */

@@ -63,7 +63,9 @@ struct ahk_env {
     unsigned adapt_tick = 0, adapt_every = 8;
     int switch_in = 0;
     bool balance = true; // A/B switch AHK_BALANCE=0
-    int pdl = -1;        // programmatic dependent launch of consecutive step kernels; -1: by size (ahk_create); A/B switch AHK_PDL=0/1
+    int dyn_units = 1;   // warps claim raster units from a shared counter; A/B switch AHK_UNITS=static: round-robin
+    int last_mode = -1;  // mode of the previous fused launch (step_args)
+    int pdl = -1;        // programmatic dependent launch of consecutive step kernels; -1: by size (ahk_create); A/B switch AHK_PDL=0/1/3
     cudaEvent_t ev[3] = {nullptr, nullptr, nullptr}; // ahk_step_profiled: before env_kernel, between, after raster
 };
 
@@ -119,7 +121,11 @@ ahk::StepArgs step_args(ahk_env *e, const ahk::EnvArgs &a, int mode)
     st.envs_per_cta = e->envs_per_cta;
     // two trace slots, alternating per launch, so that overlapped consecutive launches can be laid side by side
     st.trace = e->trace ? e->trace + (e->launches & 1u) * static_cast<size_t>(e->step_grid) * (ahk::kStepThreads / 32) * 4 : nullptr;
-    st.pdl = e->pdl;
+    // Deferred wait (pdl 3) only between two consecutive STEP launches: a reset launch writes all three ring slots, so it
+    // and the step after it keep the wait in front of their first store.
+    st.pdl = (e->pdl == 3 && !(mode == 1 && e->last_mode == 1)) ? 1 : e->pdl;
+    e->last_mode = mode;
+    st.dyn_units = e->dyn_units;
     if (e->balance && !e->split) {
         // New boundaries are taken into use two launches after the one that computes them: with overlapped launches
         // the very next kernel may already be reading its boundaries while the last CTA of this one writes.
@@ -190,6 +196,7 @@ int ahk_create(const ahk_config *cfg, ahk_env **out)
     if (const char *s = getenv("AHK_PATH")) e->split = strcmp(s, "split") == 0;
     if (const char *s = getenv("AHK_ADAPT_EVERY")) e->adapt_every = atoi(s) > 0 ? atoi(s) : 1;
     if (const char *s = getenv("AHK_PDL")) e->pdl = atoi(s);
+    if (const char *s = getenv("AHK_UNITS")) e->dyn_units = strcmp(s, "static") != 0;
     if (const char *s = getenv("AHK_BALANCE")) e->balance = atoi(s) != 0;
     if (const char *s = getenv("AHK_RASTER")) e->staged = strcmp(s, "staged") == 0;
     if (const char *s = getenv("AHK_ZEROCOPY")) e->zero_copy = atoi(s) != 0;
@@ -199,10 +206,13 @@ int ahk_create(const ahk_config *cfg, ahk_env **out)
     e->step_grid = (cfg->n_envs + e->envs_per_cta - 1) / e->envs_per_cta;
     if (e->balance && !e->split && cfg->n_envs >= 4 * e->sms) e->step_grid = e->sms; // the adaptive partition uses every SM
     else e->balance = false;
-    // Overlapping consecutive launches hides ~5 us of prologue + launch latency per step, but the next launch's CTAs
-    // then land on whichever SM retires first, so CTA index no longer names an SM and the adaptive partition (worth 7 %
-    // on long launches) loses its footing.  Measured cross-over ~10 k envs (profiles/launch_modes_r1.txt).
-    if (e->pdl < 0) e->pdl = cfg->n_envs <= 10240 ? 1 : 0;
+    // Consecutive step kernels overlap (programmatic dependent launch): the next launch's CTAs move onto SMs as this
+    // launch's CTAs retire and run their prologue and game tick under its tail.  pdl 1: griddepcontrol.wait before the
+    // first frame store.  pdl 3 (default when the grid fills the device): the wait moves to the END of the kernel, so an SM
+    // that retires early goes straight on with the next step's frames.  Why that is safe needs one CTA per SM and a grid
+    // of at least one CTA per SM; smaller grids keep pdl 1.  A/B switch AHK_PDL=0/1/3.
+    if (e->pdl < 0) e->pdl = 3;
+    if (e->pdl == 3 && e->step_grid < e->sms) e->pdl = 1;
     cudaError_t err = cudaMalloc(&e->table_dev, ahk::kFrameBytes);
     if (err == cudaSuccess) err = cudaMalloc(&e->action_stage, 2 * static_cast<size_t>(cfg->n_envs));
     if (err == cudaSuccess && e->balance) {

@@ -124,6 +124,7 @@ __device__ __forceinline__ void env_update(const EnvArgs &a, int i, uint4 (&rec)
         } else {
             rec[0] = draw_record(s, use);
         }
+        if (!do_reset && steps == 1u) rec[0].w |= kDrawDefer; // the previous step reset this env (or was its first)
         steps += 1u;
         if (a.auto_reset && (terminal || (a.max_episode_steps > 0 && steps >= static_cast<uint32_t>(a.max_episode_steps)))) pending = 1u;
 

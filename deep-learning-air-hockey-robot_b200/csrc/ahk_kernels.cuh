@@ -53,7 +53,8 @@ struct StepArgs { // the fused kernel: env block b of envs_per_cta environments 
     int *bounds_next;        // [grid + 1] written by the last CTA (nullptr: do not adapt)
     unsigned long long *end_ns; // [grid] %globaltimer at each CTA's end, this launch
     unsigned *done_count;    // CTAs finished in this launch
-    int pdl;                 // launched with programmatic stream serialization: griddepcontrol.* are live (2: experiment, no wait)
+    int dyn_units;           // 1: warps claim raster units from a shared-memory counter instead of round-robin (default; AHK_UNITS=static for A/B)
+    int pdl;                 // launched with programmatic stream serialization: griddepcontrol.* are live; 1: wait before the first frame store, 3: wait at the end (2: experiment, no wait)
     unsigned long long *trace; // measurement aid (ahk_set_trace): [grid][32 warps][4] %globaltimer stamps; selects the traced kernel
 };
 

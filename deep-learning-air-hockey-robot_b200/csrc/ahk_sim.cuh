@@ -30,6 +30,9 @@ constexpr uint32_t kScoredTop = 1u, kScoredBottom = 2u;
 
 // draw record flags (w3 low byte): bits 0..2 use mask, bit 3 noise frame, bit 4 record valid
 constexpr uint32_t kDrawNoise = 8u, kDrawValid = 16u;
+// the env was reset in the PREVIOUS step: that launch rewrote this very ring slot with a warm-up frame, so with overlapped
+// launches (StepArgs::pdl == 3) this frame is drawn after griddepcontrol.wait, with the frames that rewrite older slots
+constexpr uint32_t kDrawDefer = 32u;
 
 __device__ __forceinline__ float add(float a, float b) { return __fadd_rn(a, b); }
 __device__ __forceinline__ float sub(float a, float b) { return __fsub_rn(a, b); }

@@ -287,7 +287,7 @@ constexpr int kStepSmem = kLutOffset + static_cast<int>(sizeof(Luts));
 // every CTA's share of the envs against its lateness relative to the mean (an integral controller, gain 1/2, shares kept
 // within +-50 % of even) and writes the boundaries a later launch will use.  Results do not depend on the partition:
 // state lives in HBM, every env is ticked and drawn exactly once whoever owns it.
-__device__ __forceinline__ void rebalance(const StepArgs &a, unsigned *warps_done, const unsigned long long *raster_start, int lane)
+__device__ __forceinline__ void rebalance(const StepArgs &a, int slot, unsigned *warps_done, const unsigned long long *raster_start, int lane)
 {
     unsigned k = 0;
     if (lane == 0) { __threadfence_block(); k = atomicAdd(warps_done, 1u); }
@@ -298,7 +298,7 @@ __device__ __forceinline__ void rebalance(const StepArgs &a, unsigned *warps_don
     unsigned long long end = 0;
     if (lane == 0) {
         end = global_ns();
-        a.end_ns[blockIdx.x] = end;
+        a.end_ns[slot] = end;
         __threadfence();
         finished = atomicAdd(a.done_count, 1u);
     }
@@ -366,6 +366,8 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_kernel(StepArgs a)
     Luts &luts = *reinterpret_cast<Luts *>(smem + kLutOffset);
     __shared__ __align__(8) uint64_t s_table_ready;
     __shared__ int s_count;
+    __shared__ int s_next;
+    __shared__ int s_count_old, s_next_old; // records that rewrite OLDER ring slots (after a reset), kept apart: see a.pdl == 3
     __shared__ unsigned s_stats[kStatWords];
     __shared__ unsigned s_warps_done;
     __shared__ unsigned long long s_raster_start;
@@ -388,15 +390,16 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_kernel(StepArgs a)
                      :: "r"(static_cast<uint32_t>(__cvta_generic_to_shared(smem))), "l"(a.ras.table), "r"(kFrameBytes), "r"(bar) : "memory");
     }
     build_luts(luts);
-    bool table_ready = false;
+    bool table_ready = false, waited = false;
 
     const int n = a.ras.n;
-    int lo = blockIdx.x * a.envs_per_cta, hi = min(n, lo + a.envs_per_cta);
-    if (a.bounds != nullptr) { lo = a.bounds[blockIdx.x]; hi = a.bounds[blockIdx.x + 1]; }
+    const int part = static_cast<int>(blockIdx.x);
+    int lo = part * a.envs_per_cta, hi = min(n, lo + a.envs_per_cta);
+    if (a.bounds != nullptr) { lo = a.bounds[part]; hi = a.bounds[part + 1]; }
     const size_t stride = static_cast<size_t>(n);
 
     for (int base = lo; base < hi; base += kStepThreads) {
-        if (tid == 0) s_count = 0;
+        if (tid == 0) { s_count = 0; s_next = 0; s_count_old = 0; s_next_old = 0; }
         __syncthreads(); // s_count cleared; previous round's records consumed; first round: tables built, barrier initialised
 
         const int i = base + tid;
@@ -413,41 +416,72 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_kernel(StepArgs a)
         }
         if (a.pdl) __threadfence(); // this thread's state and outputs are out before the barrier below, hence before the trigger
         if (kTrace && lane == 0 && base == lo) trace[1] = global_ns();
-        // compact the valid records into shared memory: one atomic per warp per ring slot
+        // compact the valid records into shared memory: one atomic per warp per ring slot.  Records of the newest frame
+        // grow from the bottom of the list, records that rewrite the two older slots (warm-up frames after a reset) from
+        // the top, so that the two kinds can be drawn in separate phases.
 #pragma unroll
         for (int b = 0; b < 3; ++b) {
             const bool valid = live && (rec[b].w & kDrawValid);
             const unsigned votes = __ballot_sync(0xFFFFFFFFu, valid);
             if (votes == 0u) continue;
-            int at = 0;
-            if (lane == 0) at = atomicAdd(&s_count, __popc(votes));
-            at = __shfl_sync(0xFFFFFFFFu, at, 0) + __popc(votes & ((1u << lane) - 1u));
-            if (valid) s_recs[at] = make_uint4(rec[b].x, rec[b].y, rec[b].z, (rec[b].w & 0xFFu) | static_cast<uint32_t>(tid) << 8 | static_cast<uint32_t>(b) << 20);
+            const bool later = b != 0 || (rec[b].w & kDrawDefer); // phase 1: after the wait on the previous launch
+            const unsigned votes_later = __ballot_sync(0xFFFFFFFFu, valid && later), votes_now = votes & ~votes_later;
+            int at = 0, at_later = 0;
+            if (lane == 0) {
+                if (votes_now) at = atomicAdd(&s_count, __popc(votes_now));
+                if (votes_later) at_later = atomicAdd(&s_count_old, __popc(votes_later));
+            }
+            at = __shfl_sync(0xFFFFFFFFu, at, 0) + __popc(votes_now & ((1u << lane) - 1u));
+            at_later = __shfl_sync(0xFFFFFFFFu, at_later, 0) + __popc(votes_later & ((1u << lane) - 1u));
+            if (later) at = 3 * kStepThreads - 1 - at_later;
+            if (valid) s_recs[at] = make_uint4(rec[b].x, rec[b].y, rec[b].z, (rec[b].w & 0x1Fu) | static_cast<uint32_t>(tid) << 8 | static_cast<uint32_t>(b) << 20);
         }
         __syncthreads();
         // Programmatic dependent launch: once every CTA has ticked its last round the NEXT step kernel may be scheduled;
         // its CTAs move in as ours retire, and its prologue and game tick (which read only the state fenced above) run
         // while the rest of this grid is still draining its stores.
         if (a.pdl && base + kStepThreads >= hi) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-        const int units = s_count * kUnitsPerFrame;
+        const int units = s_count * kUnitsPerFrame, units_old = s_count_old * kUnitsPerFrame;
         if (!table_ready) {
             mbarrier_wait(bar, 0u);
             table_ready = true;
-            if (a.pdl == 1) asm volatile("griddepcontrol.wait;" ::: "memory"); // no frame is written before the previous launch has completed
+            // pdl 1: no frame is written before the previous launch has completed
+            if (a.pdl == 1) { asm volatile("griddepcontrol.wait;" ::: "memory"); waited = true; }
         }
         if (kTrace && lane == 0 && base == lo) trace[2] = global_ns();
         if (a.bounds_next != nullptr && tid == 0 && base == lo) s_raster_start = global_ns();
-        for (int u = warp; u < units; u += kStepThreads / 32) {
-            const uint4 rec_u = s_recs[u / kUnitsPerFrame];
-            const int env = base + static_cast<int>((rec_u.w >> 8) & 0x3FFu), back = static_cast<int>(rec_u.w >> 20); // back 0 = newest
-            const int slot = (a.ras.head + 3 - back) % 3;
-            uint8_t *frame = a.ras.frames + (static_cast<size_t>(slot) * stride + env) * kFrameBytes;
-            draw_unit(s_table, s_patch, luts, rec_u, u % kUnitsPerFrame, frame, a.ras.env_id_base + static_cast<uint32_t>(env), a.ras.key, lane);
+        // phase 0: the newest frame of every env, into ring slot `head` — a slot the previous launch does not touch.
+        // phase 1: frames that replace the two older slots (reset envs only).  The previous launch may still be writing
+        // those very frames, so with the wait deferred (pdl 3) it comes first, here.
+#pragma unroll 1
+        for (int phase = 0; phase < 2; ++phase) {
+            const int total = phase == 0 ? units : units_old;
+            if (phase == 1) {
+                if (total == 0) break;
+                if (!waited) { asm volatile("griddepcontrol.wait;" ::: "memory"); waited = true; }
+            }
+            int *next = phase == 0 ? &s_next : &s_next_old;
+            for (int u = warp;; u += kStepThreads / 32) {
+                if (a.dyn_units) { // claim the next unit: whichever warp is free takes it (composed units cost more than copies)
+                    if (lane == 0) u = atomicAdd(next, 1);
+                    u = __shfl_sync(0xFFFFFFFFu, u, 0);
+                }
+                if (u >= total) break;
+                const int r = u / kUnitsPerFrame;
+                const uint4 rec_u = s_recs[phase == 0 ? r : 3 * kStepThreads - 1 - r];
+                const int env = base + static_cast<int>((rec_u.w >> 8) & 0x3FFu), back = static_cast<int>(rec_u.w >> 20); // back 0 = newest
+                const int slot = (a.ras.head + 3 - back) % 3;
+                uint8_t *frame = a.ras.frames + (static_cast<size_t>(slot) * stride + env) * kFrameBytes;
+                draw_unit(s_table, s_patch, luts, rec_u, u % kUnitsPerFrame, frame, a.ras.env_id_base + static_cast<uint32_t>(env), a.ras.key, lane);
+            }
         }
         if (base + kStepThreads < hi) __syncthreads(); // every warp has read this round's record count before it is cleared
     }
     if (kTrace && lane == 0) trace[3] = global_ns();
-    if (kMode == 1 && a.bounds_next != nullptr) rebalance(a, &s_warps_done, &s_raster_start, lane);
+    // pdl 3: the wait sits at the END.  It keeps completion in launch order (this grid cannot complete before the previous
+    // one has), which is all that later launches and stream consumers rely on; DESIGN.md §3.5 has the hazard analysis.
+    if (a.pdl == 3 && !waited) asm volatile("griddepcontrol.wait;" ::: "memory");
+    if (kMode == 1 && a.bounds_next != nullptr) rebalance(a, part, &s_warps_done, &s_raster_start, lane);
     if (!table_ready) mbarrier_wait(bar, 0u); // never exit with the table copy still in flight
     if (kMode < 2 && a.env.stats != nullptr) {
         unsigned long long *st = reinterpret_cast<unsigned long long *>(a.env.stats);

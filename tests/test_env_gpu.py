@@ -126,12 +126,15 @@ def test_forced_episodes_and_masks(cuda, orc, noise_table):
         assert np.array_equal(ring[i], o.ring()), i
 
 
-def test_back_to_back_steps_overlap(cuda, orc, noise_table):
+@pytest.mark.parametrize("n,limit,steps", [(333, 17, 45), (1184, 5, 42)])
+def test_back_to_back_steps_overlap(cuda, orc, noise_table, n, limit, steps):
     """Step kernels launched back to back overlap (the next launch's game tick runs under this launch's rasterising,
-    csrc/ahk_step.cu): no host synchronisation for 45 steps, then state, the whole 3-frame ring, the last step's
-    outputs and the statistics must equal the oracle's."""
-    n, seed, steps = 333, 21, 45
-    env = make_env(n, noise_table, seed=seed, max_episode_steps=17)
+    csrc/ahk_step.cu): no host synchronisation for `steps` steps, then state, the whole 3-frame ring, the last step's
+    outputs and the statistics must equal the oracle's.  333 envs: a grid smaller than the device, wait before the first
+    store; 1184 envs: one CTA per SM, the wait deferred to the end of the kernel, and a reset every 5 steps so that the
+    frames rewriting older ring slots (the ones that must still wait) are exercised in every launch."""
+    seed = 21
+    env = make_env(n, noise_table, seed=seed, max_episode_steps=limit)
     oracles = oracle_envs(orc, n, noise_table, seed)
     env.reset()
     for _ in range(steps):
@@ -141,7 +144,7 @@ def test_back_to_back_steps_overlap(cuda, orc, noise_table):
     for o in oracles:
         o.reset()
         for _ in range(steps):
-            out = o.step_auto(255, 255, 17)
+            out = o.step_auto(255, 255, limit)
         outs.append(out)
     assert_same_state(env, oracles, "after %d unsynchronised steps" % steps)
     ring = ring_newest_first(env)

@@ -1,0 +1,81 @@
+"""RL-step measurement: the batched train.py loop on one GPU, with its parts timed by CUDA events.
+    python tools/rl_bench.py [--envs 8192] [--steps 200] [--batch 32] [--interval 25] > profiles/rl_<round>.json
+"""
+import argparse
+import json
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "deep-learning-air-hockey-robot_b200"))
+
+import torch  # noqa: E402
+
+from gym_air_hockey_b200 import BatchedAirHockeyEnv  # noqa: E402
+from gym_air_hockey_b200.rl import DDQNAgent  # noqa: E402
+
+
+def timed(fn, reps=1):
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    a.record()
+    for _ in range(reps):
+        out = fn()
+    b.record()
+    torch.cuda.synchronize()
+    return a.elapsed_time(b) / reps, out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--envs", type=int, default=8192)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--batch", type=int, default=32)       # train.py:49
+    ap.add_argument("--interval", type=int, default=25)    # train.py:47
+    ap.add_argument("--buffer-steps", type=int, default=32)
+    args = ap.parse_args()
+    env = BatchedAirHockeyEnv(args.envs, seed=0, max_episode_steps=256)
+    env.reset()
+    agent = DDQNAgent(env, buffer_steps=args.buffer_steps, batch_size=args.batch, discount_rate=0.98, eps_min=0.05, eps_max=0.99,
+                      eps_decay_steps=100000)
+    agent.replay.record_observation(env)
+
+    def rollout_step():
+        action = agent.act()
+        _, reward, done, _ = env.step(action)
+        agent.store_experience(action, reward, done)
+
+    for _ in range(8):
+        rollout_step()
+    agent.train()
+    out = {"envs": args.envs, "batch": args.batch, "interval": args.interval, "buffer_steps": args.buffer_steps}
+    out["rollout_step_ms"], _ = timed(rollout_step, 50)                        # act (6 forward kernels) + step + store
+    out["act_ms"], _ = timed(agent.act, 20)
+    out["store_ms"], _ = timed(lambda: agent.store_experience(agent.greedy, env.reward, env.done), 20)
+    batch = agent.replay.sample(args.batch, agent.gen)
+    out["sample_ms"], _ = timed(lambda: agent.replay.sample(args.batch, agent.gen), 10)
+    big = min(4096, args.envs)
+    t_idx = torch.randint(2, args.buffer_steps - 2, (big,), device=env.device)
+    e_idx = torch.randint(0, args.envs, (big,), device=env.device)
+    ms, _ = timed(lambda: agent.replay.gather(t_idx, e_idx), 20)
+    out["gather"] = {"batch": big, "ms": ms, "GBs_read_plus_write": 2 * 4 * big * 49152 / ms / 1e6}
+    out["train_ms"], _ = timed(agent.train, 10)                                 # sample, 3 Q forwards, targets, fit, push
+    t0 = time.perf_counter()
+    agent.push_weights()
+    torch.cuda.synchronize()
+    out["push_weights_ms_host"] = (time.perf_counter() - t0) * 1e3
+
+    def loop():
+        for _ in range(args.steps):
+            rollout_step()
+            if agent.iteration % args.interval == 0:
+                agent.train()
+    ms, _ = timed(loop)
+    out["loop"] = {"steps": args.steps, "ms": ms, "env_steps_per_s": args.envs * args.steps / ms * 1e3,
+                   "trainings": args.steps // args.interval}
+    print(json.dumps(out))
+
+
+if __name__ == "__main__":
+    main()

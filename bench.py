@@ -363,6 +363,22 @@ def main():
     barrier()
     e2e_s = time.perf_counter() - t0
 
+    # ---- the same loop through ahk_step_host_results: the call returns when reward / done / labels of the step are in the
+    # host buffers (the kernel signals the end of its game ticks through mapped memory) and the frames are still being
+    # rasterised; the host reads the result, then makes the next call — so the next actions MAY depend on this step's
+    # results (policy in the loop), yet the kernels run back to back.  host_sync (all frames written) is inside the timing.
+    for _ in range(3):
+        env.step_host_results(act, act, out)
+    env.host_sync()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        env.step_host_results(act, act, out)
+        checksum = float(out['reward'][0])  # the host reads the step's result before the next call
+    env.host_sync()
+    barrier()
+    res_s = time.perf_counter() - t0
+
     # ---- the same call pipelined (ahk_step_host_begin/_wait, 4 steps in flight, each with its own host buffers): valid
     # for this workload because the AI plays both sides — the next actions do not depend on this step's results
     depth = 4
@@ -396,12 +412,12 @@ def main():
         barrier()
         frames_s = (time.perf_counter() - t0) / frame_steps
 
-    t = torch.tensor([ms, e2e_s, raster_ms, env_ms, pipe_s, frames_s], dtype=torch.float64, device="cuda")
+    t = torch.tensor([ms, e2e_s, raster_ms, env_ms, pipe_s, frames_s, res_s], dtype=torch.float64, device="cuda")
     stats = env.stats.clone()
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(stats, op=dist.ReduceOp.SUM)  # episode statistics: the only collective, off the step path
-    ms, e2e_s, raster_ms, env_ms, pipe_s, frames_s = (v.item() for v in t)
+    ms, e2e_s, raster_ms, env_ms, pipe_s, frames_s, res_s = (v.item() for v in t)
 
     if rank == 0:
         peaks, peak_kind = measured_peaks()
@@ -443,9 +459,10 @@ def main():
                          "write_only_peak": write_peak,
                          "frac_of_write_only_peak": (achieved / write_peak) if write_peak else None,
                          "note": "the path only WRITES; write_only_peak = best steady-state pure write stream (st.global.cs.v4 / cp.async.bulk) over the same 3 x 201 MB ring, tools/wprobe.cu -> profiles/wprobe_r1b.json; peak = MEASURED_PEAKS.json copy (read+write)"},
-            "e2e": {"value": total_envs * e2e_steps / e2e_s, "unit": "env-steps/s", "h2d_bytes_per_step": 2 * n,
+            "e2e": {"value": total_envs * e2e_steps / res_s, "unit": "env-steps/s", "h2d_bytes_per_step": 2 * n,
                     "d2h_bytes_per_step": 7 * n,
-                    "note": "ahk_step_host, one synchronous call per step: actions (2 B/env) read from pinned host memory and reward/done/labels (7 B/env) written to pinned host memory by the step kernel itself (mapped, zero-copy), then the host waits; frames stay in the HBM ring",
+                    "note": "ahk_step_host_results, one call per step, the host reads the step's result before the next call: actions (2 B/env) read from pinned host memory and reward/done/labels (7 B/env) written to pinned host memory by the step kernel itself (mapped, zero-copy); the call returns when the results have landed (game ticks over), the frames stay in the HBM ring and are complete at the host_sync that closes the timed region",
+                    "full_wait": {"value": total_envs * e2e_steps / e2e_s, "note": "ahk_step_host: the same bytes, but every call waits for the whole kernel (frames included) before returning"},
                     "pipelined": {"value": total_envs * e2e_steps / pipe_s, "depth": depth, "note": "ahk_step_host_begin/_wait, same bytes per step; legal when actions do not depend on results (AI vs AI data generation)"},
                     "with_frames_to_host": {"value": (total_envs / frames_s) if frames_s == frames_s else None, "d2h_bytes_per_step": (7 + 49152) * n, "note": "new uint8 frame of every env copied to pinned host memory each step (PCIe-bound)"}},
             "stats": {"steps": int(stats[0]), "episodes": int(stats[1]), "goals_top": int(stats[2]), "goals_bottom": int(stats[3])},

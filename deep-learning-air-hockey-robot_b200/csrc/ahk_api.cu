@@ -45,6 +45,10 @@ struct ahk_env {
     static constexpr int kHostDepth = 8;  // ahk_step_host_begin calls that may be in flight
     cudaEvent_t host_ev[kHostDepth] = {};
     uint64_t host_ticket = 0;
+    // ahk_step_host_results: 8 mapped host words the step kernel signals through, their device alias, CTA counters
+    unsigned long long *tick_flag_host = nullptr, *tick_flag_dev = nullptr;
+    unsigned *tick_count_dev = nullptr;
+    uint64_t tick_seq = 0;
     bool zero_copy = true;                // A/B switch AHK_ZEROCOPY=0: always use the copy engine in ahk_step_host
     int head = 0;
     int sms = 0;
@@ -229,6 +233,13 @@ int ahk_create(const ahk_config *cfg, ahk_env **out)
         if (err == cudaSuccess) err = cudaMemset(e->done_dev, 0, sizeof(unsigned));
     }
     if (err == cudaSuccess) err = cudaStreamCreateWithFlags(&e->host_stream, cudaStreamNonBlocking);
+    if (err == cudaSuccess) err = cudaHostAlloc(&e->tick_flag_host, 8 * sizeof(unsigned long long), cudaHostAllocMapped);
+    if (err == cudaSuccess) {
+        memset(e->tick_flag_host, 0, 8 * sizeof(unsigned long long));
+        err = cudaHostGetDevicePointer(&e->tick_flag_dev, e->tick_flag_host, 0);
+    }
+    if (err == cudaSuccess) err = cudaMalloc(&e->tick_count_dev, 8 * sizeof(unsigned));
+    if (err == cudaSuccess) err = cudaMemset(e->tick_count_dev, 0, 8 * sizeof(unsigned));
     for (int k = 0; k < 3 && err == cudaSuccess; ++k) err = cudaEventCreate(&e->ev[k]);
     for (int k = 0; k < ahk_env::kHostDepth && err == cudaSuccess; ++k) err = cudaEventCreateWithFlags(&e->host_ev[k], cudaEventDisableTiming);
     if (err == cudaSuccess) err = ahk::step_prepare();
@@ -251,6 +262,8 @@ void ahk_destroy(ahk_env *e)
     if (e->end_dev) cudaFree(e->end_dev);
     if (e->done_dev) cudaFree(e->done_dev);
     if (e->host_stream) cudaStreamDestroy(e->host_stream);
+    if (e->tick_flag_host) cudaFreeHost(e->tick_flag_host);
+    if (e->tick_count_dev) cudaFree(e->tick_count_dev);
     for (int k = 0; k < 3; ++k) if (e->ev[k]) cudaEventDestroy(e->ev[k]);
     for (int k = 0; k < ahk_env::kHostDepth; ++k) if (e->host_ev[k]) cudaEventDestroy(e->host_ev[k]);
     delete e;
@@ -342,8 +355,10 @@ int ahk_step_profiled(ahk_env *e, const uint8_t *robot, const uint8_t *human, vo
     return AHK_OK;
 }
 
-int ahk_step_host_begin(ahk_env *e, const uint8_t *robot, const uint8_t *human, float *reward, uint8_t *done,
-                        uint8_t *robot_label, uint8_t *human_label, uint8_t *frame)
+// early != nullptr: ask the kernel to signal the end of its game ticks (ahk_step_host_results); *early = the sequence
+// number to wait for, or 0 when some output buffer is not mapped and the caller has to wait for the whole step.
+static int step_host_enqueue(ahk_env *e, const uint8_t *robot, const uint8_t *human, float *reward, uint8_t *done,
+                             uint8_t *robot_label, uint8_t *human_label, uint8_t *frame, uint64_t *early)
 {
     if (int rc = check_ready(e)) return rc;
     AHK_CUDA(cudaSetDevice(e->cfg.device));
@@ -364,6 +379,16 @@ int ahk_step_host_begin(ahk_env *e, const uint8_t *robot, const uint8_t *human, 
         a.h_robot_label = mapped(robot_label);
         a.h_human_label = mapped(human_label);
     }
+    if (early) {
+        const bool all_mapped = zc && (!reward || a.h_reward) && (!done || a.h_done) && (!robot_label || a.h_robot_label) &&
+                                (!human_label || a.h_human_label) && !frame;
+        *early = 0;
+        if (all_mapped) {
+            a.h_tick_flag = e->tick_flag_dev;
+            a.tick_count = e->tick_count_dev;
+            a.tick_seq = *early = ++e->tick_seq;
+        }
+    }
     e->head = (e->head + 1) % 3;
     if (int rc = run(e, a, 1, s)) return rc;
     if (reward && !a.h_reward) AHK_CUDA(cudaMemcpyAsync(reward, e->buf.reward, n * sizeof(float), cudaMemcpyDeviceToHost, s));
@@ -376,6 +401,40 @@ int ahk_step_host_begin(ahk_env *e, const uint8_t *robot, const uint8_t *human, 
     const int ticket = static_cast<int>(e->host_ticket++ % ahk_env::kHostDepth);
     AHK_CUDA(cudaEventRecord(e->host_ev[ticket], s));
     return ticket;
+}
+
+int ahk_step_host_begin(ahk_env *e, const uint8_t *robot, const uint8_t *human, float *reward, uint8_t *done,
+                        uint8_t *robot_label, uint8_t *human_label, uint8_t *frame)
+{
+    return step_host_enqueue(e, robot, human, reward, done, robot_label, human_label, frame, nullptr);
+}
+
+int ahk_step_host_results(ahk_env *e, const uint8_t *robot, const uint8_t *human, float *reward, uint8_t *done,
+                          uint8_t *robot_label, uint8_t *human_label)
+{
+    uint64_t seq = 0;
+    const int ticket = step_host_enqueue(e, robot, human, reward, done, robot_label, human_label, nullptr, &seq);
+    if (ticket < 0) return ticket;
+    if (seq == 0) return ahk_step_host_wait(e, ticket); // pageable buffers: results arrive with the copies, after the kernel
+    const volatile unsigned long long *flag = e->tick_flag_host + (seq & 7u);
+    for (unsigned spins = 1; *flag != seq; ++spins) {
+        if ((spins & 0xFFFu) == 0u) { // a failed launch never signals: fall back to the event every 4096 polls
+            const cudaError_t st = cudaEventQuery(e->host_ev[ticket]);
+            if (st == cudaSuccess) break;
+            if (st != cudaErrorNotReady) return fail(AHK_ERR_CUDA, "ahk_step_host_results: %s", cudaGetErrorString(st));
+        }
+#if defined(__x86_64__)
+        __builtin_ia32_pause();
+#endif
+    }
+    return AHK_OK;
+}
+
+int ahk_host_sync(ahk_env *e)
+{
+    if (!e) return fail(AHK_ERR_ARG, "env is NULL");
+    AHK_CUDA(cudaStreamSynchronize(e->host_stream));
+    return AHK_OK;
 }
 
 int ahk_step_host_wait(ahk_env *e, int ticket)

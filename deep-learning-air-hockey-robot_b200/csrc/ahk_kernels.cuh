@@ -27,6 +27,11 @@ struct EnvArgs {
     // the kernel itself over PCIe next to the device copies (nullptr: none) — no copy engine on the e2e path
     float *h_reward;
     uint8_t *h_done, *h_robot_label, *h_human_label;
+    // ahk_step_host_results: once every CTA has ticked, the last one stores tick_seq into the mapped host word
+    // h_tick_flag[tick_seq & 7]; tick_count[tick_seq & 7] counts the CTAs (device memory, left at 0 again)
+    unsigned long long *h_tick_flag;
+    unsigned *tick_count;
+    unsigned long long tick_seq;
     const uint8_t *reset_mask, *episode_override, *use_override; // reset
     uint2 key;
     uint32_t env_id_base;

@@ -53,6 +53,8 @@ SYMBOLS = {
     "ahk_step_host": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "ahk_step_host_begin": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "ahk_step_host_wait": (_i, [_vp, _i]),
+    "ahk_step_host_results": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "ahk_host_sync": (_i, [_vp]),
     "ahk_observe": (_i, [_vp, _i, _vp, _vp]),
     "ahk_head": (_i, [_vp]),
     "ahk_set_head": (_i, [_vp, _i]),

@@ -162,6 +162,22 @@ class BatchedAirHockeyEnv(object):
             _lib.check(rc)
         return out
 
+    def step_host_results(self, robot_action=None, human_action=None, out=None):
+        """step_host that returns as soon as reward / done / labels are in `out` (ahk_step_host_results): the kernel signals
+        the end of its game ticks through mapped host memory and goes on rasterising.  For loops whose next actions depend
+        on this step's results but which leave the frames on the device.  host_sync() waits for the frames too."""
+        if out is None:
+            out = self.host_buffers()
+        p = self._host_ptr
+        rc = self.lib.ahk_step_host_results(self._h, p(robot_action), p(human_action), p(out['reward']), p(out['done']),
+                                            p(out['robot_action']), p(out['human_action']))
+        if rc:
+            _lib.check(rc)
+        return out
+
+    def host_sync(self):
+        _lib.check(self.lib.ahk_host_sync(self._h))
+
     def _host_ptr(self, a):
         """Address of a host array, cached per array object: building a ctypes pointer costs more than the C call."""
         if a is None:

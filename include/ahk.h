@@ -107,6 +107,16 @@ int ahk_step_host_begin(ahk_env *env, const uint8_t *robot_host, const uint8_t *
                         uint8_t *done_host, uint8_t *robot_label_host, uint8_t *human_label_host, uint8_t *frame_host);
 int ahk_step_host_wait(ahk_env *env, int ticket);
 
+/* ahk_step_host for a loop that needs each step's RESULTS before it chooses the next actions (reinforcement/train.py:87-96,
+ * keras/test.py:42-51) but leaves the frames on the device: returns as soon as reward / done / labels of this step are in
+ * the host buffers — the step kernel signals the end of its game ticks through mapped host memory — while the frames are
+ * still being rasterised on the engine's own stream.  The next ahk_step_host* call is ordered behind it as usual;
+ * ahk_host_sync waits for everything enqueued by the _host calls (call it before touching the ring from another stream).
+ * Needs pinned output buffers; with pageable ones it behaves like ahk_step_host. */
+int ahk_step_host_results(ahk_env *env, const uint8_t *robot_host, const uint8_t *human_host, float *reward_host,
+                          uint8_t *done_host, uint8_t *robot_label_host, uint8_t *human_label_host);
+int ahk_host_sync(ahk_env *env);
+
 /* ahk_step with CUDA events recorded on `stream` around its kernel(s); waits, then reports the durations.  Default
  * (fused) path: *env_ms = 0 and *raster_ms = the one fused kernel (physics + AI + labels + raster).  With the A/B switch
  * AHK_PATH=split in the environment: the env kernel and the raster kernel separately.  Measurement aid for bench.py's

@@ -286,6 +286,37 @@ def test_step_host_matches_device_path(cuda, table):
         assert np.array_equal(a.frames[a.head].cpu().numpy(), out['frame'])
 
 
+@pytest.mark.parametrize("n", [300, 1500])
+def test_step_host_results_early_return(cuda, table, n):
+    """ahk_step_host_results returns when reward / done / labels are in the host buffers (the kernel's game ticks are
+    over, its frames may not be): every step's results, fed back as the next actions, equal the device path's; after
+    host_sync the ring and the state do too.  300 envs: a grid smaller than the device; 1500: one CTA per SM."""
+    a = make_env(n, table, seed=13, max_episode_steps=20)
+    b = make_env(n, table, seed=13, max_episode_steps=20)
+    a.reset(); b.reset()
+    cuda.cuda.synchronize()
+    out = b.host_buffers()
+    act = cuda.zeros(n, dtype=cuda.uint8).pin_memory().numpy()
+    act[:] = 4
+    for t in range(60):
+        _, reward, done, info = a.step(act.copy(), None)
+        b.step_host_results(act, None, out)
+        assert np.array_equal(reward.cpu().numpy(), out['reward']), t
+        assert np.array_equal(done.cpu().numpy().astype(np.uint8), out['done']), t
+        assert np.array_equal(info['robot_action'].cpu().numpy(), out['robot_action']), t
+        assert np.array_equal(info['human_action'].cpu().numpy(), out['human_action']), t
+        act[:] = (out['human_action'] + out['robot_action'] + t) % 10   # the next actions depend on this step's results
+    b.host_sync()
+    cuda.cuda.synchronize()
+    assert b.head == a.head
+    assert np.array_equal(a.frames.cpu().numpy(), b.frames.cpu().numpy())
+    assert np.array_equal(a.get_state()[0].view(np.uint32), b.get_state()[0].view(np.uint32))
+    pageable = {k: np.empty_like(v) for k, v in out.items()}              # pageable buffers: falls back to the full wait
+    _, reward, _, _ = a.step(None, None)
+    b.step_host_results(None, None, pageable)
+    assert np.array_equal(reward.cpu().numpy(), pageable['reward'])
+
+
 def test_step_host_pipelined_and_pageable(cuda, table):
     """ahk_step_host_begin/_wait with four steps in flight (pinned buffers: the kernel reads the actions and writes the
     results through mapped host memory) and plain pageable numpy buffers (copy engine) both replay the device path."""

@@ -49,6 +49,8 @@ struct ahk_env {
     unsigned long long *tick_flag_host = nullptr, *tick_flag_dev = nullptr;
     unsigned *tick_count_dev = nullptr;
     uint64_t tick_seq = 0;
+    int host_early_ticket = -1; // >= 0: ahk_step_host_results returned before this launch (host_ev[ticket]) had completed
+    cudaStream_t last_stream = nullptr; // stream of the previous fused launch
     bool zero_copy = true;                // A/B switch AHK_ZEROCOPY=0: always use the copy engine in ahk_step_host
     int head = 0;
     int sms = 0;
@@ -117,7 +119,7 @@ ahk::RasterArgs raster_args(const ahk_env *e)
     return r;
 }
 
-ahk::StepArgs step_args(ahk_env *e, const ahk::EnvArgs &a, int mode)
+ahk::StepArgs step_args(ahk_env *e, const ahk::EnvArgs &a, int mode, cudaStream_t s)
 {
     ahk::StepArgs st{};
     st.env = a;
@@ -127,8 +129,9 @@ ahk::StepArgs step_args(ahk_env *e, const ahk::EnvArgs &a, int mode)
     st.trace = e->trace ? e->trace + (e->launches & 1u) * static_cast<size_t>(e->step_grid) * (ahk::kStepThreads / 32) * 4 : nullptr;
     // Deferred wait (pdl 3) only between two consecutive STEP launches: a reset launch writes all three ring slots, so it
     // and the step after it keep the wait in front of their first store.
-    st.pdl = (e->pdl == 3 && !(mode == 1 && e->last_mode == 1)) ? 1 : e->pdl;
+    st.pdl = (e->pdl == 3 && !(mode == 1 && e->last_mode == 1 && e->last_stream == s)) ? 1 : e->pdl;
     e->last_mode = mode;
+    e->last_stream = s;
     st.dyn_units = e->dyn_units;
     if (e->balance && !e->split) {
         // New boundaries are taken into use two launches after the one that computes them: with overlapped launches
@@ -150,7 +153,9 @@ ahk::StepArgs step_args(ahk_env *e, const ahk::EnvArgs &a, int mode)
 // One pass of the hot path: mode 0 = reset (+ warm-up frames), 1 = step.  Default: ONE fused kernel.
 int run(ahk_env *e, const ahk::EnvArgs &a, int mode, cudaStream_t s)
 {
-    ahk::StepArgs st = step_args(e, a, mode);
+    // a launch that ahk_step_host_results left running on the engine's own stream: order this stream behind it
+    if (e->host_early_ticket >= 0 && s != e->host_stream) AHK_CUDA(cudaStreamWaitEvent(s, e->host_ev[e->host_early_ticket], 0));
+    ahk::StepArgs st = step_args(e, a, mode, s);
     if (!e->split) {
         AHK_CUDA(ahk::launch_step(st, mode, e->step_grid, s));
         e->launches += 1;
@@ -342,7 +347,7 @@ int ahk_step_profiled(ahk_env *e, const uint8_t *robot, const uint8_t *human, vo
         AHK_CUDA(cudaEventElapsedTime(raster_ms, e->ev[0], e->ev[2]));
         return AHK_OK;
     }
-    ahk::StepArgs st = step_args(e, a, 1);
+    ahk::StepArgs st = step_args(e, a, 1, s);
     AHK_CUDA(ahk::launch_env(a, true, s));
     AHK_CUDA(cudaEventRecord(e->ev[1], s));
     if (e->staged) AHK_CUDA(ahk::launch_raster_staged(st.ras, e->raster_grid, s));
@@ -415,6 +420,7 @@ int ahk_step_host_results(ahk_env *e, const uint8_t *robot, const uint8_t *human
     uint64_t seq = 0;
     const int ticket = step_host_enqueue(e, robot, human, reward, done, robot_label, human_label, nullptr, &seq);
     if (ticket < 0) return ticket;
+    e->host_early_ticket = ticket;
     if (seq == 0) return ahk_step_host_wait(e, ticket); // pageable buffers: results arrive with the copies, after the kernel
     const volatile unsigned long long *flag = e->tick_flag_host + (seq & 7u);
     for (unsigned spins = 1; *flag != seq; ++spins) {
@@ -434,6 +440,7 @@ int ahk_host_sync(ahk_env *e)
 {
     if (!e) return fail(AHK_ERR_ARG, "env is NULL");
     AHK_CUDA(cudaStreamSynchronize(e->host_stream));
+    e->host_early_ticket = -1;
     return AHK_OK;
 }
 
@@ -442,6 +449,7 @@ int ahk_step_host_wait(ahk_env *e, int ticket)
     if (!e) return fail(AHK_ERR_ARG, "env is NULL");
     if (ticket < 0 || ticket >= ahk_env::kHostDepth) return fail(AHK_ERR_ARG, "ticket %d out of range", ticket);
     AHK_CUDA(cudaEventSynchronize(e->host_ev[ticket]));
+    if (ticket == e->host_early_ticket) e->host_early_ticket = -1;
     return AHK_OK;
 }
 
@@ -458,6 +466,8 @@ int ahk_observe(ahk_env *e, int format, void *out, void *stream)
     if (int rc = check_ready(e)) return rc;
     if (!out) return fail(AHK_ERR_ARG, "out is NULL");
     if (format < AHK_OBS_U8 || format > AHK_OBS_GRAY_DIFF_F64) return fail(AHK_ERR_ARG, "Processing mode is not supported");
+    if (e->host_early_ticket >= 0 && static_cast<cudaStream_t>(stream) != e->host_stream)
+        AHK_CUDA(cudaStreamWaitEvent(static_cast<cudaStream_t>(stream), e->host_ev[e->host_early_ticket], 0));
     ahk::ObserveArgs a{e->buf.frames, out, e->cfg.n_envs, e->head, format};
     const size_t work = static_cast<size_t>(e->cfg.n_envs) * (format == AHK_OBS_GRAY_DIFF_F64 ? 1024 : 3 * ahk::kFrameVecs);
     size_t grid = (work + 255) / 256;

@@ -905,6 +905,97 @@ __global__ void __launch_bounds__(256) gray_diff_kernel(const uint8_t *__restric
     }
 }
 
+// ------------------------------------------------------------------------------------------------ device: fold + pack
+// ahk_policy_set_weights_dev: the same folding and packing as the host path below (load_rgb_weights), from float32
+// Keras-layout weights that already live in device memory — after an optimizer step nothing has to cross PCIe.
+struct DevWeights { const float *f[24]; }; // ahk_policy_weights with device pointers, same order
+
+__device__ __forceinline__ float bn_scale(const float *gamma, const float *var, int c) { return __fdiv_rn(gamma[c], __fsqrt_rn(__fadd_rn(var[c], 1e-3f))); }
+__device__ __forceinline__ float bn_shift(const float *gamma, const float *beta, const float *mean, const float *var, int c)
+{
+    return __fsub_rn(beta[c], __fmul_rn(mean[c], bn_scale(gamma, var, c)));
+}
+__device__ __forceinline__ uint16_t dev_bf16(float v) { return __bfloat16_as_ushort(__float2bfloat16_rn(v)); }
+
+// layer 1 conv2, 2 conv3, 3 dense1, 4 dense2, 5 out: folded value of GEMM element (k, col), 0 in the padding
+template <int L> __device__ __forceinline__ float folded(const DevWeights &w, int k, int col)
+{
+    if (L == 1) { // k = (ky*4+kx)*8 + c, BN1 folded
+        const int tap = k >> 3, c = k & 7;
+        return c < 5 ? __fmul_rn(w.f[6][(tap * 5 + c) * 32 + col], bn_scale(w.f[2], w.f[5], c)) : 0.0f;
+    }
+    if (L == 2) return __fmul_rn(w.f[12][k * 64 + col], bn_scale(w.f[8], w.f[11], k & 31)); // k = tap*32 + c, BN2 folded
+    if (L == 3) { // ours k = pixel*64 + c; Keras flatten index c*64 + pixel; BN3 folded
+        const int px = k >> 6, c = k & 63;
+        return __fmul_rn(w.f[18][static_cast<size_t>(c * 64 + px) * 512 + col], bn_scale(w.f[14], w.f[17], c));
+    }
+    if (L == 4) return w.f[20][k * 512 + col];
+    return col < 10 ? w.f[22][k * 10 + col] : 0.0f;
+}
+
+template <int L> __global__ void __launch_bounds__(256) pack_b_kernel(DevWeights w, uint16_t *__restrict__ out, int k_total, int n_pad, int n_split)
+{
+    const int total = k_total * n_pad * n_split, groups = n_pad / 8;
+    for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
+        const int n = idx % n_pad, k = (idx / n_pad) % k_total, sp = idx / (n_pad * k_total); // consecutive threads: consecutive columns
+        const int ch = k / kBK, kc = (k % kBK) / 8, ke = k % 8;
+        const size_t at = ((static_cast<size_t>(sp) * (k_total / kBK) + ch) * 8 + kc) * groups * 64 + static_cast<size_t>(n / 8) * 64 + (n % 8) * 8 + ke;
+        out[at] = dev_bf16(folded<L>(w, k, sp * n_pad + n));
+    }
+}
+
+// biases: layer 0 conv1 b - sum(W) (normalisation folded), 1..3 b + sum(W * BN shift of the input channel), 4, 5 copies
+__global__ void __launch_bounds__(128) fold_bias_kernel(DevWeights w, float *b0, float *b1, float *b2, float *b3, float *b4, float *b5)
+{
+    const int layer = blockIdx.y, o = blockIdx.x * blockDim.x + threadIdx.x;
+    if (layer == 0) {
+        if (o >= 16) return;
+        double sum = 0.0;
+        if (o < 5) for (int i = 0; i < 576; ++i) sum += static_cast<double>(w.f[0][i * 5 + o]);
+        b0[o] = o < 5 ? __fsub_rn(w.f[1][o], static_cast<float>(sum)) : 0.0f;
+    } else if (layer == 1) {
+        if (o >= 32) return;
+        double add = 0.0;
+        for (int i = 0; i < 80; ++i) add += static_cast<double>(w.f[6][i * 32 + o]) * static_cast<double>(bn_shift(w.f[2], w.f[3], w.f[4], w.f[5], i % 5));
+        b1[o] = __fadd_rn(w.f[7][o], static_cast<float>(add));
+    } else if (layer == 2) {
+        if (o >= 64) return;
+        double add = 0.0;
+        for (int i = 0; i < 512; ++i) add += static_cast<double>(w.f[12][i * 64 + o]) * static_cast<double>(bn_shift(w.f[8], w.f[9], w.f[10], w.f[11], i & 31));
+        b2[o] = __fadd_rn(w.f[13][o], static_cast<float>(add));
+    } else if (layer == 3) {
+        if (o >= 512) return;
+        double add = 0.0;
+        for (int i = 0; i < 4096; ++i) add += static_cast<double>(w.f[18][static_cast<size_t>(i) * 512 + o]) * static_cast<double>(bn_shift(w.f[14], w.f[15], w.f[16], w.f[17], i >> 6));
+        b3[o] = __fadd_rn(w.f[19][o], static_cast<float>(add));
+    } else if (layer == 4) {
+        if (o < 512) b4[o] = w.f[21][o];
+    } else {
+        if (o < 16) b5[o] = o < 10 ? w.f[23][o] : 0.0f;
+    }
+}
+
+// conv1 in Toeplitz form (pack_conv1_toeplitz below): one thread per (plane, class, kernel-row group, phase, output, channel, kx)
+__global__ void __launch_bounds__(256) pack_conv1_kernel(DevWeights w, uint16_t *__restrict__ out)
+{
+    constexpr int N = 144;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= 9 * 3 * 3 * 3 * 3 * 5 * 8) return;
+    int r = idx;
+    const int kx = r % 8; r /= 8;
+    const int ch = r % 5; r /= 5;
+    const int j = r % 3; r /= 3;
+    const int ph = r % 3; r /= 3;
+    const int kv = r % 3; r /= 3;
+    const int cls = r % 3; r /= 3;
+    const int plane = r;
+    const int ky = cls + 3 * kv;
+    const int k = kx + ph + 3 * j, n = kv * 48 + ph * 16 + j * 5 + ch;
+    if (ky >= 8 || k >= 16) return;
+    const size_t at = static_cast<size_t>(plane * 3 + cls) * (16 * N) + (k / 8) * (8 * N) + (n / 8) * 64 + (n % 8) * 8 + (k % 8);
+    out[at] = dev_bf16(__fdiv_rn(w.f[0][((ky * 8 + kx) * 9 + plane) * 5 + ch], 128.0f));
+}
+
 // ------------------------------------------------------------------------------------------------ host: fold + pack
 uint16_t to_bf16(float f)
 { // round to nearest even
@@ -1135,6 +1226,31 @@ int ahk_policy_set_weights(ahk_policy *p, const ahk_policy_weights *w)
     POL_CUDA(cudaSetDevice(p->device));
     POL_CUDA(cudaDeviceSynchronize()); // forward passes in flight still read the old weights
     return load_rgb_weights(p, w);
+}
+
+int ahk_policy_set_weights_dev(ahk_policy *p, const ahk_policy_weights *w_dev, void *stream)
+{
+    if (!p || !w_dev) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_set_weights_dev: NULL argument");
+    if (p->gray) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_set_weights_dev: handle holds the 'gray-diff' network");
+    DevWeights w;
+    const float *const *fields = reinterpret_cast<const float *const *>(w_dev);
+    for (int i = 0; i < 24; ++i) {
+        if (!fields[i]) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_set_weights_dev: every weight pointer must be non-NULL");
+        w.f[i] = fields[i];
+    }
+    POL_CUDA(cudaSetDevice(p->device));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    POL_CUDA(cudaMemsetAsync(p->w1t, 0, static_cast<size_t>(27) * 16 * 144 * 2, s)); // the Toeplitz bands leave zeros between them
+    pack_conv1_kernel<<<(9 * 3 * 3 * 3 * 3 * 5 * 8 + 255) / 256, 256, 0, s>>>(w, p->w1t);
+    pack_b_kernel<1><<<16, 256, 0, s>>>(w, p->w[1], 128, 32, 1);
+    pack_b_kernel<2><<<128, 256, 0, s>>>(w, p->w[2], 512, 64, 1);
+    pack_b_kernel<3><<<p->sms * 8, 256, 0, s>>>(w, p->w[3], 4096, 256, 2);
+    pack_b_kernel<4><<<p->sms * 4, 256, 0, s>>>(w, p->w[4], 512, 256, 2);
+    pack_b_kernel<5><<<32, 256, 0, s>>>(w, p->w[5], 512, 16, 1);
+    fold_bias_kernel<<<dim3(4, 6), 128, 0, s>>>(w, p->b[0], p->b[1], p->b[2], p->b[3], p->b[4], p->b[5]);
+    POL_CUDA(cudaGetLastError());
+    p->launches += 8;
+    return AHK_OK;
 }
 
 int ahk_policy_gray_create(int device, int max_batch, const ahk_policy_gray_weights *w, ahk_policy **out)

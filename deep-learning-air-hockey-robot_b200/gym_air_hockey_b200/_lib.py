@@ -68,6 +68,7 @@ SYMBOLS = {
     "ahk_policy_create": (_i, [_i, _i, C.POINTER(PolicyWeights), C.POINTER(_vp)]),
     "ahk_policy_gray_create": (_i, [_i, _i, C.POINTER(GrayPolicyWeights), C.POINTER(_vp)]),
     "ahk_policy_set_weights": (_i, [_vp, C.POINTER(PolicyWeights)]),
+    "ahk_policy_set_weights_dev": (_i, [_vp, C.POINTER(PolicyWeights), _vp]),
     "ahk_replay_gather": (_i, [_vp, _i, _i, _vp, _vp, _i, _vp, _vp]),
     "ahk_rl_ddqn_targets": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, C.c_double, _vp, _vp, _vp, _vp, _vp]),
     "ahk_rl_pg_returns": (_i, [_vp, _vp, _i, _i, C.c_double, _vp, _vp]),

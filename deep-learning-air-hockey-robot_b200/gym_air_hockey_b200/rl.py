@@ -75,6 +75,22 @@ class TrainableNetwork(nn.Module):
                 lin.weight.copy_(torch.from_numpy(np.ascontiguousarray(np.asarray(w[name + '_w'], dtype=np.float32).T)))
                 lin.bias.copy_(torch.from_numpy(np.asarray(w[name + '_b'], dtype=np.float32)))
 
+    def keras_weights_device(self):
+        """-> dict of contiguous float32 tensors on the module's device, in Keras layouts (policy.SHAPES)."""
+        w = {}
+        with torch.no_grad():
+            for i in (1, 2, 3):
+                conv, bn = getattr(self, 'conv%d' % i), getattr(self, 'bn%d' % i)
+                w['conv%d_w' % i] = conv.weight.permute(2, 3, 1, 0).contiguous()
+                w['conv%d_b' % i] = conv.bias.contiguous()
+                w['bn%d_gamma' % i], w['bn%d_beta' % i] = bn.weight.contiguous(), bn.bias.contiguous()
+                w['bn%d_mean' % i], w['bn%d_var' % i] = bn.running_mean.contiguous(), bn.running_var.contiguous()
+            for name in ('dense1', 'dense2', 'out'):
+                lin = getattr(self, name)
+                w[name + '_w'] = lin.weight.t().contiguous()
+                w[name + '_b'] = lin.bias.contiguous()
+        return w
+
     def keras_weights(self):
         """-> dict of float32 numpy arrays in Keras layouts (what model.get_weights() would list; policy.SHAPES)."""
         w = {}
@@ -247,9 +263,18 @@ class Agent(object):
         self.action_distribution += torch.bincount(action.long(), minlength=self.n_actions)
         return action
 
-    def push_weights(self, policy=None):
-        """The fitted network -> the forward kernels (ahk_policy_set_weights)."""
+    def push_weights(self, policy=None, on_device=True):
+        """The fitted network -> the forward kernels.  on_device: the module's parameters are laid out the Keras way by a
+        few torch transposes and folded / packed by kernels on the current stream (ahk_policy_set_weights_dev, ~0.1 ms);
+        otherwise through host memory (ahk_policy_set_weights: D2H, host packing, H2D, a device synchronisation, ~14 ms)."""
         policy = policy or self.policy
+        if on_device:
+            w = self.model.keras_weights_device()
+            st = _lib.PolicyWeights()
+            for name, _ in SHAPES:
+                setattr(st, name, C.c_void_p(w[name].data_ptr()))
+            _lib.check(self.lib.ahk_policy_set_weights_dev(policy._h, C.byref(st), _stream(self.device)))
+            return
         w = self.model.keras_weights()
         st = _lib.PolicyWeights()
         for name, _ in SHAPES:

@@ -177,6 +177,11 @@ int ahk_policy_forward_profiled(ahk_policy *p, const uint8_t *frames_dev, int n,
  * the forward kernels every training interval.  Waits for the device first (forward passes in flight read the old ones). */
 int ahk_policy_set_weights(ahk_policy *p, const ahk_policy_weights *w);
 
+/* The same with float32 Keras-layout weights that already live in DEVICE memory (w_dev holds device pointers): folded and
+ * packed by kernels on `stream`, stream-ordered with the forward passes around it — after an optimizer step on the device
+ * nothing crosses PCIe. */
+int ahk_policy_set_weights_dev(ahk_policy *p, const ahk_policy_weights *w_dev, void *stream);
+
 /* ---- batched RL step: ai/reinforcement/rl_agents.py around the CNN, on the device ----
  * Replay memory ≙ Agent.experience_buffer (rl_agents.py:61-62,88-90), kept as a time-ordered store of single uint8
  * frames, store_dev [capacity][n][3][128][128] (slot = step index mod capacity; the newest ring slot of every env is

@@ -306,6 +306,12 @@ def test_step_host_results_early_return(cuda, table, n):
         assert np.array_equal(info['robot_action'].cpu().numpy(), out['robot_action']), t
         assert np.array_equal(info['human_action'].cpu().numpy(), out['human_action']), t
         act[:] = (out['human_action'] + out['robot_action'] + t) % 10   # the next actions depend on this step's results
+    # a device-path call on another stream is ordered behind the launch still rasterising on the engine's stream
+    _, reward, _, _ = a.step(None, None)
+    _, reward_b, _, _ = b.step(None, None)
+    obs_b = b.observation('u8')
+    assert np.array_equal(reward.cpu().numpy(), reward_b.cpu().numpy())
+    assert np.array_equal(a.observation('u8').cpu().numpy(), obs_b.cpu().numpy())
     b.host_sync()
     cuda.cuda.synchronize()
     assert b.head == a.head

@@ -218,6 +218,29 @@ def test_set_weights_reaches_the_forward_kernels(cuda, table):
 
 
 @pytest.mark.gpu
+def test_set_weights_dev_equals_host_path(cuda):
+    """ahk_policy_set_weights_dev (fold + pack by kernels, from device tensors) leaves the forward kernels with the same
+    network as the host path: weights are bit-identical bf16, biases differ at most by the order of a float64 sum."""
+    import ctypes as C
+    torch = cuda
+    from gym_air_hockey_b200 import _lib
+    from gym_air_hockey_b200.policy import SHAPES, PolicyNetwork, keras_default_init
+    from gym_air_hockey_b200.rl import TrainableNetwork
+    w0, w1 = keras_default_init(seed=1, randomize_bn=True), keras_default_init(seed=2, randomize_bn=True)
+    host, dev = PolicyNetwork(w1, max_batch=64), PolicyNetwork(w0, max_batch=64)
+    module = TrainableNetwork(w1).cuda()
+    wd = module.keras_weights_device()
+    st = _lib.PolicyWeights()
+    for name, _ in SHAPES:
+        setattr(st, name, C.c_void_p(wd[name].data_ptr()))
+    _lib.check(dev.lib.ahk_policy_set_weights_dev(dev._h, C.byref(st), None))
+    frames = torch.from_numpy(np.random.RandomState(0).randint(0, 256, size=(3, 50, 3, 128, 128)).astype(np.uint8)).cuda()
+    a = host.forward_ring(frames, 1)[0].cpu().numpy()
+    b = dev.forward_ring(frames, 1)[0].cpu().numpy()
+    assert np.abs(a - b).max() <= 1e-5 * np.abs(a).max(), np.abs(a - b).max()
+
+
+@pytest.mark.gpu
 def test_ddqn_training_loop(cuda, table):
     """train.py:76-118 batched: act / step / store / train every 5 iterations / target copy.  The fitted weights must
     reach the forward kernels (their Q values track the float32 module) and the losses must be finite."""

@@ -60,6 +60,13 @@ __device__ __forceinline__ void env_update(const EnvArgs &a, int i, uint4 (&rec)
 {
     Sim s;
     uint32_t reset_count, noise_count, meta;
+    // The caller's actions are fetched with the state, not where they are used: through ahk_step_host they sit in mapped host
+    // memory, and a PCIe round trip issued now is over by the time the reset branch and the AI have run.
+    uint32_t robot_in = kActNone, human_in = kActNone;
+    if (kStep) {
+        if (a.robot) robot_in = a.robot[i];
+        if (a.human) human_in = a.human[i];
+    }
     load_sim(a.state, a.n, i, s, reset_count, noise_count, meta);
     if (stamps) stamps[0] = static_cast<long long>(__float_as_uint(s.puck.x) + meta) * 0 + clock64();
     uint32_t steps = meta & 0xFFFFu, episode = (meta >> 16) & 3u, use = (meta >> 18) & 7u, pending = (meta >> 21) & 1u;
@@ -109,8 +116,7 @@ __device__ __forceinline__ void env_update(const EnvArgs &a, int i, uint4 (&rec)
     }
 
     if (kStep) { // ≙ AirHockeyEnv.step, air_hockey_env.py:84-155
-        const uint32_t robot = a.robot ? a.robot[i] : kActNone;
-        const uint32_t human = a.human ? a.human[i] : kActNone;
+        const uint32_t robot = robot_in, human = human_in;
         Tick t;
         sim_tick(s, robot, human, use, env_id, a.key, t);
         if (stamps) stamps[1] = static_cast<long long>(t.info + __float_as_uint(s.puck.x)) * 0 + clock64();

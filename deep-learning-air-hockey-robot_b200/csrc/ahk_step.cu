@@ -414,8 +414,7 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_kernel(StepArgs a)
 #pragma unroll
             for (int b = 0; b < 3; ++b) rec[b] = __ldg(dl + b * stride + i);
         }
-        if (a.env.h_tick_flag) __threadfence_system(); // outputs written to mapped host memory: ordered before the flag below
-        else if (a.pdl) __threadfence(); // this thread's state and outputs are out before the barrier below, hence before the trigger
+        if (a.pdl) __threadfence(); // this thread's state and outputs are out before the barrier below, hence before the trigger
         if (kTrace && lane == 0 && base == lo) trace[1] = global_ns();
         // compact the valid records into shared memory: one atomic per warp per ring slot.  Records of the newest frame
         // grow from the bottom of the list, records that rewrite the two older slots (warm-up frames after a reset) from
@@ -444,7 +443,10 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_kernel(StepArgs a)
         if (a.pdl && base + kStepThreads >= hi) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
         // ahk_step_host_results: the host is waiting for reward / done / labels, not for the frames.  The last CTA to finish
         // its game ticks tells it so through mapped host memory; rasterising goes on underneath.
-        if (a.env.h_tick_flag != nullptr && tid == 0 && base + kStepThreads >= hi) {
+        // One thread of the LAST warp does it: the system-scope fence (a PCIe round trip; cumulative over the outputs the
+        // other threads wrote before the barrier above) then delays that one warp's first unit claim, not the CTA's raster.
+        if (a.env.h_tick_flag != nullptr && tid == kStepThreads - 32 && base + kStepThreads >= hi) {
+            __threadfence_system();
             const unsigned slot = static_cast<unsigned>(a.env.tick_seq & 7ull);
             if (atomicAdd(a.env.tick_count + slot, 1u) == gridDim.x - 1u) {
                 a.env.tick_count[slot] = 0u;

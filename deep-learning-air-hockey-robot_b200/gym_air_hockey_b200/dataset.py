@@ -6,8 +6,8 @@ Reference: one env, `env.step()` with no actions (the programmed AI plays both s
 a goal or every 200 steps (`:57-58`), states as float32 (n, 9, 128, 128) normalised `(x-128)/128`, labels int8, one
 HDF5 file `<time>_<mode>_<n>.h5` (`:68-73`).  Here: the batched engine with `auto_reset` and `max_episode_steps=200`
 plays the same protocol per env; every step the stacked observation of all envs is materialised on the GPU
-(`ahk_observe`), copied to one of two pinned host buffers on a side stream while the next step runs, and appended to
-the output by a writer thread.  `h5py` is not installed in this image, so the container is chosen at run time: HDF5
+(`ahk_observe`), copied to one of two pinned host buffers on a side stream while the next step runs, copied once more into
+the current shard's buffer by a writer thread, and full shards are written by a pool of saver threads.  `h5py` is not installed in this image, so the container is chosen at run time: HDF5
 through h5py when it imports, else `.npz` shards holding the same three arrays (`load_data` reads either).
 
 Sample order is step-major: sample `t * n_envs + e` is env `e` after step `t`.  `states='u8'` keeps the uint8 stack
@@ -72,29 +72,52 @@ def load_data(data_file, normalise=False):
 
 
 class _Writer(threading.Thread):
-    """Appends finished host buffers to shards of `shard_states` samples; runs beside the generation loop."""
+    """Fills shard buffers of `shard_states` samples straight from the pinned host buffers (one copy per sample, no
+    concatenation) and hands every full shard to a small pool of saver threads — the container write (`np.savez`: CRC32
+    + file I/O, both release the GIL) of one shard runs beside the filling of the next ones.  At most `savers` shards are
+    being written at any time, which bounds the host memory to (savers + 1) shards."""
 
-    def __init__(self, out_dir, mode, shard_states, when, ext):
+    def __init__(self, out_dir, mode, shard_states, when, ext, total_states, savers=4):
         super().__init__(daemon=True)
         self.out_dir, self.mode, self.shard_states, self.when, self.ext = out_dir, mode, shard_states, when, ext
+        self.total = int(total_states)
         self.q = queue.Queue(maxsize=2)
         self.files, self.error = [], None
-        self._acc, self._count, self._shard = [], 0, 0
+        self._named = {}
+        self._buf, self._fill, self._shard, self._done = None, 0, 0, 0
+        self._slots = threading.Semaphore(max(1, int(savers)))
+        self._savers = []
+        self._lock = threading.Lock()
+
+    def _capacity(self):
+        left = self.total - self._done
+        return min(self.shard_states, left) if self.shard_states else left
+
+    def _save(self, shard, states, robot, human):
+        try:
+            name = data_file_name(self.mode, len(states), self.when, self.ext)
+            if shard or self.shard_states:
+                base, ext = os.path.splitext(name)
+                name = '%s_part%04d%s' % (base, shard, ext)
+            path = os.path.join(self.out_dir, name)
+            save_data(path, states, robot, human)
+            with self._lock:
+                self._named[shard] = path
+        except Exception as e:  # surfaced by generate()
+            self.error = e
+        finally:
+            self._slots.release()
 
     def _flush(self):
-        if not self._acc:
+        if self._buf is None or self._fill == 0:
             return
-        states = np.concatenate([a[0] for a in self._acc])
-        robot = np.concatenate([a[1] for a in self._acc])
-        human = np.concatenate([a[2] for a in self._acc])
-        name = data_file_name(self.mode, len(states), self.when, self.ext)
-        if self._shard or self.shard_states:
-            base, ext = os.path.splitext(name)
-            name = '%s_part%04d%s' % (base, self._shard, ext)
-        path = os.path.join(self.out_dir, name)
-        save_data(path, states, robot, human)
-        self.files.append(path)
-        self._acc, self._count, self._shard = [], 0, self._shard + 1
+        states, robot, human = (a[:self._fill] for a in self._buf)
+        self._slots.acquire()
+        t = threading.Thread(target=self._save, args=(self._shard, states, robot, human), daemon=True)
+        t.start()
+        self._savers.append(t)
+        self._done += self._fill
+        self._buf, self._fill, self._shard = None, 0, self._shard + 1
 
     def run(self):
         try:
@@ -103,12 +126,24 @@ class _Writer(threading.Thread):
                 if item is None:
                     break
                 states, robot, human, release = item
-                self._acc.append((states.copy(), robot.copy(), human.copy()))
+                at = 0
+                while at < len(robot):
+                    if self._buf is None:
+                        cap = self._capacity()
+                        self._buf = (np.empty((cap,) + states.shape[1:], dtype=states.dtype),
+                                     np.empty((cap,), dtype=robot.dtype), np.empty((cap,), dtype=human.dtype))
+                    k = min(len(robot) - at, len(self._buf[1]) - self._fill)
+                    for dst, src in zip(self._buf, (states, robot, human)):
+                        dst[self._fill:self._fill + k] = src[at:at + k]
+                    self._fill += k
+                    at += k
+                    if self._fill == len(self._buf[1]):
+                        self._flush()
                 release.set()  # the pinned buffer may be refilled
-                self._count += len(robot)
-                if self.shard_states and self._count >= self.shard_states:
-                    self._flush()
             self._flush()
+            for t in self._savers:
+                t.join()
+            self.files = [self._named[k] for k in sorted(self._named)]
         except Exception as e:  # surfaced by generate()
             self.error = e
             while self.q.get() is not None:
@@ -116,7 +151,7 @@ class _Writer(threading.Thread):
 
 
 def generate(env, n_states, out_dir, states='f32', shard_states=0, when=None, keep_in_memory=False,
-             label_random_as_undefined=False):
+             label_random_as_undefined=False, writer_threads=4):
     """Run the data-generation loop on `env` (a BatchedAirHockeyEnv built with auto_reset=True, max_episode_steps=200)
     until at least n_states samples exist (whole steps: ceil(n_states / n_envs) * n_envs samples are produced and the
     surplus dropped), writing `states` / `robot_actions` / `human_actions`.
@@ -126,6 +161,7 @@ def generate(env, n_states, out_dir, states='f32', shard_states=0, when=None, ke
     label_random_as_undefined: samples of `random` episodes (pure-noise frames, air_hockey_env.py:73-74,147-151; one reset
     in twenty, :28) get label 9 = "Undefined" on both sides — the class the reference only obtains by mixing foreign
     images into the data afterwards (mix_random_images_with_data.py:44-71).
+    writer_threads: shards written concurrently (host memory: writer_threads + 1 shards).
     -> dict(files, samples, seconds, samples_per_s, bytes_to_host).  keep_in_memory also returns the arrays (tests)."""
     if states not in ('f32', 'u8'):
         raise ValueError("states must be 'f32' or 'u8'")
@@ -149,7 +185,7 @@ def generate(env, n_states, out_dir, states='f32', shard_states=0, when=None, ke
                       'ready': torch.cuda.Event(), 'free': threading.Event()})
         slots[-1]['free'].set()
     del probe
-    writer = _Writer(out_dir, mode, int(shard_states), when, None)
+    writer = _Writer(out_dir, mode, int(shard_states), when, None, int(n_states), savers=writer_threads)
     writer.start()
     kept = []
     t0 = time.perf_counter()

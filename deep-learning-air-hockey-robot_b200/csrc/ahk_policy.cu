@@ -689,6 +689,7 @@ constexpr int kProducers = 128, kCta = kProducers + 32 + 128;
 // tile) runs three CTAs per SM with a short pipeline each, conv3 (64 KB of weights) one CTA with a deep one.
 template <int L> struct Cfg { static constexpr int kStages = 8, kDepth = 6, kPerSm = 1; };
 template <> struct Cfg<kConv2> { static constexpr int kStages = 4, kDepth = 2, kPerSm = 3; };
+template <> struct Cfg<kG2> { static constexpr int kStages = 4, kDepth = 2, kPerSm = 2; }; // 16 KB of weights, 4 chunks per tile
 // K-core pitch of the A stage: 16 bytes more than the 16 row groups, so that the 8 lanes that fetch one row's 8 K cores
 // (128 contiguous global bytes: one L1 wavefront instead of two half-used ones) land in 8 different bank groups
 constexpr int kLbo = 16 * 128 + 16, kStage = 8 * kLbo;
@@ -727,7 +728,8 @@ __global__ void __launch_bounds__(ws::kCta, ws::Cfg<L>::kPerSm) conv_ws_kernel(A
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (tid < N) s_bias[tid] = a.bias[tid];
-    if (warp == kProducers / 32) tmem_alloc(&s_tmem, 2 * (N < 32 ? 32 : N));
+    constexpr uint32_t kBufCols = N <= 32 ? 32 : (N <= 64 ? 64 : 128); // one accumulator; the allocation (two of them) must be a power of two
+    if (warp == kProducers / 32) tmem_alloc(&s_tmem, 2 * kBufCols);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -759,9 +761,18 @@ __global__ void __launch_bounds__(ws::kCta, ws::Cfg<L>::kPerSm) conv_ws_kernel(A
                         if (L == kConv2) {
                             const int s = row / kP2, p = row - s * kP2, y = p / kC2, x = p - y * kC2;
                             r0[i] = (s * kP1 + 2 * y * kC1 + 2 * x) * kAct1C;
-                        } else {
+                        } else if (L == kConv3) {
                             const int s = row / kP3, p = row - s * kP3, y = p / kC3, x = p - y * kC3;
                             r0[i] = (s * kP2 + 2 * y * kC2 + 2 * x) * 32;
+                        } else if (L == kG2) { // 16 channels, stride 2
+                            const int s = row / kGP2, p = row - s * kGP2, y = p / kGS2, x = p - y * kGS2;
+                            r0[i] = (s * kGP1 + 2 * y * kGS1 + 2 * x) * 16;
+                        } else if (L == kG3) { // 32 channels (24 real), stride 1
+                            const int s = row / kGP3, p = row - s * kGP3, y = p / kGS3, x = p - y * kGS3;
+                            r0[i] = (s * kGP2 + y * kGS2 + x) * 32;
+                        } else { // kG4
+                            const int s = row / kGP4, p = row - s * kGP4, y = p / kGS4, x = p - y * kGS4;
+                            r0[i] = (s * kGP3 + y * kGS3 + x) * 32;
                         }
                     }
                 }
@@ -770,8 +781,15 @@ __global__ void __launch_bounds__(ws::kCta, ws::Cfg<L>::kPerSm) conv_ws_kernel(A
             if (c >= kStages) mbar_wait(&s_empty[st], ((c / kStages) - 1) & 1);
             const int kc = ch * 8 + kc_lane;
             int off;
+            // the same K order as gather<L>: a chunk of 8 K cores is 128 contiguous bytes of the input (conv2, kG2: the four
+            // pixels of one kernel row; 32-channel inputs: two adjacent pixels)
             if (L == kConv2) off = ((kc >> 2) * kC1 + (kc & 3)) * kAct1C;
-            else { const int tap = kc >> 2; off = ((tap >> 2) * kC2 + (tap & 3)) * 32 + (kc & 3) * 8; }
+            else if (L == kG2) { const int tap = kc >> 1; off = ((tap >> 2) * kGS1 + (tap & 3)) * 16 + (kc & 1) * 8; }
+            else {
+                constexpr int kSide = L == kConv3 ? kC2 : (L == kG3 ? kGS2 : kGS3);
+                const int tap = kc >> 2;
+                off = ((tap >> 2) * kSide + (tap & 3)) * 32 + (kc & 3) * 8;
+            }
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
                 const bool v = (ok >> i) & 1u;
@@ -790,7 +808,6 @@ __global__ void __launch_bounds__(ws::kCta, ws::Cfg<L>::kPerSm) conv_ws_kernel(A
             mbar_wait(&s_wfull, 0);
             constexpr uint32_t kIdesc = instr_desc(N);
             const uint32_t b_base = smem_u32(s_b);
-            constexpr uint32_t kBufCols = N < 32 ? 32 : N;
             int c = 0;
             for (int t = 0; t < my_tiles; ++t) {
                 const uint32_t buf = t & 1;
@@ -815,7 +832,6 @@ __global__ void __launch_bounds__(ws::kCta, ws::Cfg<L>::kPerSm) conv_ws_kernel(A
     } else {
         // ---------------------------------------------------------------- epilogue: thread = TMEM lane = tile row
         const int q4 = warp & 3;
-        constexpr uint32_t kBufCols = N < 32 ? 32 : N;
         for (int t = 0; t < my_tiles; ++t) {
             const int tile = blockIdx.x + t * gridDim.x;
             const uint32_t buf = t & 1;
@@ -848,7 +864,7 @@ __global__ void __launch_bounds__(ws::kCta, ws::Cfg<L>::kPerSm) conv_ws_kernel(A
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == kProducers / 32) tmem_dealloc(tmem, 2 * (N < 32 ? 32 : N));
+    if (warp == kProducers / 32) tmem_dealloc(tmem, 2 * kBufCols);
 }
 
 template <int L>
@@ -1372,13 +1388,13 @@ static int policy_forward(ahk_policy *p, const uint8_t *frames, int n, int head,
         POL_CUDA(launch<kG1>(a, tiles(ln * kGP1), 1, p->sms, s));
         if (timed) POL_CUDA(cudaEventRecord(p->ev[1], s));
         a.in = p->ga1; a.weights = reinterpret_cast<const uint4 *>(p->gw[1]); a.bias = p->gb[1]; a.out = p->ga2; a.m_total = n * kGP2;
-        POL_CUDA(launch<kG2>(a, tiles(ln * kGP2), 1, p->sms, s));
+        POL_CUDA(p->legacy_conv ? launch<kG2>(a, tiles(ln * kGP2), 1, p->sms, s) : launch_ws<kG2>(a, tiles(ln * kGP2), p->sms, s));
         if (timed) POL_CUDA(cudaEventRecord(p->ev[2], s));
         a.in = p->ga2; a.weights = reinterpret_cast<const uint4 *>(p->gw[2]); a.bias = p->gb[2]; a.out = p->ga3; a.m_total = n * kGP3;
-        POL_CUDA(launch<kG3>(a, tiles(ln * kGP3), 1, p->sms, s));
+        POL_CUDA(p->legacy_conv ? launch<kG3>(a, tiles(ln * kGP3), 1, p->sms, s) : launch_ws<kG3>(a, tiles(ln * kGP3), p->sms, s));
         if (timed) POL_CUDA(cudaEventRecord(p->ev[3], s));
         a.in = p->ga3; a.weights = reinterpret_cast<const uint4 *>(p->gw[3]); a.bias = p->gb[3]; a.out = p->ga4; a.m_total = n * kGP4;
-        POL_CUDA(launch<kG4>(a, tiles(ln * kGP4), 1, p->sms, s));
+        POL_CUDA(p->legacy_conv ? launch<kG4>(a, tiles(ln * kGP4), 1, p->sms, s) : launch_ws<kG4>(a, tiles(ln * kGP4), p->sms, s));
         if (timed) POL_CUDA(cudaEventRecord(p->ev[4], s));
         a.in = p->ga4; a.weights = reinterpret_cast<const uint4 *>(p->gw[4]); a.bias = p->gb[4]; a.out = p->gh1; a.m_total = n;
         POL_CUDA(launch<kGDense1>(a, tiles(n), 2, p->sms, s));

@@ -71,6 +71,7 @@ __device__ __forceinline__ void env_update(const EnvArgs &a, int i, uint4 (&rec)
     if (stamps) stamps[0] = static_cast<long long>(__float_as_uint(s.puck.x) + meta) * 0 + clock64();
     uint32_t steps = meta & 0xFFFFu, episode = (meta >> 16) & 3u, use = (meta >> 18) & 7u, pending = (meta >> 21) & 1u;
     const uint32_t env_id = a.env_id_base + static_cast<uint32_t>(i);
+    const bool prev_step_reset = kStep && steps == 1u; // the previous step reset this env (or was its first): kDrawDefer
     rec[0] = rec[1] = rec[2] = make_uint4(0, 0, 0, 0);
 
     bool do_reset;
@@ -130,7 +131,7 @@ __device__ __forceinline__ void env_update(const EnvArgs &a, int i, uint4 (&rec)
         } else {
             rec[0] = draw_record(s, use);
         }
-        if (!do_reset && steps == 1u) rec[0].w |= kDrawDefer; // the previous step reset this env (or was its first)
+        if (prev_step_reset) rec[0].w |= kDrawDefer; // also when this step resets again (max_episode_steps == 1)
         steps += 1u;
         if (a.auto_reset && (terminal || (a.max_episode_steps > 0 && steps >= static_cast<uint32_t>(a.max_episode_steps)))) pending = 1u;
 

@@ -126,13 +126,14 @@ def test_forced_episodes_and_masks(cuda, orc, noise_table):
         assert np.array_equal(ring[i], o.ring()), i
 
 
-@pytest.mark.parametrize("n,limit,steps", [(333, 17, 45), (1184, 5, 42)])
+@pytest.mark.parametrize("n,limit,steps", [(333, 17, 45), (1184, 5, 42), (1184, 1, 30)])
 def test_back_to_back_steps_overlap(cuda, orc, noise_table, n, limit, steps):
     """Step kernels launched back to back overlap (the next launch's game tick runs under this launch's rasterising,
     csrc/ahk_step.cu): no host synchronisation for `steps` steps, then state, the whole 3-frame ring, the last step's
     outputs and the statistics must equal the oracle's.  333 envs: a grid smaller than the device, wait before the first
     store; 1184 envs: one CTA per SM, the wait deferred to the end of the kernel, and a reset every 5 steps so that the
-    frames rewriting older ring slots (the ones that must still wait) are exercised in every launch."""
+    frames rewriting older ring slots (the ones that must still wait) are exercised in every launch; limit 1: every env
+    resets in every step, so every frame of every launch is one that has to wait."""
     seed = 21
     env = make_env(n, noise_table, seed=seed, max_episode_steps=limit)
     oracles = oracle_envs(orc, n, noise_table, seed)

@@ -282,6 +282,21 @@ class Agent(object):
         _lib.check(self.lib.ahk_policy_set_weights(policy._h, C.byref(st)))
         policy.weights = w
 
+    def _sync_batchnorm_statistics(self):
+        """With several ranks every rank fits its own batch: gradients are averaged by the bucket, and so are the BatchNorm
+        moving statistics here (one small all-reduce), so that all ranks keep acting with the same network."""
+        import torch.distributed as dist
+        if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(self.group) == 1:
+            return
+        bufs = [b for bn in (self.model.bn1, self.model.bn2, self.model.bn3) for b in (bn.running_mean, bn.running_var)]
+        flat = torch.cat([b.reshape(-1) for b in bufs])
+        dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group)
+        flat /= dist.get_world_size(self.group)
+        at = 0
+        for b in bufs:
+            b.copy_(flat[at:at + b.numel()].reshape(b.shape))
+            at += b.numel()
+
     def _fit(self, obs_u8, backward_from):
         """One `model.fit` batch (rl_agents.py:189,276): training-mode forward, `backward_from(logits) -> (dlogits, loss)`,
         backward, gradient all-reduce over ranks, optimizer step, weights pushed to the forward kernels."""
@@ -293,6 +308,7 @@ class Agent(object):
         logits.backward(dlogits)
         self.bucket.all_reduce(group=self.group)
         self.optimizer.step()
+        self._sync_batchnorm_statistics()
         self.model.eval()
         self.push_weights()
         return loss

@@ -1,5 +1,7 @@
-"""RL-step measurement: the batched train.py loop on one GPU, with its parts timed by CUDA events.
+"""RL-step measurement: the batched train.py loop, with its parts timed by CUDA events.
     python tools/rl_bench.py [--envs 8192] [--steps 200] [--batch 32] [--interval 25] > profiles/rl_<round>.json
+Under torchrun (one rank per GPU, NCCL) every rank runs its own shard of the envs, gradients and BatchNorm statistics are
+all-reduced at every fit, rank 0 prints the line (times = max over ranks) and the ranks' parameters are compared at the end.
 """
 import argparse
 import json
@@ -35,7 +37,12 @@ def main():
     ap.add_argument("--interval", type=int, default=25)    # train.py:47
     ap.add_argument("--buffer-steps", type=int, default=32)
     args = ap.parse_args()
-    env = BatchedAirHockeyEnv(args.envs, seed=0, max_episode_steps=256)
+    import torch.distributed as dist
+    world, rank, local = int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    env = BatchedAirHockeyEnv(args.envs, device=local, seed=0, env_id_base=rank * args.envs, max_episode_steps=256)
     env.reset()
     agent = DDQNAgent(env, buffer_steps=args.buffer_steps, batch_size=args.batch, discount_rate=0.98, eps_min=0.05, eps_max=0.99,
                       eps_decay_steps=100000)
@@ -49,7 +56,7 @@ def main():
     for _ in range(8):
         rollout_step()
     agent.train()
-    out = {"envs": args.envs, "batch": args.batch, "interval": args.interval, "buffer_steps": args.buffer_steps}
+    out = {"n_gpus": world, "envs": args.envs, "batch": args.batch, "interval": args.interval, "buffer_steps": args.buffer_steps}
     out["rollout_step_ms"], _ = timed(rollout_step, 50)                        # act (6 forward kernels) + step + store
     out["act_ms"], _ = timed(agent.act, 20)
     out["store_ms"], _ = timed(lambda: agent.store_experience(agent.greedy, env.reward, env.done), 20)
@@ -71,10 +78,25 @@ def main():
             rollout_step()
             if agent.iteration % args.interval == 0:
                 agent.train()
+    if world > 1:
+        dist.barrier()
     ms, _ = timed(loop)
-    out["loop"] = {"steps": args.steps, "ms": ms, "env_steps_per_s": args.envs * args.steps / ms * 1e3,
-                   "trainings": args.steps // args.interval}
-    print(json.dumps(out))
+    if world > 1:  # max over ranks; all ranks must still hold the same network
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = t.item()
+        flat = torch.cat([p.detach().reshape(-1) for p in agent.model.parameters()] +
+                         [b.reshape(-1) for b in (agent.model.bn1.running_mean, agent.model.bn3.running_var)])
+        lo, hi = flat.clone(), flat.clone()
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        out["max_parameter_spread_across_ranks"] = float((hi - lo).abs().max().item())
+    out["loop"] = {"steps": args.steps, "ms": ms, "env_steps_per_s": world * args.envs * args.steps / ms * 1e3,
+                   "trainings": args.steps // args.interval, "losses_tail": agent.loss_buffer[-3:]}
+    if rank == 0:
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
 
 
 if __name__ == "__main__":

@@ -10,6 +10,7 @@
 
 #include "../../include/ahk.h"
 #include "ahk_kernels.cuh"
+#include "ahk_sim.cuh"
 
 namespace ahk {
 namespace rl {
@@ -163,6 +164,35 @@ __global__ void __launch_bounds__(256) pg_targets_kernel(const float *__restrict
     }
 }
 
+// rl_agents.py:48-56, one draw per env: with probability epsilon a uniform action in [0, 10), else the greedy one.
+// Counter-based like every draw of the engine (SPEC.md §4): Philox keyed by the seed, counter (iteration, 0, GLOBAL env id,
+// 'EPSG'), so the actions do not depend on how the envs are sharded over GPUs.  hist[10] += the actions taken
+// (Agent.action_distribution, rl_agents.py:99).
+__global__ void __launch_bounds__(256) epsilon_greedy_kernel(const uint8_t *__restrict__ greedy, int n, float epsilon, uint2 key,
+                                                             uint32_t env_id_base, uint32_t iteration, uint8_t *__restrict__ action,
+                                                             unsigned long long *__restrict__ hist)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    int a = -1;
+    if (i < n) {
+        const uint4 r = philox(iteration, 0u, env_id_base + static_cast<uint32_t>(i), 0x45505347u, key);
+        a = unit(r.x) < epsilon ? static_cast<int>(__umulhi(r.y, 10u)) : static_cast<int>(greedy[i]);
+        action[i] = static_cast<uint8_t>(a);
+    }
+    if (hist) {
+        __shared__ unsigned s_hist[AHK_N_ACTIONS];
+        if (threadIdx.x < AHK_N_ACTIONS) s_hist[threadIdx.x] = 0u;
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < AHK_N_ACTIONS; ++k) {
+            const unsigned votes = __ballot_sync(0xffffffffu, a == k);
+            if ((threadIdx.x & 31) == 0 && votes) atomicAdd(&s_hist[k], __popc(votes));
+        }
+        __syncthreads();
+        if (threadIdx.x < AHK_N_ACTIONS && s_hist[threadIdx.x]) atomicAdd(hist + threadIdx.x, static_cast<unsigned long long>(s_hist[threadIdx.x]));
+    }
+}
+
 static int rfail(int code, const char *text)
 {
     set_error_text(text);
@@ -197,6 +227,16 @@ int ahk_replay_gather(const uint8_t *store_dev, int capacity, int n, const int32
     replay_gather_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(reinterpret_cast<const uint4 *>(store_dev), capacity, n, t_dev,
                                                                             env_dev, batch, reinterpret_cast<uint4 *>(out_dev));
     return launched("ahk_replay_gather");
+}
+
+int ahk_rl_epsilon_greedy(const uint8_t *greedy_dev, int n, float epsilon, uint64_t seed, uint32_t env_id_base, uint32_t iteration,
+                          uint8_t *action_dev, uint64_t *hist_dev, void *stream)
+{
+    if (!greedy_dev || !action_dev || n <= 0) return rfail(AHK_ERR_ARG, "ahk_rl_epsilon_greedy: bad argument");
+    const uint2 key = make_uint2(static_cast<uint32_t>(seed), static_cast<uint32_t>(seed >> 32));
+    epsilon_greedy_kernel<<<(n + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(greedy_dev, n, epsilon, key, env_id_base, iteration, action_dev,
+                                                                                        reinterpret_cast<unsigned long long *>(hist_dev));
+    return launched("ahk_rl_epsilon_greedy");
 }
 
 int ahk_rl_ddqn_targets(const float *q_dev, const float *q_next_online_dev, const float *q_next_target_dev, const uint8_t *action_dev,

@@ -54,6 +54,7 @@ class BatchedAirHockeyEnv(object):
         self.processor = DataProcessor(mode=mode)
         self.processor.check_mode()
         self.n_envs = int(n_envs)
+        self.env_id_base = int(env_id_base)
         self.device = torch.device('cuda', device if isinstance(device, int) else torch.device(device).index or 0)
         self.obs_format = obs
         self.height = self.width = self.processor.dim

@@ -244,6 +244,7 @@ class Agent(object):
         self.bucket = GradientBucket(self.model.parameters())
         self.gen = torch.Generator(device=self.device)
         self.gen.manual_seed(int(seed))
+        self.seed, self.env_id_base = int(seed), int(getattr(env, 'env_id_base', 0))
         self.action_distribution = torch.zeros(self.n_actions, dtype=torch.int64, device=self.device)
         self.loss_buffer = []
         self.logits = torch.zeros((self.n, 10), dtype=torch.float32, device=self.device)
@@ -256,11 +257,10 @@ class Agent(object):
         """≙ Agent.act (rl_agents.py:92-101) on the env's current ring: forward kernels, then ε-greedy per env."""
         self.iteration += 1
         self.policy.forward(self.env, self.logits, self.greedy)
-        eps = self.epsilon()
-        explore = torch.rand(self.n, device=self.device, generator=self.gen) < eps
-        rand = torch.randint(0, self.n_actions, (self.n,), device=self.device, generator=self.gen, dtype=torch.int64).to(torch.uint8)
-        action = torch.where(explore, rand, self.greedy)
-        self.action_distribution += torch.bincount(action.long(), minlength=self.n_actions)
+        action = torch.empty_like(self.greedy)
+        _lib.check(self.lib.ahk_rl_epsilon_greedy(_ptr(self.greedy), self.n, float(self.epsilon()), self.seed, self.env_id_base,
+                                                  self.iteration & 0xFFFFFFFF, _ptr(action), _ptr(self.action_distribution),
+                                                  _stream(self.device)))
         return action
 
     def push_weights(self, policy=None, on_device=True):

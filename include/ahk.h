@@ -191,6 +191,12 @@ int ahk_policy_set_weights_dev(ahk_policy *p, const ahk_policy_weights *w_dev, v
  * out_dev + batch*AHK_FRAME_BYTES (slots 1..3) with head 2 is s_{t+1}: both go to ahk_policy_forward as they are. */
 int ahk_replay_gather(const uint8_t *store_dev, int capacity, int n, const int32_t *t_dev, const int32_t *env_dev, int batch,
                       uint8_t *out_dev, void *stream);
+/* ≙ the epsilon_greedy policy of Agent.__init__ / Agent.act (rl_agents.py:48-56,92-101) for n envs: action = a uniform draw
+ * in [0, 10) with probability epsilon, else greedy_dev[i] (the argmax ahk_policy_forward wrote).  Draws are Philox4x32-10
+ * keyed by `seed` with counter (iteration, GLOBAL env id), so they do not depend on the sharding.  hist_dev uint64[10]
+ * (nullable) accumulates Agent.action_distribution. */
+int ahk_rl_epsilon_greedy(const uint8_t *greedy_dev, int n, float epsilon, uint64_t seed, uint32_t env_id_base, uint32_t iteration,
+                          uint8_t *action_dev, uint64_t *hist_dev, void *stream);
 /* ≙ DDQNAgent.train (rl_agents.py:177-191), all float[n][10]: q = Q(s), q_next_online = Q(s'), q_next_target =
  * Q_target(s').  targets = q with targets[a] = reward + (1 - done) * discount * q_next_target[argmax q_next_online],
  * clipped to [-1, 1].  Also the Keras mean_squared_error loss of q_fit against targets (loss_dev, one float) and its

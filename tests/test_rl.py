@@ -152,6 +152,36 @@ def test_pg_returns_and_targets_kernels(cuda, T, n):
 
 
 @pytest.mark.gpu
+def test_epsilon_greedy_kernel(cuda):
+    """rl_agents.py:48-56 per env: epsilon 0 -> greedy, 1 -> uniform over the 10 actions, in between the explored fraction
+    is epsilon; draws are keyed by the GLOBAL env id (two shards reproduce the whole) and by the iteration."""
+    torch = cuda
+    _lib, lib, ptr = _lib_and_ptr()
+    n = 200000
+    greedy = torch.full((n,), 7, dtype=torch.uint8, device='cuda')
+
+    def draw(eps, base=0, count=n, it=5, hist=None, g=greedy):
+        out = torch.empty(count, dtype=torch.uint8, device='cuda')
+        _lib.check(lib.ahk_rl_epsilon_greedy(ptr(g), count, eps, 1234, base, it, ptr(out), ptr(hist), None))
+        return out
+
+    assert bool((draw(0.0) == 7).all())
+    hist = torch.zeros(10, dtype=torch.int64, device='cuda')
+    a = draw(1.0, hist=hist)
+    counts = torch.bincount(a.long(), minlength=10)
+    assert torch.equal(counts, hist) and int(a.max()) == 9
+    assert (counts.float() / n - 0.1).abs().max().item() < 0.004          # uniform: 5 sigma at n = 200 000
+    b = draw(0.3)
+    explored = (b != 7).float().mean().item()                              # 0.3 * 0.9 of the draws leave the greedy action
+    assert abs(explored - 0.27) < 0.005
+    whole = draw(0.5)
+    halves = torch.cat([draw(0.5, 0, n // 2, g=greedy[:n // 2]), draw(0.5, n // 2, n - n // 2, g=greedy[n // 2:])])
+    assert torch.equal(whole, halves)                                       # independent of the sharding
+    assert not torch.equal(whole, draw(0.5, it=6))                          # a new iteration, new draws
+    assert torch.equal(whole, draw(0.5))                                    # deterministic
+
+
+@pytest.mark.gpu
 def test_replay_store_windows_are_the_ring(cuda, table):
     """Every sampled transition's gathered frames equal the observation the env actually showed at that step (and the
     next one); windows that would straddle a reset are never sampled."""

@@ -47,10 +47,19 @@ class TrainableNetwork(nn.Module):
         self.conv3, self.bn3 = nn.Conv2d(32, 64, 4, stride=2), nn.BatchNorm2d(64, eps=1e-3, momentum=0.01)
         self.dense1, self.dense2, self.out = nn.Linear(4096, 512), nn.Linear(512, 512), nn.Linear(512, 10)
         self.load_keras(keras_default_init() if weights is None else weights)
+        self.channels_last = False
+
+    def use_channels_last(self):
+        """NHWC memory format for the convolutions (same float32 arithmetic): cuDNN's forward + backward of this network at
+        4096 samples takes 32.8 ms instead of 52.4 (tools/fit_probe.py)."""
+        self.channels_last = True
+        return self.to(memory_format=torch.channels_last)
 
     def forward(self, obs_u8):
         """obs_u8: uint8 [B, 9, 128, 128], newest frame first (processor.py:47-49) -> logits float32 [B, 10]."""
         x = (obs_u8.float() - 128.0) / 128.0  # processor.py:39-42
+        if self.channels_last:
+            x = x.contiguous(memory_format=torch.channels_last)
         x = self.bn1(F.relu(self.conv1(x)))
         x = self.bn2(F.relu(self.conv2(x)))
         x = self.bn3(F.relu(self.conv3(x)))
@@ -238,7 +247,7 @@ class Agent(object):
         self.eps_min, self.eps_max, self.eps_decay_steps = eps_min, eps_max, eps_decay_steps
         self.iteration = 0
         self.group = group
-        self.model = TrainableNetwork(weights).to(self.device)
+        self.model = TrainableNetwork(weights).to(self.device).use_channels_last()
         self.policy = PolicyNetwork(self.model.keras_weights(), max_batch=max(self.n, self.batch_size), device=self.device.index)
         self.replay = ReplayStore(env, buffer_steps)
         self.bucket = GradientBucket(self.model.parameters())

@@ -15,7 +15,7 @@ sys.path.insert(0, os.path.join(ROOT, "deep-learning-air-hockey-robot_b200"))
 import torch  # noqa: E402
 
 from gym_air_hockey_b200 import BatchedAirHockeyEnv  # noqa: E402
-from gym_air_hockey_b200.rl import DDQNAgent  # noqa: E402
+from gym_air_hockey_b200.rl import DDQNAgent, PGAgent, run_training  # noqa: E402
 
 
 def timed(fn, reps=1):
@@ -29,6 +29,25 @@ def timed(fn, reps=1):
     return a.elapsed_time(b) / reps, out
 
 
+def pg_main(args):
+    """PGAgent (rl_agents.py:199-286) batched: `episode_length` rollout steps, then one pass of fits over every recorded
+    sample (returns per episode by ahk_rl_pg_returns, targets and output gradient by ahk_rl_pg_targets)."""
+    if os.environ.get("RL_CUDNN_BENCHMARK"):
+        torch.backends.cudnn.benchmark = True
+    if os.environ.get("RL_TF32"):
+        torch.backends.cuda.matmul.allow_tf32 = True
+    env = BatchedAirHockeyEnv(args.envs, seed=0, max_episode_steps=256)
+    env.reset()
+    agent = PGAgent(env, episode_length=args.episode_length, fit_batch=args.fit_batch, discount_rate=0.98, eps_min=0.05, eps_max=0.99,
+                    eps_decay_steps=100000)
+    run_training(agent, args.episode_length)   # warm-up: one rollout + one training pass
+    steps = 2 * args.episode_length
+    ms, losses = timed(lambda: run_training(agent, steps))
+    print(json.dumps({"agent": "pg", "envs": args.envs, "episode_length": args.episode_length, "fit_batch": args.fit_batch,
+                      "steps": steps, "ms": ms, "env_steps_per_s": args.envs * steps / ms * 1e3,
+                      "samples_fitted_per_s": args.envs * steps / ms * 1e3, "losses": losses}))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--envs", type=int, default=8192)
@@ -36,7 +55,12 @@ def main():
     ap.add_argument("--batch", type=int, default=32)       # train.py:49
     ap.add_argument("--interval", type=int, default=25)    # train.py:47
     ap.add_argument("--buffer-steps", type=int, default=32)
+    ap.add_argument("--agent", choices=["ddqn", "pg"], default="ddqn")
+    ap.add_argument("--episode-length", type=int, default=64)   # pg: steps between fits (train.py:45 uses 256)
+    ap.add_argument("--fit-batch", type=int, default=4096)      # pg: samples per optimizer step
     args = ap.parse_args()
+    if args.agent == "pg":
+        return pg_main(args)
     import torch.distributed as dist
     world, rank, local = int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)

@@ -95,7 +95,10 @@ int ahk_step(ahk_env *env, const uint8_t *robot_dev, const uint8_t *human_dev, v
  * frame_host != NULL, the new uint8 frame [n][3][128][128]) out, then waits.  Any pointer may be NULL.
  * PINNED buffers (cudaHostAlloc / cudaHostRegister, e.g. torch's pin_memory) are read and written by the step kernel
  * itself through their device mapping — 2 bytes in, 7 bytes out per env over PCIe, ONE kernel launch, no copy-engine
- * transfers; pageable buffers go through cudaMemcpyAsync.  The frame, when asked for, is always a copy (49 152 B/env). */
+ * transfers; pageable buffers go through cudaMemcpyAsync.  The frame, when asked for, is always a copy (49 152 B/env).
+ * Stream rule for all ahk_step_host* calls: they run on a stream the engine owns.  Work the engine itself enqueues later on
+ * another stream (ahk_step / ahk_reset / ahk_observe) is ordered behind them; work enqueued EARLIER on another stream is
+ * not waited for — synchronise that stream before switching an env from the device path to the host path. */
 int ahk_step_host(ahk_env *env, const uint8_t *robot_host, const uint8_t *human_host, float *reward_host,
                   uint8_t *done_host, uint8_t *robot_label_host, uint8_t *human_label_host, uint8_t *frame_host);
 

@@ -45,6 +45,8 @@ class GradientBucket(object):
         self.flat = torch.zeros(n, dtype=dtype or first.dtype, device=first.device)
 
     def all_reduce(self, group=None, async_op=False):
+        if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+            return None  # one rank: .grad already holds the average
         offset = 0
         for p in self.params:
             k = p.numel()

@@ -222,8 +222,18 @@ int ahk_replay_gather(const uint8_t *store_dev, int capacity, int n, const int32
         return rfail(AHK_ERR_ARG, "ahk_replay_gather: bad argument (capacity must be >= 4, pointers non-NULL)");
     if ((reinterpret_cast<uintptr_t>(store_dev) | reinterpret_cast<uintptr_t>(out_dev)) & 15)
         return rfail(AHK_ERR_ARG, "ahk_replay_gather: frame buffers must be 16-byte aligned");
+    // persistent over the frames: exactly as many CTAs as are resident at once (a second, partial wave would start its
+    // whole share late)
+    static int resident = 0;
+    if (resident == 0) {
+        int dev = 0, sms = 0, per_sm = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess ||
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, replay_gather_kernel, 256, 0) != cudaSuccess || per_sm < 1)
+            return launched("ahk_replay_gather");
+        resident = sms * per_sm;
+    }
     const long units = 4L * batch;
-    const int grid = static_cast<int>(units < 148L * 8 ? units : 148L * 8);
+    const int grid = static_cast<int>(units < resident ? units : resident);
     replay_gather_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(reinterpret_cast<const uint4 *>(store_dev), capacity, n, t_dev,
                                                                             env_dev, batch, reinterpret_cast<uint4 *>(out_dev));
     return launched("ahk_replay_gather");

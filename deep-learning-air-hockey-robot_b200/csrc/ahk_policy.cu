@@ -1282,6 +1282,7 @@ int ahk_policy_gray_create(int device, int max_batch, const ahk_policy_gray_weig
     p->device = device;
     p->max_batch = max_batch;
     p->gray = true;
+    if (const char *sw = getenv("AHK_CONV23")) p->legacy_conv = strcmp(sw, "tile") == 0; // A/B: conv2-conv4 through layer_kernel
     cudaDeviceGetAttribute(&p->sms, cudaDevAttrMultiProcessorCount, device);
 
     // BatchNorm after the ReLU: y = s * r + t per channel, folded into the next layer

@@ -7,7 +7,9 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <new>
+#include <unordered_map>
 #include <vector>
 
 namespace {
@@ -28,6 +30,29 @@ int fail(int code, const char *fmt, ...)
         cudaError_t err__ = (expr);                                                                         \
         if (err__ != cudaSuccess) return fail(AHK_ERR_CUDA, "%s: %s", #expr, cudaGetErrorString(err__));   \
     } while (0)
+
+// Entry points run on the device of their handle and leave the caller's current device as they found it (two engines on
+// different GPUs in one process, or a torch current device other than cfg.device, must not disturb each other).
+struct DeviceGuard {
+    int prev = -1;
+    bool changed = false;
+    cudaError_t status = cudaSuccess;
+    explicit DeviceGuard(int device)
+    {
+        status = cudaGetDevice(&prev);
+        if (status == cudaSuccess && prev != device) {
+            status = cudaSetDevice(device);
+            changed = status == cudaSuccess;
+        }
+    }
+    ~DeviceGuard() { if (changed) cudaSetDevice(prev); }
+    DeviceGuard(const DeviceGuard &) = delete;
+    DeviceGuard &operator=(const DeviceGuard &) = delete;
+};
+
+#define AHK_ON_DEVICE(dev)                                                                                         \
+    DeviceGuard guard__(dev);                                                                                      \
+    if (guard__.status != cudaSuccess) return fail(AHK_ERR_CUDA, "cudaSetDevice(%d): %s", dev, cudaGetErrorString(guard__.status))
 
 } // namespace
 
@@ -76,6 +101,29 @@ struct ahk_env {
 };
 
 namespace {
+
+// Which engine launched the last step / reset kernel on each stream (any handle of this process).  The deferred
+// griddepcontrol.wait (pdl 3) is only valid when the previous programmatic launch on the stream was THIS engine's own step
+// ("a CTA of launch k runs => launch k-2 is complete" counts launches of one engine); two engines
+// alternating on one stream see each other here and keep the wait in front of their first store (pdl 1).
+std::mutex g_stream_mu;
+std::unordered_map<cudaStream_t, const ahk_env *> g_stream_owner;
+
+bool own_previous_launch(const ahk_env *e, cudaStream_t s)
+{
+    std::lock_guard<std::mutex> lock(g_stream_mu);
+    auto it = g_stream_owner.find(s);
+    const bool own = it != g_stream_owner.end() && it->second == e;
+    g_stream_owner[s] = e;
+    return own;
+}
+
+void forget_engine(const ahk_env *e)
+{
+    std::lock_guard<std::mutex> lock(g_stream_mu);
+    for (auto it = g_stream_owner.begin(); it != g_stream_owner.end();)
+        it = it->second == e ? g_stream_owner.erase(it) : std::next(it);
+}
 
 uint2 key_of(uint64_t seed) { return make_uint2(static_cast<uint32_t>(seed), static_cast<uint32_t>(seed >> 32)); }
 
@@ -129,7 +177,15 @@ ahk::StepArgs step_args(ahk_env *e, const ahk::EnvArgs &a, int mode, cudaStream_
     st.trace = e->trace ? e->trace + (e->launches & 1u) * static_cast<size_t>(e->step_grid) * (ahk::kStepThreads / 32) * 4 : nullptr;
     // Deferred wait (pdl 3) only between two consecutive STEP launches: a reset launch writes all three ring slots, so it
     // and the step after it keep the wait in front of their first store.
-    st.pdl = (e->pdl == 3 && !(mode == 1 && e->last_mode == 1 && e->last_stream == s)) ? 1 : e->pdl;
+    const bool own_chain = own_previous_launch(e, s) && mode == 1 && e->last_mode == 1 && e->last_stream == s;
+    st.pdl = (e->pdl == 3 && !own_chain) ? 1 : e->pdl;
+    // Inputs another kernel (or copy) on the stream may have produced — action labels, reset masks, overrides, and the state
+    // itself when the previous launch was not this engine's own step — are only guaranteed visible after
+    // griddepcontrol.wait: the kernel then waits BEFORE its first load.  This costs nothing unless the predecessor is a
+    // step kernel that triggered early.  Actions in mapped HOST memory (ahk_step_host*) are written by the host before the
+    // launch and need no wait: only the engine's own action-free / host-action step-to-step chain runs its prologue under
+    // the previous launch's tail.
+    st.wait_first = st.pdl != 0 && (!own_chain || a.ext_inputs);
     e->last_mode = mode;
     e->last_stream = s;
     st.dyn_units = e->dyn_units;
@@ -194,7 +250,7 @@ int ahk_create(const ahk_config *cfg, ahk_env **out)
     if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0)
         return fail(AHK_ERR_NO_DEVICE, "no CUDA device: this engine has no CPU fallback");
     if (cfg->device < 0 || cfg->device >= count) return fail(AHK_ERR_ARG, "device %d out of range [0, %d)", cfg->device, count);
-    AHK_CUDA(cudaSetDevice(cfg->device));
+    AHK_ON_DEVICE(cfg->device);
     cudaDeviceProp prop{};
     AHK_CUDA(cudaGetDeviceProperties(&prop, cfg->device));
     if (prop.major < 10) return fail(AHK_ERR_NO_DEVICE, "device %d is sm_%d%d; this library is built for sm_100a only", cfg->device, prop.major, prop.minor);
@@ -260,7 +316,8 @@ int ahk_create(const ahk_config *cfg, ahk_env **out)
 void ahk_destroy(ahk_env *e)
 {
     if (!e) return;
-    cudaSetDevice(e->cfg.device);
+    forget_engine(e);
+    DeviceGuard guard(e->cfg.device);
     if (e->table_dev) cudaFree(e->table_dev);
     if (e->action_stage) cudaFree(e->action_stage);
     for (int k = 0; k < 2; ++k) if (e->bounds_dev[k]) cudaFree(e->bounds_dev[k]);
@@ -289,7 +346,7 @@ int ahk_set_table_image(ahk_env *e, const uint8_t *rgb, int height, int width)
             for (int c = 0; c < 3; ++c) chw[(c * ahk::kDim + i) * ahk::kDim + j] = p[c];
         }
     }
-    AHK_CUDA(cudaSetDevice(e->cfg.device));
+    AHK_ON_DEVICE(e->cfg.device);
     AHK_CUDA(cudaMemcpy(e->table_dev, chw.data(), chw.size(), cudaMemcpyHostToDevice));
     e->table_set = true;
     return AHK_OK;
@@ -310,8 +367,10 @@ int ahk_bind_buffers(ahk_env *e, const ahk_buffers *b)
 int ahk_reset(ahk_env *e, const uint8_t *mask, const uint8_t *episode, const uint8_t *use, void *stream)
 {
     if (int rc = check_ready(e)) return rc;
+    AHK_ON_DEVICE(e->cfg.device);
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     ahk::EnvArgs a = env_args(e);
+    a.ext_inputs = 1;
     a.reset_mask = mask;
     a.episode_override = episode;
     a.use_override = use;
@@ -321,22 +380,48 @@ int ahk_reset(ahk_env *e, const uint8_t *mask, const uint8_t *episode, const uin
 int ahk_step(ahk_env *e, const uint8_t *robot, const uint8_t *human, void *stream)
 {
     if (int rc = check_ready(e)) return rc;
+    AHK_ON_DEVICE(e->cfg.device);
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     ahk::EnvArgs a = env_args(e);
     a.robot = robot;
     a.human = human;
+    a.ext_inputs = robot != nullptr || human != nullptr;
     e->head = (e->head + 1) % 3;
     return run(e, a, 1, s);
+}
+
+int ahk_step_many(ahk_env *e, int steps, const ahk_step_log *log, void *stream)
+{
+    if (int rc = check_ready(e)) return rc;
+    if (steps < 0) return fail(AHK_ERR_ARG, "steps must be >= 0, got %d", steps);
+    AHK_ON_DEVICE(e->cfg.device);
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const size_t n = static_cast<size_t>(e->cfg.n_envs);
+    const bool logging = log && (log->robot_label || log->human_label || log->done || log->reward);
+    for (int t = 0; t < steps; ++t) {
+        ahk::EnvArgs a = env_args(e);
+        e->head = (e->head + 1) % 3;
+        if (int rc = run(e, a, 1, s)) return rc;
+        if (logging) {
+            if (log->robot_label) AHK_CUDA(cudaMemcpyAsync(log->robot_label + t * n, e->buf.robot_label, n, cudaMemcpyDeviceToDevice, s));
+            if (log->human_label) AHK_CUDA(cudaMemcpyAsync(log->human_label + t * n, e->buf.human_label, n, cudaMemcpyDeviceToDevice, s));
+            if (log->done) AHK_CUDA(cudaMemcpyAsync(log->done + t * n, e->buf.done, n, cudaMemcpyDeviceToDevice, s));
+            if (log->reward) AHK_CUDA(cudaMemcpyAsync(log->reward + t * n, e->buf.reward, n * sizeof(float), cudaMemcpyDeviceToDevice, s));
+        }
+    }
+    return AHK_OK;
 }
 
 int ahk_step_profiled(ahk_env *e, const uint8_t *robot, const uint8_t *human, void *stream, float *env_ms, float *raster_ms)
 {
     if (int rc = check_ready(e)) return rc;
     if (!env_ms || !raster_ms) return fail(AHK_ERR_ARG, "env_ms/raster_ms is NULL");
+    AHK_ON_DEVICE(e->cfg.device);
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     ahk::EnvArgs a = env_args(e);
     a.robot = robot;
     a.human = human;
+    a.ext_inputs = robot != nullptr || human != nullptr;
     e->head = (e->head + 1) % 3;
     AHK_CUDA(cudaEventRecord(e->ev[0], s));
     if (!e->split) { // the fused kernel is the whole step: reported as the second figure, the first is 0
@@ -366,7 +451,7 @@ static int step_host_enqueue(ahk_env *e, const uint8_t *robot, const uint8_t *hu
                              uint8_t *robot_label, uint8_t *human_label, uint8_t *frame, uint64_t *early)
 {
     if (int rc = check_ready(e)) return rc;
-    AHK_CUDA(cudaSetDevice(e->cfg.device));
+    AHK_ON_DEVICE(e->cfg.device);
     cudaStream_t s = e->host_stream;
     const size_t n = static_cast<size_t>(e->cfg.n_envs);
     // Pinned buffers are read and written by the step kernel itself (mapped host memory, 2 + 7 bytes per env over PCIe):
@@ -439,6 +524,7 @@ int ahk_step_host_results(ahk_env *e, const uint8_t *robot, const uint8_t *human
 int ahk_host_sync(ahk_env *e)
 {
     if (!e) return fail(AHK_ERR_ARG, "env is NULL");
+    AHK_ON_DEVICE(e->cfg.device);
     AHK_CUDA(cudaStreamSynchronize(e->host_stream));
     e->host_early_ticket = -1;
     return AHK_OK;
@@ -448,6 +534,7 @@ int ahk_step_host_wait(ahk_env *e, int ticket)
 {
     if (!e) return fail(AHK_ERR_ARG, "env is NULL");
     if (ticket < 0 || ticket >= ahk_env::kHostDepth) return fail(AHK_ERR_ARG, "ticket %d out of range", ticket);
+    AHK_ON_DEVICE(e->cfg.device);
     AHK_CUDA(cudaEventSynchronize(e->host_ev[ticket]));
     if (ticket == e->host_early_ticket) e->host_early_ticket = -1;
     return AHK_OK;
@@ -466,6 +553,7 @@ int ahk_observe(ahk_env *e, int format, void *out, void *stream)
     if (int rc = check_ready(e)) return rc;
     if (!out) return fail(AHK_ERR_ARG, "out is NULL");
     if (format < AHK_OBS_U8 || format > AHK_OBS_GRAY_DIFF_F64) return fail(AHK_ERR_ARG, "Processing mode is not supported");
+    AHK_ON_DEVICE(e->cfg.device);
     if (e->host_early_ticket >= 0 && static_cast<cudaStream_t>(stream) != e->host_stream)
         AHK_CUDA(cudaStreamWaitEvent(static_cast<cudaStream_t>(stream), e->host_ev[e->host_early_ticket], 0));
     ahk::ObserveArgs a{e->buf.frames, out, e->cfg.n_envs, e->head, format};
@@ -490,7 +578,9 @@ int ahk_set_pending(ahk_env *e, const uint8_t *pending, void *stream)
 {
     if (int rc = check_ready(e)) return rc;
     if (!pending) return fail(AHK_ERR_ARG, "pending is NULL");
+    AHK_ON_DEVICE(e->cfg.device);
     AHK_CUDA(ahk::launch_set_pending(e->buf.state, pending, e->cfg.n_envs, static_cast<cudaStream_t>(stream)));
+    e->last_mode = -1; // the state was written by another kernel: the next step waits before it loads it
     e->launches += 1;
     return AHK_OK;
 }
@@ -519,7 +609,7 @@ int ahk_get_partition(ahk_env *e, int32_t *bounds_host, int capacity)
         for (int b = 0; b <= g; ++b) bounds_host[b] = b * e->envs_per_cta < e->cfg.n_envs ? b * e->envs_per_cta : e->cfg.n_envs;
         return g;
     }
-    AHK_CUDA(cudaSetDevice(e->cfg.device));
+    AHK_ON_DEVICE(e->cfg.device);
     AHK_CUDA(cudaDeviceSynchronize());
     AHK_CUDA(cudaMemcpy(bounds_host, e->bounds_dev[e->bounds_cur], (g + 1) * sizeof(int), cudaMemcpyDeviceToHost));
     return g;

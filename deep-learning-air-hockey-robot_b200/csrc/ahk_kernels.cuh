@@ -33,6 +33,7 @@ struct EnvArgs {
     unsigned *tick_count;
     unsigned long long tick_seq;
     const uint8_t *reset_mask, *episode_override, *use_override; // reset
+    int ext_inputs; // robot / human / reset inputs may have been produced by earlier work on the stream (device pointers)
     uint2 key;
     uint32_t env_id_base;
     int n, auto_reset, max_episode_steps;
@@ -59,6 +60,7 @@ struct StepArgs { // the fused kernel: env block b of envs_per_cta environments 
     unsigned long long *end_ns; // [grid] %globaltimer at each CTA's end, this launch
     unsigned *done_count;    // CTAs finished in this launch
     int dyn_units;           // 1: warps claim raster units from a shared-memory counter instead of round-robin (default; AHK_UNITS=static for A/B)
+    int wait_first;          // griddepcontrol.wait before the first load of caller-produced inputs (actions, masks, overrides)
     int pdl;                 // launched with programmatic stream serialization: griddepcontrol.* are live; 1: wait before the first frame store, 3: wait at the end (2: experiment, no wait)
     unsigned long long *trace; // measurement aid (ahk_set_trace): [grid][32 warps][4] %globaltimer stamps; selects the traced kernel
 };

@@ -391,6 +391,9 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_kernel(StepArgs a)
     }
     build_luts(luts);
     bool table_ready = false, waited = false;
+    // Caller-produced inputs (action labels, reset masks, overrides) are read by env_update below: what an earlier kernel
+    // or copy on the stream wrote is only guaranteed visible after the wait.
+    if (a.wait_first) { asm volatile("griddepcontrol.wait;" ::: "memory"); waited = true; }
 
     const int n = a.ras.n;
     const int part = static_cast<int>(blockIdx.x);
@@ -459,7 +462,7 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_kernel(StepArgs a)
             mbarrier_wait(bar, 0u);
             table_ready = true;
             // pdl 1: no frame is written before the previous launch has completed
-            if (a.pdl == 1) { asm volatile("griddepcontrol.wait;" ::: "memory"); waited = true; }
+            if (a.pdl == 1 && !waited) { asm volatile("griddepcontrol.wait;" ::: "memory"); waited = true; }
         }
         if (kTrace && lane == 0 && base == lo) trace[2] = global_ns();
         if (a.bounds_next != nullptr && tid == 0 && base == lo) s_raster_start = global_ns();

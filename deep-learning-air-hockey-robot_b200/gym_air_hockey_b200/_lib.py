@@ -25,6 +25,10 @@ class Buffers(C.Structure):  # ahk_buffers
                 ("state", "frames", "reward", "done", "robot_label", "human_label", "info", "stats", "drawlist")]
 
 
+class StepLog(C.Structure):  # ahk_step_log
+    _fields_ = [("robot_label", C.c_void_p), ("human_label", C.c_void_p), ("done", C.c_void_p), ("reward", C.c_void_p)]
+
+
 class PolicyWeights(C.Structure):  # ahk_policy_weights
     NAMES = ("conv1_w", "conv1_b", "bn1_gamma", "bn1_beta", "bn1_mean", "bn1_var",
              "conv2_w", "conv2_b", "bn2_gamma", "bn2_beta", "bn2_mean", "bn2_var",
@@ -49,6 +53,7 @@ SYMBOLS = {
     "ahk_bind_buffers": (_i, [_vp, C.POINTER(Buffers)]),
     "ahk_reset": (_i, [_vp, _vp, _vp, _vp, _vp]),
     "ahk_step": (_i, [_vp, _vp, _vp, _vp]),
+    "ahk_step_many": (_i, [_vp, _i, C.POINTER(StepLog), _vp]),
     "ahk_step_profiled": (_i, [_vp, _vp, _vp, _vp, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
     "ahk_step_host": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "ahk_step_host_begin": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
@@ -91,12 +96,8 @@ def load():
         raise ImportError(
             "%s is missing: build it with `python __graft_entry__.py` (or make -C deep-learning-air-hockey-robot_b200/csrc). "
             "The engine has no CPU or PyTorch fallback." % LIB_PATH)
-    # AHK_LIB: an older build of the same ABI for same-box A/B timing (tools/); never a different implementation
-    override = os.environ.get("AHK_LIB")
-    lib = C.CDLL(override or LIB_PATH)
+    lib = C.CDLL(LIB_PATH)
     for name, (restype, argtypes) in SYMBOLS.items():
-        if override and not hasattr(lib, name):
-            continue
         fn = getattr(lib, name)  # AttributeError if the ABI and the binding disagree
         fn.restype = restype
         fn.argtypes = argtypes

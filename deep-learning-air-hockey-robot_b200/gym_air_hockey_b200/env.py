@@ -143,6 +143,25 @@ class BatchedAirHockeyEnv(object):
         info = {'robot_action': self.robot_label, 'human_action': self.human_label}
         return self._obs(), self.reward, self.done.view(torch.bool), info
 
+    def step_many(self, steps, log=None):
+        """`steps` consecutive action-free steps in ONE call (ahk_step_many) — the data-generation loop
+        (generate_data.py:44-58), where the programmed AI plays both sides.  log: optional dict of preallocated CUDA
+        tensors [steps, N] under 'robot_action', 'human_action' (uint8), 'done' (uint8), 'reward' (float32) that receive
+        every step's outputs.  Returns like step(): the outputs of the LAST step."""
+        st = None
+        if log:
+            st = _lib.StepLog()
+            for key, field, dt in (('robot_action', 'robot_label', torch.uint8), ('human_action', 'human_label', torch.uint8),
+                                   ('done', 'done', torch.uint8), ('reward', 'reward', torch.float32)):
+                t = log.get(key)
+                if t is not None:
+                    if t.dtype != dt or tuple(t.shape) != (int(steps), self.n_envs) or not t.is_contiguous() or t.device != self.device:
+                        raise ValueError("log[%r] must be a contiguous %s CUDA tensor [steps, n_envs]" % (key, dt))
+                    setattr(st, field, t.data_ptr())
+        _lib.check(self.lib.ahk_step_many(self._h, int(steps), C.byref(st) if st is not None else None, self._stream()))
+        info = {'robot_action': self.robot_label, 'human_action': self.human_label}
+        return self._obs(), self.reward, self.done.view(torch.bool), info
+
     def step_profiled(self, robot_action=None, human_action=None):
         """step() with CUDA events around each kernel: -> (env_kernel ms, raster kernel ms).  For bench.py's roofline."""
         r, h = self._labels(robot_action), self._labels(human_action)
@@ -269,6 +288,7 @@ class BatchedAirHockeyEnv(object):
         st[15] = (np.minimum(pick(episode_steps, 'episode_steps'), 0xFFFF) | pick(episode, 'episode') << 16 |
                   pick(use, 'use') << 18 | pick(pending, 'pending') << 21)
         self.state.copy_(torch.from_numpy(st.view(np.int32)))
+        torch.cuda.current_stream(self.device).synchronize()  # written outside the engine: complete before the next launch
 
     def partition(self):
         """Env boundaries of the step kernel's CTAs right now (int32[ctas + 1]; the adaptive partition)."""

@@ -117,6 +117,9 @@ class TrainableNetwork(nn.Module):
         return {name: np.ascontiguousarray(w[name], dtype=np.float32) for name, _ in SHAPES}
 
 
+L2_REGULARIZER = 1e-4  # models.py:17
+
+
 class KerasSGD(object):
     """keras.optimizers.SGD(lr, momentum, decay, clipnorm) as compiled at rl_agents.py:111,170 (Keras 2.x semantics):
     gradients scaled by clipnorm / max(global L2 norm, clipnorm); lr_t = lr / (1 + decay * iterations);
@@ -259,6 +262,21 @@ class Agent(object):
         self.loss_buffer = []
         self.logits = torch.zeros((self.n, 10), dtype=torch.float32, device=self.device)
         self.greedy = torch.zeros(self.n, dtype=torch.uint8, device=self.device)
+        # kernel_regularizer=regularizers.l2(0.0001) on conv1..dense2 and 'out' (models.py:17,22-62): model.fit minimises
+        # loss + l2 * sum ||W||^2 over these kernels (biases and BatchNorm carry no regulariser)
+        self.l2 = L2_REGULARIZER
+        self.l2_params = [m.weight for m in (self.model.conv1, self.model.conv2, self.model.conv3, self.model.dense1,
+                                             self.model.dense2, self.model.out)]
+
+    def _agree(self, value, op='min'):
+        """An integer every rank must agree on before issuing collectives (how many fit batches, whether to fit at all):
+        the MIN (or MAX) over the ranks of `group`; a no-op on one rank."""
+        import torch.distributed as dist
+        if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(self.group) == 1:
+            return int(value)
+        t = torch.tensor([int(value)], dtype=torch.int64, device=self.device)
+        dist.all_reduce(t, op=dist.ReduceOp.MIN if op == 'min' else dist.ReduceOp.MAX, group=self.group)
+        return int(t.item())
 
     def epsilon(self):
         return max(self.eps_min, self.eps_max - (self.eps_max - self.eps_min) * self.iteration / self.eps_decay_steps)
@@ -316,6 +334,11 @@ class Agent(object):
         logits = self.model(obs_u8)
         dlogits, loss = backward_from(logits.detach())
         logits.backward(dlogits)
+        if self.l2 and self.l2_params:  # the kernel regulariser's share of the objective and of the gradients
+            with torch.no_grad():
+                for p in self.l2_params:
+                    p.grad.add_(p, alpha=2.0 * self.l2)
+                loss.add_(self.l2 * torch.stack([p.pow(2).sum() for p in self.l2_params]).sum())
         self.bucket.all_reduce(group=self.group)
         self.optimizer.step()
         self._sync_batchnorm_statistics()
@@ -334,6 +357,8 @@ class DDQNAgent(Agent):
             fresh = keras_default_init(seed=kw.get('seed', 0) + 1)
             weights['out_w'], weights['out_b'] = fresh['out_w'], fresh['out_b']
         super().__init__(env, weights, **kw)
+        if replace_softmax:  # the new Dense(10, activation='linear') is built without a kernel_regularizer (rl_agents.py:166)
+            self.l2_params = self.l2_params[:-1]
         self.optimizer = KerasSGD(self.model.parameters())
         self.target_policy = PolicyNetwork(self.model.keras_weights(), max_batch=self.batch_size, device=self.device.index)
         self.use_target = False
@@ -349,7 +374,7 @@ class DDQNAgent(Agent):
     def train(self):
         """≙ DDQNAgent.train (rl_agents.py:177-191).  -> loss (float) or None if nothing can be sampled yet."""
         batch = self.replay.sample(self.batch_size, self.gen)
-        if batch is None:
+        if not self._agree(batch is not None):  # every rank fits or none does: a fit issues collectives
             return None
         g, b = batch['frames'], int(batch['t'].numel())
         q = self.policy.forward_ring(g[0:3], 2)[0]
@@ -412,8 +437,12 @@ class PGAgent(Agent):
         ok = valid_transitions(rp.pending, rp.cursor, rp.filled, need_next=True)[order]
         k_idx, e_idx = ok[:-1].nonzero(as_tuple=True)  # state slot = order[k]; its action/reward/prob are at order[k+1]
         perm = torch.randperm(k_idx.numel(), device=self.device, generator=self.gen)  # fit(shuffle=True)
+        # every fit batch issues two collectives (gradients, BatchNorm statistics) and the number of valid transitions
+        # depends on each rank's own resets and goals: all ranks run the same number of batches, the smallest any of them
+        # has (a rank's surplus samples — less than one episode's worth — are dropped)
+        n_batches = self._agree(-(-int(perm.numel()) // self.fit_batch))
         losses = []
-        for lo in range(0, int(perm.numel()), self.fit_batch):
+        for lo in range(0, n_batches * self.fit_batch, self.fit_batch):
             sel = perm[lo:lo + self.fit_batch]
             k, e = k_idx[sel], e_idx[sel]
             g = rp.gather(order[k], e)

@@ -90,6 +90,19 @@ int ahk_reset(ahk_env *env, const uint8_t *mask_dev, const uint8_t *episode_dev,
  * then the new frame of every env rasterised into ring slot `head` (advanced first).  robot_dev/human_dev [n] labels or NULL. */
 int ahk_step(ahk_env *env, const uint8_t *robot_dev, const uint8_t *human_dev, void *stream);
 
+/* T consecutive ACTION-FREE steps in one call — the data-generation loop, where the programmed AI plays both sides and
+ * nothing outside the engine feeds a step (generate_data.py:44-58: `env.step()` with no arguments, reset on a goal or at
+ * the step limit = auto_reset + max_episode_steps).  Same results as `steps` calls of ahk_step(env, NULL, NULL, stream);
+ * the outputs of every step, which the loop appends to its dataset (generate_data.py:53-55), are kept when `log_dev` is
+ * given: each member is a device array [steps][n] or NULL. */
+typedef struct {
+    uint8_t *robot_label; /* info['robot_action'] per step */
+    uint8_t *human_label; /* info['human_action'] per step */
+    uint8_t *done;        /* terminal per step */
+    float *reward;        /* reward per step */
+} ahk_step_log;
+int ahk_step_many(ahk_env *env, int steps, const ahk_step_log *log_dev, void *stream);
+
 /* The same call with HOST buffers, for callers that live on the CPU like the reference's loops do
  * (generate_data.py:44-58, reinforcement/train.py:87-96): actions in, step, reward/done/labels (and, if
  * frame_host != NULL, the new uint8 frame [n][3][128][128]) out, then waits.  Any pointer may be NULL.

@@ -442,6 +442,7 @@ typedef struct {
     uint8_t ring[3][ORC_FRAME]; /* ring[0] newest */
     uint8_t *native;            /* scratch uint8[700][450][3] */
     const uint8_t *table;
+    int skip_draw;              /* orc_run_trace: advance state and counters, leave the ring alone (long-horizon sweeps) */
 } orc_env;
 
 orc_env *orc_env_create(uint64_t seed, uint32_t env_id, const uint8_t *table)
@@ -468,6 +469,7 @@ static void env_push(orc_env *e, const uint8_t *chw)
 static void env_render_push(orc_env *e, int use)
 {
     uint8_t chw[ORC_FRAME];
+    if (e->skip_draw) return;
     orc_draw(&e->sim, use, e->table, e->native);
     orc_resize_nearest_chw(e->native, ORC_H, ORC_W, chw);
     env_push(e, chw);
@@ -476,8 +478,9 @@ static void env_render_push(orc_env *e, int use)
 static void env_noise_push(orc_env *e)
 {
     uint8_t chw[ORC_FRAME];
-    orc_noise_frame(e->sim.key, e->sim.env_id, e->noise_count, chw);
     e->noise_count += 1;
+    if (e->skip_draw) return;
+    orc_noise_frame(e->sim.key, e->sim.env_id, e->noise_count - 1, chw);
     env_push(e, chw);
 }
 
@@ -602,22 +605,171 @@ static void *run_job(void *arg)
     return NULL;
 }
 
+/* A persistent pool of worker threads (bench.py: the reference arm and the cpu_baseline leg share it, so that neither
+ * pays thread creation inside its timed region).  A job = one function over a slice of [0, n). */
+typedef struct orc_pool {
+    pthread_mutex_t mu;
+    pthread_cond_t go, done;
+    pthread_t *tids;
+    int threads, generation, remaining, quit;
+    void (*fn)(void *ctx, int lo, int hi, int worker);
+    void *ctx;
+    int n;
+} orc_pool;
+
+typedef struct { orc_pool *pool; int k; } orc_worker_arg;
+
+static void *pool_worker(void *arg)
+{
+    orc_worker_arg *wa = (orc_worker_arg *)arg;
+    orc_pool *p = wa->pool;
+    const int k = wa->k;
+    int seen = 0;
+    free(wa);
+    for (;;) {
+        pthread_mutex_lock(&p->mu);
+        while (p->generation == seen && !p->quit) pthread_cond_wait(&p->go, &p->mu);
+        if (p->quit) { pthread_mutex_unlock(&p->mu); return NULL; }
+        seen = p->generation;
+        const int n = p->n;
+        pthread_mutex_unlock(&p->mu);
+        const int lo = (int)((long long)n * k / p->threads), hi = (int)((long long)n * (k + 1) / p->threads);
+        if (hi > lo) p->fn(p->ctx, lo, hi, k);
+        pthread_mutex_lock(&p->mu);
+        if (--p->remaining == 0) pthread_cond_signal(&p->done);
+        pthread_mutex_unlock(&p->mu);
+    }
+}
+
+orc_pool *orc_pool_create(int threads)
+{
+    if (threads < 1) threads = 1;
+    orc_pool *p = (orc_pool *)calloc(1, sizeof *p);
+    if (!p) return NULL;
+    pthread_mutex_init(&p->mu, NULL);
+    pthread_cond_init(&p->go, NULL);
+    pthread_cond_init(&p->done, NULL);
+    p->threads = threads;
+    p->tids = (pthread_t *)calloc((size_t)threads, sizeof *p->tids);
+    for (int k = 0; k < threads; ++k) {
+        orc_worker_arg *wa = (orc_worker_arg *)malloc(sizeof *wa);
+        wa->pool = p; wa->k = k;
+        pthread_create(&p->tids[k], NULL, pool_worker, wa);
+    }
+    return p;
+}
+
+void orc_pool_destroy(orc_pool *p)
+{
+    if (!p) return;
+    pthread_mutex_lock(&p->mu);
+    p->quit = 1;
+    pthread_cond_broadcast(&p->go);
+    pthread_mutex_unlock(&p->mu);
+    for (int k = 0; k < p->threads; ++k) pthread_join(p->tids[k], NULL);
+    pthread_mutex_destroy(&p->mu);
+    pthread_cond_destroy(&p->go);
+    pthread_cond_destroy(&p->done);
+    free(p->tids);
+    free(p);
+}
+
+int orc_pool_threads(const orc_pool *p) { return p ? p->threads : 0; }
+
+static void pool_run(orc_pool *p, void (*fn)(void *, int, int, int), void *ctx, int n)
+{
+    pthread_mutex_lock(&p->mu);
+    p->fn = fn; p->ctx = ctx; p->n = n;
+    p->remaining = p->threads;
+    p->generation += 1;
+    pthread_cond_broadcast(&p->go);
+    while (p->remaining > 0) pthread_cond_wait(&p->done, &p->mu);
+    pthread_mutex_unlock(&p->mu);
+}
+
+typedef struct { orc_job job; uint64_t *checks; } orc_batch_ctx;
+
+static void batch_slice(void *ctx, int lo, int hi, int worker)
+{
+    orc_batch_ctx *c = (orc_batch_ctx *)ctx;
+    orc_job j = c->job;
+    j.lo = lo; j.hi = hi;
+    run_job(&j);
+    c->checks[worker] = j.check;
+}
+
+/* orc_run_batch on a persistent pool: same work per env-step, no thread creation and no allocation inside the call */
+uint64_t orc_pool_run_batch(orc_pool *p, orc_env **envs, int n, int steps, int max_episode_steps, float *obs_out,
+                            float *reward_out, uint8_t *done_out, uint8_t *labels_out)
+{
+    uint64_t checks[1024] = { 0 }, check = 0;
+    if (!p || p->threads > 1024) return 0;
+    orc_batch_ctx c = { { envs, 0, 0, steps, max_episode_steps, obs_out, reward_out, done_out, labels_out, 0 }, checks };
+    pool_run(p, batch_slice, &c, n);
+    for (int k = 0; k < p->threads; ++k) check += checks[k];
+    return check;
+}
+
 uint64_t orc_run_batch(orc_env **envs, int n, int steps, int max_episode_steps, int threads, float *obs_out,
                        float *reward_out, uint8_t *done_out, uint8_t *labels_out)
 {
     if (threads < 1) threads = 1;
     if (threads > n) threads = n > 0 ? n : 1;
-    orc_job *jobs = (orc_job *)calloc((size_t)threads, sizeof *jobs);
-    pthread_t *tids = (pthread_t *)calloc((size_t)threads, sizeof *tids);
-    uint64_t check = 0;
-    for (int k = 0; k < threads; ++k) {
-        jobs[k] = (orc_job){ envs, (int)((long long)n * k / threads), (int)((long long)n * (k + 1) / threads), steps,
-                             max_episode_steps, obs_out, reward_out, done_out, labels_out, 0 };
-        pthread_create(&tids[k], NULL, run_job, &jobs[k]);
-    }
-    for (int k = 0; k < threads; ++k) { pthread_join(tids[k], NULL); check += jobs[k].check; }
-    free(jobs); free(tids);
+    orc_pool *p = orc_pool_create(threads);
+    uint64_t check = orc_pool_run_batch(p, envs, n, steps, max_episode_steps, obs_out, reward_out, done_out, labels_out);
+    orc_pool_destroy(p);
     return check;
+}
+
+/* ---------------------------------------------------------------- long-horizon trace (tools/stress_sweep.py, tests) */
+/* Every env does `steps` steps (auto_reset: the batched engine's reset-if-pending protocol, else plain steps), AI on both
+ * sides, and logs per step the engine's 16 state words — state_out[t][w][i], the SoA layout of ahk_buffers.state: float
+ * bits of puck/bottom/top, serve/reset/noise counters, meta = episode_steps | episode << 16 | use << 18 | pending << 21 —
+ * and out_out[t][i] = (reward * 2 + 2) | terminal << 3 | robot_label << 4 | human_label << 8 | flags << 12 | scored << 17.
+ * robot / human: optional caller actions per step and env.
+ * Frames are drawn only during the last `draw_last` steps (the ring at the end is then exact provided draw_last >= 3). */
+typedef struct {
+    orc_env **envs; int n, steps, max_episode_steps, auto_reset, draw_last;
+    const uint8_t *robot, *human; /* [steps][n] action labels (ACT_NONE = programmed AI) or NULL = AI throughout */
+    uint32_t *state_out, *out_out;
+} orc_trace_ctx;
+
+static void trace_slice(void *ctx, int lo, int hi, int worker)
+{
+    orc_trace_ctx *c = (orc_trace_ctx *)ctx;
+    (void)worker;
+    for (int i = lo; i < hi; ++i) {
+        orc_env *e = c->envs[i];
+        for (int t = 0; t < c->steps; ++t) {
+            orc_step_out o;
+            e->skip_draw = t < c->steps - c->draw_last;
+            const int r = c->robot ? c->robot[(size_t)t * c->n + i] : ACT_NONE, h = c->human ? c->human[(size_t)t * c->n + i] : ACT_NONE;
+            if (c->auto_reset) orc_env_step_auto(e, r, h, c->max_episode_steps, &o);
+            else orc_env_step(e, r, h, &o);
+            if (c->state_out) {
+                uint32_t *w = c->state_out + (size_t)t * 16 * c->n + i;
+                const uint32_t *f = (const uint32_t *)&e->sim.puck;
+                for (int k = 0; k < 12; ++k) w[(size_t)k * c->n] = f[k];
+                w[(size_t)12 * c->n] = e->sim.serve_count;
+                w[(size_t)13 * c->n] = e->reset_count;
+                w[(size_t)14 * c->n] = e->noise_count;
+                w[(size_t)15 * c->n] = (e->episode_steps > 0xFFFFu ? 0xFFFFu : e->episode_steps) | (uint32_t)e->episode << 16 |
+                                       (uint32_t)e->use << 18 | (uint32_t)e->pending_reset << 21;
+            }
+            if (c->out_out)
+                c->out_out[(size_t)t * c->n + i] = (uint32_t)(int)(o.reward * 2.0f + 2.0f) | (uint32_t)o.terminal << 3 |
+                                                   (uint32_t)o.robot_label << 4 | (uint32_t)o.human_label << 8 |
+                                                   (uint32_t)o.flags << 12 | (uint32_t)o.scored << 17;
+        }
+        e->skip_draw = 0;
+    }
+}
+
+void orc_run_trace(orc_pool *p, orc_env **envs, int n, int steps, int max_episode_steps, int auto_reset, int draw_last,
+                   const uint8_t *robot, const uint8_t *human, uint32_t *state_out, uint32_t *out_out)
+{
+    orc_trace_ctx c = { envs, n, steps, max_episode_steps, auto_reset, draw_last, robot, human, state_out, out_out };
+    pool_run(p, trace_slice, &c, n);
 }
 
 int orc_sizeof_sim(void) { return (int)sizeof(orc_sim); }

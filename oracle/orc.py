@@ -80,6 +80,12 @@ def lib():
     L.orc_env_observe_rgb.argtypes = [vp, f32p]
     L.orc_run_batch.argtypes = [C.POINTER(vp), C.c_int, C.c_int, C.c_int, C.c_int, f32p, f32p, u8p, u8p]
     L.orc_run_batch.restype = C.c_uint64
+    L.orc_pool_create.argtypes = [C.c_int]
+    L.orc_pool_create.restype = vp
+    L.orc_pool_destroy.argtypes = [vp]
+    L.orc_pool_run_batch.argtypes = [vp, C.POINTER(vp), C.c_int, C.c_int, C.c_int, f32p, f32p, u8p, u8p]
+    L.orc_pool_run_batch.restype = C.c_uint64
+    L.orc_run_trace.argtypes = [vp, C.POINTER(vp), C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, u8p, u8p, u32p, u32p]
     _lib = L
     return L
 
@@ -230,3 +236,52 @@ def run_batch(envs, steps, max_episode_steps=200, threads=1, want_obs=True):
                               _p(obs, C.c_float) if want_obs else None, _p(reward, C.c_float),
                               _p(done, C.c_uint8), _p(labels, C.c_uint8))
     return chk, obs, reward, done, labels
+
+
+class Pool:
+    """A persistent pool of worker threads plus preallocated outputs: the timed CPU arm (bench.py) calls `run` in a loop
+    without creating threads or arrays inside the timed region; `trace` logs long horizons for the stress sweep."""
+
+    def __init__(self, envs, threads=1, want_obs=True):
+        self.envs, self.n = envs, len(envs)
+        self.threads = max(1, min(int(threads), self.n))
+        self._p = lib().orc_pool_create(self.threads)
+        self._handles = (C.c_void_p * self.n)(*[e._h for e in envs])
+        self.obs = np.empty((self.n, 9, DIM, DIM), dtype=np.float32) if want_obs else None
+        self.reward = np.empty(self.n, dtype=np.float32)
+        self.done = np.empty(self.n, dtype=np.uint8)
+        self.labels = np.empty((self.n, 2), dtype=np.uint8)
+
+    def run(self, steps, max_episode_steps=200):
+        """Every env does `steps` auto-reset AI-vs-AI steps, each producing what the reference's env.step() hands back
+        (float32 (9,128,128) observation, reward, terminal, two labels).  -> checksum."""
+        return lib().orc_pool_run_batch(self._p, self._handles, self.n, steps, max_episode_steps,
+                                        _p(self.obs, C.c_float) if self.obs is not None else None,
+                                        _p(self.reward, C.c_float), _p(self.done, C.c_uint8), _p(self.labels, C.c_uint8))
+
+    def trace(self, steps, max_episode_steps=0, auto_reset=True, draw_last=3, want_state=True, want_out=True,
+              robot=None, human=None):
+        """robot / human: optional uint8[steps, n] action labels (255 = programmed AI).
+        -> (state uint32[steps,16,n] in the engine's SoA word layout, out uint32[steps,n] packed step results)."""
+        state = np.empty((steps, 16, self.n), dtype=np.uint32) if want_state else None
+        out = np.empty((steps, self.n), dtype=np.uint32) if want_out else None
+        r = None if robot is None else np.ascontiguousarray(robot, dtype=np.uint8).reshape(steps, self.n)
+        h = None if human is None else np.ascontiguousarray(human, dtype=np.uint8).reshape(steps, self.n)
+        lib().orc_run_trace(self._p, self._handles, self.n, steps, max_episode_steps, int(auto_reset), draw_last,
+                            None if r is None else _p(r, C.c_uint8), None if h is None else _p(h, C.c_uint8),
+                            _p(state, C.c_uint32) if want_state else None, _p(out, C.c_uint32) if want_out else None)
+        return state, out
+
+    def close(self):
+        if getattr(self, "_p", None):
+            lib().orc_pool_destroy(self._p)
+            self._p = None
+
+    def __del__(self):
+        self.close()
+
+
+def unpack_out(out):
+    """Fields of Pool.trace's packed step results."""
+    return {"reward": ((out & 7).astype(np.float32) - 2.0) * 0.5, "terminal": (out >> 3) & 1, "robot_label": (out >> 4) & 15,
+            "human_label": (out >> 8) & 15, "flags": (out >> 12) & 31, "scored": (out >> 17) & 3}

@@ -78,3 +78,10 @@ def keras_sgd_steps(params, grads_per_step, lr=0.0075, momentum=0.5, decay=1e-6,
             v -= lr_t * g
             p += v
     return params
+
+
+def l2_penalty_and_grads(kernels, l2=1e-4):
+    """kernel_regularizer=regularizers.l2(l2) (models.py:17,22-62): what model.fit adds to the loss, l2 * sum ||W||^2, and to
+    the gradient of every regularised kernel, 2 * l2 * W."""
+    penalty = float(sum(l2 * np.sum(np.asarray(k, dtype=np.float64) ** 2) for k in kernels))
+    return penalty, [(2.0 * l2 * np.asarray(k, dtype=np.float64)).astype(np.float32) for k in kernels]

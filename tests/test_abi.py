@@ -89,3 +89,17 @@ def test_product_does_not_import_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
                 text = open(os.path.join(dirpath, f)).read()
                 assert "import orc" not in text and "ahk_oracle" not in text and "libahk_oracle" not in text, f
+
+
+def test_bench_reads_ncu_traffic_from_the_newest_profile():
+    """bench.py's roofline.traffic comes from the newest committed ncu summary, not from a constant."""
+    import importlib.util
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("bench", os.path.join(root, "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    traffic, src = bench.ncu_traffic("step_kernel_*_ncu.txt")
+    assert src is not None and src.startswith("step_kernel_") and 100e6 < traffic < 250e6
+    assert bench.ncu_traffic("no_such_kernel_*.txt") == (None, None)
+    assert bench.cpu_reference_wrapper()["B3_reference_wrapper_over_oracle_simulator"]["rgb"]["frames"] == 10000

@@ -24,29 +24,33 @@ def test_file_name_and_round_trip(tmp_path):
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("states", ["f32", "u8"])
-def test_generate_matches_stepping(cuda, table, tmp_path, states):
-    """The writer's samples are exactly what stepping the same engine by hand produces, in step-major order, in the
-    reference's dtypes: float32 normalised (n, 9, 128, 128) states, int8 labels."""
+def test_generate_matches_oracle(cuda, orc, table, tmp_path, states):
+    """The written samples are what the ORACLE produces for the same seeds — the reference's data-generation loop
+    (generate_data.py:44-58: env.step() with no actions, reset on a goal or at the step limit) over the oracle env, whose
+    observation is the reference processor's float32 (x-128)/128 stack (processor.py:39-52) — in step-major order and in
+    the reference's dtypes: float32 normalised (n, 9, 128, 128) states, int8 labels (data_utils.py:3-7)."""
     from gym_air_hockey_b200 import BatchedAirHockeyEnv, dataset
-    n, total = 6, 50
-    env = BatchedAirHockeyEnv(n, table=table, seed=21, max_episode_steps=20)
+    n, total, seed, limit = 6, 50, 21, 20
+    env = BatchedAirHockeyEnv(n, table=table, seed=seed, max_episode_steps=limit)
     env.reset()
     out = dataset.generate(env, total, str(tmp_path), states=states, shard_states=24, when=1500000000)
     assert out['samples'] == total and out['steps'] == 9 and len(out['files']) >= 2
-    s, r, h = dataset.load_data(os.path.join(str(tmp_path), '*.npz'))
+    s, r, h = dataset.load_data(os.path.join(str(tmp_path), '*' + os.path.splitext(out['files'][0])[1]))
     assert s.shape == (total, 9, 128, 128) and r.shape == (total,) and r.dtype == np.int8 and h.dtype == np.int8
     assert s.dtype == (np.float32 if states == 'f32' else np.uint8)
 
-    ref = BatchedAirHockeyEnv(n, table=table, seed=21, max_episode_steps=20)
-    ref.reset()
+    oracles = [orc.Env(seed=seed, env_id=i, table=table) for i in range(n)]
+    for o in oracles:
+        o.reset()
     want_s, want_r, want_h = [], [], []
     for _ in range(9):
-        _, _, _, info = ref.step()
-        want_s.append(ref.observation('rgb' if states == 'f32' else 'u8').cpu().numpy())
-        want_r.append(info['robot_action'].cpu().numpy().astype(np.int8))
-        want_h.append(info['human_action'].cpu().numpy().astype(np.int8))
-    assert np.array_equal(s, np.concatenate(want_s)[:total])
-    assert np.array_equal(r, np.concatenate(want_r)[:total]) and np.array_equal(h, np.concatenate(want_h)[:total])
+        for o in oracles:
+            res = o.step_auto(255, 255, limit)
+            want_s.append(o.observe_rgb() if states == 'f32' else o.ring().reshape(9, 128, 128))
+            want_r.append(res.robot_label)
+            want_h.append(res.human_label)
+    assert np.array_equal(s, np.stack(want_s)[:total])
+    assert np.array_equal(r, np.array(want_r, dtype=np.int8)[:total]) and np.array_equal(h, np.array(want_h, dtype=np.int8)[:total])
     assert set(np.unique(r)) <= set(range(9))   # label 9 never comes from the simulator (SURVEY Appendix B.5)
 
 

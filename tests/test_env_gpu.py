@@ -157,41 +157,15 @@ def test_back_to_back_steps_overlap(cuda, orc, noise_table, n, limit, steps):
     assert env.statistics()['steps'] == n * steps
 
 
-def stress_states(n, rs):
-    """configs[4]: pucks at top speed aimed at corners, walls at grazing angles, posts and mallet edges."""
-    s = np.zeros((n, 12), dtype=np.float32)
-    s[:, 4:6] = (225, 600)
-    s[:, 8:10] = (225, 100)
-    for i in range(n):
-        kind = i % 6
-        ang = rs.uniform(0, 2 * np.pi)
-        v = 18.0 * np.array([np.cos(ang), np.sin(ang)])
-        if kind == 0:   # next to a corner arc
-            cx, cy = rs.choice([85, 365]), rs.choice([85, 615])
-            p = np.array([cx, cy]) + rs.uniform(-1, 1, 2) * 30
-        elif kind == 1:  # grazing a side wall
-            p = np.array([rs.choice([44, 406]), rs.uniform(100, 600)]); v = np.array([rs.choice([-1, 1]) * 0.3, rs.choice([-18, 18])])
-        elif kind == 2:  # at a goal post
-            p = np.array([rs.choice([163, 287]) + rs.uniform(-3, 3), rs.choice([50, 650])]); v = np.array([rs.uniform(-2, 2), 17 if p[1] > 350 else -17])
-        elif kind == 3:  # on a mallet's rim
-            m = s[i, 4:6] if i % 2 else s[i, 8:10]
-            p = m + 42.0 * np.array([np.cos(ang), np.sin(ang)]); v = -v
-        elif kind == 4:  # exactly on top of a mallet (coincident centres)
-            p = s[i, 4:6].copy(); v = np.zeros(2)
-        else:
-            p = np.array([rs.uniform(43, 407), rs.uniform(43, 657)])
-        s[i, 0:2] = p
-        s[i, 2:4] = v
-    return s
-
-
 def test_collision_stress(cuda, orc, table):
+    """configs[4] in small, with every frame checked: pucks at top speed aimed at corners, walls at grazing angles, posts
+    and mallet edges (oracle/stress.py)."""
+    import stress
     n, seed = 60, 8
-    rs = np.random.RandomState(5)
     env = make_env(n, table, seed=seed, auto_reset=False, max_episode_steps=0)
     oracles = oracle_envs(orc, n, table, seed)
     env.reset(episode=np.zeros(n, dtype=np.uint8), use_object=np.full(n, 7, dtype=np.uint8))
-    s = stress_states(n, rs)
+    s = stress.stress_states(0, n)
     env.set_state(s)
     for i, o in enumerate(oracles):
         o.reset(0, 7)
@@ -199,6 +173,24 @@ def test_collision_stress(cuda, orc, table):
         o.set_state(s[i], m)
     goals = run_lockstep(env, oracles, 250, auto=False, check_frames_every=25)
     assert goals >= 1
+
+
+def test_stress_sweep_long_horizon(cuda, orc):
+    """configs[4] as tools/stress_sweep.py runs it (there: 384 envs x 10 000 steps at 1/2/4/8 GPUs, profiles/stress_sweep_N*.json),
+    here 96 envs x 2 000 steps: state compared with the oracle at every step, ring at every chunk end, and the per-env
+    checksums of a 2-shard run (global ids) equal those of the whole."""
+    import importlib.util
+    import os
+    spec = importlib.util.spec_from_file_location("stress_sweep", os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools", "stress_sweep.py"))
+    sw = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(sw)
+    whole = sw.sweep(96, 2000, 500, threads=8)
+    assert whole["first_divergence_step"] is None and whole["max_abs_delta"] == 0.0
+    assert whole["output_mismatches"] == 0 and whole["frame_mismatches"] == 0 and whole["frames_checked"] == 4 * 96 * 3
+    assert whole["goals"] > 0 and whole["env_resets"] > 96
+    parts = [sw.sweep(96, 2000, 1000, rank=r, world=2, threads=8) for r in range(2)]
+    assert all(p["first_divergence_step"] is None for p in parts)
+    assert np.array_equal(np.concatenate([p["checksums"] for p in parts]), whole["checksums"])
 
 
 def crc(a):
@@ -357,6 +349,125 @@ def test_step_host_pipelined_and_pageable(cuda, table):
     assert np.array_equal(a.frames.cpu().numpy(), b.frames.cpu().numpy())
     assert np.array_equal(a.get_state()[0].view(np.uint32), b.get_state()[0].view(np.uint32))
     assert np.array_equal(b.reward.cpu().numpy(), expect[-1][0])  # the device copies are written as well
+
+
+def state_words(env, ids):
+    """uint32 [16, len(ids)] of the engine's SoA state for the sampled local env ids."""
+    return env.state.cpu().numpy().view(np.uint32)[:, ids]
+
+
+def test_configs1_4096_envs_vs_oracle(cuda, orc, table):
+    """BASELINE.json configs[1] at its own size: 4096 envs (28 per CTA — the benchmarked shape), AI on both sides,
+    auto-reset on goals and every 200 steps (generate_data.py:44-58), 130 + 140 steps launched back to back with no host
+    synchronisation in between.  Trajectories are independent and keyed by the global env id, so the oracle only runs a
+    sample of 320 ids (first and last env, both sides of CTA boundaries 27|28, 55|56, ..., and 300 random ones): state
+    bits, the whole 3-slot ring and the last step's outputs must be equal at both checkpoints."""
+    n, seed, limit = 4096, 20181104, 200
+    rs = np.random.RandomState(4096)
+    ids = np.unique(np.concatenate([[0, 1, 27, 28, 55, 56, 2047, 2048, 4067, 4068, n - 2, n - 1], rs.choice(n, 300, replace=False)]))
+    assert len(ids) >= 256
+    env = make_env(n, table, seed=seed, auto_reset=True, max_episode_steps=limit)
+    oracles = [orc.Env(seed=seed, env_id=int(i), table=table) for i in ids]
+    pool = orc.Pool(oracles, threads=8, want_obs=False)
+    env.reset()
+    for o in oracles:
+        o.reset()
+    done_steps = 0
+    for steps in (130, 140):
+        for _ in range(steps):
+            _, reward, done, info = env.step()
+        cuda.cuda.synchronize()
+        done_steps += steps
+        st, out = pool.trace(steps, limit, auto_reset=True, draw_last=3)
+        assert np.array_equal(state_words(env, ids), st[-1]), "state after %d steps" % done_steps
+        u = orc.unpack_out(out[-1])
+        assert np.array_equal(reward.cpu().numpy()[ids], u['reward'])
+        assert np.array_equal(done.cpu().numpy()[ids].astype(np.uint32), u['terminal'])
+        assert np.array_equal(info['robot_action'].cpu().numpy()[ids].astype(np.uint32), u['robot_label'])
+        assert np.array_equal(info['human_action'].cpu().numpy()[ids].astype(np.uint32), u['human_label'])
+        assert np.array_equal(env.info_bits.cpu().numpy()[ids].astype(np.uint32), u['flags'] | u['scored'] << 5)
+        fr, h = env.frames[:, ids].cpu().numpy(), env.head
+        for k, o in enumerate(oracles):
+            ring = o.ring()
+            for age in range(3):
+                assert np.array_equal(fr[(h + 3 - age) % 3, k], ring[age]), (done_steps, int(ids[k]), age)
+    _, meta = env.get_state()
+    assert set(meta['episode'][ids].tolist()) == {0, 1, 2}  # the sample saw all three episode types
+    assert env.statistics()['steps'] == n * done_steps
+    pool.close()
+
+
+def test_producer_kernel_before_step_two_engines_one_stream(cuda, orc, noise_table):
+    """Actions written by a kernel immediately before every unsynchronised step, and two engines alternating on ONE stream
+    (ADVICE r1): the step kernel must wait for its predecessor before it loads caller-produced inputs
+    (griddepcontrol.wait), and the deferred wait of the step-to-step chain must not be used when another engine launched
+    in between.  1184 envs = one CTA per SM (the shape that takes the deferred wait when it is legal)."""
+    torch = cuda
+    n, steps, limit = 1184, 36, 7
+    seeds = (5, 6)
+    envs = [make_env(n, noise_table, seed=s, auto_reset=True, max_episode_steps=limit) for s in seeds]
+    iota = torch.arange(n, device='cuda', dtype=torch.int32)
+    acts = [torch.empty(n, dtype=torch.uint8, device='cuda') for _ in envs]
+    for e in envs:
+        e.reset()
+    for t in range(steps):
+        for k, e in enumerate(envs):
+            # produced on the device right before the launch that consumes it, rewritten every step in place
+            acts[k].copy_(((iota * (3 + k) + t * 7) % 10).to(torch.uint8))
+            e.step(robot_action=acts[k], human_action=None if t % 2 else acts[k])
+    torch.cuda.synchronize()
+    i_np = np.arange(n)
+    for k, (e, s) in enumerate(zip(envs, seeds)):
+        oracles = oracle_envs(orc, n, noise_table, s)
+        for o in oracles:
+            o.reset()
+        pool = orc.Pool(oracles, threads=8, want_obs=False)
+        robot = np.stack([((i_np * (3 + k) + t * 7) % 10).astype(np.uint8) for t in range(steps)])
+        human = np.stack([robot[t] if t % 2 == 0 else np.full(n, 255, np.uint8) for t in range(steps)])
+        st, out = pool.trace(steps, limit, auto_reset=True, draw_last=3, robot=robot, human=human)
+        assert np.array_equal(e.state.cpu().numpy().view(np.uint32), st[-1]), k
+        ring = ring_newest_first(e)
+        for i, o in enumerate(oracles):
+            assert np.array_equal(ring[i], o.ring()), (k, i)
+        assert np.array_equal(e.reward.cpu().numpy(), orc.unpack_out(out[-1])['reward'])
+        pool.close()
+
+
+@pytest.mark.parametrize("n,T,limit", [(333, 1, 9), (1184, 7, 5), (4096, 64, 23)])
+def test_step_many_matches_oracle(cuda, orc, table, n, T, limit):
+    """ahk_step_many(T): T action-free steps in one call, resets inside the window (limit < T), every step's outputs
+    logged.  A sample of envs against the oracle: state, ring, and the whole [T, n] log; twice in a row, so that the second
+    window starts from envs armed for a reset."""
+    torch = cuda
+    seed = 1000 + T
+    env = make_env(n, table, seed=seed, auto_reset=True, max_episode_steps=limit)
+    rs = np.random.RandomState(T)
+    ids = np.unique(np.concatenate([[0, n - 1, n // 2], rs.choice(n, min(n, 96), replace=False)]))
+    oracles = [orc.Env(seed=seed, env_id=int(i), table=table) for i in ids]
+    pool = orc.Pool(oracles, threads=8, want_obs=False)
+    env.reset()
+    for o in oracles:
+        o.reset()
+    log = {'robot_action': torch.zeros((T, n), dtype=torch.uint8, device='cuda'), 'human_action': torch.zeros((T, n), dtype=torch.uint8, device='cuda'),
+           'done': torch.zeros((T, n), dtype=torch.uint8, device='cuda'), 'reward': torch.zeros((T, n), dtype=torch.float32, device='cuda')}
+    for window in range(2):
+        _, reward, done, info = env.step_many(T, log)
+        torch.cuda.synchronize()
+        st, out = pool.trace(T, limit, auto_reset=True, draw_last=3)
+        u = orc.unpack_out(out)
+        assert np.array_equal(state_words(env, ids), st[-1]), window
+        assert np.array_equal(log['reward'].cpu().numpy()[:, ids], u['reward'])
+        assert np.array_equal(log['done'].cpu().numpy()[:, ids].astype(np.uint32), u['terminal'])
+        assert np.array_equal(log['robot_action'].cpu().numpy()[:, ids].astype(np.uint32), u['robot_label'])
+        assert np.array_equal(log['human_action'].cpu().numpy()[:, ids].astype(np.uint32), u['human_label'])
+        assert np.array_equal(reward.cpu().numpy()[ids], u['reward'][-1])
+        fr, h = env.frames[:, ids].cpu().numpy(), env.head
+        for k, o in enumerate(oracles):
+            ring = o.ring()
+            for age in range(3):
+                assert np.array_equal(fr[(h + 3 - age) % 3, k], ring[age]), (window, int(ids[k]), age)
+    assert env.statistics()['steps'] == 2 * T * n
+    pool.close()
 
 
 def test_full_size_properties(cuda, table):

@@ -149,3 +149,40 @@ def test_noise_frame_range(orc):
     assert f.max() <= 254 and f.min() == 0 and f.std() > 60   # randint(0, 255): 255 never appears
     assert not np.array_equal(f, orc.noise_frame(3, 9, 1))
     assert not np.array_equal(f, orc.noise_frame(3, 10, 0))
+
+
+def test_pool_and_trace_replay_stepping(orc, table):
+    """The persistent pool (bench.py's CPU arm) and the long-horizon trace (tools/stress_sweep.py, the 4096-env parity test)
+    give what stepping the same envs one call at a time gives: checksums, logged state words, packed outputs, ring."""
+    n, steps, limit = 12, 45, 16
+    a = [orc.Env(seed=3, env_id=i, table=table) for i in range(n)]
+    b = [orc.Env(seed=3, env_id=i, table=table) for i in range(n)]
+    for e in a + b:
+        e.reset()
+    pool = orc.Pool(a, threads=3)
+    assert pool.run(7, limit) == orc.run_batch(b, 7, limit, 2)[0]
+    rs = np.random.RandomState(0)
+    robot = rs.randint(0, 10, size=(steps, n)).astype(np.uint8)
+    human = np.where(rs.rand(steps, n) < 0.5, 255, rs.randint(0, 10, size=(steps, n))).astype(np.uint8)
+    st, out = pool.trace(steps, limit, auto_reset=True, draw_last=3, robot=robot, human=human)
+    u = orc.unpack_out(out)
+    for i, e in enumerate(b):
+        for t in range(steps):
+            o = e.step_auto(int(robot[t, i]), int(human[t, i]), limit)
+            s, m = e.get_state()
+            assert np.array_equal(st[t, :12, i], s.view(np.uint32)), (t, i)
+            assert (st[t, 12, i], st[t, 13, i], st[t, 14, i]) == (m[0], m[1], m[2])
+            assert st[t, 15, i] == (m[3] | m[4] << 16 | m[5] << 18 | m[6] << 21)
+            assert (u['reward'][t, i], u['terminal'][t, i], u['robot_label'][t, i], u['human_label'][t, i], u['flags'][t, i], u['scored'][t, i]) == \
+                   (o.reward, o.terminal, o.robot_label, o.human_label, o.flags, o.scored)
+        assert np.array_equal(a[i].ring(), e.ring()), i  # frames skipped on the way, the last three drawn
+    pool.close()
+
+
+def test_stress_states_are_a_function_of_the_global_id():
+    import stress
+    whole = stress.stress_states(0, 24)
+    assert whole.shape == (24, 12) and whole.dtype == np.float32
+    assert np.array_equal(np.concatenate([stress.stress_states(0, 10), stress.stress_states(10, 24)]), whole)
+    assert np.array_equal(whole[4, 0:2], whole[4, 4:6])          # kind 4: the puck exactly on the bottom mallet
+    assert np.hypot(whole[0, 2], whole[0, 3]) > 17.9             # kind 0: top speed

@@ -69,6 +69,50 @@ def test_policy_forward_matches_reference(cuda, table, n, source):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("mode", ["rgb", "gray-diff"])
+def test_policy_forward_8192_samples_matches_reference(cuda, table, mode):
+    """BASELINE.json configs[3]'s per-GPU batch: PolicyNetwork(max_batch=8192) on 8192 GAME frames (mixed episode types,
+    resets in flight), both modes.  The persistent multi-tile paths of every kernel run at full grid here (conv1: 57 344
+    work items over 148 CTAs; conv2: 23 104 tiles; dense: 64 row tiles x 2 N halves).  640 sampled rows — the first and
+    last 128-row tile of the dense layers, both sides of tile boundaries, the first and last sample, random others — are
+    compared with oracle/cnn_ref.py at the same tolerances as the small tests."""
+    import cnn_ref
+    from gym_air_hockey_b200 import BatchedAirHockeyEnv
+    from gym_air_hockey_b200.policy import GRAY_SHAPES, SHAPES, PolicyNetwork, keras_default_init
+    torch = cuda
+    n = 8192
+    w = keras_default_init(seed=7, randomize_bn=True, shapes=SHAPES if mode == 'rgb' else GRAY_SHAPES)
+    net = PolicyNetwork(w, max_batch=n, mode=mode)
+    env = BatchedAirHockeyEnv(n, table=table, seed=31, max_episode_steps=6)
+    env.reset()
+    for _ in range(8):
+        env.step()
+    logits, action = net.forward(env)
+    torch.cuda.synchronize()
+    rs = np.random.RandomState(8192)
+    ids = np.unique(np.concatenate([np.arange(0, 128), np.arange(n - 128, n), [127, 128, 129, 255, 256, 4095, 4096, 4097],
+                                    rs.choice(n, 400, replace=False)]))
+    assert len(ids) >= 512
+    fr = env.frames[:, ids].cpu().numpy()
+    head = env.head
+    obs = np.concatenate([fr[(head + 3 - age) % 3] for age in range(3)], axis=1)
+    fwd = cnn_ref.forward if mode == 'rgb' else cnn_ref.forward_gray
+    ref32, ref16 = fwd(w, obs), fwd(w, obs, emulate_bf16=True)
+    got, act = logits.cpu().numpy()[ids], action.cpu().numpy()[ids]
+    scale = max(np.abs(ref32).max(), 1e-6)
+    assert np.isfinite(logits.cpu().numpy()).all()
+    assert np.abs(got - ref16).max() <= 6e-3 * scale, np.abs(got - ref16).max() / scale
+    assert np.abs(got - ref32).max() <= 3e-2 * scale, np.abs(got - ref32).max() / scale
+    assert np.array_equal(action.cpu().numpy(), logits.cpu().numpy().argmax(axis=1))
+    top2 = np.sort(ref32, axis=1)
+    clear = (top2[:, -1] - top2[:, -2]) > 6e-2 * scale
+    assert np.array_equal(act[clear], ref32.argmax(axis=1)[clear])
+    # a second pass over the same ring gives the same bits (no cross-tile state left behind by the persistent kernels)
+    logits2, _ = net.forward(env)
+    assert torch.equal(logits, logits2)
+
+
+@pytest.mark.gpu
 def test_policy_in_the_loop(cuda, table):
     """keras/test.py:36-51 as a batched loop: frames -> CNN -> argmax -> env.step, all on the device."""
     from gym_air_hockey_b200 import BatchedAirHockeyEnv

@@ -46,6 +46,48 @@ def test_keras_sgd_matches_restatement():
         assert np.allclose(p.detach().numpy(), w, rtol=1e-5, atol=1e-6)
 
 
+def test_fit_includes_the_l2_kernel_regulariser():
+    """models.py:17,22-62: every conv / dense kernel carries regularizers.l2(1e-4); `_fit` must minimise
+    loss + 1e-4 * sum ||W||^2, i.e. add 2e-4 * W to those gradients (not to biases or BatchNorm) and the penalty to the
+    reported loss.  Checked on the CPU against the restatement with a stub agent (no engine needed)."""
+    import rl_ref
+    import torch
+    from gym_air_hockey_b200 import rl
+    from gym_air_hockey_b200.policy import keras_default_init
+
+    class Stub(rl.Agent):
+        def __init__(self):  # the parts of Agent.__init__ that _fit touches, without an engine
+            self.model = rl.TrainableNetwork(keras_default_init(seed=4, randomize_bn=True))
+            self.group, self.l2 = None, rl.L2_REGULARIZER
+            self.l2_params = [m.weight for m in (self.model.conv1, self.model.conv2, self.model.conv3, self.model.dense1,
+                                                 self.model.dense2, self.model.out)]
+            self.bucket = rl.GradientBucket(self.model.parameters())
+            self.optimizer = type('NoStep', (), {'step': lambda self: None})()
+            self.pushed = 0
+
+        def push_weights(self, policy=None, on_device=True):
+            self.pushed += 1
+
+    agent = Stub()
+    obs = torch.from_numpy(np.random.RandomState(0).randint(0, 256, size=(4, 9, 128, 128)).astype(np.uint8))
+    d = torch.from_numpy(np.random.RandomState(1).randn(4, 10).astype(np.float32) * 0.01)
+    loss = agent._fit(obs, lambda logits: (d, torch.zeros(1)))
+    got = {name: p.grad.clone() for name, p in agent.model.named_parameters()}
+    # the same backward pass without the regulariser
+    agent.model.train()
+    for p in agent.model.parameters():
+        p.grad = None
+    agent.model(obs).backward(d)
+    kernels = [p.detach().numpy() for p in agent.l2_params]
+    penalty, extra = rl_ref.l2_penalty_and_grads(kernels)
+    assert abs(loss.item() - penalty) <= 1e-6 * penalty and penalty > 0
+    reg = {id(p): e for p, e in zip(agent.l2_params, extra)}
+    for name, p in agent.model.named_parameters():
+        want = p.grad + (torch.from_numpy(reg[id(p)]) if id(p) in reg else 0)
+        assert torch.allclose(got[name], want, rtol=1e-5, atol=1e-8), name
+    assert agent.pushed == 1
+
+
 def test_valid_transitions_window_logic():
     import torch
     from gym_air_hockey_b200.rl import valid_transitions

@@ -78,6 +78,7 @@ struct ahk_env {
     cudaStream_t last_stream = nullptr; // stream of the previous fused launch
     bool zero_copy = true;                // A/B switch AHK_ZEROCOPY=0: always use the copy engine in ahk_step_host
     int head = 0;
+    int depth = 3;              // ring slots (cfg.ring_depth; 0 = 3)
     int sms = 0;
     int raster_grid = 0;        // staged rasteriser (split path): one persistent CTA per SM
     int step_grid = 0, envs_per_cta = 0; // fused kernel: CTA b owns envs [b * envs_per_cta, (b + 1) * envs_per_cta)
@@ -94,6 +95,7 @@ struct ahk_env {
     unsigned adapt_tick = 0, adapt_every = 8;
     int switch_in = 0;
     bool balance = true; // A/B switch AHK_BALANCE=0
+    bool many_kernel = true; // ahk_step_many through the persistent kernel; A/B switch AHK_MANY=loop: one launch per step
     int dyn_units = 1;   // warps claim raster units from a shared counter; A/B switch AHK_UNITS=static: round-robin
     int last_mode = -1;  // mode of the previous fused launch (step_args)
     int pdl = -1;        // programmatic dependent launch of consecutive step kernels; -1: by size (ahk_create); A/B switch AHK_PDL=0/1/3
@@ -160,6 +162,8 @@ ahk::RasterArgs raster_args(const ahk_env *e)
     r.drawlist = e->buf.drawlist;
     r.table = e->table_dev;
     r.frames = e->buf.frames;
+    r.warm = e->depth > 3 ? e->buf.warm : nullptr;
+    r.depth = e->depth;
     r.key = key_of(e->cfg.seed);
     r.env_id_base = e->cfg.env_id_base;
     r.n = e->cfg.n_envs;
@@ -196,7 +200,7 @@ ahk::StepArgs step_args(ahk_env *e, const ahk::EnvArgs &a, int mode, cudaStream_
         st.bounds = e->bounds_dev[e->bounds_cur];
         // steps adapt, every 8th one (the last CTA's boundary computation is ~2 us on the launch's tail); a reset (three
         // frames per env, once) only uses the current boundaries
-        if (mode == 1 && e->switch_in == 0 && (e->adapt_tick++ % e->adapt_every) == 0) {
+        if ((mode == 1 || mode == 3) && e->switch_in == 0 && (mode == 3 || (e->adapt_tick++ % e->adapt_every) == 0)) {
             st.bounds_next = e->bounds_dev[e->bounds_cur ^ 1];
             st.end_ns = e->end_dev;
             st.done_count = e->done_dev;
@@ -246,6 +250,8 @@ int ahk_create(const ahk_config *cfg, ahk_env **out)
     if (cfg->n_envs <= 0) return fail(AHK_ERR_ARG, "n_envs must be positive, got %d", cfg->n_envs);
     if (cfg->max_episode_steps < 0 || cfg->max_episode_steps > 65535)
         return fail(AHK_ERR_ARG, "max_episode_steps must be in [0, 65535], got %d", cfg->max_episode_steps);
+    if (cfg->ring_depth != 0 && (cfg->ring_depth < 3 || cfg->ring_depth > 65536))
+        return fail(AHK_ERR_ARG, "ring_depth must be 0 (= 3) or in [3, 65536], got %d", cfg->ring_depth);
     int count = 0;
     if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0)
         return fail(AHK_ERR_NO_DEVICE, "no CUDA device: this engine has no CPU fallback");
@@ -258,13 +264,15 @@ int ahk_create(const ahk_config *cfg, ahk_env **out)
     ahk_env *e = new (std::nothrow) ahk_env();
     if (!e) return fail(AHK_ERR_ARG, "out of host memory");
     e->cfg = *cfg;
-    if (const char *s = getenv("AHK_PATH")) e->split = strcmp(s, "split") == 0;
+    e->depth = cfg->ring_depth ? cfg->ring_depth : 3;
+    if (const char *s = getenv("AHK_PATH")) e->split = strcmp(s, "split") == 0 && e->depth == 3; // the A/B path knows the 3-slot ring only
     if (const char *s = getenv("AHK_ADAPT_EVERY")) e->adapt_every = atoi(s) > 0 ? atoi(s) : 1;
     if (const char *s = getenv("AHK_PDL")) e->pdl = atoi(s);
     if (const char *s = getenv("AHK_UNITS")) e->dyn_units = strcmp(s, "static") != 0;
     if (const char *s = getenv("AHK_BALANCE")) e->balance = atoi(s) != 0;
     if (const char *s = getenv("AHK_RASTER")) e->staged = strcmp(s, "staged") == 0;
     if (const char *s = getenv("AHK_ZEROCOPY")) e->zero_copy = atoi(s) != 0;
+    if (const char *s = getenv("AHK_MANY")) e->many_kernel = strcmp(s, "loop") != 0;
     e->sms = prop.multiProcessorCount;
     e->raster_grid = e->sms;
     e->envs_per_cta = (cfg->n_envs + e->sms - 1) / e->sms;
@@ -356,9 +364,10 @@ int ahk_bind_buffers(ahk_env *e, const ahk_buffers *b)
 {
     if (!e || !b) return fail(AHK_ERR_ARG, "env/bufs is NULL");
     if (!b->state || !b->frames || !b->reward || !b->done || !b->robot_label || !b->human_label || !b->info || !b->drawlist)
-        return fail(AHK_ERR_ARG, "every buffer except stats must be non-NULL");
-    if ((reinterpret_cast<uintptr_t>(b->frames) | reinterpret_cast<uintptr_t>(b->drawlist)) & 15u)
-        return fail(AHK_ERR_ARG, "frames and drawlist must be 16-byte aligned");
+        return fail(AHK_ERR_ARG, "every buffer except stats and warm must be non-NULL");
+    if (e->depth > 3 && !b->warm) return fail(AHK_ERR_ARG, "ring_depth %d > 3 needs the warm buffer [3][n][3][128][128]", e->depth);
+    if ((reinterpret_cast<uintptr_t>(b->frames) | reinterpret_cast<uintptr_t>(b->drawlist) | reinterpret_cast<uintptr_t>(b->warm)) & 15u)
+        return fail(AHK_ERR_ARG, "frames, warm and drawlist must be 16-byte aligned");
     e->buf = *b;
     e->bound = true;
     return AHK_OK;
@@ -386,7 +395,7 @@ int ahk_step(ahk_env *e, const uint8_t *robot, const uint8_t *human, void *strea
     a.robot = robot;
     a.human = human;
     a.ext_inputs = robot != nullptr || human != nullptr;
-    e->head = (e->head + 1) % 3;
+    e->head = (e->head + 1) % e->depth;
     return run(e, a, 1, s);
 }
 
@@ -394,13 +403,33 @@ int ahk_step_many(ahk_env *e, int steps, const ahk_step_log *log, void *stream)
 {
     if (int rc = check_ready(e)) return rc;
     if (steps < 0) return fail(AHK_ERR_ARG, "steps must be >= 0, got %d", steps);
+    if (steps == 0) return AHK_OK;
     AHK_ON_DEVICE(e->cfg.device);
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     const size_t n = static_cast<size_t>(e->cfg.n_envs);
     const bool logging = log && (log->robot_label || log->human_label || log->done || log->reward);
+    // The persistent kernel keeps two record buffers of 3 * kManyEnvs records per CTA: it takes the call when no CTA can own
+    // more envs than that (the adaptive partition moves shares within +-50 % of even).  Larger batches — where a launch
+    // is long and its fixed cost small — go step by step.  A/B switch AHK_MANY=loop.
+    const int even = (e->cfg.n_envs + e->step_grid - 1) / e->step_grid;
+    const bool fits = (e->balance ? even + (even + 1) / 2 + 1 : e->envs_per_cta) <= ahk::kManyEnvs;
+    if (fits && !e->split && e->many_kernel) {
+        if (e->host_early_ticket >= 0 && s != e->host_stream) AHK_CUDA(cudaStreamWaitEvent(s, e->host_ev[e->host_early_ticket], 0));
+        ahk::EnvArgs a = env_args(e);
+        ahk::StepArgs st = step_args(e, a, 3, s);
+        st.pdl = 0;
+        st.wait_first = 0;
+        st.ras.head = (e->head + 1) % e->depth; // slot of the window's first step
+        ahk::StepLogArgs lg{};
+        if (logging) { lg.robot_label = log->robot_label; lg.human_label = log->human_label; lg.done = log->done; lg.reward = log->reward; }
+        AHK_CUDA(ahk::launch_step_many(st, steps, lg, e->step_grid, s));
+        e->head = (e->head + steps) % e->depth;
+        e->launches += 1;
+        return AHK_OK;
+    }
     for (int t = 0; t < steps; ++t) {
         ahk::EnvArgs a = env_args(e);
-        e->head = (e->head + 1) % 3;
+        e->head = (e->head + 1) % e->depth;
         if (int rc = run(e, a, 1, s)) return rc;
         if (logging) {
             if (log->robot_label) AHK_CUDA(cudaMemcpyAsync(log->robot_label + t * n, e->buf.robot_label, n, cudaMemcpyDeviceToDevice, s));
@@ -422,7 +451,7 @@ int ahk_step_profiled(ahk_env *e, const uint8_t *robot, const uint8_t *human, vo
     a.robot = robot;
     a.human = human;
     a.ext_inputs = robot != nullptr || human != nullptr;
-    e->head = (e->head + 1) % 3;
+    e->head = (e->head + 1) % e->depth;
     AHK_CUDA(cudaEventRecord(e->ev[0], s));
     if (!e->split) { // the fused kernel is the whole step: reported as the second figure, the first is 0
         if (int rc = run(e, a, 1, s)) return rc;
@@ -479,7 +508,7 @@ static int step_host_enqueue(ahk_env *e, const uint8_t *robot, const uint8_t *hu
             a.tick_seq = *early = ++e->tick_seq;
         }
     }
-    e->head = (e->head + 1) % 3;
+    e->head = (e->head + 1) % e->depth;
     if (int rc = run(e, a, 1, s)) return rc;
     if (reward && !a.h_reward) AHK_CUDA(cudaMemcpyAsync(reward, e->buf.reward, n * sizeof(float), cudaMemcpyDeviceToHost, s));
     if (done && !a.h_done) AHK_CUDA(cudaMemcpyAsync(done, e->buf.done, n, cudaMemcpyDeviceToHost, s));
@@ -556,7 +585,15 @@ int ahk_observe(ahk_env *e, int format, void *out, void *stream)
     AHK_ON_DEVICE(e->cfg.device);
     if (e->host_early_ticket >= 0 && static_cast<cudaStream_t>(stream) != e->host_stream)
         AHK_CUDA(cudaStreamWaitEvent(static_cast<cudaStream_t>(stream), e->host_ev[e->host_early_ticket], 0));
-    ahk::ObserveArgs a{e->buf.frames, out, e->cfg.n_envs, e->head, format};
+    ahk::ObserveArgs a{};
+    a.frames = e->buf.frames;
+    a.warm = e->depth > 3 ? e->buf.warm : nullptr;
+    a.meta = e->buf.state + static_cast<size_t>(15) * e->cfg.n_envs;
+    a.out = out;
+    a.n = e->cfg.n_envs;
+    a.head = e->head;
+    a.format = format;
+    a.depth = e->depth;
     const size_t work = static_cast<size_t>(e->cfg.n_envs) * (format == AHK_OBS_GRAY_DIFF_F64 ? 1024 : 3 * ahk::kFrameVecs);
     size_t grid = (work + 255) / 256;
     if (grid > static_cast<size_t>(e->raster_grid) * 16) grid = static_cast<size_t>(e->raster_grid) * 16;
@@ -566,10 +603,24 @@ int ahk_observe(ahk_env *e, int format, void *out, void *stream)
 }
 
 int ahk_head(const ahk_env *e) { return e ? e->head : fail(AHK_ERR_ARG, "env is NULL"); }
+int ahk_ring_depth(const ahk_env *e) { return e ? e->depth : fail(AHK_ERR_ARG, "env is NULL"); }
+
+int ahk_stack_view(const ahk_env *e, ahk_stack *out)
+{
+    if (!e || !out) return fail(AHK_ERR_ARG, "env/out is NULL");
+    if (!e->bound) return fail(AHK_ERR_STATE, "ahk_bind_buffers has not been called");
+    out->frames = e->buf.frames;
+    out->warm = e->depth > 3 ? e->buf.warm : nullptr;
+    out->meta = e->buf.state + static_cast<size_t>(15) * e->cfg.n_envs;
+    out->n = e->cfg.n_envs;
+    out->depth = e->depth;
+    out->head = e->head;
+    return AHK_OK;
+}
 
 int ahk_set_head(ahk_env *e, int head)
 {
-    if (!e || head < 0 || head > 2) return fail(AHK_ERR_ARG, "head must be 0, 1 or 2");
+    if (!e || head < 0 || head >= e->depth) return fail(AHK_ERR_ARG, "head must be in [0, ring_depth)");
     e->head = head;
     return AHK_OK;
 }

@@ -49,7 +49,7 @@ __device__ __forceinline__ uint32_t make_meta(uint32_t steps, uint32_t episode, 
 struct StatDelta {
     unsigned steps = 0, episodes = 0, goals_top = 0, goals_bottom = 0;
     int reward2 = 0;
-    uint32_t robot_label = 0xFFu, human_label = 0xFFu;
+    uint32_t robot_label = 0xFFu, human_label = 0xFFu, terminal = 0;
 };
 
 // Resets (if due) and/or steps env i; rec[0..2] are the draw records of ring slots head, head-1, head-2 (w == 0:
@@ -145,6 +145,7 @@ __device__ __forceinline__ void env_update(const EnvArgs &a, int i, uint4 (&rec)
         if (a.h_robot_label) a.h_robot_label[i] = static_cast<uint8_t>(d.robot_label);
         if (a.h_human_label) a.h_human_label[i] = static_cast<uint8_t>(d.human_label);
         d.steps = 1;
+        d.terminal = terminal;
         d.reward2 = r2;
         d.goals_top = (t.info >> 5) == kScoredTop;
         d.goals_bottom = (t.info >> 5) == kScoredBottom;

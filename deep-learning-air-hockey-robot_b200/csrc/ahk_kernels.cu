@@ -37,8 +37,7 @@ __global__ void __launch_bounds__(256) observe_kernel(ObserveArgs a)
             uint4 q[3][3]; // [age][channel]
 #pragma unroll
             for (int age = 0; age < 3; ++age) {
-                const int slot = (a.head + 3 - age) % 3;
-                const uint4 *f = reinterpret_cast<const uint4 *>(a.frames + (static_cast<size_t>(slot) * n + env) * kFrameBytes);
+                const uint4 *f = reinterpret_cast<const uint4 *>(stack_frame(a.frames, a.warm, a.meta, a.depth, n, a.head, env, age));
 #pragma unroll
                 for (int c = 0; c < 3; ++c) q[age][c] = f[c * 1024 + v];
             }
@@ -65,8 +64,7 @@ __global__ void __launch_bounds__(256) observe_kernel(ObserveArgs a)
         const size_t rem = idx - env * (3 * kFrameVecs);
         const int age = static_cast<int>(rem / kFrameVecs);
         const size_t v = rem - static_cast<size_t>(age) * kFrameVecs;
-        const int slot = (a.head + 3 - age) % 3;
-        const uint4 q = *reinterpret_cast<const uint4 *>(a.frames + (static_cast<size_t>(slot) * n + env) * kFrameBytes + v * 16);
+        const uint4 q = *reinterpret_cast<const uint4 *>(stack_frame(a.frames, a.warm, a.meta, a.depth, n, a.head, env, age) + v * 16);
         if (a.format == 0) {
             reinterpret_cast<uint4 *>(a.out)[idx] = q;
         } else {

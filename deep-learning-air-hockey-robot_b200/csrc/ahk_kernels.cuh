@@ -11,6 +11,7 @@ constexpr int kFrameBytes = 3 * kDim * kDim;
 constexpr int kFrameVecs = kFrameBytes / 16; // 3072 128-bit vectors per frame
 constexpr int kEnvThreads = 128;
 constexpr int kStepThreads = 1024;                                             // fused step kernel: 32 warps, one CTA per SM
+constexpr int kManyEnvs = 512;                                                 // ahk_step_many's persistent kernel: envs per CTA (two record buffers)
 constexpr int kRasterThreads = 256;
 constexpr int kRasterGroups = 3;                                               // independent 256-thread groups per CTA
 constexpr int kRasterGroupTail = kDim * 8 + kRasterThreads * 20 + 16;          // per-row spans + record batch + counter
@@ -42,11 +43,33 @@ struct EnvArgs {
 struct RasterArgs {
     const uint32_t *drawlist;
     const uint4 *table; // [3][128][8] vectors: the table image at the 128x128 sample points, CHW
-    uint8_t *frames;    // [3][n][3][128][128]
+    uint8_t *frames;    // [depth][n][3][128][128]
+    uint8_t *warm;      // deep ring (depth > 3) only: [3][n][3][128][128] warm-up frames of each env's latest reset; else nullptr
     uint2 key;
     uint32_t env_id_base;
-    int n, head;
+    int n, head, depth;
 };
+
+// per-step outputs kept by ahk_step_many: each [steps][n] or nullptr
+struct StepLogArgs {
+    uint8_t *robot_label, *human_label, *done;
+    float *reward;
+};
+
+// Where frame `age` (0 = newest) of env's 3-frame stack lives.  3-slot ring: slot (head - age) mod 3, always.  Deep ring:
+// a reset leaves its three warm-up frames (air_hockey_env.py:69-72) in the side buffer `warm` instead of rewriting older
+// ring slots (which hold the previous episode's last frames — replay memory), so a frame older than the env's episode
+// (age >= episode_steps, the low 16 bits of the meta word) is warm-up frame 3 - (age - episode_steps), stored at index
+// 2 - (age - episode_steps).
+__device__ __forceinline__ const uint8_t *stack_frame(const uint8_t *frames, const uint8_t *warm, const uint32_t *meta, int depth,
+                                                      size_t n, int head, size_t env, int age)
+{
+    if (warm != nullptr) {
+        const int steps = static_cast<int>(meta[env] & 0xFFFFu);
+        if (age >= steps) return warm + (static_cast<size_t>(2 - (age - steps)) * n + env) * kFrameBytes;
+    }
+    return frames + (static_cast<size_t>((head + depth - age) % depth) * n + env) * kFrameBytes;
+}
 
 struct StepArgs { // the fused kernel: env block b of envs_per_cta environments belongs to CTA b
     EnvArgs env;
@@ -67,8 +90,10 @@ struct StepArgs { // the fused kernel: env block b of envs_per_cta environments 
 
 struct ObserveArgs {
     const uint8_t *frames;
+    const uint8_t *warm;   // deep ring only
+    const uint32_t *meta;  // state word 15 of every env (deep ring only)
     void *out;
-    int n, head, format;
+    int n, head, format, depth;
 };
 
 void set_error_text(const char *text); // ahk_api.cu: fills the buffer behind ahk_last_error()
@@ -76,6 +101,7 @@ void set_error_text(const char *text); // ahk_api.cu: fills the buffer behind ah
 cudaError_t launch_env(const EnvArgs &a, bool step, cudaStream_t stream);
 cudaError_t step_prepare();
 cudaError_t launch_step(const StepArgs &a, int mode, int grid, cudaStream_t stream); // mode 0 reset, 1 step, 2 draw only
+cudaError_t launch_step_many(const StepArgs &a, int steps, const StepLogArgs &log, int grid, cudaStream_t stream);
 cudaError_t raster_staged_prepare();
 cudaError_t launch_raster_staged(const RasterArgs &a, int grid, cudaStream_t stream);
 cudaError_t launch_observe(const ObserveArgs &a, int grid, cudaStream_t stream);

@@ -71,6 +71,9 @@ struct Args {
     int n;                      // samples
     int m_total;                // valid rows of the flattened GEMM (conv1: per sample)
     int head;
+    int depth;                  // ring slots (3, or a deep ring: ahk_stack)
+    const uint8_t *warm;        // deep ring: warm-up frames of each env's latest reset, else nullptr (stack_frame, ahk_kernels.cuh)
+    const uint32_t *meta;       // deep ring: state word 15 per env
 };
 
 // ------------------------------------------------------------------------------------------------ PTX wrappers
@@ -503,7 +506,7 @@ __global__ void __launch_bounds__(c1::kCta, 1) conv1_kernel(Args a)
             const int sample = item / kTilesPerSample, r_first = 3 * (item - sample * kTilesPerSample) * kYTile;
 #pragma unroll
             for (int age = 0; age < 3; ++age) {
-                const uint8_t *src = a.frames + (static_cast<size_t>((a.head + 3 - age) % 3) * a.n + sample) * kFrameBytes + r_first * kDim;
+                const uint8_t *src = stack_frame(a.frames, a.warm, a.meta, a.depth, static_cast<size_t>(a.n), a.head, static_cast<size_t>(sample), age) + r_first * kDim;
 #pragma unroll
                 for (int t = 0; t < 3; ++t) {
                     px[age][t] = make_uint4(0, 0, 0, 0);
@@ -885,7 +888,8 @@ cudaError_t launch_ws(const Args &a, int tiles, int sms, cudaStream_t s)
 // DataProcessor's 'gray-diff' observation (processor.py:53-64) straight from the ring, as the network's bf16 input:
 // per colour the uint8 wrap-around double difference oldest - middle - newest, 0.2989 R + 0.5870 G + 0.1140 B,
 // (x - 128) / 128.  One thread per 16 pixels.
-__global__ void __launch_bounds__(256) gray_diff_kernel(const uint8_t *__restrict__ frames, __nv_bfloat16 *__restrict__ out, int n, int head)
+__global__ void __launch_bounds__(256) gray_diff_kernel(const uint8_t *__restrict__ frames, __nv_bfloat16 *__restrict__ out, int n, int head,
+                                                        int depth, const uint8_t *__restrict__ warm, const uint32_t *__restrict__ meta)
 {
     const size_t total = static_cast<size_t>(n) * 1024;
     for (size_t idx = blockIdx.x * 256ull + threadIdx.x; idx < total; idx += gridDim.x * 256ull) {
@@ -893,7 +897,7 @@ __global__ void __launch_bounds__(256) gray_diff_kernel(const uint8_t *__restric
         uint4 q[3][3]; // [age][colour]
 #pragma unroll
         for (int age = 0; age < 3; ++age) {
-            const uint4 *f = reinterpret_cast<const uint4 *>(frames + (static_cast<size_t>((head + 3 - age) % 3) * n + env) * kFrameBytes);
+            const uint4 *f = reinterpret_cast<const uint4 *>(stack_frame(frames, warm, meta, depth, static_cast<size_t>(n), head, env, age));
 #pragma unroll
             for (int c = 0; c < 3; ++c) q[age][c] = __ldg(f + c * 1024 + v);
         }
@@ -1369,21 +1373,31 @@ void ahk_policy_destroy(ahk_policy *p)
     delete p;
 }
 
-static int policy_forward(ahk_policy *p, const uint8_t *frames, int n, int head, float *logits, uint8_t *action, void *stream, bool timed)
+static int policy_forward(ahk_policy *p, const ahk_stack &stack, float *logits, uint8_t *action, void *stream, bool timed)
 {
+    const uint8_t *frames = stack.frames;
+    const int n = stack.n, head = stack.head;
     if (!p || !frames) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_forward: policy/frames is NULL");
     if (n <= 0 || n > p->max_batch) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_forward: n must be in [1, max_batch]");
-    if (head < 0 || head > 2) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_forward: head must be 0, 1 or 2");
+    if (stack.depth < 3 || head < 0 || head >= stack.depth) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_forward: head must be in [0, depth), depth >= 3");
+    if (stack.warm && !stack.meta) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_forward: a deep ring needs the meta words");
+    int prev_device = -1;
+    POL_CUDA(cudaGetDevice(&prev_device));
+    if (prev_device != p->device) POL_CUDA(cudaSetDevice(p->device));
+    struct Restore { int prev, cur; ~Restore() { if (prev != cur) cudaSetDevice(prev); } } restore{prev_device, p->device};
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     auto tiles = [](long long rows) { return static_cast<int>((rows + kBM - 1) / kBM); };
     Args a{};
     a.n = n;
     a.head = head;
+    a.depth = stack.depth;
+    a.warm = stack.warm;
+    a.meta = stack.meta;
     if (p->gray) { // the 'gray-diff' network: input image + six GEMM-tile layers
         const long long ln = n;
         if (timed) POL_CUDA(cudaEventRecord(p->ev[0], s));
         const int blocks = static_cast<int>((ln * 1024 + 255) / 256);
-        gray_diff_kernel<<<blocks < p->sms * 16 ? blocks : p->sms * 16, 256, 0, s>>>(frames, p->gimg, n, head);
+        gray_diff_kernel<<<blocks < p->sms * 16 ? blocks : p->sms * 16, 256, 0, s>>>(frames, p->gimg, n, head, stack.depth, stack.warm, stack.meta);
         POL_CUDA(cudaGetLastError());
         a.in = p->gimg; a.weights = reinterpret_cast<const uint4 *>(p->gw[0]); a.bias = p->gb[0]; a.out = p->ga1; a.m_total = n * kGP1;
         POL_CUDA(launch<kG1>(a, tiles(ln * kGP1), 1, p->sms, s));
@@ -1433,19 +1447,46 @@ static int policy_forward(ahk_policy *p, const uint8_t *frames, int n, int head,
     return AHK_OK;
 }
 
+static ahk_stack plain_ring(const uint8_t *frames, int n, int head)
+{
+    ahk_stack st{};
+    st.frames = frames;
+    st.n = n;
+    st.depth = 3;
+    st.head = head;
+    return st;
+}
+
 int ahk_policy_forward(ahk_policy *p, const uint8_t *frames, int n, int head, float *logits, uint8_t *action, void *stream)
 {
-    return policy_forward(p, frames, n, head, logits, action, stream, false);
+    return policy_forward(p, plain_ring(frames, n, head), logits, action, stream, false);
+}
+
+int ahk_policy_forward_stack(ahk_policy *p, const ahk_stack *stack, float *logits, uint8_t *action, void *stream)
+{
+    if (!stack) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_forward_stack: stack is NULL");
+    return policy_forward(p, *stack, logits, action, stream, false);
+}
+
+static int forward_profiled(ahk_policy *p, const ahk_stack &stack, float *logits, uint8_t *action, void *stream, float *layer_ms)
+{
+    if (!layer_ms) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_forward_profiled: layer_ms is NULL");
+    if (int rc = policy_forward(p, stack, logits, action, stream, true)) return rc;
+    POL_CUDA(cudaEventSynchronize(p->ev[6]));
+    for (int i = 0; i < 6; ++i) POL_CUDA(cudaEventElapsedTime(layer_ms + i, p->ev[i], p->ev[i + 1]));
+    return AHK_OK;
 }
 
 int ahk_policy_forward_profiled(ahk_policy *p, const uint8_t *frames, int n, int head, float *logits, uint8_t *action,
                                 void *stream, float *layer_ms)
 {
-    if (!layer_ms) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_forward_profiled: layer_ms is NULL");
-    if (int rc = policy_forward(p, frames, n, head, logits, action, stream, true)) return rc;
-    POL_CUDA(cudaEventSynchronize(p->ev[6]));
-    for (int i = 0; i < 6; ++i) POL_CUDA(cudaEventElapsedTime(layer_ms + i, p->ev[i], p->ev[i + 1]));
-    return AHK_OK;
+    return forward_profiled(p, plain_ring(frames, n, head), logits, action, stream, layer_ms);
+}
+
+int ahk_policy_forward_stack_profiled(ahk_policy *p, const ahk_stack *stack, float *logits, uint8_t *action, void *stream, float *layer_ms)
+{
+    if (!stack) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_forward_stack_profiled: stack is NULL");
+    return forward_profiled(p, *stack, logits, action, stream, layer_ms);
 }
 
 } // extern "C"

@@ -52,6 +52,7 @@ struct Luts {
 };
 
 constexpr int kRecordBytes = 3 * kStepThreads * 16;
+static_assert(2 * 3 * kManyEnvs * 16 <= kRecordBytes, "ahk_step_many keeps two record buffers in the space of one");
 
 __device__ __forceinline__ void build_luts(Luts &l)
 {
@@ -274,6 +275,21 @@ __device__ __forceinline__ void draw_unit(const uint4 *__restrict__ s_table, uin
     }
 }
 
+// Where the frame of a draw record goes.  back = 0: the newest frame, ring slot `head`.  back = 1, 2: the warm-up frames
+// that a reset puts behind it in the stack (air_hockey_env.py:69-72) — in the 3-slot ring they rewrite the two older
+// slots; in a deep ring they go to the env's side buffer (stack_frame() in ahk_kernels.cuh reads them back), so that the
+// previous episode's last frames stay in the ring for replay.  An explicit reset (kReset: no step follows in the launch)
+// files all three frames w1, w2, w3 (back 2, 1, 0) at side-buffer indices 0, 1, 2; a step that resets first drops w1 and
+// files w2, w3 (back 2, 1) at indices 1, 2.
+template <bool kReset>
+__device__ __forceinline__ uint8_t *record_frame(const RasterArgs &r, int head, int env, int back)
+{
+    const size_t n = static_cast<size_t>(r.n);
+    if (r.warm != nullptr && (kReset || back > 0))
+        return r.warm + (static_cast<size_t>((kReset ? 2 : 3) - back) * n + static_cast<size_t>(env)) * kFrameBytes;
+    return r.frames + (static_cast<size_t>((head + r.depth - back) % r.depth) * n + static_cast<size_t>(env)) * kFrameBytes;
+}
+
 constexpr int kLutOffset = kFrameBytes + kRecordBytes + (kStepThreads / 32) * kPatchBytes;
 constexpr int kStepSmem = kLutOffset + static_cast<int>(sizeof(Luts));
 
@@ -486,8 +502,7 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_kernel(StepArgs a)
                 const int r = u / kUnitsPerFrame;
                 const uint4 rec_u = s_recs[phase == 0 ? r : 3 * kStepThreads - 1 - r];
                 const int env = base + static_cast<int>((rec_u.w >> 8) & 0x3FFu), back = static_cast<int>(rec_u.w >> 20); // back 0 = newest
-                const int slot = (a.ras.head + 3 - back) % 3;
-                uint8_t *frame = a.ras.frames + (static_cast<size_t>(slot) * stride + env) * kFrameBytes;
+                uint8_t *frame = record_frame<kMode == 0>(a.ras, a.ras.head, env, back);
                 draw_unit(s_table, s_patch, luts, rec_u, u % kUnitsPerFrame, frame, a.ras.env_id_base + static_cast<uint32_t>(env), a.ras.key, lane);
             }
         }
@@ -506,12 +521,122 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_kernel(StepArgs a)
     }
 }
 
+// ------------------------------------------------------------------------------------------------ ahk_step_many
+// T consecutive ACTION-FREE steps in ONE launch (generate_data.py:44-58: the programmed AI plays both sides, nothing outside
+// the engine feeds a step).  Envs are CTA-private, so a CTA simply runs T steps of its own envs: the table and the lookup
+// tables are staged once per launch instead of once per step, there is no launch boundary (no grid-wide drain, no cold
+// instruction cache) between steps, and the game tick of step t + 1 runs on the owner warps (one thread per env) UNDER
+// the stores of step t: owners tick first and leave their records in the other half of the record buffer, then join the
+// other warps in claiming step t's raster units.  One block barrier per step.  State goes through L2 every step as in the
+// single-step kernel (same device code: env_update), so the results are those of T ahk_step calls, bit for bit.
+template <bool kBalance>
+__global__ void __launch_bounds__(kStepThreads, 1) step_many_kernel(StepArgs a, int steps, StepLogArgs log)
+{
+    extern __shared__ __align__(128) uint8_t smem[];
+    const uint4 *s_table = reinterpret_cast<const uint4 *>(smem);
+    uint4 *s_recs = reinterpret_cast<uint4 *>(smem + kFrameBytes); // [2][3 * kManyEnvs] records: step t uses half t & 1
+    Luts &luts = *reinterpret_cast<Luts *>(smem + kLutOffset);
+    __shared__ __align__(8) uint64_t s_table_ready;
+    __shared__ int s_count[4], s_next[4]; // records / claimed units of step t at index t & 3
+    __shared__ unsigned s_stats[kStatWords];
+    __shared__ unsigned s_warps_done;
+    __shared__ unsigned long long s_raster_start;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    uint4 *s_patch = reinterpret_cast<uint4 *>(smem + kFrameBytes + kRecordBytes + warp * kPatchBytes);
+    const uint32_t bar = static_cast<uint32_t>(__cvta_generic_to_shared(&s_table_ready));
+    if (tid < kStatWords) s_stats[tid] = 0u;
+    if (tid < 4) { s_count[tid] = 0; s_next[tid] = 0; }
+    if (tid == 0) {
+        s_warps_done = 0u;
+        s_raster_start = 0ull;
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(bar) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (tid == 0) {
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(kFrameBytes) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     :: "r"(static_cast<uint32_t>(__cvta_generic_to_shared(smem))), "l"(a.ras.table), "r"(kFrameBytes), "r"(bar) : "memory");
+    }
+    build_luts(luts);
+
+    const int n = a.ras.n;
+    const int part = static_cast<int>(blockIdx.x);
+    int lo = part * a.envs_per_cta, hi = min(n, lo + a.envs_per_cta);
+    if (a.bounds != nullptr) { lo = a.bounds[part]; hi = a.bounds[part + 1]; }
+    const int cnt = hi - lo;                       // <= kManyEnvs (checked on the host)
+    const bool owner = tid < ((cnt + 31) & ~31);   // whole warps: the statistics reduce with warp collectives
+    const size_t stride = static_cast<size_t>(n);
+
+    // the game tick of step t for this CTA's envs: records into half t & 1, count at index t & 3
+    auto tick = [&](int t) {
+        const bool live = tid < cnt;
+        const int i = lo + tid;
+        uint4 rec[3] = {make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0)};
+        StatDelta d;
+        if (live) {
+            env_update<true>(a.env, i, rec, d);
+            const size_t at = static_cast<size_t>(t) * stride + i;
+            if (log.robot_label) log.robot_label[at] = static_cast<uint8_t>(d.robot_label);
+            if (log.human_label) log.human_label[at] = static_cast<uint8_t>(d.human_label);
+            if (log.done) log.done[at] = static_cast<uint8_t>(d.terminal);
+            if (log.reward) log.reward[at] = 0.5f * static_cast<float>(d.reward2);
+        }
+        if (a.env.stats != nullptr) stat_to_shared<true>(s_stats, d, live);
+        uint4 *recs = s_recs + (t & 1) * (3 * kManyEnvs);
+#pragma unroll
+        for (int b = 0; b < 3; ++b) {
+            const bool valid = live && (rec[b].w & kDrawValid);
+            const unsigned votes = __ballot_sync(0xFFFFFFFFu, valid);
+            if (votes == 0u) continue;
+            int at = 0;
+            if (lane == 0) at = atomicAdd(&s_count[t & 3], __popc(votes));
+            at = __shfl_sync(0xFFFFFFFFu, at, 0) + __popc(votes & ((1u << lane) - 1u));
+            if (valid) recs[at] = make_uint4(rec[b].x, rec[b].y, rec[b].z, (rec[b].w & 0x1Fu) | static_cast<uint32_t>(tid) << 8 | static_cast<uint32_t>(b) << 20);
+        }
+    };
+
+    if (owner && steps > 0) tick(0);
+    __syncthreads();
+    mbarrier_wait(bar, 0u); // the table is staged
+    if (kBalance && tid == 0) s_raster_start = global_ns();
+
+#pragma unroll 1
+    for (int t = 0; t < steps; ++t) {
+        if (tid == 0) { s_count[(t + 2) & 3] = 0; s_next[(t + 2) & 3] = 0; } // free since the barrier that ended step t - 1
+        if (owner && t + 1 < steps) tick(t + 1);
+        const int total = s_count[t & 3] * kUnitsPerFrame;
+        const uint4 *recs = s_recs + (t & 1) * (3 * kManyEnvs);
+        const int head = (a.ras.head + t) % a.ras.depth; // a.ras.head: the slot of the window's first step
+        for (;;) {
+            int u = 0;
+            if (lane == 0) u = atomicAdd(&s_next[t & 3], 1);
+            u = __shfl_sync(0xFFFFFFFFu, u, 0);
+            if (u >= total) break;
+            const uint4 rec_u = recs[u / kUnitsPerFrame];
+            const int env = lo + static_cast<int>((rec_u.w >> 8) & 0x3FFu), back = static_cast<int>(rec_u.w >> 20);
+            uint8_t *frame = record_frame<false>(a.ras, head, env, back);
+            draw_unit(s_table, s_patch, luts, rec_u, u % kUnitsPerFrame, frame, a.ras.env_id_base + static_cast<uint32_t>(env), a.ras.key, lane);
+        }
+        __syncthreads(); // step t is drawn, step t + 1's records are complete
+    }
+    if (kBalance && a.bounds_next != nullptr) rebalance(a, part, &s_warps_done, &s_raster_start, lane);
+    if (a.env.stats != nullptr) {
+        unsigned long long *st = reinterpret_cast<unsigned long long *>(a.env.stats);
+        if (tid < kStatWords && s_stats[tid] != 0u)
+            atomicAdd(st + tid, tid == 4 ? static_cast<unsigned long long>(static_cast<long long>(static_cast<int>(s_stats[tid]))) : static_cast<unsigned long long>(s_stats[tid]));
+    }
+}
+
 cudaError_t step_prepare()
 {
     cudaError_t e = cudaFuncSetAttribute(step_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStepSmem);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(step_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStepSmem);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(step_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStepSmem);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(step_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStepSmem);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(step_many_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStepSmem);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(step_many_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStepSmem);
     return e;
 }
 
@@ -531,6 +656,14 @@ cudaError_t launch_step(const StepArgs &a, int mode, int grid, cudaStream_t stre
     if (mode == 1 && a.trace) return cudaLaunchKernelEx(&cfg, step_kernel<1, true>, a);
     if (mode == 1) return cudaLaunchKernelEx(&cfg, step_kernel<1>, a);
     return cudaLaunchKernelEx(&cfg, step_kernel<2>, a);
+}
+
+// plain launch: no programmatic overlap with its neighbours (the launch boundary is paid once per `steps` steps)
+cudaError_t launch_step_many(const StepArgs &a, int steps, const StepLogArgs &log, int grid, cudaStream_t stream)
+{
+    if (a.bounds_next != nullptr) step_many_kernel<true><<<grid, kStepThreads, kStepSmem, stream>>>(a, steps, log);
+    else step_many_kernel<false><<<grid, kStepThreads, kStepSmem, stream>>>(a, steps, log);
+    return cudaGetLastError();
 }
 
 } // namespace ahk

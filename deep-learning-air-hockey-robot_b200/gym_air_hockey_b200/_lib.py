@@ -17,12 +17,16 @@ STATE_WORDS, STATS_WORDS, FRAME_BYTES, DIM = 16, 32, 3 * 128 * 128, 128
 
 class Config(C.Structure):  # ahk_config
     _fields_ = [("n_envs", C.c_int32), ("device", C.c_int32), ("seed", C.c_uint64), ("env_id_base", C.c_uint32),
-                ("auto_reset", C.c_int32), ("max_episode_steps", C.c_int32), ("reserved", C.c_int32 * 5)]
+                ("auto_reset", C.c_int32), ("max_episode_steps", C.c_int32), ("ring_depth", C.c_int32), ("reserved", C.c_int32 * 4)]
 
 
 class Buffers(C.Structure):  # ahk_buffers
     _fields_ = [(name, C.c_void_p) for name in
-                ("state", "frames", "reward", "done", "robot_label", "human_label", "info", "stats", "drawlist")]
+                ("state", "frames", "reward", "done", "robot_label", "human_label", "info", "stats", "drawlist", "warm")]
+
+
+class Stack(C.Structure):  # ahk_stack
+    _fields_ = [("frames", C.c_void_p), ("warm", C.c_void_p), ("meta", C.c_void_p), ("n", C.c_int32), ("depth", C.c_int32), ("head", C.c_int32)]
 
 
 class StepLog(C.Structure):  # ahk_step_log
@@ -62,6 +66,10 @@ SYMBOLS = {
     "ahk_host_sync": (_i, [_vp]),
     "ahk_observe": (_i, [_vp, _i, _vp, _vp]),
     "ahk_head": (_i, [_vp]),
+    "ahk_ring_depth": (_i, [_vp]),
+    "ahk_stack_view": (_i, [_vp, C.POINTER(Stack)]),
+    "ahk_policy_forward_stack": (_i, [_vp, C.POINTER(Stack), _vp, _vp, _vp]),
+    "ahk_policy_forward_stack_profiled": (_i, [_vp, C.POINTER(Stack), _vp, _vp, _vp, C.POINTER(C.c_float)]),
     "ahk_set_head": (_i, [_vp, _i]),
     "ahk_set_pending": (_i, [_vp, _vp, _vp]),
     "ahk_launch_count": (_i, [_vp, C.POINTER(C.c_uint64)]),

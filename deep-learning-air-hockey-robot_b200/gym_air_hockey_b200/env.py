@@ -43,10 +43,17 @@ class BatchedAirHockeyEnv(object):
     reward float32[N], terminal bool[N], info {'robot_action': uint8[N], 'human_action': uint8[N]}.
     The observation lives in `self.frames` — uint8 [3, N, 3, 128, 128], a ring whose slot `self.head` is the newest
     frame — and is never copied on the step path; `observation(fmt)` materialises the stacked forms.
+
+    ring_depth > 3 makes the ring DEEP: frames [ring_depth, N, 3, 128, 128], slot = step mod ring_depth, every frame
+    written once and kept for ring_depth steps — the ring then IS the replay memory of the RL loop (rl_agents.py:59-90;
+    `rl.ReplayStore` becomes a view of it) and the staging area of `step_many`.  A reset then files its three warm-up
+    frames in `self.warm` [3, N, 3, 128, 128] instead of rewriting the two older slots (they hold the previous episode's
+    last frames), so the 3-frame stack of an env is found through `stack_view()` / `observation()` / the policy kernels,
+    not by indexing `frames` alone.
     """
 
     def __init__(self, n_envs, mode='rgb', device=0, seed=0, env_id_base=0, auto_reset=True, max_episode_steps=200,
-                 table=None, obs='ring'):
+                 table=None, obs='ring', ring_depth=3):
         self.lib = _lib.load()
         self._ptr_cache = {}
         if not torch.cuda.is_available():
@@ -57,6 +64,9 @@ class BatchedAirHockeyEnv(object):
         self.env_id_base = int(env_id_base)
         self.device = torch.device('cuda', device if isinstance(device, int) else torch.device(device).index or 0)
         self.obs_format = obs
+        self.ring_depth = int(ring_depth)
+        if self.ring_depth < 3:
+            raise ValueError('ring_depth must be at least 3 (the 3-frame stack, processor.py:23)')
         self.height = self.width = self.processor.dim
         self.action_space = Discrete(len(self.processor.actions))
         self.observation_space = Box(0, 255, (9, self.height, self.width))
@@ -66,7 +76,8 @@ class BatchedAirHockeyEnv(object):
         n, dev = self.n_envs, self.device
         with torch.cuda.device(dev):
             self.state = torch.zeros((_lib.STATE_WORDS, n), dtype=torch.int32, device=dev)
-            self.frames = torch.zeros((3, n, 3, 128, 128), dtype=torch.uint8, device=dev)
+            self.frames = torch.zeros((self.ring_depth, n, 3, 128, 128), dtype=torch.uint8, device=dev)
+            self.warm = torch.zeros((3, n, 3, 128, 128), dtype=torch.uint8, device=dev) if self.ring_depth > 3 else None
             self.reward = torch.zeros(n, dtype=torch.float32, device=dev)
             self.done = torch.zeros(n, dtype=torch.uint8, device=dev)
             self.robot_label = torch.zeros(n, dtype=torch.uint8, device=dev)
@@ -76,7 +87,8 @@ class BatchedAirHockeyEnv(object):
             self.drawlist = torch.zeros((3, n, 4), dtype=torch.int32, device=dev)
 
         cfg = _lib.Config(n_envs=n, device=self.device.index, seed=seed, env_id_base=env_id_base,
-                          auto_reset=int(bool(auto_reset)), max_episode_steps=int(max_episode_steps))
+                          auto_reset=int(bool(auto_reset)), max_episode_steps=int(max_episode_steps),
+                          ring_depth=self.ring_depth)
         handle = C.c_void_p()
         _lib.check(self.lib.ahk_create(C.byref(cfg), C.byref(handle)))
         self._h = handle
@@ -86,7 +98,8 @@ class BatchedAirHockeyEnv(object):
         bufs = _lib.Buffers(state=self.state.data_ptr(), frames=self.frames.data_ptr(), reward=self.reward.data_ptr(),
                             done=self.done.data_ptr(), robot_label=self.robot_label.data_ptr(),
                             human_label=self.human_label.data_ptr(), info=self.info_bits.data_ptr(),
-                            stats=self.stats.data_ptr(), drawlist=self.drawlist.data_ptr())
+                            stats=self.stats.data_ptr(), drawlist=self.drawlist.data_ptr(),
+                            warm=self.warm.data_ptr() if self.warm is not None else None)
         _lib.check(self.lib.ahk_bind_buffers(self._h, C.byref(bufs)))
 
     # ------------------------------------------------------------------ lifetime
@@ -119,6 +132,12 @@ class BatchedAirHockeyEnv(object):
     @property
     def head(self):
         return self.lib.ahk_head(self._h)
+
+    def stack_view(self):
+        """ahk_stack: where the current 3-frame stack of every env lives (ring + warm-up side buffer + episode steps)."""
+        st = _lib.Stack()
+        _lib.check(self.lib.ahk_stack_view(self._h, C.byref(st)))
+        return st
 
     @property
     def launches(self):
@@ -245,6 +264,8 @@ class BatchedAirHockeyEnv(object):
             self.processor = DataProcessor(mode=mode)
             self.processor.check_mode()
             self.frames.zero_()
+            if self.warm is not None:
+                self.warm.zero_()
 
     def observation(self, fmt=None):
         """Materialise the stacked observation: 'u8' uint8[N,9,128,128] (newest frame first, processor.py:47-49),

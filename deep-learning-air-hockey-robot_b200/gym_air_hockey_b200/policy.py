@@ -146,13 +146,25 @@ class PolicyNetwork(object):
         """forward() with CUDA events around each layer kernel -> [conv1, conv2, conv3, dense1, dense2, out] in ms."""
         ms = (C.c_float * 6)()
         stream = C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
-        _lib.check(self.lib.ahk_policy_forward_profiled(self._h, C.c_void_p(env.frames.data_ptr()), env.n_envs, int(env.head),
-                                                        C.c_void_p(logits.data_ptr()), C.c_void_p(action.data_ptr()), stream, ms))
+        st = env.stack_view()
+        _lib.check(self.lib.ahk_policy_forward_stack_profiled(self._h, C.byref(st), C.c_void_p(logits.data_ptr()),
+                                                              C.c_void_p(action.data_ptr()), stream, ms))
         self.launches += 6
         return list(ms)
 
     def forward(self, env, logits=None, action=None):
-        return self.forward_ring(env.frames, env.head, logits, action)
+        """The network on the env's current observation — the 3-slot ring or a deep ring (ahk_stack_view)."""
+        n = env.n_envs
+        if logits is None:
+            logits = torch.empty((n, 10), dtype=torch.float32, device=self.device)
+        if action is None:
+            action = torch.empty((n,), dtype=torch.uint8, device=self.device)
+        stream = C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+        st = env.stack_view()
+        _lib.check(self.lib.ahk_policy_forward_stack(self._h, C.byref(st), C.c_void_p(logits.data_ptr()),
+                                                     C.c_void_p(action.data_ptr()), stream))
+        self.launches += 6 if self.mode == 'rgb' else 7
+        return logits, action
 
     def close(self):
         if getattr(self, '_h', None):

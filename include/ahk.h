@@ -56,13 +56,17 @@ typedef struct {
     uint32_t env_id_base;      /* global id of local env 0: results are independent of sharding */
     int32_t auto_reset;        /* 1: reset an env at the start of the step after a terminal / max_episode_steps */
     int32_t max_episode_steps; /* 0 = unlimited; generate_data.py:57 uses 200 */
-    int32_t reserved[5];
+    int32_t ring_depth;        /* frame ring slots: 0 or 3 = the 3-frame stack of processor.py:23; > 3 = a DEEP ring that doubles as
+                                  replay memory / dataset staging (rl_agents.py:59-90: experience_buffer): every frame is written
+                                  to HBM once, slot = step mod ring_depth, and a reset files its warm-up frames in ahk_buffers.warm
+                                  instead of rewriting older slots */
+    int32_t reserved[4];
 } ahk_config;
 
 /* Device memory the engine works in; all caller-owned (SURVEY.md §8b "Ownership"). */
 typedef struct {
     uint32_t *state;      /* [AHK_STATE_WORDS][n] SoA: f32 puck x,y,vx,vy | bottom | top | serve,reset,noise counters | meta */
-    uint8_t *frames;      /* [3][n][3][128][128] ring of CHW uint8 frames; slot `head` is the newest */
+    uint8_t *frames;      /* [ring_depth][n][3][128][128] ring of CHW uint8 frames; slot `head` is the newest */
     float *reward;        /* [n]  air_hockey_env.py:95-145 */
     uint8_t *done;        /* [n]  terminal, air_hockey_env.py:90,147-148 */
     uint8_t *robot_label; /* [n]  info['robot_action'], air_hockey_env.py:92,155 */
@@ -70,6 +74,9 @@ typedef struct {
     uint8_t *info;        /* [n]  bit0 puck_was_hit 1 hit_the_border 2 puck_is_at_the_bottom 3 distance_decreased 4 in_the_target, bits5-6 scored (0 none,1 top,2 bottom) */
     uint64_t *stats;      /* [AHK_STATS_WORDS] running sums: 0 steps, 1 episodes, 2 goals_top, 3 goals_bottom, 4 reward*2 (int64), 5.. robot label hist[10], 15.. human label hist[10] */
     uint32_t *drawlist;   /* [3][n][4] scratch between the env and raster kernels (split path only; the fused kernel keeps it in shared memory) */
+    uint8_t *warm;        /* ring_depth > 3 only (else NULL): [3][n][3][128][128] the warm-up frames w1, w2, w3 of each env's latest reset
+                             (air_hockey_env.py:69-72).  Frame `age` of an env's stack is ring slot (head - age) mod ring_depth when
+                             age < episode_steps (state word 15, low 16 bits), else warm[2 - (age - episode_steps)] */
 } ahk_buffers;
 
 /* ≙ AirHockeyEnv.__init__ (air_hockey_env.py:9-24) minus the first reset. */
@@ -146,6 +153,15 @@ int ahk_step_profiled(ahk_env *env, const uint8_t *robot_dev, const uint8_t *hum
 int ahk_observe(ahk_env *env, int format, void *out_dev, void *stream);
 
 int ahk_head(const ahk_env *env);                 /* ring slot holding the newest frame */
+int ahk_ring_depth(const ahk_env *env);
+/* Everything a consumer needs to find the 3-frame stack of every env (see ahk_buffers.warm): device pointers + head. */
+typedef struct {
+    const uint8_t *frames;  /* [depth][n][3][128][128] */
+    const uint8_t *warm;    /* NULL for the 3-slot ring */
+    const uint32_t *meta;   /* [n] state word 15 (episode_steps in the low 16 bits) */
+    int32_t n, depth, head;
+} ahk_stack;
+int ahk_stack_view(const ahk_env *env, ahk_stack *out);
 int ahk_set_head(ahk_env *env, int head);
 int ahk_set_pending(ahk_env *env, const uint8_t *pending_dev, void *stream); /* arm/disarm the auto-reset per env */
 int ahk_launch_count(const ahk_env *env, uint64_t *kernels); /* kernels launched so far by this handle */
@@ -183,6 +199,11 @@ void ahk_policy_destroy(ahk_policy *p);
  * (either may be NULL). */
 int ahk_policy_forward(ahk_policy *p, const uint8_t *frames_dev, int n, int head, float *logits_dev,
                        uint8_t *action_dev, void *stream);
+/* The same forward pass on an engine's current observation, whatever its ring depth (ahk_stack_view): the act() of the RL
+ * loop (rl_agents.py:92-101) reading the deep ring that doubles as replay memory. */
+int ahk_policy_forward_stack(ahk_policy *p, const ahk_stack *stack, float *logits_dev, uint8_t *action_dev, void *stream);
+int ahk_policy_forward_stack_profiled(ahk_policy *p, const ahk_stack *stack, float *logits_dev, uint8_t *action_dev, void *stream,
+                                      float *layer_ms);
 /* The same forward pass with CUDA events recorded on `stream` around each of its six kernels (conv1, conv2, conv3,
  * dense1, dense2, out); waits, then reports their durations in layer_ms[6].  Measurement aid for bench.py's roofline. */
 int ahk_policy_forward_profiled(ahk_policy *p, const uint8_t *frames_dev, int n, int head, float *logits_dev,

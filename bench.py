@@ -225,7 +225,8 @@ def measure_rollout(args, world, rank, local, barrier, min_s=MIN_REGION_S):
     from gym_air_hockey_b200.rl import DDQNAgent
 
     n = args.rollout_envs
-    env = BatchedAirHockeyEnv(n, device=local, seed=0, env_id_base=rank * n, auto_reset=True, max_episode_steps=256)
+    # ring_depth = replay capacity: the rasteriser writes every frame once, into the slot replay sampling reads it from
+    env = BatchedAirHockeyEnv(n, device=local, seed=0, env_id_base=rank * n, auto_reset=True, max_episode_steps=256, ring_depth=32)
     env.reset()
     agent = DDQNAgent(env, buffer_steps=32, batch_size=32, discount_rate=0.98, eps_min=0.05, eps_max=0.99, eps_decay_steps=100000,
                       seed=0, group=None)
@@ -297,7 +298,7 @@ def measure_rollout(args, world, rank, local, barrier, min_s=MIN_REGION_S):
         "value": total * steps / (train_ms * 1e-3), "unit": "env-steps/s", "steps": steps, "ms_per_step": train_ms / steps,
         "rollout_only": {"value": total * steps / (roll_ms * 1e-3), "ms_per_step": roll_ms / steps},
         "fits": fits, "fit_batch": 32, "fit_interval": interval,
-        "config": {"workload": "configs[3]: %d envs/GPU, act = CNN forward (models.py:20-65, random init) on the uint8 ring + epsilon-greedy, env step (human = programmed AI), replay store, DDQN fit every 25 steps (rl_agents.py:177-191)%s"
+        "config": {"workload": "configs[3]: %d envs/GPU, act = CNN forward (models.py:20-65, random init) on the uint8 ring + epsilon-greedy, env step (human = programmed AI), replay memory = the engine's 32-deep frame ring (no copies), DDQN fit every 25 steps (rl_agents.py:177-191)%s"
                                % (n, ", gradients + BatchNorm statistics all-reduced over NCCL (2 403 961 float32)" if world > 1 else ""),
                    "envs_per_gpu": n, "total_envs": total, "mode": "rgb", "episode_length": 256},
         "gpu_launches": launches,
@@ -380,6 +381,7 @@ def main():
         env.step_many(chunk)
         t_host += time.perf_counter() - h0
         evs[k + 1].record(stream)
+    t_host_calls = steps
     barrier()
     t_region1 = time.perf_counter()
     ms = evs[0].elapsed_time(evs[steps])
@@ -521,8 +523,8 @@ def main():
             "bench_step_ms": {"median": step_med, "min": step_min, "max": step_max},
             "timed_region_s": ms * 1e-3,
             "gpu_launches": launches,
-            "host": {"us_per_env_step_in_step_many": t_host / env_steps * 1e6, "us_per_env_step_call_python": host_us_step,
-                     "note": "host time to ENQUEUE one env step: inside ahk_step_many (C loop) and through env.step() from Python; both must stay below us_per_env_step or the stream starves"},
+            "host": {"us_per_step_many_call": t_host / t_host_calls * 1e6, "us_per_env_step_call_python": host_us_step,
+                     "note": "host time to ENQUEUE work: one ahk_step_many call (%d env steps in one kernel launch) and one env.step() call from Python (one launch per env step, on an idle stream); the latter must stay below us_per_env_step or a step-by-step loop starves the stream" % chunk},
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                          "frac": achieved / peaks["hbm_gbs"], "traffic": traffic, "traffic_source": traffic_src,

@@ -147,12 +147,14 @@ class KerasSGD(object):
 
 
 # ---------------------------------------------------------------------------------------------- replay memory
-def valid_transitions(pending, cursor, filled, need_next=True):
+def valid_transitions(pending, cursor, filled, need_next=True, stale=None):
     """Which (slot, env) pairs of a ReplayStore can be sampled.  pending: uint8 [capacity, n], 1 where the env was armed
     for an auto-reset after that step (so the NEXT step rewrote all three ring slots with warm-up frames,
     air_hockey_env.py:69-72).  A transition at slot t uses frames t-2..t+1 (state = t, t-1, t-2; next state = t+1, t,
     t-1): all four must be recorded, consecutive, and no reset may fall on steps t-1, t, t+1 (pending at t-2, t-1, t).
-    `cursor` = slot the next step will be written to, `filled` = recorded steps (<= capacity).  Returns bool [capacity, n]."""
+    `cursor` = slot the next step will be written to, `filled` = recorded steps (<= capacity).  stale: optional uint8
+    [capacity, n], 1 where the slot holds no frame of that env (a deep ring right after an explicit reset, whose frames sit
+    in the warm-up side buffer): no window may contain such a slot.  Returns bool [capacity, n]."""
     cap = pending.shape[0]
     age = (cursor - 1 - torch.arange(cap, device=pending.device)) % cap  # 0 = newest recorded slot
     lo = 1 if need_next else 0                                              # t+1 must exist
@@ -161,29 +163,48 @@ def valid_transitions(pending, cursor, filled, need_next=True):
     ok = clear.roll(2, 0) & clear.roll(1, 0)                                # steps t-1, t were not resets
     if need_next:
         ok = ok & clear                                                     # step t+1 was not a reset
+    if stale is not None:
+        good = stale == 0
+        ok = ok & good & good.roll(1, 0) & good.roll(2, 0)                  # frames t, t-1, t-2
+        if need_next:
+            ok = ok & good.roll(-1, 0)                                      # frame t+1
     return ok & ok_t[:, None]
 
 
 class ReplayStore(object):
     """≙ Agent.experience_buffer (rl_agents.py:61-62,88-90): `capacity` steps of all n envs.  Frames are kept once, as
-    uint8 (49 152 B per env-step); the reference keeps two float32 (9,128,128) stacks per transition (1.18 MB)."""
+    uint8 (49 152 B per env-step); the reference keeps two float32 (9,128,128) stacks per transition (1.18 MB).
 
-    def __init__(self, env, capacity):
-        if capacity < 4:
-            raise ValueError('capacity must be at least 4 steps')
+    Two forms.  With the engine's 3-slot ring the store is its own uint8 [capacity, n, 3, 128, 128] buffer and every step's
+    newest frame is copied in (one device-to-device copy per step).  With a DEEP ring (`BatchedAirHockeyEnv(ring_depth=D)`,
+    D > 3) the store is a VIEW of the ring: the rasteriser wrote each frame where replay sampling reads it, nothing is
+    copied, capacity = D and slot = the ring slot of the step (`env.head`)."""
+
+    def __init__(self, env, capacity=None):
         self.lib = _lib.load()
+        self.view = getattr(env, 'ring_depth', 3) > 3
+        capacity = env.ring_depth if self.view else capacity
+        if capacity is None or capacity < 4:
+            raise ValueError('capacity must be at least 4 steps')
         self.n, self.capacity, self.device = env.n_envs, int(capacity), env.device
         n, dev = self.n, self.device
-        self.frames = torch.zeros((self.capacity, n, 3, 128, 128), dtype=torch.uint8, device=dev)
+        self.frames = env.frames if self.view else torch.zeros((self.capacity, n, 3, 128, 128), dtype=torch.uint8, device=dev)
         self.action = torch.zeros((self.capacity, n), dtype=torch.uint8, device=dev)
         self.reward = torch.zeros((self.capacity, n), dtype=torch.float32, device=dev)
         self.done = torch.zeros((self.capacity, n), dtype=torch.uint8, device=dev)
         self.pending = torch.zeros((self.capacity, n), dtype=torch.uint8, device=dev)
-        self.cursor, self.filled = 0, 0
+        self.stale = torch.zeros((self.capacity, n), dtype=torch.uint8, device=dev) if self.view else None
+        self.cursor, self.filled = (env.head + 1) % self.capacity if self.view else 0, 0
 
     def reset(self):
-        """≙ Agent._reset_experience_buffer (rl_agents.py:61-62)."""
-        self.cursor, self.filled = 0, 0
+        """≙ Agent._reset_experience_buffer (rl_agents.py:61-62).  (A view keeps following the ring's slots.)"""
+        self.filled = 0
+        if not self.view:
+            self.cursor = 0
+
+    def next_slot(self, env):
+        """The slot the next record() will fill: the ring slot of the coming step (view) or the store's own cursor."""
+        return (env.head + 1) % self.capacity if self.view else self.cursor
 
     def record_observation(self, env):
         """Store the newest frame of every env with no transition attached (the observation an episode starts from)."""
@@ -195,8 +216,12 @@ class ReplayStore(object):
         self._put(env, action, reward, done)
 
     def _put(self, env, action, reward, done):
-        t = self.cursor
-        self.frames[t].copy_(env.frames[env.head])  # 49 152 B per env, device to device
+        if self.view:
+            t = env.head                                 # the rasteriser already wrote the frame here
+            self.stale[t].copy_((env.state[15] & 0xFFFF) == 0)  # no step since an explicit reset: its frames are in env.warm
+        else:
+            t = self.cursor
+            self.frames[t].copy_(env.frames[env.head])  # 49 152 B per env, device to device
         if action is None:
             self.action[t].zero_(); self.reward[t].zero_(); self.done[t].zero_()
         else:
@@ -219,7 +244,7 @@ class ReplayStore(object):
     def sample(self, batch_size, generator=None, need_next=True):
         """≙ Agent._sample_experiences (rl_agents.py:64-77): up to batch_size distinct transitions, uniformly.
         -> dict(frames [4,B,...], action = the action taken in s_t, reward, done of s_t -> s_{t+1}, t, env) or None."""
-        ok = valid_transitions(self.pending, self.cursor, self.filled, need_next)
+        ok = valid_transitions(self.pending, self.cursor, self.filled, need_next, self.stale)
         flat = ok.reshape(-1).nonzero().squeeze(1)
         if flat.numel() == 0:
             return None
@@ -253,7 +278,7 @@ class Agent(object):
         self.group = group
         self.model = TrainableNetwork(weights).to(self.device).use_channels_last()
         self.policy = PolicyNetwork(self.model.keras_weights(), max_batch=max(self.n, self.batch_size), device=self.device.index)
-        self.replay = ReplayStore(env, buffer_steps)
+        self.replay = ReplayStore(env, buffer_steps)  # a view of the ring when the env has a deep one (then capacity = its depth)
         self.bucket = GradientBucket(self.model.parameters())
         self.gen = torch.Generator(device=self.device)
         self.gen.manual_seed(int(seed))
@@ -403,6 +428,8 @@ class PGAgent(Agent):
 
     def __init__(self, env, weights=None, learning_rate=0.01, episode_length=256, fit_batch=32, **kw):
         kw.setdefault('buffer_steps', episode_length + 3)
+        if getattr(env, 'ring_depth', 3) > 3 and env.ring_depth < episode_length + 3:
+            raise ValueError('PGAgent needs ring_depth >= episode_length + 3 to keep an episode in a deep ring')
         super().__init__(env, weights, **kw)
         self.learning_rate, self.episode_length, self.fit_batch = float(learning_rate), int(episode_length), int(fit_batch)
         self.optimizer = torch.optim.Adam(self.model.parameters(), lr=1e-3, betas=(0.9, 0.999), eps=1e-7)
@@ -416,7 +443,7 @@ class PGAgent(Agent):
     def store_experience(self, action, reward, done):
         """≙ PGAgent.store_experience (rl_agents.py:246-253); the prediction of the state the action was taken in is
         filed with the step's slot."""
-        self.prob[self.replay.cursor].copy_(self._prediction)
+        self.prob[self.env.head if self.replay.view else self.replay.cursor].copy_(self._prediction)  # the slot record() fills
         self.replay.record(self.env, action, reward, done)
 
     def train(self):
@@ -434,7 +461,7 @@ class PGAgent(Agent):
         _lib.check(self.lib.ahk_rl_pg_returns(_ptr(reward), _ptr(ends), steps - 1, self.n, self.discount_rate, _ptr(returns),
                                               _stream(self.device)))
         # sample (k, e): the action of step k was taken in the state whose newest frame sits one slot earlier
-        ok = valid_transitions(rp.pending, rp.cursor, rp.filled, need_next=True)[order]
+        ok = valid_transitions(rp.pending, rp.cursor, rp.filled, need_next=True, stale=rp.stale)[order]
         k_idx, e_idx = ok[:-1].nonzero(as_tuple=True)  # state slot = order[k]; its action/reward/prob are at order[k+1]
         perm = torch.randperm(k_idx.numel(), device=self.device, generator=self.gen)  # fit(shuffle=True)
         # every fit batch issues two collectives (gradients, BatchNorm statistics) and the number of valid transitions

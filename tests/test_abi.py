@@ -29,8 +29,11 @@ def test_library_exports_every_declared_symbol():
 
 def test_struct_layouts_match_header():
     from gym_air_hockey_b200 import _lib
-    assert C.sizeof(_lib.Config) == 48            # int32 x2, uint64, uint32, int32 x2, int32 x5 (+ padding to 8)
-    assert C.sizeof(_lib.Buffers) == 9 * 8
+    assert C.sizeof(_lib.Config) == 48            # int32 x2, uint64, uint32, int32 x3, int32 x4 (+ padding to 8)
+    assert _lib.Config.ring_depth.offset == 28
+    assert C.sizeof(_lib.Buffers) == 10 * 8
+    assert C.sizeof(_lib.Stack) == 3 * 8 + 3 * 4 + 4
+    assert C.sizeof(_lib.StepLog) == 4 * 8
     assert C.sizeof(_lib.PolicyWeights) == 24 * 8
     assert C.sizeof(_lib.GrayPolicyWeights) == 28 * 8
 

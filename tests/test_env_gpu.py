@@ -470,6 +470,59 @@ def test_step_many_matches_oracle(cuda, orc, table, n, T, limit):
     pool.close()
 
 
+@pytest.mark.parametrize("depth", [3, 8, 67])
+def test_ring_depth_matches_oracle(cuda, orc, noise_table, depth):
+    """ahk_config.ring_depth: the ring as replay memory / staging area.  Every step's newest frame goes to slot
+    step mod depth and stays there for `depth` steps (written once); a reset files its warm-up frames in the side buffer
+    instead of rewriting older slots, and the 3-frame stack found through ahk_stack_view (observation('u8')) is the
+    oracle's ring at every step — single steps, step_many windows, explicit masked resets, resets one step apart
+    (limit 1 on the last stretch is covered by max_episode_steps=2 here: every other step resets)."""
+    torch = cuda
+    n, seed, limit = 333, 77, 2 if depth == 8 else 11
+    env = make_env(n, noise_table, seed=seed, auto_reset=True, max_episode_steps=limit, ring_depth=depth)
+    oracles = oracle_envs(orc, n, noise_table, seed)
+    assert env.frames.shape[0] == depth and (env.warm is None) == (depth == 3)
+    env.reset()
+    for o in oracles:
+        o.reset()
+    newest_log = {}                                     # absolute step -> the oracle's newest frame of every env
+
+    def check(step):
+        u8 = env.observation('u8').cpu().numpy().reshape(n, 3, 3, 128, 128)
+        for i, o in enumerate(oracles):
+            assert np.array_equal(u8[i], o.ring()), (step, i)
+        assert_same_state(env, oracles, "step %d" % step)
+
+    check(0)
+    step = 0
+    for chunk in (1, 1, 1, 5, 1, depth + 2, 1, 2):
+        if chunk == 1:
+            env.step()
+        else:
+            env.step_many(chunk)
+        for _ in range(chunk):
+            step += 1
+            for o in oracles:
+                o.step_auto(255, 255, limit)
+            newest_log[step] = np.stack([o.ring()[0] for o in oracles[:40]])
+        check(step)
+        if step == 8:                                   # an explicit masked reset in the middle
+            mask = (np.arange(n) % 3 == 0).astype(np.uint8)
+            env.reset(mask=mask)
+            for i in np.nonzero(mask)[0]:
+                oracles[i].reset()
+            check(step)
+    # the deep ring still holds the newest frames of the last `depth` steps, each where it was written
+    fr = env.frames[:, :40].cpu().numpy()
+    h = env.head
+    _, meta = env.get_state()
+    for back in range(min(depth, step)):
+        if depth == 3 and back > 0:
+            break                                       # the 3-slot ring rewrites older slots on a reset: only the newest is certain
+        assert np.array_equal(fr[(h - back) % depth], newest_log[step - back]), back
+    assert env.statistics()['steps'] == n * step
+
+
 def test_full_size_properties(cuda, table):
     """configs[1] at full size (4096 envs): properties that need no oracle — determinism, independence of sharding
     (global env ids, SPEC.md §4), bodies inside the rink, statistics that add up."""

@@ -113,6 +113,37 @@ def test_policy_forward_8192_samples_matches_reference(cuda, table, mode):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("mode", ["rgb", "gray-diff"])
+def test_policy_forward_on_a_deep_ring(cuda, table, mode):
+    """ahk_policy_forward_stack: the network on an engine whose ring is deep (ring_depth 9) — envs one and two steps past a
+    reset take their older frames from the warm-up side buffer.  The logits must be the bits the same network gives on
+    the materialised stack laid out as a plain 3-slot ring, and match the float32 restatement."""
+    import cnn_ref
+    from gym_air_hockey_b200 import BatchedAirHockeyEnv
+    from gym_air_hockey_b200.policy import GRAY_SHAPES, SHAPES, PolicyNetwork, keras_default_init
+    torch = cuda
+    n = 150
+    w = keras_default_init(seed=8, randomize_bn=True, shapes=SHAPES if mode == 'rgb' else GRAY_SHAPES)
+    net = PolicyNetwork(w, max_batch=256, mode=mode)
+    env = BatchedAirHockeyEnv(n, table=table, seed=17, max_episode_steps=3, ring_depth=9)
+    env.reset()
+    for _ in range(11):
+        env.step()
+    _, meta = env.get_state()
+    assert {1, 2, 3} <= set(meta['episode_steps'].tolist())      # stacks with two, one and no warm-up frames
+    logits, action = net.forward(env)
+    u8 = env.observation('u8')                                    # [n, 9, 128, 128] newest first
+    ring = u8.reshape(n, 3, 3, 128, 128).permute(1, 0, 2, 3, 4).flip(0).contiguous()  # slots oldest..newest, head = 2
+    logits3, action3 = net.forward_ring(ring, 2)
+    torch.cuda.synchronize()
+    assert torch.equal(logits, logits3) and torch.equal(action, action3)
+    fwd = cnn_ref.forward if mode == 'rgb' else cnn_ref.forward_gray
+    ref16 = fwd(w, u8.cpu().numpy(), emulate_bf16=True)
+    scale = max(np.abs(ref16).max(), 1e-6)
+    assert np.abs(logits.cpu().numpy() - ref16).max() <= 6e-3 * scale
+
+
+@pytest.mark.gpu
 def test_policy_in_the_loop(cuda, table):
     """keras/test.py:36-51 as a batched loop: frames -> CNN -> argmax -> env.step, all on the device."""
     from gym_air_hockey_b200 import BatchedAirHockeyEnv

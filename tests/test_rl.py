@@ -224,16 +224,19 @@ def test_epsilon_greedy_kernel(cuda):
 
 
 @pytest.mark.gpu
-def test_replay_store_windows_are_the_ring(cuda, table):
+@pytest.mark.parametrize("view", [False, True])
+def test_replay_store_windows_are_the_ring(cuda, table, view):
     """Every sampled transition's gathered frames equal the observation the env actually showed at that step (and the
-    next one); windows that would straddle a reset are never sampled."""
+    next one); windows that would straddle a reset are never sampled.  view: the store is the engine's deep ring itself
+    (ring_depth = capacity): no frame is copied, and sampling must give exactly what the copying store gives."""
     torch = cuda
     from gym_air_hockey_b200 import BatchedAirHockeyEnv
     from gym_air_hockey_b200.rl import ReplayStore, stacked
     n, cap, steps = 24, 16, 41
-    env = BatchedAirHockeyEnv(n, table=table, seed=21, max_episode_steps=9)
+    env = BatchedAirHockeyEnv(n, table=table, seed=21, max_episode_steps=9, ring_depth=cap if view else 3)
     env.reset()
     store = ReplayStore(env, cap)
+    assert store.view == view and (store.frames.data_ptr() == env.frames.data_ptr()) == view
     obs_log, act_log, rew_log, done_log = {}, {}, {}, {}
     store.record_observation(env)
     obs_log[0] = env.observation('u8').cpu().numpy()
@@ -244,7 +247,9 @@ def test_replay_store_windows_are_the_ring(cuda, table):
         store.record(env, action, reward, done)
         obs_log[s] = env.observation('u8').cpu().numpy()
         act_log[s], rew_log[s], done_log[s] = action.cpu().numpy(), reward.cpu().numpy().copy(), done.cpu().numpy().copy()
-    assert store.filled == cap and store.cursor == (steps + 1) % cap
+    assert store.filled == cap
+    if not view:
+        assert store.cursor == (steps + 1) % cap
     batch = store.sample(10 ** 6, gen)          # everything that is valid
     b = batch['t'].numel()
     assert 0 < b < cap * n
@@ -313,13 +318,15 @@ def test_set_weights_dev_equals_host_path(cuda):
 
 
 @pytest.mark.gpu
-def test_ddqn_training_loop(cuda, table):
+@pytest.mark.parametrize("ring_depth", [3, 16])
+def test_ddqn_training_loop(cuda, table, ring_depth):
     """train.py:76-118 batched: act / step / store / train every 5 iterations / target copy.  The fitted weights must
-    reach the forward kernels (their Q values track the float32 module) and the losses must be finite."""
+    reach the forward kernels (their Q values track the float32 module) and the losses must be finite.  ring_depth 16: the
+    replay memory is the engine's deep ring (no frame copies), acting reads the stack through ahk_stack_view."""
     torch = cuda
     from gym_air_hockey_b200 import BatchedAirHockeyEnv
     from gym_air_hockey_b200.rl import DDQNAgent, run_training, stacked
-    env = BatchedAirHockeyEnv(48, table=table, seed=5, max_episode_steps=40)
+    env = BatchedAirHockeyEnv(48, table=table, seed=5, max_episode_steps=40, ring_depth=ring_depth)
     env.reset()
     agent = DDQNAgent(env, buffer_steps=16, batch_size=32, discount_rate=0.98, eps_min=0.05, eps_max=0.99, eps_decay_steps=100, seed=7)
     w_before = agent.model.keras_weights()
@@ -341,11 +348,12 @@ def test_ddqn_training_loop(cuda, table):
 
 
 @pytest.mark.gpu
-def test_pg_training_loop(cuda, table):
+@pytest.mark.parametrize("ring_depth", [3, 13])
+def test_pg_training_loop(cuda, table, ring_depth):
     torch = cuda
     from gym_air_hockey_b200 import BatchedAirHockeyEnv
     from gym_air_hockey_b200.rl import PGAgent, run_training
-    env = BatchedAirHockeyEnv(16, table=table, seed=6, max_episode_steps=12)
+    env = BatchedAirHockeyEnv(16, table=table, seed=6, max_episode_steps=12, ring_depth=ring_depth)
     env.reset()
     agent = PGAgent(env, episode_length=10, fit_batch=32, discount_rate=0.98, eps_min=0.05, eps_max=0.99, eps_decay_steps=100, seed=8)
     w_before = agent.model.keras_weights()

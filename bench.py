@@ -64,7 +64,8 @@ def measured_peaks():
 
 def ncu_traffic(pattern):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch from the NEWEST committed ncu summary matching `pattern`
-    (tools/ncu_summary.py output under profiles/), or None.  Returns (bytes, file name)."""
+    (tools/ncu_summary.py output under profiles/), or None.  Returns (bytes, file name).  A `_T<k>_` in the file name says
+    the captured launches ran k env steps each (the persistent ahk_step_many kernel)."""
     files = sorted(glob.glob(os.path.join(ROOT, "profiles", pattern)), key=os.path.getmtime)
     unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
     for path in reversed(files):
@@ -495,21 +496,27 @@ def main():
         env_steps = steps * chunk
         value = total_envs * env_steps / (ms * 1e-3)
         fused = env_ms == 0.0
-        kernel_bytes = n * (BYTES_PER_STEP if fused else RASTER_BYTES_PER_FRAME)
-        kernel_name = "step_kernel<1> (fused physics+AI+label+raster)" if fused else \
+        persistent = fused and launches == steps  # ahk_step_many took the persistent kernel: one launch per bench step
+        steps_per_launch = env_steps / max(launches, 1) if fused else 1
+        kernel_bytes = n * (BYTES_PER_STEP if fused else RASTER_BYTES_PER_FRAME) * steps_per_launch
+        kernel_name = ("step_many_kernel (persistent: %d env steps per launch, fused physics+AI+label+raster)" % steps_per_launch) if persistent else \
+            "step_kernel<1> (fused physics+AI+label+raster)" if fused else \
             ("raster_staged_kernel" if os.environ.get("AHK_RASTER") == "staged" else "step_kernel<2> (raster only)")
         # Fused path: the timed region consists of exactly `launches` launches of the one kernel, back to back on one
-        # stream, so its average launch duration is region / launches.  (Consecutive launches overlap by programmatic
-        # dependent launch; isolated_kernel_ms, taken with events BETWEEN launches, cannot overlap.)
+        # stream, so its average launch duration is region / launches.  (isolated_kernel_ms: ONE single-step launch of
+        # step_kernel<1> with events on both sides — what ahk_step costs when nothing overlaps it.)
         kernel_ms = ms / max(launches, 1) if fused else raster_ms
         achieved = kernel_bytes / (kernel_ms * 1e-3) / 1e9
         step_gbs = n * BYTES_PER_STEP / (ms / env_steps * 1e-3) / 1e9
         write_peak = None
-        wp = os.path.join(ROOT, "profiles", "wprobe_r1b.json")  # tools/wprobe.cu: pure write streams over the same footprint
-        if os.path.exists(wp):
-            with open(wp) as f:
+        wps = sorted(glob.glob(os.path.join(ROOT, "profiles", "wprobe_*.json")), key=os.path.getmtime)  # tools/wprobe.cu
+        if wps:
+            with open(wps[-1]) as f:
                 write_peak = max(r["steady_GBs"] for r in json.load(f)["results"])
-        traffic, traffic_src = ncu_traffic("step_kernel_*_ncu.txt") if (fused and n == 4096) else (None, None)
+        traffic, traffic_src = ncu_traffic("step_many_T*_ncu.txt") if (fused and n == 4096) else (None, None)
+        if traffic is not None:  # per captured launch of T env steps -> per launch of this run
+            t_cap = int(re.search(r"_T(\d+)_", traffic_src).group(1))
+            traffic = traffic / t_cap * (env_steps / max(launches, 1))
         e2e_value = total_envs * e2e_steps / res_s
         line = {
             "metric": METRIC, "value": value, "unit": "env-steps/s", "n_gpus": world, "steps": steps,
@@ -534,7 +541,8 @@ def main():
                          "whole_step": {"achieved": step_gbs, "frac": step_gbs / peaks["hbm_gbs"], "bytes_per_env_step": BYTES_PER_STEP},
                          "write_only_peak": write_peak,
                          "frac_of_write_only_peak": (achieved / write_peak) if write_peak else None,
-                         "note": "the path only WRITES; write_only_peak = best steady-state pure write stream over the same 3 x 201 MB ring (tools/wprobe.cu -> profiles/wprobe_r1b.json); peak = MEASURED_PEAKS.json copy (read+write); traffic = ncu dram bytes of one launch from the newest profiles/step_kernel_*_ncu.txt (below the algorithmic bytes: a launch ends with part of its frames still dirty in L2)"},
+                         "env_steps_per_launch": steps_per_launch,
+                         "note": "the path only WRITES; write_only_peak = best steady-state pure write stream over the same 3 x 201 MB ring (tools/wprobe.cu -> profiles/wprobe_*.json); peak = MEASURED_PEAKS.json copy (read+write); traffic = ncu dram bytes per launch scaled from the newest profiles/step_many_T*_ncu.txt capture"},
             "e2e": {"value": e2e_value, "unit": "env-steps/s", "h2d_bytes_per_step": 2 * n, "d2h_bytes_per_step": 7 * n,
                     "calls": e2e_steps, "timed_region_s": res_s, "le_value": bool(e2e_value <= value * 1.02),
                     "note": "ahk_step_host_results, ONE call per ENV step, the host reads the step's result before the next call: actions (2 B/env) read from pinned host memory and reward/done/labels (7 B/env) written to pinned host memory by the step kernel itself (mapped, zero-copy); the call returns when the results have landed (game ticks over), the frames stay in the HBM ring and are complete at the host_sync that closes the timed region",

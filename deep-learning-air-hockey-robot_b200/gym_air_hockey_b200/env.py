@@ -255,6 +255,12 @@ class BatchedAirHockeyEnv(object):
             out['frame'] = pin((n, 3, 128, 128), torch.uint8)
         return out
 
+    def set_pending(self, pending):
+        """Arm (1) or disarm (0) the auto-reset of each env: an armed env restarts at the beginning of its next step
+        (ahk_set_pending) — what `if reset: env.reset()` does per env in the reference's loops (generate_data.py:47-49)."""
+        p = self._labels(pending)
+        _lib.check(self.lib.ahk_set_pending(self._h, _ptr(p), self._stream()))
+
     def update(self, video_file=None, mode=None):
         """≙ AirHockeyEnv.update (air_hockey_env.py:78-82).  A new mode means a new DataProcessor, whose frame stack
         starts as zeros (processor.py:23) — so the ring is cleared, as in the reference."""

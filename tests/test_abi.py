@@ -104,5 +104,7 @@ def test_bench_reads_ncu_traffic_from_the_newest_profile():
     spec.loader.exec_module(bench)
     traffic, src = bench.ncu_traffic("step_kernel_*_ncu.txt")
     assert src is not None and src.startswith("step_kernel_") and 100e6 < traffic < 250e6
+    traffic, src = bench.ncu_traffic("step_many_T*_ncu.txt")
+    assert src.startswith("step_many_T16_") and 16 * 150e6 < traffic < 16 * 250e6
     assert bench.ncu_traffic("no_such_kernel_*.txt") == (None, None)
     assert bench.cpu_reference_wrapper()["B3_reference_wrapper_over_oracle_simulator"]["rgb"]["frames"] == 10000

@@ -125,9 +125,11 @@ def test_policy_forward_on_a_deep_ring(cuda, table, mode):
     n = 150
     w = keras_default_init(seed=8, randomize_bn=True, shapes=SHAPES if mode == 'rgb' else GRAY_SHAPES)
     net = PolicyNetwork(w, max_batch=256, mode=mode)
-    env = BatchedAirHockeyEnv(n, table=table, seed=17, max_episode_steps=3, ring_depth=9)
+    env = BatchedAirHockeyEnv(n, table=table, seed=17, max_episode_steps=50, ring_depth=9)
     env.reset()
-    for _ in range(11):
+    for t in range(11):
+        if t in (8, 9, 10):  # a third of the envs restarts before each of the last three steps: episode_steps 3, 2, 1 at the end
+            env.set_pending(cuda.from_numpy((np.arange(n) % 3 == t - 8).astype(np.uint8)).cuda() | ((env.state[15] >> 21) & 1).to(cuda.uint8))
         env.step()
     _, meta = env.get_state()
     assert {1, 2, 3} <= set(meta['episode_steps'].tolist())      # stacks with two, one and no warm-up frames

@@ -21,6 +21,7 @@
 #include "ahk_kernels.cuh"
 
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 
 #include <cmath>
 #include <cstdio>
@@ -677,6 +678,253 @@ cudaError_t launch_conv1(const Args &a, int grid, cudaStream_t s)
     return cudaGetLastError();
 }
 
+
+// ------------------------------------------------------------------------------------------------ conv1, phase-separated
+// The Toeplitz form above spends two thirds of its columns on stride phases a row does not have (N = 144 = 3 kernel-row
+// groups x 3 PHASES x 16; a row (i, xb) only uses the 48 columns of phase xb mod 3), and its K window starts 16 bytes
+// into a 128-byte core matrix, so every second core matrix straddles two shared-memory lines.  Here the M rows of one
+// MMA all have the SAME phase, so N = 48 (3 kernel-row groups x (3 outputs x 5 channels, padded to 16)):
+//   * shared layout per colour plane and row class c = row mod 3: four arrays A0..A3 of [q = 0..4][il = 0..22] x 16 bytes
+//     (one 8-pixel block of one input row, fp16), A_a holding blocks 3q + a — A3 repeats blocks 3, 6, 9, 12 of A0 next
+//     to block 15 (+25 % of the conversion stores).  For phase ph the K = 16 window of row (q, il) is block 3q + ph in
+//     A_ph followed by block 3q + ph + 1 in A_{ph+1}: K core 1 lies one array pitch (LBO = 2048) behind K core 0, both
+//     128-byte aligned, and the 128 M rows are simply 128 consecutive 16-byte rows of the array (SBO = 128): r = 23 q + il.
+//     Outputs x = 8q + 3 ph + jj (jj < 3) sit at offset ph + 3 jj of the window; x = 40 = 8*4 + 6 + 2 is phase 2's third
+//     output of q = 4, so five blocks per phase suffice (5 x 23 = 115 of 128 rows).
+//   * a work item is HALF a sample: input-row indices i0 .. i0 + 22 (i0 = 0 or 20) give output rows 0..19 or 20..40 — one
+//     M tile per phase, three accumulators of 48 columns per item, double-buffered in TMEM (2 x 256 columns), nine
+//     24 KB stages (one colour plane of one stack age each) of 9 MMAs per item: 162 MMAs of N = 48 per sample instead
+//     of 189 of N = 144.
+//   * the A operand is fp16, not bf16: 0..255 is exact in both, and uint8 -> fp16 is one PRMT + one HSUB2 per two pixels
+//     (0x6400 | v is the half 1024 + v) against five instructions through float32; the weights are fp16 too (kind::f16
+//     takes either; |w| <= 0.09 stays in fp16's normal range with 11 significant bits against bf16's 8) and the 1/128
+//     of the input normalisation moves from the weights to the epilogue.
+// Roles as before: 8 producer warps (global uint8 -> registers -> fp16 -> shared, three tasks of 1 KB in flight per
+// warp), 1 MMA warp, 4 epilogue warps (kernel-row groups summed across rows through a 14 KB exchange).
+namespace c1p {
+constexpr int kProducers = 256, kCta = kProducers + 32 + 128;
+constexpr int kStages = 3;
+constexpr int kRowsQ = 23, kQ = 5, kRowsUsed = kRowsQ * kQ;     // 115 M rows per phase
+constexpr int kAP = 128 * 16;                                   // array pitch = LBO: 128 rows of 16 bytes
+constexpr int kClassBytes = 4 * kAP, kStageBytes = 3 * kClassBytes; // 24 576 B: one colour plane of one half sample
+constexpr int kN = 48;
+constexpr int kWBlock = 16 * kN * 2;                            // one (plane, class, phase) B operand
+constexpr int kWBlocks = 9 * 3 * 3, kWBytes = kWBlocks * kWBlock; // 124 416 B, resident
+constexpr int kExBytes = 2 * kRowsQ * kQ * 16 * 4;              // exchange of the kv = 1, 2 partial sums
+constexpr int kSmem = kWBytes + kStages * kStageBytes + kExBytes; // 212 864 B
+constexpr int kTasksPerStage = 12;                              // (class, 32-pixel quarter of the row)
+constexpr int kTmemCols = 512, kBufCols = 256;
+} // namespace c1p
+
+// instruction descriptor: D f32, A/B fp16, both K-major, M = 128
+__host__ __device__ constexpr uint32_t instr_desc_f16(int n) { return 1u << 4 | static_cast<uint32_t>(n >> 3) << 17 | (128u >> 4) << 24; }
+
+// 4 uint8 -> 4 fp16 (exact): 0x6400 | v is 1024 + v as a half
+__device__ __forceinline__ uint2 u8x4_to_f16x4(uint32_t w)
+{
+    const uint32_t lo = __byte_perm(w, 0x64646464u, 0x4140), hi = __byte_perm(w, 0x64646464u, 0x4342);
+    const __half2 k = __halves2half2(__ushort_as_half(0x6400), __ushort_as_half(0x6400));
+    const __half2 a = __hsub2(*reinterpret_cast<const __half2 *>(&lo), k), b = __hsub2(*reinterpret_cast<const __half2 *>(&hi), k);
+    return make_uint2(*reinterpret_cast<const uint32_t *>(&a), *reinterpret_cast<const uint32_t *>(&b));
+}
+
+__global__ void __launch_bounds__(c1p::kCta, 1) conv1p_kernel(Args a)
+{
+    using namespace c1p;
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint8_t *s_w = smem;
+    uint8_t *s_stage = smem + kWBytes;
+    float *s_ex = reinterpret_cast<float *>(smem + kWBytes + kStages * kStageBytes);
+    __shared__ __align__(8) uint64_t s_wfull, s_full[kStages], s_empty[kStages], s_tfull[2], s_tempty[2];
+    __shared__ uint32_t s_tmem;
+    __shared__ float s_bias[8];
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int items = a.n * 2;
+    const int my_items = static_cast<int>(blockIdx.x) < items ? (items - 1 - static_cast<int>(blockIdx.x)) / static_cast<int>(gridDim.x) + 1 : 0;
+    if (tid == 0) {
+        mbar_init(&s_wfull, 1);
+        for (int i = 0; i < kStages; ++i) { mbar_init(&s_full[i], kProducers); mbar_init(&s_empty[i], 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&s_tfull[i], 1); mbar_init(&s_tempty[i], 128); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (tid < 8) s_bias[tid] = tid < 5 ? a.bias[tid] : 0.0f;
+    for (int i = tid; i < kStages * kStageBytes / 16; i += kCta) // rows 115..127 of every array are never written: keep them finite
+        reinterpret_cast<uint4 *>(s_stage)[i] = make_uint4(0, 0, 0, 0);
+    if (warp == kProducers / 32) tmem_alloc(&s_tmem, kTmemCols);
+    fence_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = s_tmem;
+
+    if (tid < kProducers) {
+        // ---------------------------------------------------------------- producers
+        // task g = stage f * 12 + (class c * 4 + quarter j); warp w takes the tasks g = w (mod 8); lane = il (23 of 32 lanes)
+        const int total = my_items * 9 * kTasksPerStage;
+        const bool active = lane < kRowsQ;
+        auto load = [&](int g, uint4 (&px)[2]) {
+            px[0] = px[1] = make_uint4(0, 0, 0, 0);
+            if (g >= total || !active) return;
+            const int f = g / kTasksPerStage, k = g - f * kTasksPerStage, c = k >> 2, j = k & 3;
+            const int il_item = f / 9, plane = f - il_item * 9;
+            const int item = static_cast<int>(blockIdx.x) + il_item * static_cast<int>(gridDim.x);
+            const int sample = item >> 1, i0 = (item & 1) ? 20 : 0;
+            const int row = 3 * (i0 + lane) + c;
+            if (row >= kDim) return; // below the image (half 1, il = 22, class 2): zeros
+            const int age = plane / 3, colour = plane - age * 3;
+            const uint8_t *src = stack_frame(a.frames, a.warm, a.meta, a.depth, static_cast<size_t>(a.n), a.head, static_cast<size_t>(sample), age) +
+                                 (colour * kDim + row) * kDim + j * 32;
+            px[0] = load_stream(src);
+            px[1] = load_stream(src + 16);
+        };
+        auto store = [&](int g, const uint4 (&px)[2]) {
+            const int f = g / kTasksPerStage, k = g - f * kTasksPerStage, c = k >> 2, j = k & 3;
+            const uint32_t st = static_cast<uint32_t>(f) % kStages;
+            if (f >= kStages) mbar_wait(&s_empty[st], ((static_cast<uint32_t>(f) / kStages) - 1u) & 1u);
+            if (active) {
+                uint8_t *base = s_stage + st * kStageBytes + c * kClassBytes + lane * 16;
+                const uint32_t w[8] = {px[0].x, px[0].y, px[0].z, px[0].w, px[1].x, px[1].y, px[1].z, px[1].w};
+#pragma unroll
+                for (int t = 0; t < 4; ++t) { // block b = 4 j + t: 8 pixels
+                    const uint2 lo = u8x4_to_f16x4(w[2 * t]), hi = u8x4_to_f16x4(w[2 * t + 1]);
+                    const uint4 v = make_uint4(lo.x, lo.y, hi.x, hi.y);
+                    const int b = 4 * j + t, arr = b % 3, q = b / 3;
+                    if (b <= 14) *reinterpret_cast<uint4 *>(base + arr * kAP + q * (kRowsQ * 16)) = v;
+                    if (arr == 0 && b >= 3) *reinterpret_cast<uint4 *>(base + 3 * kAP + (q - 1) * (kRowsQ * 16)) = v; // A3: blocks 3, 6, 9, 12, 15
+                }
+            }
+            // the warp's last task of stage f: publish the stage (every warp has one or two tasks in every stage)
+            if ((g + 8) / kTasksPerStage != f) {
+                fence_async_smem();
+                mbar_arrive(&s_full[st]);
+            }
+        };
+        // three tasks in flight per warp (3 x 1 KB x 8 warps per SM) beside the one being converted
+        uint4 r0[2], r1[2], r2[2], r3[2];
+        int g = warp;
+        load(g, r0); load(g + 8, r1); load(g + 16, r2);
+#pragma unroll 1
+        for (; g < total; g += 32) {
+            load(g + 24, r3); store(g, r0);
+            if (g + 8 < total) { load(g + 32, r0); store(g + 8, r1); }
+            if (g + 16 < total) { load(g + 40, r1); store(g + 16, r2); }
+            if (g + 24 < total) { load(g + 48, r2); store(g + 24, r3); }
+        }
+    } else if (warp == kProducers / 32) {
+        // ---------------------------------------------------------------- MMA issue (one thread)
+        if (lane == 0) {
+            mbar_expect_tx(&s_wfull, kWBytes);
+            for (int i = 0; i < 9; ++i) bulk_load(s_w + i * (kWBytes / 9), reinterpret_cast<const uint8_t *>(a.weights) + i * (kWBytes / 9), kWBytes / 9, &s_wfull);
+            mbar_wait(&s_wfull, 0);
+            constexpr uint32_t kIdesc = instr_desc_f16(kN);
+            const uint32_t w_base = smem_u32(s_w);
+            uint32_t fill = 0;
+            for (int t = 0; t < my_items; ++t) {
+                const uint32_t buf = t & 1u;
+                if (t >= 2) mbar_wait(&s_tempty[buf], ((t >> 1) - 1) & 1);
+                tc_fence_after();
+                for (int plane = 0; plane < 9; ++plane, ++fill) {
+                    const uint32_t st = fill % kStages;
+                    mbar_wait(&s_full[st], (fill / kStages) & 1);
+                    tc_fence_after();
+                    const uint32_t stage = smem_u32(s_stage + st * kStageBytes);
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) {
+#pragma unroll
+                        for (int ph = 0; ph < 3; ++ph) {
+                            const uint64_t ad = smem_desc(stage + c * kClassBytes + ph * kAP, kAP, 128);
+                            const uint64_t bd = smem_desc(w_base + ((plane * 3 + c) * 3 + ph) * kWBlock, (kN / 8) * 128, 128);
+                            umma_bf16(tmem + buf * kBufCols + ph * kN, ad, bd, kIdesc, (plane | c) != 0);
+                        }
+                    }
+                    umma_commit(&s_empty[st]);
+                }
+                umma_commit(&s_tfull[buf]);
+            }
+        }
+    } else {
+        // ---------------------------------------------------------------- epilogue: 4 warps, thread = TMEM lane = M row 23 q + il
+        const int q4 = warp & 3;
+        const int m = q4 * 32 + lane;
+        const int q = m / kRowsQ, il = m - q * kRowsQ;
+        const bool row_ok = m < kRowsUsed;
+        for (int t = 0; t < my_items; ++t) {
+            const int item = static_cast<int>(blockIdx.x) + t * static_cast<int>(gridDim.x);
+            const int sample = item >> 1, y0 = (item & 1) ? 20 : 0, ny = (item & 1) ? 21 : 20;
+            const uint32_t buf = t & 1u;
+            mbar_wait(&s_tfull[buf], (t >> 1) & 1);
+            tc_fence_after();
+#pragma unroll 1
+            for (int ph = 0; ph < 3; ++ph) {
+                const uint32_t taddr = tmem + buf * kBufCols + ph * kN + (static_cast<uint32_t>(q4 * 32) << 16);
+                uint32_t v0[16], v1[16], v2[16]; // kernel-row groups kv = 0, 1, 2: [3 outputs x 5 channels]
+                tmem_load16_async(taddr, v0);
+                tmem_load16_async(taddr + 16, v1);
+                tmem_load16_async(taddr + 32, v2);
+                tmem_wait_ld();
+                if (ph == 2) { // the item's accumulators are all in registers: the MMA warp may overwrite them
+                    tc_fence_before();
+                    mbar_arrive(&s_tempty[buf]);
+                }
+                // kernel-row group kv of input-row index il belongs to output row il - kv
+                if (row_ok && il >= 1 && il - 1 < ny) {
+                    float4 *dst = reinterpret_cast<float4 *>(s_ex + ((0 * kRowsQ + (il - 1)) * kQ + q) * 16);
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) dst[e] = make_float4(__uint_as_float(v1[4 * e]), __uint_as_float(v1[4 * e + 1]), __uint_as_float(v1[4 * e + 2]), __uint_as_float(v1[4 * e + 3]));
+                }
+                if (row_ok && il >= 2 && il - 2 < ny) {
+                    float4 *dst = reinterpret_cast<float4 *>(s_ex + ((1 * kRowsQ + (il - 2)) * kQ + q) * 16);
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) dst[e] = make_float4(__uint_as_float(v2[4 * e]), __uint_as_float(v2[4 * e + 1]), __uint_as_float(v2[4 * e + 2]), __uint_as_float(v2[4 * e + 3]));
+                }
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+                if (row_ok && il < ny) {
+                    const float4 *p1 = reinterpret_cast<const float4 *>(s_ex + ((0 * kRowsQ + il) * kQ + q) * 16);
+                    const float4 *p2 = reinterpret_cast<const float4 *>(s_ex + ((1 * kRowsQ + il) * kQ + q) * 16);
+                    float sum[16];
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const float4 u = p1[e], w = p2[e];
+                        sum[4 * e] = __uint_as_float(v0[4 * e]) + u.x + w.x;
+                        sum[4 * e + 1] = __uint_as_float(v0[4 * e + 1]) + u.y + w.y;
+                        sum[4 * e + 2] = __uint_as_float(v0[4 * e + 2]) + u.z + w.z;
+                        sum[4 * e + 3] = __uint_as_float(v0[4 * e + 3]) + u.w + w.w;
+                    }
+                    const int y = y0 + il, x0 = 8 * q + 3 * ph;
+                    uint4 *out = reinterpret_cast<uint4 *>(a.out + (static_cast<size_t>(sample) * kP1 + y * kC1 + x0) * kAct1C);
+#pragma unroll
+                    for (int j = 0; j < 3; ++j) {
+                        if (j < 2 || ph < 2 || q == kQ - 1) { // phase 2's third output is the next block's first, except x = 40
+                            float c[5];
+#pragma unroll
+                            for (int ch = 0; ch < 5; ++ch) c[ch] = fmaxf(sum[j * 5 + ch] * (1.0f / 128.0f) + s_bias[ch], 0.0f); // (x - 128) / 128: processor.py:39-42
+                            const __nv_bfloat162 p01 = __floats2bfloat162_rn(c[0], c[1]), p23 = __floats2bfloat162_rn(c[2], c[3]), p4 = __floats2bfloat162_rn(c[4], 0.0f);
+                            out[j] = make_uint4(*reinterpret_cast<const uint32_t *>(&p01), *reinterpret_cast<const uint32_t *>(&p23), *reinterpret_cast<const uint32_t *>(&p4), 0u);
+                        }
+                    }
+                }
+                asm volatile("bar.sync 1, 128;" ::: "memory"); // the exchange buffer is free for the next phase
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == kProducers / 32) tmem_dealloc(tmem, kTmemCols);
+}
+
+cudaError_t launch_conv1p(const Args &a, int grid, cudaStream_t s)
+{
+    static bool prepared = false;
+    if (!prepared) {
+        cudaError_t e = cudaFuncSetAttribute(conv1p_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, c1p::kSmem);
+        if (e != cudaSuccess) return e;
+        prepared = true;
+    }
+    conv1p_kernel<<<grid, c1p::kCta, c1p::kSmem, s>>>(a);
+    return cudaGetLastError();
+}
+
 // ------------------------------------------------------------------------------------------------ conv2 / conv3, pipelined
 // The same GEMM tiles as layer_kernel, as a persistent warp-specialised pipeline (the layer_kernel form of these two
 // layers sat at 5-6 % tensor-pipe activity: every chunk was gathered, stored, barriered and multiplied in sequence):
@@ -1016,6 +1264,27 @@ __global__ void __launch_bounds__(256) pack_conv1_kernel(DevWeights w, uint16_t 
     out[at] = dev_bf16(__fdiv_rn(w.f[0][((ky * 8 + kx) * 9 + plane) * 5 + ch], 128.0f));
 }
 
+// conv1, phase-separated form (conv1p_kernel): 81 blocks (plane, class, phase) of [K = 16][N = 48] fp16, unscaled weights
+__global__ void __launch_bounds__(256) pack_conv1p_kernel(DevWeights w, uint16_t *__restrict__ out)
+{
+    constexpr int N = 48;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= 9 * 3 * 3 * 3 * 3 * 5 * 8) return;
+    int r = idx;
+    const int kx = r % 8; r /= 8;
+    const int ch = r % 5; r /= 5;
+    const int j = r % 3; r /= 3;
+    const int ph = r % 3; r /= 3;
+    const int kv = r % 3; r /= 3;
+    const int cls = r % 3; r /= 3;
+    const int plane = r;
+    const int ky = cls + 3 * kv;
+    const int k = kx + ph + 3 * j, n = kv * 16 + j * 5 + ch;
+    if (ky >= 8) return;
+    const size_t at = static_cast<size_t>((plane * 3 + cls) * 3 + ph) * (16 * N) + (k / 8) * (8 * N) + (n / 8) * 64 + (n % 8) * 8 + (k % 8);
+    out[at] = __half_as_ushort(__float2half_rn(w.f[0][((ky * 8 + kx) * 9 + plane) * 5 + ch]));
+}
+
 // ------------------------------------------------------------------------------------------------ host: fold + pack
 uint16_t to_bf16(float f)
 { // round to nearest even
@@ -1071,6 +1340,30 @@ std::vector<uint16_t> pack_conv1_toeplitz(const std::vector<float> &wf)
     return out;
 }
 
+// conv1, phase-separated form: W [576][5] UNSCALED (k = plane*64 + ky*8 + kx) -> 81 blocks (plane, class, phase) of the
+// K-major canonical B operand [K = 16][N = 48] in fp16: n = kv*16 + j*5 + channel holds
+// W[plane][ky = class + 3 kv][kx = k - (phase + 3 j)][channel] (0 outside the 8 taps and for ky = 8)
+std::vector<uint16_t> pack_conv1_phase(const std::vector<float> &wf)
+{
+    constexpr int N = 48;
+    std::vector<uint16_t> out(static_cast<size_t>(81) * 16 * N, 0);
+    for (int plane = 0; plane < 9; ++plane)
+        for (int cls = 0; cls < 3; ++cls)
+            for (int ph = 0; ph < 3; ++ph)
+                for (int kv = 0; kv < 3; ++kv) {
+                    const int ky = cls + 3 * kv;
+                    if (ky >= 8) continue;
+                    for (int j = 0; j < 3; ++j)
+                        for (int ch = 0; ch < 5; ++ch)
+                            for (int kx = 0; kx < 8; ++kx) {
+                                const int k = kx + ph + 3 * j, n = kv * 16 + j * 5 + ch;
+                                const size_t at = static_cast<size_t>((plane * 3 + cls) * 3 + ph) * (16 * N) + (k / 8) * (8 * N) + (n / 8) * 64 + (n % 8) * 8 + (k % 8);
+                                out[at] = __half_as_ushort(__float2half_rn(wf[(static_cast<size_t>(plane * 8 + ky) * 8 + kx) * 5 + ch]));
+                            }
+                }
+    return out;
+}
+
 } // namespace policy
 } // namespace ahk
 
@@ -1081,7 +1374,9 @@ struct ahk_policy {
     int device = 0, max_batch = 0;
     uint16_t *w[6] = {};
     float *b[6] = {};
-    uint16_t *w1t = nullptr; // conv1 in Toeplitz form (conv1_kernel)
+    uint16_t *w1t = nullptr; // conv1 in Toeplitz form (conv1_kernel, A/B switch AHK_CONV1=n144)
+    uint16_t *w1p = nullptr; // conv1 in phase-separated form (conv1p_kernel, the default), fp16, unscaled
+    bool conv1_n144 = false;
     cudaEvent_t ev[7] = {};  // ahk_policy_forward_profiled: around each of the six layer kernels
     // the 'gray-diff' network (ahk_policy_gray_create): weights/biases of its six layers, input image and activations
     bool gray = false;
@@ -1142,17 +1437,23 @@ static int load_rgb_weights(ahk_policy *p, const ahk_policy_weights *w)
     int rc = AHK_OK;
 
     { // conv1: Keras kernel [ky][kx][c][o]; GEMM k = c*64 + ky*8 + kx; (x-128)/128 folded: W/128, b - sum(W)
-        std::vector<float> wf(576 * 5), bf(16, 0.0f);
+        std::vector<float> wf(576 * 5), wraw(576 * 5), bf(16, 0.0f);
         for (int o = 0; o < 5; ++o) {
             double sum = 0.0;
             for (int ky = 0; ky < 8; ++ky) for (int kx = 0; kx < 8; ++kx) for (int c = 0; c < 9; ++c) {
                 const float v = w->conv1_w[((ky * 8 + kx) * 9 + c) * 5 + o];
                 wf[(c * 64 + ky * 8 + kx) * 5 + o] = v / 128.0f;
+                wraw[(c * 64 + ky * 8 + kx) * 5 + o] = v;
                 sum += v;
             }
             bf[o] = w->conv1_b[o] - static_cast<float>(sum);
         }
         rc = upload(pack_conv1_toeplitz(wf), bf, &p->w1t, &p->b[0]);
+        if (rc == AHK_OK) { // the phase-separated form: fp16, unscaled (the 1/128 is applied to the accumulator)
+            const std::vector<uint16_t> wp = pack_conv1_phase(wraw);
+            if (!p->w1p) POL_CUDA(cudaMalloc(&p->w1p, wp.size() * 2));
+            POL_CUDA(cudaMemcpy(p->w1p, wp.data(), wp.size() * 2, cudaMemcpyHostToDevice));
+        }
     }
     if (rc == AHK_OK) { // conv2: k = (ky*4+kx)*8 + c, BN1 folded
         std::vector<float> wf(128 * 32, 0.0f), bf(32);
@@ -1217,6 +1518,7 @@ int ahk_policy_create(int device, int max_batch, const ahk_policy_weights *w, ah
     p->max_batch = max_batch;
     cudaDeviceGetAttribute(&p->sms, cudaDevAttrMultiProcessorCount, device);
     if (const char *sw = getenv("AHK_CONV23")) p->legacy_conv = strcmp(sw, "tile") == 0;
+    if (const char *sw = getenv("AHK_CONV1")) p->conv1_n144 = strcmp(sw, "n144") == 0;
     int rc = load_rgb_weights(p, w);
     const size_t nb = static_cast<size_t>(max_batch);
     cudaError_t err = cudaSuccess;
@@ -1262,6 +1564,8 @@ int ahk_policy_set_weights_dev(ahk_policy *p, const ahk_policy_weights *w_dev, v
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     POL_CUDA(cudaMemsetAsync(p->w1t, 0, static_cast<size_t>(27) * 16 * 144 * 2, s)); // the Toeplitz bands leave zeros between them
     pack_conv1_kernel<<<(9 * 3 * 3 * 3 * 3 * 5 * 8 + 255) / 256, 256, 0, s>>>(w, p->w1t);
+    POL_CUDA(cudaMemsetAsync(p->w1p, 0, static_cast<size_t>(c1p::kWBytes), s));
+    pack_conv1p_kernel<<<(9 * 3 * 3 * 3 * 3 * 5 * 8 + 255) / 256, 256, 0, s>>>(w, p->w1p);
     pack_b_kernel<1><<<16, 256, 0, s>>>(w, p->w[1], 128, 32, 1);
     pack_b_kernel<2><<<128, 256, 0, s>>>(w, p->w[2], 512, 64, 1);
     pack_b_kernel<3><<<p->sms * 8, 256, 0, s>>>(w, p->w[3], 4096, 256, 2);
@@ -1366,6 +1670,7 @@ void ahk_policy_destroy(ahk_policy *p)
     cudaSetDevice(p->device);
     for (int i = 0; i < 6; ++i) { if (p->w[i]) cudaFree(p->w[i]); if (p->b[i]) cudaFree(p->b[i]); }
     if (p->w1t) cudaFree(p->w1t);
+    if (p->w1p) cudaFree(p->w1p);
     for (int i = 0; i < 7; ++i) if (p->ev[i]) cudaEventDestroy(p->ev[i]);
     for (int i = 0; i < 6; ++i) { if (p->gw[i]) cudaFree(p->gw[i]); if (p->gb[i]) cudaFree(p->gb[i]); }
     cudaFree(p->gimg); cudaFree(p->ga1); cudaFree(p->ga2); cudaFree(p->ga3); cudaFree(p->ga4); cudaFree(p->gh1);
@@ -1422,10 +1727,15 @@ static int policy_forward(ahk_policy *p, const ahk_stack &stack, float *logits, 
     }
     if (timed) POL_CUDA(cudaEventRecord(p->ev[0], s));
 
-    a.frames = frames; a.weights = reinterpret_cast<const uint4 *>(p->w1t); a.bias = p->b[0]; a.out = p->act1; a.m_total = kP1;
-    {
+    a.frames = frames; a.bias = p->b[0]; a.out = p->act1; a.m_total = kP1;
+    if (p->conv1_n144) {
+        a.weights = reinterpret_cast<const uint4 *>(p->w1t);
         const int items = n * c1::kTilesPerSample;
         POL_CUDA(launch_conv1(a, items < p->sms ? items : p->sms, s));
+    } else {
+        a.weights = reinterpret_cast<const uint4 *>(p->w1p);
+        const int items = n * 2;
+        POL_CUDA(launch_conv1p(a, items < p->sms ? items : p->sms, s));
     }
     if (timed) POL_CUDA(cudaEventRecord(p->ev[1], s));
     a.in = p->act1; a.weights = reinterpret_cast<const uint4 *>(p->w[1]); a.bias = p->b[1]; a.out = p->act2; a.m_total = n * kP2;

@@ -20,6 +20,8 @@
 #include "../../include/ahk.h"
 #include "ahk_kernels.cuh"
 
+#include <cuda.h>
+#include <cudaTypedefs.h>
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 
@@ -702,17 +704,19 @@ cudaError_t launch_conv1(const Args &a, int grid, cudaStream_t s)
 // Roles as before: 8 producer warps (global uint8 -> registers -> fp16 -> shared, three tasks of 1 KB in flight per
 // warp), 1 MMA warp, 4 epilogue warps (kernel-row groups summed across rows through a 14 KB exchange).
 namespace c1p {
-constexpr int kProducers = 256, kCta = kProducers + 32 + 128;
-constexpr int kStages = 3;
+constexpr int kConverters = 256, kMmaWarp = kConverters / 32, kLoadWarp = kMmaWarp + 1, kCta = kConverters + 64 + 128;
+constexpr int kStages = 2;                                      // converted A stages (MMA of plane f overlaps conversion of f + 1)
+constexpr int kRaw = 4;                                         // raw uint8 stages in flight: 4 x 8.6 KB per SM keeps HBM busy
 constexpr int kRowsQ = 23, kQ = 5, kRowsUsed = kRowsQ * kQ;     // 115 M rows per phase
 constexpr int kAP = 128 * 16;                                   // array pitch = LBO: 128 rows of 16 bytes
 constexpr int kClassBytes = 4 * kAP, kStageBytes = 3 * kClassBytes; // 24 576 B: one colour plane of one half sample
+constexpr int kRawRows = 3 * kRowsQ;                             // 69 image rows of one colour plane: ONE tiled TMA copy per stage
+constexpr int kRawBytes = 9 * 1024;                             // 8 832 B of pixels, 128-byte swizzle: stages are 1024-byte aligned
 constexpr int kN = 48;
 constexpr int kWBlock = 16 * kN * 2;                            // one (plane, class, phase) B operand
 constexpr int kWBlocks = 9 * 3 * 3, kWBytes = kWBlocks * kWBlock; // 124 416 B, resident
 constexpr int kExBytes = 2 * kRowsQ * kQ * 16 * 4;              // exchange of the kv = 1, 2 partial sums
-constexpr int kSmem = kWBytes + kStages * kStageBytes + kExBytes; // 212 864 B
-constexpr int kTasksPerStage = 12;                              // (class, 32-pixel quarter of the row)
+constexpr int kSmem = 1024 + kRaw * kRawBytes + kWBytes + kStages * kStageBytes + kExBytes; // 226 176 B (1 KB of alignment slack)
 constexpr int kTmemCols = 512, kBufCols = 256;
 } // namespace c1p
 
@@ -728,14 +732,15 @@ __device__ __forceinline__ uint2 u8x4_to_f16x4(uint32_t w)
     return make_uint2(*reinterpret_cast<const uint32_t *>(&a), *reinterpret_cast<const uint32_t *>(&b));
 }
 
-__global__ void __launch_bounds__(c1p::kCta, 1) conv1p_kernel(Args a)
+__global__ void __launch_bounds__(c1p::kCta, 1) conv1p_kernel(Args a, const __grid_constant__ CUtensorMap tm_ring, const __grid_constant__ CUtensorMap tm_warm)
 {
     using namespace c1p;
-    extern __shared__ __align__(128) uint8_t smem[];
-    uint8_t *s_w = smem;
-    uint8_t *s_stage = smem + kWBytes;
-    float *s_ex = reinterpret_cast<float *>(smem + kWBytes + kStages * kStageBytes);
-    __shared__ __align__(8) uint64_t s_wfull, s_full[kStages], s_empty[kStages], s_tfull[2], s_tempty[2];
+    extern __shared__ __align__(128) uint8_t smem_unaligned[];
+    uint8_t *s_raw = smem_unaligned + ((1024u - (smem_u32(smem_unaligned) & 1023u)) & 1023u); // swizzle atoms are 1024-byte aligned
+    uint8_t *s_w = s_raw + kRaw * kRawBytes;
+    uint8_t *s_stage = s_w + kWBytes;
+    float *s_ex = reinterpret_cast<float *>(s_stage + kStages * kStageBytes);
+    __shared__ __align__(8) uint64_t s_wfull, s_rfull[kRaw], s_rempty[kRaw], s_full[kStages], s_empty[kStages], s_tfull[2], s_tempty[2];
     __shared__ uint32_t s_tmem;
     __shared__ float s_bias[8];
 
@@ -744,74 +749,104 @@ __global__ void __launch_bounds__(c1p::kCta, 1) conv1p_kernel(Args a)
     const int my_items = static_cast<int>(blockIdx.x) < items ? (items - 1 - static_cast<int>(blockIdx.x)) / static_cast<int>(gridDim.x) + 1 : 0;
     if (tid == 0) {
         mbar_init(&s_wfull, 1);
-        for (int i = 0; i < kStages; ++i) { mbar_init(&s_full[i], kProducers); mbar_init(&s_empty[i], 1); }
+        for (int i = 0; i < kRaw; ++i) { mbar_init(&s_rfull[i], 1); mbar_init(&s_rempty[i], kConverters / 32); }
+        for (int i = 0; i < kStages; ++i) { mbar_init(&s_full[i], kConverters / 32); mbar_init(&s_empty[i], 1); }
         for (int i = 0; i < 2; ++i) { mbar_init(&s_tfull[i], 1); mbar_init(&s_tempty[i], 128); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (tid < 8) s_bias[tid] = tid < 5 ? a.bias[tid] : 0.0f;
     for (int i = tid; i < kStages * kStageBytes / 16; i += kCta) // rows 115..127 of every array are never written: keep them finite
         reinterpret_cast<uint4 *>(s_stage)[i] = make_uint4(0, 0, 0, 0);
-    if (warp == kProducers / 32) tmem_alloc(&s_tmem, kTmemCols);
+    if (warp == kMmaWarp) tmem_alloc(&s_tmem, kTmemCols);
     fence_async_smem();
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = s_tmem;
 
-    if (tid < kProducers) {
-        // ---------------------------------------------------------------- producers
-        // task g = stage f * 12 + (class c * 4 + quarter j); warp w takes the tasks g = w (mod 8); lane = il (23 of 32 lanes)
-        const int total = my_items * 9 * kTasksPerStage;
-        const bool active = lane < kRowsQ;
-        auto load = [&](int g, uint4 (&px)[2]) {
-            px[0] = px[1] = make_uint4(0, 0, 0, 0);
-            if (g >= total || !active) return;
-            const int f = g / kTasksPerStage, k = g - f * kTasksPerStage, c = k >> 2, j = k & 3;
-            const int il_item = f / 9, plane = f - il_item * 9;
-            const int item = static_cast<int>(blockIdx.x) + il_item * static_cast<int>(gridDim.x);
-            const int sample = item >> 1, i0 = (item & 1) ? 20 : 0;
-            const int row = 3 * (i0 + lane) + c;
-            if (row >= kDim) return; // below the image (half 1, il = 22, class 2): zeros
-            const int age = plane / 3, colour = plane - age * 3;
-            const uint8_t *src = stack_frame(a.frames, a.warm, a.meta, a.depth, static_cast<size_t>(a.n), a.head, static_cast<size_t>(sample), age) +
-                                 (colour * kDim + row) * kDim + j * 32;
-            px[0] = load_stream(src);
-            px[1] = load_stream(src + 16);
-        };
-        auto store = [&](int g, const uint4 (&px)[2]) {
-            const int f = g / kTasksPerStage, k = g - f * kTasksPerStage, c = k >> 2, j = k & 3;
-            const uint32_t st = static_cast<uint32_t>(f) % kStages;
-            if (f >= kStages) mbar_wait(&s_empty[st], ((static_cast<uint32_t>(f) / kStages) - 1u) & 1u);
-            if (active) {
-                uint8_t *base = s_stage + st * kStageBytes + c * kClassBytes + lane * 16;
-                const uint32_t w[8] = {px[0].x, px[0].y, px[0].z, px[0].w, px[1].x, px[1].y, px[1].z, px[1].w};
+    if (warp == kLoadWarp) {
+        // ---------------------------------------------------------------- loader: one tiled TMA copy per stage
+        // Stage f = (item, plane): the 69 image rows 3 i0 .. 3 i0 + 68 of one colour plane (128 x 69 bytes, 128-byte swizzle:
+        // the 16-byte chunk k of row r lands at chunk k ^ (r & 7), so that lanes = every third row read conflict-free).
+        // The ring and the warm-up side buffer are two tensor maps over [frame][colour][row] x 128 bytes; the frame indices
+        // of the NEXT item (a dependent load of the episode word when the ring is deep) are fetched while this item's
+        // nine planes are issued.  Row 128 of the last band (half 1) is the next plane's first row or out of bounds
+        // (zero fill): the converters never use it.
+        if (lane == 0) {
+            auto frame_rows = [&](int t, int (&p)[3]) { // row index of (frame, colour 0, row 0); bit 31: warm-up buffer
+                const int sample = (static_cast<int>(blockIdx.x) + t * static_cast<int>(gridDim.x)) >> 1;
+                const int steps = a.warm != nullptr ? static_cast<int>(a.meta[sample] & 0xFFFFu) : 0x7FFFFFFF;
 #pragma unroll
-                for (int t = 0; t < 4; ++t) { // block b = 4 j + t: 8 pixels
-                    const uint2 lo = u8x4_to_f16x4(w[2 * t]), hi = u8x4_to_f16x4(w[2 * t + 1]);
-                    const uint4 v = make_uint4(lo.x, lo.y, hi.x, hi.y);
-                    const int b = 4 * j + t, arr = b % 3, q = b / 3;
-                    if (b <= 14) *reinterpret_cast<uint4 *>(base + arr * kAP + q * (kRowsQ * 16)) = v;
-                    if (arr == 0 && b >= 3) *reinterpret_cast<uint4 *>(base + 3 * kAP + (q - 1) * (kRowsQ * 16)) = v; // A3: blocks 3, 6, 9, 12, 15
+                for (int age = 0; age < 3; ++age)
+                    p[age] = age >= steps ? static_cast<int>((static_cast<uint32_t>(2 - (age - steps)) * a.n + sample) * (3u * kDim) | 0x80000000u)
+                                          : ((a.head + a.depth - age) % a.depth * a.n + sample) * (3 * kDim);
+            };
+            int cur[3] = {0, 0, 0}, nxt[3] = {0, 0, 0};
+            if (my_items > 0) frame_rows(0, cur);
+            uint32_t fill = 0;
+            for (int t = 0; t < my_items; ++t) {
+                if (t + 1 < my_items) frame_rows(t + 1, nxt);
+                const int item = static_cast<int>(blockIdx.x) + t * static_cast<int>(gridDim.x);
+                const int row0 = (item & 1) ? 60 : 0;
+#pragma unroll
+                for (int plane = 0; plane < 9; ++plane, ++fill) {
+                    const uint32_t r = fill % kRaw;
+                    if (fill >= kRaw) mbar_wait(&s_rempty[r], ((fill / kRaw) - 1u) & 1u);
+                    mbar_expect_tx(&s_rfull[r], kRawRows * kDim);
+                    const int f = cur[plane / 3];
+                    const int row = (f & 0x7FFFFFFF) + (plane % 3) * kDim + row0;
+                    const CUtensorMap *tm = f < 0 ? &tm_warm : &tm_ring;
+                    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                                 :: "r"(smem_u32(s_raw + r * kRawBytes)), "l"(reinterpret_cast<uint64_t>(tm)), "r"(0), "r"(row), "r"(smem_u32(&s_rfull[r])) : "memory");
                 }
+#pragma unroll
+                for (int age = 0; age < 3; ++age) cur[age] = nxt[age];
             }
-            // the warp's last task of stage f: publish the stage (every warp has one or two tasks in every stage)
-            if ((g + 8) / kTasksPerStage != f) {
-                fence_async_smem();
-                mbar_arrive(&s_full[st]);
-            }
-        };
-        // three tasks in flight per warp (3 x 1 KB x 8 warps per SM) beside the one being converted
-        uint4 r0[2], r1[2], r2[2], r3[2];
-        int g = warp;
-        load(g, r0); load(g + 8, r1); load(g + 16, r2);
-#pragma unroll 1
-        for (; g < total; g += 32) {
-            load(g + 24, r3); store(g, r0);
-            if (g + 8 < total) { load(g + 32, r0); store(g + 8, r1); }
-            if (g + 16 < total) { load(g + 40, r1); store(g + 16, r2); }
-            if (g + 24 < total) { load(g + 48, r2); store(g + 24, r3); }
         }
-    } else if (warp == kProducers / 32) {
+    } else if (warp < kMmaWarp) {
+        // ---------------------------------------------------------------- converters: uint8 rows -> the fp16 phase arrays
+        // warp w owns the 16-pixel chunk w of every row (8-pixel blocks 2 w and 2 w + 1); lane = input-row index il, whose
+        // three rows 3 il + c are the row classes c
+        const bool active = lane < kRowsQ;
+        uint32_t src[3];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) src[c] = (3 * lane + c) * kDim + ((warp ^ ((3 * lane + c) & 7)) << 4);
+        uint32_t fill = 0;
+        for (int t = 0; t < my_items; ++t) {
+            const int item = static_cast<int>(blockIdx.x) + t * static_cast<int>(gridDim.x);
+            const bool short_row = (item & 1) && lane == kRowsQ - 1; // class 2 of il = 22 is image row 128: zeros
+#pragma unroll 1
+            for (int plane = 0; plane < 9; ++plane, ++fill) {
+                const uint32_t r = fill % kRaw, st = fill % kStages;
+                mbar_wait(&s_rfull[r], (fill / kRaw) & 1u);
+                uint4 px[3];
+#pragma unroll
+                for (int c = 0; c < 3; ++c) px[c] = active ? *reinterpret_cast<const uint4 *>(s_raw + r * kRawBytes + src[c]) : make_uint4(0, 0, 0, 0);
+                if (short_row) px[2] = make_uint4(0, 0, 0, 0);
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&s_rempty[r]);
+                if (fill >= kStages) mbar_wait(&s_empty[st], ((fill / kStages) - 1u) & 1u);
+                if (active) {
+                    uint8_t *base = s_stage + st * kStageBytes + lane * 16;
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) {
+                        const uint32_t w[4] = {px[c].x, px[c].y, px[c].z, px[c].w};
+#pragma unroll
+                        for (int h = 0; h < 2; ++h) {
+                            const uint2 lo = u8x4_to_f16x4(w[2 * h]), hi = u8x4_to_f16x4(w[2 * h + 1]);
+                            const uint4 v = make_uint4(lo.x, lo.y, hi.x, hi.y);
+                            const int b = 2 * warp + h, arr = b % 3, q = b / 3;
+                            if (b <= 14) *reinterpret_cast<uint4 *>(base + c * kClassBytes + arr * kAP + q * (kRowsQ * 16)) = v;
+                            if (arr == 0 && b >= 3) *reinterpret_cast<uint4 *>(base + c * kClassBytes + 3 * kAP + (q - 1) * (kRowsQ * 16)) = v; // A3: blocks 3, 6, 9, 12, 15
+                        }
+                    }
+                }
+                fence_async_smem();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&s_full[st]);
+            }
+        }
+    } else if (warp == kMmaWarp) {
         // ---------------------------------------------------------------- MMA issue (one thread)
         if (lane == 0) {
             mbar_expect_tx(&s_wfull, kWBytes);
@@ -910,18 +945,45 @@ __global__ void __launch_bounds__(c1p::kCta, 1) conv1p_kernel(Args a)
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == kProducers / 32) tmem_dealloc(tmem, kTmemCols);
+    if (warp == kMmaWarp) tmem_dealloc(tmem, kTmemCols);
+}
+
+// [frame][colour][row] x 128 bytes as a 2-D uint8 tensor, box = 69 rows, 128-byte swizzle
+static cudaError_t frame_tensor_map(CUtensorMap *tm, const uint8_t *base, size_t frames)
+{
+    static PFN_cuTensorMapEncodeTiled_v12000 encode = nullptr;
+    if (encode == nullptr) {
+        cudaDriverEntryPointQueryResult q;
+        void *fn = nullptr;
+        cudaError_t e = cudaGetDriverEntryPointByVersion("cuTensorMapEncodeTiled", &fn, 12000, cudaEnableDefault, &q);
+        if (e != cudaSuccess) return e;
+        if (q != cudaDriverEntryPointSuccess || fn == nullptr) return cudaErrorNotSupported;
+        encode = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(fn);
+    }
+    const cuuint64_t dims[2] = {static_cast<cuuint64_t>(kDim), static_cast<cuuint64_t>(frames) * 3 * kDim};
+    const cuuint64_t strides[1] = {static_cast<cuuint64_t>(kDim)};
+    const cuuint32_t box[2] = {static_cast<cuuint32_t>(kDim), static_cast<cuuint32_t>(c1p::kRawRows)};
+    const cuuint32_t estr[2] = {1, 1};
+    if (dims[1] >= (1ull << 31)) return cudaErrorInvalidValue;
+    const CUresult r = encode(tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<uint8_t *>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? cudaSuccess : cudaErrorInvalidValue;
 }
 
 cudaError_t launch_conv1p(const Args &a, int grid, cudaStream_t s)
 {
-    static bool prepared = false;
-    if (!prepared) {
-        cudaError_t e = cudaFuncSetAttribute(conv1p_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, c1p::kSmem);
-        if (e != cudaSuccess) return e;
-        prepared = true;
+    cudaError_t e = cudaFuncSetAttribute(conv1p_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, c1p::kSmem); // per device
+    if (e != cudaSuccess) return e;
+    // the maps are a pure function of (pointer, frame count): keep the last pair per calling thread
+    struct Cached { const uint8_t *frames = nullptr, *warm = nullptr; int n = 0, depth = 0; CUtensorMap ring, side; };
+    static thread_local Cached c;
+    if (c.frames != a.frames || c.warm != a.warm || c.n != a.n || c.depth != a.depth) {
+        if ((e = frame_tensor_map(&c.ring, a.frames, static_cast<size_t>(a.depth) * a.n)) != cudaSuccess) return e;
+        if (a.warm != nullptr) { if ((e = frame_tensor_map(&c.side, a.warm, static_cast<size_t>(3) * a.n)) != cudaSuccess) return e; }
+        else c.side = c.ring;
+        c.frames = a.frames; c.warm = a.warm; c.n = a.n; c.depth = a.depth;
     }
-    conv1p_kernel<<<grid, c1p::kCta, c1p::kSmem, s>>>(a);
+    conv1p_kernel<<<grid, c1p::kCta, c1p::kSmem, s>>>(a, c.ring, c.side);
     return cudaGetLastError();
 }
 

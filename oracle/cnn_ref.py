@@ -6,8 +6,10 @@ epsilon 1e-3, inference mode, comes AFTER the ReLU), Flatten in (C, H, W) order,
 Keras itself is not installed on either box, so parity for the network is pinned to this restatement
 plus the layer shapes that follow from models.py: (5,41,41) -> (32,19,19) -> (64,8,8) -> 4096.
 
-`forward(..., emulate_bf16=True)` rounds the operands to bfloat16 at exactly the points where the tcgen05 kernels do
-(weights after folding; activations after each ReLU), so the CUDA result can be checked tightly, while
+`forward(..., emulate_bf16=True)` rounds the operands at exactly the points where the tcgen05 kernels do (weights after
+folding, activations after each ReLU: bfloat16 everywhere except conv1, whose default kernel multiplies the exact uint8
+pixels with UNSCALED float16 weights and applies 1/128 and the folded bias to the float32 sum; `conv1='bf16'` is the
+older kernel kept behind AHK_CONV1=n144: bfloat16 weights / 128), so the CUDA result can be checked tightly, while
 `emulate_bf16=False` is the float32 model the stated tolerance refers to.
 """
 import numpy as np
@@ -21,7 +23,7 @@ def _t(a):
     return torch.from_numpy(np.ascontiguousarray(a, dtype=np.float32)).double()
 
 
-def forward(w, obs_u8, emulate_bf16=False):
+def forward(w, obs_u8, emulate_bf16=False, conv1=None):
     """w: dict of Keras-layout float32 arrays (gym_air_hockey_b200.policy.SHAPES); obs_u8: uint8 [n, 9, 128, 128]
     stacked newest-first (processor.py:47-49).  Returns float32 logits [n, 10] (pre-softmax)."""
     x = torch.from_numpy(np.ascontiguousarray(obs_u8)).double()
@@ -64,7 +66,13 @@ def forward(w, obs_u8, emulate_bf16=False):
     def conv(v, k, b, stride):
         kk = q(_t(k.transpose(3, 2, 0, 1)))
         return q(F.relu(F.conv2d(v, kk, _t(b), stride=stride).float().double()))
-    x = conv(x, k1, b1, 3)
+    import os
+    if (conv1 or ('bf16' if os.environ.get('AHK_CONV1') == 'n144' else 'fp16')) == 'fp16':
+        kk = _t(w['conv1_w'].astype(np.float16).astype(np.float32).transpose(3, 2, 0, 1))
+        acc = F.conv2d(x, kk, None, stride=3).float()  # exact products, float32 accumulator
+        x = q(F.relu(acc * np.float32(1.0 / 128.0) + torch.from_numpy(b1).view(1, -1, 1, 1)).double())
+    else:
+        x = conv(x, k1, b1, 3)
     x = conv(x, k2, b2, 2)
     x = conv(x, k3, b3, 2)
     x = x.reshape(x.shape[0], -1)

@@ -970,20 +970,321 @@ static cudaError_t frame_tensor_map(CUtensorMap *tm, const uint8_t *base, size_t
     return r == CUDA_SUCCESS ? cudaSuccess : cudaErrorInvalidValue;
 }
 
-cudaError_t launch_conv1p(const Args &a, int grid, cudaStream_t s)
+// the tensor maps of conv1p_kernel / conv1t_kernel are a pure function of (pointer, frame count): keep the last pair per calling thread
+struct FrameMaps { const uint8_t *frames = nullptr, *warm = nullptr; int n = 0, depth = 0; CUtensorMap ring, side; };
+static cudaError_t frame_maps(const Args &a, const FrameMaps **out)
 {
-    cudaError_t e = cudaFuncSetAttribute(conv1p_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, c1p::kSmem); // per device
-    if (e != cudaSuccess) return e;
-    // the maps are a pure function of (pointer, frame count): keep the last pair per calling thread
-    struct Cached { const uint8_t *frames = nullptr, *warm = nullptr; int n = 0, depth = 0; CUtensorMap ring, side; };
-    static thread_local Cached c;
+    static thread_local FrameMaps c;
     if (c.frames != a.frames || c.warm != a.warm || c.n != a.n || c.depth != a.depth) {
+        cudaError_t e;
         if ((e = frame_tensor_map(&c.ring, a.frames, static_cast<size_t>(a.depth) * a.n)) != cudaSuccess) return e;
         if (a.warm != nullptr) { if ((e = frame_tensor_map(&c.side, a.warm, static_cast<size_t>(3) * a.n)) != cudaSuccess) return e; }
         else c.side = c.ring;
         c.frames = a.frames; c.warm = a.warm; c.n = a.n; c.depth = a.depth;
     }
-    conv1p_kernel<<<grid, c1p::kCta, c1p::kSmem, s>>>(a, c.ring, c.side);
+    *out = &c;
+    return cudaSuccess;
+}
+
+cudaError_t launch_conv1p(const Args &a, int grid, cudaStream_t s)
+{
+    cudaError_t e = cudaFuncSetAttribute(conv1p_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, c1p::kSmem); // per device
+    if (e != cudaSuccess) return e;
+    const FrameMaps *m = nullptr;
+    if ((e = frame_maps(a, &m)) != cudaSuccess) return e;
+    conv1p_kernel<<<grid, c1p::kCta, c1p::kSmem, s>>>(a, m->ring, m->side);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------ conv1, A operand in TMEM
+// ncu of conv1p_kernel (profiles/conv1p_r2c_ncu.txt): tensor pipe 18 %, "tc" pipe 50 %, converters busy 65-80 % of the
+// time, a third of that in fence.proxy.async + mbarrier.  Two limits meet there: an MMA whose A operand comes from shared
+// memory reads it at 64 B/clk — 4 KB = 64 cycles per M128 x K16 tile whatever N is, against a floor of 128 N / 256 = 24
+// cycles at N = 48 — and every converted byte goes register -> shared (generic proxy) -> fence -> tensor core.
+// Here the converters write the A tiles straight into TENSOR MEMORY (tcgen05.st, 256 B/clk, no proxy fence) and the MMAs
+// take A from TMEM (tcgen05.mma [d], [a], b-desc: only the 1.5 KB B block is read from shared memory):
+//   * same work items, M rows (r = 23 q + il), phases, weights (pack_conv1_phase) and epilogue as conv1p_kernel;
+//   * TMEM lane r of tile (class c, phase ph) holds the 16 fp16 pixels 24 q + 8 ph .. + 15 of image row 3 il + c in 8
+//     columns (two K elements per 32-bit column).  A thread owns one lane: per class it reads its row's 32 pixels
+//     24 q .. 24 q + 31 from the swizzled raw stage (four 8-byte loads), converts each pixel ONCE (16 registers) and stores
+//     the three overlapping phase windows — registers 4 ph .. 4 ph + 7 — with three tcgen05.st.32x32b.x8;
+//   * 512 TMEM columns = 2 accumulator buffers x 3 phases x 48 + 3 A stages x 9 tiles x 8;
+//   * 8 converter warps = 2 groups x 4 lane quarters, the groups taking alternate planes; no converted stage in shared
+//     memory, so 8 raw stages (72 KB per SM) of TMA loads are in flight.
+namespace c1t {
+constexpr int kGroups = 2, kConverters = kGroups * 128, kMmaWarp = kConverters / 32, kLoadWarp = kMmaWarp + 1, kCta = kConverters + 64 + 128;
+constexpr int kAStages = 3, kRaw = 8;
+constexpr int kRowsQ = c1p::kRowsQ, kQ = c1p::kQ, kRowsUsed = c1p::kRowsUsed;
+constexpr int kRawRows = c1p::kRawRows, kRawBytes = c1p::kRawBytes;
+constexpr int kN = 48, kWBlock = c1p::kWBlock, kWBytes = c1p::kWBytes, kExBytes = c1p::kExBytes;
+constexpr int kSmem = 1024 + kRaw * kRawBytes + kWBytes + kExBytes; // 213 888 B
+constexpr int kTmemCols = 512, kBufCols = 3 * kN, kACol = 2 * kBufCols, kATile = 8, kAStageCols = 9 * kATile; // 288 + 3 x 72 = 504
+} // namespace c1t
+
+// D[tmem] (+)= A[tmem] * B[smem]: A is lanes 0..127 x 8 columns (16 fp16), issued by ONE thread
+__device__ __forceinline__ void umma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+        :: "r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// 8 consecutive 32-bit columns of this thread's TMEM lane
+__device__ __forceinline__ void tmem_store8(uint32_t taddr, uint32_t r0, uint32_t r1, uint32_t r2, uint32_t r3, uint32_t r4, uint32_t r5, uint32_t r6, uint32_t r7)
+{
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+                 :: "r"(taddr), "r"(r0), "r"(r1), "r"(r2), "r"(r3), "r"(r4), "r"(r5), "r"(r6), "r"(r7) : "memory");
+}
+// true in exactly one lane of a converged warp
+__device__ __forceinline__ bool elect_one()
+{
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.b32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
+__device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+__global__ void __launch_bounds__(c1t::kCta, 1) conv1t_kernel(Args a, const __grid_constant__ CUtensorMap tm_ring, const __grid_constant__ CUtensorMap tm_warm)
+{
+    using namespace c1t;
+    extern __shared__ __align__(128) uint8_t smem_unaligned[];
+    uint8_t *s_raw = smem_unaligned + ((1024u - (smem_u32(smem_unaligned) & 1023u)) & 1023u); // swizzle atoms are 1024-byte aligned
+    uint8_t *s_w = s_raw + kRaw * kRawBytes;
+    float *s_ex = reinterpret_cast<float *>(s_w + kWBytes);
+    __shared__ __align__(8) uint64_t s_wfull, s_rfull[kRaw], s_rempty[kRaw], s_afull[kAStages], s_aempty[kAStages], s_tfull[2], s_tempty[2];
+    __shared__ uint32_t s_tmem;
+    __shared__ float s_bias[8];
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int items = a.n * 2;
+    const int my_items = static_cast<int>(blockIdx.x) < items ? (items - 1 - static_cast<int>(blockIdx.x)) / static_cast<int>(gridDim.x) + 1 : 0;
+    if (tid == 0) {
+        mbar_init(&s_wfull, 1);
+        for (int i = 0; i < kRaw; ++i) { mbar_init(&s_rfull[i], 1); mbar_init(&s_rempty[i], 4); }
+        for (int i = 0; i < kAStages; ++i) { mbar_init(&s_afull[i], 4); mbar_init(&s_aempty[i], 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&s_tfull[i], 1); mbar_init(&s_tempty[i], 128); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (tid < 8) s_bias[tid] = tid < 5 ? a.bias[tid] : 0.0f;
+    if (warp == kMmaWarp) tmem_alloc(&s_tmem, kTmemCols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = s_tmem;
+
+    if (warp == kLoadWarp) {
+        // ---------------------------------------------------------------- loader: one tiled TMA copy per plane (as conv1p_kernel)
+        if (lane == 0) {
+            auto frame_rows = [&](int t, int (&p)[3]) { // row index of (frame, colour 0, row 0); bit 31: warm-up buffer
+                const int sample = (static_cast<int>(blockIdx.x) + t * static_cast<int>(gridDim.x)) >> 1;
+                const int steps = a.warm != nullptr ? static_cast<int>(a.meta[sample] & 0xFFFFu) : 0x7FFFFFFF;
+#pragma unroll
+                for (int age = 0; age < 3; ++age)
+                    p[age] = age >= steps ? static_cast<int>((static_cast<uint32_t>(2 - (age - steps)) * a.n + sample) * (3u * kDim) | 0x80000000u)
+                                          : ((a.head + a.depth - age) % a.depth * a.n + sample) * (3 * kDim);
+            };
+            int cur[3] = {0, 0, 0}, nxt[3] = {0, 0, 0};
+            if (my_items > 0) frame_rows(0, cur);
+            uint32_t fill = 0;
+            for (int t = 0; t < my_items; ++t) {
+                if (t + 1 < my_items) frame_rows(t + 1, nxt);
+                const int item = static_cast<int>(blockIdx.x) + t * static_cast<int>(gridDim.x);
+                const int row0 = (item & 1) ? 60 : 0;
+#pragma unroll
+                for (int plane = 0; plane < 9; ++plane, ++fill) {
+                    const uint32_t r = fill % kRaw;
+                    if (fill >= kRaw) mbar_wait(&s_rempty[r], ((fill / kRaw) - 1u) & 1u);
+                    mbar_expect_tx(&s_rfull[r], kRawRows * kDim);
+                    const int f = cur[plane / 3];
+                    const int row = (f & 0x7FFFFFFF) + (plane % 3) * kDim + row0;
+                    const CUtensorMap *tm = f < 0 ? &tm_warm : &tm_ring;
+                    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                                 :: "r"(smem_u32(s_raw + r * kRawBytes)), "l"(reinterpret_cast<uint64_t>(tm)), "r"(0), "r"(row), "r"(smem_u32(&s_rfull[r])) : "memory");
+                }
+#pragma unroll
+                for (int age = 0; age < 3; ++age) cur[age] = nxt[age];
+            }
+        }
+    } else if (warp < kMmaWarp) {
+        // ---------------------------------------------------------------- converters: raw uint8 rows -> fp16 A tiles in TMEM
+        // warp = (group, lane quarter); thread = TMEM lane r = 23 q + il; group g takes the planes with fill % kGroups == g
+        const int quarter = warp & 3, group = warp >> 2;
+        const int r = quarter * 32 + lane, q = r / kRowsQ, il = r - q * kRowsQ;
+        const bool active = r < kRowsUsed;
+        uint32_t off[3][4]; // the four 8-pixel pieces 24 q + 8 j of image row 3 il + c in the swizzled stage
+#pragma unroll
+        for (int c = 0; c < 3; ++c)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int row = 3 * il + c, o = 24 * q + 8 * j;
+                off[c][j] = active ? row * kDim + ((((o >> 4) ^ (row & 7)) << 4) | (o & 8)) : 0u;
+            }
+        const uint32_t lane_base = tmem + (static_cast<uint32_t>(quarter * 32) << 16) + kACol;
+        for (int t = 0; t < my_items; ++t) {
+            const int item = static_cast<int>(blockIdx.x) + t * static_cast<int>(gridDim.x);
+            const bool short_row = (item & 1) && il == kRowsQ - 1; // class 2 of il = 22 is image row 128: zeros
+#pragma unroll 1
+            for (int plane = 0; plane < 9; ++plane) {
+                const uint32_t fill = static_cast<uint32_t>(t) * 9u + plane;
+                if (static_cast<int>(fill % kGroups) != group) continue;
+                const uint32_t rs = fill % kRaw, st = fill % kAStages;
+                mbar_wait(&s_rfull[rs], (fill / kRaw) & 1u);
+                uint2 px[3][4];
+                const uint8_t *raw = s_raw + rs * kRawBytes;
+#pragma unroll
+                for (int c = 0; c < 3; ++c)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) px[c][j] = *reinterpret_cast<const uint2 *>(raw + off[c][j]);
+                if (short_row || !active) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) px[2][j] = make_uint2(0u, 0u);
+                }
+                if (!active) {
+#pragma unroll
+                    for (int c = 0; c < 2; ++c)
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) px[c][j] = make_uint2(0u, 0u);
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&s_rempty[rs]);
+                if (fill >= kAStages) mbar_wait(&s_aempty[st], ((fill / kAStages) - 1u) & 1u);
+                tc_fence_after();
+                const uint32_t stage = lane_base + st * kAStageCols;
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    uint32_t h[16];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const uint2 lo = u8x4_to_f16x4(px[c][j].x), hi = u8x4_to_f16x4(px[c][j].y);
+                        h[4 * j] = lo.x; h[4 * j + 1] = lo.y; h[4 * j + 2] = hi.x; h[4 * j + 3] = hi.y;
+                    }
+#pragma unroll
+                    for (int ph = 0; ph < 3; ++ph)
+                        tmem_store8(stage + (c * 3 + ph) * kATile, h[4 * ph], h[4 * ph + 1], h[4 * ph + 2], h[4 * ph + 3], h[4 * ph + 4], h[4 * ph + 5], h[4 * ph + 6], h[4 * ph + 7]);
+                }
+                tmem_wait_st();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&s_afull[st]);
+            }
+        }
+    } else if (warp == kMmaWarp) {
+        // ---------------------------------------------------------------- MMA issue
+        // The WHOLE warp runs the loop and one elected lane issues: with every operand warp-uniform the compiler feeds the
+        // MMA from uniform registers; under `if (lane == 0)` it wrapped each MMA in an election loop of ~13 instructions
+        // (~100 cycles per MMA for the single issuing thread — the limit of conv1p_kernel and of the first version of this one).
+        if (lane == 0) {
+            mbar_expect_tx(&s_wfull, kWBytes);
+            for (int i = 0; i < 9; ++i) bulk_load(s_w + i * (kWBytes / 9), reinterpret_cast<const uint8_t *>(a.weights) + i * (kWBytes / 9), kWBytes / 9, &s_wfull);
+        }
+        __syncwarp();
+        mbar_wait(&s_wfull, 0);
+        constexpr uint32_t kIdesc = instr_desc_f16(kN);
+        const uint64_t w_desc = smem_desc(smem_u32(s_w), (kN / 8) * 128, 128);
+        uint32_t fill = 0;
+        for (int t = 0; t < my_items; ++t) {
+            const uint32_t buf = t & 1u;
+            if (t >= 2) mbar_wait(&s_tempty[buf], ((t >> 1) - 1) & 1);
+            tc_fence_after();
+            const uint32_t d_base = tmem + buf * kBufCols;
+#pragma unroll 1
+            for (int plane = 0; plane < 9; ++plane, ++fill) {
+                const uint32_t st = fill % kAStages;
+                mbar_wait(&s_afull[st], (fill / kAStages) & 1);
+                tc_fence_after();
+                const uint32_t a_stage = tmem + kACol + st * kAStageCols;
+                const uint64_t bd0 = w_desc + static_cast<uint64_t>(plane * (9 * kWBlock / 16));
+                if (elect_one()) {
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) {
+#pragma unroll
+                        for (int ph = 0; ph < 3; ++ph)
+                            umma_f16_ts(d_base + ph * kN, a_stage + (c * 3 + ph) * kATile, bd0 + static_cast<uint64_t>((c * 3 + ph) * (kWBlock / 16)), kIdesc, (plane | c) != 0);
+                    }
+                    umma_commit(&s_aempty[st]);
+                    if (plane == 8) umma_commit(&s_tfull[buf]);
+                }
+                __syncwarp();
+            }
+        }
+    } else {
+        // ---------------------------------------------------------------- epilogue: 4 warps, thread = TMEM lane = M row 23 q + il
+        const int q4 = warp & 3;
+        const int m = q4 * 32 + lane;
+        const int q = m / kRowsQ, il = m - q * kRowsQ;
+        const bool row_ok = m < kRowsUsed;
+        for (int t = 0; t < my_items; ++t) {
+            const int item = static_cast<int>(blockIdx.x) + t * static_cast<int>(gridDim.x);
+            const int sample = item >> 1, y0 = (item & 1) ? 20 : 0, ny = (item & 1) ? 21 : 20;
+            const uint32_t buf = t & 1u;
+            mbar_wait(&s_tfull[buf], (t >> 1) & 1);
+            tc_fence_after();
+#pragma unroll 1
+            for (int ph = 0; ph < 3; ++ph) {
+                const uint32_t taddr = tmem + buf * kBufCols + ph * kN + (static_cast<uint32_t>(q4 * 32) << 16);
+                uint32_t v0[16], v1[16], v2[16]; // kernel-row groups kv = 0, 1, 2: [3 outputs x 5 channels]
+                tmem_load16_async(taddr, v0);
+                tmem_load16_async(taddr + 16, v1);
+                tmem_load16_async(taddr + 32, v2);
+                tmem_wait_ld();
+                if (ph == 2) { // the item's accumulators are all in registers: the MMA warp may overwrite them
+                    tc_fence_before();
+                    mbar_arrive(&s_tempty[buf]);
+                }
+                // kernel-row group kv of input-row index il belongs to output row il - kv
+                if (row_ok && il >= 1 && il - 1 < ny) {
+                    float4 *dst = reinterpret_cast<float4 *>(s_ex + ((0 * kRowsQ + (il - 1)) * kQ + q) * 16);
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) dst[e] = make_float4(__uint_as_float(v1[4 * e]), __uint_as_float(v1[4 * e + 1]), __uint_as_float(v1[4 * e + 2]), __uint_as_float(v1[4 * e + 3]));
+                }
+                if (row_ok && il >= 2 && il - 2 < ny) {
+                    float4 *dst = reinterpret_cast<float4 *>(s_ex + ((1 * kRowsQ + (il - 2)) * kQ + q) * 16);
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) dst[e] = make_float4(__uint_as_float(v2[4 * e]), __uint_as_float(v2[4 * e + 1]), __uint_as_float(v2[4 * e + 2]), __uint_as_float(v2[4 * e + 3]));
+                }
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+                if (row_ok && il < ny) {
+                    const float4 *p1 = reinterpret_cast<const float4 *>(s_ex + ((0 * kRowsQ + il) * kQ + q) * 16);
+                    const float4 *p2 = reinterpret_cast<const float4 *>(s_ex + ((1 * kRowsQ + il) * kQ + q) * 16);
+                    float sum[16];
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const float4 u = p1[e], w = p2[e];
+                        sum[4 * e] = __uint_as_float(v0[4 * e]) + u.x + w.x;
+                        sum[4 * e + 1] = __uint_as_float(v0[4 * e + 1]) + u.y + w.y;
+                        sum[4 * e + 2] = __uint_as_float(v0[4 * e + 2]) + u.z + w.z;
+                        sum[4 * e + 3] = __uint_as_float(v0[4 * e + 3]) + u.w + w.w;
+                    }
+                    const int y = y0 + il, x0 = 8 * q + 3 * ph;
+                    uint4 *out = reinterpret_cast<uint4 *>(a.out + (static_cast<size_t>(sample) * kP1 + y * kC1 + x0) * kAct1C);
+#pragma unroll
+                    for (int j = 0; j < 3; ++j) {
+                        if (j < 2 || ph < 2 || q == kQ - 1) { // phase 2's third output is the next block's first, except x = 40
+                            float c[5];
+#pragma unroll
+                            for (int ch = 0; ch < 5; ++ch) c[ch] = fmaxf(sum[j * 5 + ch] * (1.0f / 128.0f) + s_bias[ch], 0.0f); // (x - 128) / 128: processor.py:39-42
+                            const __nv_bfloat162 p01 = __floats2bfloat162_rn(c[0], c[1]), p23 = __floats2bfloat162_rn(c[2], c[3]), p4 = __floats2bfloat162_rn(c[4], 0.0f);
+                            out[j] = make_uint4(*reinterpret_cast<const uint32_t *>(&p01), *reinterpret_cast<const uint32_t *>(&p23), *reinterpret_cast<const uint32_t *>(&p4), 0u);
+                        }
+                    }
+                }
+                asm volatile("bar.sync 1, 128;" ::: "memory"); // the exchange buffer is free for the next phase
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == kMmaWarp) tmem_dealloc(tmem, kTmemCols);
+}
+
+cudaError_t launch_conv1t(const Args &a, int grid, cudaStream_t s)
+{
+    cudaError_t e = cudaFuncSetAttribute(conv1t_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, c1t::kSmem); // per device
+    if (e != cudaSuccess) return e;
+    const FrameMaps *m = nullptr;
+    if ((e = frame_maps(a, &m)) != cudaSuccess) return e;
+    conv1t_kernel<<<grid, c1t::kCta, c1t::kSmem, s>>>(a, m->ring, m->side);
     return cudaGetLastError();
 }
 
@@ -1439,6 +1740,7 @@ struct ahk_policy {
     uint16_t *w1t = nullptr; // conv1 in Toeplitz form (conv1_kernel, A/B switch AHK_CONV1=n144)
     uint16_t *w1p = nullptr; // conv1 in phase-separated form (conv1p_kernel, the default), fp16, unscaled
     bool conv1_n144 = false;
+    bool conv1_smem = false; // A/B switch AHK_CONV1=smem: conv1p_kernel (A operand converted into shared memory) instead of conv1t_kernel (A in TMEM)
     cudaEvent_t ev[7] = {};  // ahk_policy_forward_profiled: around each of the six layer kernels
     // the 'gray-diff' network (ahk_policy_gray_create): weights/biases of its six layers, input image and activations
     bool gray = false;
@@ -1580,7 +1882,7 @@ int ahk_policy_create(int device, int max_batch, const ahk_policy_weights *w, ah
     p->max_batch = max_batch;
     cudaDeviceGetAttribute(&p->sms, cudaDevAttrMultiProcessorCount, device);
     if (const char *sw = getenv("AHK_CONV23")) p->legacy_conv = strcmp(sw, "tile") == 0;
-    if (const char *sw = getenv("AHK_CONV1")) p->conv1_n144 = strcmp(sw, "n144") == 0;
+    if (const char *sw = getenv("AHK_CONV1")) { p->conv1_n144 = strcmp(sw, "n144") == 0; p->conv1_smem = strcmp(sw, "smem") == 0; }
     int rc = load_rgb_weights(p, w);
     const size_t nb = static_cast<size_t>(max_batch);
     cudaError_t err = cudaSuccess;
@@ -1797,7 +2099,7 @@ static int policy_forward(ahk_policy *p, const ahk_stack &stack, float *logits, 
     } else {
         a.weights = reinterpret_cast<const uint4 *>(p->w1p);
         const int items = n * 2;
-        POL_CUDA(launch_conv1p(a, items < p->sms ? items : p->sms, s));
+        POL_CUDA(p->conv1_smem ? launch_conv1p(a, items < p->sms ? items : p->sms, s) : launch_conv1t(a, items < p->sms ? items : p->sms, s));
     }
     if (timed) POL_CUDA(cudaEventRecord(p->ev[1], s));
     a.in = p->act1; a.weights = reinterpret_cast<const uint4 *>(p->w[1]); a.bias = p->b[1]; a.out = p->act2; a.m_total = n * kP2;

@@ -127,6 +127,13 @@ __device__ __forceinline__ void umma_commit(uint64_t *bar)
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(smem_u32(bar)) : "memory");
 }
 
+// true in exactly one lane of a converged warp
+__device__ __forceinline__ bool elect_one()
+{
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.b32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
 // 16 consecutive fp32 columns of this thread's TMEM lane, without waiting for the data (tmem_wait_ld before use)
 __device__ __forceinline__ void tmem_load16_async(uint32_t taddr, uint32_t (&r)[16])
 {
@@ -327,18 +334,18 @@ __global__ void __launch_bounds__(kThreads) layer_kernel(Args a)
             prefetch();
             fence_async_smem();
             __syncthreads();
-            if (tid == 0) {
+            if (warp == 0) { // the whole warp runs this with uniform operands and one elected lane issues (see conv1t_kernel)
                 mbar_wait(&s_full[st], use & 1u);
                 tc_fence_after();
-                const uint32_t a_base = smem_u32(s_a + st * kAStage), b_base = smem_u32(s_b + st * kBBytes);
+                const uint64_t ad0 = smem_desc(smem_u32(s_a + st * kAStage), kALbo, 128), bd0 = smem_desc(smem_u32(s_b + st * kBBytes), N / 8 * 128, 128);
+                if (elect_one()) {
 #pragma unroll
-                for (int j = 0; j < kBK / 16; ++j) {
-                    const uint64_t ad = smem_desc(a_base + j * 2 * kALbo, kALbo, 128);
-                    const uint64_t bd = smem_desc(b_base + j * 2 * (N / 8 * 128), N / 8 * 128, 128);
-                    umma_bf16(tmem, ad, bd, kIdesc, (ch | j) != 0);
+                    for (int j = 0; j < kBK / 16; ++j)
+                        umma_bf16(tmem, ad0 + static_cast<uint64_t>(j * 2 * kALbo / 16), bd0 + static_cast<uint64_t>(j * 2 * (N / 8 * 128) / 16), kIdesc, (ch | j) != 0);
+                    umma_commit(&s_free[st]);
+                    if (ch == NCH - 1) umma_commit(&s_done);
                 }
-                umma_commit(&s_free[st]);
-                if (ch == NCH - 1) umma_commit(&s_done);
+                __syncwarp();
             }
         }
         mbar_wait(&s_done, it & 1u);
@@ -1012,12 +1019,12 @@ cudaError_t launch_conv1p(const Args &a, int grid, cudaStream_t s)
 //   * 8 converter warps = 2 groups x 4 lane quarters, the groups taking alternate planes; no converted stage in shared
 //     memory, so 8 raw stages (72 KB per SM) of TMA loads are in flight.
 namespace c1t {
-constexpr int kGroups = 2, kConverters = kGroups * 128, kMmaWarp = kConverters / 32, kLoadWarp = kMmaWarp + 1, kCta = kConverters + 64 + 128;
+constexpr int kGroups = 2, kConverters = kGroups * 128, kMmaWarp = kConverters / 32, kLoadWarp = kMmaWarp + 1, kEpiSets = 2, kCta = kConverters + 64 + kEpiSets * 128;
 constexpr int kAStages = 3, kRaw = 8;
 constexpr int kRowsQ = c1p::kRowsQ, kQ = c1p::kQ, kRowsUsed = c1p::kRowsUsed;
 constexpr int kRawRows = c1p::kRawRows, kRawBytes = c1p::kRawBytes;
 constexpr int kN = 48, kWBlock = c1p::kWBlock, kWBytes = c1p::kWBytes, kExBytes = c1p::kExBytes;
-constexpr int kSmem = 1024 + kRaw * kRawBytes + kWBytes + kExBytes; // 213 888 B
+constexpr int kSmem = 1024 + kRaw * kRawBytes + kWBytes + kEpiSets * kExBytes; // 228 608 B
 constexpr int kTmemCols = 512, kBufCols = 3 * kN, kACol = 2 * kBufCols, kATile = 8, kAStageCols = 9 * kATile; // 288 + 3 x 72 = 504
 } // namespace c1t
 
@@ -1035,13 +1042,6 @@ __device__ __forceinline__ void tmem_store8(uint32_t taddr, uint32_t r0, uint32_
 {
     asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
                  :: "r"(taddr), "r"(r0), "r"(r1), "r"(r2), "r"(r3), "r"(r4), "r"(r5), "r"(r6), "r"(r7) : "memory");
-}
-// true in exactly one lane of a converged warp
-__device__ __forceinline__ bool elect_one()
-{
-    uint32_t pred;
-    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.b32 %0, 1, 0, p;\n\t}" : "=r"(pred));
-    return pred != 0;
 }
 __device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
@@ -1121,53 +1121,38 @@ __global__ void __launch_bounds__(c1t::kCta, 1) conv1t_kernel(Args a, const __gr
                 off[c][j] = active ? row * kDim + ((((o >> 4) ^ (row & 7)) << 4) | (o & 8)) : 0u;
             }
         const uint32_t lane_base = tmem + (static_cast<uint32_t>(quarter * 32) << 16) + kACol;
-        for (int t = 0; t < my_items; ++t) {
-            const int item = static_cast<int>(blockIdx.x) + t * static_cast<int>(gridDim.x);
-            const bool short_row = (item & 1) && il == kRowsQ - 1; // class 2 of il = 22 is image row 128: zeros
+        // (lanes r >= 115 and, in the second half of a sample, image row 128 hold whatever the copy brought: finite fp16
+        // either way, and they only reach accumulator rows / kernel rows (ky = 8: zero weights) that are never used)
+        const uint32_t fills = static_cast<uint32_t>(my_items) * 9u;
 #pragma unroll 1
-            for (int plane = 0; plane < 9; ++plane) {
-                const uint32_t fill = static_cast<uint32_t>(t) * 9u + plane;
-                if (static_cast<int>(fill % kGroups) != group) continue;
-                const uint32_t rs = fill % kRaw, st = fill % kAStages;
-                mbar_wait(&s_rfull[rs], (fill / kRaw) & 1u);
-                uint2 px[3][4];
-                const uint8_t *raw = s_raw + rs * kRawBytes;
+        for (uint32_t fill = group; fill < fills; fill += kGroups) {
+            const uint32_t rs = fill % kRaw, st = fill % kAStages;
+            mbar_wait(&s_rfull[rs], (fill / kRaw) & 1u);
+            uint2 px[3][4];
+            const uint8_t *raw = s_raw + rs * kRawBytes;
 #pragma unroll
-                for (int c = 0; c < 3; ++c)
+            for (int c = 0; c < 3; ++c)
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) px[c][j] = *reinterpret_cast<const uint2 *>(raw + off[c][j]);
-                if (short_row || !active) {
+                for (int j = 0; j < 4; ++j) px[c][j] = *reinterpret_cast<const uint2 *>(raw + off[c][j]);
+            if (fill >= kAStages) mbar_wait(&s_aempty[st], ((fill / kAStages) - 1u) & 1u);
+            tc_fence_after();
+            const uint32_t stage = lane_base + st * kAStageCols;
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) px[2][j] = make_uint2(0u, 0u);
+            for (int c = 0; c < 3; ++c) {
+                uint32_t h[16];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const uint2 lo = u8x4_to_f16x4(px[c][j].x), hi = u8x4_to_f16x4(px[c][j].y);
+                    h[4 * j] = lo.x; h[4 * j + 1] = lo.y; h[4 * j + 2] = hi.x; h[4 * j + 3] = hi.y;
                 }
-                if (!active) {
 #pragma unroll
-                    for (int c = 0; c < 2; ++c)
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) px[c][j] = make_uint2(0u, 0u);
-                }
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&s_rempty[rs]);
-                if (fill >= kAStages) mbar_wait(&s_aempty[st], ((fill / kAStages) - 1u) & 1u);
-                tc_fence_after();
-                const uint32_t stage = lane_base + st * kAStageCols;
-#pragma unroll
-                for (int c = 0; c < 3; ++c) {
-                    uint32_t h[16];
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        const uint2 lo = u8x4_to_f16x4(px[c][j].x), hi = u8x4_to_f16x4(px[c][j].y);
-                        h[4 * j] = lo.x; h[4 * j + 1] = lo.y; h[4 * j + 2] = hi.x; h[4 * j + 3] = hi.y;
-                    }
-#pragma unroll
-                    for (int ph = 0; ph < 3; ++ph)
-                        tmem_store8(stage + (c * 3 + ph) * kATile, h[4 * ph], h[4 * ph + 1], h[4 * ph + 2], h[4 * ph + 3], h[4 * ph + 4], h[4 * ph + 5], h[4 * ph + 6], h[4 * ph + 7]);
-                }
-                tmem_wait_st();
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&s_afull[st]);
+                for (int ph = 0; ph < 3; ++ph)
+                    tmem_store8(stage + (c * 3 + ph) * kATile, h[4 * ph], h[4 * ph + 1], h[4 * ph + 2], h[4 * ph + 3], h[4 * ph + 4], h[4 * ph + 5], h[4 * ph + 6], h[4 * ph + 7]);
             }
+            tmem_wait_st();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) { mbar_arrive(&s_afull[st]); mbar_arrive(&s_rempty[rs]); } // every pixel register has been consumed: the raw stage is free
         }
     } else if (warp == kMmaWarp) {
         // ---------------------------------------------------------------- MMA issue
@@ -1210,11 +1195,14 @@ __global__ void __launch_bounds__(c1t::kCta, 1) conv1t_kernel(Args a, const __gr
         }
     } else {
         // ---------------------------------------------------------------- epilogue: 4 warps, thread = TMEM lane = M row 23 q + il
-        const int q4 = warp & 3;
+        // two sets of 4 warps, set s taking the items of accumulator buffer s (one warp per scheduler runs at the latency of
+        // its own instruction chain: with a single set the epilogue was busy 70 % of the time)
+        const int q4 = warp & 3, set = (warp - (kLoadWarp + 1)) >> 2;
         const int m = q4 * 32 + lane;
         const int q = m / kRowsQ, il = m - q * kRowsQ;
         const bool row_ok = m < kRowsUsed;
-        for (int t = 0; t < my_items; ++t) {
+        s_ex += set * (kExBytes / 4);
+        for (int t = set; t < my_items; t += kEpiSets) {
             const int item = static_cast<int>(blockIdx.x) + t * static_cast<int>(gridDim.x);
             const int sample = item >> 1, y0 = (item & 1) ? 20 : 0, ny = (item & 1) ? 21 : 20;
             const uint32_t buf = t & 1u;
@@ -1243,7 +1231,7 @@ __global__ void __launch_bounds__(c1t::kCta, 1) conv1t_kernel(Args a, const __gr
 #pragma unroll
                     for (int e = 0; e < 4; ++e) dst[e] = make_float4(__uint_as_float(v2[4 * e]), __uint_as_float(v2[4 * e + 1]), __uint_as_float(v2[4 * e + 2]), __uint_as_float(v2[4 * e + 3]));
                 }
-                asm volatile("bar.sync 1, 128;" ::: "memory");
+                asm volatile("bar.sync %0, 128;" :: "r"(set + 1) : "memory");
                 if (row_ok && il < ny) {
                     const float4 *p1 = reinterpret_cast<const float4 *>(s_ex + ((0 * kRowsQ + il) * kQ + q) * 16);
                     const float4 *p2 = reinterpret_cast<const float4 *>(s_ex + ((1 * kRowsQ + il) * kQ + q) * 16);
@@ -1269,7 +1257,7 @@ __global__ void __launch_bounds__(c1t::kCta, 1) conv1t_kernel(Args a, const __gr
                         }
                     }
                 }
-                asm volatile("bar.sync 1, 128;" ::: "memory"); // the exchange buffer is free for the next phase
+                asm volatile("bar.sync %0, 128;" :: "r"(set + 1) : "memory"); // the exchange buffer is free for the next phase
             }
         }
     }
@@ -1416,31 +1404,34 @@ __global__ void __launch_bounds__(ws::kCta, ws::Cfg<L>::kPerSm) conv_ws_kernel(A
         for (int c = chunks > kDepth ? chunks - kDepth : 0; c < chunks; ++c) publish(c);
     } else if (warp == kProducers / 32) {
         // ---------------------------------------------------------------- MMA issue (one thread)
+        // (the whole warp runs the loop with uniform operands, one elected lane issues: see conv1t_kernel)
         if (lane == 0) {
             mbar_expect_tx(&s_wfull, NCH * kBBytes);
             for (int i = 0; i < NCH; ++i) bulk_load(s_b + i * kBBytes, reinterpret_cast<const uint8_t *>(a.weights) + i * kBBytes, kBBytes, &s_wfull);
-            mbar_wait(&s_wfull, 0);
-            constexpr uint32_t kIdesc = instr_desc(N);
-            const uint32_t b_base = smem_u32(s_b);
-            int c = 0;
-            for (int t = 0; t < my_tiles; ++t) {
-                const uint32_t buf = t & 1;
-                if (t >= 2) mbar_wait(&s_tempty[buf], ((t >> 1) - 1) & 1);
+        }
+        __syncwarp();
+        mbar_wait(&s_wfull, 0);
+        constexpr uint32_t kIdesc = instr_desc(N);
+        const uint64_t b_desc = smem_desc(smem_u32(s_b), N / 8 * 128, 128);
+        int c = 0;
+        for (int t = 0; t < my_tiles; ++t) {
+            const uint32_t buf = t & 1;
+            if (t >= 2) mbar_wait(&s_tempty[buf], ((t >> 1) - 1) & 1);
+            tc_fence_after();
+#pragma unroll 1
+            for (int ch = 0; ch < NCH; ++ch, ++c) {
+                const int st = c % kStages;
+                mbar_wait(&s_full[st], (c / kStages) & 1);
                 tc_fence_after();
-                for (int ch = 0; ch < NCH; ++ch, ++c) {
-                    const int st = c % kStages;
-                    mbar_wait(&s_full[st], (c / kStages) & 1);
-                    tc_fence_after();
-                    const uint32_t a_base = smem_u32(s_a + st * kStage);
+                const uint64_t ad0 = smem_desc(smem_u32(s_a + st * kStage), kLbo, 128), bd0 = b_desc + static_cast<uint64_t>(ch * (kBBytes / 16));
+                if (elect_one()) {
 #pragma unroll
-                    for (int j = 0; j < kBK / 16; ++j) {
-                        const uint64_t ad = smem_desc(a_base + j * 2 * kLbo, kLbo, 128);
-                        const uint64_t bd = smem_desc(b_base + ch * kBBytes + j * 2 * (N / 8 * 128), N / 8 * 128, 128);
-                        umma_bf16(tmem + buf * kBufCols, ad, bd, kIdesc, (ch | j) != 0);
-                    }
+                    for (int j = 0; j < kBK / 16; ++j)
+                        umma_bf16(tmem + buf * kBufCols, ad0 + static_cast<uint64_t>(j * 2 * kLbo / 16), bd0 + static_cast<uint64_t>(j * 2 * (N / 8 * 128) / 16), kIdesc, (ch | j) != 0);
                     umma_commit(&s_empty[st]);
+                    if (ch == NCH - 1) umma_commit(&s_tfull[buf]);
                 }
-                umma_commit(&s_tfull[buf]);
+                __syncwarp();
             }
         }
     } else {

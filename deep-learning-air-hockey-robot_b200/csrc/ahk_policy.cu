@@ -1112,12 +1112,17 @@ __global__ void __launch_bounds__(c1t::kCta, 1) conv1t_kernel(Args a, const __gr
         const int quarter = warp & 3, group = warp >> 2;
         const int r = quarter * 32 + lane, q = r / kRowsQ, il = r - q * kRowsQ;
         const bool active = r < kRowsUsed;
-        uint32_t off[3][4]; // the four 8-pixel pieces 24 q + 8 j of image row 3 il + c in the swizzled stage
+        // The four 8-pixel pieces 24 q + 8 j of image row 3 il + c in the swizzled stage.  Eight consecutive il give eight
+        // different 16-byte chunks (3 il + c mod 8), the next eight repeat them: those lanes fetch their pieces in the order
+        // 1, 0, 3, 2 — the other 8-byte half (or the neighbouring chunk) — so that an 8-byte load instruction is served in two
+        // wavefronts instead of four, and swap the registers back afterwards.
+        const bool flip = (il >> 3) & 1;
+        uint32_t off[3][4];
 #pragma unroll
         for (int c = 0; c < 3; ++c)
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-                const int row = 3 * il + c, o = 24 * q + 8 * j;
+                const int row = 3 * il + c, o = 24 * q + 8 * (flip ? j ^ 1 : j);
                 off[c][j] = active ? row * kDim + ((((o >> 4) ^ (row & 7)) << 4) | (o & 8)) : 0u;
             }
         const uint32_t lane_base = tmem + (static_cast<uint32_t>(quarter * 32) << 16) + kACol;
@@ -1134,6 +1139,14 @@ __global__ void __launch_bounds__(c1t::kCta, 1) conv1t_kernel(Args a, const __gr
             for (int c = 0; c < 3; ++c)
 #pragma unroll
                 for (int j = 0; j < 4; ++j) px[c][j] = *reinterpret_cast<const uint2 *>(raw + off[c][j]);
+#pragma unroll
+            for (int c = 0; c < 3; ++c)
+#pragma unroll
+                for (int j = 0; j < 4; j += 2) {
+                    const uint2 u = px[c][j], v = px[c][j + 1];
+                    px[c][j] = make_uint2(flip ? v.x : u.x, flip ? v.y : u.y);
+                    px[c][j + 1] = make_uint2(flip ? u.x : v.x, flip ? u.y : v.y);
+                }
             if (fill >= kAStages) mbar_wait(&s_aempty[st], ((fill / kAStages) - 1u) & 1u);
             tc_fence_after();
             const uint32_t stage = lane_base + st * kAStageCols;
@@ -1221,24 +1234,24 @@ __global__ void __launch_bounds__(c1t::kCta, 1) conv1t_kernel(Args a, const __gr
                     mbar_arrive(&s_tempty[buf]);
                 }
                 // kernel-row group kv of input-row index il belongs to output row il - kv
+                // (exchange layout [kv][e][q][il] x 16 bytes: consecutive lanes = consecutive il = consecutive 16 bytes; as
+                // [il][q][16 floats] rows were 320 bytes apart and every 128-bit access took 4x its wavefronts — the shared-memory
+                // pipe was 77 % busy, two thirds of it here)
+                float4 *ex4 = reinterpret_cast<float4 *>(s_ex);
                 if (row_ok && il >= 1 && il - 1 < ny) {
-                    float4 *dst = reinterpret_cast<float4 *>(s_ex + ((0 * kRowsQ + (il - 1)) * kQ + q) * 16);
 #pragma unroll
-                    for (int e = 0; e < 4; ++e) dst[e] = make_float4(__uint_as_float(v1[4 * e]), __uint_as_float(v1[4 * e + 1]), __uint_as_float(v1[4 * e + 2]), __uint_as_float(v1[4 * e + 3]));
+                    for (int e = 0; e < 4; ++e) ex4[((0 * 4 + e) * kQ + q) * kRowsQ + il - 1] = make_float4(__uint_as_float(v1[4 * e]), __uint_as_float(v1[4 * e + 1]), __uint_as_float(v1[4 * e + 2]), __uint_as_float(v1[4 * e + 3]));
                 }
                 if (row_ok && il >= 2 && il - 2 < ny) {
-                    float4 *dst = reinterpret_cast<float4 *>(s_ex + ((1 * kRowsQ + (il - 2)) * kQ + q) * 16);
 #pragma unroll
-                    for (int e = 0; e < 4; ++e) dst[e] = make_float4(__uint_as_float(v2[4 * e]), __uint_as_float(v2[4 * e + 1]), __uint_as_float(v2[4 * e + 2]), __uint_as_float(v2[4 * e + 3]));
+                    for (int e = 0; e < 4; ++e) ex4[((1 * 4 + e) * kQ + q) * kRowsQ + il - 2] = make_float4(__uint_as_float(v2[4 * e]), __uint_as_float(v2[4 * e + 1]), __uint_as_float(v2[4 * e + 2]), __uint_as_float(v2[4 * e + 3]));
                 }
                 asm volatile("bar.sync %0, 128;" :: "r"(set + 1) : "memory");
                 if (row_ok && il < ny) {
-                    const float4 *p1 = reinterpret_cast<const float4 *>(s_ex + ((0 * kRowsQ + il) * kQ + q) * 16);
-                    const float4 *p2 = reinterpret_cast<const float4 *>(s_ex + ((1 * kRowsQ + il) * kQ + q) * 16);
                     float sum[16];
 #pragma unroll
                     for (int e = 0; e < 4; ++e) {
-                        const float4 u = p1[e], w = p2[e];
+                        const float4 u = ex4[((0 * 4 + e) * kQ + q) * kRowsQ + il], w = ex4[((1 * 4 + e) * kQ + q) * kRowsQ + il];
                         sum[4 * e] = __uint_as_float(v0[4 * e]) + u.x + w.x;
                         sum[4 * e + 1] = __uint_as_float(v0[4 * e + 1]) + u.y + w.y;
                         sum[4 * e + 2] = __uint_as_float(v0[4 * e + 2]) + u.z + w.z;

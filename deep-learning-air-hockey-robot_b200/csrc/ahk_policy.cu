@@ -830,8 +830,6 @@ __global__ void __launch_bounds__(c1p::kCta, 1) conv1p_kernel(Args a, const __gr
 #pragma unroll
                 for (int c = 0; c < 3; ++c) px[c] = active ? *reinterpret_cast<const uint4 *>(s_raw + r * kRawBytes + src[c]) : make_uint4(0, 0, 0, 0);
                 if (short_row) px[2] = make_uint4(0, 0, 0, 0);
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&s_rempty[r]);
                 if (fill >= kStages) mbar_wait(&s_empty[st], ((fill / kStages) - 1u) & 1u);
                 if (active) {
                     uint8_t *base = s_stage + st * kStageBytes + lane * 16;
@@ -850,7 +848,10 @@ __global__ void __launch_bounds__(c1p::kCta, 1) conv1p_kernel(Args a, const __gr
                 }
                 fence_async_smem();
                 __syncwarp();
-                if (lane == 0) mbar_arrive(&s_full[st]);
+                // the raw stage is released only here, after every pixel register has been consumed: an arrive issued right behind
+                // the loads does not wait for their data, and the loader's next copy overwrote rows still being read (seen as
+                // run-to-run differences at 8192 samples, tools/conv1_ab.py)
+                if (lane == 0) { mbar_arrive(&s_full[st]); mbar_arrive(&s_rempty[r]); }
             }
         }
     } else if (warp == kMmaWarp) {
@@ -1020,12 +1021,22 @@ cudaError_t launch_conv1p(const Args &a, int grid, cudaStream_t s)
 //     memory, so 8 raw stages (72 KB per SM) of TMA loads are in flight.
 namespace c1t {
 constexpr int kGroups = 2, kConverters = kGroups * 128, kMmaWarp = kConverters / 32, kLoadWarp = kMmaWarp + 1, kEpiSets = 2, kCta = kConverters + 64 + kEpiSets * 128;
-constexpr int kAStages = 3, kRaw = 8;
+constexpr int kAStages = 4, kRaw = 8;
 constexpr int kRowsQ = c1p::kRowsQ, kQ = c1p::kQ, kRowsUsed = c1p::kRowsUsed;
 constexpr int kRawRows = c1p::kRawRows, kRawBytes = c1p::kRawBytes;
 constexpr int kN = 48, kWBlock = c1p::kWBlock, kWBytes = c1p::kWBytes, kExBytes = c1p::kExBytes;
 constexpr int kSmem = 1024 + kRaw * kRawBytes + kWBytes + kEpiSets * kExBytes; // 228 608 B
-constexpr int kTmemCols = 512, kBufCols = 3 * kN, kACol = 2 * kBufCols, kATile = 8, kAStageCols = 9 * kATile; // 288 + 3 x 72 = 504
+constexpr int kTmemCols = 512, kBufCols = 3 * kN, kACol = 2 * kBufCols, kAClassCols = 16, kAStageCols = 3 * kAClassCols; // 288 + 4 x 48 = 480
+// TMEM lane m <-> M row (q, il): lanes are laid out [il / 8][q][il % 8], so that a warp's 32 lanes are 4 pixel blocks x 8
+// consecutive rows: their 8-byte loads from the swizzled stage hit 32 different (chunk, half) slots and the exchange rows
+// of the epilogue are contiguous.  120 lanes, 115 of them rows.
+__device__ __forceinline__ bool lane_row(int m, int &q, int &il)
+{
+    const int g = m / 40, rem = m - g * 40;
+    q = rem >> 3;
+    il = g * 8 + (rem & 7);
+    return m < 120 && il < kRowsQ;
+}
 } // namespace c1t
 
 // D[tmem] (+)= A[tmem] * B[smem]: A is lanes 0..127 x 8 columns (16 fp16), issued by ONE thread
@@ -1043,8 +1054,28 @@ __device__ __forceinline__ void tmem_store8(uint32_t taddr, uint32_t r0, uint32_
     asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
                  :: "r"(taddr), "r"(r0), "r"(r1), "r"(r2), "r"(r3), "r"(r4), "r"(r5), "r"(r6), "r"(r7) : "memory");
 }
+__device__ __forceinline__ void tmem_store16(uint32_t taddr, const uint32_t (&r)[16])
+{
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+                 :: "r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+                    "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]) : "memory");
+}
+// 4 uint8 -> 4 fp16 denormals (v * 2^-24, exact): zero-extended bytes
+__device__ __forceinline__ uint2 u8x4_to_f16x4_denormal(uint32_t w) { return make_uint2(__byte_perm(w, 0u, 0x4140), __byte_perm(w, 0u, 0x4342)); }
+// mbarrier wait that lets the hardware suspend the thread for up to ~1 us per try instead of spinning through the issue slots
+__device__ __forceinline__ void mbar_wait_sleep(uint64_t *bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n\t.reg .pred done;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 done, [%0], %1, %2;\n\t"
+        "@!done bra WAIT_%=;\n\t}"
+        :: "r"(smem_u32(bar)), "r"(parity), "r"(1000) : "memory");
+}
 __device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
+// kDenormal: pixels as fp16 DENORMALS (bit pattern 0x00vv = v * 2^-24): one PRMT per two pixels, the 2^24 goes to the epilogue
+template <bool kDenormal>
 __global__ void __launch_bounds__(c1t::kCta, 1) conv1t_kernel(Args a, const __grid_constant__ CUtensorMap tm_ring, const __grid_constant__ CUtensorMap tm_warm)
 {
     using namespace c1t;
@@ -1094,7 +1125,7 @@ __global__ void __launch_bounds__(c1t::kCta, 1) conv1t_kernel(Args a, const __gr
 #pragma unroll
                 for (int plane = 0; plane < 9; ++plane, ++fill) {
                     const uint32_t r = fill % kRaw;
-                    if (fill >= kRaw) mbar_wait(&s_rempty[r], ((fill / kRaw) - 1u) & 1u);
+                    if (fill >= kRaw) mbar_wait_sleep(&s_rempty[r], ((fill / kRaw) - 1u) & 1u);
                     mbar_expect_tx(&s_rfull[r], kRawRows * kDim);
                     const int f = cur[plane / 3];
                     const int row = (f & 0x7FFFFFFF) + (plane % 3) * kDim + row0;
@@ -1110,19 +1141,14 @@ __global__ void __launch_bounds__(c1t::kCta, 1) conv1t_kernel(Args a, const __gr
         // ---------------------------------------------------------------- converters: raw uint8 rows -> fp16 A tiles in TMEM
         // warp = (group, lane quarter); thread = TMEM lane r = 23 q + il; group g takes the planes with fill % kGroups == g
         const int quarter = warp & 3, group = warp >> 2;
-        const int r = quarter * 32 + lane, q = r / kRowsQ, il = r - q * kRowsQ;
-        const bool active = r < kRowsUsed;
-        // The four 8-pixel pieces 24 q + 8 j of image row 3 il + c in the swizzled stage.  Eight consecutive il give eight
-        // different 16-byte chunks (3 il + c mod 8), the next eight repeat them: those lanes fetch their pieces in the order
-        // 1, 0, 3, 2 — the other 8-byte half (or the neighbouring chunk) — so that an 8-byte load instruction is served in two
-        // wavefronts instead of four, and swap the registers back afterwards.
-        const bool flip = (il >> 3) & 1;
-        uint32_t off[3][4];
+        int q, il;
+        const bool active = lane_row(quarter * 32 + lane, q, il);
+        uint32_t off[3][4]; // the four 8-pixel pieces 24 q + 8 j of image row 3 il + c in the swizzled stage
 #pragma unroll
         for (int c = 0; c < 3; ++c)
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-                const int row = 3 * il + c, o = 24 * q + 8 * (flip ? j ^ 1 : j);
+                const int row = 3 * il + c, o = 24 * q + 8 * j;
                 off[c][j] = active ? row * kDim + ((((o >> 4) ^ (row & 7)) << 4) | (o & 8)) : 0u;
             }
         const uint32_t lane_base = tmem + (static_cast<uint32_t>(quarter * 32) << 16) + kACol;
@@ -1132,35 +1158,27 @@ __global__ void __launch_bounds__(c1t::kCta, 1) conv1t_kernel(Args a, const __gr
 #pragma unroll 1
         for (uint32_t fill = group; fill < fills; fill += kGroups) {
             const uint32_t rs = fill % kRaw, st = fill % kAStages;
-            mbar_wait(&s_rfull[rs], (fill / kRaw) & 1u);
+            mbar_wait_sleep(&s_rfull[rs], (fill / kRaw) & 1u);
             uint2 px[3][4];
             const uint8_t *raw = s_raw + rs * kRawBytes;
 #pragma unroll
             for (int c = 0; c < 3; ++c)
 #pragma unroll
                 for (int j = 0; j < 4; ++j) px[c][j] = *reinterpret_cast<const uint2 *>(raw + off[c][j]);
-#pragma unroll
-            for (int c = 0; c < 3; ++c)
-#pragma unroll
-                for (int j = 0; j < 4; j += 2) {
-                    const uint2 u = px[c][j], v = px[c][j + 1];
-                    px[c][j] = make_uint2(flip ? v.x : u.x, flip ? v.y : u.y);
-                    px[c][j + 1] = make_uint2(flip ? u.x : v.x, flip ? u.y : v.y);
-                }
-            if (fill >= kAStages) mbar_wait(&s_aempty[st], ((fill / kAStages) - 1u) & 1u);
+            if (fill >= kAStages) mbar_wait_sleep(&s_aempty[st], ((fill / kAStages) - 1u) & 1u);
             tc_fence_after();
             const uint32_t stage = lane_base + st * kAStageCols;
 #pragma unroll
             for (int c = 0; c < 3; ++c) {
+                // the class's 32 pixels, converted once, as ONE 16-column strip: phase ph reads its 16-pixel window from columns 4 ph .. 4 ph + 7
                 uint32_t h[16];
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
-                    const uint2 lo = u8x4_to_f16x4(px[c][j].x), hi = u8x4_to_f16x4(px[c][j].y);
+                    const uint2 lo = kDenormal ? u8x4_to_f16x4_denormal(px[c][j].x) : u8x4_to_f16x4(px[c][j].x);
+                    const uint2 hi = kDenormal ? u8x4_to_f16x4_denormal(px[c][j].y) : u8x4_to_f16x4(px[c][j].y);
                     h[4 * j] = lo.x; h[4 * j + 1] = lo.y; h[4 * j + 2] = hi.x; h[4 * j + 3] = hi.y;
                 }
-#pragma unroll
-                for (int ph = 0; ph < 3; ++ph)
-                    tmem_store8(stage + (c * 3 + ph) * kATile, h[4 * ph], h[4 * ph + 1], h[4 * ph + 2], h[4 * ph + 3], h[4 * ph + 4], h[4 * ph + 5], h[4 * ph + 6], h[4 * ph + 7]);
+                tmem_store16(stage + c * kAClassCols, h);
             }
             tmem_wait_st();
             tc_fence_before();
@@ -1177,19 +1195,19 @@ __global__ void __launch_bounds__(c1t::kCta, 1) conv1t_kernel(Args a, const __gr
             for (int i = 0; i < 9; ++i) bulk_load(s_w + i * (kWBytes / 9), reinterpret_cast<const uint8_t *>(a.weights) + i * (kWBytes / 9), kWBytes / 9, &s_wfull);
         }
         __syncwarp();
-        mbar_wait(&s_wfull, 0);
+        mbar_wait_sleep(&s_wfull, 0);
         constexpr uint32_t kIdesc = instr_desc_f16(kN);
         const uint64_t w_desc = smem_desc(smem_u32(s_w), (kN / 8) * 128, 128);
         uint32_t fill = 0;
         for (int t = 0; t < my_items; ++t) {
             const uint32_t buf = t & 1u;
-            if (t >= 2) mbar_wait(&s_tempty[buf], ((t >> 1) - 1) & 1);
+            if (t >= 2) mbar_wait_sleep(&s_tempty[buf], ((t >> 1) - 1) & 1);
             tc_fence_after();
             const uint32_t d_base = tmem + buf * kBufCols;
 #pragma unroll 1
             for (int plane = 0; plane < 9; ++plane, ++fill) {
                 const uint32_t st = fill % kAStages;
-                mbar_wait(&s_afull[st], (fill / kAStages) & 1);
+                mbar_wait_sleep(&s_afull[st], (fill / kAStages) & 1);
                 tc_fence_after();
                 const uint32_t a_stage = tmem + kACol + st * kAStageCols;
                 const uint64_t bd0 = w_desc + static_cast<uint64_t>(plane * (9 * kWBlock / 16));
@@ -1198,7 +1216,7 @@ __global__ void __launch_bounds__(c1t::kCta, 1) conv1t_kernel(Args a, const __gr
                     for (int c = 0; c < 3; ++c) {
 #pragma unroll
                         for (int ph = 0; ph < 3; ++ph)
-                            umma_f16_ts(d_base + ph * kN, a_stage + (c * 3 + ph) * kATile, bd0 + static_cast<uint64_t>((c * 3 + ph) * (kWBlock / 16)), kIdesc, (plane | c) != 0);
+                            umma_f16_ts(d_base + ph * kN, a_stage + c * kAClassCols + ph * 4, bd0 + static_cast<uint64_t>((c * 3 + ph) * (kWBlock / 16)), kIdesc, (plane | c) != 0);
                     }
                     umma_commit(&s_aempty[st]);
                     if (plane == 8) umma_commit(&s_tfull[buf]);
@@ -1211,15 +1229,14 @@ __global__ void __launch_bounds__(c1t::kCta, 1) conv1t_kernel(Args a, const __gr
         // two sets of 4 warps, set s taking the items of accumulator buffer s (one warp per scheduler runs at the latency of
         // its own instruction chain: with a single set the epilogue was busy 70 % of the time)
         const int q4 = warp & 3, set = (warp - (kLoadWarp + 1)) >> 2;
-        const int m = q4 * 32 + lane;
-        const int q = m / kRowsQ, il = m - q * kRowsQ;
-        const bool row_ok = m < kRowsUsed;
+        int q, il;
+        const bool row_ok = lane_row(q4 * 32 + lane, q, il);
         s_ex += set * (kExBytes / 4);
         for (int t = set; t < my_items; t += kEpiSets) {
             const int item = static_cast<int>(blockIdx.x) + t * static_cast<int>(gridDim.x);
             const int sample = item >> 1, y0 = (item & 1) ? 20 : 0, ny = (item & 1) ? 21 : 20;
             const uint32_t buf = t & 1u;
-            mbar_wait(&s_tfull[buf], (t >> 1) & 1);
+            mbar_wait_sleep(&s_tfull[buf], (t >> 1) & 1);
             tc_fence_after();
 #pragma unroll 1
             for (int ph = 0; ph < 3; ++ph) {
@@ -1264,7 +1281,7 @@ __global__ void __launch_bounds__(c1t::kCta, 1) conv1t_kernel(Args a, const __gr
                         if (j < 2 || ph < 2 || q == kQ - 1) { // phase 2's third output is the next block's first, except x = 40
                             float c[5];
 #pragma unroll
-                            for (int ch = 0; ch < 5; ++ch) c[ch] = fmaxf(sum[j * 5 + ch] * (1.0f / 128.0f) + s_bias[ch], 0.0f); // (x - 128) / 128: processor.py:39-42
+                            for (int ch = 0; ch < 5; ++ch) c[ch] = fmaxf(sum[j * 5 + ch] * (kDenormal ? 131072.0f : 1.0f / 128.0f) + s_bias[ch], 0.0f); // (x - 128) / 128: processor.py:39-42 (2^17 = 2^24 / 128)
                             const __nv_bfloat162 p01 = __floats2bfloat162_rn(c[0], c[1]), p23 = __floats2bfloat162_rn(c[2], c[3]), p4 = __floats2bfloat162_rn(c[4], 0.0f);
                             out[j] = make_uint4(*reinterpret_cast<const uint32_t *>(&p01), *reinterpret_cast<const uint32_t *>(&p23), *reinterpret_cast<const uint32_t *>(&p4), 0u);
                         }
@@ -1279,13 +1296,14 @@ __global__ void __launch_bounds__(c1t::kCta, 1) conv1t_kernel(Args a, const __gr
     if (warp == kMmaWarp) tmem_dealloc(tmem, kTmemCols);
 }
 
-cudaError_t launch_conv1t(const Args &a, int grid, cudaStream_t s)
+cudaError_t launch_conv1t(const Args &a, int grid, bool denormal, cudaStream_t s)
 {
-    cudaError_t e = cudaFuncSetAttribute(conv1t_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, c1t::kSmem); // per device
+    cudaError_t e = cudaFuncSetAttribute(denormal ? conv1t_kernel<true> : conv1t_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, c1t::kSmem); // per device
     if (e != cudaSuccess) return e;
     const FrameMaps *m = nullptr;
     if ((e = frame_maps(a, &m)) != cudaSuccess) return e;
-    conv1t_kernel<<<grid, c1t::kCta, c1t::kSmem, s>>>(a, m->ring, m->side);
+    if (denormal) conv1t_kernel<true><<<grid, c1t::kCta, c1t::kSmem, s>>>(a, m->ring, m->side);
+    else conv1t_kernel<false><<<grid, c1t::kCta, c1t::kSmem, s>>>(a, m->ring, m->side);
     return cudaGetLastError();
 }
 
@@ -1744,6 +1762,7 @@ struct ahk_policy {
     uint16_t *w1t = nullptr; // conv1 in Toeplitz form (conv1_kernel, A/B switch AHK_CONV1=n144)
     uint16_t *w1p = nullptr; // conv1 in phase-separated form (conv1p_kernel, the default), fp16, unscaled
     bool conv1_n144 = false;
+    bool conv1_normal = false; // A/B switch AHK_CONV1=normal: conv1t_kernel with the pixels as NORMAL fp16 numbers (1024 + v - 1024)
     bool conv1_smem = false; // A/B switch AHK_CONV1=smem: conv1p_kernel (A operand converted into shared memory) instead of conv1t_kernel (A in TMEM)
     cudaEvent_t ev[7] = {};  // ahk_policy_forward_profiled: around each of the six layer kernels
     // the 'gray-diff' network (ahk_policy_gray_create): weights/biases of its six layers, input image and activations
@@ -1886,7 +1905,7 @@ int ahk_policy_create(int device, int max_batch, const ahk_policy_weights *w, ah
     p->max_batch = max_batch;
     cudaDeviceGetAttribute(&p->sms, cudaDevAttrMultiProcessorCount, device);
     if (const char *sw = getenv("AHK_CONV23")) p->legacy_conv = strcmp(sw, "tile") == 0;
-    if (const char *sw = getenv("AHK_CONV1")) { p->conv1_n144 = strcmp(sw, "n144") == 0; p->conv1_smem = strcmp(sw, "smem") == 0; }
+    if (const char *sw = getenv("AHK_CONV1")) { p->conv1_n144 = strcmp(sw, "n144") == 0; p->conv1_smem = strcmp(sw, "smem") == 0; p->conv1_normal = strcmp(sw, "normal") == 0; }
     int rc = load_rgb_weights(p, w);
     const size_t nb = static_cast<size_t>(max_batch);
     cudaError_t err = cudaSuccess;
@@ -2103,7 +2122,7 @@ static int policy_forward(ahk_policy *p, const ahk_stack &stack, float *logits, 
     } else {
         a.weights = reinterpret_cast<const uint4 *>(p->w1p);
         const int items = n * 2;
-        POL_CUDA(p->conv1_smem ? launch_conv1p(a, items < p->sms ? items : p->sms, s) : launch_conv1t(a, items < p->sms ? items : p->sms, s));
+        POL_CUDA(p->conv1_smem ? launch_conv1p(a, items < p->sms ? items : p->sms, s) : launch_conv1t(a, items < p->sms ? items : p->sms, !p->conv1_normal, s));
     }
     if (timed) POL_CUDA(cudaEventRecord(p->ev[1], s));
     a.in = p->act1; a.weights = reinterpret_cast<const uint4 *>(p->w[1]); a.bias = p->b[1]; a.out = p->act2; a.m_total = n * kP2;

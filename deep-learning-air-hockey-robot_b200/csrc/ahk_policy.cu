@@ -19,6 +19,8 @@
 // after the ReLU) into the NEXT layer's weights and bias.
 #include "../../include/ahk.h"
 #include "ahk_kernels.cuh"
+#include "ahk_tc.cuh"
+#include "ahk_gemm.cuh"
 
 #include <cuda.h>
 #include <cudaTypedefs.h>
@@ -79,102 +81,7 @@ struct Args {
     const uint32_t *meta;       // deep ring: state word 15 per env
 };
 
-// ------------------------------------------------------------------------------------------------ PTX wrappers
-__device__ __forceinline__ uint32_t smem_u32(const void *p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
-
-__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) { asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(bar)), "r"(count) : "memory"); }
-__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) { asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(bar)), "r"(bytes) : "memory"); }
-__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
-{
-    asm volatile(
-        "{\n\t.reg .pred done;\n\t"
-        "WAIT_%=:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 done, [%0], %1;\n\t"
-        "@!done bra WAIT_%=;\n\t}"
-        :: "r"(smem_u32(bar)), "r"(parity) : "memory");
-}
-__device__ __forceinline__ void bulk_load(void *smem_dst, const void *gmem_src, uint32_t bytes, uint64_t *bar)
-{
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 :: "r"(smem_u32(smem_dst)), "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-
-__device__ __forceinline__ void tmem_alloc(uint32_t *result_in_smem, uint32_t cols)
-{ // one full warp
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(smem_u32(result_in_smem)), "r"(cols) : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols)
-{
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(taddr), "r"(cols) : "memory");
-}
-
-// D[tmem] (+)= A[smem] * B[smem], M = 128, K = 16, bf16 x bf16 -> f32, issued by ONE thread
-__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate)
-{
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-        :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
-}
-// the mbarrier gets one arrival when every tcgen05 op issued so far by this thread has completed
-__device__ __forceinline__ void umma_commit(uint64_t *bar)
-{
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(smem_u32(bar)) : "memory");
-}
-
-// true in exactly one lane of a converged warp
-__device__ __forceinline__ bool elect_one()
-{
-    uint32_t pred;
-    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.b32 %0, 1, 0, p;\n\t}" : "=r"(pred));
-    return pred != 0;
-}
-// 16 consecutive fp32 columns of this thread's TMEM lane, without waiting for the data (tmem_wait_ld before use)
-__device__ __forceinline__ void tmem_load16_async(uint32_t taddr, uint32_t (&r)[16])
-{
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
-        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-        : "r"(taddr) : "memory");
-}
-// c != 0 ? a : b without a branch
-__device__ __forceinline__ uint32_t select(uint32_t a, uint32_t b, int c)
-{
-    uint32_t d;
-    asm("{\n\t.reg .pred p;\n\tsetp.ne.s32 p, %3, 0;\n\tselp.b32 %0, %1, %2, p;\n\t}" : "=r"(d) : "r"(a), "r"(b), "r"(c));
-    return d;
-}
-__device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
-
-// 16 consecutive fp32 columns of this thread's TMEM lane
-__device__ __forceinline__ void tmem_load16(uint32_t taddr, float (&v)[16])
-{
-    uint32_t r[16];
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
-        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-        : "r"(taddr) : "memory");
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
-}
-
-// shared-memory matrix descriptor, no swizzle, K-major (cute::UMMA::SmemDescriptor, version 1):
-//   LBO = bytes between the two K core matrices of one MMA, SBO = bytes between 8-row groups
-__device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t lbo, uint32_t sbo)
-{
-    return static_cast<uint64_t>((addr & 0x3FFFFu) >> 4) | static_cast<uint64_t>(lbo >> 4) << 16 |
-           static_cast<uint64_t>(sbo >> 4) << 32 | 1ull << 46;
-}
-// instruction descriptor (cute::UMMA::InstrDescriptor): D f32, A/B bf16, both K-major, M = 128
-__host__ __device__ constexpr uint32_t instr_desc(int n) { return 1u << 4 | 1u << 7 | 1u << 10 | static_cast<uint32_t>(n >> 3) << 17 | (128u >> 4) << 24; }
+using namespace ahk::tc; // inline-PTX wrappers: ahk_tc.cuh
 
 // ------------------------------------------------------------------------------------------------ A gathers
 __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi)
@@ -465,7 +372,6 @@ __device__ __forceinline__ uint4 load_stream(const uint8_t *p)
     asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
     return v;
 }
-__device__ __forceinline__ void mbar_arrive(uint64_t *bar) { asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(bar)) : "memory"); }
 
 __global__ void __launch_bounds__(c1::kCta, 1) conv1_kernel(Args a)
 {
@@ -1062,16 +968,6 @@ __device__ __forceinline__ void tmem_store16(uint32_t taddr, const uint32_t (&r)
 }
 // 4 uint8 -> 4 fp16 denormals (v * 2^-24, exact): zero-extended bytes
 __device__ __forceinline__ uint2 u8x4_to_f16x4_denormal(uint32_t w) { return make_uint2(__byte_perm(w, 0u, 0x4140), __byte_perm(w, 0u, 0x4342)); }
-// mbarrier wait that lets the hardware suspend the thread for up to ~1 us per try instead of spinning through the issue slots
-__device__ __forceinline__ void mbar_wait_sleep(uint64_t *bar, uint32_t parity)
-{
-    asm volatile(
-        "{\n\t.reg .pred done;\n\t"
-        "WAIT_%=:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 done, [%0], %1, %2;\n\t"
-        "@!done bra WAIT_%=;\n\t}"
-        :: "r"(smem_u32(bar)), "r"(parity), "r"(1000) : "memory");
-}
 __device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
 // kDenormal: pixels as fp16 DENORMALS (bit pattern 0x00vv = v * 2^-24): one PRMT per two pixels, the 2^24 goes to the epilogue
@@ -1597,6 +1493,16 @@ template <int L> __global__ void __launch_bounds__(256) pack_b_kernel(DevWeights
     }
 }
 
+// the same folded weights as a plain [N][K] bf16 matrix (the B operand of the TMA-fed GEMM, ahk_gemm.cuh)
+template <int L> __global__ void __launch_bounds__(256) pack_nk_kernel(DevWeights w, uint16_t *__restrict__ out, int k_total, int n_total)
+{
+    const int total = k_total * n_total;
+    for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
+        const int n = idx % n_total, k = idx / n_total; // consecutive threads: consecutive columns of the Keras matrix
+        out[static_cast<size_t>(n) * k_total + k] = dev_bf16(folded<L>(w, k, n));
+    }
+}
+
 // biases: layer 0 conv1 b - sum(W) (normalisation folded), 1..3 b + sum(W * BN shift of the input channel), 4, 5 copies
 __global__ void __launch_bounds__(128) fold_bias_kernel(DevWeights w, float *b0, float *b1, float *b2, float *b3, float *b4, float *b5)
 {
@@ -1699,6 +1605,15 @@ std::vector<uint16_t> pack_b(const std::vector<float> &w, int k_total, int n_rea
 }
 
 
+// W: [K][n_real] row-major (fp32, already folded) -> plain [n_real][K] bf16 (the B operand of the TMA-fed GEMM)
+std::vector<uint16_t> pack_nk(const std::vector<float> &w, int k_total, int n_real)
+{
+    std::vector<uint16_t> out(static_cast<size_t>(k_total) * n_real);
+    for (int k = 0; k < k_total; ++k)
+        for (int n = 0; n < n_real; ++n) out[static_cast<size_t>(n) * k_total + k] = to_bf16(w[static_cast<size_t>(k) * n_real + n]);
+    return out;
+}
+
 // conv1, Toeplitz form: W [576][5] folded (k = plane*64 + ky*8 + kx) -> 27 blocks (plane, class) of the K-major canonical
 // B operand [K = 16][N = 144]: element (n, k) at (k/8) * 2304 + (n/8) * 128 + (n%8) * 16 + (k%8) * 2 bytes;
 // n = kv*48 + phase*16 + j*5 + channel holds W[plane][ky = class + 3 kv][kx = k - (phase + 3j)][channel]
@@ -1772,6 +1687,11 @@ struct ahk_policy {
     __nv_bfloat16 *gimg = nullptr, *ga1 = nullptr, *ga2 = nullptr, *ga3 = nullptr, *ga4 = nullptr, *gh1 = nullptr;
     int sms = 148;
     bool legacy_conv = false; // A/B switch AHK_CONV23=tile: conv2/conv3 through layer_kernel instead of conv_ws_kernel
+    // conv2, conv3, dense1, dense2 on the TMA-fed GEMM (ahk_gemm.cuh; the default; AHK_GEMM=gather selects the cp.async /
+    // register-gather kernels): weights as plain [N][K] bf16 matrices, tensor maps over them and over the activations
+    bool tma_gemm = true, tma_conv2 = false;
+    uint16_t *wn[5] = {};    // [1] conv2 32 x 128, [2] conv3 64 x 512, [3] dense1 512 x 4096, [4] dense2 512 x 512
+    CUtensorMap tm_w[5], tm_a[5];
     __nv_bfloat16 *act1 = nullptr, *act2 = nullptr, *act3 = nullptr, *h1 = nullptr, *h2 = nullptr;
     uint64_t launches = 0;
 };
@@ -1798,6 +1718,13 @@ int upload(const std::vector<uint16_t> &w, const std::vector<float> &b, uint16_t
     POL_CUDA(cudaMemcpy(*wd, w.data(), w.size() * 2, cudaMemcpyHostToDevice));
     if (!*bd) POL_CUDA(cudaMalloc(bd, b.size() * 4));
     POL_CUDA(cudaMemcpy(*bd, b.data(), b.size() * 4, cudaMemcpyHostToDevice));
+    return AHK_OK;
+}
+
+int upload_nk(const std::vector<uint16_t> &w, uint16_t **wd)
+{
+    if (!*wd) POL_CUDA(cudaMalloc(wd, w.size() * 2));
+    POL_CUDA(cudaMemcpy(*wd, w.data(), w.size() * 2, cudaMemcpyHostToDevice));
     return AHK_OK;
 }
 
@@ -1854,6 +1781,7 @@ static int load_rgb_weights(ahk_policy *p, const ahk_policy_weights *w)
             bf[o] = w->conv2_b[o] + static_cast<float>(add);
         }
         rc = upload(pack_b(wf, 128, 32, 32, 1), bf, &p->w[1], &p->b[1]);
+        if (rc == AHK_OK) rc = upload_nk(pack_nk(wf, 128, 32), &p->wn[1]);
     }
     if (rc == AHK_OK) { // conv3: k = (ky*4+kx)*32 + c, BN2 folded
         std::vector<float> wf(512 * 64), bf(64);
@@ -1867,6 +1795,7 @@ static int load_rgb_weights(ahk_policy *p, const ahk_policy_weights *w)
             bf[o] = w->conv3_b[o] + static_cast<float>(add);
         }
         rc = upload(pack_b(wf, 512, 64, 64, 1), bf, &p->w[2], &p->b[2]);
+        if (rc == AHK_OK) rc = upload_nk(pack_nk(wf, 512, 64), &p->wn[2]);
     }
     if (rc == AHK_OK) { // dense1: Keras flatten index f = c*64 + pixel; ours k = pixel*64 + c; BN3 folded
         std::vector<float> wf(static_cast<size_t>(4096) * 512), bf(512);
@@ -1878,10 +1807,12 @@ static int load_rgb_weights(ahk_policy *p, const ahk_policy_weights *w)
         }
         for (int o = 0; o < 512; ++o) bf[o] = w->dense1_b[o] + static_cast<float>(add[o]);
         rc = upload(pack_b(wf, 4096, 512, 256, 2), bf, &p->w[3], &p->b[3]);
+        if (rc == AHK_OK) rc = upload_nk(pack_nk(wf, 4096, 512), &p->wn[3]);
     }
     if (rc == AHK_OK) {
         std::vector<float> wf(w->dense2_w, w->dense2_w + 512 * 512), bf(w->dense2_b, w->dense2_b + 512);
         rc = upload(pack_b(wf, 512, 512, 256, 2), bf, &p->w[4], &p->b[4]);
+        if (rc == AHK_OK) rc = upload_nk(pack_nk(wf, 512, 512), &p->wn[4]);
     }
     if (rc == AHK_OK) {
         std::vector<float> wf(w->out_w, w->out_w + 512 * 10), bf(16, 0.0f);
@@ -1916,6 +1847,26 @@ int ahk_policy_create(int device, int max_batch, const ahk_policy_weights *w, ah
         if (err == cudaSuccess) err = cudaMalloc(&p->act3, nb * 4096 * 2);
         if (err == cudaSuccess) err = cudaMalloc(&p->h1, nb * 512 * 2);
         if (err == cudaSuccess) err = cudaMalloc(&p->h2, nb * 512 * 2);
+    }
+    if (const char *sw = getenv("AHK_GEMM")) { p->tma_gemm = strcmp(sw, "gather") != 0; p->tma_conv2 = strcmp(sw, "tma2") == 0; }
+    if (rc == AHK_OK && err == cudaSuccess) { // tensor maps of the TMA-fed GEMM layers (ahk_gemm.cuh): weights [N][K], activations as im2col views
+        namespace tg = ahk::tg;
+        err = tg::matrix_map(&p->tm_w[1], p->wn[1], 32, 128, 32, 32, 64);
+        if (err == cudaSuccess) err = tg::matrix_map(&p->tm_w[2], p->wn[2], 64, 512, 64, 64);
+        if (err == cudaSuccess) err = tg::matrix_map(&p->tm_w[3], p->wn[3], 512, 4096, 64, 256);
+        if (err == cudaSuccess) err = tg::matrix_map(&p->tm_w[4], p->wn[4], 512, 512, 64, 256);
+        if (err == cudaSuccess) { // conv2 reads act1 [sample][41 x 41][8]: element (tap offset + 4 pixels x 8 channels), x2, y2 (stride 2 pixels / rows), sample
+            const unsigned long long dims[4] = {static_cast<unsigned long long>(kP1) * kAct1C, kC2, kC2, nb}, strides[3] = {2 * kAct1C * 2, 2 * kC1 * kAct1C * 2, static_cast<unsigned long long>(kP1) * kAct1C * 2};
+            const unsigned box[4] = {32, kC2, 6, 1};
+            err = tg::encode_bf16_map(&p->tm_a[1], p->act1, 4, dims, strides, box, 64);
+        }
+        if (err == cudaSuccess) { // conv3 reads act2 [sample][19 x 19][32]: element (tap offset + 2 pixels x 32 channels), x3, y3, sample
+            const unsigned long long dims[4] = {static_cast<unsigned long long>(kP2) * 32, kC3, kC3, nb}, strides[3] = {2 * 32 * 2, 2 * kC2 * 32 * 2, static_cast<unsigned long long>(kP2) * 32 * 2};
+            const unsigned box[4] = {64, kC3, kC3, 2};
+            err = tg::encode_bf16_map(&p->tm_a[2], p->act2, 4, dims, strides, box, 128);
+        }
+        if (err == cudaSuccess) err = tg::matrix_map(&p->tm_a[3], p->act3, nb, 4096, 64, 128);
+        if (err == cudaSuccess) err = tg::matrix_map(&p->tm_a[4], p->h1, nb, 512, 64, 128);
     }
     if (rc != AHK_OK || err != cudaSuccess) {
         ahk_policy_destroy(p);
@@ -1958,9 +1909,13 @@ int ahk_policy_set_weights_dev(ahk_policy *p, const ahk_policy_weights *w_dev, v
     pack_b_kernel<3><<<p->sms * 8, 256, 0, s>>>(w, p->w[3], 4096, 256, 2);
     pack_b_kernel<4><<<p->sms * 4, 256, 0, s>>>(w, p->w[4], 512, 256, 2);
     pack_b_kernel<5><<<32, 256, 0, s>>>(w, p->w[5], 512, 16, 1);
+    pack_nk_kernel<1><<<16, 256, 0, s>>>(w, p->wn[1], 128, 32);
+    pack_nk_kernel<2><<<128, 256, 0, s>>>(w, p->wn[2], 512, 64);
+    pack_nk_kernel<3><<<p->sms * 8, 256, 0, s>>>(w, p->wn[3], 4096, 512);
+    pack_nk_kernel<4><<<p->sms * 4, 256, 0, s>>>(w, p->wn[4], 512, 512);
     fold_bias_kernel<<<dim3(4, 6), 128, 0, s>>>(w, p->b[0], p->b[1], p->b[2], p->b[3], p->b[4], p->b[5]);
     POL_CUDA(cudaGetLastError());
-    p->launches += 8;
+    p->launches += 12;
     return AHK_OK;
 }
 
@@ -2057,6 +2012,7 @@ void ahk_policy_destroy(ahk_policy *p)
     cudaSetDevice(p->device);
     for (int i = 0; i < 6; ++i) { if (p->w[i]) cudaFree(p->w[i]); if (p->b[i]) cudaFree(p->b[i]); }
     if (p->w1t) cudaFree(p->w1t);
+    for (int i = 0; i < 5; ++i) if (p->wn[i]) cudaFree(p->wn[i]);
     if (p->w1p) cudaFree(p->w1p);
     for (int i = 0; i < 7; ++i) if (p->ev[i]) cudaEventDestroy(p->ev[i]);
     for (int i = 0; i < 6; ++i) { if (p->gw[i]) cudaFree(p->gw[i]); if (p->gb[i]) cudaFree(p->gb[i]); }
@@ -2125,18 +2081,41 @@ static int policy_forward(ahk_policy *p, const ahk_stack &stack, float *logits, 
         POL_CUDA(p->conv1_smem ? launch_conv1p(a, items < p->sms ? items : p->sms, s) : launch_conv1t(a, items < p->sms ? items : p->sms, !p->conv1_normal, s));
     }
     if (timed) POL_CUDA(cudaEventRecord(p->ev[1], s));
-    a.in = p->act1; a.weights = reinterpret_cast<const uint4 *>(p->w[1]); a.bias = p->b[1]; a.out = p->act2; a.m_total = n * kP2;
-    POL_CUDA(p->legacy_conv ? launch<kConv2>(a, tiles(static_cast<long long>(n) * kP2), 1, p->sms, s) : launch_ws<kConv2>(a, tiles(static_cast<long long>(n) * kP2), p->sms, s));
-    if (timed) POL_CUDA(cudaEventRecord(p->ev[2], s));
-    a.in = p->act2; a.weights = reinterpret_cast<const uint4 *>(p->w[2]); a.bias = p->b[2]; a.out = p->act3; a.m_total = n * kP3;
-    POL_CUDA(p->legacy_conv ? launch<kConv3>(a, tiles(static_cast<long long>(n) * kP3), 1, p->sms, s) : launch_ws<kConv3>(a, tiles(static_cast<long long>(n) * kP3), p->sms, s));
-    if (timed) POL_CUDA(cudaEventRecord(p->ev[3], s));
-    a.in = p->act3; a.weights = reinterpret_cast<const uint4 *>(p->w[3]); a.bias = p->b[3]; a.out = p->h1; a.m_total = n;
-    POL_CUDA(launch<kDense1>(a, tiles(n), 2, p->sms, s));
-    if (timed) POL_CUDA(cudaEventRecord(p->ev[4], s));
-    a.in = p->h1; a.weights = reinterpret_cast<const uint4 *>(p->w[4]); a.bias = p->b[4]; a.out = p->h2; a.m_total = n;
-    POL_CUDA(launch<kDense2>(a, tiles(n), 2, p->sms, s));
-    if (timed) POL_CUDA(cudaEventRecord(p->ev[5], s));
+    if (p->tma_gemm) {
+        namespace tg = ahk::tg;
+        tg::Args g{};
+        g.k_splits = 1; g.m_total = n; g.scale = 1.0f;
+        // conv2 stays on the cp.async pipeline: as a tensor-map im2col its overlapping 64-byte windows read every act1 pixel
+        // four times over L2 -> SM (1.2 GB per 8192 samples: 0.25 ms against 0.155; AHK_GEMM=tma2 runs it for the record)
+        a.in = p->act1; a.weights = reinterpret_cast<const uint4 *>(p->w[1]); a.bias = p->b[1]; a.out = p->act2; a.m_total = n * kP2;
+        g.tiles_m = n * 4; g.blocks_n = 1; g.k_chunks = 4; g.n_valid = 32; g.bias = p->b[1]; g.out_bf16 = p->act2; g.out_pitch = 32;
+        if (p->tma_conv2) POL_CUDA((tg::launch<32, 64, tg::kConv2, false, tg::kBiasReluBf16, 8, 4>(g, p->tm_a[1], p->tm_w[1], p->sms, s)));
+        else POL_CUDA(launch_ws<kConv2>(a, tiles(static_cast<long long>(n) * kP2), p->sms, s));
+        if (timed) POL_CUDA(cudaEventRecord(p->ev[2], s));
+        g.tiles_m = (n + 1) / 2; g.k_chunks = 8; g.n_valid = 64; g.bias = p->b[2]; g.out_bf16 = p->act3; g.out_pitch = 64;
+        g.blocks_n = 1;
+        POL_CUDA((tg::launch<64, 128, tg::kConv3, false, tg::kBiasReluBf16, 6, 8>(g, p->tm_a[2], p->tm_w[2], p->sms, s)));
+        if (timed) POL_CUDA(cudaEventRecord(p->ev[3], s));
+        g.tiles_m = tiles(n); g.blocks_n = 2; g.k_chunks = 64; g.n_valid = 256; g.bias = p->b[3]; g.out_bf16 = p->h1; g.out_pitch = 512;
+        POL_CUDA((tg::launch<256, 128, tg::kLinear, false, tg::kBiasReluBf16, 4>(g, p->tm_a[3], p->tm_w[3], p->sms, s)));
+        if (timed) POL_CUDA(cudaEventRecord(p->ev[4], s));
+        g.k_chunks = 8; g.bias = p->b[4]; g.out_bf16 = p->h2;
+        POL_CUDA((tg::launch<256, 128, tg::kLinear, false, tg::kBiasReluBf16, 4>(g, p->tm_a[4], p->tm_w[4], p->sms, s)));
+        if (timed) POL_CUDA(cudaEventRecord(p->ev[5], s));
+    } else {
+        a.in = p->act1; a.weights = reinterpret_cast<const uint4 *>(p->w[1]); a.bias = p->b[1]; a.out = p->act2; a.m_total = n * kP2;
+        POL_CUDA(p->legacy_conv ? launch<kConv2>(a, tiles(static_cast<long long>(n) * kP2), 1, p->sms, s) : launch_ws<kConv2>(a, tiles(static_cast<long long>(n) * kP2), p->sms, s));
+        if (timed) POL_CUDA(cudaEventRecord(p->ev[2], s));
+        a.in = p->act2; a.weights = reinterpret_cast<const uint4 *>(p->w[2]); a.bias = p->b[2]; a.out = p->act3; a.m_total = n * kP3;
+        POL_CUDA(p->legacy_conv ? launch<kConv3>(a, tiles(static_cast<long long>(n) * kP3), 1, p->sms, s) : launch_ws<kConv3>(a, tiles(static_cast<long long>(n) * kP3), p->sms, s));
+        if (timed) POL_CUDA(cudaEventRecord(p->ev[3], s));
+        a.in = p->act3; a.weights = reinterpret_cast<const uint4 *>(p->w[3]); a.bias = p->b[3]; a.out = p->h1; a.m_total = n;
+        POL_CUDA(launch<kDense1>(a, tiles(n), 2, p->sms, s));
+        if (timed) POL_CUDA(cudaEventRecord(p->ev[4], s));
+        a.in = p->h1; a.weights = reinterpret_cast<const uint4 *>(p->w[4]); a.bias = p->b[4]; a.out = p->h2; a.m_total = n;
+        POL_CUDA(launch<kDense2>(a, tiles(n), 2, p->sms, s));
+        if (timed) POL_CUDA(cudaEventRecord(p->ev[5], s));
+    }
     a.in = p->h2; a.weights = reinterpret_cast<const uint4 *>(p->w[5]); a.bias = p->b[5]; a.out = nullptr; a.logits = logits; a.action = action; a.m_total = n;
     POL_CUDA(launch<kOut>(a, tiles(n), 1, p->sms, s));
     if (timed) POL_CUDA(cudaEventRecord(p->ev[6], s));

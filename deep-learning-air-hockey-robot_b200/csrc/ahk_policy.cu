@@ -1504,9 +1504,10 @@ template <int L> __global__ void __launch_bounds__(256) pack_nk_kernel(DevWeight
 }
 
 // biases: layer 0 conv1 b - sum(W) (normalisation folded), 1..3 b + sum(W * BN shift of the input channel), 4, 5 copies
-__global__ void __launch_bounds__(128) fold_bias_kernel(DevWeights w, float *b0, float *b1, float *b2, float *b3, float *b4, float *b5)
+__global__ void __launch_bounds__(128) fold_bias_kernel(DevWeights w, float *b0, float *b1, float *b2, float *b3, float *b4, float *b5, int only = -1)
 {
     const int layer = blockIdx.y, o = blockIdx.x * blockDim.x + threadIdx.x;
+    if (only >= 0 && layer != only) return;
     if (layer == 0) {
         if (o >= 16) return;
         double sum = 0.0;
@@ -1574,6 +1575,49 @@ __global__ void __launch_bounds__(256) pack_conv1p_kernel(DevWeights w, uint16_t
     if (ky >= 8) return;
     const size_t at = static_cast<size_t>((plane * 3 + cls) * 3 + ph) * (16 * N) + (k / 8) * (8 * N) + (n / 8) * 64 + (n % 8) * 8 + (k % 8);
     out[at] = __half_as_ushort(__float2half_rn(w.f[0][((ky * 8 + kx) * 9 + plane) * 5 + ch]));
+}
+
+// ------------------------------------------------------------------------------------------------ batch statistics
+// Training-mode BatchNormalization (model.fit, rl_agents.py:189,276) normalises with the batch's own per-channel mean and
+// (biased) variance of the layer's post-ReLU output.  act: bf16 [rows][kCPad]; sums: double [2][kCPad] (zeroed).
+template <int kCPad>
+__global__ void __launch_bounds__(256) bn_sums_kernel(const __nv_bfloat16 *__restrict__ act, long long rows, double *__restrict__ sums)
+{
+    constexpr int kGroups = kCPad / 8; // 16-byte vectors per row
+    __shared__ float s_part[256][17];
+    const int tid = threadIdx.x, grp = tid % kGroups;
+    float sum[8] = {0, 0, 0, 0, 0, 0, 0, 0}, sq[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    const long long row_stride = static_cast<long long>(gridDim.x) * (256 / kGroups);
+    for (long long row = static_cast<long long>(blockIdx.x) * (256 / kGroups) + tid / kGroups; row < rows; row += row_stride) {
+        const uint4 v = __ldg(reinterpret_cast<const uint4 *>(act + row * kCPad + grp * 8));
+        const uint32_t wds[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float lo = __uint_as_float(wds[j] << 16), hi = __uint_as_float(wds[j] & 0xFFFF0000u);
+            sum[2 * j] += lo; sq[2 * j] += lo * lo;
+            sum[2 * j + 1] += hi; sq[2 * j + 1] += hi * hi;
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { s_part[tid][j] = sum[j]; s_part[tid][8 + j] = sq[j]; }
+    __syncthreads();
+    if (tid < kCPad * 2) { // one thread per (channel, sum | sum of squares)
+        const int c = tid % kCPad, which = tid / kCPad, g = c / 8, j = c % 8;
+        double acc = 0.0;
+        for (int t = g; t < 256; t += kGroups) acc += static_cast<double>(s_part[t][which * 8 + j]);
+        atomicAdd(sums + which * kCPad + c, acc);
+    }
+}
+// mean / biased variance of the batch -> stats[0 .. c) and stats[kStatStride .. ), and the sums cleared for the next use
+__global__ void bn_finalize_kernel(double *__restrict__ sums, int c_pad, long long count, float *__restrict__ mean, float *__restrict__ var)
+{
+    const int c = threadIdx.x;
+    if (c >= c_pad) return;
+    const double m = sums[c] / static_cast<double>(count), v = sums[c_pad + c] / static_cast<double>(count) - m * m;
+    mean[c] = static_cast<float>(m);
+    var[c] = static_cast<float>(v > 0.0 ? v : 0.0);
+    sums[c] = 0.0;
+    sums[c_pad + c] = 0.0;
 }
 
 // ------------------------------------------------------------------------------------------------ host: fold + pack
@@ -1693,6 +1737,7 @@ struct ahk_policy {
     uint16_t *wn[5] = {};    // [1] conv2 32 x 128, [2] conv3 64 x 512, [3] dense1 512 x 4096, [4] dense2 512 x 512
     CUtensorMap tm_w[5], tm_a[5];
     __nv_bfloat16 *act1 = nullptr, *act2 = nullptr, *act3 = nullptr, *h1 = nullptr, *h2 = nullptr;
+    double *bn_sums = nullptr; // ahk_policy_forward_train: [2][64] running sums of the layer being normalised
     uint64_t launches = 0;
 };
 
@@ -2013,12 +2058,69 @@ void ahk_policy_destroy(ahk_policy *p)
     for (int i = 0; i < 6; ++i) { if (p->w[i]) cudaFree(p->w[i]); if (p->b[i]) cudaFree(p->b[i]); }
     if (p->w1t) cudaFree(p->w1t);
     for (int i = 0; i < 5; ++i) if (p->wn[i]) cudaFree(p->wn[i]);
+    if (p->bn_sums) cudaFree(p->bn_sums);
     if (p->w1p) cudaFree(p->w1p);
     for (int i = 0; i < 7; ++i) if (p->ev[i]) cudaEventDestroy(p->ev[i]);
     for (int i = 0; i < 6; ++i) { if (p->gw[i]) cudaFree(p->gw[i]); if (p->gb[i]) cudaFree(p->gb[i]); }
     cudaFree(p->gimg); cudaFree(p->ga1); cudaFree(p->ga2); cudaFree(p->ga3); cudaFree(p->ga4); cudaFree(p->gh1);
     cudaFree(p->act1); cudaFree(p->act2); cudaFree(p->act3); cudaFree(p->h1); cudaFree(p->h2);
     delete p;
+}
+
+// One layer of the 'rgb' network on n samples (a: frames / ring geometry filled in): 0 conv1 ... 5 out
+static int rgb_layer(ahk_policy *p, Args a, int layer, float *logits, uint8_t *action, cudaStream_t s)
+{
+    namespace tg = ahk::tg;
+    const int n = a.n;
+    auto tiles = [](long long rows) { return static_cast<int>((rows + kBM - 1) / kBM); };
+    tg::Args g{};
+    g.k_splits = 1; g.m_total = n; g.scale = 1.0f;
+    switch (layer) {
+    case 0:
+        a.bias = p->b[0]; a.out = p->act1; a.m_total = kP1;
+        if (p->conv1_n144) {
+            a.weights = reinterpret_cast<const uint4 *>(p->w1t);
+            const int items = n * c1::kTilesPerSample;
+            POL_CUDA(launch_conv1(a, items < p->sms ? items : p->sms, s));
+        } else {
+            a.weights = reinterpret_cast<const uint4 *>(p->w1p);
+            const int items = n * 2;
+            POL_CUDA(p->conv1_smem ? launch_conv1p(a, items < p->sms ? items : p->sms, s) : launch_conv1t(a, items < p->sms ? items : p->sms, !p->conv1_normal, s));
+        }
+        return AHK_OK;
+    case 1:
+        // conv2 stays on the cp.async pipeline: as a tensor-map im2col its overlapping 64-byte windows read every act1 pixel
+        // four times over L2 -> SM (1.2 GB per 8192 samples: 0.21-0.25 ms against 0.155; AHK_GEMM=tma2 runs it for the record)
+        a.in = p->act1; a.weights = reinterpret_cast<const uint4 *>(p->w[1]); a.bias = p->b[1]; a.out = p->act2; a.m_total = n * kP2;
+        g.tiles_m = n * 4; g.blocks_n = 1; g.k_chunks = 4; g.n_valid = 32; g.bias = p->b[1]; g.out_bf16 = p->act2; g.out_pitch = 32;
+        if (p->tma_gemm && p->tma_conv2) POL_CUDA((tg::launch<32, 64, tg::kConv2, false, tg::kBiasReluBf16, 8, 4>(g, p->tm_a[1], p->tm_w[1], p->sms, s)));
+        else if (p->legacy_conv) POL_CUDA(launch<kConv2>(a, tiles(static_cast<long long>(n) * kP2), 1, p->sms, s));
+        else POL_CUDA(launch_ws<kConv2>(a, tiles(static_cast<long long>(n) * kP2), p->sms, s));
+        return AHK_OK;
+    case 2:
+        a.in = p->act2; a.weights = reinterpret_cast<const uint4 *>(p->w[2]); a.bias = p->b[2]; a.out = p->act3; a.m_total = n * kP3;
+        g.tiles_m = (n + 1) / 2; g.blocks_n = 1; g.k_chunks = 8; g.n_valid = 64; g.bias = p->b[2]; g.out_bf16 = p->act3; g.out_pitch = 64;
+        if (p->tma_gemm) POL_CUDA((tg::launch<64, 128, tg::kConv3, false, tg::kBiasReluBf16, 6, 8>(g, p->tm_a[2], p->tm_w[2], p->sms, s)));
+        else if (p->legacy_conv) POL_CUDA(launch<kConv3>(a, tiles(static_cast<long long>(n) * kP3), 1, p->sms, s));
+        else POL_CUDA(launch_ws<kConv3>(a, tiles(static_cast<long long>(n) * kP3), p->sms, s));
+        return AHK_OK;
+    case 3:
+        a.in = p->act3; a.weights = reinterpret_cast<const uint4 *>(p->w[3]); a.bias = p->b[3]; a.out = p->h1; a.m_total = n;
+        g.tiles_m = tiles(n); g.blocks_n = 2; g.k_chunks = 64; g.n_valid = 256; g.bias = p->b[3]; g.out_bf16 = p->h1; g.out_pitch = 512;
+        if (p->tma_gemm) POL_CUDA((tg::launch<256, 128, tg::kLinear, false, tg::kBiasReluBf16, 4>(g, p->tm_a[3], p->tm_w[3], p->sms, s)));
+        else POL_CUDA(launch<kDense1>(a, tiles(n), 2, p->sms, s));
+        return AHK_OK;
+    case 4:
+        a.in = p->h1; a.weights = reinterpret_cast<const uint4 *>(p->w[4]); a.bias = p->b[4]; a.out = p->h2; a.m_total = n;
+        g.tiles_m = tiles(n); g.blocks_n = 2; g.k_chunks = 8; g.n_valid = 256; g.bias = p->b[4]; g.out_bf16 = p->h2; g.out_pitch = 512;
+        if (p->tma_gemm) POL_CUDA((tg::launch<256, 128, tg::kLinear, false, tg::kBiasReluBf16, 4>(g, p->tm_a[4], p->tm_w[4], p->sms, s)));
+        else POL_CUDA(launch<kDense2>(a, tiles(n), 2, p->sms, s));
+        return AHK_OK;
+    default:
+        a.in = p->h2; a.weights = reinterpret_cast<const uint4 *>(p->w[5]); a.bias = p->b[5]; a.out = nullptr; a.logits = logits; a.action = action; a.m_total = n;
+        POL_CUDA(launch<kOut>(a, tiles(n), 1, p->sms, s));
+        return AHK_OK;
+    }
 }
 
 static int policy_forward(ahk_policy *p, const ahk_stack &stack, float *logits, uint8_t *action, void *stream, bool timed)
@@ -2069,57 +2171,98 @@ static int policy_forward(ahk_policy *p, const ahk_stack &stack, float *logits, 
         return AHK_OK;
     }
     if (timed) POL_CUDA(cudaEventRecord(p->ev[0], s));
-
-    a.frames = frames; a.bias = p->b[0]; a.out = p->act1; a.m_total = kP1;
-    if (p->conv1_n144) {
-        a.weights = reinterpret_cast<const uint4 *>(p->w1t);
-        const int items = n * c1::kTilesPerSample;
-        POL_CUDA(launch_conv1(a, items < p->sms ? items : p->sms, s));
-    } else {
-        a.weights = reinterpret_cast<const uint4 *>(p->w1p);
-        const int items = n * 2;
-        POL_CUDA(p->conv1_smem ? launch_conv1p(a, items < p->sms ? items : p->sms, s) : launch_conv1t(a, items < p->sms ? items : p->sms, !p->conv1_normal, s));
+    a.frames = frames;
+    for (int layer = 0; layer < 6; ++layer) {
+        if (int rc = rgb_layer(p, a, layer, logits, action, s)) return rc;
+        if (timed) POL_CUDA(cudaEventRecord(p->ev[layer + 1], s));
     }
-    if (timed) POL_CUDA(cudaEventRecord(p->ev[1], s));
-    if (p->tma_gemm) {
-        namespace tg = ahk::tg;
-        tg::Args g{};
-        g.k_splits = 1; g.m_total = n; g.scale = 1.0f;
-        // conv2 stays on the cp.async pipeline: as a tensor-map im2col its overlapping 64-byte windows read every act1 pixel
-        // four times over L2 -> SM (1.2 GB per 8192 samples: 0.25 ms against 0.155; AHK_GEMM=tma2 runs it for the record)
-        a.in = p->act1; a.weights = reinterpret_cast<const uint4 *>(p->w[1]); a.bias = p->b[1]; a.out = p->act2; a.m_total = n * kP2;
-        g.tiles_m = n * 4; g.blocks_n = 1; g.k_chunks = 4; g.n_valid = 32; g.bias = p->b[1]; g.out_bf16 = p->act2; g.out_pitch = 32;
-        if (p->tma_conv2) POL_CUDA((tg::launch<32, 64, tg::kConv2, false, tg::kBiasReluBf16, 8, 4>(g, p->tm_a[1], p->tm_w[1], p->sms, s)));
-        else POL_CUDA(launch_ws<kConv2>(a, tiles(static_cast<long long>(n) * kP2), p->sms, s));
-        if (timed) POL_CUDA(cudaEventRecord(p->ev[2], s));
-        g.tiles_m = (n + 1) / 2; g.k_chunks = 8; g.n_valid = 64; g.bias = p->b[2]; g.out_bf16 = p->act3; g.out_pitch = 64;
-        g.blocks_n = 1;
-        POL_CUDA((tg::launch<64, 128, tg::kConv3, false, tg::kBiasReluBf16, 6, 8>(g, p->tm_a[2], p->tm_w[2], p->sms, s)));
-        if (timed) POL_CUDA(cudaEventRecord(p->ev[3], s));
-        g.tiles_m = tiles(n); g.blocks_n = 2; g.k_chunks = 64; g.n_valid = 256; g.bias = p->b[3]; g.out_bf16 = p->h1; g.out_pitch = 512;
-        POL_CUDA((tg::launch<256, 128, tg::kLinear, false, tg::kBiasReluBf16, 4>(g, p->tm_a[3], p->tm_w[3], p->sms, s)));
-        if (timed) POL_CUDA(cudaEventRecord(p->ev[4], s));
-        g.k_chunks = 8; g.bias = p->b[4]; g.out_bf16 = p->h2;
-        POL_CUDA((tg::launch<256, 128, tg::kLinear, false, tg::kBiasReluBf16, 4>(g, p->tm_a[4], p->tm_w[4], p->sms, s)));
-        if (timed) POL_CUDA(cudaEventRecord(p->ev[5], s));
-    } else {
-        a.in = p->act1; a.weights = reinterpret_cast<const uint4 *>(p->w[1]); a.bias = p->b[1]; a.out = p->act2; a.m_total = n * kP2;
-        POL_CUDA(p->legacy_conv ? launch<kConv2>(a, tiles(static_cast<long long>(n) * kP2), 1, p->sms, s) : launch_ws<kConv2>(a, tiles(static_cast<long long>(n) * kP2), p->sms, s));
-        if (timed) POL_CUDA(cudaEventRecord(p->ev[2], s));
-        a.in = p->act2; a.weights = reinterpret_cast<const uint4 *>(p->w[2]); a.bias = p->b[2]; a.out = p->act3; a.m_total = n * kP3;
-        POL_CUDA(p->legacy_conv ? launch<kConv3>(a, tiles(static_cast<long long>(n) * kP3), 1, p->sms, s) : launch_ws<kConv3>(a, tiles(static_cast<long long>(n) * kP3), p->sms, s));
-        if (timed) POL_CUDA(cudaEventRecord(p->ev[3], s));
-        a.in = p->act3; a.weights = reinterpret_cast<const uint4 *>(p->w[3]); a.bias = p->b[3]; a.out = p->h1; a.m_total = n;
-        POL_CUDA(launch<kDense1>(a, tiles(n), 2, p->sms, s));
-        if (timed) POL_CUDA(cudaEventRecord(p->ev[4], s));
-        a.in = p->h1; a.weights = reinterpret_cast<const uint4 *>(p->w[4]); a.bias = p->b[4]; a.out = p->h2; a.m_total = n;
-        POL_CUDA(launch<kDense2>(a, tiles(n), 2, p->sms, s));
-        if (timed) POL_CUDA(cudaEventRecord(p->ev[5], s));
-    }
-    a.in = p->h2; a.weights = reinterpret_cast<const uint4 *>(p->w[5]); a.bias = p->b[5]; a.out = nullptr; a.logits = logits; a.action = action; a.m_total = n;
-    POL_CUDA(launch<kOut>(a, tiles(n), 1, p->sms, s));
-    if (timed) POL_CUDA(cudaEventRecord(p->ev[6], s));
     p->launches += 6;
+    return AHK_OK;
+}
+
+// model.fit's forward pass: see include/ahk.h
+int ahk_policy_forward_train(ahk_policy *p, const ahk_policy_weights *w_dev, const uint8_t *frames_dev, int n, int head, float *logits_dev,
+                             float *batch_stats_dev, void *stream)
+{
+    if (!p || !w_dev || !frames_dev || !logits_dev || !batch_stats_dev) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_forward_train: NULL argument");
+    if (p->gray) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_forward_train: handle holds the 'gray-diff' network");
+    if (n <= 0 || n > p->max_batch || head < 0 || head > 2) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_forward_train: n must be in [1, max_batch], head in [0, 3)");
+    if (p->conv1_n144 || p->legacy_conv || !p->tma_gemm) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_forward_train: runs on the default kernels only (unset AHK_CONV1 / AHK_CONV23 / AHK_GEMM)");
+    DevWeights w;
+    const float *const *fields = reinterpret_cast<const float *const *>(w_dev);
+    for (int i = 0; i < 24; ++i) {
+        if (!fields[i]) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_forward_train: every weight pointer must be non-NULL");
+        w.f[i] = fields[i];
+    }
+    int prev_device = -1;
+    POL_CUDA(cudaGetDevice(&prev_device));
+    if (prev_device != p->device) POL_CUDA(cudaSetDevice(p->device));
+    struct Restore { int prev, cur; ~Restore() { if (prev != cur) cudaSetDevice(prev); } } restore{prev_device, p->device};
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (!p->bn_sums) {
+        POL_CUDA(cudaMalloc(&p->bn_sums, 2 * 64 * sizeof(double)));
+        POL_CUDA(cudaMemsetAsync(p->bn_sums, 0, 2 * 64 * sizeof(double), s));
+    }
+    // the BatchNorm moving statistics of the weight set are replaced by the batch statistics, layer by layer
+    float *mean = batch_stats_dev, *var = batch_stats_dev + AHK_BN_STATS;
+    w.f[4] = mean; w.f[5] = var; w.f[10] = mean + 8; w.f[11] = var + 8; w.f[16] = mean + 40; w.f[17] = var + 40;
+    Args a{};
+    a.n = n; a.head = head; a.depth = 3; a.frames = frames_dev;
+    const int stat_grid = p->sms * 4;
+    // conv1 (no BatchNorm before it)
+    POL_CUDA(cudaMemsetAsync(p->w1p, 0, static_cast<size_t>(c1p::kWBytes), s));
+    pack_conv1p_kernel<<<(9 * 3 * 3 * 3 * 3 * 5 * 8 + 255) / 256, 256, 0, s>>>(w, p->w1p);
+    fold_bias_kernel<<<dim3(4, 6), 128, 0, s>>>(w, p->b[0], p->b[1], p->b[2], p->b[3], p->b[4], p->b[5], 0);
+    if (int rc = rgb_layer(p, a, 0, nullptr, nullptr, s)) return rc;
+    bn_sums_kernel<8><<<stat_grid, 256, 0, s>>>(p->act1, static_cast<long long>(n) * kP1, p->bn_sums);
+    bn_finalize_kernel<<<1, 64, 0, s>>>(p->bn_sums, 8, static_cast<long long>(n) * kP1, mean, var);
+    // conv2 with BatchNorm 1 (batch statistics) folded in
+    pack_b_kernel<1><<<16, 256, 0, s>>>(w, p->w[1], 128, 32, 1);
+    fold_bias_kernel<<<dim3(4, 6), 128, 0, s>>>(w, p->b[0], p->b[1], p->b[2], p->b[3], p->b[4], p->b[5], 1);
+    if (int rc = rgb_layer(p, a, 1, nullptr, nullptr, s)) return rc;
+    bn_sums_kernel<32><<<stat_grid, 256, 0, s>>>(p->act2, static_cast<long long>(n) * kP2, p->bn_sums);
+    bn_finalize_kernel<<<1, 64, 0, s>>>(p->bn_sums, 32, static_cast<long long>(n) * kP2, mean + 8, var + 8);
+    // conv3
+    pack_nk_kernel<2><<<128, 256, 0, s>>>(w, p->wn[2], 512, 64);
+    fold_bias_kernel<<<dim3(4, 6), 128, 0, s>>>(w, p->b[0], p->b[1], p->b[2], p->b[3], p->b[4], p->b[5], 2);
+    if (int rc = rgb_layer(p, a, 2, nullptr, nullptr, s)) return rc;
+    bn_sums_kernel<64><<<stat_grid, 256, 0, s>>>(p->act3, static_cast<long long>(n) * kP3, p->bn_sums);
+    bn_finalize_kernel<<<1, 64, 0, s>>>(p->bn_sums, 64, static_cast<long long>(n) * kP3, mean + 40, var + 40);
+    // dense layers
+    pack_nk_kernel<3><<<p->sms * 8, 256, 0, s>>>(w, p->wn[3], 4096, 512);
+    pack_nk_kernel<4><<<p->sms * 4, 256, 0, s>>>(w, p->wn[4], 512, 512);
+    pack_b_kernel<5><<<32, 256, 0, s>>>(w, p->w[5], 512, 16, 1);
+    for (int layer = 3; layer < 6; ++layer) fold_bias_kernel<<<dim3(4, 6), 128, 0, s>>>(w, p->b[0], p->b[1], p->b[2], p->b[3], p->b[4], p->b[5], layer);
+    for (int layer = 3; layer < 6; ++layer)
+        if (int rc = rgb_layer(p, a, layer, logits_dev, nullptr, s)) return rc;
+    POL_CUDA(cudaGetLastError());
+    p->launches += 25;
+    return AHK_OK;
+}
+
+__global__ void __launch_bounds__(256) bf16_to_f32_kernel(const __nv_bfloat16 *__restrict__ src, float *__restrict__ dst, size_t count)
+{
+    for (size_t i = blockIdx.x * 256ull + threadIdx.x; i < count; i += gridDim.x * 256ull) dst[i] = __bfloat162float(src[i]);
+}
+
+int ahk_policy_copy_activation(ahk_policy *p, int which, float *dst_dev, size_t count, void *stream)
+{
+    if (!p || !dst_dev || which < 0 || which > 4 || p->gray) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_copy_activation: bad argument");
+    const __nv_bfloat16 *src[5] = {p->act1, p->act2, p->act3, p->h1, p->h2};
+    const size_t per[5] = {static_cast<size_t>(kP1) * kAct1C, static_cast<size_t>(kP2) * 32, 4096, 512, 512};
+    if (count > per[which] * static_cast<size_t>(p->max_batch)) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_copy_activation: count exceeds the buffer");
+    POL_CUDA(cudaSetDevice(p->device));
+    bf16_to_f32_kernel<<<p->sms * 4, 256, 0, static_cast<cudaStream_t>(stream)>>>(src[which], dst_dev, count);
+    POL_CUDA(cudaGetLastError());
+    return AHK_OK;
+}
+
+int ahk_policy_get_activations(ahk_policy *p, ahk_policy_acts *out)
+{
+    if (!p || !out) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_get_activations: NULL argument");
+    if (p->gray) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_get_activations: handle holds the 'gray-diff' network");
+    out->act1 = p->act1; out->act2 = p->act2; out->act3 = p->act3; out->h1 = p->h1; out->h2 = p->h2;
+    out->max_batch = p->max_batch;
     return AHK_OK;
 }
 

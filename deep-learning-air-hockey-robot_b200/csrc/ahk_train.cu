@@ -1,0 +1,631 @@
+// ahk_train.cu — the backward pass and the optimizer step of `model.fit` (ai/reinforcement/rl_agents.py:189,276;
+// compiled at rl_agents.py:111,170 and ai/supervised/keras/models.py:119), hand-written: no autograd, no cuDNN, no cuBLAS.
+//
+// Forward (training mode): ahk_policy_forward_train (ahk_policy.cu) — the tcgen05 forward kernels with each BatchNorm's
+// BATCH statistics folded into the next layer.  It leaves r1 = relu(conv1), r2, r3, h1, h2 (bf16) in the policy handle.
+// Backward, from d loss / d logits (ahk_rl_ddqn_targets / ahk_rl_pg_targets), layer by layer:
+//   * dense2 / dense1 data gradients: the TMA-fed tcgen05 GEMM (ahk_gemm.cuh) on bf16 copies, ReLU mask in its epilogue;
+//   * every other GEMM-shaped gradient (weight gradients, whose reduction runs over batch x pixels; the transposed
+//     convolutions, split by the parity of the input pixel so that no tap is a zero) on `simt_gemm`, a register-tiled
+//     float32 CUDA-core GEMM whose operands are FUNCTORS: im2col, the BatchNorm affine map, the Keras layouts and the
+//     (x - 128) / 128 of the uint8 frames are index arithmetic inside the loads, nothing is materialised;
+//   * conv1's weight gradient (47 % of the network's MACs, uint8 input, 5 output channels): `conv1_wgrad_kernel`;
+//   * BatchNorm backward with batch statistics (two passes: per-channel sums, then the elementwise map + ReLU mask);
+//   * `sgd_step_kernel` / `adam_step_kernel`: one launch over the flat parameter vector — L2 kernel regulariser
+//     (models.py:17), clipnorm on the global norm, learning-rate decay, momentum / Adam moments, BatchNorm moving statistics.
+// Layouts are the Keras ones (conv [kh][kw][cin][cout], dense [in][out]) so the flat vector IS model.get_weights().
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/ahk.h"
+#include "ahk_gemm.cuh"
+#include "ahk_kernels.cuh"
+
+namespace ahk {
+namespace train {
+
+constexpr int kP1 = 41 * 41, kP2 = 19 * 19, kP3 = 64;
+constexpr float kBnEps = 1e-3f; // Keras BatchNormalization default (models.py:26)
+
+__device__ __forceinline__ float bf(const __nv_bfloat16 *p, long long i) { return __bfloat162float(p[i]); }
+
+// ------------------------------------------------------------------------------------------------ functor GEMM
+// C[m][n] (+)= sum_k A(m, k) * B(k, n).  F provides  float a(int m, int k), float b(int k, int n), void store(int m, int n, float v, bool atomic)
+// and the flags kAAlongM / kBAlongN: which index consecutive threads walk when a tile is staged (the contiguous one of the source).
+template <class F, int TM, int TN, int RM, int RN>
+__global__ void __launch_bounds__((TM / RM) * (TN / RN)) simt_gemm(F f, int M, int N, int K, int k_per_split)
+{
+    constexpr int TK = 16, kThreads = (TM / RM) * (TN / RN);
+    __shared__ float s_a[TK][TM + 4], s_b[TK][TN + 4];
+    const int tid = threadIdx.x, tn = tid % (TN / RN), tm = tid / (TN / RN);
+    const int m0 = blockIdx.y * TM, n0 = blockIdx.x * TN;
+    const int k_begin = blockIdx.z * k_per_split, k_end = min(K, k_begin + k_per_split);
+    float acc[RM][RN];
+#pragma unroll
+    for (int i = 0; i < RM; ++i)
+#pragma unroll
+        for (int j = 0; j < RN; ++j) acc[i][j] = 0.0f;
+    for (int k0 = k_begin; k0 < k_end; k0 += TK) {
+#pragma unroll
+        for (int e = tid; e < TM * TK; e += kThreads) {
+            const int mm = F::kAAlongM ? e % TM : e / TK, kk = F::kAAlongM ? e / TM : e % TK;
+            s_a[kk][mm] = (m0 + mm < M && k0 + kk < k_end) ? f.a(m0 + mm, k0 + kk) : 0.0f;
+        }
+#pragma unroll
+        for (int e = tid; e < TN * TK; e += kThreads) {
+            const int nn = F::kBAlongN ? e % TN : e / TK, kk = F::kBAlongN ? e / TN : e % TK;
+            s_b[kk][nn] = (n0 + nn < N && k0 + kk < k_end) ? f.b(k0 + kk, n0 + nn) : 0.0f;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int kk = 0; kk < TK; ++kk) {
+            float av[RM], bv[RN];
+#pragma unroll
+            for (int i = 0; i < RM; ++i) av[i] = s_a[kk][tm * RM + i];
+#pragma unroll
+            for (int j = 0; j < RN; ++j) bv[j] = s_b[kk][tn * RN + j];
+#pragma unroll
+            for (int i = 0; i < RM; ++i)
+#pragma unroll
+                for (int j = 0; j < RN; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int i = 0; i < RM; ++i)
+#pragma unroll
+        for (int j = 0; j < RN; ++j) {
+            const int m = m0 + tm * RM + i, n = n0 + tn * RN + j;
+            if (m < M && n < N) f.store(m, n, acc[i][j], gridDim.z > 1);
+        }
+}
+
+template <class F, int TM = 64, int TN = 64, int RM = 4, int RN = 4>
+cudaError_t run_gemm(const F &f, int M, int N, int K, int want_ctas, cudaStream_t s)
+{
+    if (M <= 0 || N <= 0 || K <= 0) return cudaSuccess;
+    const int gm = (M + TM - 1) / TM, gn = (N + TN - 1) / TN;
+    int splits = want_ctas / (gm * gn);
+    if (splits < 1) splits = 1;
+    int per = ((K + splits - 1) / splits + 15) / 16 * 16;
+    if (per < 64) per = 64;
+    splits = (K + per - 1) / per;
+    simt_gemm<F, TM, TN, RM, RN><<<dim3(gn, gm, splits), (TM / RM) * (TN / RN), 0, s>>>(f, M, N, K, per);
+    return cudaGetLastError();
+}
+
+// ---- weight gradients: C = dW (Keras layout, float32, zeroed before), reduction over rows
+// dense: dW[in][out] = sum_b act(b, in) * dz[b][out];  act(b, in) = scale[in % cdiv] * x[b][in'] + shift[...]   (BatchNorm output, or plain)
+struct DenseWgrad {
+    static constexpr bool kAAlongM = true, kBAlongN = true;
+    const __nv_bfloat16 *x; // [B][M]
+    const float *dz;        // [B][N]
+    float *dw;              // [rows][N]
+    const float *s, *t;     // BatchNorm affine map per channel (nullptr: identity); channel = m % 64 (dense1: input index pixel * 64 + channel)
+    int M, N, keras_perm;   // keras_perm: dW row of input (pixel, channel) is channel * 64 + pixel (Flatten of (C, H, W), models.py:44)
+    __device__ float a(int m, int k) const
+    {
+        const float v = bf(x, static_cast<long long>(k) * M + m);
+        return s ? fmaf(s[m & 63], v, t[m & 63]) : v;
+    }
+    __device__ float b(int k, int n) const { return dz[static_cast<long long>(k) * N + n]; }
+    __device__ void store(int m, int n, float v, bool atomic) const
+    {
+        float *p = dw + static_cast<long long>(keras_perm ? (m & 63) * 64 + (m >> 6) : m) * N + n;
+        if (atomic) atomicAdd(p, v); else *p = v;
+    }
+};
+// conv (4x4, stride 2): dW[(tap, c)][o] = sum_{s, y, x} bn(r[s][2y + ky][2x + kx][c]) * dz[(s, y, x)][o]
+struct ConvWgrad {
+    static constexpr bool kAAlongM = true, kBAlongN = true;
+    const __nv_bfloat16 *r; // [B][in_side^2][cpad]
+    const float *dz;        // [B * out_side^2][N]
+    float *dw;              // [16][cin][N]
+    const float *s, *t;
+    int cin, cpad, in_side, out_side, N;
+    __device__ float a(int m, int k) const
+    {
+        const int tap = m / cin, c = m - tap * cin, ky = tap >> 2, kx = tap & 3;
+        const int px = out_side * out_side, smp = k / px, p = k - smp * px, y = p / out_side, x = p - y * out_side;
+        const float v = bf(r, (static_cast<long long>(smp) * in_side * in_side + (2 * y + ky) * in_side + 2 * x + kx) * cpad + c);
+        return fmaf(s[c], v, t[c]);
+    }
+    __device__ float b(int k, int n) const { return dz[static_cast<long long>(k) * N + n]; }
+    __device__ void store(int m, int n, float v, bool atomic) const
+    {
+        float *p = dw + static_cast<long long>(m) * N + n;
+        if (atomic) atomicAdd(p, v); else *p = v;
+    }
+};
+// ---- data gradients
+// dense: dx[b][in] = sum_out dz[b][out] * W[keras(in)][out]
+struct DenseDgrad {
+    static constexpr bool kAAlongM = false, kBAlongN = false;
+    const float *dz;  // [B][K]
+    const float *w;   // Keras [in][K]
+    float *dx;        // [B][N]
+    const __nv_bfloat16 *mask; // ReLU output of the layer below ([B][N]; nullptr: no mask)
+    __nv_bfloat16 *dx_bf16;    // optional bf16 copy
+    int K, N, keras_perm;
+    __device__ float a(int m, int k) const { return dz[static_cast<long long>(m) * K + k]; }
+    __device__ float b(int k, int n) const { return w[static_cast<long long>(keras_perm ? (n & 63) * 64 + (n >> 6) : n) * K + k]; }
+    __device__ void store(int m, int n, float v, bool) const
+    {
+        const long long at = static_cast<long long>(m) * N + n;
+        if (mask && !(bf(mask, at) > 0.0f)) v = 0.0f;
+        dx[at] = v;
+        if (dx_bf16) dx_bf16[at] = __float2bfloat16_rn(v);
+    }
+};
+// transposed 4x4 stride-2 convolution, one PARITY CLASS (py, px) of the input pixels per launch: input pixel (Y, X) =
+// (2 y' + py, 2 x' + px) receives taps ky = py + 2 jy, kx = px + 2 jx from output pixel (y' - jy, x' - jx):
+// da[s][Y][X][c] = sum_{jy, jx, o} dz[s][y' - jy][x' - jx][o] * W[ky][kx][c][o]      (K = 4 * cout, no zero taps)
+struct ConvDgrad {
+    static constexpr bool kAAlongM = false, kBAlongN = false;
+    const float *dz; // [B][out_side^2][cout]
+    const float *w;  // Keras [16][cin][cout]
+    float *da;       // [B][in_side^2][cpad]
+    int cin, cpad, cout, in_side, out_side, py, px, ny, nx; // ny x nx input pixels of this parity per sample
+    __device__ float a(int m, int k) const
+    {
+        const int per = ny * nx, smp = m / per, p = m - smp * per, yq = p / nx, xq = p - yq * nx;
+        const int j = k / cout, o = k - j * cout, y = yq - (j >> 1), x = xq - (j & 1);
+        if (y < 0 || x < 0 || y >= out_side || x >= out_side) return 0.0f;
+        return dz[(static_cast<long long>(smp) * out_side * out_side + y * out_side + x) * cout + o];
+    }
+    __device__ float b(int k, int n) const
+    {
+        const int j = k / cout, o = k - j * cout, ky = py + 2 * (j >> 1), kx = px + 2 * (j & 1);
+        return w[(static_cast<long long>(ky * 4 + kx) * cin + n) * cout + o];
+    }
+    __device__ void store(int m, int n, float v, bool) const
+    {
+        const int per = ny * nx, smp = m / per, p = m - smp * per, yq = p / nx, xq = p - yq * nx;
+        da[(static_cast<long long>(smp) * in_side * in_side + (2 * yq + py) * in_side + 2 * xq + px) * cpad + n] = v;
+    }
+};
+
+// ------------------------------------------------------------------------------------------------ small kernels
+// column sums: out[c] = sum_rows x[row][pitch * .. + c]  (bias gradients)
+__global__ void __launch_bounds__(256) colsum_kernel(const float *__restrict__ x, long long rows, int cols, int pitch, float *__restrict__ out)
+{
+    // grid.x blocks stride over rows; thread = (row lane, column)
+    const int c = threadIdx.x % cols, lanes = 256 / cols, rl = threadIdx.x / cols;
+    if (rl >= lanes) return;
+    float acc = 0.0f;
+    for (long long row = static_cast<long long>(blockIdx.x) * lanes + rl; row < rows; row += static_cast<long long>(gridDim.x) * lanes) acc += x[row * pitch + c];
+    atomicAdd(out + c, acc);
+}
+
+// output layer (512 -> 10, linear): dh2 = dq W^T masked by h2 > 0 -> dz5;  one thread per (b, k)
+__global__ void __launch_bounds__(256) out_dgrad_kernel(const float *__restrict__ dq, const float *__restrict__ w_out, const __nv_bfloat16 *__restrict__ h2,
+                                                        int batch, float *__restrict__ dz, __nv_bfloat16 *__restrict__ dz_bf16)
+{
+    const long long i = static_cast<long long>(blockIdx.x) * 256 + threadIdx.x;
+    if (i >= static_cast<long long>(batch) * 512) return;
+    const int b = static_cast<int>(i >> 9), k = static_cast<int>(i & 511);
+    float acc = 0.0f;
+#pragma unroll
+    for (int o = 0; o < 10; ++o) acc = fmaf(dq[b * 10 + o], w_out[k * 10 + o], acc);
+    if (!(bf(h2, i) > 0.0f)) acc = 0.0f;
+    dz[i] = acc;
+    dz_bf16[i] = __float2bfloat16_rn(acc);
+}
+
+// BatchNorm backward, training mode (batch statistics), for y = gamma * (r - mean) / sigma + beta applied to r = relu(z):
+//   pass 1: sums[c] = sum da, sums[cpad + c] = sum da * xhat          (= d beta, d gamma)
+//   pass 2: dr = gamma / sigma * (da - dbeta / n - xhat * dgamma / n);  dz = dr where r > 0
+template <int kCPad>
+__global__ void __launch_bounds__(256) bn_bwd_sums_kernel(const float *__restrict__ da, const __nv_bfloat16 *__restrict__ r, long long rows,
+                                                          const float *__restrict__ mean, const float *__restrict__ var, int da_pitch, double *__restrict__ sums)
+{
+    __shared__ float s_part[2][256];
+    const int c = threadIdx.x % kCPad, lanes = 256 / kCPad, rl = threadIdx.x / kCPad;
+    const float mu = mean[c], inv = rsqrtf(var[c] + kBnEps);
+    float sb = 0.0f, sg = 0.0f;
+    for (long long row = static_cast<long long>(blockIdx.x) * lanes + rl; row < rows; row += static_cast<long long>(gridDim.x) * lanes) {
+        const float d = da[row * da_pitch + c], xh = (bf(r, row * kCPad + c) - mu) * inv;
+        sb += d;
+        sg = fmaf(d, xh, sg);
+    }
+    s_part[0][threadIdx.x] = sb;
+    s_part[1][threadIdx.x] = sg;
+    __syncthreads();
+    if (threadIdx.x < 2 * kCPad) {
+        const int cc = threadIdx.x % kCPad, which = threadIdx.x / kCPad;
+        double acc = 0.0;
+        for (int l = 0; l < lanes; ++l) acc += static_cast<double>(s_part[which][l * kCPad + cc]);
+        atomicAdd(sums + which * kCPad + cc, acc);
+    }
+}
+template <int kCPad>
+__global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const float *__restrict__ da, const __nv_bfloat16 *__restrict__ r, long long rows,
+                                                           const float *__restrict__ gamma, const float *__restrict__ mean, const float *__restrict__ var,
+                                                           int c_real, int da_pitch, const double *__restrict__ sums, float *__restrict__ dz,
+                                                           float *__restrict__ dgamma, float *__restrict__ dbeta)
+{
+    const long long total = rows * kCPad;
+    for (long long i = static_cast<long long>(blockIdx.x) * 256 + threadIdx.x; i < total; i += static_cast<long long>(gridDim.x) * 256) {
+        const int c = static_cast<int>(i % kCPad);
+        const long long row = i / kCPad;
+        float out = 0.0f;
+        if (c < c_real) {
+            const float inv = rsqrtf(var[c] + kBnEps), rv = bf(r, i), xh = (rv - mean[c]) * inv;
+            const float db = static_cast<float>(sums[c] / static_cast<double>(rows)), dg = static_cast<float>(sums[kCPad + c] / static_cast<double>(rows));
+            out = rv > 0.0f ? gamma[c] * inv * (da[row * da_pitch + c] - db - xh * dg) : 0.0f;
+        }
+        dz[i] = out;
+    }
+    if (blockIdx.x == 0 && threadIdx.x < c_real) {
+        dbeta[threadIdx.x] = static_cast<float>(sums[threadIdx.x]);
+        dgamma[threadIdx.x] = static_cast<float>(sums[kCPad + threadIdx.x]);
+    }
+}
+// per-channel affine map of a BatchNorm on batch statistics: s = gamma / sigma, t = beta - mean * s
+__global__ void bn_affine_kernel(const float *gamma, const float *beta, const float *mean, const float *var, int c, float *s, float *t)
+{
+    const int i = threadIdx.x;
+    if (i >= c) return;
+    const float sc = gamma[i] * rsqrtf(var[i] + kBnEps);
+    s[i] = sc;
+    t[i] = beta[i] - mean[i] * sc;
+}
+
+// conv1 weight gradient: dW1[ky][kx][c][o] = sum_{s, y, x} ((pix[s][c][3y + ky][3x + kx] - 128) / 128) * dz1[s][y][x][o]
+// (c = stacked plane: age * 3 + colour, newest frame first, processor.py:47-49).  A CTA owns a run of (sample, output row)
+// pairs: the 8 input rows of the 9 planes (9 KB of uint8) and the 41 x 5 gradients of the row go to shared memory, thread
+// (c, ky, kx) — 576 of them — keeps its 5 sums in registers: per output pixel one shared byte, one conversion and 5 FMAs
+// against broadcast gradients.  Partial sums are added to dW1 with atomics at the end.
+__global__ void __launch_bounds__(576) conv1_wgrad_kernel(const uint8_t *__restrict__ frames, int n, int head, const float *__restrict__ dz1,
+                                                          float *__restrict__ dw, float *__restrict__ dz_colsum_unused)
+{
+    __shared__ __align__(16) uint8_t s_img[9][8][144]; // row pitch 144: the four kernel rows of a warp fall into different banks
+    __shared__ __align__(16) float s_dz[41][8];
+    const int tid = threadIdx.x, c = tid >> 6, ky = (tid >> 3) & 7, kx = tid & 7;
+    float acc[5] = {0, 0, 0, 0, 0};
+    const int units = n * 41;
+    for (int u = blockIdx.x; u < units; u += gridDim.x) {
+        const int smp = u / 41, y = u - smp * 41;
+        __syncthreads();
+        for (int i = tid; i < 9 * 8 * 8; i += 576) { // 16-byte vectors: plane, row, 8 vectors per row
+            const int pl = i >> 6, row = (i >> 3) & 7, v = i & 7, age = pl / 3, col = pl - age * 3;
+            const uint8_t *src = frames + ((static_cast<size_t>((head + 3 - age) % 3) * n + smp) * 3 + col) * (128 * 128) + (3 * y + row) * 128 + v * 16;
+            *reinterpret_cast<uint4 *>(&s_img[pl][row][v * 16]) = __ldg(reinterpret_cast<const uint4 *>(src));
+        }
+        for (int i = tid; i < 41 * 8; i += 576) s_dz[i >> 3][i & 7] = dz1[(static_cast<size_t>(smp) * kP1 + y * 41) * 8 + i];
+        __syncthreads();
+        const uint8_t *rowp = &s_img[c][ky][kx];
+#pragma unroll 4
+        for (int x = 0; x < 41; ++x) {
+            const float v = static_cast<float>(rowp[3 * x]);
+            const float4 d = *reinterpret_cast<const float4 *>(&s_dz[x][0]);
+            const float d4 = s_dz[x][4];
+            acc[0] = fmaf(v, d.x, acc[0]); acc[1] = fmaf(v, d.y, acc[1]); acc[2] = fmaf(v, d.z, acc[2]); acc[3] = fmaf(v, d.w, acc[3]);
+            acc[4] = fmaf(v, d4, acc[4]);
+        }
+    }
+    float *out = dw + ((ky * 8 + kx) * 9 + c) * 5;
+#pragma unroll
+    for (int o = 0; o < 5; ++o) atomicAdd(out + o, acc[o] * (1.0f / 128.0f));
+}
+// dW1 -= sum dz1 (the "- 128 / 128" of the normalisation): every tap sees every output pixel once
+__global__ void conv1_wgrad_shift_kernel(float *__restrict__ dw, const float *__restrict__ db)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < 576 * 5) dw[i] -= db[i % 5];
+}
+
+// ------------------------------------------------------------------------------------------------ optimizer
+struct Segments { ahk_param_segment seg[24]; int count; };
+
+// sum over the trainable elements of (g + 2 l2 p [regularised])^2 -> norm2 (double); sum of l2 * p^2 -> penalty (double)
+__global__ void __launch_bounds__(256) grad_norm_kernel(const float *__restrict__ p, const float *__restrict__ g, Segments segs, float l2,
+                                                        double *__restrict__ norm2, double *__restrict__ penalty)
+{
+    double acc = 0.0, pen = 0.0;
+    for (int si = 0; si < segs.count; ++si) {
+        const ahk_param_segment sg = segs.seg[si];
+        if (!(sg.flags & AHK_SEG_TRAINABLE)) continue;
+        const bool reg = (sg.flags & AHK_SEG_L2) != 0;
+        for (int i = blockIdx.x * 256 + threadIdx.x; i < sg.count; i += gridDim.x * 256) {
+            const float w = p[sg.offset + i];
+            const float gv = g[sg.offset + i] + (reg ? 2.0f * l2 * w : 0.0f);
+            acc += static_cast<double>(gv) * gv;
+            if (reg) pen += static_cast<double>(l2) * w * w;
+        }
+    }
+    __shared__ double s_acc[256], s_pen[256];
+    s_acc[threadIdx.x] = acc;
+    s_pen[threadIdx.x] = pen;
+    __syncthreads();
+    for (int w = 128; w > 0; w >>= 1) {
+        if (threadIdx.x < w) { s_acc[threadIdx.x] += s_acc[threadIdx.x + w]; s_pen[threadIdx.x] += s_pen[threadIdx.x + w]; }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) { atomicAdd(norm2, s_acc[0]); atomicAdd(penalty, s_pen[0]); }
+}
+
+// keras.optimizers.SGD (Keras 2.x): g *= clipnorm / max(norm, clipnorm); v = momentum * v - lr_t * g; p += v
+// keras.optimizers.Adam:            m = b1 m + (1 - b1) g; v = b2 v + (1 - b2) g^2; p -= lr_t * m / (sqrt(v) + eps),
+//                                   lr_t = lr * sqrt(1 - b2^t) / (1 - b1^t) passed in by the host
+// BatchNorm moving statistics (momentum 0.99): moving = 0.99 * moving + 0.01 * batch
+template <bool kAdam>
+__global__ void __launch_bounds__(256) step_kernel(float *__restrict__ p, const float *__restrict__ g, float *__restrict__ m1, float *__restrict__ m2,
+                                                   Segments segs, float lr_t, float momentum, float clipnorm, float l2, float beta1, float beta2, float eps,
+                                                   const double *__restrict__ norm2, const float *__restrict__ batch_stats, float bn_momentum,
+                                                   float *__restrict__ loss, const double *__restrict__ penalty)
+{
+    float scale = 1.0f;
+    if (clipnorm > 0.0f) {
+        const float norm = static_cast<float>(sqrt(*norm2));
+        if (norm >= clipnorm) scale = clipnorm / norm; // K.clip_norm
+    }
+    if (loss && blockIdx.x == 0 && threadIdx.x == 0) *loss += static_cast<float>(*penalty);
+    for (int si = 0; si < segs.count; ++si) {
+        const ahk_param_segment sg = segs.seg[si];
+        if (sg.flags & (AHK_SEG_BN_MEAN | AHK_SEG_BN_VAR)) {
+            if (!batch_stats) continue;
+            const float *src = batch_stats + ((sg.flags & AHK_SEG_BN_VAR) ? AHK_BN_STATS : 0) + sg.stat_offset;
+            for (int i = blockIdx.x * 256 + threadIdx.x; i < sg.count; i += gridDim.x * 256)
+                p[sg.offset + i] = bn_momentum * p[sg.offset + i] + (1.0f - bn_momentum) * src[i];
+            continue;
+        }
+        if (!(sg.flags & AHK_SEG_TRAINABLE)) continue;
+        const bool reg = (sg.flags & AHK_SEG_L2) != 0;
+        for (int i = blockIdx.x * 256 + threadIdx.x; i < sg.count; i += gridDim.x * 256) {
+            const int at = sg.offset + i;
+            const float w = p[at];
+            const float gv = (g[at] + (reg ? 2.0f * l2 * w : 0.0f)) * scale;
+            if (kAdam) {
+                const float a = beta1 * m1[at] + (1.0f - beta1) * gv, b = beta2 * m2[at] + (1.0f - beta2) * gv * gv;
+                m1[at] = a;
+                m2[at] = b;
+                p[at] = w - lr_t * a / (sqrtf(b) + eps);
+            } else {
+                const float v = momentum * m1[at] - lr_t * gv;
+                m1[at] = v;
+                p[at] = w + v;
+            }
+        }
+    }
+}
+
+} // namespace train
+} // namespace ahk
+
+// ------------------------------------------------------------------------------------------------ C ABI
+using namespace ahk::train;
+
+struct ahk_trainer {
+    int device = 0, max_batch = 0, sms = 148;
+    // gradients with respect to layer inputs / pre-activations (float32) and bf16 copies where a tensor-core GEMM reads them
+    float *dz5 = nullptr, *dz4 = nullptr, *da3 = nullptr, *dz3 = nullptr, *da2 = nullptr, *dz2 = nullptr, *da1 = nullptr, *dz1 = nullptr;
+    __nv_bfloat16 *dz5h = nullptr, *dz4h = nullptr;
+    float *affine = nullptr;  // s1[8] t1[8] s2[32] t2[32] s3[64] t3[64]
+    double *sums = nullptr;   // [2][64] BatchNorm backward sums; [128..129] gradient norm^2, penalty
+    uint64_t launches = 0;
+};
+
+namespace {
+
+int tfail(int code, const char *fmt, const char *detail)
+{
+    char text[512];
+    snprintf(text, sizeof text, fmt, detail);
+    ahk::set_error_text(text);
+    return code;
+}
+#define TR_CUDA(expr)                                                                        \
+    do {                                                                                     \
+        cudaError_t err__ = (expr);                                                          \
+        if (err__ != cudaSuccess) return tfail(AHK_ERR_CUDA, #expr ": %s", cudaGetErrorString(err__)); \
+    } while (0)
+
+struct DeviceGuard {
+    int prev = -1, cur;
+    explicit DeviceGuard(int device) : cur(device) { cudaGetDevice(&prev); if (prev != cur) cudaSetDevice(cur); }
+    ~DeviceGuard() { if (prev != cur && prev >= 0) cudaSetDevice(prev); }
+};
+
+} // namespace
+
+extern "C" {
+
+int ahk_trainer_create(int device, int max_batch, ahk_trainer **out)
+{
+    if (!out || max_batch <= 0 || max_batch > 16384) return tfail(AHK_ERR_ARG, "%s", "ahk_trainer_create: bad argument (max_batch must be in [1, 16384])");
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) return tfail(AHK_ERR_NO_DEVICE, "%s", "no CUDA device: the trainer has no CPU fallback");
+    DeviceGuard guard(device);
+    ahk_trainer *t = new ahk_trainer();
+    t->device = device;
+    t->max_batch = max_batch;
+    cudaDeviceGetAttribute(&t->sms, cudaDevAttrMultiProcessorCount, device);
+    const size_t nb = static_cast<size_t>(max_batch);
+    cudaError_t e = cudaMalloc(&t->dz5, nb * 512 * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&t->dz4, nb * 512 * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&t->da3, nb * 4096 * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&t->dz3, nb * 4096 * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&t->da2, nb * kP2 * 32 * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&t->dz2, nb * kP2 * 32 * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&t->da1, nb * kP1 * 8 * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&t->dz1, nb * kP1 * 8 * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&t->dz5h, nb * 512 * 2);
+    if (e == cudaSuccess) e = cudaMalloc(&t->dz4h, nb * 512 * 2);
+    if (e == cudaSuccess) e = cudaMalloc(&t->affine, 256 * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&t->sums, 160 * 8);
+    if (e == cudaSuccess) e = cudaMemset(t->sums, 0, 160 * 8);
+    if (e == cudaSuccess) e = cudaMemset(t->da1, 0, nb * kP1 * 8 * 4); // channels 5..7 are never written
+    if (e != cudaSuccess) {
+        ahk_trainer_destroy(t);
+        return tfail(AHK_ERR_CUDA, "ahk_trainer_create: %s", cudaGetErrorString(e));
+    }
+    *out = t;
+    return AHK_OK;
+}
+
+void ahk_trainer_destroy(ahk_trainer *t)
+{
+    if (!t) return;
+    DeviceGuard guard(t->device);
+    cudaFree(t->dz5); cudaFree(t->dz4); cudaFree(t->da3); cudaFree(t->dz3); cudaFree(t->da2); cudaFree(t->dz2); cudaFree(t->da1); cudaFree(t->dz1);
+    cudaFree(t->dz5h); cudaFree(t->dz4h); cudaFree(t->affine); cudaFree(t->sums);
+    delete t;
+}
+
+int ahk_train_backward(ahk_trainer *t, ahk_policy *p, const ahk_policy_weights *w_dev, const uint8_t *frames_dev, int n, int head,
+                       const float *batch_stats_dev, const float *dlogits_dev, const ahk_policy_weights *grads_dev, void *stream)
+{
+    if (!t || !p || !w_dev || !frames_dev || !batch_stats_dev || !dlogits_dev || !grads_dev) return tfail(AHK_ERR_ARG, "%s", "ahk_train_backward: NULL argument");
+    if (n <= 0 || n > t->max_batch || head < 0 || head > 2) return tfail(AHK_ERR_ARG, "%s", "ahk_train_backward: n must be in [1, max_batch], head in [0, 3)");
+    ahk_policy_acts acts;
+    if (int rc = ahk_policy_get_activations(p, &acts)) return rc;
+    if (acts.max_batch < n) return tfail(AHK_ERR_ARG, "%s", "ahk_train_backward: the policy handle's max_batch is smaller than n");
+    const float *const *wf = reinterpret_cast<const float *const *>(w_dev);
+    float *const *gf = reinterpret_cast<float *const *>(const_cast<ahk_policy_weights *>(grads_dev));
+    for (int i = 0; i < 24; ++i)
+        if (!wf[i] || !gf[i]) return tfail(AHK_ERR_ARG, "%s", "ahk_train_backward: every weight / gradient pointer must be non-NULL");
+    DeviceGuard guard(t->device);
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const __nv_bfloat16 *r1 = static_cast<const __nv_bfloat16 *>(acts.act1), *r2 = static_cast<const __nv_bfloat16 *>(acts.act2),
+                        *r3 = static_cast<const __nv_bfloat16 *>(acts.act3), *h1 = static_cast<const __nv_bfloat16 *>(acts.h1), *h2 = static_cast<const __nv_bfloat16 *>(acts.h2);
+    const float *mean = batch_stats_dev, *var = batch_stats_dev + AHK_BN_STATS;
+    // field indices of ahk_policy_weights
+    enum { C1W = 0, C1B, G1, B1, M1, V1, C2W, C2B, G2, B2, M2, V2, C3W, C3B, G3, B3, M3, V3, D1W, D1B, D2W, D2B, OW, OB };
+    float *s1 = t->affine, *t1 = s1 + 8, *s2 = s1 + 16, *t2 = s1 + 48, *s3 = s1 + 80, *t3 = s1 + 144;
+    bn_affine_kernel<<<1, 64, 0, s>>>(wf[G1], wf[B1], mean, var, 5, s1, t1);
+    bn_affine_kernel<<<1, 64, 0, s>>>(wf[G2], wf[B2], mean + 8, var + 8, 32, s2, t2);
+    bn_affine_kernel<<<1, 64, 0, s>>>(wf[G3], wf[B3], mean + 40, var + 40, 64, s3, t3);
+    const int ctas = t->sms * 2;
+    auto zero = [&](float *ptr, size_t count) { return cudaMemsetAsync(ptr, 0, count * 4, s); };
+    // bias gradients are column sums (atomics): clear them, and the weight gradients that are accumulated with split K
+    TR_CUDA(zero(gf[OB], 10)); TR_CUDA(zero(gf[D2B], 512)); TR_CUDA(zero(gf[D1B], 512)); TR_CUDA(zero(gf[C3B], 64)); TR_CUDA(zero(gf[C2B], 32)); TR_CUDA(zero(gf[C1B], 5));
+    TR_CUDA(zero(gf[OW], 5120)); TR_CUDA(zero(gf[D2W], 512 * 512)); TR_CUDA(zero(gf[D1W], 4096 * 512)); TR_CUDA(zero(gf[C3W], 512 * 64)); TR_CUDA(zero(gf[C2W], 80 * 32)); TR_CUDA(zero(gf[C1W], 576 * 5));
+
+    // ---- output layer: dW6 = h2^T dq, db6 = sum dq, dz5 = (dq W6^T) . [h2 > 0]
+    {
+        DenseWgrad f{h2, dlogits_dev, gf[OW], nullptr, nullptr, 512, 10, 0};
+        TR_CUDA((run_gemm<DenseWgrad>(f, 512, 10, n, ctas, s)));
+        colsum_kernel<<<min(ctas, (n + 24) / 25), 256, 0, s>>>(dlogits_dev, n, 10, 10, gf[OB]);
+        out_dgrad_kernel<<<(n * 512 + 255) / 256, 256, 0, s>>>(dlogits_dev, wf[OW], h2, n, t->dz5, t->dz5h);
+    }
+    // ---- dense2: dW5 = h1^T dz5, db5, dz4 = (dz5 W5^T) . [h1 > 0]
+    {
+        DenseWgrad f{h1, t->dz5, gf[D2W], nullptr, nullptr, 512, 512, 0};
+        TR_CUDA((run_gemm<DenseWgrad>(f, 512, 512, n, ctas, s)));
+        colsum_kernel<<<min(ctas, n), 256, 0, s>>>(t->dz5, n, 256, 512, gf[D2B]);
+        colsum_kernel<<<min(ctas, n), 256, 0, s>>>(t->dz5 + 256, n, 256, 512, gf[D2B] + 256);
+        DenseDgrad d{t->dz5, wf[D2W], t->dz4, h1, t->dz4h, 512, 512, 0};
+        TR_CUDA((run_gemm<DenseDgrad>(d, n, 512, 512, 1, s)));
+    }
+    // ---- dense1: dW4 = bn3(r3)^T dz4 (Keras row order channel * 64 + pixel), db4, da3 = dz4 W4^T
+    {
+        DenseWgrad f{r3, t->dz4, gf[D1W], s3, t3, 4096, 512, 1};
+        TR_CUDA((run_gemm<DenseWgrad>(f, 4096, 512, n, ctas, s)));
+        colsum_kernel<<<min(ctas, n), 256, 0, s>>>(t->dz4, n, 256, 512, gf[D1B]);
+        colsum_kernel<<<min(ctas, n), 256, 0, s>>>(t->dz4 + 256, n, 256, 512, gf[D1B] + 256);
+        DenseDgrad d{t->dz4, wf[D1W], t->da3, nullptr, nullptr, 512, 4096, 1};
+        TR_CUDA((run_gemm<DenseDgrad>(d, n, 4096, 512, 1, s)));
+    }
+    // ---- BatchNorm 3 + ReLU backward: da3 [n * 64 rows][64] -> dz3, d gamma3, d beta3
+    {
+        const long long rows = static_cast<long long>(n) * 64;
+        bn_bwd_sums_kernel<64><<<ctas, 256, 0, s>>>(t->da3, r3, rows, mean + 40, var + 40, 64, t->sums);
+        bn_bwd_apply_kernel<64><<<ctas * 2, 256, 0, s>>>(t->da3, r3, rows, wf[G3], mean + 40, var + 40, 64, 64, t->sums, t->dz3, gf[G3], gf[B3]);
+        TR_CUDA(cudaMemsetAsync(t->sums, 0, 128 * 8, s));
+    }
+    // ---- conv3: dW3 = im2col(bn2(r2))^T dz3, db3, da2 = transposed conv (4 parity classes)
+    {
+        ConvWgrad f{r2, t->dz3, gf[C3W], s2, t2, 32, 32, 19, 8, 64};
+        TR_CUDA((run_gemm<ConvWgrad>(f, 512, 64, n * 64, ctas, s)));
+        colsum_kernel<<<min(ctas, n * 16), 256, 0, s>>>(t->dz3, static_cast<long long>(n) * 64, 64, 64, gf[C3B]);
+        for (int cls = 0; cls < 4; ++cls) {
+            const int py = cls >> 1, px = cls & 1, ny = py ? 9 : 10, nx = px ? 9 : 10;
+            ConvDgrad d{t->dz3, wf[C3W], t->da2, 32, 32, 64, 19, 8, py, px, ny, nx};
+            TR_CUDA((run_gemm<ConvDgrad, 64, 32, 4, 2>(d, n * ny * nx, 32, 4 * 64, 1, s)));
+        }
+    }
+    // ---- BatchNorm 2 + ReLU backward
+    {
+        const long long rows = static_cast<long long>(n) * kP2;
+        bn_bwd_sums_kernel<32><<<ctas, 256, 0, s>>>(t->da2, r2, rows, mean + 8, var + 8, 32, t->sums);
+        bn_bwd_apply_kernel<32><<<ctas * 2, 256, 0, s>>>(t->da2, r2, rows, wf[G2], mean + 8, var + 8, 32, 32, t->sums, t->dz2, gf[G2], gf[B2]);
+        TR_CUDA(cudaMemsetAsync(t->sums, 0, 128 * 8, s));
+    }
+    // ---- conv2: dW2 = im2col(bn1(r1))^T dz2 (80 x 32), db2, da1 (5 channels of 8)
+    {
+        ConvWgrad f{r1, t->dz2, gf[C2W], s1, t1, 5, 8, 41, 19, 32};
+        TR_CUDA((run_gemm<ConvWgrad, 16, 32, 1, 2>(f, 80, 32, n * kP2, ctas, s)));
+        colsum_kernel<<<min(ctas, n * 32), 256, 0, s>>>(t->dz2, static_cast<long long>(n) * kP2, 32, 32, gf[C2B]);
+        for (int cls = 0; cls < 4; ++cls) {
+            const int py = cls >> 1, px = cls & 1, ny = py ? 20 : 21, nx = px ? 20 : 21;
+            ConvDgrad d{t->dz2, wf[C2W], t->da1, 5, 8, 32, 41, 19, py, px, ny, nx};
+            TR_CUDA((run_gemm<ConvDgrad, 128, 8, 4, 1>(d, n * ny * nx, 5, 4 * 32, 1, s)));
+        }
+    }
+    // ---- BatchNorm 1 + ReLU backward, conv1 weight gradient
+    {
+        const long long rows = static_cast<long long>(n) * kP1;
+        bn_bwd_sums_kernel<8><<<ctas, 256, 0, s>>>(t->da1, r1, rows, mean, var, 8, t->sums);
+        bn_bwd_apply_kernel<8><<<ctas * 2, 256, 0, s>>>(t->da1, r1, rows, wf[G1], mean, var, 5, 8, t->sums, t->dz1, gf[G1], gf[B1]);
+        TR_CUDA(cudaMemsetAsync(t->sums, 0, 128 * 8, s));
+        colsum_kernel<<<min(ctas, n * 41), 256, 0, s>>>(t->dz1, rows, 8, 8, t->affine + 208); // 8 sums: the 5 bias gradients + 3 zeros
+        TR_CUDA(cudaMemcpyAsync(gf[C1B], t->affine + 208, 5 * 4, cudaMemcpyDeviceToDevice, s));
+        conv1_wgrad_kernel<<<min(t->sms * 2, n * 41), 576, 0, s>>>(frames_dev, n, head, t->dz1, gf[C1W], nullptr);
+        conv1_wgrad_shift_kernel<<<(576 * 5 + 255) / 256, 256, 0, s>>>(gf[C1W], gf[C1B]);
+        TR_CUDA(cudaMemsetAsync(t->affine + 208, 0, 8 * 4, s));
+    }
+    TR_CUDA(cudaGetLastError());
+    t->launches += 45;
+    return AHK_OK;
+}
+
+static int optimizer_step(bool adam, ahk_trainer *t, float *params_dev, const float *grads_dev, float *m1_dev, float *m2_dev, const ahk_param_segment *segs,
+                          int n_segs, float lr_t, float momentum, float clipnorm, float l2, float beta1, float beta2, float eps, const float *batch_stats_dev,
+                          float bn_momentum, float *loss_dev, void *stream)
+{
+    if (!t || !params_dev || !grads_dev || !m1_dev || !segs || (adam && !m2_dev)) return tfail(AHK_ERR_ARG, "%s", "ahk_train_*_step: NULL argument");
+    if (n_segs <= 0 || n_segs > 24) return tfail(AHK_ERR_ARG, "%s", "ahk_train_*_step: 1 to 24 segments");
+    DeviceGuard guard(t->device);
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    Segments sg{};
+    sg.count = n_segs;
+    for (int i = 0; i < n_segs; ++i) sg.seg[i] = segs[i];
+    double *norm2 = t->sums + 128, *penalty = t->sums + 129;
+    TR_CUDA(cudaMemsetAsync(norm2, 0, 16, s));
+    grad_norm_kernel<<<t->sms * 4, 256, 0, s>>>(params_dev, grads_dev, sg, l2, norm2, penalty);
+    if (adam) step_kernel<true><<<t->sms * 4, 256, 0, s>>>(params_dev, grads_dev, m1_dev, m2_dev, sg, lr_t, momentum, clipnorm, l2, beta1, beta2, eps, norm2, batch_stats_dev, bn_momentum, loss_dev, penalty);
+    else step_kernel<false><<<t->sms * 4, 256, 0, s>>>(params_dev, grads_dev, m1_dev, m2_dev, sg, lr_t, momentum, clipnorm, l2, beta1, beta2, eps, norm2, batch_stats_dev, bn_momentum, loss_dev, penalty);
+    TR_CUDA(cudaGetLastError());
+    t->launches += 2;
+    return AHK_OK;
+}
+
+int ahk_train_sgd_step(ahk_trainer *t, float *params_dev, const float *grads_dev, float *velocity_dev, const ahk_param_segment *segs, int n_segs, float lr_t,
+                       float momentum, float clipnorm, float l2, const float *batch_stats_dev, float bn_momentum, float *loss_dev, void *stream)
+{
+    return optimizer_step(false, t, params_dev, grads_dev, velocity_dev, nullptr, segs, n_segs, lr_t, momentum, clipnorm, l2, 0.0f, 0.0f, 0.0f, batch_stats_dev, bn_momentum,
+                          loss_dev, stream);
+}
+
+int ahk_train_adam_step(ahk_trainer *t, float *params_dev, const float *grads_dev, float *m_dev, float *v_dev, const ahk_param_segment *segs, int n_segs, float lr_t,
+                        float beta1, float beta2, float eps, float l2, const float *batch_stats_dev, float bn_momentum, float *loss_dev, void *stream)
+{
+    return optimizer_step(true, t, params_dev, grads_dev, m_dev, v_dev, segs, n_segs, lr_t, 0.0f, 0.0f, l2, beta1, beta2, eps, batch_stats_dev, bn_momentum, loss_dev, stream);
+}
+
+uint64_t ahk_trainer_launches(const ahk_trainer *t) { return t ? t->launches : 0; }
+
+int ahk_trainer_copy_buffer(ahk_trainer *t, int which, float *dst_dev, size_t count, void *stream)
+{
+    if (!t || !dst_dev || which < 0 || which > 7) return tfail(AHK_ERR_ARG, "%s", "ahk_trainer_copy_buffer: bad argument");
+    const float *src[8] = {t->dz5, t->dz4, t->da3, t->dz3, t->da2, t->dz2, t->da1, t->dz1};
+    DeviceGuard guard(t->device);
+    TR_CUDA(cudaMemcpyAsync(dst_dev, src[which], count * 4, cudaMemcpyDeviceToDevice, static_cast<cudaStream_t>(stream)));
+    return AHK_OK;
+}
+
+} // extern "C"

@@ -41,6 +41,17 @@ class PolicyWeights(C.Structure):  # ahk_policy_weights
     _fields_ = [(name, C.c_void_p) for name in NAMES]
 
 
+class PolicyActs(C.Structure):  # ahk_policy_acts
+    _fields_ = [("act1", C.c_void_p), ("act2", C.c_void_p), ("act3", C.c_void_p), ("h1", C.c_void_p), ("h2", C.c_void_p), ("max_batch", C.c_int32)]
+
+
+class ParamSegment(C.Structure):  # ahk_param_segment
+    _fields_ = [("offset", C.c_int32), ("count", C.c_int32), ("flags", C.c_int32), ("stat_offset", C.c_int32)]
+
+
+SEG_TRAINABLE, SEG_L2, SEG_BN_MEAN, SEG_BN_VAR, BN_STATS = 1, 2, 4, 8, 104
+
+
 class GrayPolicyWeights(C.Structure):  # ahk_policy_gray_weights
     NAMES = tuple("%s%d_%s" % (k, i, f) if k == "bn" else "conv%d_%s" % (i, f)
                   for i in (1, 2, 3, 4) for k, f in (("conv", "w"), ("conv", "b"), ("bn", "gamma"), ("bn", "beta"), ("bn", "mean"), ("bn", "var"))) + \
@@ -87,6 +98,16 @@ SYMBOLS = {
     "ahk_rl_ddqn_targets": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, C.c_double, _vp, _vp, _vp, _vp, _vp]),
     "ahk_rl_pg_returns": (_i, [_vp, _vp, _i, _i, C.c_double, _vp, _vp]),
     "ahk_rl_pg_targets": (_i, [_vp, _vp, _vp, _i, C.c_float, _vp, _vp, _vp, _vp, _vp]),
+    "ahk_policy_forward_train": (_i, [_vp, C.POINTER(PolicyWeights), _vp, _i, _i, _vp, _vp, _vp]),
+    "ahk_policy_get_activations": (_i, [_vp, C.POINTER(PolicyActs)]),
+    "ahk_policy_copy_activation": (_i, [_vp, _i, _vp, C.c_size_t, _vp]),
+    "ahk_trainer_create": (_i, [_i, _i, C.POINTER(_vp)]),
+    "ahk_trainer_destroy": (None, [_vp]),
+    "ahk_train_backward": (_i, [_vp, _vp, C.POINTER(PolicyWeights), _vp, _i, _i, _vp, _vp, C.POINTER(PolicyWeights), _vp]),
+    "ahk_train_sgd_step": (_i, [_vp, _vp, _vp, _vp, C.POINTER(ParamSegment), _i, C.c_float, C.c_float, C.c_float, C.c_float, _vp, C.c_float, _vp, _vp]),
+    "ahk_train_adam_step": (_i, [_vp, _vp, _vp, _vp, _vp, C.POINTER(ParamSegment), _i, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, _vp, C.c_float, _vp, _vp]),
+    "ahk_trainer_launches": (C.c_uint64, [_vp]),
+    "ahk_trainer_copy_buffer": (_i, [_vp, _i, _vp, C.c_size_t, _vp]),
     "ahk_policy_destroy": (None, [_vp]),
     "ahk_policy_forward": (_i, [_vp, _vp, _i, _i, _vp, _vp, _vp]),
     "ahk_policy_forward_profiled": (_i, [_vp, _vp, _i, _i, _vp, _vp, _vp, C.POINTER(C.c_float)]),

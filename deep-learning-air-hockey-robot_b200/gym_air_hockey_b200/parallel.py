@@ -34,43 +34,18 @@ def statistics_dict(stats):
             'robot_label_hist': s[5:15], 'human_label_hist': s[15:25]}
 
 
-class GradientBucket(object):
-    """One flat buffer for all policy gradients (2 403 961 float32 = 9.6 MB for the 'rgb' network), all-reduced with a
-    single collective and averaged: at this size the all-reduce is latency-bound, so one launch beats per-tensor calls."""
+def all_reduce_mean(flat, group=None, async_op=False):
+    """Average a flat tensor over the ranks of `group`, in place, with ONE collective: the trainer's whole gradient
+    (2 403 961 float32 = 9.6 MB for the 'rgb' network — at this size the all-reduce is latency-bound, so one launch beats
+    per-tensor calls) and the BatchNorm batch statistics.  A no-op on one rank.  async_op: returns the work handle and
+    leaves the division to `finish_mean` (call it after handle.wait())."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return None
+    work = dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group, async_op=async_op)
+    if not async_op:
+        flat /= dist.get_world_size(group)
+    return work
 
-    def __init__(self, params, dtype=None):
-        self.params = [p for p in params if p.requires_grad]
-        n = sum(p.numel() for p in self.params)
-        first = self.params[0]
-        self.flat = torch.zeros(n, dtype=dtype or first.dtype, device=first.device)
 
-    def all_reduce(self, group=None, async_op=False):
-        if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
-            return None  # one rank: .grad already holds the average
-        offset = 0
-        for p in self.params:
-            k = p.numel()
-            if p.grad is not None:
-                self.flat[offset:offset + k].copy_(p.grad.reshape(-1))
-            else:
-                self.flat[offset:offset + k].zero_()
-            offset += k
-        world = dist.get_world_size(group) if dist.is_initialized() else 1
-        work = None
-        if world > 1:
-            work = dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group, async_op=async_op)
-        if not async_op:
-            self.scatter(world)
-        return work
-
-    def scatter(self, world):
-        """Write the averaged gradients back into .grad (call after an async all_reduce has completed)."""
-        offset = 0
-        for p in self.params:
-            k = p.numel()
-            g = self.flat[offset:offset + k].reshape(p.shape) / world
-            if p.grad is None:
-                p.grad = g.clone()
-            else:
-                p.grad.copy_(g)
-            offset += k
+def finish_mean(flat, group=None):
+    flat /= dist.get_world_size(group)

@@ -7,22 +7,20 @@ What runs where
   time-ordered uint8 frame store in HBM + `ahk_replay_gather` (csrc/ahk_rl.cu);
 * targets, loss and the gradient at the network output (rl_agents.py:183-187, 246-253, 257-274): `ahk_rl_ddqn_targets`,
   `ahk_rl_pg_returns`, `ahk_rl_pg_targets` (csrc/ahk_rl.cu);
-* the backward pass and the optimizer step of `model.fit` (rl_agents.py:189, 276): **PyTorch autograd over
-  `TrainableNetwork`** (cuDNN/cuBLAS — library code, not hand-written kernels; DESIGN.md §7 says so), gradients summed
-  over ranks with `parallel.GradientBucket` (NCCL), `KerasSGD` restating the compiled optimizer (rl_agents.py:111,170);
+* the training-mode forward, the backward pass and the optimizer step of `model.fit` (rl_agents.py:189, 276):
+  `train.NativeTrainer` — hand-written kernels (csrc/ahk_train.cu, ahk_policy_forward_train): no autograd, no cuDNN, no
+  cuBLAS; the flat float32 gradient is averaged over ranks with one NCCL all-reduce, the optimizers restate the compiled
+  Keras ones (SGD lr 0.0075 momentum 0.5 decay 1e-6 clipnorm 2: rl_agents.py:111,170; Adam: models.py:119);
 * after every fit the new weights (and BatchNorm moving statistics) go back to the forward kernels with
   `ahk_policy_set_weights`.
 """
 import ctypes as C
 
-import numpy as np
 import torch
-import torch.nn as nn
-import torch.nn.functional as F
 
 from . import _lib
-from .parallel import GradientBucket
-from .policy import SHAPES, PolicyNetwork, keras_default_init
+from .policy import PolicyNetwork, keras_default_init
+from .train import L2_REGULARIZER, NativeTrainer  # noqa: F401  (L2_REGULARIZER is part of this module's interface)
 
 
 def _ptr(t):
@@ -31,119 +29,6 @@ def _ptr(t):
 
 def _stream(device):
     return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
-
-
-# ---------------------------------------------------------------------------------------------- the network, trainable
-class TrainableNetwork(nn.Module):
-    """models.py:20-65 as a torch module for autograd: Conv2D(+ReLU) -> BatchNormalization(axis=1) x3, Flatten (C,H,W),
-    Dense 512 ReLU x2, Dense 10 (linear: logits; softmax on top is the supervised / PG output, models.py:62-65).
-    BatchNorm with the Keras defaults: epsilon 1e-3, momentum 0.99 (torch counts the other way: 0.01); in training mode it
-    normalises with batch statistics, as `model.fit` does."""
-
-    def __init__(self, weights=None):
-        super().__init__()
-        self.conv1, self.bn1 = nn.Conv2d(9, 5, 8, stride=3), nn.BatchNorm2d(5, eps=1e-3, momentum=0.01)
-        self.conv2, self.bn2 = nn.Conv2d(5, 32, 4, stride=2), nn.BatchNorm2d(32, eps=1e-3, momentum=0.01)
-        self.conv3, self.bn3 = nn.Conv2d(32, 64, 4, stride=2), nn.BatchNorm2d(64, eps=1e-3, momentum=0.01)
-        self.dense1, self.dense2, self.out = nn.Linear(4096, 512), nn.Linear(512, 512), nn.Linear(512, 10)
-        self.load_keras(keras_default_init() if weights is None else weights)
-        self.channels_last = False
-
-    def use_channels_last(self):
-        """NHWC memory format for the convolutions (same float32 arithmetic): cuDNN's forward + backward of this network at
-        4096 samples takes 32.8 ms instead of 52.4 (tools/fit_probe.py)."""
-        self.channels_last = True
-        return self.to(memory_format=torch.channels_last)
-
-    def forward(self, obs_u8):
-        """obs_u8: uint8 [B, 9, 128, 128], newest frame first (processor.py:47-49) -> logits float32 [B, 10]."""
-        x = (obs_u8.float() - 128.0) / 128.0  # processor.py:39-42
-        if self.channels_last:
-            x = x.contiguous(memory_format=torch.channels_last)
-        x = self.bn1(F.relu(self.conv1(x)))
-        x = self.bn2(F.relu(self.conv2(x)))
-        x = self.bn3(F.relu(self.conv3(x)))
-        x = x.flatten(1)
-        x = F.relu(self.dense1(x))
-        x = F.relu(self.dense2(x))
-        return self.out(x)
-
-    def load_keras(self, w):
-        """w: dict in Keras layouts (policy.SHAPES), i.e. model.get_weights() by name."""
-        with torch.no_grad():
-            for i in (1, 2, 3):
-                conv, bn = getattr(self, 'conv%d' % i), getattr(self, 'bn%d' % i)
-                conv.weight.copy_(torch.from_numpy(np.ascontiguousarray(np.asarray(w['conv%d_w' % i], dtype=np.float32).transpose(3, 2, 0, 1))))
-                conv.bias.copy_(torch.from_numpy(np.asarray(w['conv%d_b' % i], dtype=np.float32)))
-                bn.weight.copy_(torch.from_numpy(np.asarray(w['bn%d_gamma' % i], dtype=np.float32)))
-                bn.bias.copy_(torch.from_numpy(np.asarray(w['bn%d_beta' % i], dtype=np.float32)))
-                bn.running_mean.copy_(torch.from_numpy(np.asarray(w['bn%d_mean' % i], dtype=np.float32)))
-                bn.running_var.copy_(torch.from_numpy(np.asarray(w['bn%d_var' % i], dtype=np.float32)))
-            for name in ('dense1', 'dense2', 'out'):
-                lin = getattr(self, name)
-                lin.weight.copy_(torch.from_numpy(np.ascontiguousarray(np.asarray(w[name + '_w'], dtype=np.float32).T)))
-                lin.bias.copy_(torch.from_numpy(np.asarray(w[name + '_b'], dtype=np.float32)))
-
-    def keras_weights_device(self):
-        """-> dict of contiguous float32 tensors on the module's device, in Keras layouts (policy.SHAPES)."""
-        w = {}
-        with torch.no_grad():
-            for i in (1, 2, 3):
-                conv, bn = getattr(self, 'conv%d' % i), getattr(self, 'bn%d' % i)
-                w['conv%d_w' % i] = conv.weight.permute(2, 3, 1, 0).contiguous()
-                w['conv%d_b' % i] = conv.bias.contiguous()
-                w['bn%d_gamma' % i], w['bn%d_beta' % i] = bn.weight.contiguous(), bn.bias.contiguous()
-                w['bn%d_mean' % i], w['bn%d_var' % i] = bn.running_mean.contiguous(), bn.running_var.contiguous()
-            for name in ('dense1', 'dense2', 'out'):
-                lin = getattr(self, name)
-                w[name + '_w'] = lin.weight.t().contiguous()
-                w[name + '_b'] = lin.bias.contiguous()
-        return w
-
-    def keras_weights(self):
-        """-> dict of float32 numpy arrays in Keras layouts (what model.get_weights() would list; policy.SHAPES)."""
-        w = {}
-        with torch.no_grad():
-            for i in (1, 2, 3):
-                conv, bn = getattr(self, 'conv%d' % i), getattr(self, 'bn%d' % i)
-                w['conv%d_w' % i] = conv.weight.permute(2, 3, 1, 0).contiguous().cpu().numpy()
-                w['conv%d_b' % i] = conv.bias.cpu().numpy().copy()
-                w['bn%d_gamma' % i], w['bn%d_beta' % i] = bn.weight.cpu().numpy().copy(), bn.bias.cpu().numpy().copy()
-                w['bn%d_mean' % i], w['bn%d_var' % i] = bn.running_mean.cpu().numpy().copy(), bn.running_var.cpu().numpy().copy()
-            for name in ('dense1', 'dense2', 'out'):
-                lin = getattr(self, name)
-                w[name + '_w'] = lin.weight.t().contiguous().cpu().numpy()
-                w[name + '_b'] = lin.bias.cpu().numpy().copy()
-        return {name: np.ascontiguousarray(w[name], dtype=np.float32) for name, _ in SHAPES}
-
-
-L2_REGULARIZER = 1e-4  # models.py:17
-
-
-class KerasSGD(object):
-    """keras.optimizers.SGD(lr, momentum, decay, clipnorm) as compiled at rl_agents.py:111,170 (Keras 2.x semantics):
-    gradients scaled by clipnorm / max(global L2 norm, clipnorm); lr_t = lr / (1 + decay * iterations);
-    v = momentum * v - lr_t * g; p += v."""
-
-    def __init__(self, params, lr=0.0075, momentum=0.5, decay=1e-6, clipnorm=2.0):
-        self.params = [p for p in params if p.requires_grad]
-        self.lr, self.momentum, self.decay, self.clipnorm = lr, momentum, decay, clipnorm
-        self.iterations = 0
-        self.velocity = [torch.zeros_like(p) for p in self.params]
-
-    @torch.no_grad()
-    def step(self):
-        """Multi-tensor form (torch._foreach_*): a handful of launches for the 18 parameter tensors instead of ~100."""
-        grads = [p.grad if p.grad is not None else torch.zeros_like(p) for p in self.params]
-        if self.clipnorm and self.clipnorm > 0:
-            norm = torch.linalg.vector_norm(torch.stack(torch._foreach_norm(grads)).double()).float()
-            scale = torch.where(norm >= self.clipnorm, self.clipnorm / norm, torch.ones_like(norm))  # K.clip_norm
-            grads = torch._foreach_mul(grads, scale)
-        lr_t = self.lr * (1.0 / (1.0 + self.decay * self.iterations))
-        torch._foreach_mul_(self.velocity, self.momentum)
-        torch._foreach_add_(self.velocity, grads, alpha=-lr_t)
-        torch._foreach_add_(self.params, self.velocity)
-        self.iterations += 1
 
 
 # ---------------------------------------------------------------------------------------------- replay memory
@@ -268,7 +153,7 @@ class Agent(object):
     schedule (rl_agents.py:48-56); `iteration` counts calls, as there."""
 
     def __init__(self, env, weights=None, buffer_steps=64, batch_size=128, discount_rate=0.99, eps_min=0.0, eps_max=0.9,
-                 eps_decay_steps=1000, seed=0, group=None):
+                 eps_decay_steps=1000, seed=0, group=None, optimizer='sgd', l2_exclude=(), max_fit_batch=None):
         self.lib = _lib.load()
         self.env, self.device, self.n = env, env.device, env.n_envs
         self.n_actions = env.n_actions
@@ -276,10 +161,13 @@ class Agent(object):
         self.eps_min, self.eps_max, self.eps_decay_steps = eps_min, eps_max, eps_decay_steps
         self.iteration = 0
         self.group = group
-        self.model = TrainableNetwork(weights).to(self.device).use_channels_last()
-        self.policy = PolicyNetwork(self.model.keras_weights(), max_batch=max(self.n, self.batch_size), device=self.device.index)
+        weights = keras_default_init() if weights is None else weights
+        # model.fit on the device: flat float32 weights in Keras layouts + hand-written forward / backward / optimizer kernels;
+        # kernel_regularizer=regularizers.l2(0.0001) on conv1..dense2 and 'out' (models.py:17,22-62) is part of its step
+        self.trainer = NativeTrainer(weights, max_batch=max(self.batch_size, int(max_fit_batch or 0)), device=self.device.index,
+                                     optimizer=optimizer, l2=L2_REGULARIZER, l2_exclude=l2_exclude)
+        self.policy = PolicyNetwork(weights, max_batch=max(self.n, self.batch_size), device=self.device.index)
         self.replay = ReplayStore(env, buffer_steps)  # a view of the ring when the env has a deep one (then capacity = its depth)
-        self.bucket = GradientBucket(self.model.parameters())
         self.gen = torch.Generator(device=self.device)
         self.gen.manual_seed(int(seed))
         self.seed, self.env_id_base = int(seed), int(getattr(env, 'env_id_base', 0))
@@ -287,11 +175,6 @@ class Agent(object):
         self.loss_buffer = []
         self.logits = torch.zeros((self.n, 10), dtype=torch.float32, device=self.device)
         self.greedy = torch.zeros(self.n, dtype=torch.uint8, device=self.device)
-        # kernel_regularizer=regularizers.l2(0.0001) on conv1..dense2 and 'out' (models.py:17,22-62): model.fit minimises
-        # loss + l2 * sum ||W||^2 over these kernels (biases and BatchNorm carry no regulariser)
-        self.l2 = L2_REGULARIZER
-        self.l2_params = [m.weight for m in (self.model.conv1, self.model.conv2, self.model.conv3, self.model.dense1,
-                                             self.model.dense2, self.model.out)]
 
     def _agree(self, value, op='min'):
         """An integer every rank must agree on before issuing collectives (how many fit batches, whether to fit at all):
@@ -316,58 +199,20 @@ class Agent(object):
                                                   _stream(self.device)))
         return action
 
-    def push_weights(self, policy=None, on_device=True):
-        """The fitted network -> the forward kernels.  on_device: the module's parameters are laid out the Keras way by a
-        few torch transposes and folded / packed by kernels on the current stream (ahk_policy_set_weights_dev, ~0.1 ms);
-        otherwise through host memory (ahk_policy_set_weights: D2H, host packing, H2D, a device synchronisation, ~14 ms)."""
-        policy = policy or self.policy
-        if on_device:
-            w = self.model.keras_weights_device()
-            st = _lib.PolicyWeights()
-            for name, _ in SHAPES:
-                setattr(st, name, C.c_void_p(w[name].data_ptr()))
-            _lib.check(self.lib.ahk_policy_set_weights_dev(policy._h, C.byref(st), _stream(self.device)))
-            return
-        w = self.model.keras_weights()
-        st = _lib.PolicyWeights()
-        for name, _ in SHAPES:
-            setattr(st, name, w[name].ctypes.data_as(C.c_void_p))
-        _lib.check(self.lib.ahk_policy_set_weights(policy._h, C.byref(st)))
-        policy.weights = w
+    def push_weights(self, policy=None):
+        """The fitted network (BatchNorm moving statistics included) -> the forward kernels: folded and packed on the device
+        from the trainer's flat weight vector (ahk_policy_set_weights_dev), stream-ordered, nothing crosses PCIe."""
+        self.trainer.push(policy or self.policy)
 
-    def _sync_batchnorm_statistics(self):
-        """With several ranks every rank fits its own batch: gradients are averaged by the bucket, and so are the BatchNorm
-        moving statistics here (one small all-reduce), so that all ranks keep acting with the same network."""
-        import torch.distributed as dist
-        if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(self.group) == 1:
-            return
-        bufs = [b for bn in (self.model.bn1, self.model.bn2, self.model.bn3) for b in (bn.running_mean, bn.running_var)]
-        flat = torch.cat([b.reshape(-1) for b in bufs])
-        dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group)
-        flat /= dist.get_world_size(self.group)
-        at = 0
-        for b in bufs:
-            b.copy_(flat[at:at + b.numel()].reshape(b.shape))
-            at += b.numel()
-
-    def _fit(self, obs_u8, backward_from):
-        """One `model.fit` batch (rl_agents.py:189,276): training-mode forward, `backward_from(logits) -> (dlogits, loss)`,
-        backward, gradient all-reduce over ranks, optimizer step, weights pushed to the forward kernels."""
-        self.model.train()
-        for p in self.model.parameters():
-            p.grad = None
-        logits = self.model(obs_u8)
-        dlogits, loss = backward_from(logits.detach())
-        logits.backward(dlogits)
-        if self.l2 and self.l2_params:  # the kernel regulariser's share of the objective and of the gradients
-            with torch.no_grad():
-                for p in self.l2_params:
-                    p.grad.add_(p, alpha=2.0 * self.l2)
-                loss.add_(self.l2 * torch.stack([p.pow(2).sum() for p in self.l2_params]).sum())
-        self.bucket.all_reduce(group=self.group)
-        self.optimizer.step()
-        self._sync_batchnorm_statistics()
-        self.model.eval()
+    def _fit(self, frames3, backward_from):
+        """One `model.fit` batch (rl_agents.py:189,276) on uint8 frames [3, B, 3, 128, 128] (ring layout, head 2): training-mode
+        forward, `backward_from(logits) -> (dlogits, loss)`, backward, gradient all-reduce over ranks, optimizer step (L2
+        regulariser, clipnorm, BatchNorm moving statistics), weights pushed to the forward kernels."""
+        logits = self.trainer.forward(frames3, 2)
+        dlogits, loss = backward_from(logits)
+        self.trainer.backward(dlogits)
+        self.trainer.all_reduce(self.group)
+        self.trainer.step(loss)
         self.push_weights()
         return loss
 
@@ -381,11 +226,9 @@ class DDQNAgent(Agent):
             weights = dict(keras_default_init() if weights is None else weights)
             fresh = keras_default_init(seed=kw.get('seed', 0) + 1)
             weights['out_w'], weights['out_b'] = fresh['out_w'], fresh['out_b']
-        super().__init__(env, weights, **kw)
-        if replace_softmax:  # the new Dense(10, activation='linear') is built without a kernel_regularizer (rl_agents.py:166)
-            self.l2_params = self.l2_params[:-1]
-        self.optimizer = KerasSGD(self.model.parameters())
-        self.target_policy = PolicyNetwork(self.model.keras_weights(), max_batch=self.batch_size, device=self.device.index)
+        # the new Dense(10, activation='linear') is built without a kernel_regularizer (rl_agents.py:166)
+        super().__init__(env, weights, optimizer='sgd', l2_exclude=('out_w',) if replace_softmax else (), **kw)
+        self.target_policy = PolicyNetwork(self.trainer.keras_weights(), max_batch=self.batch_size, device=self.device.index)
         self.use_target = False
 
     def store_experience(self, action, reward, done):
@@ -415,7 +258,7 @@ class DDQNAgent(Agent):
                                                     _ptr(q_fit), _ptr(targets), _ptr(d), _ptr(loss), _stream(self.device)))
             return d, loss
 
-        self._fit(stacked(g[0:3]), backward_from)
+        self._fit(g[0:3], backward_from)
         self.targets = targets
         self.loss_buffer.append(float(loss.item()))
         return self.loss_buffer[-1]
@@ -430,9 +273,8 @@ class PGAgent(Agent):
         kw.setdefault('buffer_steps', episode_length + 3)
         if getattr(env, 'ring_depth', 3) > 3 and env.ring_depth < episode_length + 3:
             raise ValueError('PGAgent needs ring_depth >= episode_length + 3 to keep an episode in a deep ring')
-        super().__init__(env, weights, **kw)
+        super().__init__(env, weights, optimizer='adam', max_fit_batch=fit_batch, **kw)
         self.learning_rate, self.episode_length, self.fit_batch = float(learning_rate), int(episode_length), int(fit_batch)
-        self.optimizer = torch.optim.Adam(self.model.parameters(), lr=1e-3, betas=(0.9, 0.999), eps=1e-7)
         self.prob = torch.zeros((self.replay.capacity, self.n, 10), dtype=torch.float32, device=self.device)
 
     def act(self):
@@ -485,7 +327,7 @@ class PGAgent(Agent):
                                                       _ptr(p_fit), None, _ptr(d), _ptr(loss), _stream(self.device)))
                 return d, loss
 
-            self._fit(stacked(g[0:3]), backward_from)
+            self._fit(g[0:3], backward_from)
             losses.append(loss)
         rp.reset()  # rl_agents.py:280
         if not losses:

@@ -219,6 +219,67 @@ int ahk_policy_set_weights(ahk_policy *p, const ahk_policy_weights *w);
  * nothing crosses PCIe. */
 int ahk_policy_set_weights_dev(ahk_policy *p, const ahk_policy_weights *w_dev, void *stream);
 
+/* ---- model.fit on the device (rl_agents.py:189,276; ai/supervised/keras/train.py): training-mode forward, backward, optimizer ----
+ * Training-mode forward pass of the 'rgb' network: BatchNormalization normalises each layer's post-ReLU output with the
+ * BATCH's own per-channel mean and biased variance (Keras `fit`), which this call computes layer by layer and folds into
+ * the next layer's weights exactly as the inference path folds the moving statistics — so the forward kernels are the
+ * same tcgen05 kernels.  w_dev: float32 Keras-layout weights in device memory (its bn*_mean / bn*_var are not read).
+ * frames_dev: [3][n][3][128][128] ring layout (ahk_replay_gather output), head = newest slot.  logits_dev float[n][10].
+ * batch_stats_dev float[2][AHK_BN_STATS]: mean then variance, channels of bn1 at 0 (5 used of 8), bn2 at 8, bn3 at 40.
+ * The layer outputs stay in the handle's activation buffers (ahk_policy_get_activations) for ahk_train_backward.
+ * The handle's packed weights are left folded with the batch statistics: push the real ones (ahk_policy_set_weights_dev)
+ * before the next inference call. */
+#define AHK_BN_STATS 104
+int ahk_policy_forward_train(ahk_policy *p, const ahk_policy_weights *w_dev, const uint8_t *frames_dev, int n, int head,
+                             float *logits_dev, float *batch_stats_dev, void *stream);
+typedef struct {
+    const void *act1; /* bf16 [n][41*41][8]  relu(conv1), channels 5..7 zero */
+    const void *act2; /* bf16 [n][19*19][32] relu(conv2) */
+    const void *act3; /* bf16 [n][8*8][64]   relu(conv3): the dense1 input in (pixel, channel) order */
+    const void *h1;   /* bf16 [n][512] */
+    const void *h2;   /* bf16 [n][512] */
+    int max_batch;
+} ahk_policy_acts;
+int ahk_policy_get_activations(ahk_policy *p, ahk_policy_acts *out);
+/* Diagnostics and tests: activation buffer `which` (0 act1 .. 4 h2, layouts above) converted to float32 into dst_dev. */
+int ahk_policy_copy_activation(ahk_policy *p, int which, float *dst_dev, size_t count, void *stream);
+
+/* Backward pass of the forward pass ahk_policy_forward_train has just run on `p` (same stream, same frames / n / head /
+ * batch_stats): given dlogits_dev float[n][10] = d loss / d logits (ahk_rl_ddqn_targets, ahk_rl_pg_targets), writes
+ * d loss / d weight for the 18 trainable tensors into grads_dev (device pointers, Keras layouts, overwritten; its
+ * bn*_mean / bn*_var slots are not touched).  ≙ the backward half of model.fit (rl_agents.py:189,276).  Hand-written
+ * kernels only (csrc/ahk_train.cu); float32 accumulation over the bf16 activations the forward kernels produced. */
+typedef struct ahk_trainer ahk_trainer;
+int ahk_trainer_create(int device, int max_batch, ahk_trainer **out);
+void ahk_trainer_destroy(ahk_trainer *t);
+int ahk_train_backward(ahk_trainer *t, ahk_policy *p, const ahk_policy_weights *w_dev, const uint8_t *frames_dev, int n, int head,
+                       const float *batch_stats_dev, const float *dlogits_dev, const ahk_policy_weights *grads_dev, void *stream);
+/* One optimizer step over a FLAT float32 parameter vector (params_dev / grads_dev / state share the indexing), described
+ * by up to 24 segments.  Gradients are taken as g + 2 * l2 * w on AHK_SEG_L2 segments (kernel_regularizer, models.py:17);
+ * *loss_dev (nullable) += l2 * sum w^2.  AHK_SEG_BN_MEAN / _VAR segments are the BatchNorm moving statistics:
+ * moving = bn_momentum * moving + (1 - bn_momentum) * batch_stats_dev[stat_offset + i] (Keras momentum 0.99;
+ * batch_stats_dev nullable: left alone).
+ * sgd:  keras.optimizers.SGD(lr, momentum, decay, clipnorm) as compiled at rl_agents.py:111,170: g *= clipnorm /
+ *       max(||g||, clipnorm) over ALL trainable segments; v = momentum * v - lr_t * g; w += v.  lr_t = lr / (1 + decay * iterations)
+ *       is the caller's.  clipnorm <= 0: no clipping.
+ * adam: keras.optimizers.Adam (models.py:119): m, v moments; w -= lr_t * m / (sqrt(v) + eps) with
+ *       lr_t = lr * sqrt(1 - beta2^t) / (1 - beta1^t) computed by the caller. */
+#define AHK_SEG_TRAINABLE 1
+#define AHK_SEG_L2 2
+#define AHK_SEG_BN_MEAN 4
+#define AHK_SEG_BN_VAR 8
+typedef struct { int32_t offset, count, flags, stat_offset; } ahk_param_segment;
+int ahk_train_sgd_step(ahk_trainer *t, float *params_dev, const float *grads_dev, float *velocity_dev, const ahk_param_segment *segs, int n_segs,
+                       float lr_t, float momentum, float clipnorm, float l2, const float *batch_stats_dev, float bn_momentum, float *loss_dev,
+                       void *stream);
+int ahk_train_adam_step(ahk_trainer *t, float *params_dev, const float *grads_dev, float *m_dev, float *v_dev, const ahk_param_segment *segs, int n_segs,
+                        float lr_t, float beta1, float beta2, float eps, float l2, const float *batch_stats_dev, float bn_momentum, float *loss_dev,
+                        void *stream);
+uint64_t ahk_trainer_launches(const ahk_trainer *t);
+/* Diagnostics and tests: copy one of the backward pass's intermediate gradients (float32) to dst_dev: 0 dz5 [n][512],
+ * 1 dz4 [n][512], 2 da3 [n][64 px][64], 3 dz3, 4 da2 [n][361][32], 5 dz2, 6 da1 [n][1681][8], 7 dz1. */
+int ahk_trainer_copy_buffer(ahk_trainer *t, int which, float *dst_dev, size_t count, void *stream);
+
 /* ---- batched RL step: ai/reinforcement/rl_agents.py around the CNN, on the device ----
  * Replay memory ≙ Agent.experience_buffer (rl_agents.py:61-62,88-90), kept as a time-ordered store of single uint8
  * frames, store_dev [capacity][n][3][128][128] (slot = step index mod capacity; the newest ring slot of every env is

@@ -6,7 +6,7 @@ import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
-from gym_air_hockey_b200.parallel import GradientBucket, reduce_statistics, shard_range, statistics_dict
+from gym_air_hockey_b200.parallel import all_reduce_mean, reduce_statistics, shard_range, statistics_dict
 
 
 def test_shard_range_partitions():
@@ -33,13 +33,10 @@ def _worker(rank, world, port, results):
         stats = torch.arange(32, dtype=torch.int64) * (rank + 1)
         total = reduce_statistics(stats)
         d = statistics_dict(total)
-        # gradients: every rank holds grad = rank + 1 on two tensors
-        torch.manual_seed(0)
-        params = [torch.nn.Parameter(torch.zeros(5, 3)), torch.nn.Parameter(torch.zeros(7))]
-        for p in params:
-            p.grad = torch.full_like(p, float(rank + 1))
-        GradientBucket(params).all_reduce()
-        results[rank] = (total.tolist(), d['steps'], d['goals_top'], [p.grad.unique().tolist() for p in params])
+        # gradients: every rank holds the flat gradient vector rank + 1 (the trainer's layout: one tensor, one collective)
+        flat = torch.full((22,), float(rank + 1))
+        all_reduce_mean(flat)
+        results[rank] = (total.tolist(), d['steps'], d['goals_top'], [flat[:15].unique().tolist(), flat[15:].unique().tolist()])
     finally:
         dist.destroy_process_group()
 

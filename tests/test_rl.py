@@ -14,7 +14,7 @@ def test_trainable_network_matches_restatement_and_round_trips():
     import cnn_ref
     import torch
     from gym_air_hockey_b200.policy import SHAPES, keras_default_init
-    from gym_air_hockey_b200.rl import TrainableNetwork
+    from train_ref import TrainableNetwork  # the float32 autograd checker (oracle/)
     w = keras_default_init(seed=11, randomize_bn=True)
     net = TrainableNetwork(w).eval()
     obs = np.random.RandomState(1).randint(0, 256, size=(4, 9, 128, 128)).astype(np.uint8)
@@ -27,65 +27,18 @@ def test_trainable_network_matches_restatement_and_round_trips():
         assert back[name].shape == shape and np.array_equal(back[name], w[name]), name
 
 
-def test_keras_sgd_matches_restatement():
-    import rl_ref
-    import torch
-    from gym_air_hockey_b200.rl import KerasSGD
-    rs = np.random.RandomState(2)
-    shapes = [(7, 5), (5,), (3, 2, 2)]
-    p0 = [rs.randn(*s).astype(np.float32) for s in shapes]
-    grads = [[(rs.randn(*s) * sc).astype(np.float32) for s in shapes] for sc in (0.01, 3.0, 0.5, 10.0)]  # some steps clip, some do not
-    params = [torch.nn.Parameter(torch.from_numpy(p.copy())) for p in p0]
-    opt = KerasSGD(params)
-    for g in grads:
-        for p, gi in zip(params, g):
-            p.grad = torch.from_numpy(gi.copy())
-        opt.step()
-    want = rl_ref.keras_sgd_steps(p0, grads)
-    for p, w in zip(params, want):
-        assert np.allclose(p.detach().numpy(), w, rtol=1e-5, atol=1e-6)
-
-
-def test_fit_includes_the_l2_kernel_regulariser():
-    """models.py:17,22-62: every conv / dense kernel carries regularizers.l2(1e-4); `_fit` must minimise
-    loss + 1e-4 * sum ||W||^2, i.e. add 2e-4 * W to those gradients (not to biases or BatchNorm) and the penalty to the
-    reported loss.  Checked on the CPU against the restatement with a stub agent (no engine needed)."""
-    import rl_ref
-    import torch
-    from gym_air_hockey_b200 import rl
-    from gym_air_hockey_b200.policy import keras_default_init
-
-    class Stub(rl.Agent):
-        def __init__(self):  # the parts of Agent.__init__ that _fit touches, without an engine
-            self.model = rl.TrainableNetwork(keras_default_init(seed=4, randomize_bn=True))
-            self.group, self.l2 = None, rl.L2_REGULARIZER
-            self.l2_params = [m.weight for m in (self.model.conv1, self.model.conv2, self.model.conv3, self.model.dense1,
-                                                 self.model.dense2, self.model.out)]
-            self.bucket = rl.GradientBucket(self.model.parameters())
-            self.optimizer = type('NoStep', (), {'step': lambda self: None})()
-            self.pushed = 0
-
-        def push_weights(self, policy=None, on_device=True):
-            self.pushed += 1
-
-    agent = Stub()
-    obs = torch.from_numpy(np.random.RandomState(0).randint(0, 256, size=(4, 9, 128, 128)).astype(np.uint8))
-    d = torch.from_numpy(np.random.RandomState(1).randn(4, 10).astype(np.float32) * 0.01)
-    loss = agent._fit(obs, lambda logits: (d, torch.zeros(1)))
-    got = {name: p.grad.clone() for name, p in agent.model.named_parameters()}
-    # the same backward pass without the regulariser
-    agent.model.train()
-    for p in agent.model.parameters():
-        p.grad = None
-    agent.model(obs).backward(d)
-    kernels = [p.detach().numpy() for p in agent.l2_params]
-    penalty, extra = rl_ref.l2_penalty_and_grads(kernels)
-    assert abs(loss.item() - penalty) <= 1e-6 * penalty and penalty > 0
-    reg = {id(p): e for p, e in zip(agent.l2_params, extra)}
-    for name, p in agent.model.named_parameters():
-        want = p.grad + (torch.from_numpy(reg[id(p)]) if id(p) in reg else 0)
-        assert torch.allclose(got[name], want, rtol=1e-5, atol=1e-8), name
-    assert agent.pushed == 1
+def test_product_has_no_autograd_fit():
+    """The fit is hand-written (csrc/ahk_train.cu): the product package must not define a torch module, call backward() or
+    import the optimizers — the float32 autograd restatement lives in oracle/train_ref.py as the checker."""
+    import os
+    import re
+    pkg = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), 'deep-learning-air-hockey-robot_b200', 'gym_air_hockey_b200')
+    for name in sorted(os.listdir(pkg)):
+        if name.endswith('.py'):
+            src = open(os.path.join(pkg, name)).read()
+            code = '\n'.join(line.split('#')[0] for line in src.split('\n') if not line.lstrip().startswith(('"', '*', '`')))
+            assert not re.search(r'torch\.nn|nn\.Module|logits\.backward|loss\.backward|torch\.optim|torch\.autograd|requires_grad', code), name
+    assert 'ahk_train_backward' in open(os.path.join(pkg, 'train.py')).read()
 
 
 def test_valid_transitions_window_logic():
@@ -302,11 +255,9 @@ def test_set_weights_dev_equals_host_path(cuda):
     torch = cuda
     from gym_air_hockey_b200 import _lib
     from gym_air_hockey_b200.policy import SHAPES, PolicyNetwork, keras_default_init
-    from gym_air_hockey_b200.rl import TrainableNetwork
     w0, w1 = keras_default_init(seed=1, randomize_bn=True), keras_default_init(seed=2, randomize_bn=True)
     host, dev = PolicyNetwork(w1, max_batch=64), PolicyNetwork(w0, max_batch=64)
-    module = TrainableNetwork(w1).cuda()
-    wd = module.keras_weights_device()
+    wd = {name: torch.from_numpy(w1[name]).cuda() for name, _ in SHAPES}
     st = _lib.PolicyWeights()
     for name, _ in SHAPES:
         setattr(st, name, C.c_void_p(wd[name].data_ptr()))
@@ -325,26 +276,27 @@ def test_ddqn_training_loop(cuda, table, ring_depth):
     replay memory is the engine's deep ring (no frame copies), acting reads the stack through ahk_stack_view."""
     torch = cuda
     from gym_air_hockey_b200 import BatchedAirHockeyEnv
+    import train_ref
     from gym_air_hockey_b200.rl import DDQNAgent, run_training, stacked
     env = BatchedAirHockeyEnv(48, table=table, seed=5, max_episode_steps=40, ring_depth=ring_depth)
     env.reset()
     agent = DDQNAgent(env, buffer_steps=16, batch_size=32, discount_rate=0.98, eps_min=0.05, eps_max=0.99, eps_decay_steps=100, seed=7)
-    w_before = agent.model.keras_weights()
+    w_before = agent.trainer.keras_weights()
     losses = run_training(agent, 40, training_start=8, training_interval=5, copy_interval=20)
     assert len(losses) == 7 and all(np.isfinite(l) and l >= 0 for l in losses)
     assert agent.use_target                                      # iteration 40 > 20 and 40 % 20 == 0
-    assert agent.optimizer.iterations == 7
-    w_after = agent.model.keras_weights()
+    assert agent.trainer.iterations == 7
+    w_after = agent.trainer.keras_weights()
     assert not np.array_equal(w_before['dense2_w'], w_after['dense2_w'])
     assert not np.array_equal(w_before['bn1_mean'], w_after['bn1_mean'])   # fit() moved the BatchNorm statistics
     assert int(agent.action_distribution.sum().item()) == 40 * 48
     # the kernels now hold the fitted network
     batch = agent.replay.sample(32, agent.gen)
     q_kernel = agent.policy.forward_ring(batch['frames'][0:3], 2)[0]
-    with torch.no_grad():
-        q_module = agent.model.eval()(stacked(batch['frames'][0:3]))
+    with torch.no_grad():  # the float32 checker on the fitted weights (inference mode: moving statistics)
+        q_module = train_ref.TrainableNetwork(w_after).eval()(stacked(batch['frames'][0:3]).cpu())
     scale = q_module.abs().max().item()
-    assert (q_kernel - q_module).abs().max().item() <= 3e-2 * scale
+    assert (q_kernel.cpu() - q_module).abs().max().item() <= 3e-2 * scale
 
 
 @pytest.mark.gpu
@@ -356,8 +308,8 @@ def test_pg_training_loop(cuda, table, ring_depth):
     env = BatchedAirHockeyEnv(16, table=table, seed=6, max_episode_steps=12, ring_depth=ring_depth)
     env.reset()
     agent = PGAgent(env, episode_length=10, fit_batch=32, discount_rate=0.98, eps_min=0.05, eps_max=0.99, eps_decay_steps=100, seed=8)
-    w_before = agent.model.keras_weights()
+    w_before = agent.trainer.keras_weights()
     losses = run_training(agent, 25)
     assert len(losses) == 2 and all(np.isfinite(l) for l in losses)
     assert agent.replay.filled <= 6                                # buffer reset after each train (rl_agents.py:280)
-    assert not np.array_equal(w_before['out_w'], agent.model.keras_weights()['out_w'])
+    assert not np.array_equal(w_before['out_w'], agent.trainer.keras_weights()['out_w'])

@@ -109,8 +109,7 @@ def main():
         t = torch.tensor([ms], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = t.item()
-        flat = torch.cat([p.detach().reshape(-1) for p in agent.model.parameters()] +
-                         [b.reshape(-1) for b in (agent.model.bn1.running_mean, agent.model.bn3.running_var)])
+        flat = agent.trainer.params  # the flat float32 weight vector, BatchNorm moving statistics included
         lo, hi = flat.clone(), flat.clone()
         dist.all_reduce(lo, op=dist.ReduceOp.MIN)
         dist.all_reduce(hi, op=dist.ReduceOp.MAX)

@@ -1504,7 +1504,17 @@ template <int L> __global__ void __launch_bounds__(256) pack_nk_kernel(DevWeight
 }
 
 // biases: layer 0 conv1 b - sum(W) (normalisation folded), 1..3 b + sum(W * BN shift of the input channel), 4, 5 copies
-__global__ void __launch_bounds__(128) fold_bias_kernel(DevWeights w, float *b0, float *b1, float *b2, float *b3, float *b4, float *b5, int only = -1)
+// dense1's kernel summed over the 64 pixels of each input channel: w3sum[c][o] = sum_px W[c * 64 + px][o] (what a constant
+// BatchNorm shift of channel c contributes to output o) — 64 coalesced rows per thread instead of a 4096-long loop in fold_bias_kernel
+__global__ void __launch_bounds__(512) dense1_px_sums_kernel(const float *__restrict__ w, float *__restrict__ w3sum)
+{
+    const int c = blockIdx.x, o = threadIdx.x;
+    double acc = 0.0;
+    for (int px = 0; px < 64; ++px) acc += static_cast<double>(w[static_cast<size_t>(c * 64 + px) * 512 + o]);
+    w3sum[c * 512 + o] = static_cast<float>(acc);
+}
+
+__global__ void __launch_bounds__(128) fold_bias_kernel(DevWeights w, float *b0, float *b1, float *b2, float *b3, float *b4, float *b5, const float *w3sum, int only = -1)
 {
     const int layer = blockIdx.y, o = blockIdx.x * blockDim.x + threadIdx.x;
     if (only >= 0 && layer != only) return;
@@ -1526,7 +1536,7 @@ __global__ void __launch_bounds__(128) fold_bias_kernel(DevWeights w, float *b0,
     } else if (layer == 3) {
         if (o >= 512) return;
         double add = 0.0;
-        for (int i = 0; i < 4096; ++i) add += static_cast<double>(w.f[18][static_cast<size_t>(i) * 512 + o]) * static_cast<double>(bn_shift(w.f[14], w.f[15], w.f[16], w.f[17], i >> 6));
+        for (int c = 0; c < 64; ++c) add += static_cast<double>(w3sum[c * 512 + o]) * static_cast<double>(bn_shift(w.f[14], w.f[15], w.f[16], w.f[17], c));
         b3[o] = __fadd_rn(w.f[19][o], static_cast<float>(add));
     } else if (layer == 4) {
         if (o < 512) b4[o] = w.f[21][o];
@@ -1737,6 +1747,7 @@ struct ahk_policy {
     uint16_t *wn[5] = {};    // [1] conv2 32 x 128, [2] conv3 64 x 512, [3] dense1 512 x 4096, [4] dense2 512 x 512
     CUtensorMap tm_w[5], tm_a[5];
     __nv_bfloat16 *act1 = nullptr, *act2 = nullptr, *act3 = nullptr, *h1 = nullptr, *h2 = nullptr;
+    float *w3sum = nullptr;    // [64][512]: dense1_px_sums_kernel
     double *bn_sums = nullptr; // ahk_policy_forward_train: [2][64] running sums of the layer being normalised
     uint64_t launches = 0;
 };
@@ -1958,9 +1969,11 @@ int ahk_policy_set_weights_dev(ahk_policy *p, const ahk_policy_weights *w_dev, v
     pack_nk_kernel<2><<<128, 256, 0, s>>>(w, p->wn[2], 512, 64);
     pack_nk_kernel<3><<<p->sms * 8, 256, 0, s>>>(w, p->wn[3], 4096, 512);
     pack_nk_kernel<4><<<p->sms * 4, 256, 0, s>>>(w, p->wn[4], 512, 512);
-    fold_bias_kernel<<<dim3(4, 6), 128, 0, s>>>(w, p->b[0], p->b[1], p->b[2], p->b[3], p->b[4], p->b[5]);
+    if (!p->w3sum) POL_CUDA(cudaMalloc(&p->w3sum, 64 * 512 * sizeof(float)));
+    dense1_px_sums_kernel<<<64, 512, 0, s>>>(w.f[18], p->w3sum);
+    fold_bias_kernel<<<dim3(4, 6), 128, 0, s>>>(w, p->b[0], p->b[1], p->b[2], p->b[3], p->b[4], p->b[5], p->w3sum);
     POL_CUDA(cudaGetLastError());
-    p->launches += 12;
+    p->launches += 13;
     return AHK_OK;
 }
 
@@ -2059,6 +2072,7 @@ void ahk_policy_destroy(ahk_policy *p)
     if (p->w1t) cudaFree(p->w1t);
     for (int i = 0; i < 5; ++i) if (p->wn[i]) cudaFree(p->wn[i]);
     if (p->bn_sums) cudaFree(p->bn_sums);
+    if (p->w3sum) cudaFree(p->w3sum);
     if (p->w1p) cudaFree(p->w1p);
     for (int i = 0; i < 7; ++i) if (p->ev[i]) cudaEventDestroy(p->ev[i]);
     for (int i = 0; i < 6; ++i) { if (p->gw[i]) cudaFree(p->gw[i]); if (p->gb[i]) cudaFree(p->gb[i]); }
@@ -2199,6 +2213,7 @@ int ahk_policy_forward_train(ahk_policy *p, const ahk_policy_weights *w_dev, con
     if (prev_device != p->device) POL_CUDA(cudaSetDevice(p->device));
     struct Restore { int prev, cur; ~Restore() { if (prev != cur) cudaSetDevice(prev); } } restore{prev_device, p->device};
     cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (!p->w3sum) POL_CUDA(cudaMalloc(&p->w3sum, 64 * 512 * sizeof(float)));
     if (!p->bn_sums) {
         POL_CUDA(cudaMalloc(&p->bn_sums, 2 * 64 * sizeof(double)));
         POL_CUDA(cudaMemsetAsync(p->bn_sums, 0, 2 * 64 * sizeof(double), s));
@@ -2212,19 +2227,19 @@ int ahk_policy_forward_train(ahk_policy *p, const ahk_policy_weights *w_dev, con
     // conv1 (no BatchNorm before it)
     POL_CUDA(cudaMemsetAsync(p->w1p, 0, static_cast<size_t>(c1p::kWBytes), s));
     pack_conv1p_kernel<<<(9 * 3 * 3 * 3 * 3 * 5 * 8 + 255) / 256, 256, 0, s>>>(w, p->w1p);
-    fold_bias_kernel<<<dim3(4, 6), 128, 0, s>>>(w, p->b[0], p->b[1], p->b[2], p->b[3], p->b[4], p->b[5], 0);
+    fold_bias_kernel<<<dim3(4, 6), 128, 0, s>>>(w, p->b[0], p->b[1], p->b[2], p->b[3], p->b[4], p->b[5], p->w3sum, 0);
     if (int rc = rgb_layer(p, a, 0, nullptr, nullptr, s)) return rc;
     bn_sums_kernel<8><<<stat_grid, 256, 0, s>>>(p->act1, static_cast<long long>(n) * kP1, p->bn_sums);
     bn_finalize_kernel<<<1, 64, 0, s>>>(p->bn_sums, 8, static_cast<long long>(n) * kP1, mean, var);
     // conv2 with BatchNorm 1 (batch statistics) folded in
     pack_b_kernel<1><<<16, 256, 0, s>>>(w, p->w[1], 128, 32, 1);
-    fold_bias_kernel<<<dim3(4, 6), 128, 0, s>>>(w, p->b[0], p->b[1], p->b[2], p->b[3], p->b[4], p->b[5], 1);
+    fold_bias_kernel<<<dim3(4, 6), 128, 0, s>>>(w, p->b[0], p->b[1], p->b[2], p->b[3], p->b[4], p->b[5], p->w3sum, 1);
     if (int rc = rgb_layer(p, a, 1, nullptr, nullptr, s)) return rc;
     bn_sums_kernel<32><<<stat_grid, 256, 0, s>>>(p->act2, static_cast<long long>(n) * kP2, p->bn_sums);
     bn_finalize_kernel<<<1, 64, 0, s>>>(p->bn_sums, 32, static_cast<long long>(n) * kP2, mean + 8, var + 8);
     // conv3
     pack_nk_kernel<2><<<128, 256, 0, s>>>(w, p->wn[2], 512, 64);
-    fold_bias_kernel<<<dim3(4, 6), 128, 0, s>>>(w, p->b[0], p->b[1], p->b[2], p->b[3], p->b[4], p->b[5], 2);
+    fold_bias_kernel<<<dim3(4, 6), 128, 0, s>>>(w, p->b[0], p->b[1], p->b[2], p->b[3], p->b[4], p->b[5], p->w3sum, 2);
     if (int rc = rgb_layer(p, a, 2, nullptr, nullptr, s)) return rc;
     bn_sums_kernel<64><<<stat_grid, 256, 0, s>>>(p->act3, static_cast<long long>(n) * kP3, p->bn_sums);
     bn_finalize_kernel<<<1, 64, 0, s>>>(p->bn_sums, 64, static_cast<long long>(n) * kP3, mean + 40, var + 40);
@@ -2232,7 +2247,8 @@ int ahk_policy_forward_train(ahk_policy *p, const ahk_policy_weights *w_dev, con
     pack_nk_kernel<3><<<p->sms * 8, 256, 0, s>>>(w, p->wn[3], 4096, 512);
     pack_nk_kernel<4><<<p->sms * 4, 256, 0, s>>>(w, p->wn[4], 512, 512);
     pack_b_kernel<5><<<32, 256, 0, s>>>(w, p->w[5], 512, 16, 1);
-    for (int layer = 3; layer < 6; ++layer) fold_bias_kernel<<<dim3(4, 6), 128, 0, s>>>(w, p->b[0], p->b[1], p->b[2], p->b[3], p->b[4], p->b[5], layer);
+    dense1_px_sums_kernel<<<64, 512, 0, s>>>(w.f[18], p->w3sum);
+    for (int layer = 3; layer < 6; ++layer) fold_bias_kernel<<<dim3(4, 6), 128, 0, s>>>(w, p->b[0], p->b[1], p->b[2], p->b[3], p->b[4], p->b[5], p->w3sum, layer);
     for (int layer = 3; layer < 6; ++layer)
         if (int rc = rgb_layer(p, a, layer, logits_dev, nullptr, s)) return rc;
     POL_CUDA(cudaGetLastError());

@@ -119,18 +119,19 @@ struct DenseWgrad {
     }
 };
 // conv (4x4, stride 2): dW[(tap, c)][o] = sum_{s, y, x} bn(r[s][2y + ky][2x + kx][c]) * dz[(s, y, x)][o]
+// (geometry as template constants: every division below is by a constant)
+template <int CIN, int CPAD, int IN, int OUT, int N>
 struct ConvWgrad {
     static constexpr bool kAAlongM = true, kBAlongN = true;
-    const __nv_bfloat16 *r; // [B][in_side^2][cpad]
-    const float *dz;        // [B * out_side^2][N]
-    float *dw;              // [16][cin][N]
+    const __nv_bfloat16 *r; // [B][IN^2][CPAD]
+    const float *dz;        // [B * OUT^2][N]
+    float *dw;              // [16][CIN][N]
     const float *s, *t;
-    int cin, cpad, in_side, out_side, N;
     __device__ float a(int m, int k) const
     {
-        const int tap = m / cin, c = m - tap * cin, ky = tap >> 2, kx = tap & 3;
-        const int px = out_side * out_side, smp = k / px, p = k - smp * px, y = p / out_side, x = p - y * out_side;
-        const float v = bf(r, (static_cast<long long>(smp) * in_side * in_side + (2 * y + ky) * in_side + 2 * x + kx) * cpad + c);
+        const int tap = m / CIN, c = m - tap * CIN, ky = tap >> 2, kx = tap & 3;
+        const int smp = k / (OUT * OUT), p = k - smp * (OUT * OUT), y = p / OUT, x = p - y * OUT;
+        const float v = bf(r, (static_cast<long long>(smp) * (IN * IN) + (2 * y + ky) * IN + 2 * x + kx) * CPAD + c);
         return fmaf(s[c], v, t[c]);
     }
     __device__ float b(int k, int n) const { return dz[static_cast<long long>(k) * N + n]; }
@@ -163,30 +164,68 @@ struct DenseDgrad {
 // transposed 4x4 stride-2 convolution, one PARITY CLASS (py, px) of the input pixels per launch: input pixel (Y, X) =
 // (2 y' + py, 2 x' + px) receives taps ky = py + 2 jy, kx = px + 2 jx from output pixel (y' - jy, x' - jx):
 // da[s][Y][X][c] = sum_{jy, jx, o} dz[s][y' - jy][x' - jx][o] * W[ky][kx][c][o]      (K = 4 * cout, no zero taps)
+template <int CIN, int CPAD, int COUT, int IN, int OUT>
 struct ConvDgrad {
     static constexpr bool kAAlongM = false, kBAlongN = false;
-    const float *dz; // [B][out_side^2][cout]
-    const float *w;  // Keras [16][cin][cout]
-    float *da;       // [B][in_side^2][cpad]
-    int cin, cpad, cout, in_side, out_side, py, px, ny, nx; // ny x nx input pixels of this parity per sample
+    const float *dz; // [B][OUT^2][COUT]
+    const float *w;  // Keras [16][CIN][COUT]
+    float *da;       // [B][IN^2][CPAD]
+    int py, px, ny, nx; // parity class; ny x nx input pixels of this parity per sample
     __device__ float a(int m, int k) const
     {
         const int per = ny * nx, smp = m / per, p = m - smp * per, yq = p / nx, xq = p - yq * nx;
-        const int j = k / cout, o = k - j * cout, y = yq - (j >> 1), x = xq - (j & 1);
-        if (y < 0 || x < 0 || y >= out_side || x >= out_side) return 0.0f;
-        return dz[(static_cast<long long>(smp) * out_side * out_side + y * out_side + x) * cout + o];
+        const int j = k / COUT, o = k - j * COUT, y = yq - (j >> 1), x = xq - (j & 1);
+        if (y < 0 || x < 0 || y >= OUT || x >= OUT) return 0.0f;
+        return dz[(static_cast<long long>(smp) * (OUT * OUT) + y * OUT + x) * COUT + o];
     }
     __device__ float b(int k, int n) const
     {
-        const int j = k / cout, o = k - j * cout, ky = py + 2 * (j >> 1), kx = px + 2 * (j & 1);
-        return w[(static_cast<long long>(ky * 4 + kx) * cin + n) * cout + o];
+        const int j = k / COUT, o = k - j * COUT, ky = py + 2 * (j >> 1), kx = px + 2 * (j & 1);
+        return w[(static_cast<long long>(ky * 4 + kx) * CIN + n) * COUT + o];
     }
     __device__ void store(int m, int n, float v, bool) const
     {
         const int per = ny * nx, smp = m / per, p = m - smp * per, yq = p / nx, xq = p - yq * nx;
-        da[(static_cast<long long>(smp) * in_side * in_side + (2 * yq + py) * in_side + 2 * xq + px) * cpad + n] = v;
+        da[(static_cast<long long>(smp) * (IN * IN) + (2 * yq + py) * IN + 2 * xq + px) * CPAD + n] = v;
     }
 };
+
+// conv2's transposed convolution (da1, 5 channels) as a DIRECT kernel: the 4 x 4 x 5 x 32 kernel (10 KB) sits in constant
+// memory, one launch per parity class with the class as template constants, so every weight is an immediate constant
+// operand of its FFMA and the only loads are the 128-byte gradient rows: 640 FMAs per thread against 32 16-byte loads.
+// (As a functor GEMM with N = 5 it was bound by the shared-memory return path: 3.4 ms per 4096 samples.)
+__constant__ float c_w2[16 * 5 * 32];
+template <int PY, int PX>
+__global__ void __launch_bounds__(128) conv2_dgrad_kernel(const float *__restrict__ dz2, int n, float *__restrict__ da1)
+{
+    constexpr int NY = PY ? 20 : 21, NX = PX ? 20 : 21;
+    const int i = blockIdx.x * 128 + threadIdx.x;
+    if (i >= n * NY * NX) return;
+    const int smp = i / (NY * NX), p = i - smp * (NY * NX), yq = p / NX, xq = p - yq * NX;
+    float acc[5] = {0, 0, 0, 0, 0};
+#pragma unroll
+    for (int jy = 0; jy < 2; ++jy)
+#pragma unroll
+        for (int jx = 0; jx < 2; ++jx) {
+            const int y = yq - jy, x = xq - jx;
+            if (y < 0 || x < 0 || y >= 19 || x >= 19) continue;
+            constexpr int kDummy = 0; (void)kDummy;
+            const float4 *src = reinterpret_cast<const float4 *>(dz2 + (static_cast<size_t>(smp) * kP2 + y * 19 + x) * 32);
+            const int tap = (PY + 2 * jy) * 4 + PX + 2 * jx; // compile-time after unrolling
+#pragma unroll
+            for (int o4 = 0; o4 < 8; ++o4) {
+                const float4 d = __ldg(src + o4);
+#pragma unroll
+                for (int c = 0; c < 5; ++c) {
+                    const float *w = c_w2 + (tap * 5 + c) * 32 + o4 * 4;
+                    acc[c] = fmaf(d.x, w[0], fmaf(d.y, w[1], fmaf(d.z, w[2], fmaf(d.w, w[3], acc[c]))));
+                }
+            }
+        }
+    float *out = da1 + (static_cast<size_t>(smp) * kP1 + (2 * yq + PY) * 41 + 2 * xq + PX) * 8;
+    *reinterpret_cast<float4 *>(out) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+    out[4] = acc[4];
+}
 
 // ------------------------------------------------------------------------------------------------ small kernels
 // column sums: out[c] = sum_rows x[row][pitch * .. + c]  (bias gradients)
@@ -275,41 +314,82 @@ __global__ void bn_affine_kernel(const float *gamma, const float *beta, const fl
 }
 
 // conv1 weight gradient: dW1[ky][kx][c][o] = sum_{s, y, x} ((pix[s][c][3y + ky][3x + kx] - 128) / 128) * dz1[s][y][x][o]
-// (c = stacked plane: age * 3 + colour, newest frame first, processor.py:47-49).  A CTA owns a run of (sample, output row)
-// pairs: the 8 input rows of the 9 planes (9 KB of uint8) and the 41 x 5 gradients of the row go to shared memory, thread
-// (c, ky, kx) — 576 of them — keeps its 5 sums in registers: per output pixel one shared byte, one conversion and 5 FMAs
-// against broadcast gradients.  Partial sums are added to dW1 with atomics at the end.
-__global__ void __launch_bounds__(576) conv1_wgrad_kernel(const uint8_t *__restrict__ frames, int n, int head, const float *__restrict__ dz1,
-                                                          float *__restrict__ dw, float *__restrict__ dz_colsum_unused)
+// (c = stacked plane: age * 3 + colour, newest frame first, processor.py:47-49).  A unit = (sample, 4 output rows): the 17
+// input rows of the 9 planes (22 KB of uint8) and the 4 x 41 x 5 gradients go to shared memory with cp.async, double
+// buffered, so the next unit's loads run under this unit's arithmetic; thread (c, ky, kx) — 576 of them — keeps its 5 sums in
+// registers: per output pixel one shared byte, one conversion and 5 FMAs against broadcast gradients.  Partial sums are
+// added to dW1 with atomics at the end.  (One output row per unit, single buffered: 4.2 ms per 4096 samples, bound by the
+// latency of its staging loads; profiles/fit_launches_r2.csv.)
+namespace c1w {
+constexpr int kRowsOut = 4, kRowsIn = 3 * (kRowsOut - 1) + 8, kPitch = 144, kUnitsPerSample = (41 + kRowsOut - 1) / kRowsOut;
+constexpr int kImgBytes = 9 * kRowsIn * kPitch, kDzBytes = kRowsOut * 41 * 8 * 4, kStage = kImgBytes + kDzBytes; // 22 032 + 5 248
+}
+__device__ __forceinline__ void cp16(void *dst, const void *src)
 {
-    __shared__ __align__(16) uint8_t s_img[9][8][144]; // row pitch 144: the four kernel rows of a warp fall into different banks
-    __shared__ __align__(16) float s_dz[41][8];
-    const int tid = threadIdx.x, c = tid >> 6, ky = (tid >> 3) & 7, kx = tid & 7;
-    float acc[5] = {0, 0, 0, 0, 0};
-    const int units = n * 41;
-    for (int u = blockIdx.x; u < units; u += gridDim.x) {
-        const int smp = u / 41, y = u - smp * 41;
-        __syncthreads();
-        for (int i = tid; i < 9 * 8 * 8; i += 576) { // 16-byte vectors: plane, row, 8 vectors per row
-            const int pl = i >> 6, row = (i >> 3) & 7, v = i & 7, age = pl / 3, col = pl - age * 3;
-            const uint8_t *src = frames + ((static_cast<size_t>((head + 3 - age) % 3) * n + smp) * 3 + col) * (128 * 128) + (3 * y + row) * 128 + v * 16;
-            *reinterpret_cast<uint4 *>(&s_img[pl][row][v * 16]) = __ldg(reinterpret_cast<const uint4 *>(src));
-        }
-        for (int i = tid; i < 41 * 8; i += 576) s_dz[i >> 3][i & 7] = dz1[(static_cast<size_t>(smp) * kP1 + y * 41) * 8 + i];
-        __syncthreads();
-        const uint8_t *rowp = &s_img[c][ky][kx];
-#pragma unroll 4
-        for (int x = 0; x < 41; ++x) {
-            const float v = static_cast<float>(rowp[3 * x]);
-            const float4 d = *reinterpret_cast<const float4 *>(&s_dz[x][0]);
-            const float d4 = s_dz[x][4];
-            acc[0] = fmaf(v, d.x, acc[0]); acc[1] = fmaf(v, d.y, acc[1]); acc[2] = fmaf(v, d.z, acc[2]); acc[3] = fmaf(v, d.w, acc[3]);
-            acc[4] = fmaf(v, d4, acc[4]);
-        }
-    }
-    float *out = dw + ((ky * 8 + kx) * 9 + c) * 5;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(static_cast<uint32_t>(__cvta_generic_to_shared(dst))), "l"(src) : "memory");
+}
+// Thread = (output row r of the unit, plane c, ky parity, kx): FOUR taps ky = kyp, kyp + 2, kyp + 4, kyp + 6 against the same
+// broadcast gradients — with one tap per thread the kernel was bound by the shared-memory return path (every thread fetched
+// the pixel's 20 bytes of gradient for 5 FMAs: 4.2 ms per 4096 samples whatever the staging did).
+__global__ void __launch_bounds__(576) conv1_wgrad_kernel(const uint8_t *__restrict__ frames, int n, int head, const float *__restrict__ dz1,
+                                                          float *__restrict__ dw)
+{
+    using namespace c1w;
+    extern __shared__ __align__(16) uint8_t smem[];
+    const int tid = threadIdx.x, r = tid / 144, rem = tid - r * 144, c = rem >> 4, kyp = (rem >> 3) & 1, kx = rem & 7;
+    float acc[4][5];
 #pragma unroll
-    for (int o = 0; o < 5; ++o) atomicAdd(out + o, acc[o] * (1.0f / 128.0f));
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int o = 0; o < 5; ++o) acc[i][o] = 0.0f;
+    const int units = n * kUnitsPerSample;
+    auto stage = [&](int u, int buf) {
+        const int smp = u / kUnitsPerSample, y0 = (u - smp * kUnitsPerSample) * kRowsOut;
+        uint8_t *img = smem + buf * kStage;
+        float *dzs = reinterpret_cast<float *>(img + kImgBytes);
+        for (int i = tid; i < 9 * kRowsIn * 8; i += 576) { // 16-byte vectors: plane, row, 8 vectors per row
+            const int pl = i / (kRowsIn * 8), rm = i - pl * (kRowsIn * 8), row = rm >> 3, v = rm & 7, age = pl / 3, col = pl - age * 3;
+            const int yy = 3 * y0 + row;
+            if (yy < 128)
+                cp16(img + (pl * kRowsIn + row) * kPitch + v * 16,
+                     frames + ((static_cast<size_t>((head + 3 - age) % 3) * n + smp) * 3 + col) * (128 * 128) + yy * 128 + v * 16);
+        }
+        for (int i = tid; i < kRowsOut * 41 * 2; i += 576) { // gradients: 32 bytes per output pixel; rows past 40 are zeros
+            const int px = i >> 1, rr = px / 41;
+            if (y0 + rr < 41) cp16(dzs + i * 4, dz1 + (static_cast<size_t>(smp) * kP1 + y0 * 41) * 8 + i * 4);
+            else *reinterpret_cast<float4 *>(dzs + i * 4) = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    int buf = 0;
+    if (static_cast<int>(blockIdx.x) < units) stage(blockIdx.x, 0);
+    for (int u = blockIdx.x; u < units; u += gridDim.x, buf ^= 1) {
+        const int next = u + gridDim.x;
+        if (next < units) { stage(next, buf ^ 1); asm volatile("cp.async.wait_group 1;" ::: "memory"); }
+        else asm volatile("cp.async.wait_group 0;" ::: "memory");
+        __syncthreads();
+        const uint8_t *img = smem + buf * kStage;
+        const float *dr = reinterpret_cast<const float *>(img + kImgBytes) + r * 41 * 8;
+        const uint8_t *rowp = img + (c * kRowsIn + 3 * r + kyp) * kPitch + kx;
+#pragma unroll 2
+        for (int x = 0; x < 41; ++x) {
+            const float4 d = *reinterpret_cast<const float4 *>(dr + x * 8);
+            const float d4 = dr[x * 8 + 4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const float v = static_cast<float>(rowp[2 * i * kPitch + 3 * x]);
+                acc[i][0] = fmaf(v, d.x, acc[i][0]); acc[i][1] = fmaf(v, d.y, acc[i][1]); acc[i][2] = fmaf(v, d.z, acc[i][2]);
+                acc[i][3] = fmaf(v, d.w, acc[i][3]); acc[i][4] = fmaf(v, d4, acc[i][4]);
+            }
+        }
+        __syncthreads(); // the buffer is restaged two units later
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        float *out = dw + (((kyp + 2 * i) * 8 + kx) * 9 + c) * 5;
+#pragma unroll
+        for (int o = 0; o < 5; ++o) atomicAdd(out + o, acc[i][o] * (1.0f / 128.0f));
+    }
 }
 // dW1 -= sum dz1 (the "- 128 / 128" of the normalisation): every tap sees every output pixel once
 __global__ void conv1_wgrad_shift_kernel(float *__restrict__ dw, const float *__restrict__ db)
@@ -539,13 +619,15 @@ int ahk_train_backward(ahk_trainer *t, ahk_policy *p, const ahk_policy_weights *
     }
     // ---- conv3: dW3 = im2col(bn2(r2))^T dz3, db3, da2 = transposed conv (4 parity classes)
     {
-        ConvWgrad f{r2, t->dz3, gf[C3W], s2, t2, 32, 32, 19, 8, 64};
-        TR_CUDA((run_gemm<ConvWgrad>(f, 512, 64, n * 64, ctas, s)));
+        using W3 = ConvWgrad<32, 32, 19, 8, 64>;
+        W3 f{r2, t->dz3, gf[C3W], s2, t2};
+        TR_CUDA((run_gemm<W3>(f, 512, 64, n * 64, ctas, s)));
         colsum_kernel<<<min(ctas, n * 16), 256, 0, s>>>(t->dz3, static_cast<long long>(n) * 64, 64, 64, gf[C3B]);
         for (int cls = 0; cls < 4; ++cls) {
             const int py = cls >> 1, px = cls & 1, ny = py ? 9 : 10, nx = px ? 9 : 10;
-            ConvDgrad d{t->dz3, wf[C3W], t->da2, 32, 32, 64, 19, 8, py, px, ny, nx};
-            TR_CUDA((run_gemm<ConvDgrad, 64, 32, 4, 2>(d, n * ny * nx, 32, 4 * 64, 1, s)));
+            using D3 = ConvDgrad<32, 32, 64, 19, 8>;
+            D3 d{t->dz3, wf[C3W], t->da2, py, px, ny, nx};
+            TR_CUDA((run_gemm<D3, 128, 32, 8, 2>(d, n * ny * nx, 32, 4 * 64, 1, s)));
         }
     }
     // ---- BatchNorm 2 + ReLU backward
@@ -557,14 +639,15 @@ int ahk_train_backward(ahk_trainer *t, ahk_policy *p, const ahk_policy_weights *
     }
     // ---- conv2: dW2 = im2col(bn1(r1))^T dz2 (80 x 32), db2, da1 (5 channels of 8)
     {
-        ConvWgrad f{r1, t->dz2, gf[C2W], s1, t1, 5, 8, 41, 19, 32};
-        TR_CUDA((run_gemm<ConvWgrad, 16, 32, 1, 2>(f, 80, 32, n * kP2, ctas, s)));
+        using W2 = ConvWgrad<5, 8, 41, 19, 32>;
+        W2 f{r1, t->dz2, gf[C2W], s1, t1};
+        TR_CUDA((run_gemm<W2, 80, 32, 5, 2>(f, 80, 32, n * kP2, ctas, s))); // the whole 80 x 32 gradient is one tile: split K over the CTAs
         colsum_kernel<<<min(ctas, n * 32), 256, 0, s>>>(t->dz2, static_cast<long long>(n) * kP2, 32, 32, gf[C2B]);
-        for (int cls = 0; cls < 4; ++cls) {
-            const int py = cls >> 1, px = cls & 1, ny = py ? 20 : 21, nx = px ? 20 : 21;
-            ConvDgrad d{t->dz2, wf[C2W], t->da1, 5, 8, 32, 41, 19, py, px, ny, nx};
-            TR_CUDA((run_gemm<ConvDgrad, 128, 8, 4, 1>(d, n * ny * nx, 5, 4 * 32, 1, s)));
-        }
+        TR_CUDA(cudaMemcpyToSymbolAsync(c_w2, wf[C2W], sizeof(float) * 16 * 5 * 32, 0, cudaMemcpyDeviceToDevice, s));
+        conv2_dgrad_kernel<0, 0><<<(n * 21 * 21 + 127) / 128, 128, 0, s>>>(t->dz2, n, t->da1);
+        conv2_dgrad_kernel<0, 1><<<(n * 21 * 20 + 127) / 128, 128, 0, s>>>(t->dz2, n, t->da1);
+        conv2_dgrad_kernel<1, 0><<<(n * 20 * 21 + 127) / 128, 128, 0, s>>>(t->dz2, n, t->da1);
+        conv2_dgrad_kernel<1, 1><<<(n * 20 * 20 + 127) / 128, 128, 0, s>>>(t->dz2, n, t->da1);
     }
     // ---- BatchNorm 1 + ReLU backward, conv1 weight gradient
     {
@@ -574,7 +657,12 @@ int ahk_train_backward(ahk_trainer *t, ahk_policy *p, const ahk_policy_weights *
         TR_CUDA(cudaMemsetAsync(t->sums, 0, 128 * 8, s));
         colsum_kernel<<<min(ctas, n * 41), 256, 0, s>>>(t->dz1, rows, 8, 8, t->affine + 208); // 8 sums: the 5 bias gradients + 3 zeros
         TR_CUDA(cudaMemcpyAsync(gf[C1B], t->affine + 208, 5 * 4, cudaMemcpyDeviceToDevice, s));
-        conv1_wgrad_kernel<<<min(t->sms * 2, n * 41), 576, 0, s>>>(frames_dev, n, head, t->dz1, gf[C1W], nullptr);
+        static bool prepared = false;
+        if (!prepared) {
+            TR_CUDA(cudaFuncSetAttribute(conv1_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * c1w::kStage));
+            prepared = true;
+        }
+        conv1_wgrad_kernel<<<min(t->sms * 3, n * c1w::kUnitsPerSample), 576, 2 * c1w::kStage, s>>>(frames_dev, n, head, t->dz1, gf[C1W]);
         conv1_wgrad_shift_kernel<<<(576 * 5 + 255) / 256, 256, 0, s>>>(gf[C1W], gf[C1B]);
         TR_CUDA(cudaMemsetAsync(t->affine + 208, 0, 8 * 4, s));
     }

@@ -38,6 +38,7 @@ enum Epi {
     kMaskBf16 = 2,     // out_bf16[row][n0 + c] = bf16(acc) where mask_bf16[row][n0 + c] > 0, else 0    (ReLU backward on the fly)
     kAtomicF32 = 3,    // atomicAdd(out_f32[row][n0 + c], acc * scale)                                   (split-K weight gradients)
     kStoreF32 = 4,     // out_f32[row][n0 + c] = acc * scale
+    kMaskBoth = 5,     // kMaskBf16 and the same values as float32 into out_f32
 };
 
 struct Args {
@@ -223,22 +224,24 @@ __global__ void __launch_bounds__(kCta, 1) gemm_tma_kernel(Args g, const __grid_
                 }
                 if (!row_ok) continue;
                 constexpr int kCols = N < 32 ? N : 32;
-                if (kEpi == kBiasReluBf16 || kEpi == kBiasBf16 || kEpi == kMaskBf16) {
+                if (kEpi == kBiasReluBf16 || kEpi == kBiasBf16 || kEpi == kMaskBf16 || kEpi == kMaskBoth) {
+                    constexpr bool kMasked = kEpi == kMaskBf16 || kEpi == kMaskBoth;
                     __nv_bfloat16 *out = g.out_bf16 + row * g.out_pitch + n0 + c0;
-                    const __nv_bfloat16 *mask = kEpi == kMaskBf16 ? g.mask_bf16 + row * g.out_pitch + n0 + c0 : nullptr;
+                    const __nv_bfloat16 *mask = kMasked ? g.mask_bf16 + row * g.out_pitch + n0 + c0 : nullptr;
 #pragma unroll
                     for (int c = 0; c < kCols; c += 8) {
                         if (c0 + c >= n_here) break;
                         uint32_t pk[4];
                         uint4 mk = make_uint4(0, 0, 0, 0);
-                        if (kEpi == kMaskBf16) mk = *reinterpret_cast<const uint4 *>(mask + c);
+                        if (kMasked) mk = *reinterpret_cast<const uint4 *>(mask + c);
 #pragma unroll
                         for (int j = 0; j < 4; ++j) {
                             float lo = __uint_as_float(v[c + 2 * j]), hi = __uint_as_float(v[c + 2 * j + 1]);
-                            if (kEpi == kMaskBf16) {
+                            if (kMasked) {
                                 const uint32_t m2 = (&mk.x)[j]; // two bf16: positive iff sign clear and not zero
                                 lo = (m2 & 0x7FFFu) != 0u && (m2 & 0x8000u) == 0u ? lo : 0.0f;
                                 hi = (m2 & 0x7FFF0000u) != 0u && (m2 & 0x80000000u) == 0u ? hi : 0.0f;
+                                if (kEpi == kMaskBoth) *reinterpret_cast<float2 *>(g.out_f32 + row * g.out_pitch + n0 + c0 + c + 2 * j) = make_float2(lo, hi);
                             } else {
                                 lo += g.bias[n0 + c0 + c + 2 * j];
                                 hi += g.bias[n0 + c0 + c + 2 * j + 1];

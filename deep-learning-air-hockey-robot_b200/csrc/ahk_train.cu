@@ -19,6 +19,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
 
 #include "../../include/ahk.h"
 #include "ahk_gemm.cuh"
@@ -398,6 +400,18 @@ __global__ void conv1_wgrad_shift_kernel(float *__restrict__ dw, const float *__
     if (i < 576 * 5) dw[i] -= db[i % 5];
 }
 
+// float32 Keras weights -> the bf16 [N = in][K = out] operand of the data-gradient GEMMs; keras_perm: row n = pixel * 64 + channel
+// of the copy is Keras row channel * 64 + pixel (dense1's input order here vs Flatten of (C, H, W))
+__global__ void __launch_bounds__(256) cast_weights_kernel(const float *__restrict__ w, __nv_bfloat16 *__restrict__ out, int rows, int cols, int keras_perm)
+{
+    const size_t total = static_cast<size_t>(rows) * cols;
+    for (size_t i = blockIdx.x * 256ull + threadIdx.x; i < total; i += gridDim.x * 256ull) {
+        const int n = static_cast<int>(i / cols), k = static_cast<int>(i - static_cast<size_t>(n) * cols);
+        const int src = keras_perm ? (n & 63) * 64 + (n >> 6) : n;
+        out[i] = __float2bfloat16_rn(w[static_cast<size_t>(src) * cols + k]);
+    }
+}
+
 // ------------------------------------------------------------------------------------------------ optimizer
 struct Segments { ahk_param_segment seg[24]; int count; };
 
@@ -484,6 +498,9 @@ struct ahk_trainer {
     // gradients with respect to layer inputs / pre-activations (float32) and bf16 copies where a tensor-core GEMM reads them
     float *dz5 = nullptr, *dz4 = nullptr, *da3 = nullptr, *dz3 = nullptr, *da2 = nullptr, *dz2 = nullptr, *da1 = nullptr, *dz1 = nullptr;
     __nv_bfloat16 *dz5h = nullptr, *dz4h = nullptr;
+    __nv_bfloat16 *w5h = nullptr, *w4p = nullptr; // bf16 [in][out] copies of dense2 / dense1 (rows in this file's input order) for the data-gradient GEMMs
+    CUtensorMap tm_dz5h, tm_dz4h, tm_w5h, tm_w4p;
+    bool simt_dense = false;  // A/B switch AHK_TRAIN_DENSE=simt: dense data gradients on the functor GEMM
     float *affine = nullptr;  // s1[8] t1[8] s2[32] t2[32] s3[64] t3[64]
     double *sums = nullptr;   // [2][64] BatchNorm backward sums; [128..129] gradient norm^2, penalty
     uint64_t launches = 0;
@@ -535,6 +552,13 @@ int ahk_trainer_create(int device, int max_batch, ahk_trainer **out)
     if (e == cudaSuccess) e = cudaMalloc(&t->dz1, nb * kP1 * 8 * 4);
     if (e == cudaSuccess) e = cudaMalloc(&t->dz5h, nb * 512 * 2);
     if (e == cudaSuccess) e = cudaMalloc(&t->dz4h, nb * 512 * 2);
+    if (e == cudaSuccess) e = cudaMalloc(&t->w5h, 512 * 512 * 2);
+    if (e == cudaSuccess) e = cudaMalloc(&t->w4p, 4096 * 512 * 2);
+    if (e == cudaSuccess) e = ahk::tg::matrix_map(&t->tm_dz5h, t->dz5h, nb, 512, 64, 128);
+    if (e == cudaSuccess) e = ahk::tg::matrix_map(&t->tm_dz4h, t->dz4h, nb, 512, 64, 128);
+    if (e == cudaSuccess) e = ahk::tg::matrix_map(&t->tm_w5h, t->w5h, 512, 512, 64, 256);
+    if (e == cudaSuccess) e = ahk::tg::matrix_map(&t->tm_w4p, t->w4p, 4096, 512, 64, 256);
+    if (const char *sw = getenv("AHK_TRAIN_DENSE")) t->simt_dense = strcmp(sw, "simt") == 0;
     if (e == cudaSuccess) e = cudaMalloc(&t->affine, 256 * 4);
     if (e == cudaSuccess) e = cudaMalloc(&t->sums, 160 * 8);
     if (e == cudaSuccess) e = cudaMemset(t->sums, 0, 160 * 8);
@@ -552,7 +576,7 @@ void ahk_trainer_destroy(ahk_trainer *t)
     if (!t) return;
     DeviceGuard guard(t->device);
     cudaFree(t->dz5); cudaFree(t->dz4); cudaFree(t->da3); cudaFree(t->dz3); cudaFree(t->da2); cudaFree(t->dz2); cudaFree(t->da1); cudaFree(t->dz1);
-    cudaFree(t->dz5h); cudaFree(t->dz4h); cudaFree(t->affine); cudaFree(t->sums);
+    cudaFree(t->dz5h); cudaFree(t->dz4h); cudaFree(t->w5h); cudaFree(t->w4p); cudaFree(t->affine); cudaFree(t->sums);
     delete t;
 }
 
@@ -598,8 +622,17 @@ int ahk_train_backward(ahk_trainer *t, ahk_policy *p, const ahk_policy_weights *
         TR_CUDA((run_gemm<DenseWgrad>(f, 512, 512, n, ctas, s)));
         colsum_kernel<<<min(ctas, n), 256, 0, s>>>(t->dz5, n, 256, 512, gf[D2B]);
         colsum_kernel<<<min(ctas, n), 256, 0, s>>>(t->dz5 + 256, n, 256, 512, gf[D2B] + 256);
-        DenseDgrad d{t->dz5, wf[D2W], t->dz4, h1, t->dz4h, 512, 512, 0};
-        TR_CUDA((run_gemm<DenseDgrad>(d, n, 512, 512, 1, s)));
+        if (t->simt_dense) {
+            DenseDgrad d{t->dz5, wf[D2W], t->dz4, h1, t->dz4h, 512, 512, 0};
+            TR_CUDA((run_gemm<DenseDgrad>(d, n, 512, 512, 1, s)));
+        } else { // tcgen05: dz5 (bf16) [n][512 out] x W5 (bf16) [512 in][512 out]^T, ReLU mask of h1 in the epilogue
+            namespace tg = ahk::tg;
+            cast_weights_kernel<<<t->sms * 2, 256, 0, s>>>(wf[D2W], t->w5h, 512, 512, 0);
+            tg::Args g{};
+            g.tiles_m = (n + 127) / 128; g.blocks_n = 2; g.k_chunks = 8; g.k_splits = 1; g.m_total = n; g.n_valid = 256;
+            g.out_bf16 = t->dz4h; g.out_f32 = t->dz4; g.mask_bf16 = h1; g.out_pitch = 512; g.scale = 1.0f;
+            TR_CUDA((tg::launch<256, 128, tg::kLinear, false, tg::kMaskBoth, 4>(g, t->tm_dz5h, t->tm_w5h, t->sms, s)));
+        }
     }
     // ---- dense1: dW4 = bn3(r3)^T dz4 (Keras row order channel * 64 + pixel), db4, da3 = dz4 W4^T
     {
@@ -607,8 +640,17 @@ int ahk_train_backward(ahk_trainer *t, ahk_policy *p, const ahk_policy_weights *
         TR_CUDA((run_gemm<DenseWgrad>(f, 4096, 512, n, ctas, s)));
         colsum_kernel<<<min(ctas, n), 256, 0, s>>>(t->dz4, n, 256, 512, gf[D1B]);
         colsum_kernel<<<min(ctas, n), 256, 0, s>>>(t->dz4 + 256, n, 256, 512, gf[D1B] + 256);
-        DenseDgrad d{t->dz4, wf[D1W], t->da3, nullptr, nullptr, 512, 4096, 1};
-        TR_CUDA((run_gemm<DenseDgrad>(d, n, 4096, 512, 1, s)));
+        if (t->simt_dense) {
+            DenseDgrad d{t->dz4, wf[D1W], t->da3, nullptr, nullptr, 512, 4096, 1};
+            TR_CUDA((run_gemm<DenseDgrad>(d, n, 4096, 512, 1, s)));
+        } else { // tcgen05: dz4 (bf16) [n][512] x W4 (bf16, rows in (pixel, channel) order) [4096][512]^T -> da3 float32
+            namespace tg = ahk::tg;
+            cast_weights_kernel<<<t->sms * 4, 256, 0, s>>>(wf[D1W], t->w4p, 4096, 512, 1);
+            tg::Args g{};
+            g.tiles_m = (n + 127) / 128; g.blocks_n = 16; g.k_chunks = 8; g.k_splits = 1; g.m_total = n; g.n_valid = 256;
+            g.out_f32 = t->da3; g.out_pitch = 4096; g.scale = 1.0f;
+            TR_CUDA((tg::launch<256, 128, tg::kLinear, false, tg::kStoreF32, 4>(g, t->tm_dz4h, t->tm_w4p, t->sms, s)));
+        }
     }
     // ---- BatchNorm 3 + ReLU backward: da3 [n * 64 rows][64] -> dz3, d gamma3, d beta3
     {

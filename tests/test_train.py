@@ -5,8 +5,9 @@ the CPU — and against the Keras optimizer restatements (oracle/rl_ref.py, orac
 Tolerances.  The forward kernels keep activations in bf16 (8 significant bits) and accumulate in float32; the backward
 kernels accumulate in float32 over those activations with the float32 master weights.  Two comparisons:
   * given the SAME activations (train_ref.fit_gradients_given_activations: autograd whose ReLU outputs take the kernels'
-    values and masks), every gradient tensor agrees to 1e-4 of its largest entry (measured 1e-6: float32 summation order) —
-    this pins the backward arithmetic;
+    values and masks), every gradient tensor agrees to 1e-4 of its largest entry (measured 1e-6: float32 summation order)
+    with the dense data gradients on the float32 functor GEMM (AHK_TRAIN_DENSE=simt) — this pins the backward arithmetic —
+    and to 3e-2 (measured 1.5e-2) in the default configuration, where those two GEMMs run on tcgen05 with bf16 operands;
   * against a pure float32 forward + backward the logits agree to 2e-2 of the logit range and the batch statistics to
     1e-2, but a bf16 forward flips the sign of ~0.3 % of the near-zero pre-activations, and every flipped ReLU is a whole
     gradient element: per-tensor L2 differences of 8-25 % at random initialisation (tools/train_parity.py,
@@ -34,9 +35,12 @@ GRAD_NAMES = ("conv1_w", "conv1_b", "bn1_gamma", "bn1_beta", "conv2_w", "conv2_b
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("n", [32, 200])
-def test_forward_backward_match_autograd(cuda, table, n):
+@pytest.mark.parametrize("n,dense", [(32, "tcgen05"), (200, "tcgen05"), (32, "simt"), (200, "simt")])
+def test_forward_backward_match_autograd(cuda, table, n, dense, monkeypatch):
+    """dense: the two dense data-gradient GEMMs on the tcgen05 GEMM (bf16 operands: the default) or on the float32 functor
+    GEMM (AHK_TRAIN_DENSE=simt, the A/B switch) — the latter pins the arithmetic to 1e-4, the former is bounded at 3e-2."""
     import train_ref
+    monkeypatch.setenv("AHK_TRAIN_DENSE", dense)
     from gym_air_hockey_b200.policy import keras_default_init
     from gym_air_hockey_b200.train import NativeTrainer
     torch = cuda
@@ -61,7 +65,8 @@ def test_forward_backward_match_autograd(cuda, table, n):
         got = tr.tensor(name, tr.grads).cpu().numpy()
         tight[name] = float(np.abs(got - given[name]).max() / max(np.abs(given[name]).max(), 1e-30))
         loose[name] = float(np.linalg.norm(got - want[name]) / max(np.linalg.norm(want[name]), 1e-30))
-    assert not {k: v for k, v in tight.items() if not v <= 1e-4}, tight
+    bound = 1e-4 if dense == "simt" else 3e-2  # measured 6e-6 / 1.5e-2
+    assert not {k: v for k, v in tight.items() if not v <= bound}, tight
     assert not {k: v for k, v in loose.items() if not v <= 0.6}, loose  # 5-element sums of cancelling terms (d beta1) reach 0.36
     flat_got = np.concatenate([tr.tensor(name, tr.grads).cpu().numpy().ravel() for name in GRAD_NAMES])
     flat_ref = np.concatenate([want[name].ravel() for name in GRAD_NAMES])

@@ -30,6 +30,13 @@ enum AMode {
     kConv2 = 1,    // 4-D map over act1 [sample][41 x 41][8]: element, x2 (stride 2 px), y2 (stride 2 rows), sample; box [32][19][6][1]
     kConv3 = 2,    // 4-D map over act2 [sample][19 x 19][32]: element, x3, y3, sample; box [64][8][8][2]
     kLinearMn = 3, // A is MN-major: 2-D map [M][K]: two boxes [64][chunk K rows] per chunk at (tile * 128 + 64 h, kc * chunk)
+    // conv3 weight gradient: A = im2col(act2)^T, MN-major, through the conv3 map with ONE sample per box [64][8][8][1]: M tile = kernel
+    // row ky (4 taps x 32 channels), the two boxes are its tap pairs, K chunk kc = sample kc (its 64 output pixels)
+    kConv3Wgrad = 4,
+    // conv3 data gradient, one parity class (Args::py, px) per launch: A = dz3 [sample][8][8][64] through a 4-D map, box [64][10][10][1]
+    // at (0, -jx, -jy, sample): row r = yq * 10 + xq of the tile is input pixel (2 yq + py, 2 xq + px), chunk j = (jy, jx) its tap
+    // (py + 2 jy, px + 2 jx); out-of-range output pixels are the copy engine's zero fill.  B rows = tap * 32 of the Keras kernel.
+    kConv3Dgrad = 5,
 };
 // what the epilogue does with the accumulator
 enum Epi {
@@ -52,6 +59,7 @@ struct Args {
     float *out_f32;
     long long out_pitch;             // elements per output row
     float scale;
+    int py, px;                      // kConv3Dgrad: parity class of the input pixels
 };
 
 // shared-memory matrix descriptor of a swizzled tile (cute::UMMA::SmemDescriptor, version 1): K-major: rows of `span` bytes
@@ -81,10 +89,11 @@ __device__ __forceinline__ void tma_4d(void *dst, const CUtensorMap *tm, int c0,
 
 // kBRes > 0: the whole B operand (kBRes K chunks) is loaded once per CTA and stays in shared memory (conv layers: blocks_n = 1)
 template <int N, int kSpan, int kAMode, bool kBMn, int kBRes = 0> struct Cfg {
-    static constexpr int kChunkK = kAMode == kLinearMn || kBMn ? 64 : kSpan / 2;                  // K elements per chunk
-    static constexpr int kARows = kAMode == kConv2 ? 114 : 128;
-    static constexpr int kABytes = kAMode == kLinearMn ? 2 * 64 * 128 : 128 * kSpan;             // smem footprint of an A stage (conv2: 114 rows arrive)
-    static constexpr int kATx = kAMode == kLinearMn ? 2 * 64 * 128 : kARows * kSpan;             // bytes the copies deliver
+    static constexpr bool kAMn = kAMode == kLinearMn || kAMode == kConv3Wgrad;
+    static constexpr int kChunkK = kAMn || kBMn ? 64 : kSpan / 2;                                  // K elements per chunk
+    static constexpr int kARows = kAMode == kConv2 ? 114 : (kAMode == kConv3Dgrad ? 100 : 128);
+    static constexpr int kABytes = kAMn ? 2 * 64 * 128 : 128 * kSpan;                            // smem footprint of an A stage (conv2: 114 rows arrive)
+    static constexpr int kATx = kAMn ? 2 * 64 * 128 : kARows * kSpan;                            // bytes the copies deliver
     static constexpr int kBBytes = kBMn ? (N / 64) * 64 * 128 : N * kSpan;
     static constexpr int kStageBytes = (kABytes + (kBRes ? 0 : kBBytes) + 1023) / 1024 * 1024;
     static constexpr int kResBytes = kBRes * kBBytes;
@@ -96,7 +105,7 @@ template <int N, int kSpan, int kAMode, bool kBMn, int kEpi, int kStages, int kB
 __global__ void __launch_bounds__(kCta, 1) gemm_tma_kernel(Args g, const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b)
 {
     using C = Cfg<N, kSpan, kAMode, kBMn, kBRes>;
-    static_assert(kSpan == 128 || (kSpan == 64 && kAMode != kLinearMn && !kBMn), "MN-major tiles use the 128-byte swizzle");
+    static_assert(kSpan == 128 || (kSpan == 64 && !C::kAMn && !kBMn), "MN-major tiles use the 128-byte swizzle");
     static_assert(N % 16 == 0 && N >= 16 && N <= 256 && (!kBMn || N % 64 == 0), "N");
     extern __shared__ __align__(128) uint8_t smem_unaligned[];
     uint8_t *s_res = smem_unaligned + ((1024u - (smem_u32(smem_unaligned) & 1023u)) & 1023u); // swizzle atoms are 1024-byte aligned
@@ -149,10 +158,15 @@ __global__ void __launch_bounds__(kCta, 1) gemm_tma_kernel(Args g, const __grid_
                     else if (kAMode == kLinearMn) {
                         tma_2d(sa, &tm_a, tm_i * 128, kc * C::kChunkK, &s_full[st]);
                         tma_2d(sa + 64 * 128, &tm_a, tm_i * 128 + 64, kc * C::kChunkK, &s_full[st]);
-                    } else if (kAMode == kConv2) tma_4d(sa, &tm_a, kc * (41 * 8), 0, (tm_i & 3) * 6, tm_i >> 2, &s_full[st]);          // kc = ky
+                    } else if (kAMode == kConv3Wgrad) {
+                        tma_4d(sa, &tm_a, (tm_i * 19) * 32, 0, 0, kc, &s_full[st]);
+                        tma_4d(sa + 64 * 128, &tm_a, (tm_i * 19 + 2) * 32, 0, 0, kc, &s_full[st]);
+                    } else if (kAMode == kConv3Dgrad) tma_4d(sa, &tm_a, 0, -(kc & 1), -(kc >> 1), tm_i, &s_full[st]);                   // kc = jy * 2 + jx
+                    else if (kAMode == kConv2) tma_4d(sa, &tm_a, kc * (41 * 8), 0, (tm_i & 3) * 6, tm_i >> 2, &s_full[st]);             // kc = ky
                     else tma_4d(sa, &tm_a, ((kc >> 1) * 19 + (kc & 1) * 2) * 32, 0, 0, tm_i * 2, &s_full[st]);                           // kc = ky * 2 + half
                     if (kBRes) continue;
-                    if (kBMn) {
+                    if (kAMode == kConv3Dgrad) tma_2d(sb, &tm_b, 0, ((g.py + 2 * (kc >> 1)) * 4 + g.px + 2 * (kc & 1)) * 32, &s_full[st]);
+                    else if (kBMn) {
 #pragma unroll
                         for (int h = 0; h < N / 64; ++h) tma_2d(sb + h * 64 * 128, &tm_b, nb * N + h * 64, kc * C::kChunkK, &s_full[st]);
                     } else tma_2d(sb, &tm_b, kc * C::kChunkK, nb * N, &s_full[st]);
@@ -161,7 +175,7 @@ __global__ void __launch_bounds__(kCta, 1) gemm_tma_kernel(Args g, const __grid_
         }
     } else if (warp == 1) {
         // ---------------------------------------------------------------- MMA issue (whole warp, one elected lane)
-        constexpr uint32_t kIdesc = idesc_bf16(N, kAMode == kLinearMn, kBMn);
+        constexpr uint32_t kIdesc = idesc_bf16(N, C::kAMn, kBMn);
         uint32_t fill = 0;
         if (kBRes && my_items > 0) mbar_wait_sleep(&s_bfull, 0);
         for (int it = 0; it < my_items; ++it) {
@@ -177,9 +191,9 @@ __global__ void __launch_bounds__(kCta, 1) gemm_tma_kernel(Args g, const __grid_
                 // K-major: 8-row groups 8 * span apart, a K = 16 step is 32 bytes inside the swizzle span.
                 // MN-major: K rows of 128 bytes (64 MN elements), 8-row K groups 1024 apart (SBO), next 64 MN elements at LBO
                 // = one box; a K = 16 step is two K groups = 2048 bytes.
-                const uint64_t ad = kAMode == kLinearMn ? sw_desc(sa, 64 * 128, 1024, 2u) : sw_desc(sa, 16, 8 * kSpan, kLayout);
+                const uint64_t ad = C::kAMn ? sw_desc(sa, 64 * 128, 1024, 2u) : sw_desc(sa, 16, 8 * kSpan, kLayout);
                 const uint64_t bd = kBMn ? sw_desc(sb, 64 * 128, 1024, 2u) : sw_desc(sb, 16, 8 * kSpan, kLayout);
-                constexpr uint32_t kAStep = kAMode == kLinearMn ? 2048 / 16 : 32 / 16, kBStep = kBMn ? 2048 / 16 : 32 / 16;
+                constexpr uint32_t kAStep = C::kAMn ? 2048 / 16 : 32 / 16, kBStep = kBMn ? 2048 / 16 : 32 / 16;
                 if (elect_one()) {
 #pragma unroll
                     for (int j = 0; j < C::kChunkK / 16; ++j)
@@ -203,6 +217,10 @@ __global__ void __launch_bounds__(kCta, 1) gemm_tma_kernel(Args g, const __grid_
                 const int y = r / 19, x = r - y * 19, y2 = (tm_i & 3) * 6 + y;
                 row_ok = r < 114 && y2 < 19;
                 row = static_cast<long long>(tm_i >> 2) * 361 + y2 * 19 + x;
+            } else if (kAMode == kConv3Dgrad) { // tile = sample: r = yq * 10 + xq -> input pixel (2 yq + py, 2 xq + px) of the 19 x 19 plane
+                const int yq = r / 10, xq = r - yq * 10, y = 2 * yq + g.py, x = 2 * xq + g.px;
+                row_ok = r < 100 && y < 19 && x < 19;
+                row = static_cast<long long>(tm_i) * 361 + y * 19 + x;
             } else {
                 row = static_cast<long long>(tm_i) * 128 + r;
                 row_ok = row < (kAMode == kConv3 ? static_cast<long long>(g.m_total) * 64 : static_cast<long long>(g.m_total));

@@ -286,7 +286,7 @@ template <int kCPad>
 __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const float *__restrict__ da, const __nv_bfloat16 *__restrict__ r, long long rows,
                                                            const float *__restrict__ gamma, const float *__restrict__ mean, const float *__restrict__ var,
                                                            int c_real, int da_pitch, const double *__restrict__ sums, float *__restrict__ dz,
-                                                           float *__restrict__ dgamma, float *__restrict__ dbeta)
+                                                           float *__restrict__ dgamma, float *__restrict__ dbeta, __nv_bfloat16 *__restrict__ dz_bf16 = nullptr)
 {
     const long long total = rows * kCPad;
     for (long long i = static_cast<long long>(blockIdx.x) * 256 + threadIdx.x; i < total; i += static_cast<long long>(gridDim.x) * 256) {
@@ -299,6 +299,7 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const float *__restri
             out = rv > 0.0f ? gamma[c] * inv * (da[row * da_pitch + c] - db - xh * dg) : 0.0f;
         }
         dz[i] = out;
+        if (dz_bf16) dz_bf16[i] = __float2bfloat16_rn(out);
     }
     if (blockIdx.x == 0 && threadIdx.x < c_real) {
         dbeta[threadIdx.x] = static_cast<float>(sums[threadIdx.x]);
@@ -412,6 +413,25 @@ __global__ void __launch_bounds__(256) cast_weights_kernel(const float *__restri
     }
 }
 
+// dense1's weight gradient from the raw product G = r3^T dz4 (rows in (pixel, channel) order): the BatchNorm affine map
+// a3 = s3[c] r3 + t3[c] and Keras' row order (channel * 64 + pixel): dW[c * 64 + px][o] = s3[c] G[px * 64 + c][o] + t3[c] db[o]
+__global__ void __launch_bounds__(256) dense1_wgrad_fix_kernel(const float *__restrict__ g, const float *__restrict__ s3, const float *__restrict__ t3,
+                                                               const float *__restrict__ db, float *__restrict__ dw)
+{
+    for (int i = blockIdx.x * 256 + threadIdx.x; i < 4096 * 512; i += gridDim.x * 256) {
+        const int row = i >> 9, o = i & 511, c = row >> 6, px = row & 63;
+        dw[i] = fmaf(s3[c], g[(px * 64 + c) * 512 + o], t3[c] * db[o]);
+    }
+}
+
+// conv3's weight gradient from the raw product G = im2col(r2)^T dz3: dW[(tap, c)][o] = s2[c] G[(tap, c)][o] + t2[c] db[o]
+__global__ void __launch_bounds__(256) conv3_wgrad_fix_kernel(const float *__restrict__ g, const float *__restrict__ s2, const float *__restrict__ t2,
+                                                              const float *__restrict__ db, float *__restrict__ dw)
+{
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i < 512 * 64) dw[i] = fmaf(s2[(i >> 6) & 31], g[i], t2[(i >> 6) & 31] * db[i & 63]);
+}
+
 // ------------------------------------------------------------------------------------------------ optimizer
 struct Segments { ahk_param_segment seg[24]; int count; };
 
@@ -500,6 +520,9 @@ struct ahk_trainer {
     __nv_bfloat16 *dz5h = nullptr, *dz4h = nullptr;
     __nv_bfloat16 *w5h = nullptr, *w4p = nullptr; // bf16 [in][out] copies of dense2 / dense1 (rows in this file's input order) for the data-gradient GEMMs
     CUtensorMap tm_dz5h, tm_dz4h, tm_w5h, tm_w4p;
+    float *g4 = nullptr;      // [4096][512] raw dense1 weight gradient (tensor-core path); its head doubles as conv3's [512][64]
+    __nv_bfloat16 *dz3h = nullptr, *w3h = nullptr; // bf16 dz3 [n * 64][64] and Keras conv3 kernel [16 * 32][64] for the conv3 GEMMs
+    CUtensorMap tm_w3h;
     bool simt_dense = false;  // A/B switch AHK_TRAIN_DENSE=simt: dense data gradients on the functor GEMM
     float *affine = nullptr;  // s1[8] t1[8] s2[32] t2[32] s3[64] t3[64]
     double *sums = nullptr;   // [2][64] BatchNorm backward sums; [128..129] gradient norm^2, penalty
@@ -552,6 +575,10 @@ int ahk_trainer_create(int device, int max_batch, ahk_trainer **out)
     if (e == cudaSuccess) e = cudaMalloc(&t->dz1, nb * kP1 * 8 * 4);
     if (e == cudaSuccess) e = cudaMalloc(&t->dz5h, nb * 512 * 2);
     if (e == cudaSuccess) e = cudaMalloc(&t->dz4h, nb * 512 * 2);
+    if (e == cudaSuccess) e = cudaMalloc(&t->g4, 4096 * 512 * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&t->dz3h, nb * 4096 * 2);
+    if (e == cudaSuccess) e = cudaMalloc(&t->w3h, 512 * 64 * 2);
+    if (e == cudaSuccess) e = ahk::tg::matrix_map(&t->tm_w3h, t->w3h, 512, 64, 64, 32);
     if (e == cudaSuccess) e = cudaMalloc(&t->w5h, 512 * 512 * 2);
     if (e == cudaSuccess) e = cudaMalloc(&t->w4p, 4096 * 512 * 2);
     if (e == cudaSuccess) e = ahk::tg::matrix_map(&t->tm_dz5h, t->dz5h, nb, 512, 64, 128);
@@ -576,7 +603,7 @@ void ahk_trainer_destroy(ahk_trainer *t)
     if (!t) return;
     DeviceGuard guard(t->device);
     cudaFree(t->dz5); cudaFree(t->dz4); cudaFree(t->da3); cudaFree(t->dz3); cudaFree(t->da2); cudaFree(t->dz2); cudaFree(t->da1); cudaFree(t->dz1);
-    cudaFree(t->dz5h); cudaFree(t->dz4h); cudaFree(t->w5h); cudaFree(t->w4p); cudaFree(t->affine); cudaFree(t->sums);
+    cudaFree(t->dz5h); cudaFree(t->dz4h); cudaFree(t->w5h); cudaFree(t->w4p); cudaFree(t->g4); cudaFree(t->dz3h); cudaFree(t->w3h); cudaFree(t->affine); cudaFree(t->sums);
     delete t;
 }
 
@@ -618,8 +645,20 @@ int ahk_train_backward(ahk_trainer *t, ahk_policy *p, const ahk_policy_weights *
     }
     // ---- dense2: dW5 = h1^T dz5, db5, dz4 = (dz5 W5^T) . [h1 > 0]
     {
-        DenseWgrad f{h1, t->dz5, gf[D2W], nullptr, nullptr, 512, 512, 0};
-        TR_CUDA((run_gemm<DenseWgrad>(f, 512, 512, n, ctas, s)));
+        if (t->simt_dense) {
+            DenseWgrad f{h1, t->dz5, gf[D2W], nullptr, nullptr, 512, 512, 0};
+            TR_CUDA((run_gemm<DenseWgrad>(f, 512, 512, n, ctas, s)));
+        } else { // tcgen05, both operands MN-major (the reduction runs over the batch): dW5 [in][out] += h1^T dz5, split K, atomics
+            namespace tg = ahk::tg;
+            CUtensorMap ta, tb;
+            TR_CUDA(tg::matrix_map(&ta, h1, n, 512, 64, 64));
+            TR_CUDA(tg::matrix_map(&tb, t->dz5h, n, 512, 64, 64));
+            tg::Args g{};
+            const int chunks = (n + 63) / 64;
+            g.k_splits = chunks < 16 ? chunks : 16; g.k_chunks = (chunks + g.k_splits - 1) / g.k_splits;
+            g.tiles_m = 4; g.blocks_n = 2; g.m_total = 512; g.n_valid = 256; g.out_f32 = gf[D2W]; g.out_pitch = 512; g.scale = 1.0f;
+            TR_CUDA((tg::launch<256, 128, tg::kLinearMn, true, tg::kAtomicF32, 4>(g, ta, tb, t->sms, s)));
+        }
         colsum_kernel<<<min(ctas, n), 256, 0, s>>>(t->dz5, n, 256, 512, gf[D2B]);
         colsum_kernel<<<min(ctas, n), 256, 0, s>>>(t->dz5 + 256, n, 256, 512, gf[D2B] + 256);
         if (t->simt_dense) {
@@ -636,10 +675,24 @@ int ahk_train_backward(ahk_trainer *t, ahk_policy *p, const ahk_policy_weights *
     }
     // ---- dense1: dW4 = bn3(r3)^T dz4 (Keras row order channel * 64 + pixel), db4, da3 = dz4 W4^T
     {
-        DenseWgrad f{r3, t->dz4, gf[D1W], s3, t3, 4096, 512, 1};
-        TR_CUDA((run_gemm<DenseWgrad>(f, 4096, 512, n, ctas, s)));
         colsum_kernel<<<min(ctas, n), 256, 0, s>>>(t->dz4, n, 256, 512, gf[D1B]);
         colsum_kernel<<<min(ctas, n), 256, 0, s>>>(t->dz4 + 256, n, 256, 512, gf[D1B] + 256);
+        if (t->simt_dense) {
+            DenseWgrad f{r3, t->dz4, gf[D1W], s3, t3, 4096, 512, 1};
+            TR_CUDA((run_gemm<DenseWgrad>(f, 4096, 512, n, ctas, s)));
+        } else { // tcgen05: G = r3^T dz4 on the raw activations, then the BatchNorm affine map and Keras' row order in one pass
+            namespace tg = ahk::tg;
+            CUtensorMap ta, tb;
+            TR_CUDA(tg::matrix_map(&ta, r3, n, 4096, 64, 64));
+            TR_CUDA(tg::matrix_map(&tb, t->dz4h, n, 512, 64, 64));
+            TR_CUDA(zero(t->g4, 4096 * 512));
+            tg::Args g{};
+            const int chunks = (n + 63) / 64;
+            g.k_splits = chunks < 4 ? chunks : 4; g.k_chunks = (chunks + g.k_splits - 1) / g.k_splits;
+            g.tiles_m = 32; g.blocks_n = 2; g.m_total = 4096; g.n_valid = 256; g.out_f32 = t->g4; g.out_pitch = 512; g.scale = 1.0f;
+            TR_CUDA((tg::launch<256, 128, tg::kLinearMn, true, tg::kAtomicF32, 4>(g, ta, tb, t->sms, s)));
+            dense1_wgrad_fix_kernel<<<t->sms * 4, 256, 0, s>>>(t->g4, s3, t3, gf[D1B], gf[D1W]);
+        }
         if (t->simt_dense) {
             DenseDgrad d{t->dz4, wf[D1W], t->da3, nullptr, nullptr, 512, 4096, 1};
             TR_CUDA((run_gemm<DenseDgrad>(d, n, 4096, 512, 1, s)));
@@ -656,20 +709,49 @@ int ahk_train_backward(ahk_trainer *t, ahk_policy *p, const ahk_policy_weights *
     {
         const long long rows = static_cast<long long>(n) * 64;
         bn_bwd_sums_kernel<64><<<ctas, 256, 0, s>>>(t->da3, r3, rows, mean + 40, var + 40, 64, t->sums);
-        bn_bwd_apply_kernel<64><<<ctas * 2, 256, 0, s>>>(t->da3, r3, rows, wf[G3], mean + 40, var + 40, 64, 64, t->sums, t->dz3, gf[G3], gf[B3]);
+        bn_bwd_apply_kernel<64><<<ctas * 2, 256, 0, s>>>(t->da3, r3, rows, wf[G3], mean + 40, var + 40, 64, 64, t->sums, t->dz3, gf[G3], gf[B3], t->dz3h);
         TR_CUDA(cudaMemsetAsync(t->sums, 0, 128 * 8, s));
     }
     // ---- conv3: dW3 = im2col(bn2(r2))^T dz3, db3, da2 = transposed conv (4 parity classes)
     {
-        using W3 = ConvWgrad<32, 32, 19, 8, 64>;
-        W3 f{r2, t->dz3, gf[C3W], s2, t2};
-        TR_CUDA((run_gemm<W3>(f, 512, 64, n * 64, ctas, s)));
         colsum_kernel<<<min(ctas, n * 16), 256, 0, s>>>(t->dz3, static_cast<long long>(n) * 64, 64, 64, gf[C3B]);
-        for (int cls = 0; cls < 4; ++cls) {
-            const int py = cls >> 1, px = cls & 1, ny = py ? 9 : 10, nx = px ? 9 : 10;
-            using D3 = ConvDgrad<32, 32, 64, 19, 8>;
-            D3 d{t->dz3, wf[C3W], t->da2, py, px, ny, nx};
-            TR_CUDA((run_gemm<D3, 128, 32, 8, 2>(d, n * ny * nx, 32, 4 * 64, 1, s)));
+        if (t->simt_dense) {
+            using W3 = ConvWgrad<32, 32, 19, 8, 64>;
+            W3 f{r2, t->dz3, gf[C3W], s2, t2};
+            TR_CUDA((run_gemm<W3>(f, 512, 64, n * 64, ctas, s)));
+            for (int cls = 0; cls < 4; ++cls) {
+                const int py = cls >> 1, px = cls & 1, ny = py ? 9 : 10, nx = px ? 9 : 10;
+                using D3 = ConvDgrad<32, 32, 64, 19, 8>;
+                D3 d{t->dz3, wf[C3W], t->da2, py, px, ny, nx};
+                TR_CUDA((run_gemm<D3, 128, 32, 8, 2>(d, n * ny * nx, 32, 4 * 64, 1, s)));
+            }
+        } else { // both on tcgen05 (ahk_gemm.cuh: kConv3Wgrad, kConv3Dgrad): the tensor maps do the im2col / the transposed gather
+            namespace tg = ahk::tg;
+            CUtensorMap ta, tb, td;
+            { // act2 [sample][19 x 19][32] as conv3's im2col, one sample per box
+                const unsigned long long dims[4] = {static_cast<unsigned long long>(kP2) * 32, 8, 8, static_cast<unsigned long long>(n)}, strides[3] = {2 * 32 * 2, 2 * 19 * 32 * 2, static_cast<unsigned long long>(kP2) * 32 * 2};
+                const unsigned box[4] = {64, 8, 8, 1};
+                TR_CUDA(tg::encode_bf16_map(&ta, r2, 4, dims, strides, box, 128));
+            }
+            TR_CUDA(tg::matrix_map(&tb, t->dz3h, static_cast<unsigned long long>(n) * 64, 64, 64, 64));
+            { // dz3 [sample][8][8][64]: channel, x, y, sample
+                const unsigned long long dims[4] = {64, 8, 8, static_cast<unsigned long long>(n)}, strides[3] = {128, 1024, 8192};
+                const unsigned box[4] = {64, 10, 10, 1};
+                TR_CUDA(tg::encode_bf16_map(&td, t->dz3h, 4, dims, strides, box, 128));
+            }
+            TR_CUDA(zero(t->g4, 512 * 64));
+            tg::Args g{};
+            g.k_splits = n < 37 ? n : 37; g.k_chunks = (n + g.k_splits - 1) / g.k_splits;
+            g.tiles_m = 4; g.blocks_n = 1; g.m_total = 512; g.n_valid = 64; g.out_f32 = t->g4; g.out_pitch = 64; g.scale = 1.0f;
+            TR_CUDA((tg::launch<64, 128, tg::kConv3Wgrad, true, tg::kAtomicF32, 6>(g, ta, tb, t->sms, s)));
+            conv3_wgrad_fix_kernel<<<(512 * 64 + 255) / 256, 256, 0, s>>>(t->g4, s2, t2, gf[C3B], gf[C3W]);
+            cast_weights_kernel<<<32, 256, 0, s>>>(wf[C3W], t->w3h, 512, 64, 0);
+            tg::Args d{};
+            d.k_splits = 1; d.k_chunks = 4; d.tiles_m = n; d.blocks_n = 1; d.m_total = n; d.n_valid = 32; d.out_f32 = t->da2; d.out_pitch = 32; d.scale = 1.0f;
+            for (int cls = 0; cls < 4; ++cls) {
+                d.py = cls >> 1; d.px = cls & 1;
+                TR_CUDA((tg::launch<32, 128, tg::kConv3Dgrad, false, tg::kStoreF32, 8>(d, td, t->tm_w3h, t->sms, s)));
+            }
         }
     }
     // ---- BatchNorm 2 + ReLU backward

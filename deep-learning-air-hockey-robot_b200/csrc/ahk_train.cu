@@ -263,23 +263,34 @@ template <int kCPad>
 __global__ void __launch_bounds__(256) bn_bwd_sums_kernel(const float *__restrict__ da, const __nv_bfloat16 *__restrict__ r, long long rows,
                                                           const float *__restrict__ mean, const float *__restrict__ var, int da_pitch, double *__restrict__ sums)
 {
-    __shared__ float s_part[2][256];
-    const int c = threadIdx.x % kCPad, lanes = 256 / kCPad, rl = threadIdx.x / kCPad;
-    const float mu = mean[c], inv = rsqrtf(var[c] + kBnEps);
-    float sb = 0.0f, sg = 0.0f;
-    for (long long row = static_cast<long long>(blockIdx.x) * lanes + rl; row < rows; row += static_cast<long long>(gridDim.x) * lanes) {
-        const float d = da[row * da_pitch + c], xh = (bf(r, row * kCPad + c) - mu) * inv;
-        sb += d;
-        sg = fmaf(d, xh, sg);
+    constexpr int kVecs = kCPad / 8;
+    __shared__ float s_part[256][17];
+    const int tid = threadIdx.x, grp = tid % kVecs;
+    float mu[8], inv[8], sb[8], sg[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { mu[j] = mean[grp * 8 + j]; inv[j] = rsqrtf(var[grp * 8 + j] + kBnEps); sb[j] = 0.0f; sg[j] = 0.0f; }
+    const long long stride = static_cast<long long>(gridDim.x) * (256 / kVecs);
+    for (long long row = static_cast<long long>(blockIdx.x) * (256 / kVecs) + tid / kVecs; row < rows; row += stride) {
+        const long long at = row * kCPad + grp * 8;
+        const uint4 rv = __ldg(reinterpret_cast<const uint4 *>(r + at));
+        const float4 d0 = __ldg(reinterpret_cast<const float4 *>(da + at)), d1 = __ldg(reinterpret_cast<const float4 *>(da + at + 4));
+        const float dv[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
+        const uint32_t rw[4] = {rv.x, rv.y, rv.z, rv.w};
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float rr = __uint_as_float((j & 1) ? (rw[j >> 1] & 0xFFFF0000u) : (rw[j >> 1] << 16));
+            sb[j] += dv[j];
+            sg[j] = fmaf(dv[j], (rr - mu[j]) * inv[j], sg[j]);
+        }
     }
-    s_part[0][threadIdx.x] = sb;
-    s_part[1][threadIdx.x] = sg;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { s_part[tid][j] = sb[j]; s_part[tid][8 + j] = sg[j]; }
     __syncthreads();
-    if (threadIdx.x < 2 * kCPad) {
-        const int cc = threadIdx.x % kCPad, which = threadIdx.x / kCPad;
+    if (tid < kCPad * 2) {
+        const int c = tid % kCPad, which = tid / kCPad, g = c / 8, j = c % 8;
         double acc = 0.0;
-        for (int l = 0; l < lanes; ++l) acc += static_cast<double>(s_part[which][l * kCPad + cc]);
-        atomicAdd(sums + which * kCPad + cc, acc);
+        for (int t = g; t < 256; t += kVecs) acc += static_cast<double>(s_part[t][which * 8 + j]);
+        atomicAdd(sums + which * kCPad + c, acc);
     }
 }
 template <int kCPad>
@@ -288,18 +299,45 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const float *__restri
                                                            int c_real, int da_pitch, const double *__restrict__ sums, float *__restrict__ dz,
                                                            float *__restrict__ dgamma, float *__restrict__ dbeta, __nv_bfloat16 *__restrict__ dz_bf16 = nullptr)
 {
-    const long long total = rows * kCPad;
+    // per channel: dz = k[c] * (da - db[c] - (r - mu[c]) * inv[c] * dg[c]) where r > 0   (the 8 channels of a thread's vector from shared memory)
+    __shared__ float s_k[kCPad], s_db[kCPad], s_mu[kCPad], s_inv[kCPad], s_dg[kCPad];
+    if (threadIdx.x < kCPad) {
+        const int c = threadIdx.x;
+        const float inv = rsqrtf(var[c] + kBnEps);
+        s_inv[c] = inv;
+        s_mu[c] = mean[c];
+        s_k[c] = c < c_real ? gamma[c] * inv : 0.0f;
+        s_db[c] = static_cast<float>(sums[c] / static_cast<double>(rows));
+        s_dg[c] = static_cast<float>(sums[kCPad + c] / static_cast<double>(rows));
+    }
+    __syncthreads();
+    constexpr int kVecs = kCPad / 8; // a thread handles 8 consecutive channels of one row
+    const long long total = rows * kVecs;
     for (long long i = static_cast<long long>(blockIdx.x) * 256 + threadIdx.x; i < total; i += static_cast<long long>(gridDim.x) * 256) {
-        const int c = static_cast<int>(i % kCPad);
-        const long long row = i / kCPad;
-        float out = 0.0f;
-        if (c < c_real) {
-            const float inv = rsqrtf(var[c] + kBnEps), rv = bf(r, i), xh = (rv - mean[c]) * inv;
-            const float db = static_cast<float>(sums[c] / static_cast<double>(rows)), dg = static_cast<float>(sums[kCPad + c] / static_cast<double>(rows));
-            out = rv > 0.0f ? gamma[c] * inv * (da[row * da_pitch + c] - db - xh * dg) : 0.0f;
+        const int c0 = static_cast<int>(i % kVecs) * 8;
+        const long long at = i * 8;
+        const uint4 rv = __ldg(reinterpret_cast<const uint4 *>(r + at));
+        const float4 d0 = __ldg(reinterpret_cast<const float4 *>(da + at)), d1 = __ldg(reinterpret_cast<const float4 *>(da + at + 4));
+        const float dv[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
+        const uint32_t rw[4] = {rv.x, rv.y, rv.z, rv.w};
+        float out[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float rr = __uint_as_float((j & 1) ? (rw[j >> 1] & 0xFFFF0000u) : (rw[j >> 1] << 16));
+            const int c = c0 + j;
+            out[j] = rr > 0.0f ? s_k[c] * (dv[j] - s_db[c] - (rr - s_mu[c]) * s_inv[c] * s_dg[c]) : 0.0f;
         }
-        dz[i] = out;
-        if (dz_bf16) dz_bf16[i] = __float2bfloat16_rn(out);
+        *reinterpret_cast<float4 *>(dz + at) = make_float4(out[0], out[1], out[2], out[3]);
+        *reinterpret_cast<float4 *>(dz + at + 4) = make_float4(out[4], out[5], out[6], out[7]);
+        if (dz_bf16) {
+            uint32_t pk[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const __nv_bfloat162 h = __floats2bfloat162_rn(out[2 * j], out[2 * j + 1]);
+                pk[j] = *reinterpret_cast<const uint32_t *>(&h);
+            }
+            *reinterpret_cast<uint4 *>(dz_bf16 + at) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+        }
     }
     if (blockIdx.x == 0 && threadIdx.x < c_real) {
         dbeta[threadIdx.x] = static_cast<float>(sums[threadIdx.x]);

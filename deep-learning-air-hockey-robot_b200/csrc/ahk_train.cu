@@ -297,8 +297,11 @@ template <int kCPad>
 __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const float *__restrict__ da, const __nv_bfloat16 *__restrict__ r, long long rows,
                                                            const float *__restrict__ gamma, const float *__restrict__ mean, const float *__restrict__ var,
                                                            int c_real, int da_pitch, const double *__restrict__ sums, float *__restrict__ dz,
-                                                           float *__restrict__ dgamma, float *__restrict__ dbeta, __nv_bfloat16 *__restrict__ dz_bf16 = nullptr)
+                                                           float *__restrict__ dgamma, float *__restrict__ dbeta, __nv_bfloat16 *__restrict__ dz_bf16 = nullptr,
+                                                           float *__restrict__ dz_colsum = nullptr)
 {
+    // dz_colsum (nullable, zeroed by the caller): += column sums of dz — the bias gradient of the layer below, formed here
+    // instead of a second pass over dz.
     // per channel: dz = k[c] * (da - db[c] - (r - mu[c]) * inv[c] * dg[c]) where r > 0   (the 8 channels of a thread's vector from shared memory)
     __shared__ float s_k[kCPad], s_db[kCPad], s_mu[kCPad], s_inv[kCPad], s_dg[kCPad];
     if (threadIdx.x < kCPad) {
@@ -311,8 +314,9 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const float *__restri
         s_dg[c] = static_cast<float>(sums[kCPad + c] / static_cast<double>(rows));
     }
     __syncthreads();
-    constexpr int kVecs = kCPad / 8; // a thread handles 8 consecutive channels of one row
+    constexpr int kVecs = kCPad / 8; // a thread handles 8 consecutive channels of one row (always the same 8: 256 % kVecs == 0)
     const long long total = rows * kVecs;
+    float colsum[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     for (long long i = static_cast<long long>(blockIdx.x) * 256 + threadIdx.x; i < total; i += static_cast<long long>(gridDim.x) * 256) {
         const int c0 = static_cast<int>(i % kVecs) * 8;
         const long long at = i * 8;
@@ -326,6 +330,7 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const float *__restri
             const float rr = __uint_as_float((j & 1) ? (rw[j >> 1] & 0xFFFF0000u) : (rw[j >> 1] << 16));
             const int c = c0 + j;
             out[j] = rr > 0.0f ? s_k[c] * (dv[j] - s_db[c] - (rr - s_mu[c]) * s_inv[c] * s_dg[c]) : 0.0f;
+            colsum[j] += out[j];
         }
         *reinterpret_cast<float4 *>(dz + at) = make_float4(out[0], out[1], out[2], out[3]);
         *reinterpret_cast<float4 *>(dz + at + 4) = make_float4(out[4], out[5], out[6], out[7]);
@@ -337,6 +342,18 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const float *__restri
                 pk[j] = *reinterpret_cast<const uint32_t *>(&h);
             }
             *reinterpret_cast<uint4 *>(dz_bf16 + at) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+        }
+    }
+    if (dz_colsum) {
+        __shared__ float s_cs[256][9];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s_cs[threadIdx.x][j] = colsum[j];
+        __syncthreads();
+        if (threadIdx.x < kCPad) {
+            const int c = threadIdx.x, g = c / 8, j = c % 8;
+            float acc = 0.0f;
+            for (int t = g; t < 256; t += kVecs) acc += s_cs[t][j];
+            if (c < c_real) atomicAdd(dz_colsum + c, acc);
         }
     }
     if (blockIdx.x == 0 && threadIdx.x < c_real) {
@@ -356,27 +373,25 @@ __global__ void bn_affine_kernel(const float *gamma, const float *beta, const fl
 
 // conv1 weight gradient: dW1[ky][kx][c][o] = sum_{s, y, x} ((pix[s][c][3y + ky][3x + kx] - 128) / 128) * dz1[s][y][x][o]
 // (c = stacked plane: age * 3 + colour, newest frame first, processor.py:47-49).  A unit = (sample, 4 output rows): the 17
-// input rows of the 9 planes (22 KB of uint8) and the 4 x 41 x 5 gradients go to shared memory with cp.async, double
-// buffered, so the next unit's loads run under this unit's arithmetic; thread (c, ky, kx) — 576 of them — keeps its 5 sums in
-// registers: per output pixel one shared byte, one conversion and 5 FMAs against broadcast gradients.  Partial sums are
-// added to dW1 with atomics at the end.  (One output row per unit, single buffered: 4.2 ms per 4096 samples, bound by the
-// latency of its staging loads; profiles/fit_launches_r2.csv.)
+// input rows of the 9 planes are staged in shared memory as bf16 (0..255 is exact; a pixel is converted ONCE per unit, and
+// bf16 -> float32 in the inner loop is a shift, not a conversion-pipe instruction), the 4 x 41 x 5 gradients as float32.
+// Thread = (output row r of the unit, plane c, ky parity, kx): FOUR taps ky = kyp, kyp + 2, kyp + 4, kyp + 6 against the same
+// broadcast gradients, 20 sums in registers; three CTAs per SM overlap one CTA's staging with the others' arithmetic.
+// Partial sums are added to dW1 with atomics at the end.  History (per 4096 samples, profiles/fit_launches_r2*.csv): one tap
+// per thread, one output row per unit 4.2 ms (staging latency, then the shared-memory return path: every thread fetched the
+// pixel's 20 bytes of gradient for 5 FMAs); four taps per thread on uint8 pixels 3.2 ms (one I2F per 5 FMAs on the quarter-rate pipe).
 namespace c1w {
 constexpr int kRowsOut = 4, kRowsIn = 3 * (kRowsOut - 1) + 8, kPitch = 144, kUnitsPerSample = (41 + kRowsOut - 1) / kRowsOut;
-constexpr int kImgBytes = 9 * kRowsIn * kPitch, kDzBytes = kRowsOut * 41 * 8 * 4, kStage = kImgBytes + kDzBytes; // 22 032 + 5 248
+constexpr int kPlane = kRowsIn * kPitch + 16;                 // bf16 elements; + 16: planes fall into different bank groups
+constexpr int kImgBytes = 9 * kPlane * 2, kDzBytes = kRowsOut * 41 * 8 * 4, kSmem = kImgBytes + kDzBytes; // 44 352 + 5 248
 }
-__device__ __forceinline__ void cp16(void *dst, const void *src)
-{
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(static_cast<uint32_t>(__cvta_generic_to_shared(dst))), "l"(src) : "memory");
-}
-// Thread = (output row r of the unit, plane c, ky parity, kx): FOUR taps ky = kyp, kyp + 2, kyp + 4, kyp + 6 against the same
-// broadcast gradients — with one tap per thread the kernel was bound by the shared-memory return path (every thread fetched
-// the pixel's 20 bytes of gradient for 5 FMAs: 4.2 ms per 4096 samples whatever the staging did).
 __global__ void __launch_bounds__(576) conv1_wgrad_kernel(const uint8_t *__restrict__ frames, int n, int head, const float *__restrict__ dz1,
                                                           float *__restrict__ dw)
 {
     using namespace c1w;
     extern __shared__ __align__(16) uint8_t smem[];
+    uint16_t *img = reinterpret_cast<uint16_t *>(smem);
+    float *dzs = reinterpret_cast<float *>(smem + kImgBytes);
     const int tid = threadIdx.x, r = tid / 144, rem = tid - r * 144, c = rem >> 4, kyp = (rem >> 3) & 1, kx = rem & 7;
     float acc[4][5];
 #pragma unroll
@@ -384,46 +399,47 @@ __global__ void __launch_bounds__(576) conv1_wgrad_kernel(const uint8_t *__restr
 #pragma unroll
         for (int o = 0; o < 5; ++o) acc[i][o] = 0.0f;
     const int units = n * kUnitsPerSample;
-    auto stage = [&](int u, int buf) {
+    for (int u = blockIdx.x; u < units; u += gridDim.x) {
         const int smp = u / kUnitsPerSample, y0 = (u - smp * kUnitsPerSample) * kRowsOut;
-        uint8_t *img = smem + buf * kStage;
-        float *dzs = reinterpret_cast<float *>(img + kImgBytes);
-        for (int i = tid; i < 9 * kRowsIn * 8; i += 576) { // 16-byte vectors: plane, row, 8 vectors per row
+        __syncthreads(); // the previous unit's reads are over
+        for (int i = tid; i < 9 * kRowsIn * 8; i += 576) { // 16 pixels per step: plane, row, 8 vectors per row
             const int pl = i / (kRowsIn * 8), rm = i - pl * (kRowsIn * 8), row = rm >> 3, v = rm & 7, age = pl / 3, col = pl - age * 3;
             const int yy = 3 * y0 + row;
-            if (yy < 128)
-                cp16(img + (pl * kRowsIn + row) * kPitch + v * 16,
-                     frames + ((static_cast<size_t>((head + 3 - age) % 3) * n + smp) * 3 + col) * (128 * 128) + yy * 128 + v * 16);
+            uint4 px = make_uint4(0, 0, 0, 0);
+            if (yy < 128) px = __ldg(reinterpret_cast<const uint4 *>(frames + ((static_cast<size_t>((head + 3 - age) % 3) * n + smp) * 3 + col) * (128 * 128) + yy * 128 + v * 16));
+            const uint32_t w[4] = {px.x, px.y, px.z, px.w};
+            uint32_t h[8]; // 16 bf16: the top halves of the floats 0..255
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float f0 = static_cast<float>(w[j] & 0xFFu), f1 = static_cast<float>((w[j] >> 8) & 0xFFu), f2 = static_cast<float>((w[j] >> 16) & 0xFFu),
+                            f3 = static_cast<float>(w[j] >> 24);
+                h[2 * j] = __byte_perm(__float_as_uint(f0), __float_as_uint(f1), 0x7632);
+                h[2 * j + 1] = __byte_perm(__float_as_uint(f2), __float_as_uint(f3), 0x7632);
+            }
+            uint4 *dst = reinterpret_cast<uint4 *>(img + pl * kPlane + row * kPitch + v * 16);
+            dst[0] = make_uint4(h[0], h[1], h[2], h[3]);
+            dst[1] = make_uint4(h[4], h[5], h[6], h[7]);
         }
         for (int i = tid; i < kRowsOut * 41 * 2; i += 576) { // gradients: 32 bytes per output pixel; rows past 40 are zeros
-            const int px = i >> 1, rr = px / 41;
-            if (y0 + rr < 41) cp16(dzs + i * 4, dz1 + (static_cast<size_t>(smp) * kP1 + y0 * 41) * 8 + i * 4);
-            else *reinterpret_cast<float4 *>(dzs + i * 4) = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            const int rr = (i >> 1) / 41;
+            float4 d = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            if (y0 + rr < 41) d = __ldg(reinterpret_cast<const float4 *>(dz1 + (static_cast<size_t>(smp) * kP1 + y0 * 41) * 8 + i * 4));
+            *reinterpret_cast<float4 *>(dzs + i * 4) = d;
         }
-        asm volatile("cp.async.commit_group;" ::: "memory");
-    };
-    int buf = 0;
-    if (static_cast<int>(blockIdx.x) < units) stage(blockIdx.x, 0);
-    for (int u = blockIdx.x; u < units; u += gridDim.x, buf ^= 1) {
-        const int next = u + gridDim.x;
-        if (next < units) { stage(next, buf ^ 1); asm volatile("cp.async.wait_group 1;" ::: "memory"); }
-        else asm volatile("cp.async.wait_group 0;" ::: "memory");
         __syncthreads();
-        const uint8_t *img = smem + buf * kStage;
-        const float *dr = reinterpret_cast<const float *>(img + kImgBytes) + r * 41 * 8;
-        const uint8_t *rowp = img + (c * kRowsIn + 3 * r + kyp) * kPitch + kx;
+        const float *dr = dzs + r * 41 * 8;
+        const uint16_t *rowp = img + c * kPlane + (3 * r + kyp) * kPitch + kx;
 #pragma unroll 2
         for (int x = 0; x < 41; ++x) {
             const float4 d = *reinterpret_cast<const float4 *>(dr + x * 8);
             const float d4 = dr[x * 8 + 4];
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
-                const float v = static_cast<float>(rowp[2 * i * kPitch + 3 * x]);
+                const float v = __uint_as_float(static_cast<uint32_t>(rowp[2 * i * kPitch + 3 * x]) << 16);
                 acc[i][0] = fmaf(v, d.x, acc[i][0]); acc[i][1] = fmaf(v, d.y, acc[i][1]); acc[i][2] = fmaf(v, d.z, acc[i][2]);
                 acc[i][3] = fmaf(v, d.w, acc[i][3]); acc[i][4] = fmaf(v, d4, acc[i][4]);
             }
         }
-        __syncthreads(); // the buffer is restaged two units later
     }
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
@@ -747,12 +763,11 @@ int ahk_train_backward(ahk_trainer *t, ahk_policy *p, const ahk_policy_weights *
     {
         const long long rows = static_cast<long long>(n) * 64;
         bn_bwd_sums_kernel<64><<<ctas, 256, 0, s>>>(t->da3, r3, rows, mean + 40, var + 40, 64, t->sums);
-        bn_bwd_apply_kernel<64><<<ctas * 2, 256, 0, s>>>(t->da3, r3, rows, wf[G3], mean + 40, var + 40, 64, 64, t->sums, t->dz3, gf[G3], gf[B3], t->dz3h);
+        bn_bwd_apply_kernel<64><<<ctas * 2, 256, 0, s>>>(t->da3, r3, rows, wf[G3], mean + 40, var + 40, 64, 64, t->sums, t->dz3, gf[G3], gf[B3], t->dz3h, gf[C3B]);
         TR_CUDA(cudaMemsetAsync(t->sums, 0, 128 * 8, s));
     }
     // ---- conv3: dW3 = im2col(bn2(r2))^T dz3, db3, da2 = transposed conv (4 parity classes)
     {
-        colsum_kernel<<<min(ctas, n * 16), 256, 0, s>>>(t->dz3, static_cast<long long>(n) * 64, 64, 64, gf[C3B]);
         if (t->simt_dense) {
             using W3 = ConvWgrad<32, 32, 19, 8, 64>;
             W3 f{r2, t->dz3, gf[C3W], s2, t2};
@@ -796,7 +811,7 @@ int ahk_train_backward(ahk_trainer *t, ahk_policy *p, const ahk_policy_weights *
     {
         const long long rows = static_cast<long long>(n) * kP2;
         bn_bwd_sums_kernel<32><<<ctas, 256, 0, s>>>(t->da2, r2, rows, mean + 8, var + 8, 32, t->sums);
-        bn_bwd_apply_kernel<32><<<ctas * 2, 256, 0, s>>>(t->da2, r2, rows, wf[G2], mean + 8, var + 8, 32, 32, t->sums, t->dz2, gf[G2], gf[B2]);
+        bn_bwd_apply_kernel<32><<<ctas * 2, 256, 0, s>>>(t->da2, r2, rows, wf[G2], mean + 8, var + 8, 32, 32, t->sums, t->dz2, gf[G2], gf[B2], nullptr, gf[C2B]);
         TR_CUDA(cudaMemsetAsync(t->sums, 0, 128 * 8, s));
     }
     // ---- conv2: dW2 = im2col(bn1(r1))^T dz2 (80 x 32), db2, da1 (5 channels of 8)
@@ -804,7 +819,6 @@ int ahk_train_backward(ahk_trainer *t, ahk_policy *p, const ahk_policy_weights *
         using W2 = ConvWgrad<5, 8, 41, 19, 32>;
         W2 f{r1, t->dz2, gf[C2W], s1, t1};
         TR_CUDA((run_gemm<W2, 80, 32, 5, 2>(f, 80, 32, n * kP2, ctas, s))); // the whole 80 x 32 gradient is one tile: split K over the CTAs
-        colsum_kernel<<<min(ctas, n * 32), 256, 0, s>>>(t->dz2, static_cast<long long>(n) * kP2, 32, 32, gf[C2B]);
         TR_CUDA(cudaMemcpyToSymbolAsync(c_w2, wf[C2W], sizeof(float) * 16 * 5 * 32, 0, cudaMemcpyDeviceToDevice, s));
         conv2_dgrad_kernel<0, 0><<<(n * 21 * 21 + 127) / 128, 128, 0, s>>>(t->dz2, n, t->da1);
         conv2_dgrad_kernel<0, 1><<<(n * 21 * 20 + 127) / 128, 128, 0, s>>>(t->dz2, n, t->da1);
@@ -815,18 +829,15 @@ int ahk_train_backward(ahk_trainer *t, ahk_policy *p, const ahk_policy_weights *
     {
         const long long rows = static_cast<long long>(n) * kP1;
         bn_bwd_sums_kernel<8><<<ctas, 256, 0, s>>>(t->da1, r1, rows, mean, var, 8, t->sums);
-        bn_bwd_apply_kernel<8><<<ctas * 2, 256, 0, s>>>(t->da1, r1, rows, wf[G1], mean, var, 5, 8, t->sums, t->dz1, gf[G1], gf[B1]);
+        bn_bwd_apply_kernel<8><<<ctas * 2, 256, 0, s>>>(t->da1, r1, rows, wf[G1], mean, var, 5, 8, t->sums, t->dz1, gf[G1], gf[B1], nullptr, gf[C1B]);
         TR_CUDA(cudaMemsetAsync(t->sums, 0, 128 * 8, s));
-        colsum_kernel<<<min(ctas, n * 41), 256, 0, s>>>(t->dz1, rows, 8, 8, t->affine + 208); // 8 sums: the 5 bias gradients + 3 zeros
-        TR_CUDA(cudaMemcpyAsync(gf[C1B], t->affine + 208, 5 * 4, cudaMemcpyDeviceToDevice, s));
         static bool prepared = false;
         if (!prepared) {
-            TR_CUDA(cudaFuncSetAttribute(conv1_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * c1w::kStage));
+            TR_CUDA(cudaFuncSetAttribute(conv1_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, c1w::kSmem));
             prepared = true;
         }
-        conv1_wgrad_kernel<<<min(t->sms * 3, n * c1w::kUnitsPerSample), 576, 2 * c1w::kStage, s>>>(frames_dev, n, head, t->dz1, gf[C1W]);
+        conv1_wgrad_kernel<<<min(t->sms * 3, n * c1w::kUnitsPerSample), 576, c1w::kSmem, s>>>(frames_dev, n, head, t->dz1, gf[C1W]);
         conv1_wgrad_shift_kernel<<<(576 * 5 + 255) / 256, 256, 0, s>>>(gf[C1W], gf[C1B]);
-        TR_CUDA(cudaMemsetAsync(t->affine + 208, 0, 8 * 4, s));
     }
     TR_CUDA(cudaGetLastError());
     t->launches += 45;

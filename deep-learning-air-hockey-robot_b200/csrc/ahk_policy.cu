@@ -1413,6 +1413,165 @@ cudaError_t launch_ws(const Args &a, int tiles, int sms, cudaStream_t s)
     return cudaGetLastError();
 }
 
+// ------------------------------------------------------------------------------------------------ conv2, parity arrays
+// conv2 (5 -> 32 channels, 4x4, stride 2: models.py:30-32) on act1 [sample][41 x 41][8 channels] (16 bytes per pixel).
+// Both earlier forms moved every act1 pixel to shared memory four times — conv_ws_kernel's cp.async gather (0.155 ms per
+// 8192 samples, bound by shared-memory wavefronts) and the tensor-map im2col (0.21-0.25 ms, bound by L2 -> SM traffic:
+// 1.2 GB for 220 MB of activations).  Here a sample is copied ONCE (one 26.9 KB bulk copy) and rearranged by four warps
+// into four PARITY ARRAYS P[y & 1][x & 1][y >> 1][x >> 1] (24 slots per row of 21): with the stride of 2 folded into the
+// parity, output pixel m = y2 * 24 + x2 needs, for tap (ky, kx), slot m + (ky >> 1) * 24 + (kx >> 1) of array
+// P[ky & 1][kx & 1] — LINEAR in m.  So the A operand of every MMA is a plain window of an array: rows 16 bytes apart
+// (no-swizzle K-major core matrices), the two K cores of an MMA = taps kx and kx + 2 = neighbouring slots (LBO = 16: the
+// second core of row m is the first of row m + 1).  8 MMAs (4 ky x 2 kx parities) of K = 16 per 128-row tile, 4 tiles per
+// sample (456 rows, 361 of them output pixels), weights (8 KB) resident, nothing is gathered.
+namespace c2p {
+constexpr int kCta = 320;                                   // warp 0 loader, 1-4 rearrange, 5 MMA, 6-9 epilogue
+constexpr int kRawBytes = kP1 * kAct1C * 2, kRawPitch = 27008; // 26 896 B per sample
+constexpr int kSlots = 24, kRowsP = 21, kArrBytes = kRowsP * kSlots * 16, kParPitch = 33536; // 4 arrays + 1 152 B the last tile reads past them
+constexpr int kWBytes = 128 * 32 * 2;
+constexpr int kSmem = 128 + 2 * kRawPitch + 2 * kParPitch + kWBytes; // 129 408 B
+constexpr int kTmemCols = 256;                              // 2 buffers x 4 tiles x 32 columns
+} // namespace c2p
+
+__global__ void __launch_bounds__(c2p::kCta, 1) conv2p_kernel(Args a)
+{
+    using namespace c2p;
+    extern __shared__ __align__(128) uint8_t smem_raw[];
+    uint8_t *s_base = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
+    uint8_t *s_rawbuf = s_base, *s_par = s_base + 2 * kRawPitch, *s_w = s_par + 2 * kParPitch;
+    __shared__ __align__(8) uint64_t s_wfull, s_rfull[2], s_rempty[2], s_pfull[2], s_pempty[2], s_tfull[2], s_tempty[2];
+    __shared__ uint32_t s_tmem;
+    __shared__ float s_bias[32];
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int my_items = static_cast<int>(blockIdx.x) < a.n ? (a.n - 1 - static_cast<int>(blockIdx.x)) / static_cast<int>(gridDim.x) + 1 : 0;
+    if (tid == 0) {
+        mbar_init(&s_wfull, 1);
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&s_rfull[i], 1); mbar_init(&s_rempty[i], 128); mbar_init(&s_pfull[i], 128); mbar_init(&s_pempty[i], 1);
+            mbar_init(&s_tfull[i], 1); mbar_init(&s_tempty[i], 128);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (tid < 32) s_bias[tid] = a.bias[tid];
+    for (int i = tid; i < 2 * kParPitch / 16; i += kCta) reinterpret_cast<uint4 *>(s_par)[i] = make_uint4(0, 0, 0, 0); // unused slots stay finite
+    if (warp == 5) tmem_alloc(&s_tmem, kTmemCols);
+    fence_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = s_tmem;
+
+    if (warp == 0) {
+        // ---------------------------------------------------------------- loader: one bulk copy per sample
+        if (lane == 0) {
+            mbar_expect_tx(&s_wfull, kWBytes);
+            bulk_load(s_w, a.weights, kWBytes, &s_wfull);
+            for (int t = 0; t < my_items; ++t) {
+                const uint32_t rb = t & 1u;
+                if (t >= 2) mbar_wait_sleep(&s_rempty[rb], ((t >> 1) - 1) & 1);
+                const int sample = static_cast<int>(blockIdx.x) + t * static_cast<int>(gridDim.x);
+                mbar_expect_tx(&s_rfull[rb], kRawBytes);
+                bulk_load(s_rawbuf + rb * kRawPitch, a.in + static_cast<size_t>(sample) * kP1 * kAct1C, kRawBytes, &s_rfull[rb]);
+            }
+        }
+    } else if (warp < 5) {
+        // ---------------------------------------------------------------- rearrange: pixel (y, x) -> P[y & 1][x & 1][y >> 1][x >> 1]
+        const int rt = tid - 32;
+        for (int t = 0; t < my_items; ++t) {
+            const uint32_t b = t & 1u;
+            mbar_wait_sleep(&s_rfull[b], (t >> 1) & 1);
+            if (t >= 2) mbar_wait_sleep(&s_pempty[b], ((t >> 1) - 1) & 1);
+            const uint4 *src = reinterpret_cast<const uint4 *>(s_rawbuf + b * kRawPitch);
+            uint8_t *dst = s_par + b * kParPitch;
+#pragma unroll 2
+            for (int i = rt; i < kP1; i += 128) {
+                const int y = i / kC1, x = i - y * kC1;
+                *reinterpret_cast<uint4 *>(dst + ((y & 1) * 2 + (x & 1)) * kArrBytes + ((y >> 1) * kSlots + (x >> 1)) * 16) = src[i];
+            }
+            fence_async_smem();
+            mbar_arrive(&s_pfull[b]);
+            mbar_arrive(&s_rempty[b]); // the stores above consumed every loaded pixel: the raw buffer is free
+        }
+    } else if (warp == 5) {
+        // ---------------------------------------------------------------- MMA issue (whole warp, one elected lane)
+        mbar_wait_sleep(&s_wfull, 0);
+        constexpr uint32_t kIdesc = instr_desc(32);
+        const uint64_t w_desc = smem_desc(smem_u32(s_w), 4 * 128, 128);
+        for (int t = 0; t < my_items; ++t) {
+            const uint32_t b = t & 1u;
+            if (t >= 2) mbar_wait_sleep(&s_tempty[b], ((t >> 1) - 1) & 1);
+            mbar_wait_sleep(&s_pfull[b], (t >> 1) & 1);
+            tc_fence_after();
+            const uint64_t a_desc = smem_desc(smem_u32(s_par + b * kParPitch), 16, 128);
+            if (elect_one()) {
+#pragma unroll
+                for (int tile = 0; tile < 4; ++tile) {
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) { // q = ky * 2 + kx parity
+                        const int ky = q >> 1, kxp = q & 1;
+                        const uint32_t a_off = ((ky & 1) * 2 + kxp) * kArrBytes + ((ky >> 1) * kSlots + tile * 128) * 16;
+                        // B block q of the packed weights: blob q / 4 (64 K each), K cores (q % 4) * 2 and + 1
+                        const uint32_t b_off = (q >> 2) * (64 * 32 * 2) + (q & 3) * 2 * (4 * 128);
+                        umma_bf16(tmem + b * 128 + tile * 32, a_desc + static_cast<uint64_t>(a_off >> 4), w_desc + static_cast<uint64_t>(b_off >> 4), kIdesc, q != 0);
+                    }
+                }
+                umma_commit(&s_pempty[b]);
+                umma_commit(&s_tfull[b]);
+            }
+            __syncwarp();
+        }
+    } else {
+        // ---------------------------------------------------------------- epilogue: thread = TMEM lane = row of each of the 4 tiles
+        const int q4 = warp & 3, r = q4 * 32 + lane;
+        for (int t = 0; t < my_items; ++t) {
+            const uint32_t b = t & 1u;
+            const int sample = static_cast<int>(blockIdx.x) + t * static_cast<int>(gridDim.x);
+            mbar_wait_sleep(&s_tfull[b], (t >> 1) & 1);
+            tc_fence_after();
+#pragma unroll 1
+            for (int tile = 0; tile < 4; ++tile) {
+                const uint32_t taddr = tmem + b * 128 + tile * 32 + (static_cast<uint32_t>(q4 * 32) << 16);
+                uint32_t v[32];
+                tmem_load16_async(taddr, *reinterpret_cast<uint32_t (*)[16]>(&v[0]));
+                tmem_load16_async(taddr + 16, *reinterpret_cast<uint32_t (*)[16]>(&v[16]));
+                tmem_wait_ld();
+                if (tile == 3) { // the sample's accumulators are in registers
+                    tc_fence_before();
+                    mbar_arrive(&s_tempty[b]);
+                }
+                const int m = tile * 128 + r, y2 = m / kSlots, x2 = m - y2 * kSlots;
+                if (y2 < kC2 && x2 < kC2) {
+                    uint4 *out = reinterpret_cast<uint4 *>(a.out + (static_cast<size_t>(sample) * kP2 + y2 * kC2 + x2) * 32);
+#pragma unroll
+                    for (int c0 = 0; c0 < 32; c0 += 8) {
+                        uint32_t pk[4];
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            const float lo = fmaxf(__uint_as_float(v[c0 + 2 * j]) + s_bias[c0 + 2 * j], 0.0f);
+                            const float hi = fmaxf(__uint_as_float(v[c0 + 2 * j + 1]) + s_bias[c0 + 2 * j + 1], 0.0f);
+                            const __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+                            pk[j] = *reinterpret_cast<const uint32_t *>(&h);
+                        }
+                        out[c0 / 8] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                    }
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 5) tmem_dealloc(tmem, kTmemCols);
+}
+
+cudaError_t launch_conv2p(const Args &a, int sms, cudaStream_t s)
+{
+    cudaError_t e = cudaFuncSetAttribute(conv2p_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, c2p::kSmem);
+    if (e != cudaSuccess) return e;
+    conv2p_kernel<<<a.n < sms ? a.n : sms, c2p::kCta, c2p::kSmem, s>>>(a);
+    return cudaGetLastError();
+}
+
 // ------------------------------------------------------------------------------------------------ gray-diff input
 // DataProcessor's 'gray-diff' observation (processor.py:53-64) straight from the ring, as the network's bf16 input:
 // per colour the uint8 wrap-around double difference oldest - middle - newest, 0.2989 R + 0.5870 G + 0.1140 B,
@@ -1471,6 +1630,10 @@ template <int L> __device__ __forceinline__ float folded(const DevWeights &w, in
 {
     if (L == 1) { // k = (ky*4+kx)*8 + c, BN1 folded
         const int tap = k >> 3, c = k & 7;
+        return c < 5 ? __fmul_rn(w.f[6][(tap * 5 + c) * 32 + col], bn_scale(w.f[2], w.f[5], c)) : 0.0f;
+    }
+    if (L == 6) { // conv2 in conv2p_kernel's K order: k = ((ky * 2 + kx parity) * 2 + j) * 8 + c  <->  tap (ky, kx = parity + 2 j)
+        const int c = k & 7, j = (k >> 3) & 1, kxp = (k >> 4) & 1, ky = k >> 5, tap = ky * 4 + kxp + 2 * j;
         return c < 5 ? __fmul_rn(w.f[6][(tap * 5 + c) * 32 + col], bn_scale(w.f[2], w.f[5], c)) : 0.0f;
     }
     if (L == 2) return __fmul_rn(w.f[12][k * 64 + col], bn_scale(w.f[8], w.f[11], k & 31)); // k = tap*32 + c, BN2 folded
@@ -1729,6 +1892,8 @@ struct ahk_policy {
     uint16_t *w[6] = {};
     float *b[6] = {};
     uint16_t *w1t = nullptr; // conv1 in Toeplitz form (conv1_kernel, A/B switch AHK_CONV1=n144)
+    uint16_t *w2p = nullptr; // conv2 in conv2p_kernel's K order (pack_b blobs)
+    bool conv2_parity = true; // A/B switch AHK_CONV2=ws: conv_ws_kernel instead of conv2p_kernel
     uint16_t *w1p = nullptr; // conv1 in phase-separated form (conv1p_kernel, the default), fp16, unscaled
     bool conv1_n144 = false;
     bool conv1_normal = false; // A/B switch AHK_CONV1=normal: conv1t_kernel with the pixels as NORMAL fp16 numbers (1024 + v - 1024)
@@ -1838,6 +2003,14 @@ static int load_rgb_weights(ahk_policy *p, const ahk_policy_weights *w)
         }
         rc = upload(pack_b(wf, 128, 32, 32, 1), bf, &p->w[1], &p->b[1]);
         if (rc == AHK_OK) rc = upload_nk(pack_nk(wf, 128, 32), &p->wn[1]);
+        if (rc == AHK_OK) { // the same matrix in conv2p_kernel's K order
+            std::vector<float> wp(128 * 32);
+            for (int k = 0; k < 128; ++k) {
+                const int c = k & 7, j = (k >> 3) & 1, kxp = (k >> 4) & 1, ky = k >> 5, src = ((ky * 4 + kxp + 2 * j) * 8 + c);
+                for (int o = 0; o < 32; ++o) wp[k * 32 + o] = wf[src * 32 + o];
+            }
+            rc = upload_nk(pack_b(wp, 128, 32, 32, 1), &p->w2p);
+        }
     }
     if (rc == AHK_OK) { // conv3: k = (ky*4+kx)*32 + c, BN2 folded
         std::vector<float> wf(512 * 64), bf(64);
@@ -1892,6 +2065,7 @@ int ahk_policy_create(int device, int max_batch, const ahk_policy_weights *w, ah
     p->max_batch = max_batch;
     cudaDeviceGetAttribute(&p->sms, cudaDevAttrMultiProcessorCount, device);
     if (const char *sw = getenv("AHK_CONV23")) p->legacy_conv = strcmp(sw, "tile") == 0;
+    if (const char *sw = getenv("AHK_CONV2")) p->conv2_parity = strcmp(sw, "ws") != 0;
     if (const char *sw = getenv("AHK_CONV1")) { p->conv1_n144 = strcmp(sw, "n144") == 0; p->conv1_smem = strcmp(sw, "smem") == 0; p->conv1_normal = strcmp(sw, "normal") == 0; }
     int rc = load_rgb_weights(p, w);
     const size_t nb = static_cast<size_t>(max_batch);
@@ -1961,6 +2135,7 @@ int ahk_policy_set_weights_dev(ahk_policy *p, const ahk_policy_weights *w_dev, v
     POL_CUDA(cudaMemsetAsync(p->w1p, 0, static_cast<size_t>(c1p::kWBytes), s));
     pack_conv1p_kernel<<<(9 * 3 * 3 * 3 * 3 * 5 * 8 + 255) / 256, 256, 0, s>>>(w, p->w1p);
     pack_b_kernel<1><<<16, 256, 0, s>>>(w, p->w[1], 128, 32, 1);
+    pack_b_kernel<6><<<16, 256, 0, s>>>(w, p->w2p, 128, 32, 1);
     pack_b_kernel<2><<<128, 256, 0, s>>>(w, p->w[2], 512, 64, 1);
     pack_b_kernel<3><<<p->sms * 8, 256, 0, s>>>(w, p->w[3], 4096, 256, 2);
     pack_b_kernel<4><<<p->sms * 4, 256, 0, s>>>(w, p->w[4], 512, 256, 2);
@@ -2074,6 +2249,7 @@ void ahk_policy_destroy(ahk_policy *p)
     if (p->bn_sums) cudaFree(p->bn_sums);
     if (p->w3sum) cudaFree(p->w3sum);
     if (p->w1p) cudaFree(p->w1p);
+    if (p->w2p) cudaFree(p->w2p);
     for (int i = 0; i < 7; ++i) if (p->ev[i]) cudaEventDestroy(p->ev[i]);
     for (int i = 0; i < 6; ++i) { if (p->gw[i]) cudaFree(p->gw[i]); if (p->gb[i]) cudaFree(p->gb[i]); }
     cudaFree(p->gimg); cudaFree(p->ga1); cudaFree(p->ga2); cudaFree(p->ga3); cudaFree(p->ga4); cudaFree(p->gh1);
@@ -2107,7 +2283,10 @@ static int rgb_layer(ahk_policy *p, Args a, int layer, float *logits, uint8_t *a
         // four times over L2 -> SM (1.2 GB per 8192 samples: 0.21-0.25 ms against 0.155; AHK_GEMM=tma2 runs it for the record)
         a.in = p->act1; a.weights = reinterpret_cast<const uint4 *>(p->w[1]); a.bias = p->b[1]; a.out = p->act2; a.m_total = n * kP2;
         g.tiles_m = n * 4; g.blocks_n = 1; g.k_chunks = 4; g.n_valid = 32; g.bias = p->b[1]; g.out_bf16 = p->act2; g.out_pitch = 32;
-        if (p->tma_gemm && p->tma_conv2) POL_CUDA((tg::launch<32, 64, tg::kConv2, false, tg::kBiasReluBf16, 8, 4>(g, p->tm_a[1], p->tm_w[1], p->sms, s)));
+        if (p->conv2_parity && !p->legacy_conv && !(p->tma_gemm && p->tma_conv2)) {
+            a.weights = reinterpret_cast<const uint4 *>(p->w2p);
+            POL_CUDA(launch_conv2p(a, p->sms, s));
+        } else if (p->tma_gemm && p->tma_conv2) POL_CUDA((tg::launch<32, 64, tg::kConv2, false, tg::kBiasReluBf16, 8, 4>(g, p->tm_a[1], p->tm_w[1], p->sms, s)));
         else if (p->legacy_conv) POL_CUDA(launch<kConv2>(a, tiles(static_cast<long long>(n) * kP2), 1, p->sms, s));
         else POL_CUDA(launch_ws<kConv2>(a, tiles(static_cast<long long>(n) * kP2), p->sms, s));
         return AHK_OK;
@@ -2233,6 +2412,7 @@ int ahk_policy_forward_train(ahk_policy *p, const ahk_policy_weights *w_dev, con
     bn_finalize_kernel<<<1, 64, 0, s>>>(p->bn_sums, 8, static_cast<long long>(n) * kP1, mean, var);
     // conv2 with BatchNorm 1 (batch statistics) folded in
     pack_b_kernel<1><<<16, 256, 0, s>>>(w, p->w[1], 128, 32, 1);
+    pack_b_kernel<6><<<16, 256, 0, s>>>(w, p->w2p, 128, 32, 1);
     fold_bias_kernel<<<dim3(4, 6), 128, 0, s>>>(w, p->b[0], p->b[1], p->b[2], p->b[3], p->b[4], p->b[5], p->w3sum, 1);
     if (int rc = rgb_layer(p, a, 1, nullptr, nullptr, s)) return rc;
     bn_sums_kernel<32><<<stat_grid, 256, 0, s>>>(p->act2, static_cast<long long>(n) * kP2, p->bn_sums);

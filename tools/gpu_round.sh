@@ -1,7 +1,7 @@
 #!/bin/bash
 # One gpurun call, assembled from arguments (replaces the per-experiment gpu_r*.sh scripts of round 1).
 #   bash tools/gpu_round.sh TAG [part ...]
-# parts: tests | tests:<pytest -k expr> | bench | driver | ref | stress | stress8 | ncu:<kernel regex> | policy | rl | scale8
+# parts: tests | tests:<pytest -k expr> | bench | driver | long | ref | stress | stress8 | ncu:<kernel regex> | policy | rl | rl8 | scale8
 # Everything is written to gpurun_out/ with TAG in the name.  ncu parts run only after the same command exited 0 plainly.
 set -u
 TAG=${1:-r2}; shift || true
@@ -20,6 +20,7 @@ for PART in "$@"; do
     stress8) for N in 2 4 8; do timeout 1200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 2953$N tools/stress_sweep.py --envs 384 --horizon 10000 --out $OUT/stress_sweep_N$N.json 2> $OUT/stress_N${N}_$TAG.err; echo "stress N=$N rc=$?"; done ;;
     scale8)  for N in 2 4 8; do timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 2954$N bench.py --gpus $N --steps 20 --warmup 5 > $OUT/bench_${N}gpu_$TAG.json 2> $OUT/bench_${N}gpu_$TAG.err; echo "bench N=$N rc=$?"; cat $OUT/bench_${N}gpu_$TAG.json; done ;;
     policy)  timeout 600 python tools/policy_bench.py > $OUT/policy_$TAG.json 2> $OUT/policy_$TAG.err; echo "policy rc=$?"; cat $OUT/policy_$TAG.json ;;
+    rl8)     for N in 2 8; do timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 2955$N tools/rl_bench.py > $OUT/rl_${N}gpu_$TAG.json 2> $OUT/rl_${N}gpu_$TAG.err; echo "rl N=$N rc=$?"; cat $OUT/rl_${N}gpu_$TAG.json; done ;;
     rl)      timeout 900 python tools/rl_bench.py > $OUT/rl_$TAG.json 2> $OUT/rl_$TAG.err; echo "rl rc=$?"; cat $OUT/rl_$TAG.json ;;
     ncu:*)   KRE=${PART#ncu:}
              CMD="python bench.py --steps 2 --warmup 3 --chunk 16 --no-cpu-baseline --no-rollout"

@@ -478,6 +478,29 @@ __global__ void __launch_bounds__(256) dense1_wgrad_fix_kernel(const float *__re
     }
 }
 
+// conv2's im2col, materialised once per fit as the MN-major A operand of its weight-gradient GEMM: col[row = (s, y2, x2)][tap][8]
+// = r1[s][2 y2 + ky][2 x2 + kx][8]; one 16-byte copy per (row, tap).  (As a tensor map the 64-byte windows would need a
+// 64-byte-swizzle MN-major variant of the GEMM; 378 MB of extra traffic per 4096 samples is 0.15 ms.)
+__global__ void __launch_bounds__(256) conv2_im2col_kernel(const __nv_bfloat16 *__restrict__ r1, int n, uint4 *__restrict__ col)
+{
+    const long long total = static_cast<long long>(n) * kP2 * 16;
+    for (long long i = static_cast<long long>(blockIdx.x) * 256 + threadIdx.x; i < total; i += static_cast<long long>(gridDim.x) * 256) {
+        const int tap = static_cast<int>(i & 15);
+        const long long row = i >> 4;
+        const int smp = static_cast<int>(row / kP2), p = static_cast<int>(row - static_cast<long long>(smp) * kP2), y = p / 19, x = p - y * 19;
+        col[i] = __ldg(reinterpret_cast<const uint4 *>(r1) + static_cast<long long>(smp) * kP1 + (2 * y + (tap >> 2)) * 41 + 2 * x + (tap & 3));
+    }
+}
+// dW2[(tap, c)][o] = s1[c] G[tap * 8 + c][o] + t1[c] db[o]  (Keras [4][4][5][32])
+__global__ void __launch_bounds__(256) conv2_wgrad_fix_kernel(const float *__restrict__ g, const float *__restrict__ s1, const float *__restrict__ t1,
+                                                              const float *__restrict__ db, float *__restrict__ dw)
+{
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= 80 * 32) return;
+    const int o = i & 31, tc = i >> 5, tap = tc / 5, c = tc - tap * 5;
+    dw[i] = fmaf(s1[c], g[(tap * 8 + c) * 32 + o], t1[c] * db[o]);
+}
+
 // conv3's weight gradient from the raw product G = im2col(r2)^T dz3: dW[(tap, c)][o] = s2[c] G[(tap, c)][o] + t2[c] db[o]
 __global__ void __launch_bounds__(256) conv3_wgrad_fix_kernel(const float *__restrict__ g, const float *__restrict__ s2, const float *__restrict__ t2,
                                                               const float *__restrict__ db, float *__restrict__ dw)
@@ -575,6 +598,7 @@ struct ahk_trainer {
     __nv_bfloat16 *w5h = nullptr, *w4p = nullptr; // bf16 [in][out] copies of dense2 / dense1 (rows in this file's input order) for the data-gradient GEMMs
     CUtensorMap tm_dz5h, tm_dz4h, tm_w5h, tm_w4p;
     float *g4 = nullptr;      // [4096][512] raw dense1 weight gradient (tensor-core path); its head doubles as conv3's [512][64]
+    __nv_bfloat16 *dz2h = nullptr, *col2 = nullptr; // bf16 dz2 [n * 361][32] and conv2's im2col [n * 361][128] for its weight-gradient GEMM
     __nv_bfloat16 *dz3h = nullptr, *w3h = nullptr; // bf16 dz3 [n * 64][64] and Keras conv3 kernel [16 * 32][64] for the conv3 GEMMs
     CUtensorMap tm_w3h;
     bool simt_dense = false;  // A/B switch AHK_TRAIN_DENSE=simt: dense data gradients on the functor GEMM
@@ -631,6 +655,8 @@ int ahk_trainer_create(int device, int max_batch, ahk_trainer **out)
     if (e == cudaSuccess) e = cudaMalloc(&t->dz4h, nb * 512 * 2);
     if (e == cudaSuccess) e = cudaMalloc(&t->g4, 4096 * 512 * 4);
     if (e == cudaSuccess) e = cudaMalloc(&t->dz3h, nb * 4096 * 2);
+    if (e == cudaSuccess) e = cudaMalloc(&t->dz2h, nb * kP2 * 32 * 2);
+    if (e == cudaSuccess) e = cudaMalloc(&t->col2, nb * kP2 * 128 * 2);
     if (e == cudaSuccess) e = cudaMalloc(&t->w3h, 512 * 64 * 2);
     if (e == cudaSuccess) e = ahk::tg::matrix_map(&t->tm_w3h, t->w3h, 512, 64, 64, 32);
     if (e == cudaSuccess) e = cudaMalloc(&t->w5h, 512 * 512 * 2);
@@ -657,7 +683,7 @@ void ahk_trainer_destroy(ahk_trainer *t)
     if (!t) return;
     DeviceGuard guard(t->device);
     cudaFree(t->dz5); cudaFree(t->dz4); cudaFree(t->da3); cudaFree(t->dz3); cudaFree(t->da2); cudaFree(t->dz2); cudaFree(t->da1); cudaFree(t->dz1);
-    cudaFree(t->dz5h); cudaFree(t->dz4h); cudaFree(t->w5h); cudaFree(t->w4p); cudaFree(t->g4); cudaFree(t->dz3h); cudaFree(t->w3h); cudaFree(t->affine); cudaFree(t->sums);
+    cudaFree(t->dz5h); cudaFree(t->dz4h); cudaFree(t->w5h); cudaFree(t->w4p); cudaFree(t->g4); cudaFree(t->dz3h); cudaFree(t->w3h); cudaFree(t->dz2h); cudaFree(t->col2); cudaFree(t->affine); cudaFree(t->sums);
     delete t;
 }
 
@@ -811,14 +837,30 @@ int ahk_train_backward(ahk_trainer *t, ahk_policy *p, const ahk_policy_weights *
     {
         const long long rows = static_cast<long long>(n) * kP2;
         bn_bwd_sums_kernel<32><<<ctas, 256, 0, s>>>(t->da2, r2, rows, mean + 8, var + 8, 32, t->sums);
-        bn_bwd_apply_kernel<32><<<ctas * 2, 256, 0, s>>>(t->da2, r2, rows, wf[G2], mean + 8, var + 8, 32, 32, t->sums, t->dz2, gf[G2], gf[B2], nullptr, gf[C2B]);
+        bn_bwd_apply_kernel<32><<<ctas * 2, 256, 0, s>>>(t->da2, r2, rows, wf[G2], mean + 8, var + 8, 32, 32, t->sums, t->dz2, gf[G2], gf[B2], t->dz2h, gf[C2B]);
         TR_CUDA(cudaMemsetAsync(t->sums, 0, 128 * 8, s));
     }
     // ---- conv2: dW2 = im2col(bn1(r1))^T dz2 (80 x 32), db2, da1 (5 channels of 8)
     {
-        using W2 = ConvWgrad<5, 8, 41, 19, 32>;
-        W2 f{r1, t->dz2, gf[C2W], s1, t1};
-        TR_CUDA((run_gemm<W2, 80, 32, 5, 2>(f, 80, 32, n * kP2, ctas, s))); // the whole 80 x 32 gradient is one tile: split K over the CTAs
+        if (t->simt_dense) {
+            using W2 = ConvWgrad<5, 8, 41, 19, 32>;
+            W2 f{r1, t->dz2, gf[C2W], s1, t1};
+            TR_CUDA((run_gemm<W2, 80, 32, 5, 2>(f, 80, 32, n * kP2, ctas, s))); // the whole 80 x 32 gradient is one tile: split K over the CTAs
+        } else { // tcgen05: G[128][32] = col^T dz2 with both operands MN-major, split K over the SMs, then the BatchNorm affine map
+            namespace tg = ahk::tg;
+            const unsigned long long rows = static_cast<unsigned long long>(n) * kP2;
+            conv2_im2col_kernel<<<t->sms * 8, 256, 0, s>>>(r1, n, reinterpret_cast<uint4 *>(t->col2));
+            CUtensorMap ta, tb;
+            TR_CUDA(tg::matrix_map(&ta, t->col2, rows, 128, 64, 64));
+            TR_CUDA(tg::matrix_map(&tb, t->dz2h, rows, 32, 64, 64)); // box wider than the 32 columns: the other 32 are zero fill
+            TR_CUDA(zero(t->g4, 128 * 32));
+            tg::Args g{};
+            const int chunks = static_cast<int>((rows + 63) / 64);
+            g.k_splits = chunks < t->sms ? chunks : t->sms; g.k_chunks = (chunks + g.k_splits - 1) / g.k_splits;
+            g.tiles_m = 1; g.blocks_n = 1; g.m_total = 128; g.n_valid = 32; g.out_f32 = t->g4; g.out_pitch = 32; g.scale = 1.0f;
+            TR_CUDA((tg::launch<64, 128, tg::kLinearMn, true, tg::kAtomicF32, 6>(g, ta, tb, t->sms, s)));
+            conv2_wgrad_fix_kernel<<<(80 * 32 + 255) / 256, 256, 0, s>>>(t->g4, s1, t1, gf[C2B], gf[C2W]);
+        }
         TR_CUDA(cudaMemcpyToSymbolAsync(c_w2, wf[C2W], sizeof(float) * 16 * 5 * 32, 0, cudaMemcpyDeviceToDevice, s));
         conv2_dgrad_kernel<0, 0><<<(n * 21 * 21 + 127) / 128, 128, 0, s>>>(t->dz2, n, t->da1);
         conv2_dgrad_kernel<0, 1><<<(n * 21 * 20 + 127) / 128, 128, 0, s>>>(t->dz2, n, t->da1);

@@ -954,6 +954,10 @@ __device__ __forceinline__ void umma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, ui
         "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
         :: "r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
+__device__ __forceinline__ void umma_f16_ts_bf16(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t accumulate)
+{
+    umma_f16_ts(tmem_d, tmem_a, bdesc, idesc, accumulate); // the operand types are in the instruction descriptor
+}
 // 8 consecutive 32-bit columns of this thread's TMEM lane
 __device__ __forceinline__ void tmem_store8(uint32_t taddr, uint32_t r0, uint32_t r1, uint32_t r2, uint32_t r3, uint32_t r4, uint32_t r5, uint32_t r6, uint32_t r7)
 {
@@ -1572,6 +1576,203 @@ cudaError_t launch_conv2p(const Args &a, int sms, cudaStream_t s)
     return cudaGetLastError();
 }
 
+// ------------------------------------------------------------------------------------------------ conv2 / conv3, A in TMEM
+// The im2col of a small convolution built where the tensor core reads it: an item (conv2: one sample of act1, 26.9 KB;
+// conv3: two samples of act2, 46 KB) is bulk-copied to shared memory ONCE, and converter threads — thread = TMEM lane =
+// output pixel — copy each MMA's 32-byte A row (two adjacent taps of 8 channels for conv2, half a tap's 32 channels for
+// conv3) from the raw sample straight into tensor memory (two 16-byte loads, one tcgen05.st.x8).  The MMAs take A from TMEM
+// (floor 128 N / 256 cycles instead of the 64 cycles an A tile costs from shared memory), B = the layer's packed weights,
+// resident.  Activations cross L2 -> SM once instead of four times.  Measured per 8192 samples: conv2 0.110 ms (parity arrays
+// 0.116, cp.async gather 0.155, tensor-map im2col 0.21-0.25) — the default; conv3 0.165 ms against 0.075 for the TMA-fed GEMM:
+// its pixels are 64 bytes and every window starts a multiple of 128 bytes into the sample, so the 32 lanes of each 16-byte
+// load hit the same four banks (80 % of the shared-memory pipe, profiles/conv_tm_r2v_ncu.txt) — kept as AHK_CONVTM=23.
+namespace ctm {
+template <int L> struct Cfg;
+template <> struct Cfg<kConv2> {
+    static constexpr int N = 32, kMmas = 8, kGroup = 8, kTiles = 3, kAStages = 4;     // MMAs per tile, MMAs per A stage, tiles per item
+    static constexpr int kSamples = 1, kRowsOut = kP2, kItemBytes = kP1 * kAct1C * 2, kRawPitch = 27008, kWBytes = 128 * 32 * 2;
+};
+template <> struct Cfg<kConv3> {
+    static constexpr int N = 64, kMmas = 32, kGroup = 16, kTiles = 1, kAStages = 3;
+    static constexpr int kSamples = 2, kRowsOut = 2 * kP3, kItemBytes = 2 * kP2 * 32 * 2, kRawPitch = 46336, kWBytes = 512 * 64 * 2;
+};
+constexpr int kCta = 256 + 64 + 128; // 8 converter warps (2 groups x 4 lane quarters), loader, MMA, 4 epilogue warps
+template <int L> constexpr int smem_bytes() { return 128 + 2 * Cfg<L>::kRawPitch + Cfg<L>::kWBytes; }
+} // namespace ctm
+
+template <int L>
+__global__ void __launch_bounds__(ctm::kCta, 1) conv_tm_kernel(Args a)
+{
+    using C = ctm::Cfg<L>;
+    constexpr int N = C::N, kStagesPerItem = C::kTiles * (C::kMmas / C::kGroup), kACols = C::kGroup * 8, kDCols = C::kTiles * N;
+    constexpr int kABase = 2 * kDCols;
+    static_assert(kABase + C::kAStages * kACols <= 512, "TMEM");
+    extern __shared__ __align__(128) uint8_t smem_raw[];
+    uint8_t *s_base = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
+    uint8_t *s_in = s_base, *s_w = s_base + 2 * C::kRawPitch;
+    __shared__ __align__(8) uint64_t s_wfull, s_rfull[2], s_rempty[2], s_afull[C::kAStages], s_aempty[C::kAStages], s_tfull[2], s_tempty[2];
+    __shared__ uint32_t s_tmem;
+    __shared__ float s_bias[N];
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int items = (a.n + C::kSamples - 1) / C::kSamples;
+    const int my_items = static_cast<int>(blockIdx.x) < items ? (items - 1 - static_cast<int>(blockIdx.x)) / static_cast<int>(gridDim.x) + 1 : 0;
+    if (tid == 0) {
+        mbar_init(&s_wfull, 1);
+        for (int i = 0; i < 2; ++i) { mbar_init(&s_rfull[i], 1); mbar_init(&s_rempty[i], 8); mbar_init(&s_tfull[i], 1); mbar_init(&s_tempty[i], 128); }
+        for (int i = 0; i < C::kAStages; ++i) { mbar_init(&s_afull[i], 4); mbar_init(&s_aempty[i], 1); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (tid < N) s_bias[tid] = a.bias[tid];
+    if (warp == 8) tmem_alloc(&s_tmem, 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = s_tmem;
+
+    if (warp == 9) {
+        // ---------------------------------------------------------------- loader: one bulk copy per item
+        if (lane == 0) {
+            mbar_expect_tx(&s_wfull, C::kWBytes);
+            for (int i = 0; i < C::kWBytes; i += 8192) bulk_load(s_w + i, reinterpret_cast<const uint8_t *>(a.weights) + i, 8192, &s_wfull);
+            for (int t = 0; t < my_items; ++t) {
+                const uint32_t rb = t & 1u;
+                if (t >= 2) mbar_wait_sleep(&s_rempty[rb], ((t >> 1) - 1) & 1);
+                const int item = static_cast<int>(blockIdx.x) + t * static_cast<int>(gridDim.x);
+                const int samples = (item + 1) * C::kSamples <= a.n ? C::kSamples : a.n - item * C::kSamples;
+                const uint32_t bytes = static_cast<uint32_t>(samples) * (C::kItemBytes / C::kSamples);
+                mbar_expect_tx(&s_rfull[rb], bytes);
+                bulk_load(s_in + rb * C::kRawPitch, reinterpret_cast<const uint8_t *>(a.in) + static_cast<size_t>(item) * C::kItemBytes, bytes, &s_rfull[rb]);
+            }
+        }
+    } else if (warp < 8) {
+        // ---------------------------------------------------------------- converters: raw sample -> A rows in TMEM
+        const int quarter = warp & 3, group = warp >> 2, r = quarter * 32 + lane;
+        const uint32_t lane_base = tmem + (static_cast<uint32_t>(quarter * 32) << 16) + kABase;
+        uint32_t f = 0; // A stages so far (both groups count all of them)
+        for (int t = 0; t < my_items; ++t) {
+            const uint32_t rb = t & 1u;
+            mbar_wait_sleep(&s_rfull[rb], (t >> 1) & 1);
+            const uint8_t *raw = s_in + rb * C::kRawPitch;
+#pragma unroll 1
+            for (int sidx = 0; sidx < kStagesPerItem; ++sidx, ++f) {
+                if (static_cast<int>(f & 1u) != group) continue;
+                const int tile = sidx / (C::kMmas / C::kGroup), q0 = (sidx % (C::kMmas / C::kGroup)) * C::kGroup;
+                // the row's base offset in the raw item
+                uint32_t off;
+                if (L == kConv2) {
+                    int p = tile * 128 + r;
+                    p = p < kP2 ? p : 0;
+                    const int y = p / kC2, x = p - y * kC2;
+                    off = ((2 * y) * kC1 + 2 * x) * (kAct1C * 2);
+                } else {
+                    const int smp = r >> 6, p = r & 63, y = p >> 3, x = p & 7;
+                    off = smp * (kP2 * 64) + ((2 * y) * kC2 + 2 * x) * 64;
+                }
+                const uint32_t st = f % C::kAStages;
+                if (f >= static_cast<uint32_t>(C::kAStages)) mbar_wait_sleep(&s_aempty[st], ((f / C::kAStages) - 1u) & 1u);
+                tc_fence_after();
+                const uint32_t stage = lane_base + st * kACols;
+#pragma unroll
+                for (int i = 0; i < C::kGroup; ++i) {
+                    const int q = q0 + i;
+                    uint32_t tapoff;
+                    if (L == kConv2) tapoff = ((q >> 1) * kC1 + (q & 1) * 2) * (kAct1C * 2);           // taps (ky, 2h), (ky, 2h + 1): 32 contiguous bytes
+                    else { const int tap = q >> 1; tapoff = ((tap >> 2) * kC2 + (tap & 3)) * 64 + (q & 1) * 32; } // half of a tap's 32 channels
+                    const uint4 v0 = *reinterpret_cast<const uint4 *>(raw + off + tapoff), v1 = *reinterpret_cast<const uint4 *>(raw + off + tapoff + 16);
+                    tmem_store8(stage + i * 8, v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w);
+                }
+                tmem_wait_st();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&s_afull[st]);
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&s_rempty[rb]); // this warp's loads of the item have all been consumed by their stores
+        }
+    } else if (warp == 8) {
+        // ---------------------------------------------------------------- MMA issue (whole warp, one elected lane)
+        mbar_wait_sleep(&s_wfull, 0);
+        constexpr uint32_t kIdesc = instr_desc(N);
+        const uint64_t w_desc = smem_desc(smem_u32(s_w), (N / 8) * 128, 128);
+        uint32_t f = 0;
+        for (int t = 0; t < my_items; ++t) {
+            const uint32_t b = t & 1u;
+            if (t >= 2) mbar_wait_sleep(&s_tempty[b], ((t >> 1) - 1) & 1);
+            tc_fence_after();
+#pragma unroll 1
+            for (int sidx = 0; sidx < kStagesPerItem; ++sidx, ++f) {
+                const int tile = sidx / (C::kMmas / C::kGroup), q0 = (sidx % (C::kMmas / C::kGroup)) * C::kGroup;
+                const uint32_t st = f % C::kAStages;
+                mbar_wait_sleep(&s_afull[st], (f / C::kAStages) & 1u);
+                tc_fence_after();
+                const uint32_t a_stage = tmem + kABase + st * kACols, d = tmem + b * kDCols + tile * N;
+                // B of MMA q: blob q / 4 (64 K each), K cores (q % 4) * 2 and + 1
+                const uint64_t bd0 = w_desc + static_cast<uint64_t>(((q0 >> 2) * (64 * N * 2)) >> 4);
+                if (elect_one()) {
+#pragma unroll
+                    for (int i = 0; i < C::kGroup; ++i)
+                        umma_f16_ts_bf16(d, a_stage + i * 8, bd0 + static_cast<uint64_t>((((i >> 2) * (64 * N * 2)) + (i & 3) * 2 * ((N / 8) * 128)) >> 4), kIdesc, (q0 + i) != 0);
+                    umma_commit(&s_aempty[st]);
+                    if (sidx == kStagesPerItem - 1) umma_commit(&s_tfull[b]);
+                }
+                __syncwarp();
+            }
+        }
+    } else {
+        // ---------------------------------------------------------------- epilogue: thread = TMEM lane = output pixel of each tile
+        const int q4 = warp & 3, r = q4 * 32 + lane;
+        for (int t = 0; t < my_items; ++t) {
+            const uint32_t b = t & 1u;
+            const int item = static_cast<int>(blockIdx.x) + t * static_cast<int>(gridDim.x);
+            mbar_wait_sleep(&s_tfull[b], (t >> 1) & 1);
+            tc_fence_after();
+#pragma unroll 1
+            for (int tile = 0; tile < C::kTiles; ++tile) {
+                const uint32_t taddr = tmem + b * kDCols + tile * N + (static_cast<uint32_t>(q4 * 32) << 16);
+                uint32_t v[N];
+#pragma unroll
+                for (int c0 = 0; c0 < N; c0 += 16) tmem_load16_async(taddr + c0, *reinterpret_cast<uint32_t (*)[16]>(&v[c0]));
+                tmem_wait_ld();
+                if (tile == C::kTiles - 1) { // the item's accumulators are in registers
+                    tc_fence_before();
+                    mbar_arrive(&s_tempty[b]);
+                }
+                const int p = tile * 128 + r;
+                const long long row = static_cast<long long>(item) * C::kRowsOut + p;
+                if (p < C::kRowsOut && row < static_cast<long long>(a.n) * (C::kRowsOut / C::kSamples)) {
+                    uint4 *out = reinterpret_cast<uint4 *>(a.out + row * N);
+#pragma unroll
+                    for (int c0 = 0; c0 < N; c0 += 8) {
+                        uint32_t pk[4];
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            const float lo = fmaxf(__uint_as_float(v[c0 + 2 * j]) + s_bias[c0 + 2 * j], 0.0f);
+                            const float hi = fmaxf(__uint_as_float(v[c0 + 2 * j + 1]) + s_bias[c0 + 2 * j + 1], 0.0f);
+                            const __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+                            pk[j] = *reinterpret_cast<const uint32_t *>(&h);
+                        }
+                        out[c0 / 8] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                    }
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 8) tmem_dealloc(tmem, 512);
+}
+
+template <int L>
+cudaError_t launch_tm(const Args &a, int sms, cudaStream_t s)
+{
+    cudaError_t e = cudaFuncSetAttribute(conv_tm_kernel<L>, cudaFuncAttributeMaxDynamicSharedMemorySize, ctm::smem_bytes<L>());
+    if (e != cudaSuccess) return e;
+    const int items = (a.n + ctm::Cfg<L>::kSamples - 1) / ctm::Cfg<L>::kSamples;
+    conv_tm_kernel<L><<<items < sms ? items : sms, ctm::kCta, ctm::smem_bytes<L>(), s>>>(a);
+    return cudaGetLastError();
+}
+
 // ------------------------------------------------------------------------------------------------ gray-diff input
 // DataProcessor's 'gray-diff' observation (processor.py:53-64) straight from the ring, as the network's bf16 input:
 // per colour the uint8 wrap-around double difference oldest - middle - newest, 0.2989 R + 0.5870 G + 0.1140 B,
@@ -1894,6 +2095,10 @@ struct ahk_policy {
     uint16_t *w1t = nullptr; // conv1 in Toeplitz form (conv1_kernel, A/B switch AHK_CONV1=n144)
     uint16_t *w2p = nullptr; // conv2 in conv2p_kernel's K order (pack_b blobs)
     bool conv2_parity = true; // A/B switch AHK_CONV2=ws: conv_ws_kernel instead of conv2p_kernel
+    // conv_tm_kernel (A operand built in TMEM): the default for conv2 (0.110 ms per 8192 samples against 0.116 for conv2p_kernel);
+    // conv3 stays on the TMA-fed GEMM (0.075 ms against 0.165: its 64-byte pixels put every lane of a load on the same banks).
+    // A/B switch AHK_CONVTM=0 (neither) | 2 (default) | 23 (both)
+    bool conv_tm = true, conv_tm3 = false;
     uint16_t *w1p = nullptr; // conv1 in phase-separated form (conv1p_kernel, the default), fp16, unscaled
     bool conv1_n144 = false;
     bool conv1_normal = false; // A/B switch AHK_CONV1=normal: conv1t_kernel with the pixels as NORMAL fp16 numbers (1024 + v - 1024)
@@ -2066,6 +2271,7 @@ int ahk_policy_create(int device, int max_batch, const ahk_policy_weights *w, ah
     cudaDeviceGetAttribute(&p->sms, cudaDevAttrMultiProcessorCount, device);
     if (const char *sw = getenv("AHK_CONV23")) p->legacy_conv = strcmp(sw, "tile") == 0;
     if (const char *sw = getenv("AHK_CONV2")) p->conv2_parity = strcmp(sw, "ws") != 0;
+    if (const char *sw = getenv("AHK_CONVTM")) { p->conv_tm = strcmp(sw, "0") != 0; p->conv_tm3 = strcmp(sw, "23") == 0; }
     if (const char *sw = getenv("AHK_CONV1")) { p->conv1_n144 = strcmp(sw, "n144") == 0; p->conv1_smem = strcmp(sw, "smem") == 0; p->conv1_normal = strcmp(sw, "normal") == 0; }
     int rc = load_rgb_weights(p, w);
     const size_t nb = static_cast<size_t>(max_batch);
@@ -2283,7 +2489,8 @@ static int rgb_layer(ahk_policy *p, Args a, int layer, float *logits, uint8_t *a
         // four times over L2 -> SM (1.2 GB per 8192 samples: 0.21-0.25 ms against 0.155; AHK_GEMM=tma2 runs it for the record)
         a.in = p->act1; a.weights = reinterpret_cast<const uint4 *>(p->w[1]); a.bias = p->b[1]; a.out = p->act2; a.m_total = n * kP2;
         g.tiles_m = n * 4; g.blocks_n = 1; g.k_chunks = 4; g.n_valid = 32; g.bias = p->b[1]; g.out_bf16 = p->act2; g.out_pitch = 32;
-        if (p->conv2_parity && !p->legacy_conv && !(p->tma_gemm && p->tma_conv2)) {
+        if (p->conv_tm && p->conv2_parity && !p->legacy_conv && !(p->tma_gemm && p->tma_conv2)) POL_CUDA(launch_tm<kConv2>(a, p->sms, s));
+        else if (p->conv2_parity && !p->legacy_conv && !(p->tma_gemm && p->tma_conv2)) {
             a.weights = reinterpret_cast<const uint4 *>(p->w2p);
             POL_CUDA(launch_conv2p(a, p->sms, s));
         } else if (p->tma_gemm && p->tma_conv2) POL_CUDA((tg::launch<32, 64, tg::kConv2, false, tg::kBiasReluBf16, 8, 4>(g, p->tm_a[1], p->tm_w[1], p->sms, s)));
@@ -2293,7 +2500,8 @@ static int rgb_layer(ahk_policy *p, Args a, int layer, float *logits, uint8_t *a
     case 2:
         a.in = p->act2; a.weights = reinterpret_cast<const uint4 *>(p->w[2]); a.bias = p->b[2]; a.out = p->act3; a.m_total = n * kP3;
         g.tiles_m = (n + 1) / 2; g.blocks_n = 1; g.k_chunks = 8; g.n_valid = 64; g.bias = p->b[2]; g.out_bf16 = p->act3; g.out_pitch = 64;
-        if (p->tma_gemm) POL_CUDA((tg::launch<64, 128, tg::kConv3, false, tg::kBiasReluBf16, 6, 8>(g, p->tm_a[2], p->tm_w[2], p->sms, s)));
+        if (p->conv_tm3 && p->tma_gemm && !p->legacy_conv) POL_CUDA(launch_tm<kConv3>(a, p->sms, s));
+        else if (p->tma_gemm) POL_CUDA((tg::launch<64, 128, tg::kConv3, false, tg::kBiasReluBf16, 6, 8>(g, p->tm_a[2], p->tm_w[2], p->sms, s)));
         else if (p->legacy_conv) POL_CUDA(launch<kConv3>(a, tiles(static_cast<long long>(n) * kP3), 1, p->sms, s));
         else POL_CUDA(launch_ws<kConv3>(a, tiles(static_cast<long long>(n) * kP3), p->sms, s));
         return AHK_OK;
@@ -2419,6 +2627,7 @@ int ahk_policy_forward_train(ahk_policy *p, const ahk_policy_weights *w_dev, con
     bn_finalize_kernel<<<1, 64, 0, s>>>(p->bn_sums, 32, static_cast<long long>(n) * kP2, mean + 8, var + 8);
     // conv3
     pack_nk_kernel<2><<<128, 256, 0, s>>>(w, p->wn[2], 512, 64);
+    pack_b_kernel<2><<<128, 256, 0, s>>>(w, p->w[2], 512, 64, 1);
     fold_bias_kernel<<<dim3(4, 6), 128, 0, s>>>(w, p->b[0], p->b[1], p->b[2], p->b[3], p->b[4], p->b[5], p->w3sum, 2);
     if (int rc = rgb_layer(p, a, 2, nullptr, nullptr, s)) return rc;
     bn_sums_kernel<64><<<stat_grid, 256, 0, s>>>(p->act3, static_cast<long long>(n) * kP3, p->bn_sums);

@@ -208,6 +208,26 @@ static int launched(const char *what)
     return rfail(AHK_ERR_CUDA, text);
 }
 
+
+// Agent.store_experience (rl_agents.py:88-90) for every env at once: the step's action, reward, terminal flag, and the two
+// flags replay sampling needs from the engine's state word 15 (meta): auto-reset armed (bit 21: the NEXT step starts a new
+// episode) and "no step since an explicit reset" (episode_steps == 0: the env's frames sit in the warm-up side buffer).
+// One launch instead of eight small tensor ops per step.
+__global__ void __launch_bounds__(256) replay_record_kernel(const uint32_t *__restrict__ meta, const uint8_t *__restrict__ action, const float *__restrict__ reward,
+                                                            const uint8_t *__restrict__ done, int n, uint8_t *__restrict__ action_row,
+                                                            float *__restrict__ reward_row, uint8_t *__restrict__ done_row, uint8_t *__restrict__ pending_row,
+                                                            uint8_t *__restrict__ stale_row)
+{
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t m = meta[i];
+    action_row[i] = action ? action[i] : 0;
+    reward_row[i] = reward ? reward[i] : 0.0f;
+    done_row[i] = done ? (done[i] != 0) : 0;
+    pending_row[i] = (m >> 21) & 1u;
+    if (stale_row) stale_row[i] = (m & 0xFFFFu) == 0u;
+}
+
 } // namespace rl
 } // namespace ahk
 
@@ -260,6 +280,15 @@ int ahk_rl_ddqn_targets(const float *q_dev, const float *q_next_online_dev, cons
     ddqn_targets_kernel<<<(n + 255) / 256, 256, 0, s>>>(q_dev, q_next_online_dev, q_next_target_dev, action_dev, reward_dev, done_dev, n,
                                                        discount, q_fit_dev, targets_dev, dlogits_dev, loss_dev);
     return launched("ahk_rl_ddqn_targets");
+}
+
+int ahk_replay_record(const uint32_t *meta_dev, const uint8_t *action_dev, const float *reward_dev, const uint8_t *done_dev, int n,
+                      uint8_t *action_row, float *reward_row, uint8_t *done_row, uint8_t *pending_row, uint8_t *stale_row, void *stream)
+{
+    if (!meta_dev || !action_row || !reward_row || !done_row || !pending_row || n <= 0) return rfail(AHK_ERR_ARG, "ahk_replay_record: bad argument");
+    replay_record_kernel<<<(n + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(meta_dev, action_dev, reward_dev, done_dev, n, action_row, reward_row,
+                                                                                         done_row, pending_row, stale_row);
+    return launched("ahk_replay_record");
 }
 
 int ahk_rl_pg_returns(const float *reward_dev, const uint8_t *done_dev, int steps, int n, double discount, float *returns_dev, void *stream)

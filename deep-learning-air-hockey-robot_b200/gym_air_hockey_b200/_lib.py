@@ -94,6 +94,7 @@ SYMBOLS = {
     "ahk_policy_set_weights": (_i, [_vp, C.POINTER(PolicyWeights)]),
     "ahk_policy_set_weights_dev": (_i, [_vp, C.POINTER(PolicyWeights), _vp]),
     "ahk_replay_gather": (_i, [_vp, _i, _i, _vp, _vp, _i, _vp, _vp]),
+    "ahk_replay_record": (_i, [_vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
     "ahk_rl_epsilon_greedy": (_i, [_vp, _i, C.c_float, C.c_uint64, C.c_uint32, C.c_uint32, _vp, _vp, _vp]),
     "ahk_rl_ddqn_targets": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, C.c_double, _vp, _vp, _vp, _vp, _vp]),
     "ahk_rl_pg_returns": (_i, [_vp, _vp, _i, _i, C.c_double, _vp, _vp]),

@@ -103,17 +103,20 @@ class ReplayStore(object):
     def _put(self, env, action, reward, done):
         if self.view:
             t = env.head                                 # the rasteriser already wrote the frame here
-            self.stale[t].copy_((env.state[15] & 0xFFFF) == 0)  # no step since an explicit reset: its frames are in env.warm
         else:
             t = self.cursor
             self.frames[t].copy_(env.frames[env.head])  # 49 152 B per env, device to device
-        if action is None:
-            self.action[t].zero_(); self.reward[t].zero_(); self.done[t].zero_()
-        else:
-            self.action[t].copy_(action)
-            self.reward[t].copy_(reward)
-            self.done[t].copy_(done.view(torch.uint8) if done.dtype == torch.bool else done)
-        self.pending[t].copy_((env.state[15] >> 21) & 1)  # auto-reset armed: the next step starts a new episode
+        if done is not None and done.dtype == torch.bool:
+            done = done.view(torch.uint8)
+        if action is not None and (action.dtype != torch.uint8 or not action.is_contiguous()):
+            action = action.to(torch.uint8).contiguous()
+        if reward is not None and (reward.dtype != torch.float32 or not reward.is_contiguous()):
+            reward = reward.to(torch.float32).contiguous()
+        # one kernel: action / reward / done rows, pending (auto-reset armed: the next step starts a new episode) and stale (no
+        # step since an explicit reset: the env's frames are in env.warm) from the engine's state word 15
+        _lib.check(self.lib.ahk_replay_record(_ptr(env.state[15]), _ptr(action), _ptr(reward), _ptr(done), self.n, _ptr(self.action[t]),
+                                              _ptr(self.reward[t]), _ptr(self.done[t]), _ptr(self.pending[t]),
+                                              _ptr(self.stale[t]) if self.view else None, _stream(self.device)))
         self.cursor = (t + 1) % self.capacity
         self.filled = min(self.filled + 1, self.capacity)
 

@@ -289,6 +289,12 @@ int ahk_trainer_copy_buffer(ahk_trainer *t, int which, float *dst_dev, size_t co
  * out_dev + batch*AHK_FRAME_BYTES (slots 1..3) with head 2 is s_{t+1}: both go to ahk_policy_forward as they are. */
 int ahk_replay_gather(const uint8_t *store_dev, int capacity, int n, const int32_t *t_dev, const int32_t *env_dev, int batch,
                       uint8_t *out_dev, void *stream);
+/* ≙ Agent.store_experience (rl_agents.py:88-90) for all n envs in one launch: files the step's action / reward / terminal flag
+ * (each nullable: zeros — the observation an episode starts from) into row t of the replay arrays, together with the two
+ * flags sampling needs from the engine's state word 15 (meta_dev = state_dev + 15 * n): pending_row = auto-reset armed (the
+ * next step starts a new episode), stale_row (nullable) = no step since an explicit reset (frames are in ahk_buffers.warm). */
+int ahk_replay_record(const uint32_t *meta_dev, const uint8_t *action_dev, const float *reward_dev, const uint8_t *done_dev, int n,
+                      uint8_t *action_row, float *reward_row, uint8_t *done_row, uint8_t *pending_row, uint8_t *stale_row, void *stream);
 /* ≙ the epsilon_greedy policy of Agent.__init__ / Agent.act (rl_agents.py:48-56,92-101) for n envs: action = a uniform draw
  * in [0, 10) with probability epsilon, else greedy_dev[i] (the argmax ahk_policy_forward wrote).  Draws are Philox4x32-10
  * keyed by `seed` with counter (iteration, GLOBAL env id), so they do not depend on the sharding.  hist_dev uint64[10]

@@ -56,6 +56,7 @@ def main():
     ap.add_argument("--interval", type=int, default=25)    # train.py:47
     ap.add_argument("--buffer-steps", type=int, default=32)
     ap.add_argument("--agent", choices=["ddqn", "pg"], default="ddqn")
+    ap.add_argument("--copy-store", action="store_true")       # 3-slot ring + a separate replay store filled by one frame copy per step (round 1)
     ap.add_argument("--episode-length", type=int, default=64)   # pg: steps between fits (train.py:45 uses 256)
     ap.add_argument("--fit-batch", type=int, default=4096)      # pg: samples per optimizer step
     args = ap.parse_args()
@@ -66,7 +67,8 @@ def main():
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    env = BatchedAirHockeyEnv(args.envs, device=local, seed=0, env_id_base=rank * args.envs, max_episode_steps=256)
+    env = BatchedAirHockeyEnv(args.envs, device=local, seed=0, env_id_base=rank * args.envs, max_episode_steps=256,
+                              ring_depth=0 if args.copy_store else args.buffer_steps)  # the ring is the replay memory: no frame copies
     env.reset()
     agent = DDQNAgent(env, buffer_steps=args.buffer_steps, batch_size=args.batch, discount_rate=0.98, eps_min=0.05, eps_max=0.99,
                       eps_decay_steps=100000)

@@ -553,12 +553,20 @@ def main():
             "rollout": rollout,
         }
         if world == 1 and not args.no_cpu_baseline:
-            arm = CpuArm(4096)
-            arm.run(2)
-            dt = arm.run(args.cpu_calls)
-            line["cpu_baseline"] = {"value": arm.n * arm.sub * args.cpu_calls / dt, "unit": "env-steps/s", "cores": arm.threads, "kind": "port",
-                                    "sample": arm.sample(args.cpu_calls), "seconds": dt,
-                                    "reference_wrapper_in_build_container": cpu_reference_wrapper()}
+            # the CPU leg runs as `bench.py --impl reference` in a fresh process: inside this one (CUDA context, pinned
+            # mappings, torch / NVML threads) the same pool ran up to 1.5x slower than the reference arm the driver starts
+            import subprocess
+            cmd = [sys.executable, os.path.abspath(__file__), "--impl", "reference", "--steps", str(args.cpu_calls), "--warmup", "2"]
+            proc = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, env=dict(os.environ, CUDA_VISIBLE_DEVICES=""), timeout=900)
+            ref_line = None
+            for row in proc.stdout.decode().splitlines():
+                if row.startswith("{"):
+                    ref_line = json.loads(row)
+            if ref_line is None:
+                raise RuntimeError("cpu_baseline leg failed: %s" % proc.stderr.decode()[-400:])
+            line["cpu_baseline"] = dict(ref_line["cpu_baseline"], seconds=ref_line["ms_per_step"] * 1e-3 * ref_line["steps"],
+                                        how="bench.py --impl reference in a fresh process",
+                                        reference_wrapper_in_build_container=cpu_reference_wrapper())
         emit(line)
     if world > 1:
         dist.destroy_process_group()

@@ -4,7 +4,8 @@
 read the rasteriser's uint8 ring directly — the float32 (9,128,128) observation the reference feeds to
 `model.predict` (ai/reinforcement/rl_agents.py:78-98, ai/supervised/keras/test.py:42-43) is never materialised.
 Weights are given in Keras layouts (conv kernels [kh][kw][cin][cout], dense [in][out], BatchNorm gamma/beta/moving
-mean/moving variance), i.e. what `model.get_weights()` returns, so a trained `.h5` can be loaded by name.
+mean/moving variance), i.e. what `model.get_weights()` returns; a trained Keras `.h5` is read by `load_weights`
+(h5lite.py: the package's own HDF5 reader).
 """
 import ctypes as C
 
@@ -59,16 +60,20 @@ def keras_default_init(seed=0, randomize_bn=False, shapes=None):
     return w
 
 
-def weights_from_keras(arrays):
-    """`model.get_weights()` of the reference's 'rgb' network (models.py:20-65) -> the dict PolicyNetwork takes.
-    Keras lists them layer by layer — Conv2D kernel, bias; BatchNormalization gamma, beta, moving_mean, moving_variance;
-    ... Dense kernel, bias — which is exactly the order of SHAPES (and of ahk_policy_weights).  Also accepts the
-    DDQN variant whose last layer was swapped for a linear Dense(10) (rl_agents.py:160-172): same shapes."""
+def weights_from_keras(arrays, mode=None):
+    """`model.get_weights()` of the reference's networks (models.py:20-65 'rgb', :67-116 'gray-diff') -> the dict
+    PolicyNetwork takes.  Keras lists them layer by layer — Conv2D kernel, bias; BatchNormalization gamma, beta,
+    moving_mean, moving_variance; ... Dense kernel, bias — which is exactly the order of SHAPES / GRAY_SHAPES (and of
+    ahk_policy_weights).  Also accepts the DDQN variant whose last layer was swapped for a linear Dense(10)
+    (rl_agents.py:160-172): same shapes.  mode=None picks the network by the number of arrays (24 / 28)."""
     arrays = list(arrays)
-    if len(arrays) != len(SHAPES):
-        raise ValueError('expected %d weight arrays (models.py rgb network), got %d' % (len(SHAPES), len(arrays)))
+    if mode is None:
+        mode = 'gray-diff' if len(arrays) == len(GRAY_SHAPES) else 'rgb'
+    shapes = SHAPES if mode == 'rgb' else GRAY_SHAPES
+    if len(arrays) != len(shapes):
+        raise ValueError('expected %d weight arrays (models.py %s network), got %d' % (len(shapes), mode, len(arrays)))
     out = {}
-    for (name, shape), a in zip(SHAPES, arrays):
+    for (name, shape), a in zip(shapes, arrays):
         a = np.asarray(a, dtype=np.float32)
         if a.shape != shape:
             raise ValueError('%s: expected shape %s, got %s' % (name, shape, a.shape))
@@ -76,18 +81,77 @@ def weights_from_keras(arrays):
     return out
 
 
+# layer names of models.py:20-116 (the `name=` arguments) and the weight names Keras 2.x gives their variables
+_KERAS_SUFFIX = {'w': 'kernel:0', 'b': 'bias:0', 'gamma': 'gamma:0', 'beta': 'beta:0', 'mean': 'moving_mean:0',
+                 'var': 'moving_variance:0'}
+
+
+def _keras_layers(shapes, head='out'):
+    """[(keras layer name, [(our name, keras weight name)])] in model order: conv1, batchnorm1, ..., dense1, ..., out."""
+    layers = []
+    for name, _ in shapes:
+        ours, kind = name.rsplit('_', 1)
+        layer = ours.replace('bn', 'batchnorm')
+        if layer == 'out':
+            layer = head
+        if not layers or layers[-1][0] != layer:
+            layers.append((layer, []))
+        layers[-1][1].append((name, '%s/%s' % (layer, _KERAS_SUFFIX[kind])))
+    return layers
+
+
+def load_weights_h5(path):
+    """A Keras 2.x HDF5 file of the reference — `model.save(...)` (keras/train.py:98-100, read back by `load_model`,
+    rl_agents.py:153-154; the weights sit under `/model_weights`) or `model.save_weights(...)` (weights at the root):
+    the group's `layer_names` attribute lists the layers in model order, each layer group's `weight_names` its
+    variables in `get_weights()` order (Keras saving.py `save_weights_to_hdf5_group`).  Read with the package's own
+    HDF5 reader (h5lite.py)."""
+    from . import h5lite
+    with h5lite.File(path, 'r') as f:
+        g = f['model_weights'] if 'model_weights' in f else f
+        if 'layer_names' not in g.attrs:
+            raise ValueError('%s: no Keras layer_names attribute' % path)
+        arrays = []
+        for layer in np.atleast_1d(g.attrs['layer_names']):
+            lg = g[layer.decode('utf-8')]
+            for wname in np.atleast_1d(lg.attrs.get('weight_names', np.zeros(0, 'S1'))):
+                arrays.append(np.asarray(lg[wname.decode('utf-8')], dtype=np.float32))
+    return weights_from_keras(arrays)
+
+
+def save_weights_h5(path, weights, mode='rgb', head='out'):
+    """The layout `model.save_weights(path)` writes for models.py's networks, so that the reference side can
+    `model.load_weights(path)` what was trained here (head='output' for the DDQN model, rl_agents.py:168)."""
+    from . import h5lite
+    shapes = SHAPES if mode == 'rgb' else GRAY_SHAPES
+    layers = _keras_layers(shapes, head)
+    with h5lite.File(path, 'w') as f:
+        f.attrs['layer_names'] = np.array([l.encode() for l, _ in layers])
+        f.attrs['backend'] = b'tensorflow'
+        f.attrs['keras_version'] = b'2.1.5'
+        for layer, names in layers:
+            lg = f.create_group(layer)
+            lg.attrs['weight_names'] = np.array([k.encode() for _, k in names])
+            for ours, k in names:
+                lg.create_dataset(k, data=np.asarray(weights[ours], dtype=np.float32))
+
+
 def load_weights(path):
-    """Weights saved from the reference: an .npz written with np.savez(path, *model.get_weights()) (arr_0 .. arr_23) or
-    with the SHAPES names as keys.  (Keras .h5 files need h5py, which this image lacks; `save_weights_npz` below is the
-    three-line export a reference user runs once next to `model.save`, ai/supervised/keras/train.py:98-100.)"""
+    """Weights saved from the reference: a Keras `.h5` (`load_weights_h5`), or an .npz written with
+    np.savez(path, *model.get_weights()) (arr_0 .. arr_23) or with the SHAPES names as keys."""
+    from . import h5lite
+    if h5lite.is_hdf5(path):
+        return load_weights_h5(path)
     with np.load(path) as f:
-        if all(name in f.files for name, _ in SHAPES):
-            return weights_from_keras([f[name] for name, _ in SHAPES])
-        return weights_from_keras([f['arr_%d' % i] for i in range(len(SHAPES))])
+        for shapes in (SHAPES, GRAY_SHAPES):
+            if all(name in f.files for name, _ in shapes) and len(f.files) == len(shapes):
+                return weights_from_keras([f[name] for name, _ in shapes])
+        return weights_from_keras([f['arr_%d' % i] for i in range(len(f.files))])
 
 
-def save_weights_npz(path, weights):
-    np.savez(path, **{name: np.asarray(weights[name], dtype=np.float32) for name, _ in SHAPES})
+def save_weights_npz(path, weights, mode='rgb'):
+    shapes = SHAPES if mode == 'rgb' else GRAY_SHAPES
+    np.savez(path, **{name: np.asarray(weights[name], dtype=np.float32) for name, _ in shapes})
 
 
 def softmax(logits):

@@ -156,8 +156,16 @@ class Agent(object):
     schedule (rl_agents.py:48-56); `iteration` counts calls, as there."""
 
     def __init__(self, env, weights=None, buffer_steps=64, batch_size=128, discount_rate=0.99, eps_min=0.0, eps_max=0.9,
-                 eps_decay_steps=1000, seed=0, group=None, optimizer='sgd', l2_exclude=(), max_fit_batch=None):
+                 eps_decay_steps=1000, seed=0, group=None, optimizer='sgd', l2_exclude=(), max_fit_batch=None,
+                 pretrained_model_file=None, model_file=None):
+        """pretrained_model_file: a Keras `.h5` of the reference (`load_model`, rl_agents.py:153-154) or an .npz —
+        read by policy.load_weights; model_file: where `save_model` / `update_target_weights` write the network
+        (`self.model.save(self.model_file)`, rl_agents.py:103), None = do not write."""
         self.lib = _lib.load()
+        self.model_file, self.head_name = model_file, 'out'
+        if pretrained_model_file is not None:
+            from .policy import load_weights
+            weights = load_weights(pretrained_model_file)
         self.env, self.device, self.n = env, env.device, env.n_envs
         self.n_actions = env.n_actions
         self.batch_size, self.discount_rate = int(batch_size), float(discount_rate)
@@ -202,6 +210,20 @@ class Agent(object):
                                                   _stream(self.device)))
         return action
 
+    def save_model(self, path=None):
+        """≙ `self.model.save(self.model_file)` (rl_agents.py:103): the current weights and BatchNorm moving statistics in
+        Keras' `save_weights` HDF5 layout (policy.save_weights_h5), which `model.load_weights` reads on the reference side."""
+        from .policy import save_weights_h5, save_weights_npz
+        path = path or self.model_file
+        if path is None:
+            raise ValueError('no model_file given')
+        weights = self.trainer.keras_weights()
+        if path.endswith('.npz'):
+            save_weights_npz(path, weights)
+        else:
+            save_weights_h5(path, weights, head=self.head_name)
+        return path
+
     def push_weights(self, policy=None):
         """The fitted network (BatchNorm moving statistics included) -> the forward kernels: folded and packed on the device
         from the trainer's flat weight vector (ahk_policy_set_weights_dev), stream-ordered, nothing crosses PCIe."""
@@ -225,6 +247,9 @@ class DDQNAgent(Agent):
     momentum 0.5, decay 1e-6, clipnorm 2); target network = a second set of forward-kernel weights."""
 
     def __init__(self, env, weights=None, replace_softmax=True, **kw):
+        if kw.get('pretrained_model_file') is not None:
+            from .policy import load_weights
+            weights = load_weights(kw.pop('pretrained_model_file'))
         if replace_softmax:  # rl_agents.py:160-172: a freshly initialised linear output layer (Glorot uniform, zero bias)
             weights = dict(keras_default_init() if weights is None else weights)
             fresh = keras_default_init(seed=kw.get('seed', 0) + 1)
@@ -233,6 +258,8 @@ class DDQNAgent(Agent):
         super().__init__(env, weights, optimizer='sgd', l2_exclude=('out_w',) if replace_softmax else (), **kw)
         self.target_policy = PolicyNetwork(self.trainer.keras_weights(), max_batch=self.batch_size, device=self.device.index)
         self.use_target = False
+        if replace_softmax:
+            self.head_name = 'output'  # the name of the new layer (rl_agents.py:166)
 
     def store_experience(self, action, reward, done):
         self.replay.record(self.env, action, reward, done)
@@ -241,6 +268,8 @@ class DDQNAgent(Agent):
         """≙ Agent.update_target_weights (rl_agents.py:103-107)."""
         self.push_weights(self.target_policy)
         self.use_target = True
+        if self.model_file is not None and self.env_id_base == 0:  # one writer: the rank that owns env 0
+            self.save_model()
 
     def train(self):
         """≙ DDQNAgent.train (rl_agents.py:177-191).  -> loss (float) or None if nothing can be sampled yet."""

@@ -23,8 +23,8 @@ def test_file_name_and_round_trip(tmp_path):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("states", ["f32", "u8"])
-def test_generate_matches_oracle(cuda, orc, table, tmp_path, states):
+@pytest.mark.parametrize("states,container", [("f32", "h5"), ("u8", "h5"), ("u8", "npz")])
+def test_generate_matches_oracle(cuda, orc, table, tmp_path, states, container):
     """The written samples are what the ORACLE produces for the same seeds — the reference's data-generation loop
     (generate_data.py:44-58: env.step() with no actions, reset on a goal or at the step limit) over the oracle env, whose
     observation is the reference processor's float32 (x-128)/128 stack (processor.py:39-52) — in step-major order and in
@@ -33,8 +33,8 @@ def test_generate_matches_oracle(cuda, orc, table, tmp_path, states):
     n, total, seed, limit = 6, 50, 21, 20
     env = BatchedAirHockeyEnv(n, table=table, seed=seed, max_episode_steps=limit)
     env.reset()
-    out = dataset.generate(env, total, str(tmp_path), states=states, shard_states=24, when=1500000000)
-    assert out['samples'] == total and out['steps'] == 9 and len(out['files']) >= 2
+    out = dataset.generate(env, total, str(tmp_path), states=states, shard_states=24, when=1500000000, container=container)
+    assert out['samples'] == total and out['steps'] == 9 and len(out['files']) == 3 and out['files'][0].endswith(container)
     s, r, h = dataset.load_data(os.path.join(str(tmp_path), '*' + os.path.splitext(out['files'][0])[1]))
     assert s.shape == (total, 9, 128, 128) and r.shape == (total,) and r.dtype == np.int8 and h.dtype == np.int8
     assert s.dtype == (np.float32 if states == 'f32' else np.uint8)

@@ -300,6 +300,30 @@ def test_ddqn_training_loop(cuda, table, ring_depth):
 
 
 @pytest.mark.gpu
+def test_model_files_round_trip(cuda, table, tmp_path):
+    """rl_agents.py:103 `self.model.save(self.model_file)` at every target copy and :153-154 `load_model(pretrained_model_file)`:
+    the agent writes a Keras-layout HDF5 file (h5lite.py) and a second agent started from it holds the same network."""
+    torch = cuda
+    from gym_air_hockey_b200 import BatchedAirHockeyEnv, h5lite
+    from gym_air_hockey_b200.rl import DDQNAgent, PGAgent, run_training
+    env = BatchedAirHockeyEnv(32, table=table, seed=9, max_episode_steps=40, ring_depth=16)
+    env.reset()
+    path = str(tmp_path / 'ddqn_model.h5')
+    agent = DDQNAgent(env, batch_size=32, seed=3, model_file=path)
+    run_training(agent, 20, training_start=8, training_interval=5, copy_interval=10)
+    assert agent.use_target and h5lite.is_hdf5(path)
+    with h5lite.File(path) as f:
+        assert f.attrs['layer_names'][-1] == b'output' and f['output/output/kernel:0'].shape == (512, 10)
+    saved = agent.trainer.keras_weights()
+    again = PGAgent(env, pretrained_model_file=path, episode_length=8, fit_batch=32)
+    loaded = again.trainer.keras_weights()
+    assert all(np.array_equal(saved[k], loaded[k]) for k in saved)
+    logits_a = agent.policy.forward(env)[0].clone()
+    logits_b = again.policy.forward(env)[0]
+    assert torch.equal(logits_a, logits_b)
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("ring_depth", [3, 13])
 def test_pg_training_loop(cuda, table, ring_depth):
     torch = cuda

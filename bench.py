@@ -21,6 +21,8 @@ import sys
 import threading
 import time
 
+import numpy as np
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 for p in (os.path.join(ROOT, "deep-learning-air-hockey-robot_b200"), ROOT):
     if p not in sys.path:
@@ -136,7 +138,8 @@ class ClockSampler(threading.Thread):
 class CpuArm(object):
     """The reference's per-step work for this path on the host cores: the oracle port (oracle/ahk_oracle.c — native 450x700
     draw, NEAREST resize, float32 (9,128,128) observation, reward, labels; the reference's own Pygame simulator cannot run
-    anywhere) on a persistent pool of threads with outputs allocated once.  The reference arm
+    anywhere) through the ahk_cpu_* twin of the C ABI (include/ahk_cpu.h: ahk_cpu_step + ahk_cpu_observe per
+    env step, host buffers in the engine's layouts) on a persistent pool of threads with outputs allocated once.  The reference arm
     (--impl reference) and the cpu_baseline leg both go through this class, so their numbers agree."""
 
     def __init__(self, n_envs=4096, threads=None):
@@ -157,25 +160,30 @@ class CpuArm(object):
         while n_envs > 64 and n_envs * per_env > avail // 3:
             n_envs //= 2
         self.n = n_envs
-        table = make_table_image()
-        self.envs = [orc.Env(seed=0, env_id=i, table=table) for i in range(self.n)]
-        for e in self.envs:
-            e.reset()
-        self.pool = orc.Pool(self.envs, self.threads, want_obs=True)
-        self.pool.run(1, 200)  # touches every output page
+        # the CPU twin of the engine's C ABI (include/ahk_cpu.h): same structs, buffers and call protocol as the CUDA arm
+        self.eng = orc.CpuEngine(self.n, seed=0, table=make_table_image(), auto_reset=True, max_episode_steps=200)
+        self.threads = self.eng.threads
+        self.eng.reset()
+        self.obs = np.empty((self.n, 9, 128, 128), np.float32)
+        self._steps(1)  # touches every output page
         t0 = time.perf_counter()
-        self.pool.run(1, 200)
+        self._steps(1)
         per_step = max(time.perf_counter() - t0, 1e-6)
         self.sub = max(1, int(round(1.2 * MIN_REGION_S / per_step)))  # sim steps per env per timed call: >= 0.25 s of work
+
+    def _steps(self, k):
+        for _ in range(k):  # what the reference's env.step() hands back: reward / terminal / labels and the float32 observation
+            self.eng.step()
+            self.eng.observe(1, self.obs)
 
     def run(self, calls):
         t0 = time.perf_counter()
         for _ in range(calls):
-            self.pool.run(self.sub, 200)
+            self._steps(self.sub)
         return time.perf_counter() - t0
 
     def sample(self, calls):
-        return "%d envs x %d sim-steps per call x %d calls, %d threads (persistent pool, outputs preallocated)" % (self.n, self.sub, calls, self.threads)
+        return "%d envs x %d sim-steps per call x %d calls, %d threads (ahk_cpu_step + ahk_cpu_observe(float32) per step; persistent pool, outputs preallocated)" % (self.n, self.sub, calls, self.threads)
 
 
 def cpu_reference_wrapper():

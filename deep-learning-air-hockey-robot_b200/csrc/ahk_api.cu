@@ -408,7 +408,7 @@ int ahk_step_many(ahk_env *e, int steps, const ahk_step_log *log, void *stream)
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     const size_t n = static_cast<size_t>(e->cfg.n_envs);
     const bool logging = log && (log->robot_label || log->human_label || log->done || log->reward);
-    // The persistent kernel keeps two record buffers of 3 * kManyEnvs records per CTA: it takes the call when no CTA can own
+    // The persistent kernel keeps at least two record buffers of 3 * kManyEnvs records per CTA: it takes the call when no CTA can own
     // more envs than that (the adaptive partition moves shares within +-50 % of even).  Larger batches — where a launch
     // is long and its fixed cost small — go step by step.  A/B switch AHK_MANY=loop.
     const int even = (e->cfg.n_envs + e->step_grid - 1) / e->step_grid;
@@ -424,7 +424,7 @@ int ahk_step_many(ahk_env *e, int steps, const ahk_step_log *log, void *stream)
         if (logging) { lg.robot_label = log->robot_label; lg.human_label = log->human_label; lg.done = log->done; lg.reward = log->reward; }
         AHK_CUDA(ahk::launch_step_many(st, steps, lg, e->step_grid, s));
         e->head = (e->head + steps) % e->depth;
-        e->launches += 1;
+        e->launches += ahk::many_launches(steps);
         return AHK_OK;
     }
     for (int t = 0; t < steps; ++t) {

@@ -102,6 +102,7 @@ cudaError_t launch_env(const EnvArgs &a, bool step, cudaStream_t stream);
 cudaError_t step_prepare();
 cudaError_t launch_step(const StepArgs &a, int mode, int grid, cudaStream_t stream); // mode 0 reset, 1 step, 2 draw only
 cudaError_t launch_step_many(const StepArgs &a, int steps, const StepLogArgs &log, int grid, cudaStream_t stream);
+int many_launches(int steps); // kernel launches launch_step_many makes for a window of `steps` steps
 cudaError_t raster_staged_prepare();
 cudaError_t launch_raster_staged(const RasterArgs &a, int grid, cudaStream_t stream);
 cudaError_t launch_observe(const ObserveArgs &a, int grid, cudaStream_t stream);

@@ -525,19 +525,50 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_kernel(StepArgs a)
 // T consecutive ACTION-FREE steps in ONE launch (generate_data.py:44-58: the programmed AI plays both sides, nothing outside
 // the engine feeds a step).  Envs are CTA-private, so a CTA simply runs T steps of its own envs: the table and the lookup
 // tables are staged once per launch instead of once per step, there is no launch boundary (no grid-wide drain, no cold
-// instruction cache) between steps, and the game tick of step t + 1 runs on the owner warps (one thread per env) UNDER
-// the stores of step t: owners tick first and leave their records in the other half of the record buffer, then join the
-// other warps in claiming step t's raster units.  One block barrier per step.  State goes through L2 every step as in the
-// single-step kernel (same device code: env_update), so the results are those of T ahk_step calls, bit for bit.
+// instruction cache) between steps, and the game ticks run on the owner warps (one thread per env) UNDER the stores of
+// earlier steps.  State goes through L2 every step as in the single-step kernel (same device code: env_update), so the
+// results are those of T ahk_step calls, bit for bit.
+//
+// No block barrier between steps (round 2: one __syncthreads per step cost ~1 raster unit of idle time per warp per step,
+// 7 % at 14 units per warp = 4096 envs).  Steps are decoupled through a ring of K record buffers and per-step counters in
+// shared memory; a warp that runs out of units of step t goes straight on to step t + 1:
+//   s_tick[t]  owner warps that have finished the game tick of step t  -> the records of step t are complete
+//   s_count[t] records of step t;  s_next[t] unit claim counter;  s_left[t] warps that have left step t (all units drawn)
+// * an owner warp entering step t first ticks up to step t + A (A = min(2, K - 1)); record slot t' % K is free once every
+//   warp has left step t' - K;
+// * the slowest and the fastest warp are at most K - 1 steps apart and K <= ring depth, so two steps in flight never write
+//   the same ring slot with their NEWEST frames;
+// * frames that a reset rewrites (back > 0: the two older ring slots, or the warm-up side buffer of a deep ring) wait until
+//   every earlier step still in flight has been drawn, and the newest frame of an env that was reset w < K steps ago
+//   waits for that step (its slot is one the reset rewrites when the ring has three slots) — release / acquire through the
+//   s_left counters orders the stores to the same address.
+constexpr int kManySteps = 512; // steps per launch (per-step counters in shared memory); longer windows take several launches
+
+__device__ __forceinline__ void many_arrive(int *counter, int lane)
+{
+    __syncwarp();
+    if (lane == 0) { __threadfence_block(); atomicAdd(counter, 1); }
+}
+
+__device__ __forceinline__ void many_wait(const int *counter, int want, int lane)
+{
+    if (lane == 0) {
+        const volatile int *c = counter;
+        while (*c < want) __nanosleep(32);
+        __threadfence_block();
+    }
+    __syncwarp();
+}
+
 template <bool kBalance>
-__global__ void __launch_bounds__(kStepThreads, 1) step_many_kernel(StepArgs a, int steps, StepLogArgs log)
+__global__ void __launch_bounds__(kStepThreads, 1) step_many_kernel(StepArgs a, int steps, StepLogArgs log, int ring_k)
 {
     extern __shared__ __align__(128) uint8_t smem[];
     const uint4 *s_table = reinterpret_cast<const uint4 *>(smem);
-    uint4 *s_recs = reinterpret_cast<uint4 *>(smem + kFrameBytes); // [2][3 * kManyEnvs] records: step t uses half t & 1
+    uint4 *s_recs = reinterpret_cast<uint4 *>(smem + kFrameBytes); // [K][3 * cnt32] records: step t uses buffer t % K
     Luts &luts = *reinterpret_cast<Luts *>(smem + kLutOffset);
     __shared__ __align__(8) uint64_t s_table_ready;
-    __shared__ int s_count[4], s_next[4]; // records / claimed units of step t at index t & 3
+    __shared__ int s_count[kManySteps], s_next[kManySteps], s_tick[kManySteps], s_left[kManySteps];
     __shared__ unsigned s_stats[kStatWords];
     __shared__ unsigned s_warps_done;
     __shared__ unsigned long long s_raster_start;
@@ -546,7 +577,7 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_many_kernel(StepArgs a, 
     uint4 *s_patch = reinterpret_cast<uint4 *>(smem + kFrameBytes + kRecordBytes + warp * kPatchBytes);
     const uint32_t bar = static_cast<uint32_t>(__cvta_generic_to_shared(&s_table_ready));
     if (tid < kStatWords) s_stats[tid] = 0u;
-    if (tid < 4) { s_count[tid] = 0; s_next[tid] = 0; }
+    for (int i = tid; i < kManySteps; i += kStepThreads) { s_count[i] = 0; s_next[i] = 0; s_tick[i] = 0; s_left[i] = 0; }
     if (tid == 0) {
         s_warps_done = 0u;
         s_raster_start = 0ull;
@@ -566,10 +597,19 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_many_kernel(StepArgs a, 
     int lo = part * a.envs_per_cta, hi = min(n, lo + a.envs_per_cta);
     if (a.bounds != nullptr) { lo = a.bounds[part]; hi = a.bounds[part + 1]; }
     const int cnt = hi - lo;                       // <= kManyEnvs (checked on the host)
-    const bool owner = tid < ((cnt + 31) & ~31);   // whole warps: the statistics reduce with warp collectives
+    const int cnt32 = (cnt + 31) & ~31;
+    const bool owner = tid < cnt32;                // whole warps: the statistics reduce with warp collectives
+    const int owner_warps = cnt32 >> 5;
     const size_t stride = static_cast<size_t>(n);
+    // K record buffers: as many as fit, at most the ring depth (see above), at most 8, at least 2
+    int K = cnt32 > 0 ? (kRecordBytes / 16) / (3 * cnt32) : 8;
+    K = min(min(K, 8), min(a.ras.depth, ring_k));
+    K = max(K, 2);
+    const int ahead = min(2, K - 1);
+    const int slot_recs = 3 * cnt32;
 
-    // the game tick of step t for this CTA's envs: records into half t & 1, count at index t & 3
+    int ticked = 0, since_reset = 15; // owner warps: steps ticked so far; steps since this thread's env was last reset
+    // the game tick of step t for this CTA's envs: records into buffer t % K, count in s_count[t]
     auto tick = [&](int t) {
         const bool live = tid < cnt;
         const int i = lo + tid;
@@ -584,50 +624,70 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_many_kernel(StepArgs a, 
             if (log.reward) log.reward[at] = 0.5f * static_cast<float>(d.reward2);
         }
         if (a.env.stats != nullptr) stat_to_shared<true>(s_stats, d, live);
-        uint4 *recs = s_recs + (t & 1) * (3 * kManyEnvs);
+        since_reset = ((rec[1].w | rec[2].w) & kDrawValid) ? 0 : min(since_reset + 1, 15);
+        const uint32_t wait_for = (since_reset > 0 && since_reset < K) ? static_cast<uint32_t>(since_reset) : 0u;
+        uint4 *recs = s_recs + (t % K) * slot_recs;
 #pragma unroll
         for (int b = 0; b < 3; ++b) {
             const bool valid = live && (rec[b].w & kDrawValid);
             const unsigned votes = __ballot_sync(0xFFFFFFFFu, valid);
             if (votes == 0u) continue;
             int at = 0;
-            if (lane == 0) at = atomicAdd(&s_count[t & 3], __popc(votes));
+            if (lane == 0) at = atomicAdd(&s_count[t], __popc(votes));
             at = __shfl_sync(0xFFFFFFFFu, at, 0) + __popc(votes & ((1u << lane) - 1u));
-            if (valid) recs[at] = make_uint4(rec[b].x, rec[b].y, rec[b].z, (rec[b].w & 0x1Fu) | static_cast<uint32_t>(tid) << 8 | static_cast<uint32_t>(b) << 20);
+            if (valid) recs[at] = make_uint4(rec[b].x, rec[b].y, rec[b].z, (rec[b].w & 0x1Fu) | static_cast<uint32_t>(tid) << 8 | static_cast<uint32_t>(b) << 20 |
+                                                                        (b == 0 ? wait_for << 24 : 0u));
         }
+        many_arrive(&s_tick[t], lane);
     };
 
-    if (owner && steps > 0) tick(0);
-    __syncthreads();
+    if (owner && steps > 0) { tick(0); ticked = 1; }
     mbarrier_wait(bar, 0u); // the table is staged
+    __syncthreads();        // ... and the lookup tables are built
     if (kBalance && tid == 0) s_raster_start = global_ns();
 
 #pragma unroll 1
     for (int t = 0; t < steps; ++t) {
-        if (tid == 0) { s_count[(t + 2) & 3] = 0; s_next[(t + 2) & 3] = 0; } // free since the barrier that ended step t - 1
-        if (owner && t + 1 < steps) tick(t + 1);
-        const int total = s_count[t & 3] * kUnitsPerFrame;
-        const uint4 *recs = s_recs + (t & 1) * (3 * kManyEnvs);
+        if (owner) {
+            const int upto = min(steps, t + 1 + ahead);
+            while (ticked < upto) {
+                if (ticked >= K) many_wait(&s_left[ticked - K], kStepThreads / 32, lane); // the buffer's previous step is drawn
+                tick(ticked);
+                ++ticked;
+            }
+        }
+        many_wait(&s_tick[t], owner_warps, lane);
+        const int total = s_count[t] * kUnitsPerFrame;
+        const uint4 *recs = s_recs + (t % K) * slot_recs;
         const int head = (a.ras.head + t) % a.ras.depth; // a.ras.head: the slot of the window's first step
         for (;;) {
             int u = 0;
-            if (lane == 0) u = atomicAdd(&s_next[t & 3], 1);
+            if (lane == 0) u = atomicAdd(&s_next[t], 1);
             u = __shfl_sync(0xFFFFFFFFu, u, 0);
             if (u >= total) break;
             const uint4 rec_u = recs[u / kUnitsPerFrame];
-            const int env = lo + static_cast<int>((rec_u.w >> 8) & 0x3FFu), back = static_cast<int>(rec_u.w >> 20);
+            const int env = lo + static_cast<int>((rec_u.w >> 8) & 0x3FFu), back = static_cast<int>((rec_u.w >> 20) & 3u);
+            const int wait_for = static_cast<int>((rec_u.w >> 24) & 15u);
+            if (back > 0) { // a reset's rewrite of older frames: after every earlier step still in flight
+                for (int e = max(0, t - (K - 1)); e < t; ++e) many_wait(&s_left[e], kStepThreads / 32, lane);
+            } else if (wait_for > 0 && t - wait_for >= 0) {
+                many_wait(&s_left[t - wait_for], kStepThreads / 32, lane); // after the rewrites of the reset `wait_for` steps ago
+            }
             uint8_t *frame = record_frame<false>(a.ras, head, env, back);
             draw_unit(s_table, s_patch, luts, rec_u, u % kUnitsPerFrame, frame, a.ras.env_id_base + static_cast<uint32_t>(env), a.ras.key, lane);
         }
-        __syncthreads(); // step t is drawn, step t + 1's records are complete
+        many_arrive(&s_left[t], lane);
     }
     if (kBalance && a.bounds_next != nullptr) rebalance(a, part, &s_warps_done, &s_raster_start, lane);
+    __syncthreads(); // every tick's statistics are in shared memory
     if (a.env.stats != nullptr) {
         unsigned long long *st = reinterpret_cast<unsigned long long *>(a.env.stats);
         if (tid < kStatWords && s_stats[tid] != 0u)
             atomicAdd(st + tid, tid == 4 ? static_cast<unsigned long long>(static_cast<long long>(static_cast<int>(s_stats[tid]))) : static_cast<unsigned long long>(s_stats[tid]));
     }
 }
+
+int many_launches(int steps) { return (steps + kManySteps - 1) / kManySteps; }
 
 cudaError_t step_prepare()
 {
@@ -658,12 +718,28 @@ cudaError_t launch_step(const StepArgs &a, int mode, int grid, cudaStream_t stre
     return cudaLaunchKernelEx(&cfg, step_kernel<2>, a);
 }
 
-// plain launch: no programmatic overlap with its neighbours (the launch boundary is paid once per `steps` steps)
-cudaError_t launch_step_many(const StepArgs &a, int steps, const StepLogArgs &log, int grid, cudaStream_t stream)
+// plain launches: no programmatic overlap with their neighbours (the launch boundary is paid once per kManySteps steps)
+cudaError_t launch_step_many(const StepArgs &a0, int steps, const StepLogArgs &log0, int grid, cudaStream_t stream)
 {
-    if (a.bounds_next != nullptr) step_many_kernel<true><<<grid, kStepThreads, kStepSmem, stream>>>(a, steps, log);
-    else step_many_kernel<false><<<grid, kStepThreads, kStepSmem, stream>>>(a, steps, log);
-    return cudaGetLastError();
+    static int ring_k = -1; // A/B switch AHK_MANY_DEPTH=2..8: record buffers in flight (2 ~ round 2's barrier per step)
+    if (ring_k < 0) { const char *sw = getenv("AHK_MANY_DEPTH"); ring_k = sw ? atoi(sw) : 8; if (ring_k < 2) ring_k = 2; }
+    StepArgs a = a0;
+    StepLogArgs log = log0;
+    const size_t n = static_cast<size_t>(a.ras.n);
+    for (int done = 0; done < steps; done += kManySteps) {
+        const int part = steps - done < kManySteps ? steps - done : kManySteps;
+        if (a.bounds_next != nullptr) step_many_kernel<true><<<grid, kStepThreads, kStepSmem, stream>>>(a, part, log, ring_k);
+        else step_many_kernel<false><<<grid, kStepThreads, kStepSmem, stream>>>(a, part, log, ring_k);
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+        a.ras.head = (a.ras.head + part) % a.ras.depth;
+        a.bounds_next = nullptr; // the partition adapts on the window's first launch only
+        if (log.robot_label) log.robot_label += part * n;
+        if (log.human_label) log.human_label += part * n;
+        if (log.done) log.done += part * n;
+        if (log.reward) log.reward += part * n;
+    }
+    return cudaSuccess;
 }
 
 } // namespace ahk

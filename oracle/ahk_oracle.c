@@ -773,3 +773,234 @@ void orc_run_trace(orc_pool *p, orc_env **envs, int n, int steps, int max_episod
 }
 
 int orc_sizeof_sim(void) { return (int)sizeof(orc_sim); }
+
+/* ---------------------------------------------------------------- ahk_cpu_*: the CPU twin of the engine's C ABI */
+/* SURVEY.md §8(b), last row of "C symbols": "identical ahk_cpu_* entry points for the CPU baseline".  Same ahk_config /
+ * ahk_buffers structs (include/ahk.h) and the same buffer layouts as the CUDA library, with HOST pointers: SoA state
+ * [16][n], frame ring [3][n][3][128][128] with the newest frame in slot `head`, reward / done / labels / info [n], stats.
+ * Each env is an orc_env of this file, stepped by a persistent thread pool.  Declared in include/ahk_cpu.h.  Test
+ * infrastructure like the rest of oracle/: the product library never links or loads it. */
+#include <stdio.h>
+#include <unistd.h>
+#include "../include/ahk_cpu.h"
+
+struct ahk_cpu_env {
+    ahk_config cfg;
+    ahk_buffers buf;
+    orc_env **envs;
+    orc_pool *pool;
+    uint8_t *table;
+    int head, bound;
+    uint64_t *part; /* per-worker statistics [threads][AHK_STATS_WORDS] */
+};
+
+static __thread char cpu_error[256];
+const char *ahk_cpu_last_error(void) { return cpu_error; }
+static int cpu_fail(int code, const char *text) { snprintf(cpu_error, sizeof cpu_error, "%s", text); return code; }
+
+int ahk_cpu_create(const ahk_config *cfg, ahk_cpu_env **out)
+{
+    if (!cfg || !out) return cpu_fail(AHK_ERR_ARG, "cfg/out is NULL");
+    if (cfg->n_envs < 1) return cpu_fail(AHK_ERR_ARG, "n_envs must be >= 1");
+    if (cfg->ring_depth != 0 && cfg->ring_depth != 3) return cpu_fail(AHK_ERR_ARG, "the CPU twin keeps the 3-slot ring only");
+    ahk_cpu_env *e = (ahk_cpu_env *)calloc(1, sizeof *e);
+    if (!e) return cpu_fail(AHK_ERR_ARG, "out of memory");
+    e->cfg = *cfg;
+    int threads = (int)sysconf(_SC_NPROCESSORS_ONLN);
+    const char *sw = getenv("AHK_CPU_THREADS");
+    if (sw && atoi(sw) > 0) threads = atoi(sw);
+    if (threads > cfg->n_envs) threads = cfg->n_envs;
+    if (threads > 1024) threads = 1024;
+    e->pool = orc_pool_create(threads);
+    e->part = (uint64_t *)calloc((size_t)threads * AHK_STATS_WORDS, sizeof(uint64_t));
+    e->head = 2;
+    *out = e;
+    return AHK_OK;
+}
+
+void ahk_cpu_destroy(ahk_cpu_env *e)
+{
+    if (!e) return;
+    if (e->envs) for (int i = 0; i < e->cfg.n_envs; ++i) orc_env_destroy(e->envs[i]);
+    free(e->envs);
+    orc_pool_destroy(e->pool);
+    free(e->table);
+    free(e->part);
+    free(e);
+}
+
+int ahk_cpu_threads(const ahk_cpu_env *e) { return e ? orc_pool_threads(e->pool) : 0; }
+int ahk_cpu_head(const ahk_cpu_env *e) { return e ? e->head : -1; }
+
+int ahk_cpu_set_table_image(ahk_cpu_env *e, const uint8_t *rgb, int height, int width)
+{
+    if (!e || !rgb) return cpu_fail(AHK_ERR_ARG, "env/rgb is NULL");
+    if (height != ORC_H || width != ORC_W) return cpu_fail(AHK_ERR_ARG, "the table image must be 700 x 450 x 3");
+    if (e->envs) return cpu_fail(AHK_ERR_STATE, "the table image is already set");
+    e->table = (uint8_t *)malloc((size_t)ORC_W * ORC_H * 3);
+    memcpy(e->table, rgb, (size_t)ORC_W * ORC_H * 3);
+    e->envs = (orc_env **)calloc((size_t)e->cfg.n_envs, sizeof *e->envs);
+    for (int i = 0; i < e->cfg.n_envs; ++i) e->envs[i] = orc_env_create(e->cfg.seed, e->cfg.env_id_base + (uint32_t)i, e->table);
+    return AHK_OK;
+}
+
+int ahk_cpu_bind_buffers(ahk_cpu_env *e, const ahk_buffers *b)
+{
+    if (!e || !b) return cpu_fail(AHK_ERR_ARG, "env/bufs is NULL");
+    if (!b->state || !b->frames || !b->reward || !b->done || !b->robot_label || !b->human_label)
+        return cpu_fail(AHK_ERR_ARG, "state, frames, reward, done and the two label buffers are required");
+    e->buf = *b;
+    e->bound = 1;
+    return AHK_OK;
+}
+
+typedef struct {
+    ahk_cpu_env *e;
+    int mode;                 /* 0 reset, 1 step */
+    const uint8_t *mask, *episode, *use, *robot, *human;
+    const ahk_step_log *log;
+    int t;                    /* row of the log */
+    int slots[3];             /* ring slots of the frames newest, middle, oldest after this call */
+} cpu_call;
+
+static void cpu_publish(ahk_cpu_env *h, int i, int all_frames, const int slots[3])
+{
+    const orc_env *e = h->envs[i];
+    const size_t n = (size_t)h->cfg.n_envs;
+    uint32_t *w = h->buf.state + i;
+    const uint32_t *f = (const uint32_t *)&e->sim.puck;
+    for (int k = 0; k < 12; ++k) w[(size_t)k * n] = f[k];
+    w[12 * n] = e->sim.serve_count;
+    w[13 * n] = e->reset_count;
+    w[14 * n] = e->noise_count;
+    w[15 * n] = (e->episode_steps > 0xFFFFu ? 0xFFFFu : e->episode_steps) | (uint32_t)e->episode << 16 | (uint32_t)e->use << 18 |
+                (uint32_t)e->pending_reset << 21;
+    for (int age = 0; age < (all_frames ? 3 : 1); ++age)
+        memcpy(h->buf.frames + ((size_t)slots[age] * n + (size_t)i) * ORC_FRAME, e->ring[age], ORC_FRAME);
+}
+
+static void cpu_slice(void *ctx, int lo, int hi, int worker)
+{
+    cpu_call *c = (cpu_call *)ctx;
+    ahk_cpu_env *h = c->e;
+    uint64_t *st = h->part + (size_t)worker * AHK_STATS_WORDS;
+    const size_t n = (size_t)h->cfg.n_envs;
+    for (int i = lo; i < hi; ++i) {
+        orc_env *e = h->envs[i];
+        if (c->mode == 0) {
+            if (c->mask && !c->mask[i]) continue;
+            const int ep = c->episode && c->episode[i] != AHK_EP_SAMPLE ? c->episode[i] : -1;
+            orc_env_reset(e, ep, ep < 0 ? 0 : (c->use ? c->use[i] : USE_ALL));
+            cpu_publish(h, i, 1, c->slots);
+            st[1] += 1; /* episodes: every reset counts, as in the CUDA engine */
+            continue;
+        }
+        orc_step_out o;
+        const int was_pending = h->cfg.auto_reset && e->pending_reset;
+        const int r = c->robot ? c->robot[i] : ACT_NONE, hu = c->human ? c->human[i] : ACT_NONE;
+        if (h->cfg.auto_reset) orc_env_step_auto(e, r, hu, h->cfg.max_episode_steps, &o);
+        else orc_env_step(e, r, hu, &o);
+        cpu_publish(h, i, was_pending, c->slots);
+        h->buf.reward[i] = o.reward;
+        h->buf.done[i] = o.terminal;
+        h->buf.robot_label[i] = o.robot_label;
+        h->buf.human_label[i] = o.human_label;
+        if (h->buf.info) h->buf.info[i] = (uint8_t)(o.flags | o.scored << 5);
+        if (c->log) {
+            const size_t at = (size_t)c->t * n + (size_t)i;
+            if (c->log->robot_label) c->log->robot_label[at] = o.robot_label;
+            if (c->log->human_label) c->log->human_label[at] = o.human_label;
+            if (c->log->done) c->log->done[at] = o.terminal;
+            if (c->log->reward) c->log->reward[at] = o.reward;
+        }
+        st[0] += 1;
+        st[1] += (uint64_t)was_pending;
+        st[2] += o.scored == SCORED_TOP;
+        st[3] += o.scored == SCORED_BOTTOM;
+        st[4] += (uint64_t)(int64_t)(int)(o.reward * 2.0f);
+        st[5 + o.robot_label] += 1;
+        st[15 + o.human_label] += 1;
+    }
+}
+
+static void cpu_run(ahk_cpu_env *e, cpu_call *c)
+{
+    for (int age = 0; age < 3; ++age) c->slots[age] = (e->head + 3 - age) % 3;
+    pool_run(e->pool, cpu_slice, c, e->cfg.n_envs);
+    if (e->buf.stats)
+        for (int k = 0; k < orc_pool_threads(e->pool); ++k)
+            for (int w = 0; w < AHK_STATS_WORDS; ++w) { e->buf.stats[w] += e->part[(size_t)k * AHK_STATS_WORDS + w]; e->part[(size_t)k * AHK_STATS_WORDS + w] = 0; }
+}
+
+static int cpu_ready(const ahk_cpu_env *e)
+{
+    if (!e) return cpu_fail(AHK_ERR_ARG, "env is NULL");
+    if (!e->envs) return cpu_fail(AHK_ERR_STATE, "ahk_cpu_set_table_image has not been called");
+    if (!e->bound) return cpu_fail(AHK_ERR_STATE, "ahk_cpu_bind_buffers has not been called");
+    return AHK_OK;
+}
+
+int ahk_cpu_reset(ahk_cpu_env *e, const uint8_t *mask, const uint8_t *episode, const uint8_t *use, void *stream)
+{
+    (void)stream;
+    int rc = cpu_ready(e);
+    if (rc) return rc;
+    cpu_call c = { e, 0, mask, episode, use, NULL, NULL, NULL, 0, { 0, 0, 0 } };
+    cpu_run(e, &c);
+    return AHK_OK;
+}
+
+int ahk_cpu_step(ahk_cpu_env *e, const uint8_t *robot, const uint8_t *human, void *stream)
+{
+    (void)stream;
+    int rc = cpu_ready(e);
+    if (rc) return rc;
+    e->head = (e->head + 1) % 3;
+    cpu_call c = { e, 1, NULL, NULL, NULL, robot, human, NULL, 0, { 0, 0, 0 } };
+    cpu_run(e, &c);
+    return AHK_OK;
+}
+
+int ahk_cpu_step_many(ahk_cpu_env *e, int steps, const ahk_step_log *log, void *stream)
+{
+    (void)stream;
+    int rc = cpu_ready(e);
+    if (rc) return rc;
+    if (steps < 0) return cpu_fail(AHK_ERR_ARG, "steps must be >= 0");
+    for (int t = 0; t < steps; ++t) {
+        e->head = (e->head + 1) % 3;
+        cpu_call c = { e, 1, NULL, NULL, NULL, NULL, NULL, log, t, { 0, 0, 0 } };
+        cpu_run(e, &c);
+    }
+    return AHK_OK;
+}
+
+typedef struct { ahk_cpu_env *e; int format; void *out; } cpu_obs;
+
+static void cpu_obs_slice(void *ctx, int lo, int hi, int worker)
+{
+    cpu_obs *c = (cpu_obs *)ctx;
+    (void)worker;
+    for (int i = lo; i < hi; ++i) {
+        const orc_env *e = c->e->envs[i];
+        if (c->format == AHK_OBS_U8) memcpy((uint8_t *)c->out + (size_t)i * 3 * ORC_FRAME, e->ring, 3 * ORC_FRAME);
+        else if (c->format == AHK_OBS_RGB_F32) orc_env_observe_rgb(e, (float *)c->out + (size_t)i * 3 * ORC_FRAME);
+        else {
+            float stack[3 * ORC_FRAME]; /* the processor's float32 buffer (processor.py:23,45-49) */
+            for (int k = 0; k < 3 * ORC_FRAME; ++k) stack[k] = (float)(&e->ring[0][0])[k];
+            orc_observe_gray_diff(stack, (double *)c->out + (size_t)i * 128 * 128);
+        }
+    }
+}
+
+/* ≙ ahk_observe: the stacked observation of every env in the reference's formats (processor.py:39-64), host memory */
+int ahk_cpu_observe(ahk_cpu_env *e, int format, void *out, void *stream)
+{
+    (void)stream;
+    int rc = cpu_ready(e);
+    if (rc) return rc;
+    if (!out || format < AHK_OBS_U8 || format > AHK_OBS_GRAY_DIFF_F64) return cpu_fail(AHK_ERR_ARG, "out is NULL or the format is unknown");
+    cpu_obs c = { e, format, out };
+    pool_run(e->pool, cpu_obs_slice, &c, e->cfg.n_envs);
+    return AHK_OK;
+}

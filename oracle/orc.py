@@ -285,3 +285,112 @@ def unpack_out(out):
     """Fields of Pool.trace's packed step results."""
     return {"reward": ((out & 7).astype(np.float32) - 2.0) * 0.5, "terminal": (out >> 3) & 1, "robot_label": (out >> 4) & 15,
             "human_label": (out >> 8) & 15, "flags": (out >> 12) & 31, "scored": (out >> 17) & 3}
+
+
+# ------------------------------------------------------------------------------------------------ ahk_cpu_* (include/ahk_cpu.h)
+class CpuConfig(C.Structure):  # ahk_config (include/ahk.h)
+    _fields_ = [("n_envs", C.c_int32), ("device", C.c_int32), ("seed", C.c_uint64), ("env_id_base", C.c_uint32),
+                ("auto_reset", C.c_int32), ("max_episode_steps", C.c_int32), ("ring_depth", C.c_int32), ("reserved", C.c_int32 * 4)]
+
+
+class CpuBuffers(C.Structure):  # ahk_buffers
+    _fields_ = [(name, C.c_void_p) for name in
+                ("state", "frames", "reward", "done", "robot_label", "human_label", "info", "stats", "drawlist", "warm")]
+
+
+class CpuStepLog(C.Structure):  # ahk_step_log
+    _fields_ = [("robot_label", C.c_void_p), ("human_label", C.c_void_p), ("done", C.c_void_p), ("reward", C.c_void_p)]
+
+
+# every symbol include/ahk_cpu.h declares: name -> (restype, argtypes); the twin of gym_air_hockey_b200._lib.SYMBOLS
+_vp, _i = C.c_void_p, C.c_int
+CPU_SYMBOLS = {
+    "ahk_cpu_create": (_i, [C.POINTER(CpuConfig), C.POINTER(_vp)]),
+    "ahk_cpu_destroy": (None, [_vp]),
+    "ahk_cpu_threads": (_i, [_vp]),
+    "ahk_cpu_set_table_image": (_i, [_vp, _vp, _i, _i]),
+    "ahk_cpu_bind_buffers": (_i, [_vp, C.POINTER(CpuBuffers)]),
+    "ahk_cpu_reset": (_i, [_vp, _vp, _vp, _vp, _vp]),
+    "ahk_cpu_step": (_i, [_vp, _vp, _vp, _vp]),
+    "ahk_cpu_step_many": (_i, [_vp, _i, C.POINTER(CpuStepLog), _vp]),
+    "ahk_cpu_observe": (_i, [_vp, _i, _vp, _vp]),
+    "ahk_cpu_head": (_i, [_vp]),
+    "ahk_cpu_last_error": (C.c_char_p, []),
+}
+
+
+class CpuEngine(object):
+    """The batched engine's call protocol on the host cores, through the ahk_cpu_* twins of the C ABI: numpy arrays in
+    the layouts of ahk_buffers (state [16, n] uint32, frames [3, n, 3, 128, 128] uint8 ring with the newest frame in
+    slot `head`, reward / done / labels [n])."""
+
+    def __init__(self, n_envs, seed=0, table=None, auto_reset=True, max_episode_steps=0, env_id_base=0):
+        L = lib()
+        for name, (res, args) in CPU_SYMBOLS.items():
+            fn = getattr(L, name)
+            fn.restype, fn.argtypes = res, args
+        self.L, self.n = L, int(n_envs)
+        cfg = CpuConfig(n_envs=self.n, device=-1, seed=seed, env_id_base=env_id_base, auto_reset=int(auto_reset),
+                        max_episode_steps=int(max_episode_steps), ring_depth=3)
+        h = C.c_void_p()
+        self._check(L.ahk_cpu_create(C.byref(cfg), C.byref(h)))
+        self._h = h
+        table = np.ascontiguousarray(table, dtype=np.uint8)
+        self._check(L.ahk_cpu_set_table_image(h, table.ctypes.data_as(_vp), table.shape[0], table.shape[1]))
+        n = self.n
+        self.state = np.zeros((16, n), np.uint32)
+        self.frames = np.zeros((3, n, 3, 128, 128), np.uint8)
+        self.reward = np.zeros(n, np.float32)
+        self.done, self.robot_label, self.human_label, self.info = (np.zeros(n, np.uint8) for _ in range(4))
+        self.stats = np.zeros(32, np.uint64)
+        b = CpuBuffers(**{k: getattr(self, k).ctypes.data_as(_vp) for k in
+                          ("state", "frames", "reward", "done", "robot_label", "human_label", "info", "stats")})
+        self._check(L.ahk_cpu_bind_buffers(h, C.byref(b)))
+
+    def _check(self, rc):
+        if rc != 0:
+            raise RuntimeError("ahk_cpu: %s (%d)" % (self.L.ahk_cpu_last_error().decode(), rc))
+
+    @property
+    def head(self):
+        return self.L.ahk_cpu_head(self._h)
+
+    @property
+    def threads(self):
+        return self.L.ahk_cpu_threads(self._h)
+
+    @staticmethod
+    def _u8(a):
+        return None if a is None else np.ascontiguousarray(a, dtype=np.uint8)
+
+    def reset(self, mask=None, episode=None, use=None):
+        m, e, u = self._u8(mask), self._u8(episode), self._u8(use)
+        self._check(self.L.ahk_cpu_reset(self._h, *(None if a is None else a.ctypes.data_as(_vp) for a in (m, e, u)), None))
+
+    def step(self, robot=None, human=None):
+        r, h = self._u8(robot), self._u8(human)
+        self._check(self.L.ahk_cpu_step(self._h, *(None if a is None else a.ctypes.data_as(_vp) for a in (r, h)), None))
+
+    def step_many(self, steps, log=None):
+        lg = None
+        if log is not None:
+            lg = C.byref(CpuStepLog(**{k: v.ctypes.data_as(_vp) for k, v in log.items()}))
+        self._check(self.L.ahk_cpu_step_many(self._h, int(steps), lg, None))
+
+    def observe(self, fmt, out=None):
+        """fmt 0: uint8 [n, 9, 128, 128]; 1: float32 (x - 128) / 128; 2: float64 gray-diff [n, 1, 128, 128]."""
+        shape, dt = [((self.n, 9, 128, 128), np.uint8), ((self.n, 9, 128, 128), np.float32), ((self.n, 1, 128, 128), np.float64)][fmt]
+        out = np.empty(shape, dt) if out is None else out
+        self._check(self.L.ahk_cpu_observe(self._h, int(fmt), out.ctypes.data_as(_vp), None))
+        return out
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self.L.ahk_cpu_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -433,10 +433,11 @@ def test_producer_kernel_before_step_two_engines_one_stream(cuda, orc, noise_tab
         pool.close()
 
 
-@pytest.mark.parametrize("n,T,limit", [(333, 1, 9), (1184, 7, 5), (4096, 64, 23)])
+@pytest.mark.parametrize("n,T,limit", [(333, 1, 9), (1184, 7, 5), (4096, 64, 23), (1184, 40, 1), (4096, 64, 2), (2500, 48, 3), (300, 700, 37)])
 def test_step_many_matches_oracle(cuda, orc, table, n, T, limit):
     """ahk_step_many(T): T action-free steps in one call, resets inside the window (limit < T), every step's outputs
-    logged.  A sample of envs against the oracle: state, ring, and the whole [T, n] log; twice in a row, so that the second
+    logged.  The kernel runs its steps without block barriers (warps up to two steps apart on the 3-slot ring): limit 1 / 2 / 3
+    make every env rewrite the older ring slots every / every other / every third step, T = 700 spans two launches.  A sample of envs against the oracle: state, ring, and the whole [T, n] log; twice in a row, so that the second
     window starts from envs armed for a reset."""
     torch = cuda
     seed = 1000 + T

@@ -65,10 +65,10 @@ def measured_peaks():
 
 
 def ncu_traffic(pattern):
-    """dram__bytes_read.sum + dram__bytes_write.sum per launch from the NEWEST committed ncu summary matching `pattern`
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch from the LAST (by name) committed ncu summary matching `pattern`
     (tools/ncu_summary.py output under profiles/), or None.  Returns (bytes, file name).  A `_T<k>_` in the file name says
     the captured launches ran k env steps each (the persistent ahk_step_many kernel)."""
-    files = sorted(glob.glob(os.path.join(ROOT, "profiles", pattern)), key=os.path.getmtime)
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", pattern)))  # by name: the snapshot on the GPU box does not keep mtimes
     unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
     for path in reversed(files):
         total, seen = 0.0, 0

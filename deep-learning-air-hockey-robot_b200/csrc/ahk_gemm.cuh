@@ -60,6 +60,7 @@ struct Args {
     long long out_pitch;             // elements per output row
     float scale;
     int py, px;                      // kConv3Dgrad: parity class of the input pixels
+    int pdl;                         // programmatic dependent launch of the next kernel: 0 off, 1 trigger after the prologue, 2 at the end
 };
 
 // shared-memory matrix descriptor of a swizzled tile (cute::UMMA::SmemDescriptor, version 1): K-major: rows of `span` bytes
@@ -128,6 +129,14 @@ __global__ void __launch_bounds__(kCta, 1) gemm_tma_kernel(Args g, const __grid_
     tc_fence_after();
     const uint32_t tmem = s_tmem;
     constexpr uint32_t kLayout = kSpan == 128 ? 2u : 4u; // SWIZZLE_128B / SWIZZLE_64B
+    // programmatic dependent launch (ahk_tc.cuh): the resident weights are not the previous kernel's output and are fetched
+    // before the wait; everything else — A tiles, streamed B, the epilogue's stores — comes after it
+    if (g.pdl == 1) pdl_trigger();
+    if (kBRes && my_items > 0 && tid == 0) {
+        mbar_expect_tx(&s_bfull, C::kResBytes);
+        for (int kc = 0; kc < kBRes; ++kc) tma_2d(s_res + kc * C::kBBytes, &tm_b, kc * C::kChunkK, 0, &s_bfull);
+    }
+    pdl_wait();
 
     // work item -> (M tile, N block, K split): N blocks of one M tile are neighbours, so CTAs running side by side share A in L2
     auto decode = [&](int it, int &tm_i, int &nb, int &ks) {
@@ -141,10 +150,6 @@ __global__ void __launch_bounds__(kCta, 1) gemm_tma_kernel(Args g, const __grid_
     if (warp == 0) {
         // ---------------------------------------------------------------- producer
         if (lane == 0) {
-            if (kBRes && my_items > 0) { // the resident B operand: every K chunk, once
-                mbar_expect_tx(&s_bfull, C::kResBytes);
-                for (int kc = 0; kc < kBRes; ++kc) tma_2d(s_res + kc * C::kBBytes, &tm_b, kc * C::kChunkK, 0, &s_bfull);
-            }
             uint32_t fill = 0;
             for (int it = 0; it < my_items; ++it) {
                 int tm_i, nb, ks;
@@ -285,6 +290,7 @@ __global__ void __launch_bounds__(kCta, 1) gemm_tma_kernel(Args g, const __grid_
     }
     tc_fence_before();
     __syncthreads();
+    if (g.pdl == 2) pdl_trigger();
     if (warp == 1) tmem_dealloc(tmem, C::kTmemCols);
 }
 
@@ -294,7 +300,7 @@ template <int N, int kSpan, int kAMode, bool kBMn, int kStages, int kBRes> const
 }
 
 template <int N, int kSpan, int kAMode, bool kBMn, int kEpi, int kStages, int kBRes = 0>
-cudaError_t launch(const Args &g, const CUtensorMap &tm_a, const CUtensorMap &tm_b, int sms, cudaStream_t s)
+cudaError_t launch(const Args &g, const CUtensorMap &tm_a, const CUtensorMap &tm_b, int sms, cudaStream_t s, bool pdl = false)
 {
     constexpr int bytes = smem_bytes<N, kSpan, kAMode, kBMn, kStages, kBRes>();
     static_assert(bytes <= 227 * 1024, "stages do not fit");
@@ -302,8 +308,7 @@ cudaError_t launch(const Args &g, const CUtensorMap &tm_a, const CUtensorMap &tm
     if (e != cudaSuccess) return e;
     const int items = g.tiles_m * g.blocks_n * g.k_splits;
     if (items <= 0) return cudaSuccess;
-    gemm_tma_kernel<N, kSpan, kAMode, kBMn, kEpi, kStages, kBRes><<<items < sms ? items : sms, kCta, bytes, s>>>(g, tm_a, tm_b);
-    return cudaGetLastError();
+    return launch_kernel(gemm_tma_kernel<N, kSpan, kAMode, kBMn, kEpi, kStages, kBRes>, dim3(items < sms ? items : sms), dim3(kCta), bytes, s, pdl, g, tm_a, tm_b);
 }
 
 // ---- tensor maps (host).  bf16 elements; dims[0] is the contiguous one; strides in BYTES for dims 1.. (multiples of 16)

@@ -79,6 +79,7 @@ struct Args {
     int depth;                  // ring slots (3, or a deep ring: ahk_stack)
     const uint8_t *warm;        // deep ring: warm-up frames of each env's latest reset, else nullptr (stack_frame, ahk_kernels.cuh)
     const uint32_t *meta;       // deep ring: state word 15 per env
+    int pdl;                    // programmatic dependent launch of the NEXT layer's kernel: 0 off, 1 trigger after the prologue, 2 trigger at the end
 };
 
 using namespace ahk::tc; // inline-PTX wrappers: ahk_tc.cuh
@@ -169,6 +170,7 @@ __global__ void __launch_bounds__(kThreads) layer_kernel(Args a)
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = s_tmem;
+    pdl_wait(); // programmatic dependent launch (ahk_tc.cuh): the previous layer's output is read from here on
 
     const uint4 *wsrc = a.weights + static_cast<size_t>(split) * NCH * (kBBytes / 16);
     constexpr uint32_t kIdesc = instr_desc(N);
@@ -307,7 +309,7 @@ template <int L> constexpr int smem_bytes() { return 2 * kAStage + 2 * Traits<L>
 
 // grid.x = min(tiles, resident CTAs on the device): the kernel loops over its tiles
 template <int L>
-cudaError_t launch(const Args &a, int tiles, int grid_y, int sms, cudaStream_t s)
+cudaError_t launch(const Args &a, int tiles, int grid_y, int sms, cudaStream_t s, bool pdl = false)
 {
     static int per_sm = 0;
     if (per_sm == 0) {
@@ -321,8 +323,7 @@ cudaError_t launch(const Args &a, int tiles, int grid_y, int sms, cudaStream_t s
         if (per_sm < 1) per_sm = 1;
     }
     const int resident = sms * per_sm / grid_y;
-    layer_kernel<L><<<dim3(tiles < resident ? tiles : (resident > 0 ? resident : 1), grid_y), kThreads, smem_bytes<L>(), s>>>(a);
-    return cudaGetLastError();
+    return launch_kernel(layer_kernel<L>, dim3(tiles < resident ? tiles : (resident > 0 ? resident : 1), grid_y), dim3(kThreads), smem_bytes<L>(), s, pdl, a);
 }
 
 // ------------------------------------------------------------------------------------------------ conv1, Toeplitz form
@@ -1003,6 +1004,7 @@ __global__ void __launch_bounds__(c1t::kCta, 1) conv1t_kernel(Args a, const __gr
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = s_tmem;
+    if (a.pdl == 1) pdl_trigger(); // conv2 of the same forward pass may move in as this grid's CTAs retire (ahk_tc.cuh)
 
     if (warp == kLoadWarp) {
         // ---------------------------------------------------------------- loader: one tiled TMA copy per plane (as conv1p_kernel)
@@ -1193,6 +1195,7 @@ __global__ void __launch_bounds__(c1t::kCta, 1) conv1t_kernel(Args a, const __gr
     }
     tc_fence_before();
     __syncthreads();
+    if (a.pdl == 2) pdl_trigger();
     if (warp == kMmaWarp) tmem_dealloc(tmem, kTmemCols);
 }
 
@@ -1629,12 +1632,17 @@ __global__ void __launch_bounds__(ctm::kCta, 1) conv_tm_kernel(Args a)
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = s_tmem;
+    // programmatic dependent launch (ahk_tc.cuh): the weights are fetched under the previous layer's tail, its output after the wait
+    if (a.pdl == 1) pdl_trigger();
+    if (warp == 9 && lane == 0) {
+        mbar_expect_tx(&s_wfull, C::kWBytes);
+        for (int i = 0; i < C::kWBytes; i += 8192) bulk_load(s_w + i, reinterpret_cast<const uint8_t *>(a.weights) + i, 8192, &s_wfull);
+    }
+    pdl_wait();
 
     if (warp == 9) {
         // ---------------------------------------------------------------- loader: one bulk copy per item
         if (lane == 0) {
-            mbar_expect_tx(&s_wfull, C::kWBytes);
-            for (int i = 0; i < C::kWBytes; i += 8192) bulk_load(s_w + i, reinterpret_cast<const uint8_t *>(a.weights) + i, 8192, &s_wfull);
             for (int t = 0; t < my_items; ++t) {
                 const uint32_t rb = t & 1u;
                 if (t >= 2) mbar_wait_sleep(&s_rempty[rb], ((t >> 1) - 1) & 1);
@@ -1760,17 +1768,17 @@ __global__ void __launch_bounds__(ctm::kCta, 1) conv_tm_kernel(Args a)
     }
     tc_fence_before();
     __syncthreads();
+    if (a.pdl == 2) pdl_trigger();
     if (warp == 8) tmem_dealloc(tmem, 512);
 }
 
 template <int L>
-cudaError_t launch_tm(const Args &a, int sms, cudaStream_t s)
+cudaError_t launch_tm(const Args &a, int sms, cudaStream_t s, bool pdl = false)
 {
     cudaError_t e = cudaFuncSetAttribute(conv_tm_kernel<L>, cudaFuncAttributeMaxDynamicSharedMemorySize, ctm::smem_bytes<L>());
     if (e != cudaSuccess) return e;
     const int items = (a.n + ctm::Cfg<L>::kSamples - 1) / ctm::Cfg<L>::kSamples;
-    conv_tm_kernel<L><<<items < sms ? items : sms, ctm::kCta, ctm::smem_bytes<L>(), s>>>(a);
-    return cudaGetLastError();
+    return launch_kernel(conv_tm_kernel<L>, dim3(items < sms ? items : sms), dim3(ctm::kCta), ctm::smem_bytes<L>(), s, pdl, a);
 }
 
 // ------------------------------------------------------------------------------------------------ gray-diff input
@@ -2099,6 +2107,11 @@ struct ahk_policy {
     // conv3 stays on the TMA-fed GEMM (0.075 ms against 0.165: its 64-byte pixels put every lane of a load on the same banks).
     // A/B switch AHK_CONVTM=0 (neither) | 2 (default) | 23 (both)
     bool conv_tm = true, conv_tm3 = false;
+    // the layer kernels of one inference forward chained by programmatic dependent launch: 2 (default) = a kernel releases the next
+    // layer's launch when its own work is done, so that launch latency, barrier set-up, tensor-memory allocation and the weight
+    // fetch run under its teardown (forward of 8192 samples 0.5156 -> 0.5040 ms, same box); 1 = released right after the prologue
+    // (0.529 ms: the early CTAs of the next layer take SM resources from the running one); 0 = ordinary launches.  AHK_POLICY_PDL
+    int pdl = 2;
     uint16_t *w1p = nullptr; // conv1 in phase-separated form (conv1p_kernel, the default), fp16, unscaled
     bool conv1_n144 = false;
     bool conv1_normal = false; // A/B switch AHK_CONV1=normal: conv1t_kernel with the pixels as NORMAL fp16 numbers (1024 + v - 1024)
@@ -2272,6 +2285,7 @@ int ahk_policy_create(int device, int max_batch, const ahk_policy_weights *w, ah
     if (const char *sw = getenv("AHK_CONV23")) p->legacy_conv = strcmp(sw, "tile") == 0;
     if (const char *sw = getenv("AHK_CONV2")) p->conv2_parity = strcmp(sw, "ws") != 0;
     if (const char *sw = getenv("AHK_CONVTM")) { p->conv_tm = strcmp(sw, "0") != 0; p->conv_tm3 = strcmp(sw, "23") == 0; }
+    if (const char *sw = getenv("AHK_POLICY_PDL")) p->pdl = atoi(sw);
     if (const char *sw = getenv("AHK_CONV1")) { p->conv1_n144 = strcmp(sw, "n144") == 0; p->conv1_smem = strcmp(sw, "smem") == 0; p->conv1_normal = strcmp(sw, "normal") == 0; }
     int rc = load_rgb_weights(p, w);
     const size_t nb = static_cast<size_t>(max_batch);
@@ -2464,13 +2478,15 @@ void ahk_policy_destroy(ahk_policy *p)
 }
 
 // One layer of the 'rgb' network on n samples (a: frames / ring geometry filled in): 0 conv1 ... 5 out
-static int rgb_layer(ahk_policy *p, Args a, int layer, float *logits, uint8_t *action, cudaStream_t s)
+// pdl: launch with programmatic stream serialization behind the previous layer's kernel (inference forward only: in
+// model.fit's forward the kernel before a layer folds that layer's weights, which these kernels fetch before their wait)
+static int rgb_layer(ahk_policy *p, Args a, int layer, float *logits, uint8_t *action, cudaStream_t s, bool pdl = false)
 {
     namespace tg = ahk::tg;
     const int n = a.n;
     auto tiles = [](long long rows) { return static_cast<int>((rows + kBM - 1) / kBM); };
     tg::Args g{};
-    g.k_splits = 1; g.m_total = n; g.scale = 1.0f;
+    g.k_splits = 1; g.m_total = n; g.scale = 1.0f; g.pdl = a.pdl;
     switch (layer) {
     case 0:
         a.bias = p->b[0]; a.out = p->act1; a.m_total = kP1;
@@ -2489,7 +2505,7 @@ static int rgb_layer(ahk_policy *p, Args a, int layer, float *logits, uint8_t *a
         // four times over L2 -> SM (1.2 GB per 8192 samples: 0.21-0.25 ms against 0.155; AHK_GEMM=tma2 runs it for the record)
         a.in = p->act1; a.weights = reinterpret_cast<const uint4 *>(p->w[1]); a.bias = p->b[1]; a.out = p->act2; a.m_total = n * kP2;
         g.tiles_m = n * 4; g.blocks_n = 1; g.k_chunks = 4; g.n_valid = 32; g.bias = p->b[1]; g.out_bf16 = p->act2; g.out_pitch = 32;
-        if (p->conv_tm && p->conv2_parity && !p->legacy_conv && !(p->tma_gemm && p->tma_conv2)) POL_CUDA(launch_tm<kConv2>(a, p->sms, s));
+        if (p->conv_tm && p->conv2_parity && !p->legacy_conv && !(p->tma_gemm && p->tma_conv2)) POL_CUDA(launch_tm<kConv2>(a, p->sms, s, pdl));
         else if (p->conv2_parity && !p->legacy_conv && !(p->tma_gemm && p->tma_conv2)) {
             a.weights = reinterpret_cast<const uint4 *>(p->w2p);
             POL_CUDA(launch_conv2p(a, p->sms, s));
@@ -2501,25 +2517,25 @@ static int rgb_layer(ahk_policy *p, Args a, int layer, float *logits, uint8_t *a
         a.in = p->act2; a.weights = reinterpret_cast<const uint4 *>(p->w[2]); a.bias = p->b[2]; a.out = p->act3; a.m_total = n * kP3;
         g.tiles_m = (n + 1) / 2; g.blocks_n = 1; g.k_chunks = 8; g.n_valid = 64; g.bias = p->b[2]; g.out_bf16 = p->act3; g.out_pitch = 64;
         if (p->conv_tm3 && p->tma_gemm && !p->legacy_conv) POL_CUDA(launch_tm<kConv3>(a, p->sms, s));
-        else if (p->tma_gemm) POL_CUDA((tg::launch<64, 128, tg::kConv3, false, tg::kBiasReluBf16, 6, 8>(g, p->tm_a[2], p->tm_w[2], p->sms, s)));
+        else if (p->tma_gemm) POL_CUDA((tg::launch<64, 128, tg::kConv3, false, tg::kBiasReluBf16, 6, 8>(g, p->tm_a[2], p->tm_w[2], p->sms, s, pdl)));
         else if (p->legacy_conv) POL_CUDA(launch<kConv3>(a, tiles(static_cast<long long>(n) * kP3), 1, p->sms, s));
         else POL_CUDA(launch_ws<kConv3>(a, tiles(static_cast<long long>(n) * kP3), p->sms, s));
         return AHK_OK;
     case 3:
         a.in = p->act3; a.weights = reinterpret_cast<const uint4 *>(p->w[3]); a.bias = p->b[3]; a.out = p->h1; a.m_total = n;
         g.tiles_m = tiles(n); g.blocks_n = 2; g.k_chunks = 64; g.n_valid = 256; g.bias = p->b[3]; g.out_bf16 = p->h1; g.out_pitch = 512;
-        if (p->tma_gemm) POL_CUDA((tg::launch<256, 128, tg::kLinear, false, tg::kBiasReluBf16, 4>(g, p->tm_a[3], p->tm_w[3], p->sms, s)));
+        if (p->tma_gemm) POL_CUDA((tg::launch<256, 128, tg::kLinear, false, tg::kBiasReluBf16, 4>(g, p->tm_a[3], p->tm_w[3], p->sms, s, pdl)));
         else POL_CUDA(launch<kDense1>(a, tiles(n), 2, p->sms, s));
         return AHK_OK;
     case 4:
         a.in = p->h1; a.weights = reinterpret_cast<const uint4 *>(p->w[4]); a.bias = p->b[4]; a.out = p->h2; a.m_total = n;
         g.tiles_m = tiles(n); g.blocks_n = 2; g.k_chunks = 8; g.n_valid = 256; g.bias = p->b[4]; g.out_bf16 = p->h2; g.out_pitch = 512;
-        if (p->tma_gemm) POL_CUDA((tg::launch<256, 128, tg::kLinear, false, tg::kBiasReluBf16, 4>(g, p->tm_a[4], p->tm_w[4], p->sms, s)));
+        if (p->tma_gemm) POL_CUDA((tg::launch<256, 128, tg::kLinear, false, tg::kBiasReluBf16, 4>(g, p->tm_a[4], p->tm_w[4], p->sms, s, pdl)));
         else POL_CUDA(launch<kDense2>(a, tiles(n), 2, p->sms, s));
         return AHK_OK;
     default:
         a.in = p->h2; a.weights = reinterpret_cast<const uint4 *>(p->w[5]); a.bias = p->b[5]; a.out = nullptr; a.logits = logits; a.action = action; a.m_total = n;
-        POL_CUDA(launch<kOut>(a, tiles(n), 1, p->sms, s));
+        POL_CUDA(launch<kOut>(a, tiles(n), 1, p->sms, s, pdl));
         return AHK_OK;
     }
 }
@@ -2574,7 +2590,8 @@ static int policy_forward(ahk_policy *p, const ahk_stack &stack, float *logits, 
     if (timed) POL_CUDA(cudaEventRecord(p->ev[0], s));
     a.frames = frames;
     for (int layer = 0; layer < 6; ++layer) {
-        if (int rc = rgb_layer(p, a, layer, logits, action, s)) return rc;
+        a.pdl = timed ? 0 : p->pdl;
+        if (int rc = rgb_layer(p, a, layer, logits, action, s, a.pdl != 0 && layer > 0)) return rc;
         if (timed) POL_CUDA(cudaEventRecord(p->ev[layer + 1], s));
     }
     p->launches += 6;

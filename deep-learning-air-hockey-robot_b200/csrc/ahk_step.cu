@@ -603,7 +603,7 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_many_kernel(StepArgs a, 
     const size_t stride = static_cast<size_t>(n);
     // K record buffers: as many as fit, at most the ring depth (see above), at most 8, at least 2
     int K = cnt32 > 0 ? (kRecordBytes / 16) / (3 * cnt32) : 8;
-    K = min(min(K, 8), min(a.ras.depth, ring_k));
+    K = min(min(K, 8), min(a.ras.depth, ring_k < 0 ? 2 : ring_k));
     K = max(K, 2);
     const int ahead = min(2, K - 1);
     const int slot_recs = 3 * cnt32;
@@ -677,6 +677,7 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_many_kernel(StepArgs a, 
             draw_unit(s_table, s_patch, luts, rec_u, u % kUnitsPerFrame, frame, a.ras.env_id_base + static_cast<uint32_t>(env), a.ras.key, lane);
         }
         many_arrive(&s_left[t], lane);
+        if (ring_k < 0) __syncthreads(); // A/B switch AHK_MANY_DEPTH=0: round 2's barrier per step
     }
     if (kBalance && a.bounds_next != nullptr) rebalance(a, part, &s_warps_done, &s_raster_start, lane);
     __syncthreads(); // every tick's statistics are in shared memory
@@ -721,8 +722,8 @@ cudaError_t launch_step(const StepArgs &a, int mode, int grid, cudaStream_t stre
 // plain launches: no programmatic overlap with their neighbours (the launch boundary is paid once per kManySteps steps)
 cudaError_t launch_step_many(const StepArgs &a0, int steps, const StepLogArgs &log0, int grid, cudaStream_t stream)
 {
-    static int ring_k = -1; // A/B switch AHK_MANY_DEPTH=2..8: record buffers in flight (2 ~ round 2's barrier per step)
-    if (ring_k < 0) { const char *sw = getenv("AHK_MANY_DEPTH"); ring_k = sw ? atoi(sw) : 8; if (ring_k < 2) ring_k = 2; }
+    static int ring_k = -1; // A/B switch AHK_MANY_DEPTH=2..8: record buffers in flight; 0: two buffers and a block barrier per step (round 2)
+    if (ring_k < 0) { const char *sw = getenv("AHK_MANY_DEPTH"); ring_k = sw ? atoi(sw) : 8; if (ring_k < 2) ring_k = -1; }
     StepArgs a = a0;
     StepLogArgs log = log0;
     const size_t n = static_cast<size_t>(a.ras.n);

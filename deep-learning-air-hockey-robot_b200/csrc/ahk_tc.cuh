@@ -118,5 +118,31 @@ __device__ __forceinline__ void mbar_wait_sleep(uint64_t *bar, uint32_t parity)
         :: "r"(smem_u32(bar)), "r"(parity), "r"(1000) : "memory");
 }
 
+// Programmatic dependent launch between the layer kernels of one forward pass.  pdl_trigger: the NEXT kernel on the
+// stream, if it was launched with programmatic stream serialization, may be scheduled once every CTA of this grid has
+// passed this point — its CTAs move onto SMs as ours retire and run their prologue (barriers, tensor memory, weight
+// loads) under our tail.  pdl_wait: returns when the previous grid has completed and its stores are visible — executed
+// before the first read of anything the previous kernel wrote and before the first global store.  Both are no-ops for a
+// kernel launched without the attribute / followed by an ordinary launch.
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+// kernel<<<grid, block, smem, s>>>(args...) with the programmatic-stream-serialization attribute when `pdl`
+template <typename... Params, typename... Given>
+inline cudaError_t launch_kernel(void (*kernel)(Params...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, bool pdl, Given &&...args)
+{
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<Params>(args)...);
+}
+
 } // namespace tc
 } // namespace ahk

@@ -813,7 +813,7 @@ int ahk_cpu_create(const ahk_config *cfg, ahk_cpu_env **out)
     if (threads > 1024) threads = 1024;
     e->pool = orc_pool_create(threads);
     e->part = (uint64_t *)calloc((size_t)threads * AHK_STATS_WORDS, sizeof(uint64_t));
-    e->head = 2;
+    e->head = 0; /* as ahk_create: a reset keeps the head, the first step writes slot 1 */
     *out = e;
     return AHK_OK;
 }

@@ -41,7 +41,7 @@ def test_twin_matches_per_env_oracle(orc, noise_table):
     eng.reset(episode=episode, use=use)
     for i, o in enumerate(envs):
         o.reset(-1 if episode[i] == 255 else int(episode[i]), int(use[i]))
-    assert eng.head == 2 and eng.threads >= 1
+    assert eng.head == 0 and eng.threads >= 1
     rs = np.random.RandomState(3)
     log = {k: np.zeros((4, n), np.float32 if k == 'reward' else np.uint8) for k in ('robot_label', 'human_label', 'done', 'reward')}
     for t in range(30):

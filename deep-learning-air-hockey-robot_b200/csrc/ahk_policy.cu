@@ -80,6 +80,7 @@ struct Args {
     const uint8_t *warm;        // deep ring: warm-up frames of each env's latest reset, else nullptr (stack_frame, ahk_kernels.cuh)
     const uint32_t *meta;       // deep ring: state word 15 per env
     int pdl;                    // programmatic dependent launch of the NEXT layer's kernel: 0 off, 1 trigger after the prologue, 2 trigger at the end
+    int no_swap;                // conv_tm_kernel A/B (AHK_CONV2_SWAP=0): every lane fetches its two 16-byte halves in the same order
 };
 
 using namespace ahk::tc; // inline-PTX wrappers: ahk_tc.cuh
@@ -1657,6 +1658,7 @@ __global__ void __launch_bounds__(ctm::kCta, 1) conv_tm_kernel(Args a)
         // ---------------------------------------------------------------- converters: raw sample -> A rows in TMEM
         const int quarter = warp & 3, group = warp >> 2, r = quarter * 32 + lane;
         const uint32_t lane_base = tmem + (static_cast<uint32_t>(quarter * 32) << 16) + kABase;
+        const bool swap_halves = ((lane >> 2) & 1) && !a.no_swap;
         uint32_t f = 0; // A stages so far (both groups count all of them)
         for (int t = 0; t < my_items; ++t) {
             const uint32_t rb = t & 1u;
@@ -1687,7 +1689,11 @@ __global__ void __launch_bounds__(ctm::kCta, 1) conv_tm_kernel(Args a)
                     uint32_t tapoff;
                     if (L == kConv2) tapoff = ((q >> 1) * kC1 + (q & 1) * 2) * (kAct1C * 2);           // taps (ky, 2h), (ky, 2h + 1): 32 contiguous bytes
                     else { const int tap = q >> 1; tapoff = ((tap >> 2) * kC2 + (tap & 3)) * 64 + (q & 1) * 32; } // half of a tap's 32 channels
-                    const uint4 v0 = *reinterpret_cast<const uint4 *>(raw + off + tapoff), v1 = *reinterpret_cast<const uint4 *>(raw + off + tapoff + 16);
+                    // conv2: neighbouring lanes are 32 bytes apart, so the eight lanes of a 16-byte load phase would cover only four
+                    // of the eight 16-byte bank groups, twice; lanes 4-7 of each phase fetch their two halves in the other order
+                    const uint32_t first = (L == kConv2 && swap_halves) ? 16u : 0u;
+                    const uint4 va = *reinterpret_cast<const uint4 *>(raw + off + tapoff + first), vb = *reinterpret_cast<const uint4 *>(raw + off + tapoff + (first ^ 16u));
+                    const uint4 v0 = first ? vb : va, v1 = first ? va : vb;
                     tmem_store8(stage + i * 8, v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w);
                 }
                 tmem_wait_st();
@@ -2112,6 +2118,7 @@ struct ahk_policy {
     // fetch run under its teardown (forward of 8192 samples 0.5156 -> 0.5040 ms, same box); 1 = released right after the prologue
     // (0.529 ms: the early CTAs of the next layer take SM resources from the running one); 0 = ordinary launches.  AHK_POLICY_PDL
     int pdl = 2;
+    bool conv2_no_swap = false;
     uint16_t *w1p = nullptr; // conv1 in phase-separated form (conv1p_kernel, the default), fp16, unscaled
     bool conv1_n144 = false;
     bool conv1_normal = false; // A/B switch AHK_CONV1=normal: conv1t_kernel with the pixels as NORMAL fp16 numbers (1024 + v - 1024)
@@ -2286,6 +2293,7 @@ int ahk_policy_create(int device, int max_batch, const ahk_policy_weights *w, ah
     if (const char *sw = getenv("AHK_CONV2")) p->conv2_parity = strcmp(sw, "ws") != 0;
     if (const char *sw = getenv("AHK_CONVTM")) { p->conv_tm = strcmp(sw, "0") != 0; p->conv_tm3 = strcmp(sw, "23") == 0; }
     if (const char *sw = getenv("AHK_POLICY_PDL")) p->pdl = atoi(sw);
+    if (const char *sw = getenv("AHK_CONV2_SWAP")) p->conv2_no_swap = strcmp(sw, "0") == 0;
     if (const char *sw = getenv("AHK_CONV1")) { p->conv1_n144 = strcmp(sw, "n144") == 0; p->conv1_smem = strcmp(sw, "smem") == 0; p->conv1_normal = strcmp(sw, "normal") == 0; }
     int rc = load_rgb_weights(p, w);
     const size_t nb = static_cast<size_t>(max_batch);
@@ -2591,6 +2599,7 @@ static int policy_forward(ahk_policy *p, const ahk_stack &stack, float *logits, 
     a.frames = frames;
     for (int layer = 0; layer < 6; ++layer) {
         a.pdl = timed ? 0 : p->pdl;
+        a.no_swap = p->conv2_no_swap;
         if (int rc = rgb_layer(p, a, layer, logits, action, s, a.pdl != 0 && layer > 0)) return rc;
         if (timed) POL_CUDA(cudaEventRecord(p->ev[layer + 1], s));
     }

@@ -1586,10 +1586,14 @@ cudaError_t launch_conv2p(const Args &a, int sms, cudaStream_t s)
 // output pixel — copy each MMA's 32-byte A row (two adjacent taps of 8 channels for conv2, half a tap's 32 channels for
 // conv3) from the raw sample straight into tensor memory (two 16-byte loads, one tcgen05.st.x8).  The MMAs take A from TMEM
 // (floor 128 N / 256 cycles instead of the 64 cycles an A tile costs from shared memory), B = the layer's packed weights,
-// resident.  Activations cross L2 -> SM once instead of four times.  Measured per 8192 samples: conv2 0.110 ms (parity arrays
-// 0.116, cp.async gather 0.155, tensor-map im2col 0.21-0.25) — the default; conv3 0.165 ms against 0.075 for the TMA-fed GEMM:
-// its pixels are 64 bytes and every window starts a multiple of 128 bytes into the sample, so the 32 lanes of each 16-byte
-// load hit the same four banks (80 % of the shared-memory pipe, profiles/conv_tm_r2v_ncu.txt) — kept as AHK_CONVTM=23.
+// resident.  Activations cross L2 -> SM once instead of four times.  Shared-memory bank conflicts of the converter loads decided
+// both layers (a 16-byte load runs in phases of eight lanes, one phase wants eight different 16-byte bank groups):
+//   conv2: neighbouring lanes are 32 bytes apart -> four bank groups, twice; lanes 4-7 of each phase fetch their two halves in the
+//          other order.  0.122 -> 0.100 ms per 8192 samples (parity arrays 0.116, cp.async gather 0.155, tensor-map im2col 0.21-0.25).
+//   conv3: pixels are 64 bytes and neighbouring lanes 128 bytes apart -> ONE bank group per phase with a plain copy (0.165 ms, 80 % of
+//          the shared-memory pipe, profiles/conv_tm_r2v_ncu.txt).  The item is now fetched as three tiled TMA copies of 128-byte rows
+//          with the 128-byte swizzle (chunk c of row r at c ^ (r & 7)): the eight lanes of a phase land in eight bank groups.
+//          0.064 ms against 0.084 for the TMA-fed GEMM (same box), so both layers run here by default; AHK_CONVTM=2 / 0 for A/B.
 namespace ctm {
 template <int L> struct Cfg;
 template <> struct Cfg<kConv2> {
@@ -1598,21 +1602,22 @@ template <> struct Cfg<kConv2> {
 };
 template <> struct Cfg<kConv3> {
     static constexpr int N = 64, kMmas = 32, kGroup = 16, kTiles = 1, kAStages = 3;
-    static constexpr int kSamples = 2, kRowsOut = 2 * kP3, kItemBytes = 2 * kP2 * 32 * 2, kRawPitch = 46336, kWBytes = 512 * 64 * 2;
+    // the item arrives as three tiled TMA copies of 128 rows of 128 bytes (two pixels) with the 128-byte swizzle: 361 rows used
+    static constexpr int kSamples = 2, kRowsOut = 2 * kP3, kItemBytes = 2 * kP2 * 32 * 2, kRawPitch = 3 * 128 * 128, kWBytes = 512 * 64 * 2;
 };
 constexpr int kCta = 256 + 64 + 128; // 8 converter warps (2 groups x 4 lane quarters), loader, MMA, 4 epilogue warps
-template <int L> constexpr int smem_bytes() { return 128 + 2 * Cfg<L>::kRawPitch + Cfg<L>::kWBytes; }
+template <int L> constexpr int smem_bytes() { return 1024 + 2 * Cfg<L>::kRawPitch + Cfg<L>::kWBytes; }
 } // namespace ctm
 
 template <int L>
-__global__ void __launch_bounds__(ctm::kCta, 1) conv_tm_kernel(Args a)
+__global__ void __launch_bounds__(ctm::kCta, 1) conv_tm_kernel(Args a, const __grid_constant__ CUtensorMap tm_in)
 {
     using C = ctm::Cfg<L>;
     constexpr int N = C::N, kStagesPerItem = C::kTiles * (C::kMmas / C::kGroup), kACols = C::kGroup * 8, kDCols = C::kTiles * N;
     constexpr int kABase = 2 * kDCols;
     static_assert(kABase + C::kAStages * kACols <= 512, "TMEM");
     extern __shared__ __align__(128) uint8_t smem_raw[];
-    uint8_t *s_base = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
+    uint8_t *s_base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u); // swizzle atoms are 1024-byte aligned
     uint8_t *s_in = s_base, *s_w = s_base + 2 * C::kRawPitch;
     __shared__ __align__(8) uint64_t s_wfull, s_rfull[2], s_rempty[2], s_afull[C::kAStages], s_aempty[C::kAStages], s_tfull[2], s_tempty[2];
     __shared__ uint32_t s_tmem;
@@ -1650,6 +1655,11 @@ __global__ void __launch_bounds__(ctm::kCta, 1) conv_tm_kernel(Args a)
                 const int item = static_cast<int>(blockIdx.x) + t * static_cast<int>(gridDim.x);
                 const int samples = (item + 1) * C::kSamples <= a.n ? C::kSamples : a.n - item * C::kSamples;
                 const uint32_t bytes = static_cast<uint32_t>(samples) * (C::kItemBytes / C::kSamples);
+                if (L == kConv3) { // act2 as rows of 128 bytes: rows [361 item, + 384), swizzled; rows past the end of act2 are zero-filled
+                    mbar_expect_tx(&s_rfull[rb], C::kRawPitch);
+                    for (int j = 0; j < 3; ++j) ahk::tg::tma_2d(s_in + rb * C::kRawPitch + j * (128 * 128), &tm_in, 0, item * kP2 + j * 128, &s_rfull[rb]);
+                    continue;
+                }
                 mbar_expect_tx(&s_rfull[rb], bytes);
                 bulk_load(s_in + rb * C::kRawPitch, reinterpret_cast<const uint8_t *>(a.in) + static_cast<size_t>(item) * C::kItemBytes, bytes, &s_rfull[rb]);
             }
@@ -1692,7 +1702,13 @@ __global__ void __launch_bounds__(ctm::kCta, 1) conv_tm_kernel(Args a)
                     // conv2: neighbouring lanes are 32 bytes apart, so the eight lanes of a 16-byte load phase would cover only four
                     // of the eight 16-byte bank groups, twice; lanes 4-7 of each phase fetch their two halves in the other order
                     const uint32_t first = (L == kConv2 && swap_halves) ? 16u : 0u;
-                    const uint4 va = *reinterpret_cast<const uint4 *>(raw + off + tapoff + first), vb = *reinterpret_cast<const uint4 *>(raw + off + tapoff + (first ^ 16u));
+                    uint32_t at0 = off + tapoff + first, at1 = off + tapoff + (first ^ 16u);
+                    if (L == kConv3) { // 128-byte swizzle of the TMA copy: 16-byte chunk c of row r sits at chunk c ^ (r & 7).  Neighbouring lanes are
+                        // neighbouring rows (output pixels two input pixels = 128 bytes apart), so a load phase covers all eight bank groups
+                        at0 ^= ((at0 >> 7) & 7u) << 4;
+                        at1 ^= ((at1 >> 7) & 7u) << 4;
+                    }
+                    const uint4 va = *reinterpret_cast<const uint4 *>(raw + at0), vb = *reinterpret_cast<const uint4 *>(raw + at1);
                     const uint4 v0 = first ? vb : va, v1 = first ? va : vb;
                     tmem_store8(stage + i * 8, v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w);
                 }
@@ -1779,12 +1795,12 @@ __global__ void __launch_bounds__(ctm::kCta, 1) conv_tm_kernel(Args a)
 }
 
 template <int L>
-cudaError_t launch_tm(const Args &a, int sms, cudaStream_t s, bool pdl = false)
+cudaError_t launch_tm(const Args &a, const CUtensorMap &tm_in, int sms, cudaStream_t s, bool pdl = false)
 {
     cudaError_t e = cudaFuncSetAttribute(conv_tm_kernel<L>, cudaFuncAttributeMaxDynamicSharedMemorySize, ctm::smem_bytes<L>());
     if (e != cudaSuccess) return e;
     const int items = (a.n + ctm::Cfg<L>::kSamples - 1) / ctm::Cfg<L>::kSamples;
-    return launch_kernel(conv_tm_kernel<L>, dim3(items < sms ? items : sms), dim3(ctm::kCta), ctm::smem_bytes<L>(), s, pdl, a);
+    return launch_kernel(conv_tm_kernel<L>, dim3(items < sms ? items : sms), dim3(ctm::kCta), ctm::smem_bytes<L>(), s, pdl, a, tm_in);
 }
 
 // ------------------------------------------------------------------------------------------------ gray-diff input
@@ -2109,10 +2125,9 @@ struct ahk_policy {
     uint16_t *w1t = nullptr; // conv1 in Toeplitz form (conv1_kernel, A/B switch AHK_CONV1=n144)
     uint16_t *w2p = nullptr; // conv2 in conv2p_kernel's K order (pack_b blobs)
     bool conv2_parity = true; // A/B switch AHK_CONV2=ws: conv_ws_kernel instead of conv2p_kernel
-    // conv_tm_kernel (A operand built in TMEM): the default for conv2 (0.110 ms per 8192 samples against 0.116 for conv2p_kernel);
-    // conv3 stays on the TMA-fed GEMM (0.075 ms against 0.165: its 64-byte pixels put every lane of a load on the same banks).
-    // A/B switch AHK_CONVTM=0 (neither) | 2 (default) | 23 (both)
-    bool conv_tm = true, conv_tm3 = false;
+    // conv_tm_kernel (A operand built in TMEM from a once-copied item): the default for conv2 (0.100 ms per 8192 samples) and conv3
+    // (0.064 ms; the TMA-fed GEMM 0.084).  A/B switch AHK_CONVTM=0 (neither) | 2 (conv2 only) | 23 (both, default)
+    bool conv_tm = true, conv_tm3 = true;
     // the layer kernels of one inference forward chained by programmatic dependent launch: 2 (default) = a kernel releases the next
     // layer's launch when its own work is done, so that launch latency, barrier set-up, tensor-memory allocation and the weight
     // fetch run under its teardown (forward of 8192 samples 0.5156 -> 0.5040 ms, same box); 1 = released right after the prologue
@@ -2136,6 +2151,7 @@ struct ahk_policy {
     bool tma_gemm = true, tma_conv2 = false;
     uint16_t *wn[5] = {};    // [1] conv2 32 x 128, [2] conv3 64 x 512, [3] dense1 512 x 4096, [4] dense2 512 x 512
     CUtensorMap tm_w[5], tm_a[5];
+    CUtensorMap tm_rows2; // act2 as a matrix of 128-byte rows (two 32-channel pixels each): conv_tm_kernel<conv3>'s item copies
     __nv_bfloat16 *act1 = nullptr, *act2 = nullptr, *act3 = nullptr, *h1 = nullptr, *h2 = nullptr;
     float *w3sum = nullptr;    // [64][512]: dense1_px_sums_kernel
     double *bn_sums = nullptr; // ahk_policy_forward_train: [2][64] running sums of the layer being normalised
@@ -2291,7 +2307,7 @@ int ahk_policy_create(int device, int max_batch, const ahk_policy_weights *w, ah
     cudaDeviceGetAttribute(&p->sms, cudaDevAttrMultiProcessorCount, device);
     if (const char *sw = getenv("AHK_CONV23")) p->legacy_conv = strcmp(sw, "tile") == 0;
     if (const char *sw = getenv("AHK_CONV2")) p->conv2_parity = strcmp(sw, "ws") != 0;
-    if (const char *sw = getenv("AHK_CONVTM")) { p->conv_tm = strcmp(sw, "0") != 0; p->conv_tm3 = strcmp(sw, "23") == 0; }
+    if (const char *sw = getenv("AHK_CONVTM")) { p->conv_tm = strcmp(sw, "0") != 0; p->conv_tm3 = strcmp(sw, "23") == 0; } // "2": conv2 only, "0": neither
     if (const char *sw = getenv("AHK_POLICY_PDL")) p->pdl = atoi(sw);
     if (const char *sw = getenv("AHK_CONV2_SWAP")) p->conv2_no_swap = strcmp(sw, "0") == 0;
     if (const char *sw = getenv("AHK_CONV1")) { p->conv1_n144 = strcmp(sw, "n144") == 0; p->conv1_smem = strcmp(sw, "smem") == 0; p->conv1_normal = strcmp(sw, "normal") == 0; }
@@ -2301,7 +2317,7 @@ int ahk_policy_create(int device, int max_batch, const ahk_policy_weights *w, ah
     for (int i = 0; i < 7 && err == cudaSuccess; ++i) err = cudaEventCreate(&p->ev[i]);
     if (rc == AHK_OK) {
         err = cudaMalloc(&p->act1, nb * kP1 * kAct1C * 2);
-        if (err == cudaSuccess) err = cudaMalloc(&p->act2, nb * kP2 * 32 * 2);
+        if (err == cudaSuccess) err = cudaMalloc(&p->act2, nb * kP2 * 32 * 2 + 128); // + 128: tm_rows2 rounds an odd pixel count up to whole 128-byte rows
         if (err == cudaSuccess) err = cudaMalloc(&p->act3, nb * 4096 * 2);
         if (err == cudaSuccess) err = cudaMalloc(&p->h1, nb * 512 * 2);
         if (err == cudaSuccess) err = cudaMalloc(&p->h2, nb * 512 * 2);
@@ -2323,6 +2339,7 @@ int ahk_policy_create(int device, int max_batch, const ahk_policy_weights *w, ah
             const unsigned box[4] = {64, kC3, kC3, 2};
             err = tg::encode_bf16_map(&p->tm_a[2], p->act2, 4, dims, strides, box, 128);
         }
+        if (err == cudaSuccess) err = tg::matrix_map(&p->tm_rows2, p->act2, (nb * kP2 + 1) / 2, 64, 64, 128);
         if (err == cudaSuccess) err = tg::matrix_map(&p->tm_a[3], p->act3, nb, 4096, 64, 128);
         if (err == cudaSuccess) err = tg::matrix_map(&p->tm_a[4], p->h1, nb, 512, 64, 128);
     }
@@ -2513,7 +2530,7 @@ static int rgb_layer(ahk_policy *p, Args a, int layer, float *logits, uint8_t *a
         // four times over L2 -> SM (1.2 GB per 8192 samples: 0.21-0.25 ms against 0.155; AHK_GEMM=tma2 runs it for the record)
         a.in = p->act1; a.weights = reinterpret_cast<const uint4 *>(p->w[1]); a.bias = p->b[1]; a.out = p->act2; a.m_total = n * kP2;
         g.tiles_m = n * 4; g.blocks_n = 1; g.k_chunks = 4; g.n_valid = 32; g.bias = p->b[1]; g.out_bf16 = p->act2; g.out_pitch = 32;
-        if (p->conv_tm && p->conv2_parity && !p->legacy_conv && !(p->tma_gemm && p->tma_conv2)) POL_CUDA(launch_tm<kConv2>(a, p->sms, s, pdl));
+        if (p->conv_tm && p->conv2_parity && !p->legacy_conv && !(p->tma_gemm && p->tma_conv2)) POL_CUDA(launch_tm<kConv2>(a, p->tm_rows2, p->sms, s, pdl)); // (conv2 takes its sample by a plain bulk copy: the map is unused)
         else if (p->conv2_parity && !p->legacy_conv && !(p->tma_gemm && p->tma_conv2)) {
             a.weights = reinterpret_cast<const uint4 *>(p->w2p);
             POL_CUDA(launch_conv2p(a, p->sms, s));
@@ -2524,7 +2541,7 @@ static int rgb_layer(ahk_policy *p, Args a, int layer, float *logits, uint8_t *a
     case 2:
         a.in = p->act2; a.weights = reinterpret_cast<const uint4 *>(p->w[2]); a.bias = p->b[2]; a.out = p->act3; a.m_total = n * kP3;
         g.tiles_m = (n + 1) / 2; g.blocks_n = 1; g.k_chunks = 8; g.n_valid = 64; g.bias = p->b[2]; g.out_bf16 = p->act3; g.out_pitch = 64;
-        if (p->conv_tm3 && p->tma_gemm && !p->legacy_conv) POL_CUDA(launch_tm<kConv3>(a, p->sms, s));
+        if (p->conv_tm3 && p->tma_gemm && !p->legacy_conv) POL_CUDA(launch_tm<kConv3>(a, p->tm_rows2, p->sms, s, pdl));
         else if (p->tma_gemm) POL_CUDA((tg::launch<64, 128, tg::kConv3, false, tg::kBiasReluBf16, 6, 8>(g, p->tm_a[2], p->tm_w[2], p->sms, s, pdl)));
         else if (p->legacy_conv) POL_CUDA(launch<kConv3>(a, tiles(static_cast<long long>(n) * kP3), 1, p->sms, s));
         else POL_CUDA(launch_ws<kConv3>(a, tiles(static_cast<long long>(n) * kP3), p->sms, s));

@@ -31,6 +31,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <vector>
 
 namespace ahk {
@@ -2757,3 +2758,104 @@ int ahk_policy_forward_stack_profiled(ahk_policy *p, const ahk_stack *stack, flo
 }
 
 } // extern "C"
+
+// ------------------------------------------------------------------------------------------------ ahk_policy_forward_static
+// The forward pass for callers that may not allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc):
+// the same layer kernels as ahk_policy_forward, with the activations between them — the forward's scratch memory — in a
+// file-scope array of the library's device image instead of the handle's cudaMalloc'ed buffers.  No counterpart in the reference.
+//   * AHK_POLICY_STATIC_MAX_BATCH = 64 samples: act1 [64][41 x 41][8] + act2 [64][19 x 19][32] + act3 [64][4096] + h1, h2 [64][512]
+//     bf16 = 3 855 616 bytes, held by every GPU that loads the library until the process exits.
+//   * g_static_scratch is a HOST-SIDE STAND-IN in host code, not a device address: its address on the current device is taken
+//     with cudaGetSymbolAddress once per device (static_setup, with that device current) and that pointer goes to the kernels.
+//   * Every call on a device shares the array and finds the previous call's contents in it.  Nothing in it has to start at
+//     zero: every activation row of samples [0, n) is written by the layer before the layer that reads it (ahk_policy_create
+//     does not clear its buffers either); rows of samples >= n are only ever multiplied into accumulator rows that no
+//     epilogue stores.  Two calls that overlap on the GPU (different streams, or different handles) RACE on the array.
+namespace {
+
+constexpr int kStaticBatch = AHK_POLICY_STATIC_MAX_BATCH;
+constexpr size_t kStaticAct1 = 0;
+constexpr size_t kStaticAct2 = kStaticAct1 + static_cast<size_t>(kStaticBatch) * kP1 * kAct1C * 2;
+constexpr size_t kStaticAct3 = kStaticAct2 + static_cast<size_t>(kStaticBatch) * kP2 * 32 * 2 + 256; // + 256: as act2's + 128 in ahk_policy_create, aligned
+constexpr size_t kStaticH1 = kStaticAct3 + static_cast<size_t>(kStaticBatch) * 4096 * 2;
+constexpr size_t kStaticH2 = kStaticH1 + static_cast<size_t>(kStaticBatch) * 512 * 2;
+constexpr size_t kStaticBytes = kStaticH2 + static_cast<size_t>(kStaticBatch) * 512 * 2;
+static_assert(kStaticAct2 % 256 == 0 && kStaticAct3 % 256 == 0 && kStaticH1 % 256 == 0 && kStaticH2 % 256 == 0, "256-byte aligned regions");
+
+static __device__ __align__(256) uint8_t g_static_scratch[kStaticBytes];
+
+struct StaticSetup { // per device: the array's DEVICE address and the tensor maps of the TMA-fed layers over it
+    bool ready = false;
+    uint8_t *base = nullptr;
+    CUtensorMap tm_a[5], tm_rows2;
+};
+constexpr int kStaticDevices = 64;
+StaticSetup g_static_setup[kStaticDevices];
+std::mutex g_static_mutex;
+
+// once per device, with that device current
+int static_setup(int device, const StaticSetup **out)
+{
+    namespace tg = ahk::tg;
+    if (device < 0 || device >= kStaticDevices) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_forward_static: device ordinal beyond 63");
+    std::lock_guard<std::mutex> lock(g_static_mutex);
+    StaticSetup &st = g_static_setup[device];
+    if (!st.ready) {
+        void *ptr = nullptr;
+        POL_CUDA(cudaGetSymbolAddress(&ptr, g_static_scratch));
+        uint8_t *base = static_cast<uint8_t *>(ptr);
+        const size_t nb = kStaticBatch;
+        cudaError_t err = cudaSuccess;
+        { // the same views as ahk_policy_create builds over its own buffers
+            const unsigned long long dims[4] = {static_cast<unsigned long long>(kP1) * kAct1C, kC2, kC2, nb}, strides[3] = {2 * kAct1C * 2, 2 * kC1 * kAct1C * 2, static_cast<unsigned long long>(kP1) * kAct1C * 2};
+            const unsigned box[4] = {32, kC2, 6, 1};
+            err = tg::encode_bf16_map(&st.tm_a[1], base + kStaticAct1, 4, dims, strides, box, 64);
+        }
+        if (err == cudaSuccess) {
+            const unsigned long long dims[4] = {static_cast<unsigned long long>(kP2) * 32, kC3, kC3, nb}, strides[3] = {2 * 32 * 2, 2 * kC2 * 32 * 2, static_cast<unsigned long long>(kP2) * 32 * 2};
+            const unsigned box[4] = {64, kC3, kC3, 2};
+            err = tg::encode_bf16_map(&st.tm_a[2], base + kStaticAct2, 4, dims, strides, box, 128);
+        }
+        if (err == cudaSuccess) err = tg::matrix_map(&st.tm_rows2, base + kStaticAct2, (nb * kP2 + 1) / 2, 64, 64, 128);
+        if (err == cudaSuccess) err = tg::matrix_map(&st.tm_a[3], base + kStaticAct3, nb, 4096, 64, 128);
+        if (err == cudaSuccess) err = tg::matrix_map(&st.tm_a[4], base + kStaticH1, nb, 512, 64, 128);
+        if (err != cudaSuccess) return pfail(AHK_ERR_CUDA, "ahk_policy_forward_static: tensor maps over the static scratch: %s", cudaGetErrorString(err));
+        st.base = base;
+        st.ready = true;
+    }
+    *out = &st;
+    return AHK_OK;
+}
+
+} // namespace
+
+extern "C" int ahk_policy_forward_static(ahk_policy *p, const uint8_t *frames, int n, int head, float *logits, uint8_t *action, void *stream)
+{
+    if (!p || !frames || !logits || !action) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_forward_static: NULL argument");
+    if (p->gray) return pfail(AHK_ERR_ARG, "%s", "ahk_policy_forward_static: handle holds the 'gray-diff' network (the static scratch is laid out for 'rgb')");
+    if (n < 1 || n > kStaticBatch) {
+        char text[160];
+        snprintf(text, sizeof text, "n = %d is outside [1, AHK_POLICY_STATIC_MAX_BATCH = %d]: the static scratch holds %d samples; use ahk_policy_forward", n, kStaticBatch, kStaticBatch);
+        return pfail(AHK_ERR_ARG, "ahk_policy_forward_static: %s", text);
+    }
+    int prev_device = -1;
+    POL_CUDA(cudaGetDevice(&prev_device));
+    if (prev_device != p->device) POL_CUDA(cudaSetDevice(p->device));
+    struct Restore { int prev, cur; ~Restore() { if (prev != cur) cudaSetDevice(prev); } } restore{prev_device, p->device};
+    const StaticSetup *st = nullptr;
+    if (int rc = static_setup(p->device, &st)) return rc;
+    // a host-side copy of the handle whose scratch pointers and activation maps are the static array's: weights, weight maps
+    // and kernel selection stay the handle's, so the launches are those of ahk_policy_forward
+    ahk_policy view = *p;
+    view.max_batch = kStaticBatch;
+    view.act1 = reinterpret_cast<__nv_bfloat16 *>(st->base + kStaticAct1);
+    view.act2 = reinterpret_cast<__nv_bfloat16 *>(st->base + kStaticAct2);
+    view.act3 = reinterpret_cast<__nv_bfloat16 *>(st->base + kStaticAct3);
+    view.h1 = reinterpret_cast<__nv_bfloat16 *>(st->base + kStaticH1);
+    view.h2 = reinterpret_cast<__nv_bfloat16 *>(st->base + kStaticH2);
+    for (int i = 1; i <= 4; ++i) view.tm_a[i] = st->tm_a[i];
+    view.tm_rows2 = st->tm_rows2;
+    const int rc = policy_forward(&view, plain_ring(frames, n, head), logits, action, stream, false);
+    p->launches = view.launches;
+    return rc;
+}

@@ -112,6 +112,7 @@ SYMBOLS = {
     "ahk_policy_destroy": (None, [_vp]),
     "ahk_policy_forward": (_i, [_vp, _vp, _i, _i, _vp, _vp, _vp]),
     "ahk_policy_forward_profiled": (_i, [_vp, _vp, _i, _i, _vp, _vp, _vp, C.POINTER(C.c_float)]),
+    "ahk_policy_forward_static": (_i, [_vp, _vp, _i, _i, _vp, _vp, _vp]),
 }
 
 _lib = None

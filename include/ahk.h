@@ -208,6 +208,20 @@ int ahk_policy_forward_stack_profiled(ahk_policy *p, const ahk_stack *stack, flo
  * dense1, dense2, out); waits, then reports their durations in layer_ms[6].  Measurement aid for bench.py's roofline. */
 int ahk_policy_forward_profiled(ahk_policy *p, const uint8_t *frames_dev, int n, int head, float *logits_dev,
                                 uint8_t *action_dev, void *stream, float *layer_ms);
+/* NO COUNTERPART IN THE REFERENCE — added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  ahk_policy_forward for n <=
+ * AHK_POLICY_STATIC_MAX_BATCH samples of an 'rgb' handle, with the activations between the layer kernels (the forward's
+ * scratch memory) in a fixed array of the library's device image instead of the handle's buffers: the call allocates nothing
+ * (no cudaMalloc / cudaFree / allocating library routine), the caller passes inputs and outputs as before (both required).
+ * Same kernels, same results as ahk_policy_forward.  The array — 3 855 616 bytes — is held by every GPU that loads the
+ * library until the process exits, is shared by every call on that GPU and keeps the last call's contents (nothing in it
+ * needs clearing: each layer writes the rows the next one reads): calls that OVERLAP on the GPU — other streams, other
+ * handles — race on it; issue them on one stream.  n outside [1, AHK_POLICY_STATIC_MAX_BATCH] and 'gray-diff' handles are
+ * rejected with AHK_ERR_ARG.  The first call on a device resolves the array's device address and encodes four tensor maps
+ * on the host (make it once before capturing a graph). */
+#define AHK_POLICY_STATIC_MAX_BATCH 64
+int ahk_policy_forward_static(ahk_policy *p, const uint8_t *frames_dev, int n, int head, float *logits_dev,
+                              uint8_t *action_dev, void *stream);
 
 /* Replace the weights of an 'rgb' policy handle in place (same folding and packing as ahk_policy_create): ≙
  * model.set_weights / the weights after model.fit (rl_agents.py:100-104,189) — the trainer pushes the updated network to

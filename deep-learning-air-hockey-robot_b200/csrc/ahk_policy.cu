@@ -929,7 +929,10 @@ cudaError_t launch_conv1p(const Args &a, int grid, cudaStream_t s)
 //   * 8 converter warps = 2 groups x 4 lane quarters, the groups taking alternate planes; no converted stage in shared
 //     memory, so 8 raw stages (72 KB per SM) of TMA loads are in flight.
 namespace c1t {
-constexpr int kGroups = 2, kConverters = kGroups * 128, kMmaWarp = kConverters / 32, kLoadWarp = kMmaWarp + 1, kEpiSets = 2, kCta = kConverters + 64 + kEpiSets * 128;
+// kGroups converter groups of 4 warps (one per TMEM lane quarter), then the MMA warp, the loader warp, kEpiSets x 4 epilogue warps;
+// the group count is a template parameter of the kernel (A/B switch AHK_CONV1_GROUPS=2|3|4)
+constexpr int kEpiSets = 2;
+constexpr int cta_threads(int groups) { return groups * 128 + 64 + kEpiSets * 128; }
 constexpr int kAStages = 4, kRaw = 8;
 constexpr int kRowsQ = c1p::kRowsQ, kQ = c1p::kQ, kRowsUsed = c1p::kRowsUsed;
 constexpr int kRawRows = c1p::kRawRows, kRawBytes = c1p::kRawBytes;
@@ -978,10 +981,11 @@ __device__ __forceinline__ uint2 u8x4_to_f16x4_denormal(uint32_t w) { return mak
 __device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
 // kDenormal: pixels as fp16 DENORMALS (bit pattern 0x00vv = v * 2^-24): one PRMT per two pixels, the 2^24 goes to the epilogue
-template <bool kDenormal>
-__global__ void __launch_bounds__(c1t::kCta, 1) conv1t_kernel(Args a, const __grid_constant__ CUtensorMap tm_ring, const __grid_constant__ CUtensorMap tm_warm)
+template <bool kDenormal, int kGroups>
+__global__ void __launch_bounds__(c1t::cta_threads(kGroups), 1) conv1t_kernel(Args a, const __grid_constant__ CUtensorMap tm_ring, const __grid_constant__ CUtensorMap tm_warm)
 {
     using namespace c1t;
+    constexpr int kMmaWarp = kGroups * 4, kLoadWarp = kMmaWarp + 1;
     extern __shared__ __align__(128) uint8_t smem_unaligned[];
     uint8_t *s_raw = smem_unaligned + ((1024u - (smem_u32(smem_unaligned) & 1023u)) & 1023u); // swizzle atoms are 1024-byte aligned
     uint8_t *s_w = s_raw + kRaw * kRawBytes;
@@ -1065,13 +1069,16 @@ __global__ void __launch_bounds__(c1t::kCta, 1) conv1t_kernel(Args a, const __gr
             mbar_wait_sleep(&s_rfull[rs], (fill / kRaw) & 1u);
             uint2 px[3][4];
             const uint8_t *raw = s_raw + rs * kRawBytes;
+#ifndef AHK_C1T_NO_CONVERT // timing experiment (tools/build_variant.sh): the pipeline without the converters' loads, conversions and stores
 #pragma unroll
             for (int c = 0; c < 3; ++c)
 #pragma unroll
                 for (int j = 0; j < 4; ++j) px[c][j] = *reinterpret_cast<const uint2 *>(raw + off[c][j]);
+#endif
             if (fill >= kAStages) mbar_wait_sleep(&s_aempty[st], ((fill / kAStages) - 1u) & 1u);
             tc_fence_after();
             const uint32_t stage = lane_base + st * kAStageCols;
+#ifndef AHK_C1T_NO_CONVERT
 #pragma unroll
             for (int c = 0; c < 3; ++c) {
                 // the class's 32 pixels, converted once, as ONE 16-column strip: phase ph reads its 16-pixel window from columns 4 ph .. 4 ph + 7
@@ -1084,6 +1091,9 @@ __global__ void __launch_bounds__(c1t::kCta, 1) conv1t_kernel(Args a, const __gr
                 }
                 tmem_store16(stage + c * kAClassCols, h);
             }
+#else
+            (void)stage; (void)raw; (void)px;
+#endif
             tmem_wait_st();
             tc_fence_before();
             __syncwarp();
@@ -1120,7 +1130,11 @@ __global__ void __launch_bounds__(c1t::kCta, 1) conv1t_kernel(Args a, const __gr
                     for (int c = 0; c < 3; ++c) {
 #pragma unroll
                         for (int ph = 0; ph < 3; ++ph)
+#ifndef AHK_C1T_NO_MMA // timing experiment (tools/build_variant.sh): the pipeline without its MMAs
                             umma_f16_ts(d_base + ph * kN, a_stage + c * kAClassCols + ph * 4, bd0 + static_cast<uint64_t>((c * 3 + ph) * (kWBlock / 16)), kIdesc, (plane | c) != 0);
+#else
+                            ;
+#endif
                     }
                     umma_commit(&s_aempty[st]);
                     if (plane == 8) umma_commit(&s_tfull[buf]);
@@ -1201,15 +1215,23 @@ __global__ void __launch_bounds__(c1t::kCta, 1) conv1t_kernel(Args a, const __gr
     if (warp == kMmaWarp) tmem_dealloc(tmem, kTmemCols);
 }
 
-cudaError_t launch_conv1t(const Args &a, int grid, bool denormal, cudaStream_t s)
+template <bool kDenormal, int kGroups>
+cudaError_t launch_conv1t_as(const Args &a, int grid, cudaStream_t s)
 {
-    cudaError_t e = cudaFuncSetAttribute(denormal ? conv1t_kernel<true> : conv1t_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, c1t::kSmem); // per device
+    cudaError_t e = cudaFuncSetAttribute(conv1t_kernel<kDenormal, kGroups>, cudaFuncAttributeMaxDynamicSharedMemorySize, c1t::kSmem); // per device
     if (e != cudaSuccess) return e;
     const FrameMaps *m = nullptr;
     if ((e = frame_maps(a, &m)) != cudaSuccess) return e;
-    if (denormal) conv1t_kernel<true><<<grid, c1t::kCta, c1t::kSmem, s>>>(a, m->ring, m->side);
-    else conv1t_kernel<false><<<grid, c1t::kCta, c1t::kSmem, s>>>(a, m->ring, m->side);
+    conv1t_kernel<kDenormal, kGroups><<<grid, c1t::cta_threads(kGroups), c1t::kSmem, s>>>(a, m->ring, m->side);
     return cudaGetLastError();
+}
+
+cudaError_t launch_conv1t(const Args &a, int grid, bool denormal, cudaStream_t s, int groups = 4)
+{
+    if (!denormal) return launch_conv1t_as<false, 2>(a, grid, s);
+    if (groups == 3) return launch_conv1t_as<true, 3>(a, grid, s);
+    if (groups == 2) return launch_conv1t_as<true, 2>(a, grid, s);
+    return launch_conv1t_as<true, 4>(a, grid, s);
 }
 
 // ------------------------------------------------------------------------------------------------ conv2 / conv3, pipelined
@@ -1607,10 +1629,14 @@ template <> struct Cfg<kConv3> {
     static constexpr int kSamples = 2, kRowsOut = 2 * kP3, kItemBytes = 2 * kP2 * 32 * 2, kRawPitch = 3 * 128 * 128, kWBytes = 512 * 64 * 2;
 };
 constexpr int kCta = 256 + 64 + 128; // 8 converter warps (2 groups x 4 lane quarters), loader, MMA, 4 epilogue warps
-template <int L> constexpr int smem_bytes() { return 1024 + 2 * Cfg<L>::kRawPitch + Cfg<L>::kWBytes; }
+// raw item buffers: with two, the copy of item t + 2 could only start once item t was converted whole — one item time to cover the
+// latency of a 27 KB copy (ncu: DRAM at 49 % with no unit busy, profiles/conv_tm_r2s5b_ncu.txt).  conv2: 4 buffers, 0.0965 -> 0.0927 ms per
+// 8192 samples; conv3 (48 KB items): 3 buffers were SLOWER than 2 (0.0644 vs 0.0605 ms, same box) and it keeps 2
+template <int L> constexpr int default_raw() { return L == kConv2 ? 4 : 2; }
+template <int L> constexpr int smem_bytes(int raw) { return 1024 + raw * Cfg<L>::kRawPitch + Cfg<L>::kWBytes; }
 } // namespace ctm
 
-template <int L>
+template <int L, int kRaw>
 __global__ void __launch_bounds__(ctm::kCta, 1) conv_tm_kernel(Args a, const __grid_constant__ CUtensorMap tm_in)
 {
     using C = ctm::Cfg<L>;
@@ -1619,8 +1645,8 @@ __global__ void __launch_bounds__(ctm::kCta, 1) conv_tm_kernel(Args a, const __g
     static_assert(kABase + C::kAStages * kACols <= 512, "TMEM");
     extern __shared__ __align__(128) uint8_t smem_raw[];
     uint8_t *s_base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u); // swizzle atoms are 1024-byte aligned
-    uint8_t *s_in = s_base, *s_w = s_base + 2 * C::kRawPitch;
-    __shared__ __align__(8) uint64_t s_wfull, s_rfull[2], s_rempty[2], s_afull[C::kAStages], s_aempty[C::kAStages], s_tfull[2], s_tempty[2];
+    uint8_t *s_in = s_base, *s_w = s_base + kRaw * C::kRawPitch;
+    __shared__ __align__(8) uint64_t s_wfull, s_rfull[kRaw], s_rempty[kRaw], s_afull[C::kAStages], s_aempty[C::kAStages], s_tfull[2], s_tempty[2];
     __shared__ uint32_t s_tmem;
     __shared__ float s_bias[N];
 
@@ -1629,7 +1655,8 @@ __global__ void __launch_bounds__(ctm::kCta, 1) conv_tm_kernel(Args a, const __g
     const int my_items = static_cast<int>(blockIdx.x) < items ? (items - 1 - static_cast<int>(blockIdx.x)) / static_cast<int>(gridDim.x) + 1 : 0;
     if (tid == 0) {
         mbar_init(&s_wfull, 1);
-        for (int i = 0; i < 2; ++i) { mbar_init(&s_rfull[i], 1); mbar_init(&s_rempty[i], 8); mbar_init(&s_tfull[i], 1); mbar_init(&s_tempty[i], 128); }
+        for (int i = 0; i < kRaw; ++i) { mbar_init(&s_rfull[i], 1); mbar_init(&s_rempty[i], 8); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&s_tfull[i], 1); mbar_init(&s_tempty[i], 128); }
         for (int i = 0; i < C::kAStages; ++i) { mbar_init(&s_afull[i], 4); mbar_init(&s_aempty[i], 1); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -1651,8 +1678,8 @@ __global__ void __launch_bounds__(ctm::kCta, 1) conv_tm_kernel(Args a, const __g
         // ---------------------------------------------------------------- loader: one bulk copy per item
         if (lane == 0) {
             for (int t = 0; t < my_items; ++t) {
-                const uint32_t rb = t & 1u;
-                if (t >= 2) mbar_wait_sleep(&s_rempty[rb], ((t >> 1) - 1) & 1);
+                const uint32_t rb = static_cast<uint32_t>(t) % kRaw;
+                if (t >= kRaw) mbar_wait_sleep(&s_rempty[rb], ((t / kRaw) - 1) & 1);
                 const int item = static_cast<int>(blockIdx.x) + t * static_cast<int>(gridDim.x);
                 const int samples = (item + 1) * C::kSamples <= a.n ? C::kSamples : a.n - item * C::kSamples;
                 const uint32_t bytes = static_cast<uint32_t>(samples) * (C::kItemBytes / C::kSamples);
@@ -1672,8 +1699,8 @@ __global__ void __launch_bounds__(ctm::kCta, 1) conv_tm_kernel(Args a, const __g
         const bool swap_halves = ((lane >> 2) & 1) && !a.no_swap;
         uint32_t f = 0; // A stages so far (both groups count all of them)
         for (int t = 0; t < my_items; ++t) {
-            const uint32_t rb = t & 1u;
-            mbar_wait_sleep(&s_rfull[rb], (t >> 1) & 1);
+            const uint32_t rb = static_cast<uint32_t>(t) % kRaw;
+            mbar_wait_sleep(&s_rfull[rb], (t / kRaw) & 1);
             const uint8_t *raw = s_in + rb * C::kRawPitch;
 #pragma unroll 1
             for (int sidx = 0; sidx < kStagesPerItem; ++sidx, ++f) {
@@ -1795,13 +1822,22 @@ __global__ void __launch_bounds__(ctm::kCta, 1) conv_tm_kernel(Args a, const __g
     if (warp == 8) tmem_dealloc(tmem, 512);
 }
 
-template <int L>
-cudaError_t launch_tm(const Args &a, const CUtensorMap &tm_in, int sms, cudaStream_t s, bool pdl = false)
+template <int L, int kRaw>
+cudaError_t launch_tm_as(const Args &a, const CUtensorMap &tm_in, int sms, cudaStream_t s, bool pdl)
 {
-    cudaError_t e = cudaFuncSetAttribute(conv_tm_kernel<L>, cudaFuncAttributeMaxDynamicSharedMemorySize, ctm::smem_bytes<L>());
+    constexpr int bytes = ctm::smem_bytes<L>(kRaw);
+    static_assert(bytes <= 227 * 1024, "raw stages do not fit");
+    cudaError_t e = cudaFuncSetAttribute(conv_tm_kernel<L, kRaw>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
     if (e != cudaSuccess) return e;
     const int items = (a.n + ctm::Cfg<L>::kSamples - 1) / ctm::Cfg<L>::kSamples;
-    return launch_kernel(conv_tm_kernel<L>, dim3(items < sms ? items : sms), dim3(ctm::kCta), ctm::smem_bytes<L>(), s, pdl, a, tm_in);
+    return launch_kernel(conv_tm_kernel<L, kRaw>, dim3(items < sms ? items : sms), dim3(ctm::kCta), bytes, s, pdl, a, tm_in);
+}
+
+// two_raw: the double-buffered form (A/B switch AHK_CONVTM_RAW=2)
+template <int L>
+cudaError_t launch_tm(const Args &a, const CUtensorMap &tm_in, int sms, cudaStream_t s, bool pdl = false, bool two_raw = false)
+{
+    return two_raw ? launch_tm_as<L, 2>(a, tm_in, sms, s, pdl) : launch_tm_as<L, ctm::default_raw<L>()>(a, tm_in, sms, s, pdl);
 }
 
 // ------------------------------------------------------------------------------------------------ gray-diff input
@@ -2135,6 +2171,8 @@ struct ahk_policy {
     // (0.529 ms: the early CTAs of the next layer take SM resources from the running one); 0 = ordinary launches.  AHK_POLICY_PDL
     int pdl = 2;
     bool conv2_no_swap = false;
+    int conv1_groups = 4; // converter groups of conv1t_kernel (forward of 8192 samples 0.4543 / 0.4507 / 0.4492 ms with 2 / 3 / 4, same box); A/B switch AHK_CONV1_GROUPS=2|3|4
+    bool convtm_two_raw = false; // A/B switch AHK_CONVTM_RAW=2: conv_tm_kernel<conv2> with two raw item buffers instead of 4
     uint16_t *w1p = nullptr; // conv1 in phase-separated form (conv1p_kernel, the default), fp16, unscaled
     bool conv1_n144 = false;
     bool conv1_normal = false; // A/B switch AHK_CONV1=normal: conv1t_kernel with the pixels as NORMAL fp16 numbers (1024 + v - 1024)
@@ -2311,6 +2349,8 @@ int ahk_policy_create(int device, int max_batch, const ahk_policy_weights *w, ah
     if (const char *sw = getenv("AHK_CONVTM")) { p->conv_tm = strcmp(sw, "0") != 0; p->conv_tm3 = strcmp(sw, "23") == 0; } // "2": conv2 only, "0": neither
     if (const char *sw = getenv("AHK_POLICY_PDL")) p->pdl = atoi(sw);
     if (const char *sw = getenv("AHK_CONV2_SWAP")) p->conv2_no_swap = strcmp(sw, "0") == 0;
+    if (const char *sw = getenv("AHK_CONV1_GROUPS")) p->conv1_groups = atoi(sw);
+    if (const char *sw = getenv("AHK_CONVTM_RAW")) p->convtm_two_raw = strcmp(sw, "2") == 0;
     if (const char *sw = getenv("AHK_CONV1")) { p->conv1_n144 = strcmp(sw, "n144") == 0; p->conv1_smem = strcmp(sw, "smem") == 0; p->conv1_normal = strcmp(sw, "normal") == 0; }
     int rc = load_rgb_weights(p, w);
     const size_t nb = static_cast<size_t>(max_batch);
@@ -2523,7 +2563,7 @@ static int rgb_layer(ahk_policy *p, Args a, int layer, float *logits, uint8_t *a
         } else {
             a.weights = reinterpret_cast<const uint4 *>(p->w1p);
             const int items = n * 2;
-            POL_CUDA(p->conv1_smem ? launch_conv1p(a, items < p->sms ? items : p->sms, s) : launch_conv1t(a, items < p->sms ? items : p->sms, !p->conv1_normal, s));
+            POL_CUDA(p->conv1_smem ? launch_conv1p(a, items < p->sms ? items : p->sms, s) : launch_conv1t(a, items < p->sms ? items : p->sms, !p->conv1_normal, s, p->conv1_groups));
         }
         return AHK_OK;
     case 1:
@@ -2531,7 +2571,7 @@ static int rgb_layer(ahk_policy *p, Args a, int layer, float *logits, uint8_t *a
         // four times over L2 -> SM (1.2 GB per 8192 samples: 0.21-0.25 ms against 0.155; AHK_GEMM=tma2 runs it for the record)
         a.in = p->act1; a.weights = reinterpret_cast<const uint4 *>(p->w[1]); a.bias = p->b[1]; a.out = p->act2; a.m_total = n * kP2;
         g.tiles_m = n * 4; g.blocks_n = 1; g.k_chunks = 4; g.n_valid = 32; g.bias = p->b[1]; g.out_bf16 = p->act2; g.out_pitch = 32;
-        if (p->conv_tm && p->conv2_parity && !p->legacy_conv && !(p->tma_gemm && p->tma_conv2)) POL_CUDA(launch_tm<kConv2>(a, p->tm_rows2, p->sms, s, pdl)); // (conv2 takes its sample by a plain bulk copy: the map is unused)
+        if (p->conv_tm && p->conv2_parity && !p->legacy_conv && !(p->tma_gemm && p->tma_conv2)) POL_CUDA(launch_tm<kConv2>(a, p->tm_rows2, p->sms, s, pdl, p->convtm_two_raw)); // (conv2 takes its sample by a plain bulk copy: the map is unused)
         else if (p->conv2_parity && !p->legacy_conv && !(p->tma_gemm && p->tma_conv2)) {
             a.weights = reinterpret_cast<const uint4 *>(p->w2p);
             POL_CUDA(launch_conv2p(a, p->sms, s));
@@ -2542,7 +2582,7 @@ static int rgb_layer(ahk_policy *p, Args a, int layer, float *logits, uint8_t *a
     case 2:
         a.in = p->act2; a.weights = reinterpret_cast<const uint4 *>(p->w[2]); a.bias = p->b[2]; a.out = p->act3; a.m_total = n * kP3;
         g.tiles_m = (n + 1) / 2; g.blocks_n = 1; g.k_chunks = 8; g.n_valid = 64; g.bias = p->b[2]; g.out_bf16 = p->act3; g.out_pitch = 64;
-        if (p->conv_tm3 && p->tma_gemm && !p->legacy_conv) POL_CUDA(launch_tm<kConv3>(a, p->tm_rows2, p->sms, s, pdl));
+        if (p->conv_tm3 && p->tma_gemm && !p->legacy_conv) POL_CUDA(launch_tm<kConv3>(a, p->tm_rows2, p->sms, s, pdl, p->convtm_two_raw));
         else if (p->tma_gemm) POL_CUDA((tg::launch<64, 128, tg::kConv3, false, tg::kBiasReluBf16, 6, 8>(g, p->tm_a[2], p->tm_w[2], p->sms, s, pdl)));
         else if (p->legacy_conv) POL_CUDA(launch<kConv3>(a, tiles(static_cast<long long>(n) * kP3), 1, p->sms, s));
         else POL_CUDA(launch_ws<kConv3>(a, tiles(static_cast<long long>(n) * kP3), p->sms, s));

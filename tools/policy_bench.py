@@ -26,7 +26,11 @@ def main():
     ap.add_argument("--envs", type=int, default=8192)
     ap.add_argument("--iters", type=int, default=50)
     ap.add_argument("--rollout-steps", type=int, default=256)
+    ap.add_argument("--lib", default=None, help="A/B: another build of libahk.so (tools/build_variant.sh)")
     args = ap.parse_args()
+    if args.lib:
+        from gym_air_hockey_b200 import _lib
+        _lib.LIB_PATH = os.path.abspath(args.lib)
     n = args.envs
     env = BatchedAirHockeyEnv(n, seed=0, auto_reset=True, max_episode_steps=256)
     pol = PolicyNetwork(max_batch=n)

@@ -84,6 +84,31 @@ def ncu_traffic(pattern):
     return None, None
 
 
+def forward_traffic(n):
+    """DRAM bytes one 'rgb' CNN forward of n samples moves, from the committed ncu --set full captures of its conv kernels at 8192
+    samples (dram__bytes_read.sum + dram__bytes_write.sum, scaled by n / 8192); the three dense layers are added with their
+    algorithmic bytes (activations in and out + weights once).  -> (bytes, source) or (None, None)."""
+    unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+
+    def columns(name):
+        cols = None
+        try:
+            with open(os.path.join(ROOT, "profiles", name)) as f:
+                for line in f:
+                    m = re.match(r"dram__bytes_(read|write)\.sum\s+(\w+)\s+(.*)", line)
+                    if m and m.group(2) in unit:
+                        vals = [unit[m.group(2)] * float(v.replace(",", "")) for v in m.group(3).split()]
+                        cols = vals if cols is None else [a + b for a, b in zip(cols, vals)]
+        except OSError:
+            return None
+        return cols
+    conv1, conv23 = columns("conv1t_roles_r2.txt"), columns("conv_tm_r2s5b_ncu.txt")
+    if not conv1 or not conv23 or len(conv23) < 2:
+        return None, None
+    dense = 8192 * (4096 + 512 + 512 + 512 + 512) * 2 + 8192 * 10 * 4 + (4096 * 512 + 512 * 512 + 512 * 16) * 2
+    return (conv1[0] + conv23[0] + conv23[1] + dense) * n / 8192.0, "conv1t_roles_r2.txt + conv_tm_r2s5b_ncu.txt (conv2, conv3) + algorithmic bytes of the dense layers"
+
+
 class ClockSampler(threading.Thread):
     """SM clock and throttle reasons DURING the timed region, read in-process through NVML (no fork next to the launch
     loop).  start() it at least 0.3 s before the region."""
@@ -300,6 +325,7 @@ def measure_rollout(args, world, rank, local, barrier, min_s=MIN_REGION_S):
     tensor_peak = peaks.get("bf16_tflops_sustained", peaks["bf16_tflops"])
     tflops = n * FLOPS_PER_SAMPLE / (fwd_ms * 1e-3) / 1e12
     in_gbs = n * 147456 / (fwd_ms * 1e-3) / 1e9
+    fwd_traffic, fwd_traffic_src = forward_traffic(n)
     top = max(range(6), key=lambda i: layers[i])
     total = n * world
     rec = {
@@ -311,7 +337,11 @@ def measure_rollout(args, world, rank, local, barrier, min_s=MIN_REGION_S):
                                % (n, ", gradients + BatchNorm statistics all-reduced over NCCL (2 403 961 float32)" if world > 1 else ""),
                    "envs_per_gpu": n, "total_envs": total, "mode": "rgb", "episode_length": 256},
         "gpu_launches": launches,
-        "roofline": {"bound": "hbm", "achieved": in_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": in_gbs / peaks["hbm_gbs"], "traffic": None,
+        "roofline": {"bound": "hbm", "achieved": in_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": in_gbs / peaks["hbm_gbs"], "traffic": fwd_traffic,
+                     "traffic_source": fwd_traffic_src,
+                     "traffic_GBs": (fwd_traffic / (fwd_ms * 1e-3) / 1e9) if fwd_traffic else None,
+                     "frac_of_peak_by_traffic": (fwd_traffic / (fwd_ms * 1e-3) / 1e9 / peaks["hbm_gbs"]) if fwd_traffic else None,
+                     "traffic_note": "the six kernels keep their activations in HBM between them: the forward MOVES this many bytes (ncu) for 147 456 algorithmic bytes per sample; conv1 alone is 1.41 GB of it per 8192 samples and runs at 0.76 of the copy peak (profiles/conv1t_role_removal_r2s5e.txt)",
                      "what": "CNN forward: its algorithmic input, the uint8 3-frame stack (147 456 B/sample), over the summed layer-kernel times; the network sits below the bf16 ridge at uint8 input (139 FLOP/B)",
                      "forward_ms": fwd_ms, "layer_ms": dict(zip(names, layers)),
                      "tensor": {"achieved": tflops, "peak": tensor_peak, "unit": "TFLOP/s", "frac": tflops / tensor_peak,

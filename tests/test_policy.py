@@ -34,14 +34,16 @@ def test_keras_default_init_statistics():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("n,source", [(1, "noise"), (37, "noise"), (200, "game")])
-def test_policy_forward_matches_reference(cuda, table, n, source):
+@pytest.mark.parametrize("n,source,max_batch", [(1, "noise", 256), (37, "noise", 256), (200, "game", 256), (37, "noise", 37), (3, "noise", 3)])
+def test_policy_forward_matches_reference(cuda, table, n, source, max_batch):
+    """max_batch 37 / 3: an ODD number of samples fills the activation buffers to their last byte — conv3's item copies are
+    tensor-map rows of two act2 pixels, and the last item of an odd batch reaches past the last sample."""
     import cnn_ref
     from gym_air_hockey_b200 import BatchedAirHockeyEnv
     from gym_air_hockey_b200.policy import PolicyNetwork, keras_default_init
     torch = cuda
     w = keras_default_init(seed=5, randomize_bn=True)
-    net = PolicyNetwork(w, max_batch=256)
+    net = PolicyNetwork(w, max_batch=max_batch)
     if source == "game":
         env = BatchedAirHockeyEnv(n, table=table, seed=9, max_episode_steps=50)
         env.reset()

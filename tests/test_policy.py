@@ -214,3 +214,30 @@ def test_gray_policy_forward_matches_reference(cuda, table, n, source):
     assert np.abs(logits - ref16).max() <= 6e-3 * scale, np.abs(logits - ref16).max() / scale
     assert np.abs(logits - ref32).max() <= 3e-2 * scale, np.abs(logits - ref32).max() / scale
     assert np.array_equal(action, logits.argmax(axis=1))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n", [1, 37, 300, 2051])
+def test_fused_conv23_is_bit_identical(cuda, table, n, monkeypatch):
+    """conv23_kernel (the default of inference forwards: conv2 -> conv3 in one kernel, act2 in shared memory) does the arithmetic
+    of the two conv_tm_kernel launches it replaces (AHK_FUSE23=0): same logits bit for bit, also on a second call (stale
+    accumulators / act2 of the previous pair), for odd batches and for more pairs than CTAs."""
+    from gym_air_hockey_b200 import BatchedAirHockeyEnv
+    from gym_air_hockey_b200.policy import PolicyNetwork, keras_default_init
+    torch = cuda
+    w = keras_default_init(seed=6, randomize_bn=True)
+    env = BatchedAirHockeyEnv(n, table=table, seed=4, max_episode_steps=50)
+    env.reset()
+    for _ in range(5):
+        env.step()
+    out = {}
+    for mode in ("0", "1"):
+        monkeypatch.setenv("AHK_FUSE23", mode)
+        net = PolicyNetwork(w, max_batch=n)
+        first = net.forward_ring(env.frames, env.head)[0].clone()
+        second = net.forward_ring(env.frames, env.head)[0].clone()
+        torch.cuda.synchronize()
+        assert torch.equal(first, second)
+        out[mode] = first
+        net.close()
+    assert torch.isfinite(out["1"]).all() and torch.equal(out["0"], out["1"])

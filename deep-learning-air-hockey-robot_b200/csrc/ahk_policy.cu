@@ -1845,7 +1845,9 @@ cudaError_t launch_tm(const Args &a, const CUtensorMap &tm_in, int sms, cudaStre
 // into shared memory in the 128-byte-swizzled row layout conv_tm_kernel<conv3> reads, instead of 143 MB of stores + 189 MB of
 // loads per 8192 samples through HBM, and one launch less.  Same roles, converters, MMAs and arithmetic as the two
 // conv_tm_kernel instantiations (results are bit-identical); a work item is a PAIR of samples (one conv3 tile).
-//   shared memory: act2 of the pair (46 KB, one buffer) | conv3 weights 64 KB | conv2 weights 8 KB | ring of 3 act1 samples (79 KB)
+//   shared memory: act2, a ring of 3 SAMPLE buffers (69 KB: conv2's epilogue writes the next pair's first sample while conv3 of this pair
+//                  is still being converted; with one pair buffer the converters waited 15 % of the time for act2, profiles/conv23_r2s5n_ncu.txt)
+//                  | conv3 weights 64 KB | conv2 weights 8 KB | ring of 3 act1 samples (79 KB)
 //   tensor memory: conv2 accumulators, 6 tile slots x 32 columns (handed over slot by slot) | conv3 accumulators 2 x 64 |
 //                  3 A stages x 64 columns (8 MMAs each)
 //   every role walks the same software-pipelined stage sequence: conv2(0); then per step conv2(t + 1), conv3(t) — conv3 of a
@@ -1853,7 +1855,7 @@ cudaError_t launch_tm(const Args &a, const CUtensorMap &tm_in, int sms, cudaStre
 //   soon as the converters have read pair t's act2.
 namespace c23 {
 constexpr int kCta = 256 + 64 + 128; // 8 converter warps (2 groups x 4 lane quarters), MMA warp, loader warp, 4 epilogue warps
-constexpr int kRaw = 3, kRawPitch = 27008, kAct2Bytes = 47104; // 2 x 361 pixels x 64 B = 46 208, rounded up to a multiple of 1024
+constexpr int kRaw = 3, kRawPitch = 27008, kAct2Ring = 3, kAct2Sample = 23552, kAct2Bytes = kAct2Ring * kAct2Sample; // 361 pixels x 64 B = 23 104, rounded up to a multiple of 1024
 constexpr int kW2Bytes = 128 * 32 * 2, kW3Bytes = 512 * 64 * 2;
 constexpr int kSmem = 1024 + kAct2Bytes + kW3Bytes + kW2Bytes + kRaw * kRawPitch;
 constexpr int kD2 = 0, kD3 = 192, kA = 320, kACols = 64, kAStages = 3;
@@ -1867,7 +1869,7 @@ __global__ void __launch_bounds__(c23::kCta, 1) conv23_kernel(Args a, const uint
     uint8_t *s_act2 = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u); // swizzle atoms are 1024-byte aligned
     uint8_t *s_w3 = s_act2 + kAct2Bytes, *s_w2 = s_w3 + kW3Bytes, *s_in = s_w2 + kW2Bytes;
     __shared__ __align__(8) uint64_t s_wfull, s_rfull[kRaw], s_rempty[kRaw], s_afull[kAStages], s_aempty[kAStages], s_t2full[6], s_t2empty[6], s_t3full[2],
-        s_t3empty[2], s_a2full, s_a2empty;
+        s_t3empty[2], s_a2full[kAct2Ring], s_a2empty[kAct2Ring];
     __shared__ uint32_t s_tmem;
     __shared__ float s_bias2[32], s_bias3[64];
 
@@ -1876,8 +1878,7 @@ __global__ void __launch_bounds__(c23::kCta, 1) conv23_kernel(Args a, const uint
     const int my_items = static_cast<int>(blockIdx.x) < items ? (items - 1 - static_cast<int>(blockIdx.x)) / static_cast<int>(gridDim.x) + 1 : 0;
     if (tid == 0) {
         mbar_init(&s_wfull, 1);
-        mbar_init(&s_a2full, 128);
-        mbar_init(&s_a2empty, 8);
+        for (int i = 0; i < kAct2Ring; ++i) { mbar_init(&s_a2full[i], 128); mbar_init(&s_a2empty[i], 8); }
         for (int i = 0; i < kRaw; ++i) { mbar_init(&s_rfull[i], 1); mbar_init(&s_rempty[i], 8); }
         for (int i = 0; i < kAStages; ++i) { mbar_init(&s_afull[i], 4); mbar_init(&s_aempty[i], 1); }
         for (int i = 0; i < 6; ++i) { mbar_init(&s_t2full[i], 1); mbar_init(&s_t2empty[i], 128); }
@@ -1955,9 +1956,11 @@ __global__ void __launch_bounds__(c23::kCta, 1) conv23_kernel(Args a, const uint
             }
             if (s >= 1) { // conv3 of pair s - 1, from act2 in shared memory
                 const int t = s - 1;
-                mbar_wait_sleep(&s_a2full, t & 1);
+                const uint32_t u0 = 2u * static_cast<uint32_t>(t), u1 = u0 + 1u; // the pair's samples: act2 ring slots u % 3
+                mbar_wait_sleep(&s_a2full[u0 % kAct2Ring], (u0 / kAct2Ring) & 1u);
+                mbar_wait_sleep(&s_a2full[u1 % kAct2Ring], (u1 / kAct2Ring) & 1u);
                 const int smp = r >> 6, pp = r & 63, y = pp >> 3, x = pp & 7;
-                const uint32_t off = smp * (kP2 * 64) + ((2 * y) * kC2 + 2 * x) * 64;
+                const uint32_t off = ((smp ? u1 : u0) % kAct2Ring) * kAct2Sample + ((2 * y) * kC2 + 2 * x) * 64;
 #pragma unroll 1
                 for (int g = 0; g < 4; ++g, ++f) {
                     if ((f & 1u) != group) continue;
@@ -1980,7 +1983,7 @@ __global__ void __launch_bounds__(c23::kCta, 1) conv23_kernel(Args a, const uint
                     if (lane == 0) mbar_arrive(&s_afull[st]);
                 }
                 __syncwarp();
-                if (lane == 0) mbar_arrive(&s_a2empty); // act2 of the pair has been read by this warp
+                if (lane == 0) { mbar_arrive(&s_a2empty[u0 % kAct2Ring]); mbar_arrive(&s_a2empty[u1 % kAct2Ring]); } // act2 of the pair has been read by this warp
             }
         }
     } else if (warp == 8) {
@@ -2036,9 +2039,10 @@ __global__ void __launch_bounds__(c23::kCta, 1) conv23_kernel(Args a, const uint
         const int q4 = warp & 3, r = q4 * 32 + lane;
         const uint32_t lane_addr = tmem + (static_cast<uint32_t>(q4 * 32) << 16);
         auto epilogue2 = [&](int t) { // conv2 accumulators of pair t -> bias, ReLU, bf16 -> act2 in shared memory (swizzled rows of two pixels)
-            if (t >= 1) mbar_wait_sleep(&s_a2empty, (t - 1) & 1);
 #pragma unroll 1
             for (int slot = 0; slot < 6; ++slot) {
+                const uint32_t u = 2u * static_cast<uint32_t>(t) + (slot >= 3 ? 1u : 0u), ring = u % kAct2Ring; // sample and its act2 ring slot
+                if (slot % 3 == 0 && u >= static_cast<uint32_t>(kAct2Ring)) mbar_wait_sleep(&s_a2empty[ring], ((u / kAct2Ring) - 1u) & 1u);
                 mbar_wait_sleep(&s_t2full[slot], t & 1);
                 tc_fence_after();
                 uint32_t v[32];
@@ -2049,7 +2053,7 @@ __global__ void __launch_bounds__(c23::kCta, 1) conv23_kernel(Args a, const uint
                 mbar_arrive(&s_t2empty[slot]);
                 const int j = slot / 3, pix = (slot - 3 * j) * 128 + r;
                 if (pix < kP2) {
-                    const uint32_t lin = static_cast<uint32_t>(j * kP2 + pix) * 64u;
+                    const uint32_t lin = ring * kAct2Sample + static_cast<uint32_t>(pix) * 64u;
 #pragma unroll
                     for (int c = 0; c < 4; ++c) {
                         uint32_t pk[4];
@@ -2065,8 +2069,8 @@ __global__ void __launch_bounds__(c23::kCta, 1) conv23_kernel(Args a, const uint
                         *reinterpret_cast<uint4 *>(s_act2 + at) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
                     }
                 }
+                if (slot % 3 == 2) mbar_arrive(&s_a2full[ring]); // release: this thread's rows of the sample are in shared memory
             }
-            mbar_arrive(&s_a2full); // release: this thread's rows of the pair are in shared memory
         };
         auto epilogue3 = [&](int t) { // conv3 accumulators of pair t -> act3 in global memory
             const uint32_t b = t & 1u;
@@ -2450,8 +2454,8 @@ struct ahk_policy {
     bool conv2_no_swap = false;
     int conv1_groups = 4; // converter groups of conv1t_kernel (forward of 8192 samples 0.4543 / 0.4507 / 0.4492 ms with 2 / 3 / 4, same box); A/B switch AHK_CONV1_GROUPS=2|3|4
     // conv2 -> conv3 in one kernel, act2 in shared memory (conv23_kernel): bit-identical to the two kernels, forward of 8192 samples
-    // 0.4598 -> 0.4561 ms (same box), 0.33 GB less HBM traffic; inference forwards only.  A/B switch AHK_FUSE23=0
-    bool fuse23 = true;
+    // 0.4549 -> 0.4475 ms, rollout step 0.594 -> 0.565 ms (same box), 0.33 GB less HBM traffic; inference forwards only.  A/B switch AHK_FUSE23=0
+    bool fuse23 = true, fuse23_profiled = false; // AHK_FUSE23=2: also in the profiled forward (its 'conv2' time is then the fused kernel's, 'conv3' ~ 0)
     bool convtm_two_raw = false; // A/B switch AHK_CONVTM_RAW=2: conv_tm_kernel<conv2> with two raw item buffers instead of 4
     uint16_t *w1p = nullptr; // conv1 in phase-separated form (conv1p_kernel, the default), fp16, unscaled
     bool conv1_n144 = false;
@@ -2631,7 +2635,7 @@ int ahk_policy_create(int device, int max_batch, const ahk_policy_weights *w, ah
     if (const char *sw = getenv("AHK_CONV2_SWAP")) p->conv2_no_swap = strcmp(sw, "0") == 0;
     if (const char *sw = getenv("AHK_CONV1_GROUPS")) p->conv1_groups = atoi(sw);
     if (const char *sw = getenv("AHK_CONVTM_RAW")) p->convtm_two_raw = strcmp(sw, "2") == 0;
-    if (const char *sw = getenv("AHK_FUSE23")) p->fuse23 = strcmp(sw, "0") != 0;
+    if (const char *sw = getenv("AHK_FUSE23")) { p->fuse23 = strcmp(sw, "0") != 0; p->fuse23_profiled = strcmp(sw, "2") == 0; }
     if (const char *sw = getenv("AHK_CONV1")) { p->conv1_n144 = strcmp(sw, "n144") == 0; p->conv1_smem = strcmp(sw, "smem") == 0; p->conv1_normal = strcmp(sw, "normal") == 0; }
     int rc = load_rgb_weights(p, w);
     const size_t nb = static_cast<size_t>(max_batch);
@@ -2943,7 +2947,7 @@ static int policy_forward(ahk_policy *p, const ahk_stack &stack, float *logits, 
     for (int layer = 0; layer < 6; ++layer) {
         a.pdl = timed ? 0 : p->pdl;
         a.no_swap = p->conv2_no_swap;
-        if (int rc = rgb_layer(p, a, layer, logits, action, s, a.pdl != 0 && layer > 0, p->fuse23 && !timed)) return rc; // profiled: one kernel per layer
+        if (int rc = rgb_layer(p, a, layer, logits, action, s, a.pdl != 0 && layer > 0, p->fuse23 && (!timed || p->fuse23_profiled))) return rc; // profiled: one kernel per layer unless AHK_FUSE23=2
         if (timed) POL_CUDA(cudaEventRecord(p->ev[layer + 1], s));
     }
     p->launches += 6;

@@ -102,11 +102,11 @@ def forward_traffic(n):
         except OSError:
             return None
         return cols
-    conv1, conv23 = columns("conv1t_roles_r2.txt"), columns("conv_tm_r2s5b_ncu.txt")
-    if not conv1 or not conv23 or len(conv23) < 2:
+    conv1, conv23 = columns("conv1t_roles_r2.txt"), columns("conv23_r2s5n_ncu.txt")  # conv23_kernel: conv2 -> conv3 fused, act2 stays on the SM
+    if not conv1 or not conv23:
         return None, None
     dense = 8192 * (4096 + 512 + 512 + 512 + 512) * 2 + 8192 * 10 * 4 + (4096 * 512 + 512 * 512 + 512 * 16) * 2
-    return (conv1[0] + conv23[0] + conv23[1] + dense) * n / 8192.0, "conv1t_roles_r2.txt + conv_tm_r2s5b_ncu.txt (conv2, conv3) + algorithmic bytes of the dense layers"
+    return (conv1[0] + conv23[0] + dense) * n / 8192.0, "conv1t_roles_r2.txt + conv23_r2s5n_ncu.txt (conv2 -> conv3 fused) + algorithmic bytes of the dense layers"
 
 
 class ClockSampler(threading.Thread):
@@ -341,7 +341,7 @@ def measure_rollout(args, world, rank, local, barrier, min_s=MIN_REGION_S):
                      "traffic_source": fwd_traffic_src,
                      "traffic_GBs": (fwd_traffic / (fwd_ms * 1e-3) / 1e9) if fwd_traffic else None,
                      "frac_of_peak_by_traffic": (fwd_traffic / (fwd_ms * 1e-3) / 1e9 / peaks["hbm_gbs"]) if fwd_traffic else None,
-                     "traffic_note": "the six kernels keep their activations in HBM between them: the forward MOVES this many bytes (ncu) for 147 456 algorithmic bytes per sample; conv1 alone is 1.41 GB of it per 8192 samples and runs at 0.76 of the copy peak (profiles/conv1t_role_removal_r2s5e.txt)",
+                     "traffic_note": "act1, act3, h1 and h2 travel through HBM between the kernels (act2 stays on the SM: conv2 -> conv3 are one kernel): the forward MOVES this many bytes (ncu) for 147 456 algorithmic bytes per sample; conv1 alone is 1.41 GB of it per 8192 samples and runs at 0.76 of the copy peak (profiles/conv1t_role_removal_r2s5e.txt); layer_ms come from the profiled forward, which runs conv2 and conv3 as two kernels",
                      "what": "CNN forward: its algorithmic input, the uint8 3-frame stack (147 456 B/sample), over the summed layer-kernel times; the network sits below the bf16 ridge at uint8 input (139 FLOP/B)",
                      "forward_ms": fwd_ms, "layer_ms": dict(zip(names, layers)),
                      "tensor": {"achieved": tflops, "peak": tensor_peak, "unit": "TFLOP/s", "frac": tflops / tensor_peak,

@@ -163,8 +163,9 @@ class ClockSampler(threading.Thread):
 class CpuArm(object):
     """The reference's per-step work for this path on the host cores: the oracle port (oracle/ahk_oracle.c — native 450x700
     draw, NEAREST resize, float32 (9,128,128) observation, reward, labels; the reference's own Pygame simulator cannot run
-    anywhere) through the ahk_cpu_* twin of the C ABI (include/ahk_cpu.h: ahk_cpu_step + ahk_cpu_observe per
-    env step, host buffers in the engine's layouts) on a persistent pool of threads with outputs allocated once.  The reference arm
+    anywhere) through the ahk_cpu_* twin of the C ABI (include/ahk_cpu.h: one ahk_cpu_step_many call per bench
+    step with the float32 observation bound, host buffers in the engine's layouts) on a persistent pool of threads with
+    outputs allocated once.  The reference arm
     (--impl reference) and the cpu_baseline leg both go through this class, so their numbers agree."""
 
     def __init__(self, n_envs=4096, threads=None):
@@ -190,6 +191,9 @@ class CpuArm(object):
         self.threads = self.eng.threads
         self.eng.reset()
         self.obs = np.empty((self.n, 9, 128, 128), np.float32)
+        # what the reference's env.step() hands back besides reward / terminal / labels: the float32 observation, written by the
+        # worker that just stepped the env (ahk_cpu_bind_observation)
+        self.eng.bind_observation(1, self.obs)
         self._steps(1)  # touches every output page
         t0 = time.perf_counter()
         self._steps(1)
@@ -197,9 +201,9 @@ class CpuArm(object):
         self.sub = max(1, int(round(1.2 * MIN_REGION_S / per_step)))  # sim steps per env per timed call: >= 0.25 s of work
 
     def _steps(self, k):
-        for _ in range(k):  # what the reference's env.step() hands back: reward / terminal / labels and the float32 observation
-            self.eng.step()
-            self.eng.observe(1, self.obs)
+        # one ahk_cpu_step_many call: every worker runs k consecutive steps of each of its envs (env-major, as a CTA of the CUDA
+        # kernel does and as the reference's own single-env loop does: state, ring and native frame stay in cache)
+        self.eng.step_many(k)
 
     def run(self, calls):
         t0 = time.perf_counter()
@@ -208,7 +212,7 @@ class CpuArm(object):
         return time.perf_counter() - t0
 
     def sample(self, calls):
-        return "%d envs x %d sim-steps per call x %d calls, %d threads (ahk_cpu_step + ahk_cpu_observe(float32) per step; persistent pool, outputs preallocated)" % (self.n, self.sub, calls, self.threads)
+        return "%d envs x %d sim-steps per call x %d calls, %d threads (one ahk_cpu_step_many call, float32 observation of every step bound; persistent pool, outputs preallocated)" % (self.n, self.sub, calls, self.threads)
 
 
 def cpu_reference_wrapper():

@@ -44,6 +44,12 @@ int ahk_cpu_step_many(ahk_cpu_env *env, int steps, const ahk_step_log *log_host,
 /* ≙ ahk_observe (DataProcessor.process_observation's output formats, processor.py:39-64), host memory */
 int ahk_cpu_observe(ahk_cpu_env *env, int format, void *out_host, void *stream_ignored);
 
+/* The reference's env.step() returns the processed observation every step (air_hockey_env.py:153-155).  With a host buffer bound,
+ * every ahk_cpu_step / ahk_cpu_step_many also writes each env's observation in `format` (the bytes ahk_cpu_observe would write),
+ * by the worker thread that just stepped the env — the reference's per-step work in one pass.  NULL unbinds.  No GPU counterpart
+ * (there the frames stay uint8 in the ring and ahk_observe materialises them on request). */
+int ahk_cpu_bind_observation(ahk_cpu_env *env, int format, void *out_host);
+
 /* ≙ ahk_head */
 int ahk_cpu_head(const ahk_cpu_env *env);
 

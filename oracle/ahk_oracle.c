@@ -792,6 +792,8 @@ struct ahk_cpu_env {
     uint8_t *table;
     int head, bound;
     uint64_t *part; /* per-worker statistics [threads][AHK_STATS_WORDS] */
+    void *obs_out;  /* ahk_cpu_bind_observation: every step also writes each env's observation here ... */
+    int obs_format; /* ... in this format, by the thread that stepped it */
 };
 
 static __thread char cpu_error[256];
@@ -859,9 +861,11 @@ typedef struct {
     int mode;                 /* 0 reset, 1 step */
     const uint8_t *mask, *episode, *use, *robot, *human;
     const ahk_step_log *log;
-    int t;                    /* row of the log */
-    int slots[3];             /* ring slots of the frames newest, middle, oldest after this call */
+    int steps;                /* mode 1: consecutive steps per env (ahk_cpu_step_many runs them env by env, like a CTA of the CUDA kernel) */
+    int head0;                /* ring slot of the newest frame BEFORE the call */
 } cpu_call;
+
+static void cpu_observe_one(const orc_env *e, int i, int format, void *out);
 
 static void cpu_publish(ahk_cpu_env *h, int i, int all_frames, const int slots[3])
 {
@@ -887,45 +891,52 @@ static void cpu_slice(void *ctx, int lo, int hi, int worker)
     const size_t n = (size_t)h->cfg.n_envs;
     for (int i = lo; i < hi; ++i) {
         orc_env *e = h->envs[i];
+        int slots[3]; /* ring slots of the frames newest, middle, oldest */
         if (c->mode == 0) {
             if (c->mask && !c->mask[i]) continue;
             const int ep = c->episode && c->episode[i] != AHK_EP_SAMPLE ? c->episode[i] : -1;
             orc_env_reset(e, ep, ep < 0 ? 0 : (c->use ? c->use[i] : USE_ALL));
-            cpu_publish(h, i, 1, c->slots);
+            for (int age = 0; age < 3; ++age) slots[age] = (c->head0 + 3 - age) % 3;
+            cpu_publish(h, i, 1, slots);
             st[1] += 1; /* episodes: every reset counts, as in the CUDA engine */
             continue;
         }
-        orc_step_out o;
-        const int was_pending = h->cfg.auto_reset && e->pending_reset;
-        const int r = c->robot ? c->robot[i] : ACT_NONE, hu = c->human ? c->human[i] : ACT_NONE;
-        if (h->cfg.auto_reset) orc_env_step_auto(e, r, hu, h->cfg.max_episode_steps, &o);
-        else orc_env_step(e, r, hu, &o);
-        cpu_publish(h, i, was_pending, c->slots);
-        h->buf.reward[i] = o.reward;
-        h->buf.done[i] = o.terminal;
-        h->buf.robot_label[i] = o.robot_label;
-        h->buf.human_label[i] = o.human_label;
-        if (h->buf.info) h->buf.info[i] = (uint8_t)(o.flags | o.scored << 5);
-        if (c->log) {
-            const size_t at = (size_t)c->t * n + (size_t)i;
-            if (c->log->robot_label) c->log->robot_label[at] = o.robot_label;
-            if (c->log->human_label) c->log->human_label[at] = o.human_label;
-            if (c->log->done) c->log->done[at] = o.terminal;
-            if (c->log->reward) c->log->reward[at] = o.reward;
+        for (int t = 0; t < c->steps; ++t) { /* env-major: the env's state, ring and native frame stay in cache over its steps */
+            orc_step_out o;
+            const int was_pending = h->cfg.auto_reset && e->pending_reset;
+            const int r = c->robot ? c->robot[i] : ACT_NONE, hu = c->human ? c->human[i] : ACT_NONE;
+            if (h->cfg.auto_reset) orc_env_step_auto(e, r, hu, h->cfg.max_episode_steps, &o);
+            else orc_env_step(e, r, hu, &o);
+            for (int age = 0; age < 3; ++age) slots[age] = (c->head0 + 1 + t + 3 - age) % 3;
+            cpu_publish(h, i, was_pending, slots);
+            if (h->obs_out) cpu_observe_one(e, i, h->obs_format, h->obs_out); /* what the reference's env.step() returns, while the env is in cache */
+            if (t == c->steps - 1) {
+                h->buf.reward[i] = o.reward;
+                h->buf.done[i] = o.terminal;
+                h->buf.robot_label[i] = o.robot_label;
+                h->buf.human_label[i] = o.human_label;
+                if (h->buf.info) h->buf.info[i] = (uint8_t)(o.flags | o.scored << 5);
+            }
+            if (c->log) {
+                const size_t at = (size_t)t * n + (size_t)i;
+                if (c->log->robot_label) c->log->robot_label[at] = o.robot_label;
+                if (c->log->human_label) c->log->human_label[at] = o.human_label;
+                if (c->log->done) c->log->done[at] = o.terminal;
+                if (c->log->reward) c->log->reward[at] = o.reward;
+            }
+            st[0] += 1;
+            st[1] += (uint64_t)was_pending;
+            st[2] += o.scored == SCORED_TOP;
+            st[3] += o.scored == SCORED_BOTTOM;
+            st[4] += (uint64_t)(int64_t)(int)(o.reward * 2.0f);
+            st[5 + o.robot_label] += 1;
+            st[15 + o.human_label] += 1;
         }
-        st[0] += 1;
-        st[1] += (uint64_t)was_pending;
-        st[2] += o.scored == SCORED_TOP;
-        st[3] += o.scored == SCORED_BOTTOM;
-        st[4] += (uint64_t)(int64_t)(int)(o.reward * 2.0f);
-        st[5 + o.robot_label] += 1;
-        st[15 + o.human_label] += 1;
     }
 }
 
 static void cpu_run(ahk_cpu_env *e, cpu_call *c)
 {
-    for (int age = 0; age < 3; ++age) c->slots[age] = (e->head + 3 - age) % 3;
     pool_run(e->pool, cpu_slice, c, e->cfg.n_envs);
     if (e->buf.stats)
         for (int k = 0; k < orc_pool_threads(e->pool); ++k)
@@ -945,7 +956,7 @@ int ahk_cpu_reset(ahk_cpu_env *e, const uint8_t *mask, const uint8_t *episode, c
     (void)stream;
     int rc = cpu_ready(e);
     if (rc) return rc;
-    cpu_call c = { e, 0, mask, episode, use, NULL, NULL, NULL, 0, { 0, 0, 0 } };
+    cpu_call c = { e, 0, mask, episode, use, NULL, NULL, NULL, 0, e->head };
     cpu_run(e, &c);
     return AHK_OK;
 }
@@ -955,9 +966,9 @@ int ahk_cpu_step(ahk_cpu_env *e, const uint8_t *robot, const uint8_t *human, voi
     (void)stream;
     int rc = cpu_ready(e);
     if (rc) return rc;
-    e->head = (e->head + 1) % 3;
-    cpu_call c = { e, 1, NULL, NULL, NULL, robot, human, NULL, 0, { 0, 0, 0 } };
+    cpu_call c = { e, 1, NULL, NULL, NULL, robot, human, NULL, 1, e->head };
     cpu_run(e, &c);
+    e->head = (e->head + 1) % 3;
     return AHK_OK;
 }
 
@@ -967,30 +978,31 @@ int ahk_cpu_step_many(ahk_cpu_env *e, int steps, const ahk_step_log *log, void *
     int rc = cpu_ready(e);
     if (rc) return rc;
     if (steps < 0) return cpu_fail(AHK_ERR_ARG, "steps must be >= 0");
-    for (int t = 0; t < steps; ++t) {
-        e->head = (e->head + 1) % 3;
-        cpu_call c = { e, 1, NULL, NULL, NULL, NULL, NULL, log, t, { 0, 0, 0 } };
-        cpu_run(e, &c);
-    }
+    if (steps == 0) return AHK_OK;
+    cpu_call c = { e, 1, NULL, NULL, NULL, NULL, NULL, log, steps, e->head };
+    cpu_run(e, &c);
+    e->head = (e->head + steps) % 3;
     return AHK_OK;
 }
 
 typedef struct { ahk_cpu_env *e; int format; void *out; } cpu_obs;
 
+static void cpu_observe_one(const orc_env *e, int i, int format, void *out)
+{
+    if (format == AHK_OBS_U8) memcpy((uint8_t *)out + (size_t)i * 3 * ORC_FRAME, e->ring, 3 * ORC_FRAME);
+    else if (format == AHK_OBS_RGB_F32) orc_env_observe_rgb(e, (float *)out + (size_t)i * 3 * ORC_FRAME);
+    else {
+        static __thread float stack[3 * ORC_FRAME]; /* the processor's float32 buffer (processor.py:23,45-49) */
+        for (int k = 0; k < 3 * ORC_FRAME; ++k) stack[k] = (float)(&e->ring[0][0])[k];
+        orc_observe_gray_diff(stack, (double *)out + (size_t)i * 128 * 128);
+    }
+}
+
 static void cpu_obs_slice(void *ctx, int lo, int hi, int worker)
 {
     cpu_obs *c = (cpu_obs *)ctx;
     (void)worker;
-    for (int i = lo; i < hi; ++i) {
-        const orc_env *e = c->e->envs[i];
-        if (c->format == AHK_OBS_U8) memcpy((uint8_t *)c->out + (size_t)i * 3 * ORC_FRAME, e->ring, 3 * ORC_FRAME);
-        else if (c->format == AHK_OBS_RGB_F32) orc_env_observe_rgb(e, (float *)c->out + (size_t)i * 3 * ORC_FRAME);
-        else {
-            float stack[3 * ORC_FRAME]; /* the processor's float32 buffer (processor.py:23,45-49) */
-            for (int k = 0; k < 3 * ORC_FRAME; ++k) stack[k] = (float)(&e->ring[0][0])[k];
-            orc_observe_gray_diff(stack, (double *)c->out + (size_t)i * 128 * 128);
-        }
-    }
+    for (int i = lo; i < hi; ++i) cpu_observe_one(c->e->envs[i], i, c->format, c->out);
 }
 
 /* ≙ ahk_observe: the stacked observation of every env in the reference's formats (processor.py:39-64), host memory */
@@ -1002,5 +1014,18 @@ int ahk_cpu_observe(ahk_cpu_env *e, int format, void *out, void *stream)
     if (!out || format < AHK_OBS_U8 || format > AHK_OBS_GRAY_DIFF_F64) return cpu_fail(AHK_ERR_ARG, "out is NULL or the format is unknown");
     cpu_obs c = { e, format, out };
     pool_run(e->pool, cpu_obs_slice, &c, e->cfg.n_envs);
+    return AHK_OK;
+}
+
+/* The reference's env.step() RETURNS the processed observation (air_hockey_env.py:153-155, processor.py:39-64).  Bind a host
+ * buffer and every ahk_cpu_step / ahk_cpu_step_many also writes each env's observation in `format` (as ahk_cpu_observe would),
+ * by the thread that just stepped the env.  out_host NULL: unbind.  CPU twin only: on the GPU the frames stay uint8 in the ring
+ * and ahk_observe materialises them on request. */
+int ahk_cpu_bind_observation(ahk_cpu_env *e, int format, void *out_host)
+{
+    if (!e) return cpu_fail(AHK_ERR_ARG, "env is NULL");
+    if (out_host && (format < AHK_OBS_U8 || format > AHK_OBS_GRAY_DIFF_F64)) return cpu_fail(AHK_ERR_ARG, "the format is unknown");
+    e->obs_out = out_host;
+    e->obs_format = format;
     return AHK_OK;
 }

@@ -314,6 +314,7 @@ CPU_SYMBOLS = {
     "ahk_cpu_step": (_i, [_vp, _vp, _vp, _vp]),
     "ahk_cpu_step_many": (_i, [_vp, _i, C.POINTER(CpuStepLog), _vp]),
     "ahk_cpu_observe": (_i, [_vp, _i, _vp, _vp]),
+    "ahk_cpu_bind_observation": (_i, [_vp, _i, _vp]),
     "ahk_cpu_head": (_i, [_vp]),
     "ahk_cpu_last_error": (C.c_char_p, []),
 }
@@ -383,6 +384,11 @@ class CpuEngine(object):
         out = np.empty(shape, dt) if out is None else out
         self._check(self.L.ahk_cpu_observe(self._h, int(fmt), out.ctypes.data_as(_vp), None))
         return out
+
+    def bind_observation(self, fmt, out):
+        """Every step also writes each env's observation (format as observe()) into `out`; out None unbinds."""
+        self._obs = out  # keeps the buffer alive
+        self._check(self.L.ahk_cpu_bind_observation(self._h, int(fmt), None if out is None else out.ctypes.data_as(_vp)))
 
     def close(self):
         if getattr(self, "_h", None):

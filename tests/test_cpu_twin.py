@@ -14,7 +14,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 def test_header_binding_and_library_agree(orc):
     text = re.sub(r"/\*.*?\*/", "", open(os.path.join(ROOT, "include", "ahk_cpu.h")).read(), flags=re.S)
     declared = set(re.findall(r"\b(ahk_cpu_[a-z_]+)\s*\(", text))
-    assert declared == set(orc.CPU_SYMBOLS) and len(declared) == 11
+    assert declared == set(orc.CPU_SYMBOLS) and len(declared) == 12
     L = orc.lib()
     for name in declared:
         assert hasattr(L, name), name
@@ -68,6 +68,7 @@ def test_twin_matches_per_env_oracle(orc, noise_table):
             for age in range(3):
                 assert np.array_equal(eng.frames[(h + 3 - age) % 3, i], ring[age]), (t, i, age)
     assert eng.stats[0] == n * 33 and eng.stats[5:15].sum() == n * 33
+    steps_so_far = int(eng.stats[0])
     u8, f32, gray = eng.observe(0), eng.observe(1), eng.observe(2)
     for i, o in enumerate(envs):
         assert np.array_equal(u8[i].reshape(3, 3, 128, 128), o.ring())
@@ -76,6 +77,13 @@ def test_twin_matches_per_env_oracle(orc, noise_table):
         for age in (2, 1, 0):
             st.push(o.ring()[age])
         assert np.array_equal(gray[i], st.gray_diff())
+    bound = np.zeros((n, 9, 128, 128), np.float32)   # the observation written by the step itself
+    eng.bind_observation(1, bound)
+    eng.step()
+    assert np.array_equal(bound, eng.observe(1))
+    eng.bind_observation(1, None)
+    for o in envs:
+        o.step_auto(255, 255, limit)
     with pytest.raises(RuntimeError, match="3-slot ring"):
         L = orc.lib()
         cfg = orc.CpuConfig(n_envs=2, ring_depth=8)

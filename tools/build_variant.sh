@@ -1,5 +1,5 @@
 #!/bin/bash
-# A/B builds of the CUDA library with build-time overrides:  bash tools/build_variant.sh NAME -DAHK_C1T_ASTAGES=3 ...
+# A/B builds of the CUDA library with build-time overrides:  bash tools/build_variant.sh NAME -DAHK_C1T_NO_MMA | -DAHK_C1T_NO_CONVERT  (timing experiments: conv1t_kernel with one role removed)
 # -> tools/ab/libahk_NAME.so (git-ignored; travels to the GPU box), for `python tools/policy_bench.py --lib tools/ab/libahk_NAME.so`
 set -e
 NAME=$1; shift

@@ -2950,7 +2950,7 @@ static int policy_forward(ahk_policy *p, const ahk_stack &stack, float *logits, 
         if (int rc = rgb_layer(p, a, layer, logits, action, s, a.pdl != 0 && layer > 0, p->fuse23 && (!timed || p->fuse23_profiled))) return rc; // profiled: one kernel per layer unless AHK_FUSE23=2
         if (timed) POL_CUDA(cudaEventRecord(p->ev[layer + 1], s));
     }
-    p->launches += 6;
+    p->launches += (p->fuse23 && (!timed || p->fuse23_profiled) && p->conv_tm && p->conv_tm3 && p->conv2_parity && !p->legacy_conv && p->tma_gemm && !p->tma_conv2) ? 5 : 6;
     return AHK_OK;
 }
 

@@ -8,6 +8,7 @@ mean/moving variance), i.e. what `model.get_weights()` returns; a trained Keras 
 (h5lite.py: the package's own HDF5 reader).
 """
 import ctypes as C
+import os
 
 import numpy as np
 import torch
@@ -190,6 +191,9 @@ class PolicyNetwork(object):
         _lib.check(create(self.device.index, self.max_batch, C.byref(st), C.byref(h)))
         self._h = h
         self.launches = 0
+        # kernels per inference forward: conv2 -> conv3 are ONE kernel (conv23_kernel) unless an A/B switch selects other conv kernels
+        ab = any(os.environ.get(k) for k in ('AHK_CONVTM', 'AHK_CONV2', 'AHK_CONV23', 'AHK_GEMM')) or os.environ.get('AHK_FUSE23') == '0'
+        self._forward_launches = (6 if ab else 5) if mode == 'rgb' else 7
 
     def forward_ring(self, frames, head, logits=None, action=None):
         """frames: uint8 CUDA tensor [3, n, 3, 128, 128] (the env's ring), head: newest slot."""
@@ -203,7 +207,7 @@ class PolicyNetwork(object):
         stream = C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
         _lib.check(self.lib.ahk_policy_forward(self._h, C.c_void_p(frames.data_ptr()), n, int(head),
                                                C.c_void_p(logits.data_ptr()), C.c_void_p(action.data_ptr()), stream))
-        self.launches += 6
+        self.launches += self._forward_launches
         return logits, action
 
     def forward_profiled(self, env, logits, action):
@@ -213,7 +217,7 @@ class PolicyNetwork(object):
         st = env.stack_view()
         _lib.check(self.lib.ahk_policy_forward_stack_profiled(self._h, C.byref(st), C.c_void_p(logits.data_ptr()),
                                                               C.c_void_p(action.data_ptr()), stream, ms))
-        self.launches += 6
+        self.launches += 6 if self.mode == 'rgb' else 7  # one kernel per layer (conv2 and conv3 are not fused here)
         return list(ms)
 
     def forward(self, env, logits=None, action=None):
@@ -227,7 +231,7 @@ class PolicyNetwork(object):
         st = env.stack_view()
         _lib.check(self.lib.ahk_policy_forward_stack(self._h, C.byref(st), C.c_void_p(logits.data_ptr()),
                                                      C.c_void_p(action.data_ptr()), stream))
-        self.launches += 6 if self.mode == 'rgb' else 7
+        self.launches += self._forward_launches
         return logits, action
 
     def close(self):

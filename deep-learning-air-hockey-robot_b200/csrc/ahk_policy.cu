@@ -1156,6 +1156,12 @@ __global__ void __launch_bounds__(c1t::cta_threads(kGroups), 1) conv1t_kernel(Ar
             const uint32_t buf = t & 1u;
             mbar_wait_sleep(&s_tfull[buf], (t >> 1) & 1);
             tc_fence_after();
+#ifdef AHK_C1T_NO_EPI // timing experiment (tools/build_variant.sh): the pipeline without the epilogue's TMEM loads, exchange and stores
+            tc_fence_before();
+            mbar_arrive(&s_tempty[buf]);
+            (void)sample; (void)y0; (void)ny; (void)row_ok; (void)q; (void)il;
+            continue;
+#endif
 #pragma unroll 1
             for (int ph = 0; ph < 3; ++ph) {
                 const uint32_t taddr = tmem + buf * kBufCols + ph * kN + (static_cast<uint32_t>(q4 * 32) << 16);

@@ -1860,7 +1860,9 @@ cudaError_t launch_tm(const Args &a, const CUtensorMap &tm_in, int sms, cudaStre
 //   pair is converted while the next pair's conv2 accumulators wait in their slots, and conv2's epilogue of pair t + 1 starts as
 //   soon as the converters have read pair t's act2.
 namespace c23 {
-constexpr int kCta = 256 + 64 + 128; // 8 converter warps (2 groups x 4 lane quarters), MMA warp, loader warp, 4 epilogue warps
+// 8 converter warps (2 groups x 4 lane quarters), MMA warp, loader warp, kEpi sets of 4 epilogue warps.  Two sets (default): with one the
+// epilogue warps were busy 77 % of the kernel and the converters waited 16 % of it for act2 (ncu role breakdown of call s5t)
+constexpr int cta_threads(int epi) { return 256 + 64 + epi * 128; }
 constexpr int kRaw = 3, kRawPitch = 27008, kAct2Ring = 3, kAct2Sample = 23552, kAct2Bytes = kAct2Ring * kAct2Sample; // 361 pixels x 64 B = 23 104, rounded up to a multiple of 1024
 constexpr int kW2Bytes = 128 * 32 * 2, kW3Bytes = 512 * 64 * 2;
 constexpr int kSmem = 1024 + kAct2Bytes + kW3Bytes + kW2Bytes + kRaw * kRawPitch;
@@ -1868,7 +1870,8 @@ constexpr int kD2 = 0, kD3 = 192, kA = 320, kACols = 64, kAStages = 3;
 static_assert(kSmem <= 227 * 1024 && kA + kAStages * kACols == 512, "budgets");
 } // namespace c23
 
-__global__ void __launch_bounds__(c23::kCta, 1) conv23_kernel(Args a, const uint4 *__restrict__ w3, const float *__restrict__ b3, __nv_bfloat16 *__restrict__ out3)
+template <int kEpi>
+__global__ void __launch_bounds__(c23::cta_threads(kEpi), 1) conv23_kernel(Args a, const uint4 *__restrict__ w3, const float *__restrict__ b3, __nv_bfloat16 *__restrict__ out3)
 {
     using namespace c23;
     extern __shared__ __align__(128) uint8_t smem_raw[];
@@ -1884,7 +1887,7 @@ __global__ void __launch_bounds__(c23::kCta, 1) conv23_kernel(Args a, const uint
     const int my_items = static_cast<int>(blockIdx.x) < items ? (items - 1 - static_cast<int>(blockIdx.x)) / static_cast<int>(gridDim.x) + 1 : 0;
     if (tid == 0) {
         mbar_init(&s_wfull, 1);
-        for (int i = 0; i < kAct2Ring; ++i) { mbar_init(&s_a2full[i], 128); mbar_init(&s_a2empty[i], 8); }
+        for (int i = 0; i < kAct2Ring; ++i) { mbar_init(&s_a2full[i], 128 * kEpi); mbar_init(&s_a2empty[i], 8); }
         for (int i = 0; i < kRaw; ++i) { mbar_init(&s_rfull[i], 1); mbar_init(&s_rempty[i], 8); }
         for (int i = 0; i < kAStages; ++i) { mbar_init(&s_afull[i], 4); mbar_init(&s_aempty[i], 1); }
         for (int i = 0; i < 6; ++i) { mbar_init(&s_t2full[i], 1); mbar_init(&s_t2empty[i], 128); }
@@ -2042,13 +2045,19 @@ __global__ void __launch_bounds__(c23::kCta, 1) conv23_kernel(Args a, const uint
         }
     } else {
         // ---------------------------------------------------------------- epilogues: thread = TMEM lane = output pixel of a tile
-        const int q4 = warp & 3, r = q4 * 32 + lane;
+        // set e of kEpi takes the conv2 tile slots with slot % kEpi == e and the conv3 accumulators of the pairs with t % kEpi == e
+        const int q4 = warp & 3, r = q4 * 32 + lane, set = (warp - 10) >> 2;
         const uint32_t lane_addr = tmem + (static_cast<uint32_t>(q4 * 32) << 16);
         auto epilogue2 = [&](int t) { // conv2 accumulators of pair t -> bias, ReLU, bf16 -> act2 in shared memory (swizzled rows of two pixels)
 #pragma unroll 1
             for (int slot = 0; slot < 6; ++slot) {
+                if (slot % kEpi != set) continue;
                 const uint32_t u = 2u * static_cast<uint32_t>(t) + (slot >= 3 ? 1u : 0u), ring = u % kAct2Ring; // sample and its act2 ring slot
-                if (slot % 3 == 0 && u >= static_cast<uint32_t>(kAct2Ring)) mbar_wait_sleep(&s_a2empty[ring], ((u / kAct2Ring) - 1u) & 1u);
+                const int s0 = slot >= 3 ? 3 : 0; // this set's first and last tile of the sample
+                const int first_mine = s0 + ((set - s0 % kEpi) % kEpi + kEpi) % kEpi;
+                int last_mine = first_mine;
+                while (last_mine + kEpi < s0 + 3) last_mine += kEpi;
+                if (slot == first_mine && u >= static_cast<uint32_t>(kAct2Ring)) mbar_wait_sleep(&s_a2empty[ring], ((u / kAct2Ring) - 1u) & 1u);
                 mbar_wait_sleep(&s_t2full[slot], t & 1);
                 tc_fence_after();
                 uint32_t v[32];
@@ -2075,7 +2084,7 @@ __global__ void __launch_bounds__(c23::kCta, 1) conv23_kernel(Args a, const uint
                         *reinterpret_cast<uint4 *>(s_act2 + at) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
                     }
                 }
-                if (slot % 3 == 2) mbar_arrive(&s_a2full[ring]); // release: this thread's rows of the sample are in shared memory
+                if (slot == last_mine) mbar_arrive(&s_a2full[ring]); // release: this thread's rows of the sample are in shared memory
             }
         };
         auto epilogue3 = [&](int t) { // conv3 accumulators of pair t -> act3 in global memory
@@ -2109,7 +2118,7 @@ __global__ void __launch_bounds__(c23::kCta, 1) conv23_kernel(Args a, const uint
         if (my_items > 0) epilogue2(0);
         for (int t = 0; t < my_items; ++t) {
             if (t + 1 < my_items) epilogue2(t + 1);
-            epilogue3(t);
+            if (t % kEpi == set) epilogue3(t);
         }
     }
     tc_fence_before();
@@ -2119,12 +2128,18 @@ __global__ void __launch_bounds__(c23::kCta, 1) conv23_kernel(Args a, const uint
 }
 
 // a: conv2's arguments (in = act1, weights, bias); w3 / b3 / out3: conv3's packed weights, bias and act3
-cudaError_t launch_conv23(const Args &a, const uint4 *w3, const float *b3, __nv_bfloat16 *out3, int sms, cudaStream_t s, bool pdl)
+template <int kEpi>
+cudaError_t launch_conv23_as(const Args &a, const uint4 *w3, const float *b3, __nv_bfloat16 *out3, int sms, cudaStream_t s, bool pdl)
 {
-    cudaError_t e = cudaFuncSetAttribute(conv23_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, c23::kSmem);
+    cudaError_t e = cudaFuncSetAttribute(conv23_kernel<kEpi>, cudaFuncAttributeMaxDynamicSharedMemorySize, c23::kSmem);
     if (e != cudaSuccess) return e;
     const int items = (a.n + 1) / 2;
-    return launch_kernel(conv23_kernel, dim3(items < sms ? items : sms), dim3(c23::kCta), c23::kSmem, s, pdl, a, w3, b3, out3);
+    return launch_kernel(conv23_kernel<kEpi>, dim3(items < sms ? items : sms), dim3(c23::cta_threads(kEpi)), c23::kSmem, s, pdl, a, w3, b3, out3);
+}
+
+cudaError_t launch_conv23(const Args &a, const uint4 *w3, const float *b3, __nv_bfloat16 *out3, int sms, cudaStream_t s, bool pdl, int epi = 2)
+{
+    return epi == 1 ? launch_conv23_as<1>(a, w3, b3, out3, sms, s, pdl) : launch_conv23_as<2>(a, w3, b3, out3, sms, s, pdl);
 }
 
 // ------------------------------------------------------------------------------------------------ gray-diff input
@@ -2460,7 +2475,8 @@ struct ahk_policy {
     bool conv2_no_swap = false;
     int conv1_groups = 4; // converter groups of conv1t_kernel (forward of 8192 samples 0.4543 / 0.4507 / 0.4492 ms with 2 / 3 / 4, same box); A/B switch AHK_CONV1_GROUPS=2|3|4
     // conv2 -> conv3 in one kernel, act2 in shared memory (conv23_kernel): bit-identical to the two kernels, forward of 8192 samples
-    // 0.4549 -> 0.4475 ms, rollout step 0.594 -> 0.565 ms (same box), 0.33 GB less HBM traffic; inference forwards only.  A/B switch AHK_FUSE23=0
+    // 0.4542 -> 0.4370 ms, rollout step 0.586 -> 0.556 ms (same box), 0.33 GB less HBM traffic; inference forwards only.  A/B switch AHK_FUSE23=0
+    int fuse23_epi = 2; // epilogue warp sets of conv23_kernel; A/B switch AHK_FUSE23_EPI=1|2
     bool fuse23 = true, fuse23_profiled = false; // AHK_FUSE23=2: also in the profiled forward (its 'conv2' time is then the fused kernel's, 'conv3' ~ 0)
     bool convtm_two_raw = false; // A/B switch AHK_CONVTM_RAW=2: conv_tm_kernel<conv2> with two raw item buffers instead of 4
     uint16_t *w1p = nullptr; // conv1 in phase-separated form (conv1p_kernel, the default), fp16, unscaled
@@ -2641,6 +2657,7 @@ int ahk_policy_create(int device, int max_batch, const ahk_policy_weights *w, ah
     if (const char *sw = getenv("AHK_CONV2_SWAP")) p->conv2_no_swap = strcmp(sw, "0") == 0;
     if (const char *sw = getenv("AHK_CONV1_GROUPS")) p->conv1_groups = atoi(sw);
     if (const char *sw = getenv("AHK_CONVTM_RAW")) p->convtm_two_raw = strcmp(sw, "2") == 0;
+    if (const char *sw = getenv("AHK_FUSE23_EPI")) p->fuse23_epi = atoi(sw);
     if (const char *sw = getenv("AHK_FUSE23")) { p->fuse23 = strcmp(sw, "0") != 0; p->fuse23_profiled = strcmp(sw, "2") == 0; }
     if (const char *sw = getenv("AHK_CONV1")) { p->conv1_n144 = strcmp(sw, "n144") == 0; p->conv1_smem = strcmp(sw, "smem") == 0; p->conv1_normal = strcmp(sw, "normal") == 0; }
     int rc = load_rgb_weights(p, w);
@@ -2864,7 +2881,7 @@ static int rgb_layer(ahk_policy *p, Args a, int layer, float *logits, uint8_t *a
         // four times over L2 -> SM (1.2 GB per 8192 samples: 0.21-0.25 ms against 0.155; AHK_GEMM=tma2 runs it for the record)
         a.in = p->act1; a.weights = reinterpret_cast<const uint4 *>(p->w[1]); a.bias = p->b[1]; a.out = p->act2; a.m_total = n * kP2;
         g.tiles_m = n * 4; g.blocks_n = 1; g.k_chunks = 4; g.n_valid = 32; g.bias = p->b[1]; g.out_bf16 = p->act2; g.out_pitch = 32;
-        if (fuse23) POL_CUDA(launch_conv23(a, reinterpret_cast<const uint4 *>(p->w[2]), p->b[2], p->act3, p->sms, s, pdl));
+        if (fuse23) POL_CUDA(launch_conv23(a, reinterpret_cast<const uint4 *>(p->w[2]), p->b[2], p->act3, p->sms, s, pdl, p->fuse23_epi));
         else if (p->conv_tm && p->conv2_parity && !p->legacy_conv && !(p->tma_gemm && p->tma_conv2)) POL_CUDA(launch_tm<kConv2>(a, p->tm_rows2, p->sms, s, pdl, p->convtm_two_raw)); // (conv2 takes its sample by a plain bulk copy: the map is unused)
         else if (p->conv2_parity && !p->legacy_conv && !(p->tma_gemm && p->tma_conv2)) {
             a.weights = reinterpret_cast<const uint4 *>(p->w2p);
